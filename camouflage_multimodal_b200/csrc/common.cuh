@@ -1,0 +1,76 @@
+// Shared host/device helpers for the cm_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "cm_b200.h"
+
+namespace cm {
+
+void set_error(const char* fmt, ...);
+int check_device();   // CM_OK or CM_ERR_DEVICE (cached per device)
+int num_sms();
+int post_launch(const char* what);   // cudaPeekAtLastError -> CM_ERR_LAUNCH + message
+
+static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+#define CM_REQUIRE(cond, ...)                 \
+    do {                                      \
+        if (!(cond)) {                        \
+            cm::set_error(__VA_ARGS__);       \
+            return CM_ERR_ARG;                \
+        }                                     \
+    } while (0)
+
+#define CM_DEVICE_OR_RETURN()                       \
+    do {                                            \
+        int _rc = cm::check_device();               \
+        if (_rc != CM_OK) return _rc;               \
+    } while (0)
+
+// Carves a caller-provided workspace into aligned slices.
+struct Carver {
+    char* base;
+    size_t off = 0;
+    explicit Carver(void* p) : base(reinterpret_cast<char*>(p)) {}
+    template <typename T>
+    T* take(size_t n) {
+        off = align_up(off, 256);
+        T* r = reinterpret_cast<T*>(base + off);
+        off += n * sizeof(T);
+        return r;
+    }
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(0xffffffffu, v); }
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+// inclusive scan of an int over the warp
+__device__ __forceinline__ int warp_scan_incl(int v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+#endif
+
+}  // namespace cm

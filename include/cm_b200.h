@@ -1,0 +1,203 @@
+/*
+ * cm_b200.h -- C ABI of the B200-native (sm_100a) region-graph hot path.
+ *
+ * The reference (rajan-dubey8/camouflage-multimodal) is pure Python and has no FFI of its own
+ * (SURVEY.md F2); these entry points are what a binding for the path would call.  Each one names the
+ * reference code it replaces (paths relative to the reference tree).  Conventions:
+ *   - every pointer is a DEVICE pointer on the current CUDA device unless its name ends in _host;
+ *   - outputs are caller-allocated at the stated capacity; nothing is allocated or freed here;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls are
+ *     asynchronous with respect to the host and do not synchronise;
+ *   - return value 0 = launched; negative = argument / launch error, text in cm_last_error();
+ *   - data-dependent overflows (label >= label_cap, more nodes/edges than the output capacity) are
+ *     reported through the device-side `status` word (bit mask CM_STATUS_*), never by writing out of
+ *     bounds;
+ *   - ragged batches: image b owns nodes node_ptr[b] .. node_ptr[b+1]-1 (global node ids) and directed
+ *     edges edge_ptr[b] .. edge_ptr[b+1]-1.
+ * There is no CPU fallback: every entry point fails with CM_ERR_DEVICE on a device that is not
+ * compute capability 10.x.
+ */
+#ifndef CM_B200_H
+#define CM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CM_OK 0
+#define CM_ERR_ARG (-1)
+#define CM_ERR_DEVICE (-2)
+#define CM_ERR_LAUNCH (-3)
+#define CM_ERR_WORKSPACE (-4)
+
+#define CM_STATUS_LABEL_OVERFLOW 1u /* a label >= label_cap was seen (ignored like a negative label) */
+#define CM_STATUS_NODE_OVERFLOW 2u  /* more nodes than node_cap */
+#define CM_STATUS_EDGE_OVERFLOW 4u  /* more directed edges than edge_cap */
+
+#define CM_NODE_FEATURES 15 /* extract_rg_embeddings.py:195-206 */
+
+const char* cm_last_error(void);
+int cm_abi_version(void);
+/* 0 when the current device is sm_100 (B200); CM_ERR_DEVICE otherwise. */
+int cm_device_check(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * A1 + A2: region adjacency + label compaction.
+ * Replaces skimage.graph.rag_mean_color(...).edges() (models/region_graph/extract_rg_embeddings.py:216,
+ * 220) and the region_id_map bookkeeping + edge remap (:148-149, 155-161, 210-211, 221-225).
+ *
+ * labels      [B,H,W] int32, any values; labels < 0 or >= label_cap are never nodes.
+ * id_of_label [B,label_cap] int32 out: node id LOCAL to the image (0..N_b-1, ascending label order) or -1.
+ * node_ptr    [B+1] int32 out, edge_ptr [B+1] int32 out (exclusive prefix sums over images).
+ * node_label  [node_cap] int32 out: label of every global node.
+ * node_bbox   [node_cap,4] int32 out: x0, y0, x1, y1 (inclusive) of the region.
+ * batch_vec   [node_cap] int64 out or NULL: image index of every node (PyG `batch`).
+ * csr_row_ptr [node_cap+1] int32 out: CSR over GLOBAL node ids; row i lists the neighbours of i ascending.
+ * csr_col     [edge_cap] int32 out: global node id of the neighbour.
+ * edge_index  [2,edge_cap] int64 out or NULL (row stride = edge_cap): directed edges (i -> j), both
+ *             directions of every RAG edge, sorted lexicographically by (row 0, row 1) -- the canonical
+ *             order on which parity with the reference's networkx order is defined.  Node ids are LOCAL
+ *             to the image when local_ids != 0 (one Data per image), GLOBAL otherwise (Batch.from_data_list,
+ *             train.py:231).
+ * workspace   cm_rag_workspace_bytes(B, label_cap) bytes of scratch (zeroed by the call).
+ * ------------------------------------------------------------------------------------------------ */
+size_t cm_rag_workspace_bytes(int batch, int label_cap);
+int cm_rag_build(const int32_t* labels, int batch, int h, int w, int label_cap, void* workspace,
+                 size_t workspace_bytes, int32_t* id_of_label, int32_t* node_ptr, int32_t* edge_ptr,
+                 int32_t* node_label, int32_t* node_bbox, int64_t* batch_vec, int32_t* csr_row_ptr,
+                 int32_t* csr_col, int64_t* edge_index, int local_ids, int node_cap, int edge_cap,
+                 uint32_t* status, void* stream);
+
+/* A3: the 15 region features (extract_rg_embeddings.py:154-211).
+ * image [B,H,W,3] float32 in [0,1]; canny [B,H,W] uint8 (non-zero = edge pixel, the output of
+ * skimage.feature.canny(gray, sigma=2), :152); x [node_cap,15] float32 out.
+ * norm_side is the reference's hard-coded 256.0 (:172-174). */
+int cm_node_features(const float* image, const int32_t* labels, const uint8_t* canny, int batch, int h,
+                     int w, const int32_t* node_ptr, const int32_t* node_label, const int32_t* node_bbox,
+                     float norm_side, float* x, int node_cap, void* stream);
+
+/* A4: Gaussian-kernel edge weights (extract_rg_embeddings.py:227-235), one per directed CSR entry,
+ * float32 arithmetic.  n_nodes_dev points at the device-side node count (node_ptr + B). */
+int cm_edge_weights(const float* x, const int32_t* csr_row_ptr, const int32_t* csr_col,
+                    const int32_t* n_nodes_dev, int node_cap, float* edge_w, void* stream);
+
+/* CSR keyed by TARGET node from an arbitrary PyG-style edge_index [2,E] int64 (source row 0, target row 1)
+ * with optional per-edge weights -- what RegionGraphGNN.forward receives (extract_rg_embeddings.py:54-56)
+ * when the graph did not come from cm_rag_build.  Self loops are removed from the CSR and returned in
+ * self_w (last one per node wins, default 1: PyG add_remaining_self_loops).  Row entries keep the order of
+ * the input edges.  workspace: cm_csr_workspace_bytes(n_nodes, n_edges). */
+size_t cm_csr_workspace_bytes(int n_nodes, int n_edges);
+int cm_csr_from_edge_index(const int64_t* edge_index, int64_t row_stride, const float* edge_w, int n_nodes,
+                           int n_edges, void* workspace, size_t workspace_bytes, int32_t* csr_row_ptr,
+                           int32_t* csr_col, float* csr_w, float* self_w, uint32_t* status, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A5-A7: RegionGraphGNN forward (extract_rg_embeddings.py:27-135), eval mode.
+ * The raw parameters are the reference state-dict tensors (PyG names); cm_gnn_fold turns them
+ * into the folded device blob the forward kernels read (BatchNorm folded into the preceding conv, the GAT
+ * linear folded into its attention vectors) -- call it once per weight set.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct cm_gnn_params {
+    int in_channels, hidden, heads, num_classes; /* 15, 128, 4, 2 */
+    const float* conv1_lin_weight;               /* [heads*hidden, in] */
+    const float* conv1_att_src;                  /* [heads*hidden] */
+    const float* conv1_att_dst;                  /* [heads*hidden] */
+    const float* conv1_bias;                     /* [hidden] */
+    const float* conv_lin_weight[3];             /* conv2..4 lin.weight [hidden, hidden] */
+    const float* conv_bias[3];                   /* [hidden] */
+    const float* bn_weight[4];                   /* bn1..4 */
+    const float* bn_bias[4];
+    const float* bn_mean[4];
+    const float* bn_var[4];
+    float bn_eps;
+    const float* fc_shared_weight; /* [hidden, hidden] */
+    const float* fc_shared_bias;
+    const float* head1_weight[3]; /* fc_{mask,instance,edge}_1.weight [hidden/2, hidden] */
+    const float* head1_bias[3];
+    const float* head2_weight[3]; /* [c, hidden/2], c = num_classes, num_classes, 1 */
+    const float* head2_bias[3];
+} cm_gnn_params;
+
+size_t cm_gnn_folded_bytes(const cm_gnn_params* p);
+int cm_gnn_fold(const cm_gnn_params* p, void* folded, size_t folded_bytes, void* stream);
+
+/* Scratch for one forward over at most node_cap nodes. */
+size_t cm_gnn_workspace_bytes(const cm_gnn_params* p, int node_cap);
+/* x [node_cap,15]; CSR by target (csr_w NULL = unweighted GCN, self_w NULL = all ones);
+ * n_nodes_dev NULL => exactly node_cap nodes.  Outputs (any may be NULL): node_emb [node_cap,hidden],
+ * mask_out [node_cap,num_classes], instance_out [node_cap,num_classes], edge_out [node_cap,1],
+ * mask_prob [node_cap] = softmax(mask_out,1)[:,1] (models/region_graph/test.py:238),
+ * graph_emb [n_graphs,hidden] = global_mean_pool over node_ptr segments (:129-133). */
+int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const float* x, const int32_t* csr_row_ptr,
+                   const int32_t* csr_col, const float* csr_w, const float* self_w,
+                   const int32_t* n_nodes_dev, int node_cap, const int32_t* node_ptr, int n_graphs,
+                   void* workspace, size_t workspace_bytes, float* node_emb, float* mask_out,
+                   float* instance_out, float* edge_out, float* mask_prob, float* graph_emb, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A10-A12: CrossAttentionFusion / LateFusion + the four detector heads
+ * (models/multimodal/fusion_model.py:16-246), eval mode.  Raw parameters = reference state dict.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct cm_fusion_params {
+    int rg_dim, kg_dim, hidden, heads, num_classes;
+    int fusion_type; /* 0 = cross_attention, 1 = late */
+    /* cross attention (NULL weight = nn.Identity for the two projections, fusion_model.py:29-30) */
+    const float *rg_proj_w, *rg_proj_b, *kg_proj_w, *kg_proj_b;
+    const float *r2k_in_w, *r2k_in_b, *r2k_out_w, *r2k_out_b; /* cross_attn_rg2kg */
+    const float *k2r_in_w, *k2r_in_b, *k2r_out_w, *k2r_out_b; /* cross_attn_kg2rg */
+    const float *ln_rg_w, *ln_rg_b, *ln_kg_w, *ln_kg_b;
+    const float *ffn_rg_w1, *ffn_rg_b1, *ffn_rg_w2, *ffn_rg_b2;
+    const float *ffn_kg_w1, *ffn_kg_b1, *ffn_kg_w2, *ffn_kg_b2;
+    const float *fl_w1, *fl_b1, *fl_w2, *fl_b2; /* fusion_layer.0 / .3 */
+    /* late fusion: fusion.fusion.{0,3,6} */
+    const float *late_w[3], *late_b[3];
+    /* heads: mask, instance, edge, score; layer .0 [final/2, final], layer .3 [c, final/2] */
+    const float *head_w1[4], *head_b1[4], *head_w2[4], *head_b2[4];
+} cm_fusion_params;
+
+size_t cm_fusion_workspace_bytes(const cm_fusion_params* p, int n_graphs, int node_cap, int n_kg);
+/* rg [node_cap, rg_dim] ragged rows (node_ptr [n_graphs+1]); kg [kg_graphs, n_kg, kg_dim] with kg_graphs
+ * either 1 (the knowledge-graph rows are shared by every image -- broadcast once) or n_graphs.
+ * Outputs: fused [n_graphs, final]; mask/instance [n_graphs,num_classes]; edge/score [n_graphs,1];
+ * attn_rg2kg [node_cap, n_kg] and attn_kg2rg (image b's block [n_kg, N_b] at offset n_kg*node_ptr[b])
+ * are written only when non-NULL (MultimodalCamouflageDetector.forward(return_attention=...), :243-246). */
+int cm_fusion_forward(const cm_fusion_params* p, const float* rg, const int32_t* node_ptr, int n_graphs,
+                      int node_cap, const float* kg, int kg_graphs, int n_kg, void* workspace,
+                      size_t workspace_bytes, float* fused, float* mask_out, float* instance_out,
+                      float* edge_out, float* score_out, float* attn_rg2kg, float* attn_kg2rg,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A8 + A9 (+A13): pixel-mask paint and the metric reductions.
+ * Paint: models/region_graph/test.py:241-244 -- pixel with label l gets prob[l] when 0 <= l < N_b (the
+ * reference indexes by RAW label); with id_of_label != NULL it gets prob[id_of_label[l]] instead
+ * (label_offset_fix).  Metrics: utils/metrics.py:9-76 per image with strict `>` thresholds.
+ * gt [B,H,W] uint8 (value/255.0 = the PIL 'L' convention, test.py:275).
+ * counts [B,4] int64 out: tp, sum_pred, sum_gt, n_equal; abs_err [B] float64 out: sum |pred - gt|.
+ * pred_mask [B,H,W] float32 out or NULL.
+ * ------------------------------------------------------------------------------------------------ */
+int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int batch, int h, int w,
+                     const float* mask_prob, const int32_t* node_ptr, const int32_t* id_of_label,
+                     int label_cap, float threshold, float* pred_mask, int64_t* counts, double* abs_err,
+                     void* stream);
+/* Same reductions for a caller-supplied float prediction and float ground truth (the literal signature of
+ * utils/metrics.py:evaluate_segmentation: two arrays, one threshold). */
+int cm_metrics_dense(const float* pred, const float* gt, int batch, int64_t pixels, float threshold,
+                     int64_t* counts, double* abs_err, void* stream);
+/* per_image [B,7] float64 out: iou, dice, precision, recall, f1, mae, accuracy (utils/metrics.py:57-76);
+ * partial [15] float64 out: n, sum m_k (7), sum m_k^2 (7) -- the vector that is all-reduced across ranks
+ * and from which batch_evaluate's mean / population std follow (utils/metrics.py:78-92). */
+int cm_metrics_finalize(const int64_t* counts, const double* abs_err, int batch, int64_t pixels,
+                        double* per_image, double* partial, void* stream);
+/* A13: image-level confusion counts tp, fp, fn, tn (models/multimodal/train_multimodal.py:197-220) from
+ * predicted class = argmax(mask_out) and true class ids.  counts4 [4] int64 accumulated (caller zeroes). */
+int cm_class_confusion(const float* mask_out, const int64_t* true_cls, int n, int num_classes,
+                       int64_t* counts4, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CM_B200_H */
