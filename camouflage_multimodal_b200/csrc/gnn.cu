@@ -1,0 +1,318 @@
+// A5-A7: RegionGraphGNN forward (models/region_graph/extract_rg_embeddings.py:27-135), eval mode.
+//
+// Message passing is a warp-per-target-node gather over CSR rows (rows = incoming edges).  Two algebraic
+// rewrites keep the traffic at the compulsory level:
+//   * GATConv(15 -> 4x128, concat=False): the attention logits need only x_j . (W_h^T att_h), and
+//     sum_j alpha_ij (W_h x_j) = W_h (sum_j alpha_ij x_j), so the layer aggregates in the 15-d input space
+//     (z [M, 4*15]) and applies one [60 -> 128] linear; the [M, 512] tensor PyG materialises never exists.
+//   * GCNConv: A_hat (X W^T) = (A_hat X) W^T, so the gather runs on the layer input and the linear (with
+//     BatchNorm folded into its weight and bias) follows as a dense layer.
+// PyG semantics restated: self loops removed then one added per node (GAT); add_remaining_self_loops with
+// weight 1, symmetric normalisation by the weighted in-degree (GCN); softmax denominator + 1e-16.
+#include "linear.cuh"
+
+namespace cm {
+
+struct GnnFolded {   // float offsets into the folded blob
+    size_t u_src, u_dst, wcat, bias1, convw[3], convb[3], head1w, head1b, total;
+};
+
+static GnnFolded gnn_layout(const cm_gnn_params* p) {
+    GnnFolded f;
+    size_t o = 0;
+    auto take = [&](size_t n) {
+        size_t r = o;
+        o += (n + 63) / 64 * 64;
+        return r;
+    };
+    const size_t H = p->hidden, C = p->in_channels, hd = p->heads;
+    f.u_src = take(hd * C);
+    f.u_dst = take(hd * C);
+    f.wcat = take(H * hd * C);
+    f.bias1 = take(H);
+    for (int k = 0; k < 3; ++k) {
+        f.convw[k] = take(H * H);
+        f.convb[k] = take(H);
+    }
+    f.head1w = take(3 * (H / 2) * H);
+    f.head1b = take(3 * (H / 2));
+    f.total = o;
+    return f;
+}
+
+__global__ void gnn_fold_kernel(cm_gnn_params p, GnnFolded f, float* __restrict__ blob) {
+    const int H = p.hidden, C = p.in_channels, hd = p.heads, KC = hd * C;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    // u_src / u_dst [heads, C]
+    for (long long i = tid; i < (long long)hd * C; i += stride) {
+        const int h = (int)(i / C), c = (int)(i % C);
+        float s = 0.f, d = 0.f;
+        for (int o = 0; o < H; ++o) {
+            const float w = p.conv1_lin_weight[(size_t)(h * H + o) * C + c];
+            s = fmaf(w, p.conv1_att_src[h * H + o], s);
+            d = fmaf(w, p.conv1_att_dst[h * H + o], d);
+        }
+        blob[f.u_src + i] = s;
+        blob[f.u_dst + i] = d;
+    }
+    // wcat [H, heads*C] = W[h*H+o, c] / heads * bn1 scale ; bias1
+    for (long long i = tid; i < (long long)H * KC; i += stride) {
+        const int o = (int)(i / KC), hc = (int)(i % KC), h = hc / C, c = hc % C;
+        const float s = p.bn_weight[0][o] / sqrtf(p.bn_var[0][o] + p.bn_eps);
+        blob[f.wcat + i] = p.conv1_lin_weight[(size_t)(h * H + o) * C + c] * (s / (float)hd);
+    }
+    for (long long o = tid; o < H; o += stride) {
+        const float s = p.bn_weight[0][o] / sqrtf(p.bn_var[0][o] + p.bn_eps);
+        blob[f.bias1 + o] = (p.conv1_bias[o] - p.bn_mean[0][o]) * s + p.bn_bias[0][o];
+    }
+    for (int k = 0; k < 3; ++k) {
+        const float *bw = p.bn_weight[k + 1], *bb = p.bn_bias[k + 1], *bm = p.bn_mean[k + 1], *bv = p.bn_var[k + 1];
+        for (long long i = tid; i < (long long)H * H; i += stride) {
+            const int o = (int)(i / H);
+            blob[f.convw[k] + i] = p.conv_lin_weight[k][i] * (bw[o] / sqrtf(bv[o] + p.bn_eps));
+        }
+        for (long long o = tid; o < H; o += stride) {
+            const float s = bw[o] / sqrtf(bv[o] + p.bn_eps);
+            blob[f.convb[k] + o] = (p.conv_bias[k][o] - bm[o]) * s + bb[o];
+        }
+    }
+    const int H2 = H / 2;
+    for (long long i = tid; i < 3LL * H2 * H; i += stride) {
+        const int t = (int)(i / ((long long)H2 * H));
+        blob[f.head1w + i] = p.head1_weight[t][i - (long long)t * H2 * H];
+    }
+    for (long long i = tid; i < 3LL * H2; i += stride) blob[f.head1b + i] = p.head1_bias[(int)(i / H2)][i % H2];
+}
+
+// a_src / a_dst [M, heads]; one thread per (node, head)
+__global__ void gat_logits_kernel(const float* __restrict__ x, int C, int heads, const float* __restrict__ u_src,
+                                  const float* __restrict__ u_dst, const int* n_dev, int cap, float* __restrict__ a_src,
+                                  float* __restrict__ a_dst) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = n_dev ? min(*n_dev, cap) : cap;
+    if (i >= n * heads) return;
+    const int g = i / heads, h = i - g * heads;
+    const float* xr = x + (size_t)g * C;
+    float s = 0.f, d = 0.f;
+    for (int c = 0; c < C; ++c) {
+        s = fmaf(xr[c], u_src[h * C + c], s);
+        d = fmaf(xr[c], u_dst[h * C + c], d);
+    }
+    a_src[i] = s;
+    a_dst[i] = d;
+}
+
+// One warp per target node; lane c < C owns input feature c for all heads (heads <= 8, C <= 32).
+template <int HEADS>
+__global__ void __launch_bounds__(256) gat_aggregate_kernel(const float* __restrict__ x, int C, const int* __restrict__ row_ptr,
+                                                            const int* __restrict__ col, const float* __restrict__ a_src,
+                                                            const float* __restrict__ a_dst, const int* n_dev, int cap,
+                                                            float* __restrict__ z) {
+    const int g = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int n = n_dev ? min(*n_dev, cap) : cap;
+    if (g >= n) return;
+    const int e0 = row_ptr[g], e1 = row_ptr[g + 1];
+    float ad[HEADS], mx[HEADS], den[HEADS], acc[HEADS];
+#pragma unroll
+    for (int h = 0; h < HEADS; ++h) {
+        ad[h] = a_dst[(size_t)g * HEADS + h];
+        float l = a_src[(size_t)g * HEADS + h] + ad[h];   // the added self loop
+        mx[h] = l > 0.f ? l : 0.2f * l;
+        den[h] = 0.f;
+        acc[h] = 0.f;
+    }
+    for (int e = e0; e < e1; ++e) {
+        const int j = col[e];
+        if (j == g) continue;   // PyG removes existing self loops first
+#pragma unroll
+        for (int h = 0; h < HEADS; ++h) {
+            float l = a_src[(size_t)j * HEADS + h] + ad[h];
+            l = l > 0.f ? l : 0.2f * l;
+            mx[h] = fmaxf(mx[h], l);
+        }
+    }
+    for (int e = e0; e <= e1; ++e) {   // e == e1 is the self loop (PyG appends it last)
+        const int j = e < e1 ? col[e] : g;
+        if (e < e1 && j == g) continue;
+        const float xv = lane < C ? x[(size_t)j * C + lane] : 0.f;
+#pragma unroll
+        for (int h = 0; h < HEADS; ++h) {
+            float l = a_src[(size_t)j * HEADS + h] + ad[h];
+            l = l > 0.f ? l : 0.2f * l;
+            const float w = expf(l - mx[h]);
+            den[h] += w;
+            acc[h] = fmaf(w, xv, acc[h]);
+        }
+    }
+    if (lane < C) {
+#pragma unroll
+        for (int h = 0; h < HEADS; ++h) z[(size_t)g * (HEADS * C) + h * C + lane] = acc[h] / (den[h] + 1e-16f);
+    }
+}
+
+// dis[i] = (sum of incoming weights + self weight)^-1/2, inf -> 0
+__global__ void gcn_norm_kernel(const int* __restrict__ row_ptr, const int* __restrict__ col, const float* __restrict__ w,
+                                const float* __restrict__ self_w, const int* n_dev, int cap, float* __restrict__ dis) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = n_dev ? min(*n_dev, cap) : cap;
+    if (i >= n) return;
+    float d = 0.f;
+    for (int e = row_ptr[i]; e < row_ptr[i + 1]; ++e)
+        if (col[e] != i) d += w ? w[e] : 1.0f;
+    d += self_w ? self_w[i] : 1.0f;
+    const float r = 1.0f / sqrtf(d);
+    dis[i] = isinf(r) ? 0.f : r;
+}
+
+// One warp per target node, lane owns 4 consecutive channels per 128-channel group.
+__global__ void __launch_bounds__(256) gcn_aggregate_kernel(const float* __restrict__ x, int H, const int* __restrict__ row_ptr,
+                                                            const int* __restrict__ col, const float* __restrict__ w,
+                                                            const float* __restrict__ self_w, const float* __restrict__ dis,
+                                                            const int* n_dev, int cap, float* __restrict__ out) {
+    const int g = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int n = n_dev ? min(*n_dev, cap) : cap;
+    if (g >= n) return;
+    const int e0 = row_ptr[g], e1 = row_ptr[g + 1];
+    const float di = dis[g];
+    for (int c0 = lane * 4; c0 < H; c0 += 128) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int e = e0; e < e1; ++e) {
+            const int j = col[e];
+            if (j == g) continue;
+            const float s = dis[j] * (w ? w[e] : 1.0f) * di;
+            const float4 v = *reinterpret_cast<const float4*>(x + (size_t)j * H + c0);
+            acc.x = fmaf(s, v.x, acc.x);
+            acc.y = fmaf(s, v.y, acc.y);
+            acc.z = fmaf(s, v.z, acc.z);
+            acc.w = fmaf(s, v.w, acc.w);
+        }
+        const float s = di * (self_w ? self_w[g] : 1.0f) * di;
+        const float4 v = *reinterpret_cast<const float4*>(x + (size_t)g * H + c0);
+        acc.x = fmaf(s, v.x, acc.x);
+        acc.y = fmaf(s, v.y, acc.y);
+        acc.z = fmaf(s, v.z, acc.z);
+        acc.w = fmaf(s, v.w, acc.w);
+        *reinterpret_cast<float4*>(out + (size_t)g * H + c0) = acc;
+    }
+}
+
+struct GnnWs {
+    float *a_src, *a_dst, *z, *dis, *buf0, *buf1, *hid, *emb;
+    size_t total;
+};
+static GnnWs carve_gnn(void* ws, const cm_gnn_params* p, int cap) {
+    Carver c(ws);
+    GnnWs r;
+    const size_t n = cap, H = p->hidden;
+    r.a_src = c.take<float>(n * p->heads);
+    r.a_dst = c.take<float>(n * p->heads);
+    r.z = c.take<float>(n * p->heads * p->in_channels);
+    r.dis = c.take<float>(n);
+    r.buf0 = c.take<float>(n * H);
+    r.buf1 = c.take<float>(n * H);
+    r.hid = c.take<float>(n * 3 * (H / 2));
+    r.emb = c.take<float>(n * H);
+    r.total = align_up(c.off, 256);
+    return r;
+}
+
+static int check_params(const cm_gnn_params* p) {
+    CM_REQUIRE(p, "cm_gnn: NULL params");
+    CM_REQUIRE(p->in_channels > 0 && p->in_channels <= 32, "cm_gnn: in_channels=%d outside 1..32", p->in_channels);
+    CM_REQUIRE(p->heads == 4, "cm_gnn: heads=%d (the reference fixes heads=4, extract_rg_embeddings.py:31)", p->heads);
+    CM_REQUIRE(p->hidden > 0 && p->hidden % 128 == 0 && p->hidden <= 1024, "cm_gnn: hidden=%d must be a multiple of 128", p->hidden);
+    CM_REQUIRE(p->num_classes >= 1 && p->num_classes <= 32, "cm_gnn: num_classes=%d", p->num_classes);
+    return CM_OK;
+}
+
+}  // namespace cm
+
+extern "C" size_t cm_gnn_folded_bytes(const cm_gnn_params* p) {
+    if (!p || cm::check_params(p) != CM_OK) return 0;
+    return cm::gnn_layout(p).total * sizeof(float);
+}
+
+extern "C" int cm_gnn_fold(const cm_gnn_params* p, void* folded, size_t folded_bytes, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    int rc = check_params(p);
+    if (rc != CM_OK) return rc;
+    CM_REQUIRE(folded, "cm_gnn_fold: NULL output");
+    GnnFolded f = gnn_layout(p);
+    CM_REQUIRE(folded_bytes >= f.total * sizeof(float), "cm_gnn_fold: blob %zu < %zu bytes", folded_bytes, f.total * sizeof(float));
+    gnn_fold_kernel<<<64, 256, 0, as_stream(stream)>>>(*p, f, reinterpret_cast<float*>(folded));
+    return post_launch("cm_gnn_fold");
+}
+
+extern "C" size_t cm_gnn_workspace_bytes(const cm_gnn_params* p, int node_cap) {
+    if (!p || node_cap <= 0 || cm::check_params(p) != CM_OK) return 0;
+    return cm::carve_gnn(nullptr, p, node_cap).total;
+}
+
+extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const float* x, const int32_t* csr_row_ptr,
+                              const int32_t* csr_col, const float* csr_w, const float* self_w, const int32_t* n_nodes_dev,
+                              int node_cap, const int32_t* node_ptr, int n_graphs, void* workspace, size_t workspace_bytes,
+                              float* node_emb, float* mask_out, float* instance_out, float* edge_out, float* mask_prob,
+                              float* graph_emb, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    int rc = check_params(p);
+    if (rc != CM_OK) return rc;
+    CM_REQUIRE(folded && x && csr_row_ptr && workspace, "cm_gnn_forward: NULL pointer");
+    CM_REQUIRE(node_cap > 0, "cm_gnn_forward: node_cap must be positive");
+    CM_REQUIRE(!graph_emb || (node_ptr && n_graphs > 0), "cm_gnn_forward: graph_emb needs node_ptr / n_graphs");
+    CM_REQUIRE(!mask_prob || p->num_classes == 2, "cm_gnn_forward: mask_prob is defined for num_classes == 2");
+    GnnWs ws = carve_gnn(workspace, p, node_cap);
+    if (workspace_bytes < ws.total) {
+        set_error("cm_gnn_forward: workspace %zu < %zu bytes", workspace_bytes, ws.total);
+        return CM_ERR_WORKSPACE;
+    }
+    cudaStream_t st = as_stream(stream);
+    const GnnFolded f = gnn_layout(p);
+    const float* blob = reinterpret_cast<const float*>(folded);
+    const int H = p->hidden, C = p->in_channels, hd = p->heads, M = node_cap;
+    const int warps_grid = ceil_div(M, 8);
+
+    gat_logits_kernel<<<ceil_div((long long)M * hd, 256), 256, 0, st>>>(x, C, hd, blob + f.u_src, blob + f.u_dst, n_nodes_dev, M,
+                                                                       ws.a_src, ws.a_dst);
+    gat_aggregate_kernel<4><<<warps_grid, 256, 0, st>>>(x, C, csr_row_ptr, csr_col, ws.a_src, ws.a_dst, n_nodes_dev, M, ws.z);
+    Linear l;
+    l.m_dev = n_nodes_dev;
+    l.M = M;
+    l.relu = 1;
+    l.A = ws.z; l.lda = hd * C; l.K = hd * C; l.W = blob + f.wcat; l.bias = blob + f.bias1; l.N = H; l.C = ws.buf0; l.ldc = H;
+    if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+    gcn_norm_kernel<<<ceil_div(M, 256), 256, 0, st>>>(csr_row_ptr, csr_col, csr_w, self_w, n_nodes_dev, M, ws.dis);
+    float* cur = ws.buf0;
+    for (int k = 0; k < 3; ++k) {
+        gcn_aggregate_kernel<<<warps_grid, 256, 0, st>>>(cur, H, csr_row_ptr, csr_col, csr_w, self_w, ws.dis, n_nodes_dev, M, ws.buf1);
+        l.A = ws.buf1; l.lda = H; l.K = H; l.W = blob + f.convw[k]; l.bias = blob + f.convb[k]; l.N = H; l.C = ws.buf0; l.ldc = H;
+        if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+        cur = ws.buf0;
+    }
+    float* emb = node_emb ? node_emb : ws.emb;
+    l.A = cur; l.W = p->fc_shared_weight; l.bias = p->fc_shared_bias; l.C = emb;
+    if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+    if (mask_out || instance_out || edge_out || mask_prob) {
+        const int H2 = H / 2;
+        l.A = emb; l.W = blob + f.head1w; l.bias = blob + f.head1b; l.N = 3 * H2; l.C = ws.hid; l.ldc = 3 * H2;
+        if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+        Heads2 h2;
+        h2.n_heads = 3;
+        h2.hdim = H2;
+        float* outs[3] = {mask_out, instance_out, edge_out};
+        for (int t = 0; t < 3; ++t) {
+            h2.w2[t] = p->head2_weight[t];
+            h2.b2[t] = p->head2_bias[t];
+            h2.cdim[t] = t < 2 ? p->num_classes : 1;
+            h2.out[t] = outs[t];
+        }
+        h2.prob_out = mask_prob;
+        if ((rc = launch_heads2(ws.hid, 3 * H2, M, n_nodes_dev, h2, st)) != CM_OK) return rc;
+    }
+    if (graph_emb) {
+        if ((rc = launch_segment_mean(emb, H, node_ptr, 0, n_graphs, graph_emb, H, st)) != CM_OK) return rc;
+    }
+    return post_launch("cm_gnn_forward");
+}

@@ -1,0 +1,214 @@
+// A8 + A9 + A13: pixel-mask paint through the label map fused with the segmentation-metric reductions.
+//
+// Reference: models/region_graph/test.py:241-244 (paint), utils/metrics.py:9-92 (IoU, Dice, P/R/F1, MAE,
+// accuracy, batch mean/std), models/multimodal/train_multimodal.py:197-220 (image-level F1 counts).
+// One pass over the pixels; HBM-bound on labels (i32) + gt (u8).  Confusion counts are
+// integers (bit-exact); the |pred-gt| sum is float64.  Per-thread partials -> warp-shuffle tree -> one
+// atomic per warp-leader into the image's accumulators.
+#include "common.cuh"
+
+namespace cm {
+
+__device__ __forceinline__ void flush_partials(int tp, int sp, int sg, int eq, double ae, unsigned long long* counts, double* abs_err) {
+    tp = warp_sum(tp);
+    sp = warp_sum(sp);
+    sg = warp_sum(sg);
+    eq = warp_sum(eq);
+    ae = warp_sum(ae);
+    if ((threadIdx.x & 31) == 0) {
+        if (tp) atomicAdd(counts + 0, (unsigned long long)tp);
+        if (sp) atomicAdd(counts + 1, (unsigned long long)sp);
+        if (sg) atomicAdd(counts + 2, (unsigned long long)sg);
+        if (eq) atomicAdd(counts + 3, (unsigned long long)eq);
+        atomicAdd(abs_err, ae);
+    }
+}
+
+// grid (chunks, B), block 256; each thread walks pixels with stride gridDim.x*256
+__global__ void __launch_bounds__(256) paint_metrics_kernel(const int* __restrict__ labels, const uint8_t* __restrict__ gt, int HW,
+                                                            const float* __restrict__ mask_prob, const int* __restrict__ node_ptr,
+                                                            const int* __restrict__ id_of_label, int cap, float threshold,
+                                                            float* __restrict__ pred_mask, unsigned long long* __restrict__ counts,
+                                                            double* __restrict__ abs_err) {
+    const int b = blockIdx.y;
+    const int n0 = node_ptr[b], nb = node_ptr[b + 1] - n0;
+    const int* lab = labels + (size_t)b * HW;
+    const uint8_t* g = gt + (size_t)b * HW;
+    const int* idm = id_of_label ? id_of_label + (size_t)b * cap : nullptr;
+    const double thr = (double)threshold;
+    int tp = 0, sp = 0, sg = 0, eq = 0;
+    double ae = 0.0;
+    for (int p = blockIdx.x * 256 + threadIdx.x; p < HW; p += gridDim.x * 256) {
+        const int l = lab[p];
+        int idx = l;
+        if (idm) idx = (l >= 0 && l < cap) ? idm[l] : -1;
+        float pr = 0.f;
+        if (idx >= 0 && idx < nb) pr = mask_prob[n0 + idx];
+        if (pred_mask) pred_mask[(size_t)b * HW + p] = pr;
+        const double gv = (double)g[p] / 255.0;   // test.py:275
+        const bool pb = (double)pr > thr, gb = gv > thr;
+        tp += pb && gb;
+        sp += pb;
+        sg += gb;
+        eq += pb == gb;
+        ae += fabs((double)pr - gv);
+    }
+    flush_partials(tp, sp, sg, eq, ae, counts + 4 * (size_t)b, abs_err + b);
+}
+
+__global__ void __launch_bounds__(256) metrics_dense_kernel(const float* __restrict__ pred, const float* __restrict__ gt, long long pixels,
+                                                            float threshold, unsigned long long* __restrict__ counts,
+                                                            double* __restrict__ abs_err) {
+    const int b = blockIdx.y;
+    const float* pr = pred + (size_t)b * pixels;
+    const float* g = gt + (size_t)b * pixels;
+    int tp = 0, sp = 0, sg = 0, eq = 0;
+    double ae = 0.0;
+    for (long long p = (long long)blockIdx.x * 256 + threadIdx.x; p < pixels; p += (long long)gridDim.x * 256) {
+        const float a = pr[p], c = g[p];
+        const bool pb = a > threshold, gb = c > threshold;
+        tp += pb && gb;
+        sp += pb;
+        sg += gb;
+        eq += pb == gb;
+        ae += fabs((double)a - (double)c);
+    }
+    flush_partials(tp, sp, sg, eq, ae, counts + 4 * (size_t)b, abs_err + b);
+}
+
+// single CTA of 256 threads
+__global__ void __launch_bounds__(256) metrics_finalize_kernel(const unsigned long long* __restrict__ counts, const double* __restrict__ abs_err,
+                                                               int batch, long long pixels, double* __restrict__ per_image,
+                                                               double* __restrict__ partial) {
+    __shared__ double red[8][14];
+    double s[14];
+#pragma unroll
+    for (int k = 0; k < 14; ++k) s[k] = 0.0;
+    const double eps = 1e-8, n = (double)pixels;
+    for (int i = threadIdx.x; i < batch; i += 256) {
+        const double tp = (double)counts[4 * i], sp = (double)counts[4 * i + 1], sg = (double)counts[4 * i + 2];
+        const double eq = (double)counts[4 * i + 3];
+        const double fp = sp - tp, fn = sg - tp;
+        double m[7];
+        m[0] = tp / (sp + sg - tp + eps);           // utils/metrics.py:14-17
+        m[1] = 2.0 * tp / (sp + sg + eps);          // :26
+        m[2] = tp / (tp + fp + eps);                // :39
+        m[3] = tp / (tp + fn + eps);                // :40
+        m[4] = 2.0 * (m[2] * m[3]) / (m[2] + m[3] + eps);   // :41
+        m[5] = abs_err[i] / n;                      // :47
+        m[6] = eq / n;                              // :54
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            if (per_image) per_image[7 * (size_t)i + k] = m[k];
+            s[k] += m[k];
+            s[7 + k] += m[k] * m[k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 14; ++k) s[k] = warp_sum(s[k]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0)
+        for (int k = 0; k < 14; ++k) red[warp][k] = s[k];
+    __syncthreads();
+    if (threadIdx.x < 14 && partial) {
+        double t = 0.0;
+        for (int wv = 0; wv < 8; ++wv) t += red[wv][threadIdx.x];
+        partial[1 + threadIdx.x] = t;
+    }
+    if (threadIdx.x == 0 && partial) partial[0] = (double)batch;
+}
+
+__global__ void class_confusion_kernel(const float* __restrict__ mask_out, const long long* __restrict__ true_cls, int n, int c,
+                                       unsigned long long* counts4) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int tp = 0, fp = 0, fn = 0, tn = 0;
+    if (i < n) {
+        const float* r = mask_out + (size_t)i * c;
+        int arg = 0;
+        float best = r[0];
+        for (int k = 1; k < c; ++k)
+            if (r[k] > best) {   // first maximum wins, like torch.argmax
+                best = r[k];
+                arg = k;
+            }
+        const long long t = true_cls[i];
+        tp = arg == 1 && t == 1;
+        fp = arg == 1 && t == 0;
+        fn = arg == 0 && t == 1;
+        tn = arg == 0 && t == 0;
+    }
+    tp = warp_sum(tp);
+    fp = warp_sum(fp);
+    fn = warp_sum(fn);
+    tn = warp_sum(tn);
+    if ((threadIdx.x & 31) == 0) {
+        if (tp) atomicAdd(counts4 + 0, (unsigned long long)tp);
+        if (fp) atomicAdd(counts4 + 1, (unsigned long long)fp);
+        if (fn) atomicAdd(counts4 + 2, (unsigned long long)fn);
+        if (tn) atomicAdd(counts4 + 3, (unsigned long long)tn);
+    }
+}
+
+static int metric_chunks(long long pixels, int batch) {
+    // about four CTAs per SM over the whole batch, at least 1 per image, at most one per 256 pixels
+    long long want = (4LL * num_sms() + batch - 1) / batch;
+    long long most = (pixels + 255) / 256;
+    if (want > most) want = most;
+    if (want < 1) want = 1;
+    return (int)want;
+}
+
+}  // namespace cm
+
+extern "C" int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
+                                const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, float threshold,
+                                float* pred_mask, int64_t* counts, double* abs_err, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(labels && gt && mask_prob && node_ptr && counts && abs_err, "cm_paint_metrics: NULL pointer");
+    CM_REQUIRE(batch > 0 && h > 0 && w > 0 && batch <= 65535, "cm_paint_metrics: bad shape");
+    CM_REQUIRE(!id_of_label || label_cap > 0, "cm_paint_metrics: id_of_label needs label_cap");
+    cudaStream_t st = as_stream(stream);
+    cudaMemsetAsync(counts, 0, sizeof(int64_t) * 4 * batch, st);
+    cudaMemsetAsync(abs_err, 0, sizeof(double) * batch, st);
+    dim3 grid(metric_chunks((long long)h * w, batch), batch);
+    paint_metrics_kernel<<<grid, 256, 0, st>>>(labels, gt, h * w, mask_prob, node_ptr, id_of_label, label_cap, threshold,
+                                               pred_mask, reinterpret_cast<unsigned long long*>(counts), abs_err);
+    return post_launch("cm_paint_metrics");
+}
+
+extern "C" int cm_metrics_dense(const float* pred, const float* gt, int batch, int64_t pixels, float threshold,
+                                int64_t* counts, double* abs_err, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(pred && gt && counts && abs_err, "cm_metrics_dense: NULL pointer");
+    CM_REQUIRE(batch > 0 && batch <= 65535 && pixels > 0, "cm_metrics_dense: bad shape");
+    cudaStream_t st = as_stream(stream);
+    cudaMemsetAsync(counts, 0, sizeof(int64_t) * 4 * batch, st);
+    cudaMemsetAsync(abs_err, 0, sizeof(double) * batch, st);
+    dim3 grid(metric_chunks(pixels, batch), batch);
+    metrics_dense_kernel<<<grid, 256, 0, st>>>(pred, gt, pixels, threshold, reinterpret_cast<unsigned long long*>(counts), abs_err);
+    return post_launch("cm_metrics_dense");
+}
+
+extern "C" int cm_metrics_finalize(const int64_t* counts, const double* abs_err, int batch, int64_t pixels,
+                                   double* per_image, double* partial, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(counts && abs_err && (per_image || partial), "cm_metrics_finalize: NULL pointer");
+    CM_REQUIRE(batch > 0 && pixels > 0, "cm_metrics_finalize: bad shape");
+    metrics_finalize_kernel<<<1, 256, 0, as_stream(stream)>>>(reinterpret_cast<const unsigned long long*>(counts), abs_err, batch,
+                                                              pixels, per_image, partial);
+    return post_launch("cm_metrics_finalize");
+}
+
+extern "C" int cm_class_confusion(const float* mask_out, const int64_t* true_cls, int n, int num_classes,
+                                  int64_t* counts4, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(mask_out && true_cls && counts4, "cm_class_confusion: NULL pointer");
+    CM_REQUIRE(n > 0 && num_classes >= 2, "cm_class_confusion: bad shape");
+    class_confusion_kernel<<<ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
+        mask_out, reinterpret_cast<const long long*>(true_cls), n, num_classes, reinterpret_cast<unsigned long long*>(counts4));
+    return post_launch("cm_class_confusion");
+}
