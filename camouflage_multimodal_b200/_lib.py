@@ -1,0 +1,128 @@
+"""ctypes binding of ``libcm_b200.so`` (C ABI declared in ``include/cm_b200.h``).
+
+PyTorch is used for device memory and streams only: every call below hands raw device pointers and the
+current CUDA stream to the library.  There is no CPU or eager fallback -- a missing library, a missing
+symbol or a non-sm_100 device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcm_b200.so")
+
+CM_OK, CM_ERR_ARG, CM_ERR_DEVICE, CM_ERR_LAUNCH, CM_ERR_WORKSPACE = 0, -1, -2, -3, -4
+STATUS_LABEL_OVERFLOW, STATUS_NODE_OVERFLOW, STATUS_EDGE_OVERFLOW = 1, 2, 4
+NODE_FEATURES = 15
+
+_fp = C.c_void_p   # every device pointer crosses as void*
+
+
+class GnnParams(C.Structure):
+    _fields_ = [
+        ("in_channels", C.c_int), ("hidden", C.c_int), ("heads", C.c_int), ("num_classes", C.c_int),
+        ("conv1_lin_weight", _fp), ("conv1_att_src", _fp), ("conv1_att_dst", _fp), ("conv1_bias", _fp),
+        ("conv_lin_weight", _fp * 3), ("conv_bias", _fp * 3),
+        ("bn_weight", _fp * 4), ("bn_bias", _fp * 4), ("bn_mean", _fp * 4), ("bn_var", _fp * 4),
+        ("bn_eps", C.c_float),
+        ("fc_shared_weight", _fp), ("fc_shared_bias", _fp),
+        ("head1_weight", _fp * 3), ("head1_bias", _fp * 3), ("head2_weight", _fp * 3), ("head2_bias", _fp * 3),
+    ]
+
+
+class FusionParams(C.Structure):
+    _fields_ = [
+        ("rg_dim", C.c_int), ("kg_dim", C.c_int), ("hidden", C.c_int), ("heads", C.c_int),
+        ("num_classes", C.c_int), ("fusion_type", C.c_int),
+        ("rg_proj_w", _fp), ("rg_proj_b", _fp), ("kg_proj_w", _fp), ("kg_proj_b", _fp),
+        ("r2k_in_w", _fp), ("r2k_in_b", _fp), ("r2k_out_w", _fp), ("r2k_out_b", _fp),
+        ("k2r_in_w", _fp), ("k2r_in_b", _fp), ("k2r_out_w", _fp), ("k2r_out_b", _fp),
+        ("ln_rg_w", _fp), ("ln_rg_b", _fp), ("ln_kg_w", _fp), ("ln_kg_b", _fp),
+        ("ffn_rg_w1", _fp), ("ffn_rg_b1", _fp), ("ffn_rg_w2", _fp), ("ffn_rg_b2", _fp),
+        ("ffn_kg_w1", _fp), ("ffn_kg_b1", _fp), ("ffn_kg_w2", _fp), ("ffn_kg_b2", _fp),
+        ("fl_w1", _fp), ("fl_b1", _fp), ("fl_w2", _fp), ("fl_b2", _fp),
+        ("late_w", _fp * 3), ("late_b", _fp * 3),
+        ("head_w1", _fp * 4), ("head_b1", _fp * 4), ("head_w2", _fp * 4), ("head_b2", _fp * 4),
+    ]
+
+
+# name -> (restype, argtypes); the list is also what tests/test_abi.py checks against include/cm_b200.h
+_i, _sz, _f, _i64 = C.c_int, C.c_size_t, C.c_float, C.c_int64
+SIGNATURES = {
+    "cm_last_error": (C.c_char_p, []),
+    "cm_abi_version": (_i, []),
+    "cm_device_check": (_i, []),
+    "cm_rag_workspace_bytes": (_sz, [_i, _i]),
+    "cm_rag_build": (_i, [_fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp]),
+    "cm_node_features": (_i, [_fp, _fp, _fp, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
+    "cm_edge_weights": (_i, [_fp, _fp, _fp, _fp, _i, _fp, _fp]),
+    "cm_csr_workspace_bytes": (_sz, [_i, _i]),
+    "cm_csr_from_edge_index": (_i, [_fp, _i64, _fp, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "cm_gnn_folded_bytes": (_sz, [C.POINTER(GnnParams)]),
+    "cm_gnn_fold": (_i, [C.POINTER(GnnParams), _fp, _sz, _fp]),
+    "cm_gnn_workspace_bytes": (_sz, [C.POINTER(GnnParams), _i]),
+    "cm_gnn_forward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _fp, _i, _fp, _sz,
+                            _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "cm_fusion_workspace_bytes": (_sz, [C.POINTER(FusionParams), _i, _i, _i]),
+    "cm_fusion_forward": (_i, [C.POINTER(FusionParams), _fp, _fp, _i, _i, _fp, _i, _i, _fp, _sz,
+                               _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "cm_paint_metrics": (_i, [_fp, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _f, _fp, _fp, _fp, _fp]),
+    "cm_metrics_dense": (_i, [_fp, _fp, _i, _i64, _f, _fp, _fp, _fp]),
+    "cm_metrics_finalize": (_i, [_fp, _fp, _i, _i64, _fp, _fp, _fp]),
+    "cm_class_confusion": (_i, [_fp, _fp, _i, _i, _fp, _fp]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `make -C camouflage_multimodal_b200/csrc` "
+                "(or __graft_entry__.build()); this package has no fallback path")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)   # AttributeError if the ABI and the binding drift apart
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+class CmError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc == CM_OK:
+        return
+    msg = load().cm_last_error().decode("utf-8", "replace")
+    if rc == CM_ERR_ARG:
+        raise ValueError(msg or what)
+    raise CmError(f"{what}: {msg} (code {rc})")
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    if t is None:
+        return None
+    return C.c_void_p(t.data_ptr())
+
+
+def stream_ptr(device=None):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def require_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise CmError(f"{name} lives on {t.device}; the B200 path has no CPU fallback -- move it to a CUDA device")
+
+
+def f32c(t: torch.Tensor) -> torch.Tensor:
+    return t.detach().to(torch.float32).contiguous()

@@ -223,6 +223,9 @@ static int detector_heads(const cm_fusion_params* p, const float* fused, int fin
                           float* instance_out, float* edge_out, float* score_out, cudaStream_t st) {
     const int H2 = final_dim / 2;
     int rc;
+    if (!mask_out && !instance_out && !edge_out && !score_out) return CM_OK;   // fusion module used on its own
+    for (int t = 0; t < 4; ++t)
+        CM_REQUIRE(p->head_w1[t] && p->head_b1[t] && p->head_w2[t] && p->head_b2[t], "cm_fusion_forward: head %d parameters missing", t);
     Linear l;
     l.M = G; l.K = final_dim; l.A = fused; l.lda = final_dim; l.N = H2; l.ldc = 4 * H2; l.relu = 1;
     for (int t = 0; t < 4; ++t) {

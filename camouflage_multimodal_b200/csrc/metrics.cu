@@ -84,17 +84,21 @@ __global__ void __launch_bounds__(256) metrics_finalize_kernel(const unsigned lo
     double s[14];
 #pragma unroll
     for (int k = 0; k < 14; ++k) s[k] = 0.0;
-    const double eps = 1e-8, n = (double)pixels;
+    const float epsf = 1e-8f;
+    const double n = (double)pixels;
     for (int i = threadIdx.x; i < batch; i += 256) {
-        const double tp = (double)counts[4 * i], sp = (double)counts[4 * i + 1], sg = (double)counts[4 * i + 2];
+        // The reference forms the five ratios in float32 (0/1 masks are astype(np.float32) and
+        // float32 + 1e-8 stays float32, utils/metrics.py:11-17); MAE and accuracy are float64.
+        const float tp = (float)counts[4 * i], sp = (float)counts[4 * i + 1], sg = (float)counts[4 * i + 2];
         const double eq = (double)counts[4 * i + 3];
-        const double fp = sp - tp, fn = sg - tp;
+        const float fp = __fsub_rn(sp, tp), fn = __fsub_rn(sg, tp);
+        const float iou = __fdiv_rn(tp, __fadd_rn(__fsub_rn(__fadd_rn(sp, sg), tp), epsf));            // :14-17
+        const float dice = __fdiv_rn(__fmul_rn(2.0f, tp), __fadd_rn(__fadd_rn(sp, sg), epsf));          // :26
+        const float prec = __fdiv_rn(tp, __fadd_rn(__fadd_rn(tp, fp), epsf));                           // :39
+        const float rec = __fdiv_rn(tp, __fadd_rn(__fadd_rn(tp, fn), epsf));                            // :40
+        const float f1 = __fdiv_rn(__fmul_rn(2.0f, __fmul_rn(prec, rec)), __fadd_rn(__fadd_rn(prec, rec), epsf));   // :41
         double m[7];
-        m[0] = tp / (sp + sg - tp + eps);           // utils/metrics.py:14-17
-        m[1] = 2.0 * tp / (sp + sg + eps);          // :26
-        m[2] = tp / (tp + fp + eps);                // :39
-        m[3] = tp / (tp + fn + eps);                // :40
-        m[4] = 2.0 * (m[2] * m[3]) / (m[2] + m[3] + eps);   // :41
+        m[0] = iou; m[1] = dice; m[2] = prec; m[3] = rec; m[4] = f1;
         m[5] = abs_err[i] / n;                      // :47
         m[6] = eq / n;                              // :54
 #pragma unroll

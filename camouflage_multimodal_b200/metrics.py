@@ -1,0 +1,138 @@
+"""Segmentation metrics on the B200 reduction kernels.
+
+Same names, arguments and return keys as the reference's ``utils/metrics.py`` (:9-92): numpy arrays (or
+tensors) in, Python floats / dicts out.  Confusion counts are exact integers accumulated on the device;
+ratios are formed in float64 with the reference's ``+1e-8`` guards.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+
+KEYS = ("iou", "dice", "precision", "recall", "f1", "mae", "accuracy")
+
+
+def _device():
+    if not torch.cuda.is_available():
+        raise _lib.CmError("no CUDA device: the B200 metrics path has no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _as_batch(a, dev):
+    """-> [B, P] float32 CUDA tensor (a single image becomes a batch of one)."""
+    t = a if torch.is_tensor(a) else torch.as_tensor(np.asarray(a))
+    t = t.to(device=dev, dtype=torch.float32)
+    return t.reshape(1, -1)
+
+
+def dense_counts(preds: torch.Tensor, gts: torch.Tensor, threshold: float = 0.5):
+    """Device entry: preds/gts ``[B, P]`` f32 CUDA -> (counts ``[B,4]`` i64: tp, sum_pred, sum_gt, n_equal;
+    abs_err ``[B]`` f64)."""
+    lib = _lib.load()
+    _lib.require_cuda(preds, "pred")
+    _lib.require_cuda(gts, "gt")
+    if preds.shape != gts.shape or preds.dim() != 2:
+        raise ValueError(f"pred {tuple(preds.shape)} and gt {tuple(gts.shape)} must both be [B, P]")
+    preds, gts = _lib.f32c(preds), _lib.f32c(gts)
+    B, P = preds.shape
+    counts = torch.empty((B, 4), dtype=torch.int64, device=preds.device)
+    abs_err = torch.empty(B, dtype=torch.float64, device=preds.device)
+    _lib.check(lib.cm_metrics_dense(_lib.ptr(preds), _lib.ptr(gts), B, P, float(threshold), _lib.ptr(counts),
+                                    _lib.ptr(abs_err), _lib.stream_ptr(preds.device)), "cm_metrics_dense")
+    return counts, abs_err
+
+
+def finalize(counts: torch.Tensor, abs_err: torch.Tensor, pixels: int):
+    """(per_image ``[B,7]`` f64, partial ``[15]`` f64 = n, sum m_k, sum m_k^2) on the device."""
+    lib = _lib.load()
+    B = counts.shape[0]
+    per = torch.empty((B, 7), dtype=torch.float64, device=counts.device)
+    part = torch.empty(15, dtype=torch.float64, device=counts.device)
+    _lib.check(lib.cm_metrics_finalize(_lib.ptr(counts), _lib.ptr(abs_err), B, int(pixels), _lib.ptr(per), _lib.ptr(part),
+                                       _lib.stream_ptr(counts.device)), "cm_metrics_finalize")
+    return per, part
+
+
+def summary_from_partial(partial) -> dict:
+    """``batch_evaluate``'s 14 keys (mean and population std per metric, utils/metrics.py:86-90) from the
+    15-element partial-sum vector (after any cross-rank all-reduce)."""
+    v = np.asarray(partial.detach().cpu() if torch.is_tensor(partial) else partial, dtype=np.float64)
+    n = v[0]
+    out = {}
+    for k, name in enumerate(KEYS):
+        mean = v[1 + k] / n
+        var = max(v[8 + k] / n - mean * mean, 0.0)
+        out[name] = float(mean)
+        out[f"{name}_std"] = float(np.sqrt(var))
+    return out
+
+
+def _eval_one(pred, gt, threshold):
+    dev = _device()
+    p, g = _as_batch(pred, dev), _as_batch(gt, dev)
+    counts, abs_err = dense_counts(p, g, threshold)
+    per, _ = finalize(counts, abs_err, p.shape[1])
+    return per[0].tolist()
+
+
+def calculate_iou(pred_mask, gt_mask, threshold=0.5):
+    return _eval_one(pred_mask, gt_mask, threshold)[0]
+
+
+def calculate_dice(pred_mask, gt_mask, threshold=0.5):
+    return _eval_one(pred_mask, gt_mask, threshold)[1]
+
+
+def calculate_precision_recall_f1(pred_mask, gt_mask, threshold=0.5):
+    m = _eval_one(pred_mask, gt_mask, threshold)
+    return m[2], m[3], m[4]
+
+
+def calculate_mae(pred_mask, gt_mask):
+    return _eval_one(pred_mask, gt_mask, 0.5)[5]
+
+
+def calculate_accuracy(pred_mask, gt_mask, threshold=0.5):
+    return _eval_one(pred_mask, gt_mask, threshold)[6]
+
+
+def evaluate_segmentation(pred_mask, gt_mask, threshold=0.5):
+    """utils/metrics.py:57-76 -> dict with the seven keys."""
+    return dict(zip(KEYS, _eval_one(pred_mask, gt_mask, threshold)))
+
+
+def batch_evaluate(pred_masks, gt_masks, threshold=0.5):
+    """utils/metrics.py:78-92 -> per-key mean and ``<key>_std`` (population std) over the images."""
+    dev = _device()
+    if len(pred_masks) == 0:
+        raise ValueError("batch_evaluate needs at least one image")
+    p = torch.cat([_as_batch(x, dev) for x in pred_masks], 0)
+    g = torch.cat([_as_batch(x, dev) for x in gt_masks], 0)
+    counts, abs_err = dense_counts(p, g, threshold)
+    _, part = finalize(counts, abs_err, p.shape[1])
+    return summary_from_partial(part)
+
+
+def class_confusion(mask_out: torch.Tensor, true_cls: torch.Tensor, counts4: torch.Tensor | None = None):
+    """Image-level tp, fp, fn, tn (train_multimodal.py:197-220) accumulated into ``counts4`` (i64 [4])."""
+    lib = _lib.load()
+    _lib.require_cuda(mask_out, "mask_out")
+    mask_out = _lib.f32c(mask_out)
+    true_cls = true_cls.to(device=mask_out.device, dtype=torch.int64).contiguous()
+    if counts4 is None:
+        counts4 = torch.zeros(4, dtype=torch.int64, device=mask_out.device)
+    _lib.check(lib.cm_class_confusion(_lib.ptr(mask_out), _lib.ptr(true_cls), mask_out.shape[0], mask_out.shape[1],
+                                      _lib.ptr(counts4), _lib.stream_ptr(mask_out.device)), "cm_class_confusion")
+    return counts4
+
+
+def f1_from_confusion(tp, fp, fn, tn):
+    """train_multimodal.py:206-220: per-class precision / recall / F1 (+1e-8 guards), macro average."""
+    eps = 1e-8
+    p1, r1 = tp / (tp + fp + eps), tp / (tp + fn + eps)
+    f1_1 = 2 * (p1 * r1) / (p1 + r1 + eps)
+    p0, r0 = tn / (tn + fn + eps), tn / (tn + fp + eps)
+    f1_0 = 2 * (p0 * r0) / (p0 + r0 + eps)
+    return {"f1_class_0": f1_0, "f1_class_1": f1_1, "f1_avg": (f1_0 + f1_1) / 2, "precision_1": p1, "recall_1": r1}

@@ -44,15 +44,22 @@ def confusion_counts(pred, gt, threshold=0.5):
 
 def metrics_from_counts(tp, sp, sg, neq, n, abs_err_sum):
     """The seven values of ``evaluate_segmentation`` (metrics.py:57-76) from exact integer counts and the
-    sum of |pred - gt|, with the reference's float32 0/1 products replaced by the counts they equal."""
-    tp, sp, sg = float(tp), float(sp), float(sg)
-    fp, fn = sp - tp, sg - tp
-    iou = tp / (sp + sg - tp + EPS)                       # :14-17
-    dice = 2 * tp / (sp + sg + EPS)                       # :26
-    prec = tp / (tp + fp + EPS)                           # :39
-    rec = tp / (tp + fn + EPS)                            # :40
-    f1 = 2 * (prec * rec) / (prec + rec + EPS)            # :41
-    return {"iou": iou, "dice": dice, "precision": prec, "recall": rec, "f1": f1,
+    sum of |pred - gt|.
+
+    The reference forms the five ratios in FLOAT32: the 0/1 masks are ``astype(np.float32)`` (:11-12), their
+    sums are float32 scalars (exact integers below 2^24), and ``float32_scalar + 1e-8`` stays float32, so the
+    ``1e-8`` guard only matters when the denominator is otherwise 0.  MAE and accuracy are float64.
+    """
+    f = np.float32
+    tp, sp, sg = f(tp), f(sp), f(sg)
+    eps = f(1e-8)
+    fp, fn = sp - tp, sg - tp                              # :36-37 (sums of exact 0/1 products)
+    iou = tp / ((sp + sg - tp) + eps)                      # :14-17
+    dice = (f(2) * tp) / (sp + sg + eps)                   # :26
+    prec = tp / (tp + fp + eps)                            # :39
+    rec = tp / (tp + fn + eps)                             # :40
+    f1 = f(2) * (prec * rec) / (prec + rec + eps)          # :41
+    return {"iou": float(iou), "dice": float(dice), "precision": float(prec), "recall": float(rec), "f1": float(f1),
             "mae": abs_err_sum / n, "accuracy": neq / n}
 
 
@@ -63,12 +70,21 @@ def evaluate_segmentation(pred, gt, threshold=0.5):
     return metrics_from_counts(tp, sp, sg, neq, n, float(np.abs(pred - gt).sum()))
 
 
+F32_KEYS = ("iou", "dice", "precision", "recall", "f1")
+
+
 def batch_evaluate(preds, gts, threshold=0.5):
-    """Mean and population std per key over images (metrics.py:78-92)."""
+    """Mean and population std per key over images (metrics.py:78-92).
+
+    The five ratio metrics are np.float32 scalars in the reference, so ``np.mean`` / ``np.std`` of the list
+    run with a float32 accumulator (numpy pairwise order); MAE and accuracy are float64.  The device path
+    accumulates float64 partial sums instead (order-free across ranks): it agrees to ~1e-7, the float32
+    rounding of the reference's own accumulator -- tests compare batch statistics at 1e-6.
+    """
     per = [evaluate_segmentation(p, g, threshold) for p, g in zip(preds, gts)]
     out = {}
     for k in KEYS:
-        v = np.array([m[k] for m in per], dtype=np.float64)
+        v = np.array([m[k] for m in per], dtype=np.float32 if k in F32_KEYS else np.float64)
         out[k] = float(v.mean())
         out[f"{k}_std"] = float(v.std())
     return out
