@@ -1,0 +1,194 @@
+"""GPU parity: RegionGraphGNN (A5-A7), fusion + heads (A10-A12) vs the oracle and the reference's golden
+outputs.  Tolerances (fp32 path): GNN max-abs <= 1e-4, fusion logits <= 1e-4 and attention
+probabilities <= 1e-5 -- well inside the north star's 1e-2 on mask logits."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from camouflage_multimodal_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+from test_oracle_golden import fusion_state_dict, gnn_state_dict  # noqa: E402
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+# ----------------------------------------------------------------------------------------------- GNN
+@pytest.fixture(scope="module")
+def gnn(golden_dir):
+    from camouflage_multimodal_b200.region_graph import RegionGraphGNN
+    z = np.load(os.path.join(golden_dir, "region_graph.npz"))
+    m = RegionGraphGNN(15, 128, 2)
+    m.load_state_dict(gnn_state_dict(z))
+    return m.cuda().eval(), z
+
+
+@pytest.mark.parametrize("name", ["A", "B"])
+def test_gnn_matches_reference_golden(gnn, name):
+    """Reference order edge_index (networkx order) through the general edge_index -> CSR path."""
+    from camouflage_multimodal_b200.data import Data
+    m, z = gnn
+    d = Data(x=torch.from_numpy(z[f"{name}.x"]), edge_index=torch.from_numpy(z[f"{name}.edge_index"]),
+             edge_attr=torch.from_numpy(z[f"{name}.edge_attr"])).to("cuda")
+    mask, inst, edge = m(d)
+    np.testing.assert_allclose(_np(mask), z[f"{name}.mask_out"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(_np(inst), z[f"{name}.instance_out"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(_np(edge), z[f"{name}.edge_out"], rtol=0, atol=1e-4)
+    emb = m.extract_node_embeddings(d)
+    assert tuple(emb.shape) == (d.x.shape[0], 128) and (emb >= 0).all()
+    np.testing.assert_allclose(_np(emb)[::16], z[f"{name}.node_emb_rows"], rtol=0, atol=1e-4)
+    ge = m.extract_graph_embedding(d)
+    np.testing.assert_allclose(_np(ge), z[f"{name}.graph_emb"], rtol=0, atol=1e-4)
+
+
+def test_gnn_batched_vs_oracle(gnn):
+    """Batch.from_data_list of built graphs (CSR reuse) against the oracle run per image."""
+    from camouflage_multimodal_b200.region_graph import batch_to_data, build_region_graphs
+    from oracle import gnn as ognn
+    m, z = gnn
+    sd = gnn_state_dict(z)
+    b = synth.make_batch(40, 3, seed=1234).to("cuda")
+    g = build_region_graphs(b.images, b.labels, b.canny, label_cap=544)
+    data = batch_to_data(g)
+    mask, inst, edge = m(data)
+    gemb = m.extract_graph_embedding(data)
+    assert tuple(gemb.shape) == (3, 128)
+    ptr = g.node_ptr.cpu().numpy()
+    eptr = g.edge_ptr.cpu().numpy()
+    for i in range(3):
+        n0, n1, e0, e1 = ptr[i], ptr[i + 1], eptr[i], eptr[i + 1]
+        with torch.no_grad():
+            r = ognn.rg_gnn_forward(sd, data.x[n0:n1].cpu(), (data.edge_index[:, e0:e1] - int(n0)).cpu(),
+                                    data.edge_attr[e0:e1].cpu())
+        np.testing.assert_allclose(_np(mask[n0:n1]), r["mask_out"].numpy(), rtol=0, atol=1e-4)
+        np.testing.assert_allclose(_np(edge[n0:n1]), r["edge_out"].numpy(), rtol=0, atol=1e-4)
+        np.testing.assert_allclose(_np(gemb[i]), r["graph_emb"][0].numpy(), rtol=0, atol=1e-4)
+
+
+def test_gnn_edge_cases(gnn):
+    from camouflage_multimodal_b200.data import Data
+    from oracle import gnn as ognn
+    m, z = gnn
+    sd = gnn_state_dict(z)
+    x = torch.randn(5, 15, generator=torch.Generator().manual_seed(1))
+    # no edges: edge_attr.numel() == 0 -> unweighted (extract_rg_embeddings.py:56); isolated nodes keep their self loop
+    d0 = Data(x=x, edge_index=torch.zeros((2, 0), dtype=torch.long), edge_attr=torch.zeros((0, 1)))
+    # explicit self loop + duplicate edge + asymmetric edge
+    ei = torch.tensor([[0, 1, 1, 2, 2, 3], [1, 0, 0, 2, 4, 4]])
+    d1 = Data(x=x, edge_index=ei, edge_attr=torch.tensor([[0.5], [0.25], [0.125], [0.75], [0.3], [0.9]]))
+    for d in (d0, d1):
+        with torch.no_grad():
+            r = ognn.rg_gnn_forward(sd, d.x, d.edge_index, d.edge_attr)
+        mask, inst, edge = m(d.to("cuda"))
+        np.testing.assert_allclose(_np(mask), r["mask_out"].numpy(), rtol=0, atol=1e-4)
+        np.testing.assert_allclose(_np(inst), r["instance_out"].numpy(), rtol=0, atol=1e-4)
+    with pytest.raises(IndexError):
+        m(Data(x=x, edge_index=torch.tensor([[0], [9]]), edge_attr=torch.ones(1, 1)).to("cuda"))
+    with pytest.raises(Exception, match="no CPU fallback"):
+        m(d1)                                                       # CPU tensors are refused, not silently computed
+
+
+def test_gnn_pyg23_checkpoint_names(gnn):
+    from camouflage_multimodal_b200.region_graph import RegionGraphGNN
+    m, z = gnn
+    sd = dict(gnn_state_dict(z))
+    w = sd.pop("conv1.lin.weight")
+    sd["conv1.lin_src.weight"] = w
+    sd["conv1.lin_dst.weight"] = w
+    m2 = RegionGraphGNN()
+    m2.load_state_dict(sd)
+    assert torch.equal(m2.conv1.lin.weight.cpu(), w)
+
+
+# -------------------------------------------------------------------------------------------- fusion
+@pytest.fixture(scope="module")
+def detector(golden_dir):
+    import yaml
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
+    z = np.load(os.path.join(golden_dir, "fusion.npz"))
+    cfg = {"rg_dim": 128, "kg_dim": 128, "hidden_dim": 256, "num_heads": 8, "fusion_type": "cross_attention",
+           "num_classes": 2, "dropout": 0.3}                        # configs/multimodal_config.yaml:14-21
+    m = build_multimodal_model(yaml.safe_load(yaml.safe_dump(cfg)))
+    assert list(m.state_dict().keys()) == [str(k) for k in z["shapes_keys"]]   # checkpoint-compatible names
+    m.load_state_dict(fusion_state_dict(z))
+    return m.cuda().eval(), z
+
+
+@pytest.mark.parametrize("case", ["single_4d", "batch_3d", "graph_2d", "view_4d"])
+def test_detector_matches_reference_golden(detector, case):
+    m, z = detector
+    rg, kg = torch.from_numpy(z[f"{case}.rg"]).cuda(), torch.from_numpy(z[f"{case}.kg"]).cuda()
+    mask, inst, edge, score, attn = m(rg, kg, return_attention=True)
+    for name, got in (("mask", mask), ("instance", inst), ("edge", edge), ("score", score)):
+        assert tuple(got.shape) == z[f"{case}.{name}"].shape
+        np.testing.assert_allclose(_np(got), z[f"{case}.{name}"], rtol=0, atol=1e-4, err_msg=name)
+    for name in ("rg2kg", "kg2rg"):
+        assert tuple(attn[name].shape) == z[f"{case}.{name}"].shape
+        np.testing.assert_allclose(_np(attn[name]), z[f"{case}.{name}"], rtol=0, atol=1e-5, err_msg=name)
+        np.testing.assert_allclose(_np(attn[name].sum(-1)), 1.0, atol=1e-5)
+    out4 = m(rg, kg)
+    assert len(out4) == 4 and torch.allclose(out4[0], mask, atol=1e-6)
+    fused, aw = m.fusion(rg, kg)
+    np.testing.assert_allclose(_np(fused), z[f"{case}.fused"], rtol=0, atol=1e-4)
+    assert set(aw) == {"rg2kg", "kg2rg"}
+
+
+def test_late_fusion_matches_reference_golden(golden_dir):
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
+    z = np.load(os.path.join(golden_dir, "fusion.npz"))
+    m = build_multimodal_model({"fusion_type": "late"})
+    assert list(m.state_dict().keys()) == [str(k) for k in z["late_shapes_keys"]]
+    m.load_state_dict(fusion_state_dict(z, late=True))
+    m = m.cuda().eval()
+    rg, kg = torch.from_numpy(z["batch_3d.rg"]).cuda(), torch.from_numpy(z["batch_3d.kg"]).cuda()
+    mask, inst, edge, score, attn = m(rg, kg, return_attention=True)
+    assert attn is None
+    for name, got in (("mask", mask), ("instance", inst), ("edge", edge), ("score", score)):
+        np.testing.assert_allclose(_np(got), z[f"late.{name}"], rtol=0, atol=1e-4)
+
+
+def test_fusion_errors_and_invariances(detector):
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
+    m, z = detector
+    with pytest.raises(ValueError, match="must be 2D/3D/4D"):
+        m(torch.zeros(1, 1, 1, 1, 128).cuda(), torch.zeros(1, 13, 128).cuda())
+    with pytest.raises(ValueError, match="Unknown fusion_type"):
+        build_multimodal_model({"fusion_type": "nope"})
+    rg = torch.from_numpy(z["single_4d.rg"]).cuda()
+    kg = torch.from_numpy(z["single_4d.kg"]).cuda()
+    base = m(rg, kg)
+    g = torch.Generator().manual_seed(0)
+    pn, pk = torch.randperm(rg.shape[1], generator=g).cuda(), torch.randperm(13, generator=g).cuda()
+    perm = m(rg[:, pn], kg[:, pk])                                   # node- and KG-order invariance
+    for a, b in zip(base, perm):
+        assert torch.allclose(a, b, atol=2e-5)
+
+
+def test_ragged_batch_equals_per_image(detector, golden_dir):
+    """Batch 32 forward = 32 independent B=1 reference forwards: ragged rows, shared KG."""
+    from oracle import fusion as ofus
+    m, z = detector
+    sd = fusion_state_dict(z)
+    kgz = np.load(os.path.join(golden_dir, "kg_embeddings.npz"))["kg"]          # [13,1,128]
+    kg = torch.from_numpy(kgz).reshape(13, 128)
+    gen = torch.Generator().manual_seed(3)
+    sizes = [481, 303, 530, 1, 77]
+    rows = [torch.randn(n, 128, generator=gen).clamp_min_(0) * 0.6 for n in sizes]
+    ptr = torch.tensor(np.concatenate([[0], np.cumsum(sizes)]), dtype=torch.int32).cuda()
+    res = m.forward_ragged(torch.cat(rows).cuda(), ptr, len(sizes), kg.cuda()[None], return_attention=True)
+    off = 0
+    for i, r in enumerate(rows):
+        with torch.no_grad():
+            mask, inst, edge, score, attn, fused = ofus.detector_forward(sd, r[None], torch.from_numpy(kgz)[None])
+        np.testing.assert_allclose(_np(res["mask_out"][i]), mask[0].numpy(), rtol=0, atol=1e-4)
+        np.testing.assert_allclose(_np(res["score_out"][i]), score[0].numpy(), rtol=0, atol=1e-4)
+        n = sizes[i]
+        np.testing.assert_allclose(_np(res["rg2kg"][off:off + n]), attn["rg2kg"][0].numpy(), rtol=0, atol=1e-5)
+        np.testing.assert_allclose(_np(res["kg2rg"][13 * off:13 * (off + n)]).reshape(13, n), attn["kg2rg"][0].numpy(),
+                                   rtol=0, atol=1e-5)
+        off += n

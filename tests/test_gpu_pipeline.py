@@ -1,0 +1,138 @@
+"""GPU parity: paint + metric reductions (A8, A9, A13) and the whole batched pipeline vs the oracle.
+Confusion counts bit-exact; per-image ratio metrics bit-exact (float32 arithmetic restated); MAE <= 1e-9
+given the same probabilities; end to end |dMAE| <= 1e-3 and mask logits <= 1e-2 (BASELINE.json)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from camouflage_multimodal_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+from test_oracle_golden import fusion_state_dict, gnn_state_dict  # noqa: E402
+
+
+def test_metrics_match_reference_golden(golden_dir):
+    from camouflage_multimodal_b200 import metrics as gm
+    from oracle import metrics as om
+    z = np.load(os.path.join(golden_dir, "metrics.npz"))
+    preds, gts = z["preds"], z["gts"]
+    for i in range(len(preds)):
+        # the device API computes on float32 arrays; compare with the oracle on the same rounded inputs
+        p32, g32 = preds[i].astype(np.float32), gts[i].astype(np.float32)
+        ref = om.evaluate_segmentation(p32, g32)
+        got = gm.evaluate_segmentation(preds[i], gts[i])
+        assert set(got) == set(om.KEYS)
+        for k in ("iou", "dice", "precision", "recall", "f1", "accuracy"):
+            assert got[k] == ref[k], (i, k)                          # bit-exact
+        mae64 = float(np.abs(p32.astype(np.float64) - g32.astype(np.float64)).mean())
+        assert abs(got["mae"] - mae64) < 1e-9
+        # and against the reference's float64-input numbers themselves
+        for j, k in enumerate(om.KEYS):
+            assert abs(got[k] - z["per_image"][i][j]) < 1e-6, (i, k)
+    be = gm.batch_evaluate(list(preds), list(gts))
+    for k, v in zip(z["batch_keys"], z["batch_vals"]):
+        assert abs(be[str(k)] - float(v)) < 1e-6, k
+    assert gm.calculate_iou(preds[0], gts[0]) == gm.evaluate_segmentation(preds[0], gts[0])["iou"]
+    p, r, f = gm.calculate_precision_recall_f1(preds[0], gts[0])
+    assert 0 <= p <= 1 and 0 <= r <= 1 and 0 <= f <= 1
+    assert abs(gm.calculate_mae(preds[0], gts[0]) - float(np.abs(preds[0] - gts[0]).mean())) < 1e-6
+
+
+def test_class_confusion():
+    from camouflage_multimodal_b200 import metrics as gm
+    from oracle import metrics as om
+    g = torch.Generator().manual_seed(0)
+    logits = torch.randn(1000, 2, generator=g)
+    true = torch.randint(0, 2, (1000,), generator=g)
+    c = gm.class_confusion(logits.cuda(), true.cuda()).cpu().tolist()
+    ref = om.image_level_f1(logits.argmax(1).numpy(), true.numpy())
+    assert tuple(c) == ref["counts"]
+    got = gm.f1_from_confusion(*c)
+    assert abs(got["f1_avg"] - ref["f1_avg"]) < 1e-12
+
+
+@pytest.fixture(scope="module")
+def models(golden_dir):
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
+    from camouflage_multimodal_b200.region_graph import RegionGraphGNN
+    zg = np.load(os.path.join(golden_dir, "region_graph.npz"))
+    zf = np.load(os.path.join(golden_dir, "fusion.npz"))
+    gnn = RegionGraphGNN(15, 128, 2)
+    gnn.load_state_dict(gnn_state_dict(zg))
+    det = build_multimodal_model({})
+    det.load_state_dict(fusion_state_dict(zf))
+    kg = torch.from_numpy(np.load(os.path.join(golden_dir, "kg_embeddings.npz"))["kg"]).reshape(13, 128)
+    return gnn.cuda().eval(), det.cuda().eval(), kg.cuda(), gnn_state_dict(zg), fusion_state_dict(zf)
+
+
+@pytest.mark.parametrize("fix", [False, True])
+def test_pipeline_vs_oracle(models, fix):
+    from camouflage_multimodal_b200.pipeline import EvalPipeline
+    from oracle import fusion as ofus, gnn as ognn, metrics as om, region_graph as org
+    gnn, det, kg, gsd, fsd = models
+    B = 3
+    hb = synth.make_batch(200, B, seed=1234)
+    d = hb.to("cuda")
+    pipe = EvalPipeline(gnn, det, kg, label_cap=544, label_offset_fix=fix, want_pred_mask=True)
+    out = pipe.run(d.images, d.labels, d.canny, d.gt)
+    torch.cuda.synchronize()
+    per = out["per_image"].cpu().numpy()
+    ptr = out["graph"].node_ptr.cpu().numpy()
+    for i in range(B):
+        img, lab, can = hb.images[i].numpy(), hb.labels[i].numpy(), hb.canny[i].numpy()
+        x, ei, w, id_of = org.build_region_graph(img.astype(np.float64), lab.astype(np.int64), can.astype(bool))
+        with torch.no_grad():
+            r = ognn.rg_gnn_forward(gsd, torch.from_numpy(x), torch.from_numpy(ei), torch.from_numpy(w))
+            mask, inst, edge, score, _, _ = ofus.detector_forward(fsd, r["node_emb"][None], kg.cpu()[None])
+        n0, n1 = ptr[i], ptr[i + 1]
+        np.testing.assert_allclose(out["node_mask_out"][n0:n1].cpu().numpy(), r["mask_out"].numpy(), rtol=0, atol=1e-2)
+        np.testing.assert_allclose(out["mask_out"][i].cpu().numpy(), mask[0].numpy(), rtol=0, atol=1e-2)
+        np.testing.assert_allclose(out["score_out"][i].cpu().numpy(), score[0].numpy(), rtol=0, atol=1e-2)
+        gt = hb.gt[i].numpy() / 255.0
+        # (1) the reductions alone: oracle paint of the DEVICE logits -> counts must be bit-exact
+        pm_dev = om.paint_mask(out["node_mask_out"][n0:n1].cpu().numpy(), lab, label_offset_fix=fix, id_of_label=id_of)
+        np.testing.assert_allclose(out["pred_mask"][i].cpu().numpy(), pm_dev, rtol=0, atol=1e-6)
+        pm32 = out["pred_mask"][i].cpu().numpy().astype(np.float64)
+        tp, sp, sg, neq, n = om.confusion_counts(pm32, gt)
+        assert out["counts"][i].cpu().tolist() == [tp, sp, sg, neq]
+        ref = om.metrics_from_counts(tp, sp, sg, neq, n, float(np.abs(pm32 - gt).sum()))
+        for j, k in enumerate(om.KEYS):
+            assert abs(per[i, j] - ref[k]) < (1e-9 if k == "mae" else 1e-15), k
+        # (2) end to end against the all-oracle chain: BASELINE tolerance on MAE
+        e2e = om.evaluate_segmentation(om.paint_mask(r["mask_out"].numpy(), lab, label_offset_fix=fix, id_of_label=id_of), gt)
+        assert abs(per[i, 5] - e2e["mae"]) <= 1e-3
+    # batch statistics from the partial-sum vector
+    from camouflage_multimodal_b200.pipeline import summarize
+    s = summarize(out["partial"])
+    for j, k in enumerate(om.KEYS):
+        assert abs(s[k] - per[:, j].mean()) < 1e-12 and abs(s[f"{k}_std"] - per[:, j].std()) < 1e-9
+
+
+def test_pipeline_batch32_properties(models):
+    """Config-2 batch size: idempotence across calls and buffer reuse, counts add up, probabilities in [0,1]."""
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, HostStager
+    gnn, det, kg, _, _ = models
+    B = 32
+    hb = synth.make_batch(300, B, seed=1234)
+    pipe = EvalPipeline(gnn, det, kg, label_cap=544)
+    st = HostStager(B, 256, 256, torch.device("cuda"))
+    st.fill(hb)
+    out = st.step(pipe)
+    torch.cuda.synchronize()
+    first = {k: out[k].clone() for k in ("counts", "per_image", "mask_out", "partial")}
+    out = st.step(pipe)
+    torch.cuda.synchronize()
+    assert torch.equal(first["counts"], out["counts"])
+    assert torch.allclose(first["per_image"], out["per_image"], atol=1e-12)
+    assert torch.equal(first["mask_out"], out["mask_out"])
+    assert torch.equal(st.h_mask_out, out["mask_out"].cpu())
+    c = out["counts"].cpu().numpy()
+    assert (c[:, 0] <= np.minimum(c[:, 1], c[:, 2])).all() and (c[:, 3] <= 65536).all()
+    gt_pos = (hb.gt.numpy() > 127).reshape(B, -1).sum(1)
+    assert np.array_equal(c[:, 2], gt_pos)
+    p = out["mask_prob"][: int(out["graph"].node_ptr[-1])]
+    assert (p >= 0).all() and (p <= 1).all()
+    assert int(out["graph"].status.item()) == 0

@@ -1,0 +1,138 @@
+"""GPU parity: region adjacency / compaction / features / edge weights vs the CPU oracle (A1-A4).
+Integer outputs bit-exact; features abs <= 1e-5; weights rel <= 1e-5 (float32 exp of
+features that themselves carry the 1e-7 feature tolerance)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from camouflage_multimodal_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_graph(img, lab, can):
+    from oracle import region_graph as org
+    return org.build_region_graph(img.astype(np.float64), lab.astype(np.int64), can.astype(bool))
+
+
+def _check_image(g, b, img, lab, can):
+    x, ei, w, id_of = _oracle_graph(img, lab, can)
+    n0, n1 = int(g.node_ptr[b]), int(g.node_ptr[b + 1])
+    e0, e1 = int(g.edge_ptr[b]), int(g.edge_ptr[b + 1])
+    assert n1 - n0 == x.shape[0]
+    assert e1 - e0 == ei.shape[1]
+    got_ei = g.edge_index[:, e0:e1].cpu().numpy() - n0           # global ids -> local
+    assert np.array_equal(got_ei, ei), "edge_index differs from the canonical oracle order"
+    got_id = g.id_of_label[b].cpu().numpy()
+    assert np.array_equal(got_id[: len(id_of)], id_of) and (got_id[len(id_of):] == -1).all()
+    np.testing.assert_allclose(g.x[n0:n1].cpu().numpy(), x, rtol=0, atol=1e-5)
+    np.testing.assert_allclose(g.edge_w[e0:e1].cpu().numpy(), w.reshape(-1), rtol=1e-5, atol=1e-9)
+    # CSR view is the same edge list
+    rp = g.csr_row_ptr[n0:n1 + 1].cpu().numpy()
+    assert rp[0] == e0 and rp[-1] == e1 and np.array_equal(np.repeat(np.arange(n1 - n0), np.diff(rp)), ei[0])
+    assert np.array_equal(g.csr_col[e0:e1].cpu().numpy() - n0, ei[1])
+    assert (g.batch_vec[n0:n1] == b).all()
+
+
+def test_batch_matches_oracle():
+    from camouflage_multimodal_b200.region_graph import build_region_graphs
+    b = synth.make_batch(0, 4, seed=1234)
+    d = b.to("cuda")
+    g = build_region_graphs(d.images, d.labels, d.canny, label_cap=544)
+    n, e = g.counts()
+    assert n == int(b.n_regions.sum())
+    for i in range(4):
+        _check_image(g, i, b.images[i].numpy(), b.labels[i].numpy(), b.canny[i].numpy())
+
+
+def test_default_label_cap_and_reuse():
+    from camouflage_multimodal_b200.region_graph import build_region_graphs
+    b = synth.make_batch(10, 2, seed=1234).to("cuda")
+    g1 = build_region_graphs(b.images, b.labels, b.canny)
+    g2 = build_region_graphs(b.images, b.labels, b.canny, label_cap=g1.label_cap, out=g1)
+    assert g2 is g1
+    n, e = g2.counts()
+    assert n == int(b.n_regions.sum()) and e > 0
+
+
+@pytest.mark.parametrize("name", ["A", "B"])
+def test_golden_cases(golden_dir, name):
+    """The reference's own outputs (tests/golden/region_graph.npz): case B has label 0, gaps between labels
+    and a block of negative labels."""
+    from camouflage_multimodal_b200.region_graph import create_region_graph
+    from oracle import rag as orag
+    z = np.load(os.path.join(golden_dir, "region_graph.npz"))
+    spec = {"A": dict(index=3, n_regions=None), "B": dict(index=5, n_regions=23)}[name]
+    sb = synth.make_batch(spec["index"], 1, seed=1234, n_regions=spec["n_regions"])
+    lab = z[f"{name}.labels"].astype(np.int64)
+    data, seg = create_region_graph(sb.images[0].numpy(), 500, segments=lab, edges=sb.canny[0].numpy())
+    ref_ei, ref_w = orag.canonical_sort(z[f"{name}.edge_index"], z[f"{name}.edge_attr"].reshape(-1))
+    assert data.edge_index.dtype == torch.int64 and data.x.dtype == torch.float32
+    assert np.array_equal(data.edge_index.cpu().numpy(), ref_ei)
+    np.testing.assert_allclose(data.x.cpu().numpy(), z[f"{name}.x"], rtol=0, atol=1e-5)
+    assert tuple(data.edge_attr.shape) == (ref_ei.shape[1], 1)
+    np.testing.assert_allclose(data.edge_attr.cpu().numpy().reshape(-1), ref_w, rtol=2e-5, atol=1e-9)
+    assert seg is lab
+
+
+def test_edge_cases():
+    from camouflage_multimodal_b200.region_graph import build_region_graphs, create_region_graph
+    # one region covering the whole frame: one node, no edges (reference returns zeros((2,0)), :237)
+    img = np.random.default_rng(0).random((32, 48, 3)).astype(np.float32)
+    lab = np.full((32, 48), 3, np.int32)
+    can = np.zeros((32, 48), np.uint8)
+    data, _ = create_region_graph(img, segments=lab, edges=can)
+    assert tuple(data.x.shape) == (1, 15) and tuple(data.edge_index.shape) == (2, 0)
+    assert tuple(data.edge_attr.shape) == (0, 1)
+    x, ei, w, _ = _oracle_graph(img, lab, can)
+    np.testing.assert_allclose(data.x.cpu().numpy(), x, atol=1e-5)
+    # every pixel its own region (maximum node count), ragged non-square frame
+    lab2 = np.arange(9 * 7, dtype=np.int32).reshape(9, 7)
+    img2 = np.random.default_rng(1).random((9, 7, 3)).astype(np.float32)
+    can2 = (np.random.default_rng(2).random((9, 7)) < 0.3).astype(np.uint8)
+    data2, _ = create_region_graph(img2, segments=lab2, edges=can2)
+    x2, ei2, w2, _ = _oracle_graph(img2, lab2, can2)
+    assert np.array_equal(data2.edge_index.cpu().numpy(), ei2)
+    np.testing.assert_allclose(data2.x.cpu().numpy(), x2, atol=1e-5)
+    np.testing.assert_allclose(data2.edge_attr.cpu().numpy().reshape(-1), w2.reshape(-1), rtol=1e-5, atol=1e-9)
+    # overflow is reported, not written out of bounds
+    t = lambda a: torch.as_tensor(a).cuda()[None]
+    g = build_region_graphs(t(img2), t(lab2), t(can2), label_cap=10)
+    with pytest.raises(Exception, match="label >= label_cap"):
+        g.counts()
+    # all labels negative: no nodes at all
+    g0 = build_region_graphs(t(img2), t(-np.ones_like(lab2)), t(can2), label_cap=4)
+    assert g0.counts() == (0, 0)
+
+
+def test_needs_label_map():
+    from camouflage_multimodal_b200.region_graph import create_region_graph
+    with pytest.raises(NotImplementedError):
+        create_region_graph(np.zeros((8, 8, 3), np.float32))
+
+
+def test_full_size_properties():
+    """BASELINE config 2 batch size: structural properties that need no oracle."""
+    from camouflage_multimodal_b200.region_graph import build_region_graphs
+    b = synth.make_batch(100, 32, seed=1234, device="cuda")
+    g = build_region_graphs(b.images, b.labels, b.canny, label_cap=544)
+    n, e = g.counts()
+    assert n == int(b.n_regions.sum())
+    ei = g.edge_index[:, :e]
+    assert (ei[0] != ei[1]).all()                                   # no self loops
+    key = ei[0] * n + ei[1]
+    assert (key[1:] > key[:-1]).all()                               # sorted, unique
+    rev = ei[1] * n + ei[0]
+    assert torch.equal(torch.sort(rev).values, key)                 # symmetric
+    assert torch.equal(g.batch_vec[:n], torch.repeat_interleave(torch.arange(32, device="cuda"),
+                                                                torch.as_tensor(b.n_regions, device="cuda")))
+    x = g.x[:n]
+    assert torch.isfinite(x).all() and (x[:, 10] > 0).all()
+    assert abs(float(x[:, 10].sum()) - 32.0) < 1e-3                 # region sizes tile every image
+    w = g.edge_w[:e]
+    assert (w > 0).all() and (w <= 1).all()
+    # both directions of an edge carry the same weight
+    order = torch.argsort(rev)
+    assert torch.equal(w[order], w)
