@@ -1,0 +1,374 @@
+"""bench.py -- images/sec of the region-graph hot path (BASELINE.json configs[1]: synthetic COD10K-test-shaped
+images, batch 32 forward + metrics) on N B200s, with the kernel roofline and the CPU baseline beside it.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+      bench.py --gpus N --steps K --warmup W
+
+A step = one batch of 32 images per GPU through: label map -> adjacency/edge list -> 15-d region features ->
+edge weights -> RG-GNN -> RGxKG cross-attention fusion + heads -> pixel-mask paint -> metric reductions.
+Images shard by index across ranks (weak scaling); KG rows and weights are broadcast once; the only
+data-path collective is one all-reduce of the 15-element metric partial-sum vector at the end.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+BATCH = 32
+H = W = 256
+LABEL_CAP = 544
+SET_SIZE = 2026            # COD10K test split (BASELINE.json configs[1])
+METRIC = "images/sec RG-GNN + RGxKG cross-attn fusion (graph build + GNN + fusion + heads + paint + metrics)"
+
+
+def make_models(seed=0):
+    """Random-init weights of the reference architecture (BASELINE.json: no checkpoints ship)."""
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
+    from camouflage_multimodal_b200.region_graph import RegionGraphGNN
+    torch.manual_seed(seed)
+    gnn = RegionGraphGNN(15, 128, 2).eval()
+    with torch.no_grad():
+        for bn in (gnn.bn1, gnn.bn2, gnn.bn3, gnn.bn4):
+            bn.running_mean.normal_(0, 0.1)
+            bn.running_var.uniform_(0.75, 1.25)
+    cfg = {"rg_dim": 128, "kg_dim": 128, "hidden_dim": 256, "num_heads": 8, "fusion_type": "cross_attention",
+           "num_classes": 2, "dropout": 0.3}     # configs/multimodal_config.yaml:14-21
+    det = build_multimodal_model(cfg).eval()
+    return gnn, det
+
+
+def load_kg():
+    """The 13 bundled KG embeddings (committed fixture) -> [13,128]; synthetic stand-in if absent."""
+    from camouflage_multimodal_b200 import synth
+    p = os.path.join(ROOT, "tests", "golden", "kg_embeddings.npz")
+    if os.path.exists(p):
+        return torch.from_numpy(np.load(p)["kg"]).reshape(-1, 128).float(), "bundled 13x128"
+    return synth.synthetic_kg(13), "synthetic 13x128"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, f"/tmp/cm_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=open(self.path, "w"),
+                                         stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path).read().splitlines():
+            f = [t.strip() for t in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops_sustained", 1400.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, 1590.0, "fallback (B200_PROFILING.md)"
+
+
+def kernel_work(name, B, M, E, K):
+    """Algorithmic work of ONE step's launches of a kernel: ("hbm", bytes) or ("tensor", flops).
+    M = nodes, E = directed edges in the batch, K = KG rows.  Figures follow SURVEY.md 8(d) / DESIGN.md."""
+    px = B * H * W
+    D, d = 256, 128
+    gk = B * K
+    lin_flops = 2.0 * M * (60 * 128 + 3 * 128 * 128 + 128 * 128 + 128 * 192)                        # GNN dense layers
+    lin_flops += 2.0 * M * (d * D + D * D + D * D + D * 2 * D + 2 * D * D + D * 2 * D)               # node-side fusion
+    lin_flops += 2.0 * K * (d * D + D * 2 * D + D * D) + 2.0 * gk * (D * D + 2 * (D * 2 * D))        # kg-side
+    lin_flops += 2.0 * B * (2 * D * D + D * D + 4 * D * (D // 2))                                    # fusion MLP + heads
+    table = {
+        "linear": ("tensor", lin_flops),
+        "rag_scan": ("hbm", 4.0 * px),
+        "rag_compact": ("hbm", 4.0 * B * LABEL_CAP * (4 + 17 + 2)),
+        "rag_emit": ("hbm", 4.0 * B * LABEL_CAP * 17 + 4.0 * E + 28.0 * M),
+        "node_features": ("hbm", px * (12.0 + 4.0 + 1.0) + 60.0 * M),
+        "edge_weights": ("hbm", 60.0 * M + 8.0 * E),
+        "paint_metrics": ("hbm", px * (4.0 + 1.0) + 4.0 * M),
+        "gat_logits": ("hbm", 60.0 * M + 32.0 * M),
+        "gat_aggregate": ("hbm", 60.0 * M + 4.0 * E + 240.0 * M),
+        "gcn_norm": ("hbm", 8.0 * E + 4.0 * M),
+        "gcn_aggregate": ("hbm", 3 * (2 * 512.0 * M + 8.0 * E)),
+        "layernorm": ("hbm", 2 * 1024.0 * (M + gk)),
+        "attn_rg2kg": ("hbm", 2 * 1024.0 * M),
+        "attn_kg2rg": ("hbm", 2048.0 * M + 1024.0 * gk),
+        "segment_mean": ("hbm", 1024.0 * M + 512.0 * M),
+    }
+    return table.get(name, (None, None))
+
+
+def cpu_state_dicts(gnn, det):
+    return ({k: v.detach().cpu().clone() for k, v in gnn.state_dict().items()},
+            {k: v.detach().cpu().clone() for k, v in det.state_dict().items()})
+
+
+def run_cpu_baseline(gnn_sd, fusion_sd, kg, n_images=6):
+    """The oracle port of the reference's single-threaded per-image loop, timed on this host (1 core for the
+    Python region loop; the dense layers use torch's default intra-op threads like the reference would)."""
+    from camouflage_multimodal_b200 import synth
+    from oracle import cpu_path
+    sample = synth.make_batch(0, n_images, seed=1234)
+    sec, _ = cpu_path.time_images(sample, gnn_sd, fusion_sd, kg, faithful=True, processes=1)
+    return {"value": n_images / sec, "unit": "images/sec", "cores": 1, "kind": "port",
+            "sample": f"{n_images} images of the same synthetic set through the oracle restatement of the reference's "
+                      f"per-image CPU loop (full-frame per-region masks as in extract_rg_embeddings.py:154-211), {sec:.1f} s",
+            "host_cpus": os.cpu_count(), "torch_threads": torch.get_num_threads()}
+
+
+def reference_arm(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port -- the reference's own
+    files need scikit-image / torch-geometric, which are not installable here) on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+
+    from camouflage_multimodal_b200 import synth
+    from oracle import cpu_path
+    gnn, det = make_models()
+    gsd, fsd = cpu_state_dicts(gnn, det)
+    kg, kg_src = load_kg()
+    cores = os.cpu_count() or 1
+    per_step = max(1, min(cores, BATCH))
+    torch.set_num_threads(1)
+    total = (args.steps + args.warmup) * per_step
+    data = synth.make_batch(0, total, seed=1234)
+    items = [(data.images[i].numpy(), data.labels[i].numpy(), data.canny[i].numpy(), data.gt[i].numpy(), gsd, fsd, kg, True)
+             for i in range(total)]
+    times = []
+    with mp.get_context("fork").Pool(per_step) as pool:
+        for s in range(args.steps + args.warmup):
+            t0 = time.perf_counter()
+            pool.map(cpu_path._worker, items[s * per_step:(s + 1) * per_step], chunksize=1)
+            dt = time.perf_counter() - t0
+            if s >= args.warmup:
+                times.append(dt)
+    sec = sum(times)
+    value = args.steps * per_step / sec
+    sample = (f"{per_step} images per step (one per worker process, {cores} host cpus) of the same synthetic set, "
+              f"oracle port of the reference's per-image CPU loop")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus, kg_src),
+        "cpu_baseline": {"value": value, "unit": "images/sec", "cores": per_step, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_config(n_gpus, kg_src):
+    return {"workload": f"BASELINE configs[1]: synthetic COD10K-test-shaped set ({SET_SIZE} images, 256x256), batch {BATCH} "
+                        f"per GPU: graph build + RG-GNN + RGxKG cross-attention fusion + heads + paint + utils/metrics",
+            "batch_per_gpu": BATCH, "global_batch": BATCH * n_gpus, "regions_per_image": "303-530 (empirical histogram)",
+            "kg": kg_src, "parallelism": f"dp{n_gpus} (images sharded i mod N, metric partial sums all-reduced once)",
+            "l2": "6 distinct input batches per GPU (226 MB) rotated so every step's inputs come from HBM, not L2"}
+
+
+def b200_arm(args):
+    import torch.distributed as dist
+
+    from camouflage_multimodal_b200 import _lib, synth
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, HostStager, allreduce_partials, summarize
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.check(_lib.load().cm_device_check(), "cm_device_check")
+
+    gnn, det = make_models()
+    kg, kg_src = load_kg()
+    gnn, det, kg = gnn.to(dev), det.to(dev), kg.to(dev)
+    if world > 1:   # weights and KG rows broadcast once from rank 0
+        for t in list(gnn.state_dict().values()) + list(det.state_dict().values()) + [kg]:
+            dist.broadcast(t, src=0)
+    pipe = EvalPipeline(gnn, det, kg, label_cap=LABEL_CAP)
+
+    # rank r owns images i with i mod world == r; batch j of the rank = its images [j*32, (j+1)*32)
+    n_pool = args.pool
+    pool = []
+    for j in range(n_pool):
+        first = (j * world + rank) * BATCH
+        pool.append(synth.make_batch(first % max(SET_SIZE - BATCH, 1), BATCH, seed=1234, device=dev))
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    acc = torch.zeros(15, dtype=torch.float64, device=dev)
+
+    def step(s):
+        b = pool[s % n_pool]
+        out = pipe.run(b.images, b.labels, b.canny, b.gt)
+        acc.add_(out["partial"])
+        return out
+
+    for s in range(args.warmup):
+        step(s)
+    acc.zero_()
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for s in range(args.steps):
+        out = step(s)
+    total = acc.clone()
+    allreduce_partials(total)
+    e1.record()
+    barrier()
+    clk = clocks.stop()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    value = args.steps * BATCH * world / (ms_total / 1e3)
+    status = int(out["graph"].status.item())
+    if status:
+        raise SystemExit(f"graph build overflow status {status}")
+    summary = summarize(total)
+
+    # ---- end to end through the host-facing call: pinned host inputs, H2D + path + D2H every step
+    stager = HostStager(BATCH, H, W, dev)
+    host_pool = [(b.images.cpu().pin_memory(), b.labels.cpu().pin_memory(), b.canny.cpu().pin_memory(), b.gt.cpu().pin_memory())
+                 for b in pool]
+
+    def e2e_step(s):
+        hi, hl, hc, hg = host_pool[s % n_pool]
+        stager.h_images, stager.h_labels, stager.h_canny, stager.h_gt = hi, hl, hc, hg
+        return stager.step(pipe)
+
+    for s in range(args.warmup):
+        e2e_step(s)
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        e2e_step(s)
+    torch.cuda.synchronize()          # the D2H result of the last step has landed
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = args.steps * BATCH * world / float(e2e_s.item())
+
+    # ---- per-kernel durations: CUDA events around every launch, on the launching stream (separate pass)
+    n_nodes = int(out["graph"].node_ptr[-1].item())
+    n_edges = int(out["graph"].edge_ptr[-1].item())
+    _lib.timing_enable(True)
+    for s in range(args.steps):
+        step(s)
+    torch.cuda.synchronize()
+    rep = _lib.timing_report()
+    _lib.timing_enable(False)
+    hbm_peak, tf_peak, peak_src = measured_peaks()
+    kernels = {}
+    for name, (cnt, tot_ms) in sorted(rep.items(), key=lambda kv: -kv[1][1]):
+        per_step_ms = tot_ms / args.steps
+        bound, work = kernel_work(name, BATCH, n_nodes, n_edges, kg.shape[0])
+        k = {"launches_per_step": cnt / args.steps, "ms_per_step": per_step_ms}
+        if bound == "hbm":
+            k.update(bound="hbm", achieved=work / (per_step_ms * 1e-3) / 1e9, unit="GB/s")
+            k["frac"] = k["achieved"] / hbm_peak
+        elif bound == "tensor":
+            k.update(bound="tensor", achieved=work / (per_step_ms * 1e-3) / 1e12, unit="TFLOP/s")
+            k["frac"] = k["achieved"] / tf_peak
+        kernels[name] = k
+    launches_per_step = sum(v[0] for v in rep.values()) / args.steps
+    top = next(iter(kernels))
+    tk = kernels[top]
+    roofline = {"kernel": top, "bound": tk.get("bound"), "achieved": tk.get("achieved"),
+                "peak": hbm_peak if tk.get("bound") == "hbm" else tf_peak, "unit": tk.get("unit"), "frac": tk.get("frac"),
+                "traffic": None, "peak_source": peak_src, "launches_per_step": tk["launches_per_step"],
+                "ms_per_step": tk["ms_per_step"], "share_of_kernel_time": tk["ms_per_step"] / sum(v["ms_per_step"] for v in kernels.values())}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(world, kg_src), "clocks": clk,
+            "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": stager.h2d_bytes,
+                    "d2h_bytes_per_step": stager.d2h_bytes},
+            "gpu_launches": int(round(launches_per_step * args.steps)),
+            "roofline": roofline, "kernels": kernels,
+            "nodes_per_step": n_nodes, "edges_per_step": n_edges, "metrics_summary": summary,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            gsd, fsd = cpu_state_dicts(gnn, det)
+            line["cpu_baseline"] = run_cpu_baseline(gsd, fsd, kg.cpu(), args.cpu_images)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pool", type=int, default=6, help="distinct input batches rotated per GPU (6 x 37.7 MB > L2)")
+    ap.add_argument("--cpu-images", type=int, default=6)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

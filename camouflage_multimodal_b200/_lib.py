@@ -55,6 +55,8 @@ SIGNATURES = {
     "cm_last_error": (C.c_char_p, []),
     "cm_abi_version": (_i, []),
     "cm_device_check": (_i, []),
+    "cm_timing_enable": (None, [_i]),
+    "cm_timing_report": (_i, [C.c_char_p, _i]),
     "cm_rag_workspace_bytes": (_sz, [_i, _i]),
     "cm_rag_build": (_i, [_fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp]),
     "cm_node_features": (_i, [_fp, _fp, _fp, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
@@ -126,3 +128,18 @@ def require_cuda(t: torch.Tensor, name: str) -> None:
 
 def f32c(t: torch.Tensor) -> torch.Tensor:
     return t.detach().to(torch.float32).contiguous()
+
+
+def timing_enable(on: bool) -> None:
+    load().cm_timing_enable(1 if on else 0)
+
+
+def timing_report() -> dict:
+    """{kernel name: (launches, total_ms)} since the last report."""
+    buf = C.create_string_buffer(1 << 16)
+    load().cm_timing_report(buf, len(buf))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, cnt, ms = line.split()
+        out[name] = (int(cnt), float(ms))
+    return out

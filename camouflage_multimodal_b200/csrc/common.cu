@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <vector>
+
 #include "common.cuh"
 
 namespace cm {
@@ -63,9 +65,73 @@ int post_launch(const char* what) {
     return CM_OK;
 }
 
+// ---------------------------------------------------------------------------------- kernel timing
+struct TimingRec {
+    const char* name;
+    cudaEvent_t a, b;
+};
+static bool g_timing = false;
+static std::vector<TimingRec> g_recs;
+static std::vector<cudaEvent_t> g_free_events;
+
+static cudaEvent_t take_event() {
+    if (!g_free_events.empty()) {
+        cudaEvent_t e = g_free_events.back();
+        g_free_events.pop_back();
+        return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+
+TimedLaunch::TimedLaunch(const char* name, cudaStream_t s) : slot(-1), st(s) {
+    if (!g_timing) return;
+    TimingRec r{name, take_event(), take_event()};
+    cudaEventRecord(r.a, st);
+    slot = (int)g_recs.size();
+    g_recs.push_back(r);
+}
+TimedLaunch::~TimedLaunch() {
+    if (slot >= 0) cudaEventRecord(g_recs[slot].b, st);
+}
+
 }  // namespace cm
 
 extern "C" {
+void cm_timing_enable(int on) { cm::g_timing = on != 0; }
+// Writes "name count total_ms\n" per kernel name into buf (synchronises the recorded events), clears the
+// records and returns the number of bytes written (excluding the terminator).
+int cm_timing_report(char* buf, int cap) {
+    using namespace cm;
+    struct Agg { const char* name; int count; double ms; };
+    std::vector<Agg> agg;
+    for (auto& r : g_recs) {
+        cudaEventSynchronize(r.b);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        bool found = false;
+        for (auto& a : agg)
+            if (strcmp(a.name, r.name) == 0) {
+                a.count++;
+                a.ms += ms;
+                found = true;
+                break;
+            }
+        if (!found) agg.push_back({r.name, 1, (double)ms});
+        g_free_events.push_back(r.a);
+        g_free_events.push_back(r.b);
+    }
+    g_recs.clear();
+    int off = 0;
+    if (buf && cap > 0) buf[0] = 0;
+    for (auto& a : agg) {
+        int n = snprintf(buf ? buf + off : nullptr, buf && cap > off ? cap - off : 0, "%s %d %.6f\n", a.name, a.count, a.ms);
+        if (n < 0 || off + n >= cap) break;
+        off += n;
+    }
+    return off;
+}
 const char* cm_last_error(void) { return cm::g_err; }
 int cm_abi_version(void) { return 1; }
 int cm_device_check(void) { return cm::check_device(); }

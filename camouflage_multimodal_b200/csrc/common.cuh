@@ -13,6 +13,18 @@ int check_device();   // CM_OK or CM_ERR_DEVICE (cached per device)
 int num_sms();
 int post_launch(const char* what);   // cudaPeekAtLastError -> CM_ERR_LAUNCH + message
 
+// Optional per-kernel timing (cm_timing_enable): CUDA events recorded on the launching stream around every
+// kernel launch, aggregated by kernel name in cm_timing_report.  Off by default; costs nothing when off.
+struct TimedLaunch {
+    int slot;
+    cudaStream_t st;
+    TimedLaunch(const char* name, cudaStream_t s);
+    ~TimedLaunch();
+};
+#define CM_TIMED_CAT2(a, b) a##b
+#define CM_TIMED_CAT(a, b) CM_TIMED_CAT2(a, b)
+#define CM_TIMED(name, st) cm::TimedLaunch CM_TIMED_CAT(_cm_timed_, __LINE__)(name, st)
+
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

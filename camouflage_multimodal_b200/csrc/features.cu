@@ -236,8 +236,11 @@ extern "C" int cm_node_features(const float* image, const int32_t* labels, const
     CM_DEVICE_OR_RETURN();
     CM_REQUIRE(image && labels && canny && node_ptr && node_label && node_bbox && x, "cm_node_features: NULL pointer");
     CM_REQUIRE(batch > 0 && h > 0 && w > 0 && node_cap > 0 && norm_side > 0.f, "cm_node_features: bad sizes");
-    node_features_kernel<<<ceil_div(node_cap, 8), 256, 0, as_stream(stream)>>>(image, labels, canny, batch, h, w, node_ptr,
-                                                                              node_label, node_bbox, norm_side, x, node_cap);
+    {
+        CM_TIMED("node_features", as_stream(stream));
+        node_features_kernel<<<ceil_div(node_cap, 8), 256, 0, as_stream(stream)>>>(image, labels, canny, batch, h, w, node_ptr,
+                                                                                  node_label, node_bbox, norm_side, x, node_cap);
+    }
     return post_launch("cm_node_features");
 }
 
@@ -247,8 +250,11 @@ extern "C" int cm_edge_weights(const float* x, const int32_t* csr_row_ptr, const
     CM_DEVICE_OR_RETURN();
     CM_REQUIRE(x && csr_row_ptr && csr_col && n_nodes_dev && edge_w, "cm_edge_weights: NULL pointer");
     CM_REQUIRE(node_cap > 0, "cm_edge_weights: node_cap must be positive");
-    edge_weights_kernel<<<ceil_div(node_cap, 128), 128, 0, as_stream(stream)>>>(x, csr_row_ptr, csr_col, n_nodes_dev,
-                                                                               node_cap, edge_w);
+    {
+        CM_TIMED("edge_weights", as_stream(stream));
+        edge_weights_kernel<<<ceil_div(node_cap, 128), 128, 0, as_stream(stream)>>>(x, csr_row_ptr, csr_col, n_nodes_dev,
+                                                                                   node_cap, edge_w);
+    }
     return post_launch("cm_edge_weights");
 }
 
@@ -294,12 +300,24 @@ extern "C" int cm_csr_from_edge_index(const int64_t* edge_index, int64_t row_str
     const long long* src = reinterpret_cast<const long long*>(edge_index);
     const long long* dst = src + row_stride;
     if (n_edges > 0)
-        csr_count_kernel<<<ceil_div(n_edges, 256), 256, 0, st>>>(src, dst, n_nodes, n_edges, ws.deg, ws.self_idx, status);
-    csr_scan_kernel<<<1, 1024, 0, st>>>(ws.deg, n_nodes, csr_row_ptr);
+        {
+            CM_TIMED("csr_count", st);
+            csr_count_kernel<<<ceil_div(n_edges, 256), 256, 0, st>>>(src, dst, n_nodes, n_edges, ws.deg, ws.self_idx, status);
+        }
+    {
+        CM_TIMED("csr_scan", st);
+        csr_scan_kernel<<<1, 1024, 0, st>>>(ws.deg, n_nodes, csr_row_ptr);
+    }
     if (n_edges > 0)
-        csr_fill_kernel<<<ceil_div(n_edges, 256), 256, 0, st>>>(src, dst, n_nodes, n_edges, csr_row_ptr, ws.deg, ws.tmp_edge);
+        {
+            CM_TIMED("csr_fill", st);
+            csr_fill_kernel<<<ceil_div(n_edges, 256), 256, 0, st>>>(src, dst, n_nodes, n_edges, csr_row_ptr, ws.deg, ws.tmp_edge);
+        }
     if (n_nodes > 0)
-        csr_finish_kernel<<<ceil_div(n_nodes, 128), 128, 0, st>>>(src, edge_w, n_nodes, csr_row_ptr, ws.tmp_edge, ws.self_idx,
-                                                                 csr_col, csr_w, self_w);
+        {
+            CM_TIMED("csr_finish", st);
+            csr_finish_kernel<<<ceil_div(n_nodes, 128), 128, 0, st>>>(src, edge_w, n_nodes, csr_row_ptr, ws.tmp_edge, ws.self_idx,
+                                                                     csr_col, csr_w, self_w);
+        }
     return post_launch("cm_csr_from_edge_index");
 }

@@ -216,7 +216,10 @@ static int check_fusion(const cm_fusion_params* p) {
 template <int CPL>
 static void launch_rg2kg(const float* q, const float* kv, int D, int heads, const int* node_ptr, int G, int M, int Kk, int shared,
                          float* ctx, float* attn, cudaStream_t st) {
-    attn_rg2kg_kernel<CPL><<<ceil_div(M, 8), 256, 0, st>>>(q, kv, D, heads, node_ptr, G, M, Kk, shared, ctx, attn);
+    {
+        CM_TIMED("attn_rg2kg", st);
+        attn_rg2kg_kernel<CPL><<<ceil_div(M, 8), 256, 0, st>>>(q, kv, D, heads, node_ptr, G, M, Kk, shared, ctx, attn);
+    }
 }
 
 static int detector_heads(const cm_fusion_params* p, const float* fused, int final_dim, int G, float* hid, float* mask_out,
@@ -343,10 +346,16 @@ extern "C" int cm_fusion_forward(const cm_fusion_params* p, const float* rg, con
     if ((rc = launch_linear(l, st)) != CM_OK) return rc;
     l = Linear(); l.M = M; l.m_dev = m_dev; l.A = r; l.lda = D; l.K = D; l.W = p->k2r_in_w + (size_t)D * D; l.bias = p->k2r_in_b + D; l.N = 2 * D; l.C = w.k2v2; l.ldc = 2 * D;
     if ((rc = launch_linear(l, st)) != CM_OK) return rc;
-    attn_kg2rg_kernel<<<ceil_div((long long)GK * heads, 8), 256, 0, st>>>(w.q2, w.k2v2, D, heads, node_ptr, G, Kk, shared, w.ctx2, w.stat);
+    {
+        CM_TIMED("attn_kg2rg", st);
+        attn_kg2rg_kernel<<<ceil_div((long long)GK * heads, 8), 256, 0, st>>>(w.q2, w.k2v2, D, heads, node_ptr, G, Kk, shared, w.ctx2, w.stat);
+    }
     if ((rc = post_launch("attn_kg2rg")) != CM_OK) return rc;
     if (attn_kg2rg) {
-        attn_kg2rg_weights_kernel<<<ceil_div(GK, 8), 256, 0, st>>>(w.q2, w.k2v2, D, heads, node_ptr, G, Kk, shared, w.stat, attn_kg2rg);
+        {
+            CM_TIMED("attn_kg2rg_weights", st);
+            attn_kg2rg_weights_kernel<<<ceil_div(GK, 8), 256, 0, st>>>(w.q2, w.k2v2, D, heads, node_ptr, G, Kk, shared, w.stat, attn_kg2rg);
+        }
         if ((rc = post_launch("attn_kg2rg_weights")) != CM_OK) return rc;
     }
     l = Linear(); l.M = GK; l.A = w.ctx2; l.lda = D; l.K = D; l.W = p->k2r_out_w; l.bias = p->k2r_out_b; l.N = D; l.C = w.c2; l.ldc = D; l.residual = kp; l.ldr = D;

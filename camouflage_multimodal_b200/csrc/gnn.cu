@@ -241,7 +241,10 @@ extern "C" int cm_gnn_fold(const cm_gnn_params* p, void* folded, size_t folded_b
     CM_REQUIRE(folded, "cm_gnn_fold: NULL output");
     GnnFolded f = gnn_layout(p);
     CM_REQUIRE(folded_bytes >= f.total * sizeof(float), "cm_gnn_fold: blob %zu < %zu bytes", folded_bytes, f.total * sizeof(float));
-    gnn_fold_kernel<<<64, 256, 0, as_stream(stream)>>>(*p, f, reinterpret_cast<float*>(folded));
+    {
+        CM_TIMED("gnn_fold", as_stream(stream));
+        gnn_fold_kernel<<<64, 256, 0, as_stream(stream)>>>(*p, f, reinterpret_cast<float*>(folded));
+    }
     return post_launch("cm_gnn_fold");
 }
 
@@ -274,19 +277,31 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
     const int H = p->hidden, C = p->in_channels, hd = p->heads, M = node_cap;
     const int warps_grid = ceil_div(M, 8);
 
-    gat_logits_kernel<<<ceil_div((long long)M * hd, 256), 256, 0, st>>>(x, C, hd, blob + f.u_src, blob + f.u_dst, n_nodes_dev, M,
-                                                                       ws.a_src, ws.a_dst);
-    gat_aggregate_kernel<4><<<warps_grid, 256, 0, st>>>(x, C, csr_row_ptr, csr_col, ws.a_src, ws.a_dst, n_nodes_dev, M, ws.z);
+    {
+        CM_TIMED("gat_logits", st);
+        gat_logits_kernel<<<ceil_div((long long)M * hd, 256), 256, 0, st>>>(x, C, hd, blob + f.u_src, blob + f.u_dst, n_nodes_dev, M,
+                                                                           ws.a_src, ws.a_dst);
+    }
+    {
+        CM_TIMED("gat_aggregate", st);
+        gat_aggregate_kernel<4><<<warps_grid, 256, 0, st>>>(x, C, csr_row_ptr, csr_col, ws.a_src, ws.a_dst, n_nodes_dev, M, ws.z);
+    }
     Linear l;
     l.m_dev = n_nodes_dev;
     l.M = M;
     l.relu = 1;
     l.A = ws.z; l.lda = hd * C; l.K = hd * C; l.W = blob + f.wcat; l.bias = blob + f.bias1; l.N = H; l.C = ws.buf0; l.ldc = H;
     if ((rc = launch_linear(l, st)) != CM_OK) return rc;
-    gcn_norm_kernel<<<ceil_div(M, 256), 256, 0, st>>>(csr_row_ptr, csr_col, csr_w, self_w, n_nodes_dev, M, ws.dis);
+    {
+        CM_TIMED("gcn_norm", st);
+        gcn_norm_kernel<<<ceil_div(M, 256), 256, 0, st>>>(csr_row_ptr, csr_col, csr_w, self_w, n_nodes_dev, M, ws.dis);
+    }
     float* cur = ws.buf0;
     for (int k = 0; k < 3; ++k) {
-        gcn_aggregate_kernel<<<warps_grid, 256, 0, st>>>(cur, H, csr_row_ptr, csr_col, csr_w, self_w, ws.dis, n_nodes_dev, M, ws.buf1);
+        {
+            CM_TIMED("gcn_aggregate", st);
+            gcn_aggregate_kernel<<<warps_grid, 256, 0, st>>>(cur, H, csr_row_ptr, csr_col, csr_w, self_w, ws.dis, n_nodes_dev, M, ws.buf1);
+        }
         l.A = ws.buf1; l.lda = H; l.K = H; l.W = blob + f.convw[k]; l.bias = blob + f.convb[k]; l.N = H; l.C = ws.buf0; l.ldc = H;
         if ((rc = launch_linear(l, st)) != CM_OK) return rc;
         cur = ws.buf0;

@@ -84,8 +84,14 @@ int launch_linear(const Linear& a, cudaStream_t st) {
     dim3 grid(ceil_div(a.N, BN), ceil_div(a.M, BM));
     const bool vec = (a.K % 4 == 0) && (a.lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.A) & 15) == 0) &&
                      ((reinterpret_cast<uintptr_t>(a.W) & 15) == 0);
-    if (vec) linear_kernel<true><<<grid, 256, 0, st>>>(a);
-    else linear_kernel<false><<<grid, 256, 0, st>>>(a);
+    if (vec) {
+        CM_TIMED("linear", st);
+        linear_kernel<true><<<grid, 256, 0, st>>>(a);
+    }
+    else {
+        CM_TIMED("linear", st);
+        linear_kernel<false><<<grid, 256, 0, st>>>(a);
+    }
     return post_launch("linear");
 }
 
@@ -112,7 +118,10 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
 int launch_layernorm(const float* in, float* out, const float* gamma, const float* beta, int rows, int dim,
                      const int* rows_dev, cudaStream_t st) {
     if (rows <= 0) return CM_OK;
-    layernorm_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(in, out, gamma, beta, rows, dim, rows_dev);
+    {
+        CM_TIMED("layernorm", st);
+        layernorm_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(in, out, gamma, beta, rows, dim, rows_dev);
+    }
     return post_launch("layernorm");
 }
 
@@ -140,7 +149,10 @@ int launch_segment_mean(const float* in, int dim, const int* seg_ptr, int fixed_
                         cudaStream_t st) {
     if (n_seg <= 0) return CM_OK;
     dim3 grid(n_seg, ceil_div(dim, 128));
-    segment_mean_kernel<<<grid, 128, 0, st>>>(in, dim, seg_ptr, fixed_len, out, ldo);
+    {
+        CM_TIMED("segment_mean", st);
+        segment_mean_kernel<<<grid, 128, 0, st>>>(in, dim, seg_ptr, fixed_len, out, ldo);
+    }
     return post_launch("segment_mean");
 }
 
@@ -172,7 +184,10 @@ __global__ void __launch_bounds__(256) heads2_kernel(const float* __restrict__ h
 
 int launch_heads2(const float* hid, int ld, int rows, const int* rows_dev, const Heads2& h, cudaStream_t st) {
     if (rows <= 0) return CM_OK;
-    heads2_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(hid, ld, rows, rows_dev, h);
+    {
+        CM_TIMED("heads2", st);
+        heads2_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(hid, ld, rows, rows_dev, h);
+    }
     return post_launch("heads2");
 }
 

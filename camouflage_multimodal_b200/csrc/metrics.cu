@@ -176,8 +176,11 @@ extern "C" int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int ba
     cudaMemsetAsync(counts, 0, sizeof(int64_t) * 4 * batch, st);
     cudaMemsetAsync(abs_err, 0, sizeof(double) * batch, st);
     dim3 grid(metric_chunks((long long)h * w, batch), batch);
-    paint_metrics_kernel<<<grid, 256, 0, st>>>(labels, gt, h * w, mask_prob, node_ptr, id_of_label, label_cap, threshold,
-                                               pred_mask, reinterpret_cast<unsigned long long*>(counts), abs_err);
+    {
+        CM_TIMED("paint_metrics", st);
+        paint_metrics_kernel<<<grid, 256, 0, st>>>(labels, gt, h * w, mask_prob, node_ptr, id_of_label, label_cap, threshold,
+                                                   pred_mask, reinterpret_cast<unsigned long long*>(counts), abs_err);
+    }
     return post_launch("cm_paint_metrics");
 }
 
@@ -191,7 +194,10 @@ extern "C" int cm_metrics_dense(const float* pred, const float* gt, int batch, i
     cudaMemsetAsync(counts, 0, sizeof(int64_t) * 4 * batch, st);
     cudaMemsetAsync(abs_err, 0, sizeof(double) * batch, st);
     dim3 grid(metric_chunks(pixels, batch), batch);
-    metrics_dense_kernel<<<grid, 256, 0, st>>>(pred, gt, pixels, threshold, reinterpret_cast<unsigned long long*>(counts), abs_err);
+    {
+        CM_TIMED("metrics_dense", st);
+        metrics_dense_kernel<<<grid, 256, 0, st>>>(pred, gt, pixels, threshold, reinterpret_cast<unsigned long long*>(counts), abs_err);
+    }
     return post_launch("cm_metrics_dense");
 }
 
@@ -201,8 +207,11 @@ extern "C" int cm_metrics_finalize(const int64_t* counts, const double* abs_err,
     CM_DEVICE_OR_RETURN();
     CM_REQUIRE(counts && abs_err && (per_image || partial), "cm_metrics_finalize: NULL pointer");
     CM_REQUIRE(batch > 0 && pixels > 0, "cm_metrics_finalize: bad shape");
-    metrics_finalize_kernel<<<1, 256, 0, as_stream(stream)>>>(reinterpret_cast<const unsigned long long*>(counts), abs_err, batch,
-                                                              pixels, per_image, partial);
+    {
+        CM_TIMED("metrics_finalize", as_stream(stream));
+        metrics_finalize_kernel<<<1, 256, 0, as_stream(stream)>>>(reinterpret_cast<const unsigned long long*>(counts), abs_err, batch,
+                                                                  pixels, per_image, partial);
+    }
     return post_launch("cm_metrics_finalize");
 }
 
@@ -212,7 +221,10 @@ extern "C" int cm_class_confusion(const float* mask_out, const int64_t* true_cls
     CM_DEVICE_OR_RETURN();
     CM_REQUIRE(mask_out && true_cls && counts4, "cm_class_confusion: NULL pointer");
     CM_REQUIRE(n > 0 && num_classes >= 2, "cm_class_confusion: bad shape");
-    class_confusion_kernel<<<ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
-        mask_out, reinterpret_cast<const long long*>(true_cls), n, num_classes, reinterpret_cast<unsigned long long*>(counts4));
+    {
+        CM_TIMED("class_confusion", as_stream(stream));
+        class_confusion_kernel<<<ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
+            mask_out, reinterpret_cast<const long long*>(true_cls), n, num_classes, reinterpret_cast<unsigned long long*>(counts4));
+    }
     return post_launch("cm_class_confusion");
 }

@@ -317,15 +317,24 @@ extern "C" int cm_rag_build(const int32_t* labels, int batch, int h, int w, int 
         attr_done = true;
     }
     dim3 g1(ceil_div(h, rows), batch);
-    rag_scan_kernel<<<g1, 256, smem, st>>>(labels, h, w, label_cap, cw, rows, ws.box, ws.adj, status);
-    rag_compact_kernel<<<batch, 256, 0, st>>>(label_cap, cw, batch, ws.box, ws.adj, id_of_label, ws.rowstart,
-                                              ws.n_nodes, ws.n_edges, ws.ticket, node_ptr, edge_ptr, node_cap,
-                                              edge_cap, status);
+    {
+        CM_TIMED("rag_scan", st);
+        rag_scan_kernel<<<g1, 256, smem, st>>>(labels, h, w, label_cap, cw, rows, ws.box, ws.adj, status);
+    }
+    {
+        CM_TIMED("rag_compact", st);
+        rag_compact_kernel<<<batch, 256, 0, st>>>(label_cap, cw, batch, ws.box, ws.adj, id_of_label, ws.rowstart,
+                                                  ws.n_nodes, ws.n_edges, ws.ticket, node_ptr, edge_ptr, node_cap,
+                                                  edge_cap, status);
+    }
     const long long warps = (long long)batch * label_cap;
-    rag_emit_kernel<<<ceil_div(warps, 8), 256, 0, st>>>(label_cap, cw, batch, h, w, ws.box, ws.adj, id_of_label,
-                                                        ws.rowstart, node_ptr, edge_ptr, node_label, node_bbox,
-                                                        reinterpret_cast<long long*>(batch_vec), csr_row_ptr, csr_col,
-                                                        reinterpret_cast<long long*>(edge_index), local_ids, node_cap,
-                                                        edge_cap);
+    {
+        CM_TIMED("rag_emit", st);
+        rag_emit_kernel<<<ceil_div(warps, 8), 256, 0, st>>>(label_cap, cw, batch, h, w, ws.box, ws.adj, id_of_label,
+                                                            ws.rowstart, node_ptr, edge_ptr, node_label, node_bbox,
+                                                            reinterpret_cast<long long*>(batch_vec), csr_row_ptr, csr_col,
+                                                            reinterpret_cast<long long*>(edge_index), local_ids, node_cap,
+                                                            edge_cap);
+    }
     return post_launch("cm_rag_build");
 }

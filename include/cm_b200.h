@@ -44,6 +44,12 @@ int cm_abi_version(void);
 /* 0 when the current device is sm_100 (B200); CM_ERR_DEVICE otherwise. */
 int cm_device_check(void);
 
+/* Optional per-kernel timing for bench.py: when enabled, every kernel launch made by this library is
+ * bracketed by CUDA events on its launching stream.  cm_timing_report synchronises those events, writes one
+ * line "name launches total_ms" per kernel name into buf, clears the records and returns the bytes written. */
+void cm_timing_enable(int on);
+int cm_timing_report(char* buf, int cap);
+
 /* ------------------------------------------------------------------------------------------------
  * A1 + A2: region adjacency + label compaction.
  * Replaces skimage.graph.rag_mean_color(...).edges() (models/region_graph/extract_rg_embeddings.py:216,
