@@ -1,0 +1,38 @@
+// Dense layer on the 5th-generation tensor cores (sm_100a): bf16 operands staged by TMA (128B swizzle) into a
+// 4-stage shared-memory ring, tcgen05.mma accumulating fp32 in TMEM, epilogue read back with tcgen05.ld.
+//   out[m, n] = LN?( act( alpha * (sum_k A[m,k] W[n,k] + bias[n]) + residual[m,n] ) )
+// A [M,K] and W [N,K] are K-major bf16 (W is an nn.Linear weight).  M is a capacity; *m_dev the live rows.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace cm {
+
+struct Dense {
+    const __nv_bfloat16* A = nullptr;   // [M, lda] bf16, lda % 8 == 0
+    int lda = 0;
+    const __nv_bfloat16* W = nullptr;   // [N, K] bf16 (row stride K, K % 8 == 0)
+    int M = 0, N = 0, K = 0;
+    const int* m_dev = nullptr;
+    const float* bias = nullptr;        // [N]
+    float alpha = 1.f;
+    int relu = 0;
+    const __nv_bfloat16* residual = nullptr;   // [M or res_mod, ldr] bf16, added after alpha
+    int ldr = 0;
+    int res_mod = 0;
+    const float* ln_gamma = nullptr;    // LayerNorm over the N outputs (needs N <= 256: one tile per row)
+    const float* ln_beta = nullptr;
+    __nv_bfloat16* out_bf16 = nullptr;
+    int ldo_bf16 = 0;
+    float* out_f32 = nullptr;
+    int ldo_f32 = 0;
+};
+
+int launch_dense(const Dense& d, cudaStream_t st);
+
+// fp32 -> bf16 row copy with zero padding of columns [cols, ld_out): out[r, c] = in[r, c]
+int launch_cast_bf16(const float* in, int ld_in, int rows, int cols, const int* rows_dev, __nv_bfloat16* out, int ld_out,
+                     cudaStream_t st);
+
+}  // namespace cm

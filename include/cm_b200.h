@@ -100,6 +100,15 @@ int cm_csr_from_edge_index(const int64_t* edge_index, int64_t row_stride, const 
                            int n_edges, void* workspace, size_t workspace_bytes, int32_t* csr_row_ptr,
                            int32_t* csr_col, float* csr_w, float* self_w, uint32_t* status, void* stream);
 
+/* Dense-layer building block of A5-A11 on the tcgen05 tensor cores (bf16 operands, fp32 accumulation in TMEM):
+ *   out[m,n] = LN?( relu?( alpha * (sum_k a[m,k] w[n,k] + bias[n]) + residual[m,n] ) )
+ * a [m,lda] bf16 and w [n,k] bf16 (an nn.Linear weight), k % 8 == 0, lda % 8 == 0, 16-byte aligned; m is a
+ * capacity and *m_dev (optional) the live row count; bias / ln_gamma / ln_beta fp32 [n] (LayerNorm eps 1e-5,
+ * n <= 256); residual bf16 [m,ldr]; out_bf16 and/or out_f32 [m,n]. */
+int cm_linear_bf16(const void* a_bf16, int lda, const void* w_bf16, int m, int n, int k, const int32_t* m_dev,
+                   const float* bias, float alpha, int relu, const void* residual_bf16, int ldr,
+                   const float* ln_gamma, const float* ln_beta, void* out_bf16, float* out_f32, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * A5-A7: RegionGraphGNN forward (extract_rg_embeddings.py:27-135), eval mode.
  * The raw parameters are the reference state-dict tensors (PyG names); cm_gnn_fold turns them

@@ -1,0 +1,63 @@
+"""GPU parity of the tcgen05/TMEM/TMA dense layer (cm_linear_bf16) against a plain PyTorch fp32 reference of the
+same op on the same bf16-rounded operands.  fp32 accumulation => tolerance is fp32 summation noise (1e-3 abs at
+K=512 with O(1) outputs is generous); bf16 outputs additionally carry one bf16 rounding (2^-8 relative)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(m, n, k, *, bias=True, alpha=1.0, relu=False, residual=False, ln=False, live=None, lda=None, seed=0):
+    from camouflage_multimodal_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(seed)
+    lda = lda or k
+    a = (torch.randn(m, lda, generator=g) * 0.5).to(torch.bfloat16).cuda()
+    w = (torch.randn(n, k, generator=g) * (1.0 / k ** 0.5)).to(torch.bfloat16).cuda()
+    b = torch.randn(n, generator=g).cuda() if bias else None
+    r = (torch.randn(m, n, generator=g)).to(torch.bfloat16).cuda() if residual else None
+    gam = (1 + 0.1 * torch.randn(n, generator=g)).cuda() if ln else None
+    bet = (0.1 * torch.randn(n, generator=g)).cuda() if ln else None
+    out16 = torch.full((m, n), 7.0, dtype=torch.bfloat16, device="cuda")
+    out32 = torch.full((m, n), 7.0, dtype=torch.float32, device="cuda")
+    mdev = torch.tensor([live], dtype=torch.int32, device="cuda") if live is not None else None
+    p = _lib.ptr
+    _lib.check(lib.cm_linear_bf16(p(a), lda, p(w), m, n, k, p(mdev), p(b), float(alpha), int(relu), p(r), n, p(gam), p(bet),
+                                  p(out16), p(out32), _lib.stream_ptr()), "cm_linear_bf16")
+    torch.cuda.synchronize()
+    ref = a[:, :k].float() @ w.float().t()
+    if bias:
+        ref = ref + b
+    ref = ref * alpha
+    if residual:
+        ref = ref + r.float()
+    if relu:
+        ref = ref.relu()
+    if ln:
+        ref = torch.nn.functional.layer_norm(ref, (n,), gam, bet, 1e-5)
+    rows = live if live is not None else m
+    err32 = (out32[:rows] - ref[:rows]).abs().max().item()
+    err16 = (out16[:rows].float() - ref[:rows]).abs().max().item()
+    scale = ref[:rows].abs().max().item()
+    assert err32 <= 2e-3, (m, n, k, err32)
+    assert err16 <= 2e-3 + scale * 2 ** -8, (m, n, k, err16)
+    if rows < m:   # rows past the live count are never written
+        assert (out32[rows:] == 7.0).all() and (out16[rows:].float() == 7.0).all()
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 128, 64), (300, 256, 128), (1000, 512, 256), (481, 256, 512), (77, 192, 128),
+                                   (13, 256, 256), (15466, 128, 128), (200, 128, 72), (32, 2 * 256, 512), (5, 64, 256)])
+def test_shapes(m, n, k):
+    _run(m, n, k)
+
+
+def test_epilogues():
+    _run(500, 256, 256, relu=True)
+    _run(500, 256, 256, alpha=0.1767767, bias=True)
+    _run(500, 256, 256, residual=True)
+    _run(500, 256, 256, residual=True, ln=True)
+    _run(333, 128, 128, residual=True, ln=True, relu=False)
+    _run(400, 256, 128, live=257)
+    _run(400, 256, 64, live=1, lda=64)
+    _run(260, 128, 64, lda=72, bias=False)
+    _run(640, 512, 256, relu=True, live=600)
