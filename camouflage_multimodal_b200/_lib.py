@@ -70,7 +70,9 @@ SIGNATURES = {
     "cm_gnn_forward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _fp, _i, _fp, _sz,
                             _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_fusion_workspace_bytes": (_sz, [C.POINTER(FusionParams), _i, _i, _i]),
-    "cm_fusion_forward": (_i, [C.POINTER(FusionParams), _fp, _fp, _i, _i, _fp, _i, _i, _fp, _sz,
+    "cm_fusion_folded_bytes": (_sz, [C.POINTER(FusionParams), _i]),
+    "cm_fusion_fold": (_i, [C.POINTER(FusionParams), _fp, _i, _fp, _sz, _fp]),
+    "cm_fusion_forward": (_i, [C.POINTER(FusionParams), _fp, _fp, _fp, _i, _i, _fp, _i, _i, _fp, _sz,
                                _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_paint_metrics": (_i, [_fp, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _f, _fp, _fp, _fp, _fp]),
     "cm_metrics_dense": (_i, [_fp, _fp, _i, _i64, _f, _fp, _fp, _fp]),

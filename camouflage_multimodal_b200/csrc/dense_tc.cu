@@ -15,7 +15,7 @@
 
 namespace cm {
 
-constexpr int TC_BM = 128, TC_BK = 64, TC_STAGES = 4, TC_THREADS = 192;
+constexpr int TC_BM = 128, TC_BK = 64, TC_STAGES = 4, TC_THREADS = 320, TC_EPI_THREADS = 256;
 
 // ------------------------------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -95,13 +95,52 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
+__device__ __forceinline__ uint4 pack8(const float* x) {
+    uint4 pk;
+    __nv_bfloat162 b0 = __floats2bfloat162_rn(x[0], x[1]), b1 = __floats2bfloat162_rn(x[2], x[3]);
+    __nv_bfloat162 b2 = __floats2bfloat162_rn(x[4], x[5]), b3 = __floats2bfloat162_rn(x[6], x[7]);
+    pk.x = *reinterpret_cast<uint32_t*>(&b0);
+    pk.y = *reinterpret_cast<uint32_t*>(&b1);
+    pk.z = *reinterpret_cast<uint32_t*>(&b2);
+    pk.w = *reinterpret_cast<uint32_t*>(&b3);
+    return pk;
+}
+
+// In-place softmax over each group of GS consecutive slots of a 32-column chunk; only the first `valid` slots of
+// a group are keys (the rest are layout padding and come out as 0).  am[k] accumulates slot k over the groups.
+template <int GS>
+__device__ __forceinline__ void softmax_groups(float (&x)[32], int valid, float (&am)[32]) {
+#pragma unroll
+    for (int g = 0; g < 32 / GS; ++g) {
+        float mx = -INFINITY;
+#pragma unroll
+        for (int k = 0; k < GS; ++k)
+            if (k < valid) mx = fmaxf(mx, x[g * GS + k]);
+        float sum = 0.f;
+#pragma unroll
+        for (int k = 0; k < GS; ++k) {
+            const float e = k < valid ? expf(x[g * GS + k] - mx) : 0.f;
+            x[g * GS + k] = e;
+            sum += e;
+        }
+        const float inv = 1.0f / sum;
+#pragma unroll
+        for (int k = 0; k < GS; ++k) {
+            x[g * GS + k] *= inv;
+            am[k] += x[g * GS + k];
+        }
+    }
+}
+
 template <int BN>
 struct TcSmem {
     static constexpr int A_BYTES = TC_BM * TC_BK * 2;
     static constexpr int B_BYTES = BN * TC_BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int BAR_OFFSET = TC_STAGES * STAGE_BYTES;
-    static constexpr int TOTAL = BAR_OFFSET + 128 + 1024;   // barriers + tmem slot, + slack for 1 KB alignment
+    static constexpr int VEC_OFFSET = BAR_OFFSET + 128;          // bias / gamma / beta of the tile's columns (3 x 256 fp32)
+    static constexpr int STAT_OFFSET = VEC_OFFSET + 3 * 1024;    // LayerNorm partial sums: [2 halves][128 rows] float2
+    static constexpr int TOTAL = STAT_OFFSET + 2048 + 1024;      // + slack for 1 KB alignment
 };
 
 template <int BN>
@@ -170,87 +209,205 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             __syncwarp();
         }
     } else {
-        // ---------------------------------------------------------------- epilogue (warps 2..5)
-        const int q = warp & 3;                       // TMEM lane quarter this warp may read
+        // ---------------------------------------------------------------- epilogue (warps 2..9)
+        // TMEM lane quarter q = warp % 4 (hardware rule); the two warps of a quarter split the tile's 32-column
+        // chunks between them (half 0: even chunks, half 1: odd chunks; scores mode: [0,128) / [128,256)).
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int et = threadIdx.x - 64;
         const int row = m0 + q * 32 + lane;
         const bool row_ok = row < m_live;
+        const int n_cols = min(BN, p.N - n0);
+        float* s_bias = reinterpret_cast<float*>(smem + S::VEC_OFFSET);
+        float* s_gamma = s_bias + 256;
+        float* s_beta = s_gamma + 256;
+        float2* s_stat = reinterpret_cast<float2*>(smem + S::STAT_OFFSET);
+        for (int c = et; c < BN; c += TC_EPI_THREADS) {
+            const bool in = c < n_cols;
+            s_bias[c] = (in && p.bias) ? p.bias[n0 + c] : 0.f;
+            if (p.ln_gamma) {
+                s_gamma[c] = in ? p.ln_gamma[n0 + c] : 0.f;
+                s_beta[c] = in ? p.ln_beta[n0 + c] : 0.f;
+            }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_THREADS) : "memory");
         mbar_wait(acc_ready, 0);
         __syncwarp();
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-        const __nv_bfloat16* res = nullptr;
-        if (p.residual && row_ok) res = p.residual + (size_t)(p.res_mod > 0 ? row % p.res_mod : row) * p.ldr;
-        const int n_cols = min(BN, p.N - n0);
-        float mean = 0.f, rstd = 1.f;
-        if (p.ln_gamma) {
-            float s1 = 0.f, s2 = 0.f;
-            for (int c0 = 0; c0 < n_cols; c0 += 32) {
-                uint32_t v[32];
-                tc_ld32(taddr + c0, v);
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int c = n0 + c0 + j;
-                    if (c0 + j < n_cols) {
-                        float x = __uint_as_float(v[j]);
-                        if (p.bias) x += p.bias[c];
-                        x *= p.alpha;
-                        if (res) x += __bfloat162float(res[c]);
-                        if (p.relu) x = fmaxf(x, 0.f);
-                        s1 += x;
-                        s2 = fmaf(x, x, s2);
-                    }
-                }
-            }
-            mean = s1 / (float)n_cols;
-            const float var = fmaxf(s2 / (float)n_cols - mean * mean, 0.f);
-            rstd = rsqrtf(var + 1e-5f);
-        }
-        for (int c0 = 0; c0 < n_cols; c0 += 32) {
+        const size_t res_row = (size_t)(p.res_mod > 0 ? row % p.res_mod : row) * p.ldr;
+        const __nv_bfloat16* res = (p.residual && row_ok) ? p.residual + res_row + n0 : nullptr;
+        const float* resf = (p.residual_f32 && row_ok) ? p.residual_f32 + res_row + n0 : nullptr;
+        const bool res_vec = res && (p.ldr & 7) == 0 && (reinterpret_cast<uintptr_t>(p.residual + n0) & 15) == 0;
+        const bool resf_vec = resf && (p.ldr & 3) == 0 && (reinterpret_cast<uintptr_t>(p.residual_f32 + n0) & 15) == 0;
+        const int c_begin = p.sm_gs ? half * 128 : half * 32, c_step = p.sm_gs ? 32 : 64;
+        const int c_end = p.sm_gs ? min(n_cols, c_begin + 128) : n_cols;
+
+        // x[j] = relu?( alpha * (acc + bias) + residual ) for the 32 columns starting at c0 (all lanes take part
+        // in the TMEM load; global loads only for live rows)
+        auto load_chunk = [&](int c0, float (&x)[32]) {
             uint32_t v[32];
-            tc_ld32(taddr + c0, v);   // warp-collective: every lane takes part, stores are per row
-            if (row_ok) {
-            float x[32];
+            tc_ld32(taddr + c0, v);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const int c = n0 + c0 + j;
-                float t = __uint_as_float(v[j]);
-                if (c0 + j < n_cols) {
-                    if (p.bias) t += p.bias[c];
-                    t *= p.alpha;
-                    if (res) t += __bfloat162float(res[c]);
-                    if (p.relu) t = fmaxf(t, 0.f);
-                    if (p.ln_gamma) t = (t - mean) * rstd * p.ln_gamma[c] + p.ln_beta[c];
-                }
-                x[j] = t;
+            for (int j = 0; j < 32; j += 4) {
+                const float4 b4 = *reinterpret_cast<const float4*>(s_bias + c0 + j);
+                x[j] = __uint_as_float(v[j]) + b4.x;
+                x[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
+                x[j + 2] = __uint_as_float(v[j + 2]) + b4.z;
+                x[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
             }
-            const bool full32 = c0 + 32 <= n_cols;
-            if (p.out_bf16) {
-                __nv_bfloat16* o = p.out_bf16 + (size_t)row * p.ldo_bf16 + n0 + c0;
-                if (full32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+            if (p.alpha != 1.0f) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) x[j] *= p.alpha;
+            }
+            const int valid = n_cols - c0;
+            if (res) {
+                if (res_vec && valid >= 32) {
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) {
-                        uint4 pk;
-                        __nv_bfloat162 b0 = __floats2bfloat162_rn(x[j], x[j + 1]), b1 = __floats2bfloat162_rn(x[j + 2], x[j + 3]);
-                        __nv_bfloat162 b2 = __floats2bfloat162_rn(x[j + 4], x[j + 5]), b3 = __floats2bfloat162_rn(x[j + 6], x[j + 7]);
-                        pk.x = *reinterpret_cast<uint32_t*>(&b0);
-                        pk.y = *reinterpret_cast<uint32_t*>(&b1);
-                        pk.z = *reinterpret_cast<uint32_t*>(&b2);
-                        pk.w = *reinterpret_cast<uint32_t*>(&b3);
-                        *reinterpret_cast<uint4*>(o + j) = pk;
+                        const uint4 r8 = *reinterpret_cast<const uint4*>(res + c0 + j);
+                        const uint32_t w[4] = {r8.x, r8.y, r8.z, r8.w};
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[t]));
+                            x[j + 2 * t] += f.x;
+                            x[j + 2 * t + 1] += f.y;
+                        }
                     }
                 } else {
-                    for (int j = 0; j < 32 && c0 + j < n_cols; ++j) o[j] = __float2bfloat16(x[j]);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < valid) x[j] += __bfloat162float(res[c0 + j]);
                 }
             }
-            if (p.out_f32) {
-                float* o = p.out_f32 + (size_t)row * p.ldo_f32 + n0 + c0;
-                if (full32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+            if (resf) {
+                if (resf_vec && valid >= 32) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const float4 r4 = *reinterpret_cast<const float4*>(resf + c0 + j);
+                        x[j] += r4.x;
+                        x[j + 1] += r4.y;
+                        x[j + 2] += r4.z;
+                        x[j + 3] += r4.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < valid) x[j] += resf[c0 + j];
+                }
+            }
+            if (p.relu) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+            }
+        };
+
+        float mean = 0.f, rstd = 1.f;
+        if (p.ln_gamma) {   // pass 1: row statistics over the whole tile (the two halves exchange partial sums)
+            float s1 = 0.f, s2 = 0.f;
+            for (int c0 = c_begin; c0 < c_end; c0 += c_step) {
+                float x[32];
+                load_chunk(c0, x);
+                const int valid = n_cols - c0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float t = (valid >= 32 || j < valid) ? x[j] : 0.f;
+                    s1 += t;
+                    s2 = fmaf(t, t, s2);
+                }
+            }
+            s_stat[half * 128 + q * 32 + lane] = make_float2(s1, s2);
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_THREADS) : "memory");
+            const float2 o = s_stat[(half ^ 1) * 128 + q * 32 + lane];
+            s1 += o.x;
+            s2 += o.y;
+            mean = s1 / (float)n_cols;
+            rstd = rsqrtf(fmaxf(s2 / (float)n_cols - mean * mean, 0.f) + 1e-5f);
+        }
+        float am[32];   // scores mode: head-summed probabilities of this row
+#pragma unroll
+        for (int j = 0; j < 32; ++j) am[j] = 0.f;
+        for (int c0 = c_begin; c0 < c_end; c0 += c_step) {
+            float x[32];
+            load_chunk(c0, x);
+            if (p.ln_gamma) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const float4 g4 = *reinterpret_cast<const float4*>(s_gamma + c0 + j), b4 = *reinterpret_cast<const float4*>(s_beta + c0 + j);
+                    x[j] = (x[j] - mean) * rstd * g4.x + b4.x;
+                    x[j + 1] = (x[j + 1] - mean) * rstd * g4.y + b4.y;
+                    x[j + 2] = (x[j + 2] - mean) * rstd * g4.z + b4.z;
+                    x[j + 3] = (x[j + 3] - mean) * rstd * g4.w + b4.w;
+                }
+            }
+            const int valid = n_cols - c0;
+            const bool full32 = valid >= 32;
+            if (p.sm_gs) {
+                // scores mode (N == 256): columns [0,128) hold per-head groups of sm_gs slots (sm_valid live keys
+                // each) -> softmax within the group, bf16 out [M,128]; columns [128,256) -> raw fp32 scores [M,128]
+                const int c = n0 + c0;
+                if (c < 128) {
+                    if (p.sm_gs == 16) softmax_groups<16>(x, p.sm_valid, am); else softmax_groups<32>(x, p.sm_valid, am);
+                    if (row_ok) {
+                        __nv_bfloat16* o = p.out_bf16 + (size_t)row * 128 + c;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(o + j) = pack8(x + j);
+                        if (c == 96 && p.attn_mean) {
+                            const float inv = (float)p.sm_gs / 128.f;   // 1 / heads
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (j < p.sm_valid) p.attn_mean[(size_t)row * p.sm_valid + j] = am[j] * inv;
+                        }
+                    }
+                } else if (row_ok) {
+                    float* o = p.out_f32 + (size_t)row * 128 + (c - 128);
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
-                } else {
-                    for (int j = 0; j < 32 && c0 + j < n_cols; ++j) o[j] = x[j];
                 }
-            }
+            } else if (row_ok) {
+                if (p.out_bf16 && p.split_out) {
+                    // [hi | lo | hi] thirds of a 3N-wide row: the next layer multiplies them with [W_hi | W_hi | W_lo]
+                    __nv_bfloat16* o = p.out_bf16 + (size_t)row * p.ldo_bf16 + n0 + c0;
+                    float lo[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) lo[j] = x[j] - __bfloat162float(__float2bfloat16(x[j]));
+                    if (full32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0) && (p.N & 7) == 0) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            const uint4 h8 = pack8(x + j);
+                            *reinterpret_cast<uint4*>(o + j) = h8;
+                            *reinterpret_cast<uint4*>(o + p.N + j) = pack8(lo + j);
+                            *reinterpret_cast<uint4*>(o + 2 * p.N + j) = h8;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (j < valid) {
+                                o[j] = o[2 * p.N + j] = __float2bfloat16(x[j]);
+                                o[p.N + j] = __float2bfloat16(lo[j]);
+                            }
+                    }
+                } else if (p.out_bf16) {
+                    __nv_bfloat16* o = p.out_bf16 + (size_t)row * p.ldo_bf16 + n0 + c0;
+                    if (full32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(o + j) = pack8(x + j);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (j < valid) o[j] = __float2bfloat16(x[j]);
+                    }
+                }
+                if (p.out_f32) {
+                    float* o = p.out_f32 + (size_t)row * p.ldo_f32 + n0 + c0;
+                    if (full32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (j < valid) o[j] = x[j];
+                    }
+                }
             }
             __syncwarp();
         }
@@ -335,6 +492,9 @@ int launch_dense(const Dense& d, cudaStream_t st) {
     CM_REQUIRE(d.K % 8 == 0 && d.lda % 8 == 0 && d.lda >= d.K, "dense: K=%d / lda=%d must be multiples of 8", d.K, d.lda);
     CM_REQUIRE((reinterpret_cast<uintptr_t>(d.A) & 15) == 0 && (reinterpret_cast<uintptr_t>(d.W) & 15) == 0, "dense: operands must be 16-byte aligned");
     CM_REQUIRE(!d.ln_gamma || d.N <= 256, "dense: fused LayerNorm needs N <= 256 (N=%d)", d.N);
+    CM_REQUIRE(!d.sm_gs || ((d.sm_gs == 16 || d.sm_gs == 32) && d.N == 256 && d.out_bf16 && d.out_f32 && !d.ln_gamma &&
+                            d.sm_valid >= 1 && d.sm_valid <= d.sm_gs),
+               "dense: scores mode needs N == 256, group size 16/32, bf16 + f32 outputs");
     if (d.N > 128) return launch_dense_bn<256>(d, st);
     return launch_dense_bn<128>(d, st);
 }
@@ -359,6 +519,31 @@ int launch_cast_bf16(const float* in, int ld_in, int rows, int cols, const int* 
         cast_bf16_kernel<<<blocks, 256, 0, st>>>(in, ld_in, rows, cols, rows_dev, out, ld_out);
     }
     return post_launch("cast_bf16");
+}
+
+// fp32 [rows, cols] (optionally scaled per row) -> bf16 [rows, 3*kpad] = [hi | hi | lo], each third zero-padded to kpad
+__global__ void split_weight_kernel(const float* __restrict__ in, int rows, int cols, int kpad, const float* __restrict__ row_scale,
+                                    __nv_bfloat16* __restrict__ out) {
+    const long long total = (long long)rows * kpad;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int r = (int)(i / kpad), c = (int)(i - (long long)r * kpad);
+        float v = c < cols ? in[(size_t)r * cols + c] : 0.f;
+        if (row_scale) v *= row_scale[r];
+        const __nv_bfloat16 hi = __float2bfloat16(v);
+        __nv_bfloat16* o = out + (size_t)r * 3 * kpad + c;
+        o[0] = hi;
+        o[kpad] = hi;
+        o[2 * kpad] = __float2bfloat16(v - __bfloat162float(hi));
+    }
+}
+
+int launch_split_weight(const float* in, int rows, int cols, int kpad, const float* row_scale, __nv_bfloat16* out, cudaStream_t st) {
+    if (rows <= 0) return CM_OK;
+    {
+        CM_TIMED("fold_weights", st);
+        split_weight_kernel<<<ceil_div((long long)rows * kpad, 256), 256, 0, st>>>(in, rows, cols, kpad, row_scale, out);
+    }
+    return post_launch("split_weight");
 }
 
 }  // namespace cm

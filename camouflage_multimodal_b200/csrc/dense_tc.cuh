@@ -19,14 +19,23 @@ struct Dense {
     float alpha = 1.f;
     int relu = 0;
     const __nv_bfloat16* residual = nullptr;   // [M or res_mod, ldr] bf16, added after alpha
+    const float* residual_f32 = nullptr;       // same role in fp32 (at most one of the two)
     int ldr = 0;
     int res_mod = 0;
     const float* ln_gamma = nullptr;    // LayerNorm over the N outputs (needs N <= 256: one tile per row)
     const float* ln_beta = nullptr;
     __nv_bfloat16* out_bf16 = nullptr;
     int ldo_bf16 = 0;
+    // split_out: out_bf16 rows are 3N wide, [hi | lo | hi] with hi = bf16(v), lo = bf16(v - hi): fed to the next
+    // layer against [W_hi | W_hi | W_lo] (launch_split_weight) the three products recover ~16 mantissa bits.
+    int split_out = 0;
     float* out_f32 = nullptr;
     int ldo_f32 = 0;
+    // scores mode (sm_gs = 16 or 32, N == 256): output columns [0,128) are 128/sm_gs head groups of sm_gs slots with
+    // sm_valid live keys each -> per-group softmax, written bf16 to out_bf16 [M,128]; columns [128,256) -> raw fp32
+    // to out_f32 [M,128]; attn_mean [M, sm_valid] (optional) = mean over the head groups of the probabilities.
+    int sm_gs = 0, sm_valid = 0;
+    float* attn_mean = nullptr;
 };
 
 int launch_dense(const Dense& d, cudaStream_t st);
@@ -34,5 +43,8 @@ int launch_dense(const Dense& d, cudaStream_t st);
 // fp32 -> bf16 row copy with zero padding of columns [cols, ld_out): out[r, c] = in[r, c]
 int launch_cast_bf16(const float* in, int ld_in, int rows, int cols, const int* rows_dev, __nv_bfloat16* out, int ld_out,
                      cudaStream_t st);
+
+// fp32 weight [rows, cols] (optional per-row scale) -> bf16 [rows, 3*kpad] = [hi | hi | lo] thirds, zero padded
+int launch_split_weight(const float* in, int rows, int cols, int kpad, const float* row_scale, __nv_bfloat16* out, cudaStream_t st);
 
 }  // namespace cm

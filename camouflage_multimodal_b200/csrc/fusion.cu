@@ -7,6 +7,9 @@
 // head-averaged probabilities returned only when the caller asks for them (fusion_model.py:112-129, 243-246).
 #include <math.h>
 
+#include <algorithm>
+
+#include "fusion_tc.cuh"
 #include "linear.cuh"
 
 namespace cm {
@@ -253,10 +256,31 @@ static int detector_heads(const cm_fusion_params* p, const float* fused, int fin
 
 extern "C" size_t cm_fusion_workspace_bytes(const cm_fusion_params* p, int n_graphs, int node_cap, int n_kg) {
     if (!p || n_graphs <= 0 || node_cap <= 0 || n_kg <= 0 || cm::check_fusion(p) != CM_OK) return 0;
-    return cm::carve_fusion(nullptr, p, n_graphs, node_cap, n_kg).total;
+    size_t need = cm::carve_fusion(nullptr, p, n_graphs, node_cap, n_kg).total;
+    if (cm::fusion_fold_supported(p, n_kg)) need = std::max(need, cm::fusion_tc_workspace_bytes(p, n_graphs, node_cap, n_kg));
+    return need;
 }
 
-extern "C" int cm_fusion_forward(const cm_fusion_params* p, const float* rg, const int32_t* node_ptr, int n_graphs, int node_cap,
+extern "C" size_t cm_fusion_folded_bytes(const cm_fusion_params* p, int n_kg) {
+    if (!p || n_kg <= 0 || cm::check_fusion(p) != CM_OK || !cm::fusion_fold_supported(p, n_kg)) return 0;
+    return cm::fusion_folded_layout(p, n_kg).total;
+}
+
+extern "C" int cm_fusion_fold(const cm_fusion_params* p, const float* kg, int n_kg, void* folded, size_t folded_bytes, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    int rc = check_fusion(p);
+    if (rc != CM_OK) return rc;
+    CM_REQUIRE(kg && folded && n_kg > 0, "cm_fusion_fold: NULL pointer");
+    CM_REQUIRE(fusion_fold_supported(p, n_kg),
+               "cm_fusion_fold: needs cross_attention, hidden_dim <= 256 (multiple of 32), rg_dim %% 8 == 0 and num_heads * "
+               "(16 or 32 slots >= n_kg) <= 128; got hidden=%d heads=%d n_kg=%d", p->hidden, p->heads, n_kg);
+    const size_t need = fusion_folded_layout(p, n_kg).total;
+    CM_REQUIRE(folded_bytes >= need, "cm_fusion_fold: blob %zu < %zu bytes", folded_bytes, need);
+    return fusion_fold(p, kg, n_kg, folded, as_stream(stream));
+}
+
+extern "C" int cm_fusion_forward(const cm_fusion_params* p, const void* folded, const float* rg, const int32_t* node_ptr, int n_graphs, int node_cap,
                                  const float* kg, int kg_graphs, int n_kg, void* workspace, size_t workspace_bytes, float* fused_out,
                                  float* mask_out, float* instance_out, float* edge_out, float* score_out, float* attn_rg2kg,
                                  float* attn_kg2rg, void* stream) {
@@ -274,6 +298,16 @@ extern "C" int cm_fusion_forward(const cm_fusion_params* p, const float* rg, con
         return CM_ERR_WORKSPACE;
     }
     cudaStream_t st = as_stream(stream);
+    if (folded) {
+        CM_REQUIRE(kg_graphs == 1 && fusion_fold_supported(p, Kk), "cm_fusion_forward: a folded blob needs shared kg rows (kg_graphs == 1)");
+        const size_t need = fusion_tc_workspace_bytes(p, G, M, Kk);
+        if (workspace_bytes < need) {
+            set_error("cm_fusion_forward: workspace %zu < %zu bytes", workspace_bytes, need);
+            return CM_ERR_WORKSPACE;
+        }
+        return fusion_forward_tc(p, folded, rg, node_ptr, G, M, Kk, workspace, fused_out, mask_out, instance_out, edge_out, score_out,
+                                 attn_rg2kg, attn_kg2rg, st);
+    }
     const int* m_dev = node_ptr + G;
     float* fused = fused_out ? fused_out : w.fused;
     Linear l;

@@ -9,12 +9,14 @@
 //     BatchNorm folded into its weight and bias) follows as a dense layer.
 // PyG semantics restated: self loops removed then one added per node (GAT); add_remaining_self_loops with
 // weight 1, symmetric normalisation by the weighted in-degree (GCN); softmax denominator + 1e-16.
+#include "dense_tc.cuh"
 #include "linear.cuh"
 
 namespace cm {
 
-struct GnnFolded {   // float offsets into the folded blob
-    size_t u_src, u_dst, wcat, bias1, convw[3], convb[3], head1w, head1b, total;
+struct GnnFolded {   // float offsets into the folded blob (the *_h entries hold bf16 weights for the tensor cores)
+    size_t u_src, u_dst, bias1, convb[3], head1b, wcat_h, convw_h[3], fcw_h, head1w_h, total;
+    int zk;   // K of the GAT dense layer: [z_hi | z_lo | z_hi], each third padded to a multiple of 64 columns
 };
 
 static GnnFolded gnn_layout(const cm_gnn_params* p) {
@@ -26,18 +28,34 @@ static GnnFolded gnn_layout(const cm_gnn_params* p) {
         return r;
     };
     const size_t H = p->hidden, C = p->in_channels, hd = p->heads;
+    const size_t third = (hd * C + 63) / 64 * 64;
+    f.zk = (int)(3 * third);
     f.u_src = take(hd * C);
     f.u_dst = take(hd * C);
-    f.wcat = take(H * hd * C);
     f.bias1 = take(H);
-    for (int k = 0; k < 3; ++k) {
-        f.convw[k] = take(H * H);
-        f.convb[k] = take(H);
-    }
-    f.head1w = take(3 * (H / 2) * H);
+    for (int k = 0; k < 3; ++k) f.convb[k] = take(H);
     f.head1b = take(3 * (H / 2));
+    f.wcat_h = take(H * f.zk / 2);
+    for (int k = 0; k < 3; ++k) f.convw_h[k] = take(3 * H * H / 2);   // every weight is stored [hi | hi | lo] along K
+    f.fcw_h = take(3 * H * H / 2);
+    f.head1w_h = take(3 * 3 * (H / 2) * H / 2);
     f.total = o;
     return f;
+}
+
+// weight thirds [hi | hi | lo], `third` columns apart
+__device__ __forceinline__ void store_split_w(__nv_bfloat16* o, int third, float v) {
+    const __nv_bfloat16 hi = __float2bfloat16(v);
+    o[0] = hi;
+    o[third] = hi;
+    o[2 * third] = __float2bfloat16(v - __bfloat162float(hi));
+}
+// activation thirds [hi | lo | hi]
+__device__ __forceinline__ void store_split_a(__nv_bfloat16* o, int third, float v) {
+    const __nv_bfloat16 hi = __float2bfloat16(v);
+    o[0] = hi;
+    o[third] = __float2bfloat16(v - __bfloat162float(hi));
+    o[2 * third] = hi;
 }
 
 __global__ void gnn_fold_kernel(cm_gnn_params p, GnnFolded f, float* __restrict__ blob) {
@@ -56,11 +74,20 @@ __global__ void gnn_fold_kernel(cm_gnn_params p, GnnFolded f, float* __restrict_
         blob[f.u_src + i] = s;
         blob[f.u_dst + i] = d;
     }
-    // wcat [H, heads*C] = W[h*H+o, c] / heads * bn1 scale ; bias1
-    for (long long i = tid; i < (long long)H * KC; i += stride) {
-        const int o = (int)(i / KC), hc = (int)(i % KC), h = hc / C, c = hc % C;
-        const float s = p.bn_weight[0][o] / sqrtf(p.bn_var[0][o] + p.bn_eps);
-        blob[f.wcat + i] = p.conv1_lin_weight[(size_t)(h * H + o) * C + c] * (s / (float)hd);
+    // wcat [H, zk] bf16 = [Wf_hi | Wf_hi | Wf_lo] with Wf[o, h*C+c] = W[h*H+o, c] / heads * bn1 scale; bias1.
+    // All dense layers of the GNN run in this split form: activations arrive as [a_hi | a_lo | a_hi], so the three
+    // K-thirds are a_hi W_hi + a_lo W_hi + a_hi W_lo -- bf16 tensor-core products with ~16 bits of mantissa.
+    __nv_bfloat16* wcat = reinterpret_cast<__nv_bfloat16*>(blob + f.wcat_h);
+    const int third = f.zk / 3;
+    for (long long i = tid; i < (long long)H * third; i += stride) {
+        const int o = (int)(i / third), hc = (int)(i % third);
+        float v = 0.f;
+        if (hc < KC) {
+            const int h = hc / C, c = hc % C;
+            const float s = p.bn_weight[0][o] / sqrtf(p.bn_var[0][o] + p.bn_eps);
+            v = p.conv1_lin_weight[(size_t)(h * H + o) * C + c] * (s / (float)hd);
+        }
+        store_split_w(wcat + (size_t)o * f.zk + hc, third, v);
     }
     for (long long o = tid; o < H; o += stride) {
         const float s = p.bn_weight[0][o] / sqrtf(p.bn_var[0][o] + p.bn_eps);
@@ -68,9 +95,10 @@ __global__ void gnn_fold_kernel(cm_gnn_params p, GnnFolded f, float* __restrict_
     }
     for (int k = 0; k < 3; ++k) {
         const float *bw = p.bn_weight[k + 1], *bb = p.bn_bias[k + 1], *bm = p.bn_mean[k + 1], *bv = p.bn_var[k + 1];
+        __nv_bfloat16* cw = reinterpret_cast<__nv_bfloat16*>(blob + f.convw_h[k]);
         for (long long i = tid; i < (long long)H * H; i += stride) {
-            const int o = (int)(i / H);
-            blob[f.convw[k] + i] = p.conv_lin_weight[k][i] * (bw[o] / sqrtf(bv[o] + p.bn_eps));
+            const int o = (int)(i / H), c = (int)(i % H);
+            store_split_w(cw + (size_t)o * 3 * H + c, H, p.conv_lin_weight[k][i] * (bw[o] / sqrtf(bv[o] + p.bn_eps)));
         }
         for (long long o = tid; o < H; o += stride) {
             const float s = bw[o] / sqrtf(bv[o] + p.bn_eps);
@@ -78,10 +106,14 @@ __global__ void gnn_fold_kernel(cm_gnn_params p, GnnFolded f, float* __restrict_
         }
     }
     const int H2 = H / 2;
+    __nv_bfloat16* h1 = reinterpret_cast<__nv_bfloat16*>(blob + f.head1w_h);
     for (long long i = tid; i < 3LL * H2 * H; i += stride) {
-        const int t = (int)(i / ((long long)H2 * H));
-        blob[f.head1w + i] = p.head1_weight[t][i - (long long)t * H2 * H];
+        const int t = (int)(i / ((long long)H2 * H)), o = (int)(i / H), c = (int)(i % H);
+        store_split_w(h1 + (size_t)o * 3 * H + c, H, p.head1_weight[t][i - (long long)t * H2 * H]);
     }
+    __nv_bfloat16* fw = reinterpret_cast<__nv_bfloat16*>(blob + f.fcw_h);
+    for (long long i = tid; i < (long long)H * H; i += stride)
+        store_split_w(fw + (size_t)(i / H) * 3 * H + (i % H), H, p.fc_shared_weight[i]);
     for (long long i = tid; i < 3LL * H2; i += stride) blob[f.head1b + i] = p.head1_bias[(int)(i / H2)][i % H2];
 }
 
@@ -108,7 +140,7 @@ template <int HEADS>
 __global__ void __launch_bounds__(256) gat_aggregate_kernel(const float* __restrict__ x, int C, const int* __restrict__ row_ptr,
                                                             const int* __restrict__ col, const float* __restrict__ a_src,
                                                             const float* __restrict__ a_dst, const int* n_dev, int cap,
-                                                            float* __restrict__ z) {
+                                                            __nv_bfloat16* __restrict__ z, int zk) {
     const int g = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int n = n_dev ? min(*n_dev, cap) : cap;
     if (g >= n) return;
@@ -145,10 +177,14 @@ __global__ void __launch_bounds__(256) gat_aggregate_kernel(const float* __restr
             acc[h] = fmaf(w, xv, acc[h]);
         }
     }
+    // z row = [z_hi | z_lo | z_hi], each third padded with zeros to zk/3 columns
+    __nv_bfloat16* zr = z + (size_t)g * zk;
+    const int third = zk / 3;
     if (lane < C) {
 #pragma unroll
-        for (int h = 0; h < HEADS; ++h) z[(size_t)g * (HEADS * C) + h * C + lane] = acc[h] / (den[h] + 1e-16f);
+        for (int h = 0; h < HEADS; ++h) store_split_a(zr + h * C + lane, third, acc[h] / (den[h] + 1e-16f));
     }
+    for (int c = HEADS * C + lane; c < third; c += 32) store_split_a(zr + c, third, 0.f);
 }
 
 // dis[i] = (sum of incoming weights + self weight)^-1/2, inf -> 0
@@ -165,40 +201,58 @@ __global__ void gcn_norm_kernel(const int* __restrict__ row_ptr, const int* __re
     dis[i] = isinf(r) ? 0.f : r;
 }
 
-// One warp per target node, lane owns 4 consecutive channels per 128-channel group.
-__global__ void __launch_bounds__(256) gcn_aggregate_kernel(const float* __restrict__ x, int H, const int* __restrict__ row_ptr,
+// One warp per target node, lane owns 4 consecutive channels per 128-channel group; bf16 rows, fp32 accumulation.
+__device__ __forceinline__ void fma4_bf16(float4& acc, float s, uint2 raw) {
+    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&raw.x), b = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
+    const float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+    acc.x = fmaf(s, fa.x, acc.x);
+    acc.y = fmaf(s, fa.y, acc.y);
+    acc.z = fmaf(s, fb.x, acc.z);
+    acc.w = fmaf(s, fb.y, acc.w);
+}
+
+// x and out rows are [hi | lo | hi] thirds of H channels (row stride 3H)
+__global__ void __launch_bounds__(256) gcn_aggregate_kernel(const __nv_bfloat16* __restrict__ x, int H, const int* __restrict__ row_ptr,
                                                             const int* __restrict__ col, const float* __restrict__ w,
                                                             const float* __restrict__ self_w, const float* __restrict__ dis,
-                                                            const int* n_dev, int cap, float* __restrict__ out) {
+                                                            const int* n_dev, int cap, __nv_bfloat16* __restrict__ out) {
     const int g = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int n = n_dev ? min(*n_dev, cap) : cap;
     if (g >= n) return;
     const int e0 = row_ptr[g], e1 = row_ptr[g + 1];
     const float di = dis[g];
+    const int ld = 3 * H;
     for (int c0 = lane * 4; c0 < H; c0 += 128) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int e = e0; e < e1; ++e) {
             const int j = col[e];
             if (j == g) continue;
             const float s = dis[j] * (w ? w[e] : 1.0f) * di;
-            const float4 v = *reinterpret_cast<const float4*>(x + (size_t)j * H + c0);
-            acc.x = fmaf(s, v.x, acc.x);
-            acc.y = fmaf(s, v.y, acc.y);
-            acc.z = fmaf(s, v.z, acc.z);
-            acc.w = fmaf(s, v.w, acc.w);
+            const __nv_bfloat16* xr = x + (size_t)j * ld + c0;
+            fma4_bf16(acc, s, *reinterpret_cast<const uint2*>(xr));
+            fma4_bf16(acc, s, *reinterpret_cast<const uint2*>(xr + H));
         }
         const float s = di * (self_w ? self_w[g] : 1.0f) * di;
-        const float4 v = *reinterpret_cast<const float4*>(x + (size_t)g * H + c0);
-        acc.x = fmaf(s, v.x, acc.x);
-        acc.y = fmaf(s, v.y, acc.y);
-        acc.z = fmaf(s, v.z, acc.z);
-        acc.w = fmaf(s, v.w, acc.w);
-        *reinterpret_cast<float4*>(out + (size_t)g * H + c0) = acc;
+        const __nv_bfloat16* xr = x + (size_t)g * ld + c0;
+        fma4_bf16(acc, s, *reinterpret_cast<const uint2*>(xr));
+        fma4_bf16(acc, s, *reinterpret_cast<const uint2*>(xr + H));
+        const float v[4] = {acc.x, acc.y, acc.z, acc.w};
+        __align__(8) __nv_bfloat16 hi[4], lo[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            hi[t] = __float2bfloat16(v[t]);
+            lo[t] = __float2bfloat16(v[t] - __bfloat162float(hi[t]));
+        }
+        __nv_bfloat16* o = out + (size_t)g * ld + c0;
+        *reinterpret_cast<uint2*>(o) = *reinterpret_cast<const uint2*>(hi);
+        *reinterpret_cast<uint2*>(o + H) = *reinterpret_cast<const uint2*>(lo);
+        *reinterpret_cast<uint2*>(o + 2 * H) = *reinterpret_cast<const uint2*>(hi);
     }
 }
 
 struct GnnWs {
-    float *a_src, *a_dst, *z, *dis, *buf0, *buf1, *hid, *emb;
+    float *a_src, *a_dst, *dis, *hid, *emb;
+    __nv_bfloat16 *z, *buf0, *buf1, *emb_h;
     size_t total;
 };
 static GnnWs carve_gnn(void* ws, const cm_gnn_params* p, int cap) {
@@ -207,10 +261,11 @@ static GnnWs carve_gnn(void* ws, const cm_gnn_params* p, int cap) {
     const size_t n = cap, H = p->hidden;
     r.a_src = c.take<float>(n * p->heads);
     r.a_dst = c.take<float>(n * p->heads);
-    r.z = c.take<float>(n * p->heads * p->in_channels);
+    r.z = c.take<__nv_bfloat16>(n * gnn_layout(p).zk);
     r.dis = c.take<float>(n);
-    r.buf0 = c.take<float>(n * H);
-    r.buf1 = c.take<float>(n * H);
+    r.buf0 = c.take<__nv_bfloat16>(n * 3 * H);
+    r.buf1 = c.take<__nv_bfloat16>(n * 3 * H);
+    r.emb_h = c.take<__nv_bfloat16>(n * 3 * H);
     r.hid = c.take<float>(n * 3 * (H / 2));
     r.emb = c.take<float>(n * H);
     r.total = align_up(c.off, 256);
@@ -284,35 +339,32 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
     }
     {
         CM_TIMED("gat_aggregate", st);
-        gat_aggregate_kernel<4><<<warps_grid, 256, 0, st>>>(x, C, csr_row_ptr, csr_col, ws.a_src, ws.a_dst, n_nodes_dev, M, ws.z);
+        gat_aggregate_kernel<4><<<warps_grid, 256, 0, st>>>(x, C, csr_row_ptr, csr_col, ws.a_src, ws.a_dst, n_nodes_dev, M, ws.z, f.zk);
     }
-    Linear l;
-    l.m_dev = n_nodes_dev;
-    l.M = M;
-    l.relu = 1;
-    l.A = ws.z; l.lda = hd * C; l.K = hd * C; l.W = blob + f.wcat; l.bias = blob + f.bias1; l.N = H; l.C = ws.buf0; l.ldc = H;
-    if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+    auto W = [&](size_t off) { return reinterpret_cast<const __nv_bfloat16*>(blob + off); };
+    Dense d;
+    d.M = M; d.m_dev = n_nodes_dev; d.relu = 1;
+    d.A = ws.z; d.lda = f.zk; d.K = f.zk; d.W = W(f.wcat_h); d.bias = blob + f.bias1; d.N = H; d.out_bf16 = ws.buf0; d.ldo_bf16 = 3 * H; d.split_out = 1;
+    if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     {
         CM_TIMED("gcn_norm", st);
         gcn_norm_kernel<<<ceil_div(M, 256), 256, 0, st>>>(csr_row_ptr, csr_col, csr_w, self_w, n_nodes_dev, M, ws.dis);
     }
-    float* cur = ws.buf0;
     for (int k = 0; k < 3; ++k) {
         {
             CM_TIMED("gcn_aggregate", st);
-            gcn_aggregate_kernel<<<warps_grid, 256, 0, st>>>(cur, H, csr_row_ptr, csr_col, csr_w, self_w, ws.dis, n_nodes_dev, M, ws.buf1);
+            gcn_aggregate_kernel<<<warps_grid, 256, 0, st>>>(ws.buf0, H, csr_row_ptr, csr_col, csr_w, self_w, ws.dis, n_nodes_dev, M, ws.buf1);
         }
-        l.A = ws.buf1; l.lda = H; l.K = H; l.W = blob + f.convw[k]; l.bias = blob + f.convb[k]; l.N = H; l.C = ws.buf0; l.ldc = H;
-        if ((rc = launch_linear(l, st)) != CM_OK) return rc;
-        cur = ws.buf0;
+        d.A = ws.buf1; d.lda = 3 * H; d.K = 3 * H; d.W = W(f.convw_h[k]); d.bias = blob + f.convb[k];
+        if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     }
-    float* emb = node_emb ? node_emb : ws.emb;
-    l.A = cur; l.W = p->fc_shared_weight; l.bias = p->fc_shared_bias; l.C = emb;
-    if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+    float* emb = node_emb ? node_emb : (graph_emb ? ws.emb : nullptr);
+    d.A = ws.buf0; d.W = W(f.fcw_h); d.bias = p->fc_shared_bias; d.out_bf16 = ws.emb_h; d.out_f32 = emb; d.ldo_f32 = H;
+    if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     if (mask_out || instance_out || edge_out || mask_prob) {
         const int H2 = H / 2;
-        l.A = emb; l.W = blob + f.head1w; l.bias = blob + f.head1b; l.N = 3 * H2; l.C = ws.hid; l.ldc = 3 * H2;
-        if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+        d.A = ws.emb_h; d.W = W(f.head1w_h); d.bias = blob + f.head1b; d.N = 3 * H2; d.out_bf16 = nullptr; d.out_f32 = ws.hid; d.ldo_f32 = 3 * H2;
+        if ((rc = launch_dense(d, st)) != CM_OK) return rc;
         Heads2 h2;
         h2.n_heads = 3;
         h2.hdim = H2;

@@ -39,6 +39,8 @@ class _FusionRunner:
         self.fusion, self.heads, self.num_classes = fusion, heads, num_classes
         self._key = None
         self._struct = None
+        self._fold_key = None
+        self._fold = None
 
     def _tensors(self):
         ts = list(self.fusion.parameters())
@@ -95,6 +97,23 @@ class _FusionRunner:
         self._struct, self._key = (s, keep), key
         return self._struct
 
+    def folded(self, kg):
+        """Folded blob of ``cm_fusion_fold`` for KG rows shared by the batch (``kg`` ``[1, K, kg_dim]`` fp32), cached
+        per (parameters, kg); ``None`` when the shape has no tensor-core form."""
+        lib = _lib.load()
+        s, _keep = self.params()
+        K = kg.shape[1]
+        key = (self._key, kg.data_ptr(), kg._version, K)
+        if key != self._fold_key:
+            nbytes = lib.cm_fusion_folded_bytes(C.byref(s), K)
+            blob = None
+            if nbytes:
+                blob = torch.empty(nbytes, dtype=torch.uint8, device=kg.device)
+                _lib.check(lib.cm_fusion_fold(C.byref(s), _lib.ptr(kg), K, _lib.ptr(blob), nbytes, _lib.stream_ptr(kg.device)),
+                           "cm_fusion_fold")
+            self._fold, self._fold_key = (blob, kg), key
+        return self._fold[0]
+
     def run(self, rg_rows, node_ptr, n_graphs, kg, want_attention, want_heads, out=None):
         """rg_rows [M, rg_dim] (capacity-sized allowed), node_ptr [G+1] i32, kg [kg_graphs, K, kg_dim]."""
         lib = _lib.load()
@@ -102,9 +121,14 @@ class _FusionRunner:
         _lib.require_cuda(kg, "kg_embeddings")
         dev = rg_rows.device
         s, _keep = self.params()
-        rg_rows, kg = _lib.f32c(rg_rows), _lib.f32c(kg)
+        rg_rows = _lib.f32c(rg_rows)
+        if kg.dim() == 3 and kg.shape[0] > 1 and kg.stride(0) == 0:   # expand()-ed rows: one KG for the whole batch
+            kg = kg[:1]
+        if kg.dtype != torch.float32 or not kg.is_contiguous():
+            kg = _lib.f32c(kg)
         M, G = rg_rows.shape[0], int(n_graphs)
         kg_graphs, K = kg.shape[0], kg.shape[1]
+        blob = self.folded(kg) if kg_graphs == 1 else None
         final = s.hidden if s.fusion_type == 0 else s.hidden // 2
         f32 = dict(dtype=torch.float32, device=dev)
         out = out or {}
@@ -117,11 +141,11 @@ class _FusionRunner:
             res["kg2rg"] = out.get("kg2rg", torch.empty((K * M,), **f32))
         ws_bytes = lib.cm_fusion_workspace_bytes(C.byref(s), G, max(M, 1), K)
         if ws_bytes == 0:   # parameter validation failed: surface the library's message
-            _lib.check(lib.cm_fusion_forward(C.byref(s), None, None, G, M, None, kg_graphs, K, None, 0, *([None] * 7),
+            _lib.check(lib.cm_fusion_forward(C.byref(s), None, None, None, G, M, None, kg_graphs, K, None, 0, *([None] * 7),
                                              None), "cm_fusion_forward")
         ws = WORKSPACE.get(dev, "fusion", ws_bytes)
         p = _lib.ptr
-        _lib.check(lib.cm_fusion_forward(C.byref(s), p(rg_rows), p(node_ptr), G, max(M, 1), p(kg), kg_graphs, K, p(ws),
+        _lib.check(lib.cm_fusion_forward(C.byref(s), p(blob), p(rg_rows), p(node_ptr), G, max(M, 1), p(kg), kg_graphs, K, p(ws),
                                          ws_bytes, p(res["fused"]), p(res.get("mask_out")), p(res.get("instance_out")),
                                          p(res.get("edge_out")), p(res.get("score_out")), p(res.get("rg2kg")),
                                          p(res.get("kg2rg")), _lib.stream_ptr(dev)), "cm_fusion_forward")

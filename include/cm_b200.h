@@ -174,13 +174,23 @@ typedef struct cm_fusion_params {
 } cm_fusion_params;
 
 size_t cm_fusion_workspace_bytes(const cm_fusion_params* p, int n_graphs, int node_cap, int n_kg);
-/* rg [node_cap, rg_dim] ragged rows (node_ptr [n_graphs+1]); kg [kg_graphs, n_kg, kg_dim] with kg_graphs
+/* Tensor-core path for knowledge-graph rows shared by every image (the reference feeds the same category rows
+ * to every sample -- "KG broadcast once"): cm_fusion_fold projects kg [n_kg, kg_dim] through the KG side of both
+ * attention blocks once per (weights, kg) pair and stores bf16 copies of the remaining weights; the blob is then
+ * passed to cm_fusion_forward, which runs the region-node side as tcgen05 GEMMs.  cm_fusion_folded_bytes returns
+ * 0 when the shape has no folded form (late fusion, hidden_dim > 256, num_heads * slots(n_kg) > 128). */
+size_t cm_fusion_folded_bytes(const cm_fusion_params* p, int n_kg);
+int cm_fusion_fold(const cm_fusion_params* p, const float* kg, int n_kg, void* folded, size_t folded_bytes,
+                   void* stream);
+/* folded: blob of cm_fusion_fold (requires kg_graphs == 1; kg itself is then not read again) or NULL for the
+ * general fp32 path (per-image kg rows, late fusion, large KG vocabularies).
+ * rg [node_cap, rg_dim] ragged rows (node_ptr [n_graphs+1]); kg [kg_graphs, n_kg, kg_dim] with kg_graphs
  * either 1 (the knowledge-graph rows are shared by every image -- broadcast once) or n_graphs.
  * Outputs: fused [n_graphs, final]; mask/instance [n_graphs,num_classes]; edge/score [n_graphs,1];
  * attn_rg2kg [node_cap, n_kg] and attn_kg2rg (image b's block [n_kg, N_b] at offset n_kg*node_ptr[b])
  * are written only when non-NULL (MultimodalCamouflageDetector.forward(return_attention=...), :243-246). */
-int cm_fusion_forward(const cm_fusion_params* p, const float* rg, const int32_t* node_ptr, int n_graphs,
-                      int node_cap, const float* kg, int kg_graphs, int n_kg, void* workspace,
+int cm_fusion_forward(const cm_fusion_params* p, const void* folded, const float* rg,
+                      const int32_t* node_ptr, int n_graphs, int node_cap, const float* kg, int kg_graphs, int n_kg, void* workspace,
                       size_t workspace_bytes, float* fused, float* mask_out, float* instance_out,
                       float* edge_out, float* score_out, float* attn_rg2kg, float* attn_kg2rg,
                       void* stream);

@@ -1,6 +1,11 @@
 """GPU parity: RegionGraphGNN (A5-A7), fusion + heads (A10-A12) vs the oracle and the reference's golden
-outputs.  Tolerances (fp32 path): GNN max-abs <= 1e-4, fusion logits <= 1e-4 and attention
-probabilities <= 1e-5 -- well inside the north star's 1e-2 on mask logits."""
+outputs.  Tolerances, max-abs:
+  * RegionGraphGNN (tcgen05 GEMMs in split bf16 precision, fp32 gathers): <= 1e-4 (measured 3e-5);
+  * fusion, general fp32 path (per-image KG rows, late fusion): logits <= 1e-4, attention probabilities <= 1e-5;
+  * fusion, tensor-core path (KG rows shared by the batch; bf16 operands on the region-node side): logits <= 1e-2 --
+    the north star's bound for bf16 mask logits (measured 2.7e-3) -- fused features <= 4e-2 on values up to 8
+    (measured 1.5e-2), attention probabilities <= 1e-3 (measured 5e-5)."""
+TC_LOGITS, TC_FUSED, TC_ATTN = 1e-2, 4e-2, 1e-3
 import os
 
 import numpy as np
@@ -123,18 +128,20 @@ def detector(golden_dir):
 def test_detector_matches_reference_golden(detector, case):
     m, z = detector
     rg, kg = torch.from_numpy(z[f"{case}.rg"]).cuda(), torch.from_numpy(z[f"{case}.kg"]).cuda()
+    tc = case == "single_4d"            # B = 1: the KG rows are shared by the batch -> tensor-core path
+    tol_l, tol_f, tol_a = (TC_LOGITS, TC_FUSED, TC_ATTN) if tc else (1e-4, 1e-4, 1e-5)
     mask, inst, edge, score, attn = m(rg, kg, return_attention=True)
     for name, got in (("mask", mask), ("instance", inst), ("edge", edge), ("score", score)):
         assert tuple(got.shape) == z[f"{case}.{name}"].shape
-        np.testing.assert_allclose(_np(got), z[f"{case}.{name}"], rtol=0, atol=1e-4, err_msg=name)
+        np.testing.assert_allclose(_np(got), z[f"{case}.{name}"], rtol=0, atol=tol_l, err_msg=name)
     for name in ("rg2kg", "kg2rg"):
         assert tuple(attn[name].shape) == z[f"{case}.{name}"].shape
-        np.testing.assert_allclose(_np(attn[name]), z[f"{case}.{name}"], rtol=0, atol=1e-5, err_msg=name)
-        np.testing.assert_allclose(_np(attn[name].sum(-1)), 1.0, atol=1e-5)
+        np.testing.assert_allclose(_np(attn[name]), z[f"{case}.{name}"], rtol=0, atol=tol_a, err_msg=name)
+        np.testing.assert_allclose(_np(attn[name].sum(-1)), 1.0, atol=2e-3 if tc else 1e-5)
     out4 = m(rg, kg)
     assert len(out4) == 4 and torch.allclose(out4[0], mask, atol=1e-6)
     fused, aw = m.fusion(rg, kg)
-    np.testing.assert_allclose(_np(fused), z[f"{case}.fused"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(_np(fused), z[f"{case}.fused"], rtol=0, atol=tol_f)
     assert set(aw) == {"rg2kg", "kg2rg"}
 
 
@@ -166,7 +173,7 @@ def test_fusion_errors_and_invariances(detector):
     pn, pk = torch.randperm(rg.shape[1], generator=g).cuda(), torch.randperm(13, generator=g).cuda()
     perm = m(rg[:, pn], kg[:, pk])                                   # node- and KG-order invariance
     for a, b in zip(base, perm):
-        assert torch.allclose(a, b, atol=2e-5)
+        assert torch.allclose(a, b, atol=TC_LOGITS / 2)             # B = 1 -> tensor-core path (bf16 operands)
 
 
 def test_ragged_batch_equals_per_image(detector, golden_dir):
@@ -185,10 +192,10 @@ def test_ragged_batch_equals_per_image(detector, golden_dir):
     for i, r in enumerate(rows):
         with torch.no_grad():
             mask, inst, edge, score, attn, fused = ofus.detector_forward(sd, r[None], torch.from_numpy(kgz)[None])
-        np.testing.assert_allclose(_np(res["mask_out"][i]), mask[0].numpy(), rtol=0, atol=1e-4)
-        np.testing.assert_allclose(_np(res["score_out"][i]), score[0].numpy(), rtol=0, atol=1e-4)
+        np.testing.assert_allclose(_np(res["mask_out"][i]), mask[0].numpy(), rtol=0, atol=TC_LOGITS)
+        np.testing.assert_allclose(_np(res["score_out"][i]), score[0].numpy(), rtol=0, atol=TC_LOGITS)
         n = sizes[i]
-        np.testing.assert_allclose(_np(res["rg2kg"][off:off + n]), attn["rg2kg"][0].numpy(), rtol=0, atol=1e-5)
+        np.testing.assert_allclose(_np(res["rg2kg"][off:off + n]), attn["rg2kg"][0].numpy(), rtol=0, atol=TC_ATTN)
         np.testing.assert_allclose(_np(res["kg2rg"][13 * off:13 * (off + n)]).reshape(13, n), attn["kg2rg"][0].numpy(),
-                                   rtol=0, atol=1e-5)
+                                   rtol=0, atol=TC_ATTN)
         off += n

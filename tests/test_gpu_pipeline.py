@@ -136,3 +136,27 @@ def test_pipeline_batch32_properties(models):
     p = out["mask_prob"][: int(out["graph"].node_ptr[-1])]
     assert (p >= 0).all() and (p <= 1).all()
     assert int(out["graph"].status.item()) == 0
+
+
+def test_host_pipeline_graph_replay_equals_eager(models):
+    """The captured step (CUDA graph, H2D on a copy stream, rotating slots) returns exactly what the eagerly
+    launched kernels return, batch after batch, including when a slot is reused."""
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, HostPipeline
+    gnn, det, kg, _, _ = models
+    B = 4
+    dev = torch.device("cuda")
+    pipe = EvalPipeline(gnn, det, kg, label_cap=544)
+    hp = HostPipeline(pipe, B, 256, 256, dev, slots=2, use_graph=True)
+    batches = [synth.make_batch(50 + 7 * j, B, seed=1234) for j in range(5)]
+    pinned = [tuple(t.pin_memory() for t in (b.images, b.labels, b.canny, b.gt)) for b in batches]
+    got = []
+    for j, hb in enumerate(pinned):
+        st = hp.submit(j, *hb)
+        st.ev_done.synchronize()
+        got.append((st.h_mask_out.clone(), st.h_per_image.clone()))
+    eager = EvalPipeline(gnn, det, kg, label_cap=544)
+    for j, b in enumerate(batches):
+        d = b.to("cuda")
+        out = eager.run(d.images, d.labels, d.canny, d.gt)
+        assert torch.equal(got[j][0], out["mask_out"].cpu())
+        assert torch.equal(got[j][1], out["per_image"].cpu())
