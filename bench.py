@@ -129,7 +129,7 @@ def kernel_work(name, B, M, E, K):
     lin_flops += 2.0 * B * (2 * D * D + D * D + 4 * D * (D // 2))
     table = {
         "dense_tc": ("tensor", lin_flops),
-        "cast_bf16": ("hbm", 768.0 * M),
+        "cast_f16": ("hbm", 768.0 * M),
         "rag_scan": ("hbm", 4.0 * px),
         "rag_compact": ("hbm", 4.0 * B * LABEL_CAP * (4 + 17 + 2)),
         "rag_emit": ("hbm", 4.0 * B * LABEL_CAP * 17 + 4.0 * E + 28.0 * M),
@@ -347,7 +347,7 @@ def b200_arm(args):
         line = {
             "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic", "config": workload_config(world, kg_src), "clocks": clk,
+            "dtype": "f16", "data": "synthetic", "config": workload_config(world, kg_src), "clocks": clk,
             "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": stager.h2d_bytes,
                     "d2h_bytes_per_step": stager.d2h_bytes},
             "gpu_launches": int(round(launches_per_step * args.steps)),

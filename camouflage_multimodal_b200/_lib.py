@@ -63,7 +63,7 @@ SIGNATURES = {
     "cm_edge_weights": (_i, [_fp, _fp, _fp, _fp, _i, _fp, _fp]),
     "cm_csr_workspace_bytes": (_sz, [_i, _i]),
     "cm_csr_from_edge_index": (_i, [_fp, _i64, _fp, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp]),
-    "cm_linear_bf16": (_i, [_fp, _i, _fp, _i, _i, _i, _fp, _fp, _f, _i, _fp, _i, _fp, _fp, _fp, _fp, _fp]),
+    "cm_linear_f16": (_i, [_fp, _i, _fp, _i, _i, _i, _fp, _fp, _f, _i, _fp, _i, _fp, _fp, _fp, _fp, _fp]),
     "cm_gnn_folded_bytes": (_sz, [C.POINTER(GnnParams)]),
     "cm_gnn_fold": (_i, [C.POINTER(GnnParams), _fp, _sz, _fp]),
     "cm_gnn_workspace_bytes": (_sz, [C.POINTER(GnnParams), _i]),

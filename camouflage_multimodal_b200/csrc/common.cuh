@@ -58,6 +58,26 @@ struct Carver {
 };
 
 #ifdef __CUDACC__
+}  // namespace cm
+#include <cuda_fp16.h>
+namespace cm {
+// Tensor-core operand type: IEEE fp16 (kind::f16, fp32 accumulation in TMEM).  fp16 carries 3 more mantissa bits
+// than fp16 at the same tensor-core rate; every conversion saturates to the finite range instead of producing inf.
+typedef __half op_t;
+typedef __half2 op2_t;
+__device__ __forceinline__ op_t f2op(float v) {
+    unsigned short r;
+    asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(r) : "f"(v));
+    return __ushort_as_half(r);
+}
+__device__ __forceinline__ float op2f(op_t v) { return __half2float(v); }
+__device__ __forceinline__ op2_t f2op2(float lo, float hi) {   // .x = lo, .y = hi
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return *reinterpret_cast<op2_t*>(&r);
+}
+__device__ __forceinline__ float2 op22f(op2_t v) { return __half22float2(v); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

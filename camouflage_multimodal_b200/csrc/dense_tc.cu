@@ -2,7 +2,7 @@
 //   warp 0   TMEM allocation, then TMA producer (one elected lane)
 //   warp 1   mbarrier init, then tcgen05.mma issuer (one elected lane), commits free the smem stages
 //   warps 2-5  epilogue: TMEM lane quarter (warp & 3), one output row per thread
-// Shared memory: 4 stages x (A 128x64 bf16 = 16 KB + W BNx64 bf16) in the canonical K-major SWIZZLE_128B
+// Shared memory: 4 stages x (A 128x64 fp16 = 16 KB + W BNx64 fp16) in the canonical K-major SWIZZLE_128B
 // layout that both the TMA tensor map and the UMMA shared-memory descriptor describe.
 #include <cuda.h>
 #include <cudaTypedefs.h>
@@ -54,8 +54,8 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32, issued by one thread for the CTA
-__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+// D[tmem] (+)= A[smem] * B[smem]^T, fp16 x fp16 -> fp32, issued by one thread for the CTA
+__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
@@ -89,16 +89,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
-// Instruction descriptor, kind::f16: D fp32 (bits 4-5 = 1), A = B = bf16 (bits 7-9, 10-12 = 1), both K-major,
-// N >> 3 at bits 17-22, M >> 4 at bits 24-28.
-__host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+// Instruction descriptor, kind::f16: D fp32 (bits 4-5 = 1), A = B = fp16 (format 0 at bits 7-9 and 10-12; fp16 would
+// be 1), both K-major, N >> 3 at bits 17-22, M >> 4 at bits 24-28.
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int m, int n) {
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ uint4 pack8(const float* x) {
     uint4 pk;
-    __nv_bfloat162 b0 = __floats2bfloat162_rn(x[0], x[1]), b1 = __floats2bfloat162_rn(x[2], x[3]);
-    __nv_bfloat162 b2 = __floats2bfloat162_rn(x[4], x[5]), b3 = __floats2bfloat162_rn(x[6], x[7]);
+    op2_t b0 = f2op2(x[0], x[1]), b1 = f2op2(x[2], x[3]);
+    op2_t b2 = f2op2(x[4], x[5]), b3 = f2op2(x[6], x[7]);
     pk.x = *reinterpret_cast<uint32_t*>(&b0);
     pk.y = *reinterpret_cast<uint32_t*>(&b1);
     pk.z = *reinterpret_cast<uint32_t*>(&b2);
@@ -192,7 +192,7 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         }
     } else if (warp == 1) {
         // ---------------------------------------------------------------- MMA issuer
-        constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN);
+        constexpr uint32_t idesc = umma_idesc_f16(TC_BM, BN);
         for (int kb = 0; kb < num_kb; ++kb) {
             if (lane == 0) {
                 const int s = kb % TC_STAGES, n = kb / TC_STAGES;
@@ -202,7 +202,7 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 const uint64_t adesc = umma_desc_sw128(a_addr), bdesc = umma_desc_sw128(a_addr + S::A_BYTES);
 #pragma unroll
                 for (int k = 0; k < TC_BK / 16; ++k)   // +32 bytes (2 x 16 B units) per UMMA_K = 16 step
-                    tc_mma_bf16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    tc_mma_f16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                 tc_commit(empty + s);                  // frees the stage once these MMAs retire
                 if (kb == num_kb - 1) tc_commit(acc_ready);
             }
@@ -235,7 +235,7 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
         const size_t res_row = (size_t)(p.res_mod > 0 ? row % p.res_mod : row) * p.ldr;
-        const __nv_bfloat16* res = (p.residual && row_ok) ? p.residual + res_row + n0 : nullptr;
+        const op_t* res = (p.residual && row_ok) ? p.residual + res_row + n0 : nullptr;
         const float* resf = (p.residual_f32 && row_ok) ? p.residual_f32 + res_row + n0 : nullptr;
         const bool res_vec = res && (p.ldr & 7) == 0 && (reinterpret_cast<uintptr_t>(p.residual + n0) & 15) == 0;
         const bool resf_vec = resf && (p.ldr & 3) == 0 && (reinterpret_cast<uintptr_t>(p.residual_f32 + n0) & 15) == 0;
@@ -268,7 +268,7 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         const uint32_t w[4] = {r8.x, r8.y, r8.z, r8.w};
 #pragma unroll
                         for (int t = 0; t < 4; ++t) {
-                            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[t]));
+                            const float2 f = op22f(*reinterpret_cast<const op2_t*>(&w[t]));
                             x[j + 2 * t] += f.x;
                             x[j + 2 * t + 1] += f.y;
                         }
@@ -276,7 +276,7 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 } else {
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
-                        if (j < valid) x[j] += __bfloat162float(res[c0 + j]);
+                        if (j < valid) x[j] += op2f(res[c0 + j]);
                 }
             }
             if (resf) {
@@ -343,12 +343,12 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const bool full32 = valid >= 32;
             if (p.sm_gs) {
                 // scores mode (N == 256): columns [0,128) hold per-head groups of sm_gs slots (sm_valid live keys
-                // each) -> softmax within the group, bf16 out [M,128]; columns [128,256) -> raw fp32 scores [M,128]
+                // each) -> softmax within the group, fp16 out [M,128]; columns [128,256) -> raw fp32 scores [M,128]
                 const int c = n0 + c0;
                 if (c < 128) {
                     if (p.sm_gs == 16) softmax_groups<16>(x, p.sm_valid, am); else softmax_groups<32>(x, p.sm_valid, am);
                     if (row_ok) {
-                        __nv_bfloat16* o = p.out_bf16 + (size_t)row * 128 + c;
+                        op_t* o = p.out_h + (size_t)row * 128 + c;
 #pragma unroll
                         for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(o + j) = pack8(x + j);
                         if (c == 96 && p.attn_mean) {
@@ -364,12 +364,12 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
                 }
             } else if (row_ok) {
-                if (p.out_bf16 && p.split_out) {
+                if (p.out_h && p.split_out) {
                     // [hi | lo | hi] thirds of a 3N-wide row: the next layer multiplies them with [W_hi | W_hi | W_lo]
-                    __nv_bfloat16* o = p.out_bf16 + (size_t)row * p.ldo_bf16 + n0 + c0;
+                    op_t* o = p.out_h + (size_t)row * p.ldo_h + n0 + c0;
                     float lo[32];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) lo[j] = x[j] - __bfloat162float(__float2bfloat16(x[j]));
+                    for (int j = 0; j < 32; ++j) lo[j] = x[j] - op2f(f2op(x[j]));
                     if (full32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0) && (p.N & 7) == 0) {
 #pragma unroll
                         for (int j = 0; j < 32; j += 8) {
@@ -382,19 +382,19 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
                             if (j < valid) {
-                                o[j] = o[2 * p.N + j] = __float2bfloat16(x[j]);
-                                o[p.N + j] = __float2bfloat16(lo[j]);
+                                o[j] = o[2 * p.N + j] = f2op(x[j]);
+                                o[p.N + j] = f2op(lo[j]);
                             }
                     }
-                } else if (p.out_bf16) {
-                    __nv_bfloat16* o = p.out_bf16 + (size_t)row * p.ldo_bf16 + n0 + c0;
+                } else if (p.out_h) {
+                    op_t* o = p.out_h + (size_t)row * p.ldo_h + n0 + c0;
                     if (full32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
                         for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(o + j) = pack8(x + j);
                     } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
-                            if (j < valid) o[j] = __float2bfloat16(x[j]);
+                            if (j < valid) o[j] = f2op(x[j]);
                     }
                 }
                 if (p.out_f32) {
@@ -437,7 +437,7 @@ static int get_encoder() {
     return CM_OK;
 }
 
-// 2-D bf16 tensor map: inner dim = cols (K), outer = rows; box = 64 x box_rows, 128-byte swizzle, OOB -> 0.
+// 2-D fp16 tensor map: inner dim = cols (K), outer = rows; box = 64 x box_rows, 128-byte swizzle, OOB -> 0.
 static int make_map(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
     using Key = std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t>;
     static std::map<Key, CUtensorMap> cache;
@@ -453,7 +453,7 @@ static int make_map(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t c
     cuuint64_t gstride[1] = {ld * 2};
     cuuint32_t box[2] = {(cuuint32_t)TC_BK, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+    CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -488,56 +488,56 @@ static int launch_dense_bn(const Dense& d, cudaStream_t st) {
 
 int launch_dense(const Dense& d, cudaStream_t st) {
     if (d.M <= 0 || d.N <= 0 || d.K <= 0) return CM_OK;
-    CM_REQUIRE(d.A && d.W && (d.out_bf16 || d.out_f32), "dense: NULL operand");
+    CM_REQUIRE(d.A && d.W && (d.out_h || d.out_f32), "dense: NULL operand");
     CM_REQUIRE(d.K % 8 == 0 && d.lda % 8 == 0 && d.lda >= d.K, "dense: K=%d / lda=%d must be multiples of 8", d.K, d.lda);
     CM_REQUIRE((reinterpret_cast<uintptr_t>(d.A) & 15) == 0 && (reinterpret_cast<uintptr_t>(d.W) & 15) == 0, "dense: operands must be 16-byte aligned");
     CM_REQUIRE(!d.ln_gamma || d.N <= 256, "dense: fused LayerNorm needs N <= 256 (N=%d)", d.N);
-    CM_REQUIRE(!d.sm_gs || ((d.sm_gs == 16 || d.sm_gs == 32) && d.N == 256 && d.out_bf16 && d.out_f32 && !d.ln_gamma &&
+    CM_REQUIRE(!d.sm_gs || ((d.sm_gs == 16 || d.sm_gs == 32) && d.N == 256 && d.out_h && d.out_f32 && !d.ln_gamma &&
                             d.sm_valid >= 1 && d.sm_valid <= d.sm_gs),
-               "dense: scores mode needs N == 256, group size 16/32, bf16 + f32 outputs");
+               "dense: scores mode needs N == 256, group size 16/32, fp16 + f32 outputs");
     if (d.N > 128) return launch_dense_bn<256>(d, st);
     return launch_dense_bn<128>(d, st);
 }
 
-__global__ void cast_bf16_kernel(const float* __restrict__ in, int ld_in, int rows, int cols, const int* rows_dev,
-                                 __nv_bfloat16* __restrict__ out, int ld_out) {
+__global__ void cast_f16_kernel(const float* __restrict__ in, int ld_in, int rows, int cols, const int* rows_dev,
+                                 op_t* __restrict__ out, int ld_out) {
     const int live = rows_dev ? min(*rows_dev, rows) : rows;
     const long long total = (long long)live * ld_out;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int r = (int)(i / ld_out), c = (int)(i - (long long)r * ld_out);
-        out[i] = __float2bfloat16(c < cols ? in[(size_t)r * ld_in + c] : 0.f);
+        out[i] = f2op(c < cols ? in[(size_t)r * ld_in + c] : 0.f);
     }
 }
 
-int launch_cast_bf16(const float* in, int ld_in, int rows, int cols, const int* rows_dev, __nv_bfloat16* out, int ld_out,
+int launch_cast_f16(const float* in, int ld_in, int rows, int cols, const int* rows_dev, op_t* out, int ld_out,
                      cudaStream_t st) {
     if (rows <= 0) return CM_OK;
     const long long total = (long long)rows * ld_out;
     int blocks = (int)std::min<long long>((total + 255) / 256, 148LL * 16);
     {
-        CM_TIMED("cast_bf16", st);
-        cast_bf16_kernel<<<blocks, 256, 0, st>>>(in, ld_in, rows, cols, rows_dev, out, ld_out);
+        CM_TIMED("cast_f16", st);
+        cast_f16_kernel<<<blocks, 256, 0, st>>>(in, ld_in, rows, cols, rows_dev, out, ld_out);
     }
-    return post_launch("cast_bf16");
+    return post_launch("cast_f16");
 }
 
-// fp32 [rows, cols] (optionally scaled per row) -> bf16 [rows, 3*kpad] = [hi | hi | lo], each third zero-padded to kpad
+// fp32 [rows, cols] (optionally scaled per row) -> fp16 [rows, 3*kpad] = [hi | hi | lo], each third zero-padded to kpad
 __global__ void split_weight_kernel(const float* __restrict__ in, int rows, int cols, int kpad, const float* __restrict__ row_scale,
-                                    __nv_bfloat16* __restrict__ out) {
+                                    op_t* __restrict__ out) {
     const long long total = (long long)rows * kpad;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int r = (int)(i / kpad), c = (int)(i - (long long)r * kpad);
         float v = c < cols ? in[(size_t)r * cols + c] : 0.f;
         if (row_scale) v *= row_scale[r];
-        const __nv_bfloat16 hi = __float2bfloat16(v);
-        __nv_bfloat16* o = out + (size_t)r * 3 * kpad + c;
+        const op_t hi = f2op(v);
+        op_t* o = out + (size_t)r * 3 * kpad + c;
         o[0] = hi;
         o[kpad] = hi;
-        o[2 * kpad] = __float2bfloat16(v - __bfloat162float(hi));
+        o[2 * kpad] = f2op(v - op2f(hi));
     }
 }
 
-int launch_split_weight(const float* in, int rows, int cols, int kpad, const float* row_scale, __nv_bfloat16* out, cudaStream_t st) {
+int launch_split_weight(const float* in, int rows, int cols, int kpad, const float* row_scale, op_t* out, cudaStream_t st) {
     if (rows <= 0) return CM_OK;
     {
         CM_TIMED("fold_weights", st);
@@ -549,26 +549,26 @@ int launch_split_weight(const float* in, int rows, int cols, int kpad, const flo
 }  // namespace cm
 
 // Exported building block (also the unit-test hook for the tensor-core path): see include/cm_b200.h.
-extern "C" int cm_linear_bf16(const void* a_bf16, int lda, const void* w_bf16, int m, int n, int k, const int32_t* m_dev,
-                              const float* bias, float alpha, int relu, const void* residual_bf16, int ldr,
-                              const float* ln_gamma, const float* ln_beta, void* out_bf16, float* out_f32, void* stream) {
+extern "C" int cm_linear_f16(const void* a_f16, int lda, const void* w_f16, int m, int n, int k, const int32_t* m_dev,
+                              const float* bias, float alpha, int relu, const void* residual_h, int ldr,
+                              const float* ln_gamma, const float* ln_beta, void* out_h, float* out_f32, void* stream) {
     using namespace cm;
     CM_DEVICE_OR_RETURN();
     Dense d;
-    d.A = reinterpret_cast<const __nv_bfloat16*>(a_bf16);
+    d.A = reinterpret_cast<const op_t*>(a_f16);
     d.lda = lda;
-    d.W = reinterpret_cast<const __nv_bfloat16*>(w_bf16);
+    d.W = reinterpret_cast<const op_t*>(w_f16);
     d.M = m; d.N = n; d.K = k;
     d.m_dev = m_dev;
     d.bias = bias; d.alpha = alpha; d.relu = relu;
-    d.residual = reinterpret_cast<const __nv_bfloat16*>(residual_bf16);
+    d.residual = reinterpret_cast<const op_t*>(residual_h);
     d.ldr = ldr;
     d.ln_gamma = ln_gamma; d.ln_beta = ln_beta;
-    d.out_bf16 = reinterpret_cast<__nv_bfloat16*>(out_bf16);
-    d.ldo_bf16 = n;
+    d.out_h = reinterpret_cast<op_t*>(out_h);
+    d.ldo_h = n;
     d.out_f32 = out_f32;
     d.ldo_f32 = n;
-    CM_REQUIRE(m > 0 && n > 0 && k > 0, "cm_linear_bf16: bad shape");
-    CM_REQUIRE(!ln_gamma || ln_beta, "cm_linear_bf16: ln_beta missing");
+    CM_REQUIRE(m > 0 && n > 0 && k > 0, "cm_linear_f16: bad shape");
+    CM_REQUIRE(!ln_gamma || ln_beta, "cm_linear_f16: ln_beta missing");
     return launch_dense(d, as_stream(stream));
 }

@@ -1,38 +1,38 @@
-// Dense layer on the 5th-generation tensor cores (sm_100a): bf16 operands staged by TMA (128B swizzle) into a
+// Dense layer on the 5th-generation tensor cores (sm_100a): fp16 operands staged by TMA (128B swizzle) into a
 // 4-stage shared-memory ring, tcgen05.mma accumulating fp32 in TMEM, epilogue read back with tcgen05.ld.
 //   out[m, n] = LN?( act( alpha * (sum_k A[m,k] W[n,k] + bias[n]) + residual[m,n] ) )
-// A [M,K] and W [N,K] are K-major bf16 (W is an nn.Linear weight).  M is a capacity; *m_dev the live rows.
+// A [M,K] and W [N,K] are K-major fp16 (W is an nn.Linear weight).  M is a capacity; *m_dev the live rows.
 #pragma once
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "common.cuh"
 
 namespace cm {
 
 struct Dense {
-    const __nv_bfloat16* A = nullptr;   // [M, lda] bf16, lda % 8 == 0
+    const op_t* A = nullptr;   // [M, lda] fp16, lda % 8 == 0
     int lda = 0;
-    const __nv_bfloat16* W = nullptr;   // [N, K] bf16 (row stride K, K % 8 == 0)
+    const op_t* W = nullptr;   // [N, K] fp16 (row stride K, K % 8 == 0)
     int M = 0, N = 0, K = 0;
     const int* m_dev = nullptr;
     const float* bias = nullptr;        // [N]
     float alpha = 1.f;
     int relu = 0;
-    const __nv_bfloat16* residual = nullptr;   // [M or res_mod, ldr] bf16, added after alpha
+    const op_t* residual = nullptr;   // [M or res_mod, ldr] fp16, added after alpha
     const float* residual_f32 = nullptr;       // same role in fp32 (at most one of the two)
     int ldr = 0;
     int res_mod = 0;
     const float* ln_gamma = nullptr;    // LayerNorm over the N outputs (needs N <= 256: one tile per row)
     const float* ln_beta = nullptr;
-    __nv_bfloat16* out_bf16 = nullptr;
-    int ldo_bf16 = 0;
-    // split_out: out_bf16 rows are 3N wide, [hi | lo | hi] with hi = bf16(v), lo = bf16(v - hi): fed to the next
+    op_t* out_h = nullptr;
+    int ldo_h = 0;
+    // split_out: out_h rows are 3N wide, [hi | lo | hi] with hi = fp16(v), lo = fp16(v - hi): fed to the next
     // layer against [W_hi | W_hi | W_lo] (launch_split_weight) the three products recover ~16 mantissa bits.
     int split_out = 0;
     float* out_f32 = nullptr;
     int ldo_f32 = 0;
     // scores mode (sm_gs = 16 or 32, N == 256): output columns [0,128) are 128/sm_gs head groups of sm_gs slots with
-    // sm_valid live keys each -> per-group softmax, written bf16 to out_bf16 [M,128]; columns [128,256) -> raw fp32
+    // sm_valid live keys each -> per-group softmax, written fp16 to out_h [M,128]; columns [128,256) -> raw fp32
     // to out_f32 [M,128]; attn_mean [M, sm_valid] (optional) = mean over the head groups of the probabilities.
     int sm_gs = 0, sm_valid = 0;
     float* attn_mean = nullptr;
@@ -40,11 +40,11 @@ struct Dense {
 
 int launch_dense(const Dense& d, cudaStream_t st);
 
-// fp32 -> bf16 row copy with zero padding of columns [cols, ld_out): out[r, c] = in[r, c]
-int launch_cast_bf16(const float* in, int ld_in, int rows, int cols, const int* rows_dev, __nv_bfloat16* out, int ld_out,
+// fp32 -> fp16 row copy with zero padding of columns [cols, ld_out): out[r, c] = in[r, c]
+int launch_cast_f16(const float* in, int ld_in, int rows, int cols, const int* rows_dev, op_t* out, int ld_out,
                      cudaStream_t st);
 
-// fp32 weight [rows, cols] (optional per-row scale) -> bf16 [rows, 3*kpad] = [hi | hi | lo] thirds, zero padded
-int launch_split_weight(const float* in, int rows, int cols, int kpad, const float* row_scale, __nv_bfloat16* out, cudaStream_t st);
+// fp32 weight [rows, cols] (optional per-row scale) -> fp16 [rows, 3*kpad] = [hi | hi | lo] thirds, zero padded
+int launch_split_weight(const float* in, int rows, int cols, int kpad, const float* row_scale, op_t* out, cudaStream_t st);
 
 }  // namespace cm

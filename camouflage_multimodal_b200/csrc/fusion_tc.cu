@@ -55,7 +55,7 @@ FusionFolded fusion_folded_layout(const cm_fusion_params* p, int n_kg) {
     f.fl1 = take(3 * 2 * D * D * 2);
     f.fl2 = take(3 * D * D * 2);
     f.hw1 = take(3 * 4 * (D / 2) * D * 2);
-    f.kp_bf16 = take(K * D * 2);
+    f.kp_h = take(K * D * 2);
     f.ccat = take(256 * 4);
     f.hb1 = take(4 * (D / 2) * 4);
     f.kp = take(K * D * 4);
@@ -65,15 +65,15 @@ FusionFolded fusion_folded_layout(const cm_fusion_params* p, int n_kg) {
     return f;
 }
 
-__global__ void cast_weight_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, size_t n) {
+__global__ void cast_weight_kernel(const float* __restrict__ in, op_t* __restrict__ out, size_t n) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        out[i] = __float2bfloat16(in[i]);
+        out[i] = f2op(in[i]);
 }
 
 static int cast_weight(const float* in, void* out, size_t n, cudaStream_t st) {
     {
         CM_TIMED("fusion_fold", st);
-        cast_weight_kernel<<<ceil_div((long long)n, 256 * 4), 256, 0, st>>>(in, reinterpret_cast<__nv_bfloat16*>(out), n);
+        cast_weight_kernel<<<ceil_div((long long)n, 256 * 4), 256, 0, st>>>(in, reinterpret_cast<op_t*>(out), n);
     }
     return post_launch("fusion_fold(cast)");
 }
@@ -81,7 +81,7 @@ static int cast_weight(const float* in, void* out, size_t n, cudaStream_t st) {
 // One thread per folded element: wcat rows [0,128) = U1, [128,256) = U2 (slot h*gs+k, padding rows 0), ccat,
 // vot [D,128] (VO transposed so it is an nn.Linear-style [out, in] weight for the P1 x VO product).
 __global__ void fusion_fold_kernel(cm_fusion_params p, int n_kg, int gs, const float* __restrict__ k1v1, const float* __restrict__ q2,
-                                   __nv_bfloat16* __restrict__ wcat, float* __restrict__ ccat, __nv_bfloat16* __restrict__ vot) {
+                                   op_t* __restrict__ wcat, float* __restrict__ ccat, op_t* __restrict__ vot) {
     const int D = p.hidden, H = p.heads, hd = D / H;
     const float scale = 1.0f / sqrtf((float)hd);
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (long long)gridDim.x * blockDim.x;
@@ -96,7 +96,7 @@ __global__ void fusion_fold_kernel(cm_fusion_params p, int n_kg, int gs, const f
                 for (int d = 0; d < hd; ++d) s = fmaf(p.k2r_in_w[(size_t)(D + h * hd + d) * D + c], q2[(size_t)k * D + h * hd + d], s);
             }
         }
-        wcat[i] = __float2bfloat16(s);
+        wcat[i] = f2op(s);
     }
     for (long long i = tid; i < 256; i += stride) {
         const int slot = (int)i & 127, h = slot / gs, k = slot % gs;
@@ -112,21 +112,21 @@ __global__ void fusion_fold_kernel(cm_fusion_params p, int n_kg, int gs, const f
         float s = 0.f;
         if (h < H && k < n_kg)
             for (int d = 0; d < hd; ++d) s = fmaf(p.r2k_out_w[(size_t)c * D + h * hd + d], k1v1[(size_t)k * 2 * D + D + h * hd + d], s);
-        vot[i] = __float2bfloat16(s);
+        vot[i] = f2op(s);
     }
 }
 
-__global__ void concat_heads1_kernel(cm_fusion_params p, __nv_bfloat16* __restrict__ hw1, float* __restrict__ hb1) {
+__global__ void concat_heads1_kernel(cm_fusion_params p, op_t* __restrict__ hw1, float* __restrict__ hb1) {
     const int D = p.hidden, H2 = D / 2;
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (long long)gridDim.x * blockDim.x;
     for (long long i = tid; i < 4LL * H2 * D; i += stride) {
         const int t = (int)(i / ((long long)H2 * D)), o = (int)(i / D), c = (int)(i % D);
         const float v = p.head_w1[t][i - (long long)t * H2 * D];
-        const __nv_bfloat16 hi = __float2bfloat16(v);
-        __nv_bfloat16* w = hw1 + (size_t)o * 3 * D + c;
+        const op_t hi = f2op(v);
+        op_t* w = hw1 + (size_t)o * 3 * D + c;
         w[0] = hi;
         w[D] = hi;
-        w[2 * D] = __float2bfloat16(v - __bfloat162float(hi));
+        w[2 * D] = f2op(v - op2f(hi));
     }
     for (long long i = tid; i < 4LL * H2; i += stride) hb1[i] = p.head_b1[(int)(i / H2)][i % H2];
 }
@@ -134,9 +134,9 @@ __global__ void concat_heads1_kernel(cm_fusion_params p, __nv_bfloat16* __restri
 // kg -> rg attention on the folded scores: grid (n_graphs, n_kg), one thread per channel c (head h = c / hd).
 //   p2[h][n] = softmax over the image's nodes n of s2[n, h*gs + k];  ctx2[b*K + k, c] = sum_n p2[h(c)][n] v2[n, c]
 // attn (optional) block [n_kg, N_b] at n_kg*node_ptr[b]: mean over heads of p2.
-__global__ void __launch_bounds__(256) attn_kg2rg_fold_kernel(const float* __restrict__ s2, const __nv_bfloat16* __restrict__ v2, int D,
+__global__ void __launch_bounds__(256) attn_kg2rg_fold_kernel(const float* __restrict__ s2, const op_t* __restrict__ v2, int D,
                                                               int heads, int gs, const int* __restrict__ node_ptr, int n_kg,
-                                                              __nv_bfloat16* __restrict__ ctx2, float* __restrict__ attn) {
+                                                              op_t* __restrict__ ctx2, float* __restrict__ attn) {
     __shared__ float s_max[32], s_inv[32];
     __shared__ float s_p[8][33];
     const int b = blockIdx.x, k = blockIdx.y, c = threadIdx.x;
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(256) attn_kg2rg_fold_kernel(const float* __res
         __syncthreads();
         const int cnt = min(32, n1 - base);
         if (c < D)
-            for (int i = 0; i < cnt; ++i) acc = fmaf(s_p[my_h][i], __bfloat162float(v2[(size_t)(base + i) * D + c]), acc);
+            for (int i = 0; i < cnt; ++i) acc = fmaf(s_p[my_h][i], op2f(v2[(size_t)(base + i) * D + c]), acc);
         if (attn && c < cnt) {
             float tot = 0.f;
             for (int h = 0; h < heads; ++h) tot += s_p[h][c];
@@ -176,10 +176,10 @@ __global__ void __launch_bounds__(256) attn_kg2rg_fold_kernel(const float* __res
         __syncthreads();
     }
     if (c < D) {   // split row [hi | lo | hi]
-        __nv_bfloat16* o = ctx2 + ((size_t)b * n_kg + k) * 3 * D + c;
-        const __nv_bfloat16 hi = __float2bfloat16(acc);
+        op_t* o = ctx2 + ((size_t)b * n_kg + k) * 3 * D + c;
+        const op_t hi = f2op(acc);
         o[0] = hi;
-        o[D] = __float2bfloat16(acc - __bfloat162float(hi));
+        o[D] = f2op(acc - op2f(hi));
         o[2 * D] = hi;
     }
 }
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(256) attn_kg2rg_fold_kernel(const float* __res
 // out[g, c] = mean over rows seg_ptr[g] .. (or fixed_len rows) of in, written as a split row: thirds of `third`
 // columns [hi | lo | hi], this segment mean landing at column offset col0 of each third
 __global__ void __launch_bounds__(128) segment_mean_split_kernel(const float* __restrict__ in, int dim, const int* __restrict__ seg_ptr,
-                                                                 int fixed_len, __nv_bfloat16* __restrict__ out, int third, int col0) {
+                                                                 int fixed_len, op_t* __restrict__ out, int third, int col0) {
     const int g = blockIdx.x, c = blockIdx.y * 128 + threadIdx.x;
     if (c >= dim) return;
     const int a = seg_ptr ? seg_ptr[g] : g * fixed_len;
@@ -203,14 +203,14 @@ __global__ void __launch_bounds__(128) segment_mean_split_kernel(const float* __
     for (; r < z; ++r) s0 += in[(size_t)r * dim + c];
     const int n = z - a;
     const float v = n > 0 ? ((s0 + s1) + (s2 + s3)) / (float)n : 0.f;
-    __nv_bfloat16* o = out + (size_t)g * 3 * third + col0 + c;
-    const __nv_bfloat16 hi = __float2bfloat16(v);
+    op_t* o = out + (size_t)g * 3 * third + col0 + c;
+    const op_t hi = f2op(v);
     o[0] = hi;
-    o[third] = __float2bfloat16(v - __bfloat162float(hi));
+    o[third] = f2op(v - op2f(hi));
     o[2 * third] = hi;
 }
 
-static int seg_mean_split(const float* in, int dim, const int* seg_ptr, int fixed_len, int n_seg, __nv_bfloat16* out, int third, int col0,
+static int seg_mean_split(const float* in, int dim, const int* seg_ptr, int fixed_len, int n_seg, op_t* out, int third, int col0,
                           cudaStream_t st) {
     dim3 grid(n_seg, ceil_div(dim, 128));
     {
@@ -242,8 +242,8 @@ int fusion_fold(const cm_fusion_params* p, const float* kg, int n_kg, void* fold
     if ((rc = launch_linear(l, st)) != CM_OK) return rc;
     {
         CM_TIMED("fusion_fold", st);
-        fusion_fold_kernel<<<256, 256, 0, st>>>(*p, K, f.gs, k1v1, q2, reinterpret_cast<__nv_bfloat16*>(base + f.wcat),
-                                                reinterpret_cast<float*>(base + f.ccat), reinterpret_cast<__nv_bfloat16*>(base + f.vot));
+        fusion_fold_kernel<<<256, 256, 0, st>>>(*p, K, f.gs, k1v1, q2, reinterpret_cast<op_t*>(base + f.wcat),
+                                                reinterpret_cast<float*>(base + f.ccat), reinterpret_cast<op_t*>(base + f.vot));
     }
     if ((rc = post_launch("fusion_fold")) != CM_OK) return rc;
     if (p->rg_proj_w && (rc = cast_weight(p->rg_proj_w, base + f.w_rgproj, (size_t)D * p->rg_dim, st)) != CM_OK) return rc;
@@ -251,18 +251,18 @@ int fusion_fold(const cm_fusion_params* p, const float* kg, int n_kg, void* fold
     if ((rc = cast_weight(p->ffn_rg_w1, base + f.ffn1, (size_t)2 * D * D, st)) != CM_OK) return rc;
     if ((rc = cast_weight(p->ffn_rg_w2, base + f.ffn2, (size_t)2 * D * D, st)) != CM_OK) return rc;
     auto SW = [&](const float* w, int rows, int cols, size_t off) {
-        return launch_split_weight(w, rows, cols, cols, nullptr, reinterpret_cast<__nv_bfloat16*>(base + off), st);
+        return launch_split_weight(w, rows, cols, cols, nullptr, reinterpret_cast<op_t*>(base + off), st);
     };
     if ((rc = SW(p->k2r_out_w, D, D, f.wo2)) != CM_OK) return rc;
     if ((rc = SW(p->ffn_kg_w1, 2 * D, D, f.kffn1)) != CM_OK) return rc;
     if ((rc = SW(p->ffn_kg_w2, D, 2 * D, f.kffn2)) != CM_OK) return rc;
     if ((rc = SW(p->fl_w1, D, 2 * D, f.fl1)) != CM_OK) return rc;
     if ((rc = SW(p->fl_w2, D, D, f.fl2)) != CM_OK) return rc;
-    if ((rc = cast_weight(kp, base + f.kp_bf16, (size_t)K * D, st)) != CM_OK) return rc;
+    if ((rc = cast_weight(kp, base + f.kp_h, (size_t)K * D, st)) != CM_OK) return rc;
     if (p->head_w1[0]) {
         {
             CM_TIMED("fusion_fold", st);
-            concat_heads1_kernel<<<64, 256, 0, st>>>(*p, reinterpret_cast<__nv_bfloat16*>(base + f.hw1), reinterpret_cast<float*>(base + f.hb1));
+            concat_heads1_kernel<<<64, 256, 0, st>>>(*p, reinterpret_cast<op_t*>(base + f.hw1), reinterpret_cast<float*>(base + f.hb1));
         }
         if ((rc = post_launch("fusion_fold(heads)")) != CM_OK) return rc;
     }
@@ -270,7 +270,7 @@ int fusion_fold(const cm_fusion_params* p, const float* kg, int n_kg, void* fold
 }
 
 struct FusionTcWs {
-    __nv_bfloat16 *rgb, *r, *p1, *v2, *y0, *hh, *ctx2, *z0, *hk, *both, *f1, *fusedb;
+    op_t *rgb, *r, *p1, *v2, *y0, *hh, *ctx2, *z0, *hk, *both, *f1, *fusedb;
     float *s2, *y, *z, *z0f, *fused, *hid;
     size_t total;
 };
@@ -279,18 +279,18 @@ static FusionTcWs carve_fusion_tc(void* ws, const cm_fusion_params* p, int G, in
     Carver c(ws);
     FusionTcWs w;
     const size_t D = p->hidden, m = M, gk = (size_t)G * Kk;
-    w.rgb = c.take<__nv_bfloat16>(m * p->rg_dim);
-    w.r = c.take<__nv_bfloat16>(m * D);
-    w.p1 = c.take<__nv_bfloat16>(m * 128);
-    w.v2 = c.take<__nv_bfloat16>(m * D);
-    w.y0 = c.take<__nv_bfloat16>(m * D);
-    w.hh = c.take<__nv_bfloat16>(m * 2 * D);
-    w.ctx2 = c.take<__nv_bfloat16>(gk * 3 * D);
-    w.z0 = c.take<__nv_bfloat16>(gk * 3 * D);
-    w.hk = c.take<__nv_bfloat16>(gk * 3 * 2 * D);
-    w.both = c.take<__nv_bfloat16>((size_t)G * 3 * 2 * D);
-    w.f1 = c.take<__nv_bfloat16>((size_t)G * 3 * D);
-    w.fusedb = c.take<__nv_bfloat16>((size_t)G * 3 * D);
+    w.rgb = c.take<op_t>(m * p->rg_dim);
+    w.r = c.take<op_t>(m * D);
+    w.p1 = c.take<op_t>(m * 128);
+    w.v2 = c.take<op_t>(m * D);
+    w.y0 = c.take<op_t>(m * D);
+    w.hh = c.take<op_t>(m * 2 * D);
+    w.ctx2 = c.take<op_t>(gk * 3 * D);
+    w.z0 = c.take<op_t>(gk * 3 * D);
+    w.hk = c.take<op_t>(gk * 3 * 2 * D);
+    w.both = c.take<op_t>((size_t)G * 3 * 2 * D);
+    w.f1 = c.take<op_t>((size_t)G * 3 * D);
+    w.fusedb = c.take<op_t>((size_t)G * 3 * D);
     w.z0f = c.take<float>(gk * D);
     w.s2 = c.take<float>(m * 128);
     w.y = c.take<float>(m * D);
@@ -308,37 +308,37 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
                       float* attn_rg2kg, float* attn_kg2rg, cudaStream_t st) {
     const FusionFolded f = fusion_folded_layout(p, Kk);
     const char* base = reinterpret_cast<const char*>(folded);
-    auto W = [&](size_t off) { return reinterpret_cast<const __nv_bfloat16*>(base + off); };
+    auto W = [&](size_t off) { return reinterpret_cast<const op_t*>(base + off); };
     FusionTcWs w = carve_fusion_tc(workspace, p, G, M, Kk);
     const int D = p->hidden, GK = G * Kk;
     const int* m_dev = node_ptr + G;
     int rc;
     Dense d;
 
-    if ((rc = launch_cast_bf16(rg, p->rg_dim, M, p->rg_dim, m_dev, w.rgb, p->rg_dim, st)) != CM_OK) return rc;
-    const __nv_bfloat16* r = w.rgb;
+    if ((rc = launch_cast_f16(rg, p->rg_dim, M, p->rg_dim, m_dev, w.rgb, p->rg_dim, st)) != CM_OK) return rc;
+    const op_t* r = w.rgb;
     if (p->rg_proj_w) {   // fusion_model.py:108
         d = Dense(); d.A = w.rgb; d.lda = p->rg_dim; d.W = W(f.w_rgproj); d.M = M; d.N = D; d.K = p->rg_dim; d.m_dev = m_dev;
-        d.bias = p->rg_proj_b; d.out_bf16 = w.r; d.ldo_bf16 = D;
+        d.bias = p->rg_proj_b; d.out_h = w.r; d.ldo_h = D;
         if ((rc = launch_dense(d, st)) != CM_OK) return rc;
         r = w.r;
     }
     // scores of both directions in one pass over r: P1 = softmax_k(r U1^T + c1), S2 = r U2^T
     d = Dense(); d.A = r; d.lda = D; d.W = W(f.wcat); d.M = M; d.N = 256; d.K = D; d.m_dev = m_dev;
-    d.bias = reinterpret_cast<const float*>(base + f.ccat); d.out_bf16 = w.p1; d.ldo_bf16 = 128; d.out_f32 = w.s2; d.ldo_f32 = 128;
+    d.bias = reinterpret_cast<const float*>(base + f.ccat); d.out_h = w.p1; d.ldo_h = 128; d.out_f32 = w.s2; d.ldo_f32 = 128;
     d.sm_gs = f.gs; d.sm_valid = Kk; d.attn_mean = attn_rg2kg;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     // V of the kg -> rg direction (:123-129)
     d = Dense(); d.A = r; d.lda = D; d.W = W(f.wv2); d.M = M; d.N = D; d.K = D; d.m_dev = m_dev;
-    d.bias = p->k2r_in_b + 2 * D; d.out_bf16 = w.v2; d.ldo_bf16 = D;
+    d.bias = p->k2r_in_b + 2 * D; d.out_h = w.v2; d.ldo_h = D;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     // y0 = LN(r + P1 VO + bo1) (:119)
     d = Dense(); d.A = w.p1; d.lda = 128; d.W = W(f.vot); d.M = M; d.N = D; d.K = 128; d.m_dev = m_dev;
-    d.bias = p->r2k_out_b; d.residual = r; d.ldr = D; d.ln_gamma = p->ln_rg_w; d.ln_beta = p->ln_rg_b; d.out_bf16 = w.y0; d.ldo_bf16 = D;
+    d.bias = p->r2k_out_b; d.residual = r; d.ldr = D; d.ln_gamma = p->ln_rg_w; d.ln_beta = p->ln_rg_b; d.out_h = w.y0; d.ldo_h = D;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     // y = y0 + FFN(y0) (:120), mean over the image's nodes (:134)
     d = Dense(); d.A = w.y0; d.lda = D; d.W = W(f.ffn1); d.M = M; d.N = 2 * D; d.K = D; d.m_dev = m_dev;
-    d.bias = p->ffn_rg_b1; d.relu = 1; d.out_bf16 = w.hh; d.ldo_bf16 = 2 * D;
+    d.bias = p->ffn_rg_b1; d.relu = 1; d.out_h = w.hh; d.ldo_h = 2 * D;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     d = Dense(); d.A = w.hh; d.lda = 2 * D; d.W = W(f.ffn2); d.M = M; d.N = D; d.K = 2 * D; d.m_dev = m_dev;
     d.bias = p->ffn_rg_b2; d.residual = w.y0; d.ldr = D; d.out_f32 = w.y; d.ldo_f32 = D;
@@ -355,10 +355,10 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     if ((rc = post_launch("attn_kg2rg")) != CM_OK) return rc;
     d = Dense(); d.A = w.ctx2; d.lda = 3 * D; d.W = W(f.wo2); d.M = GK; d.N = D; d.K = 3 * D;
     d.bias = p->k2r_out_b; d.residual_f32 = reinterpret_cast<const float*>(base + f.kp); d.ldr = D; d.res_mod = Kk;
-    d.ln_gamma = p->ln_kg_w; d.ln_beta = p->ln_kg_b; d.out_bf16 = w.z0; d.ldo_bf16 = 3 * D; d.split_out = 1; d.out_f32 = w.z0f; d.ldo_f32 = D;
+    d.ln_gamma = p->ln_kg_w; d.ln_beta = p->ln_kg_b; d.out_h = w.z0; d.ldo_h = 3 * D; d.split_out = 1; d.out_f32 = w.z0f; d.ldo_f32 = D;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     d = Dense(); d.A = w.z0; d.lda = 3 * D; d.W = W(f.kffn1); d.M = GK; d.N = 2 * D; d.K = 3 * D;
-    d.bias = p->ffn_kg_b1; d.relu = 1; d.out_bf16 = w.hk; d.ldo_bf16 = 6 * D; d.split_out = 1;
+    d.bias = p->ffn_kg_b1; d.relu = 1; d.out_h = w.hk; d.ldo_h = 6 * D; d.split_out = 1;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     d = Dense(); d.A = w.hk; d.lda = 6 * D; d.W = W(f.kffn2); d.M = GK; d.N = D; d.K = 6 * D;
     d.bias = p->ffn_kg_b2; d.residual_f32 = w.z0f; d.ldr = D; d.out_f32 = w.z; d.ldo_f32 = D;
@@ -368,10 +368,10 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     // ---- fusion layer (:138-139) and the four heads (:239-242)
     float* fused = fused_out ? fused_out : w.fused;
     d = Dense(); d.A = w.both; d.lda = 6 * D; d.W = W(f.fl1); d.M = G; d.N = D; d.K = 6 * D;
-    d.bias = p->fl_b1; d.relu = 1; d.out_bf16 = w.f1; d.ldo_bf16 = 3 * D; d.split_out = 1;
+    d.bias = p->fl_b1; d.relu = 1; d.out_h = w.f1; d.ldo_h = 3 * D; d.split_out = 1;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     d = Dense(); d.A = w.f1; d.lda = 3 * D; d.W = W(f.fl2); d.M = G; d.N = D; d.K = 3 * D;
-    d.bias = p->fl_b2; d.out_bf16 = w.fusedb; d.ldo_bf16 = 3 * D; d.split_out = 1; d.out_f32 = fused; d.ldo_f32 = D;
+    d.bias = p->fl_b2; d.out_h = w.fusedb; d.ldo_h = 3 * D; d.split_out = 1; d.out_f32 = fused; d.ldo_f32 = D;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     if (mask_out || instance_out || edge_out || score_out) {
         const int H2 = D / 2;

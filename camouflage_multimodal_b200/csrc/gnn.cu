@@ -14,7 +14,7 @@
 
 namespace cm {
 
-struct GnnFolded {   // float offsets into the folded blob (the *_h entries hold bf16 weights for the tensor cores)
+struct GnnFolded {   // float offsets into the folded blob (the *_h entries hold fp16 weights for the tensor cores)
     size_t u_src, u_dst, bias1, convb[3], head1b, wcat_h, convw_h[3], fcw_h, head1w_h, total;
     int zk;   // K of the GAT dense layer: [z_hi | z_lo | z_hi], each third padded to a multiple of 64 columns
 };
@@ -44,17 +44,17 @@ static GnnFolded gnn_layout(const cm_gnn_params* p) {
 }
 
 // weight thirds [hi | hi | lo], `third` columns apart
-__device__ __forceinline__ void store_split_w(__nv_bfloat16* o, int third, float v) {
-    const __nv_bfloat16 hi = __float2bfloat16(v);
+__device__ __forceinline__ void store_split_w(op_t* o, int third, float v) {
+    const op_t hi = f2op(v);
     o[0] = hi;
     o[third] = hi;
-    o[2 * third] = __float2bfloat16(v - __bfloat162float(hi));
+    o[2 * third] = f2op(v - op2f(hi));
 }
 // activation thirds [hi | lo | hi]
-__device__ __forceinline__ void store_split_a(__nv_bfloat16* o, int third, float v) {
-    const __nv_bfloat16 hi = __float2bfloat16(v);
+__device__ __forceinline__ void store_split_a(op_t* o, int third, float v) {
+    const op_t hi = f2op(v);
     o[0] = hi;
-    o[third] = __float2bfloat16(v - __bfloat162float(hi));
+    o[third] = f2op(v - op2f(hi));
     o[2 * third] = hi;
 }
 
@@ -74,10 +74,10 @@ __global__ void gnn_fold_kernel(cm_gnn_params p, GnnFolded f, float* __restrict_
         blob[f.u_src + i] = s;
         blob[f.u_dst + i] = d;
     }
-    // wcat [H, zk] bf16 = [Wf_hi | Wf_hi | Wf_lo] with Wf[o, h*C+c] = W[h*H+o, c] / heads * bn1 scale; bias1.
+    // wcat [H, zk] fp16 = [Wf_hi | Wf_hi | Wf_lo] with Wf[o, h*C+c] = W[h*H+o, c] / heads * bn1 scale; bias1.
     // All dense layers of the GNN run in this split form: activations arrive as [a_hi | a_lo | a_hi], so the three
-    // K-thirds are a_hi W_hi + a_lo W_hi + a_hi W_lo -- bf16 tensor-core products with ~16 bits of mantissa.
-    __nv_bfloat16* wcat = reinterpret_cast<__nv_bfloat16*>(blob + f.wcat_h);
+    // K-thirds are a_hi W_hi + a_lo W_hi + a_hi W_lo -- fp16 tensor-core products with ~16 bits of mantissa.
+    op_t* wcat = reinterpret_cast<op_t*>(blob + f.wcat_h);
     const int third = f.zk / 3;
     for (long long i = tid; i < (long long)H * third; i += stride) {
         const int o = (int)(i / third), hc = (int)(i % third);
@@ -95,7 +95,7 @@ __global__ void gnn_fold_kernel(cm_gnn_params p, GnnFolded f, float* __restrict_
     }
     for (int k = 0; k < 3; ++k) {
         const float *bw = p.bn_weight[k + 1], *bb = p.bn_bias[k + 1], *bm = p.bn_mean[k + 1], *bv = p.bn_var[k + 1];
-        __nv_bfloat16* cw = reinterpret_cast<__nv_bfloat16*>(blob + f.convw_h[k]);
+        op_t* cw = reinterpret_cast<op_t*>(blob + f.convw_h[k]);
         for (long long i = tid; i < (long long)H * H; i += stride) {
             const int o = (int)(i / H), c = (int)(i % H);
             store_split_w(cw + (size_t)o * 3 * H + c, H, p.conv_lin_weight[k][i] * (bw[o] / sqrtf(bv[o] + p.bn_eps)));
@@ -106,12 +106,12 @@ __global__ void gnn_fold_kernel(cm_gnn_params p, GnnFolded f, float* __restrict_
         }
     }
     const int H2 = H / 2;
-    __nv_bfloat16* h1 = reinterpret_cast<__nv_bfloat16*>(blob + f.head1w_h);
+    op_t* h1 = reinterpret_cast<op_t*>(blob + f.head1w_h);
     for (long long i = tid; i < 3LL * H2 * H; i += stride) {
         const int t = (int)(i / ((long long)H2 * H)), o = (int)(i / H), c = (int)(i % H);
         store_split_w(h1 + (size_t)o * 3 * H + c, H, p.head1_weight[t][i - (long long)t * H2 * H]);
     }
-    __nv_bfloat16* fw = reinterpret_cast<__nv_bfloat16*>(blob + f.fcw_h);
+    op_t* fw = reinterpret_cast<op_t*>(blob + f.fcw_h);
     for (long long i = tid; i < (long long)H * H; i += stride)
         store_split_w(fw + (size_t)(i / H) * 3 * H + (i % H), H, p.fc_shared_weight[i]);
     for (long long i = tid; i < 3LL * H2; i += stride) blob[f.head1b + i] = p.head1_bias[(int)(i / H2)][i % H2];
@@ -140,7 +140,7 @@ template <int HEADS>
 __global__ void __launch_bounds__(256) gat_aggregate_kernel(const float* __restrict__ x, int C, const int* __restrict__ row_ptr,
                                                             const int* __restrict__ col, const float* __restrict__ a_src,
                                                             const float* __restrict__ a_dst, const int* n_dev, int cap,
-                                                            __nv_bfloat16* __restrict__ z, int zk) {
+                                                            op_t* __restrict__ z, int zk) {
     const int g = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int n = n_dev ? min(*n_dev, cap) : cap;
     if (g >= n) return;
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(256) gat_aggregate_kernel(const float* __restr
         }
     }
     // z row = [z_hi | z_lo | z_hi], each third padded with zeros to zk/3 columns
-    __nv_bfloat16* zr = z + (size_t)g * zk;
+    op_t* zr = z + (size_t)g * zk;
     const int third = zk / 3;
     if (lane < C) {
 #pragma unroll
@@ -201,10 +201,10 @@ __global__ void gcn_norm_kernel(const int* __restrict__ row_ptr, const int* __re
     dis[i] = isinf(r) ? 0.f : r;
 }
 
-// One warp per target node, lane owns 4 consecutive channels per 128-channel group; bf16 rows, fp32 accumulation.
-__device__ __forceinline__ void fma4_bf16(float4& acc, float s, uint2 raw) {
-    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&raw.x), b = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
-    const float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+// One warp per target node, lane owns 4 consecutive channels per 128-channel group; fp16 rows, fp32 accumulation.
+__device__ __forceinline__ void fma4_h(float4& acc, float s, uint2 raw) {
+    const op2_t a = *reinterpret_cast<const op2_t*>(&raw.x), b = *reinterpret_cast<const op2_t*>(&raw.y);
+    const float2 fa = op22f(a), fb = op22f(b);
     acc.x = fmaf(s, fa.x, acc.x);
     acc.y = fmaf(s, fa.y, acc.y);
     acc.z = fmaf(s, fb.x, acc.z);
@@ -212,10 +212,10 @@ __device__ __forceinline__ void fma4_bf16(float4& acc, float s, uint2 raw) {
 }
 
 // x and out rows are [hi | lo | hi] thirds of H channels (row stride 3H)
-__global__ void __launch_bounds__(256) gcn_aggregate_kernel(const __nv_bfloat16* __restrict__ x, int H, const int* __restrict__ row_ptr,
+__global__ void __launch_bounds__(256) gcn_aggregate_kernel(const op_t* __restrict__ x, int H, const int* __restrict__ row_ptr,
                                                             const int* __restrict__ col, const float* __restrict__ w,
                                                             const float* __restrict__ self_w, const float* __restrict__ dis,
-                                                            const int* n_dev, int cap, __nv_bfloat16* __restrict__ out) {
+                                                            const int* n_dev, int cap, op_t* __restrict__ out) {
     const int g = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int n = n_dev ? min(*n_dev, cap) : cap;
     if (g >= n) return;
@@ -228,22 +228,22 @@ __global__ void __launch_bounds__(256) gcn_aggregate_kernel(const __nv_bfloat16*
             const int j = col[e];
             if (j == g) continue;
             const float s = dis[j] * (w ? w[e] : 1.0f) * di;
-            const __nv_bfloat16* xr = x + (size_t)j * ld + c0;
-            fma4_bf16(acc, s, *reinterpret_cast<const uint2*>(xr));
-            fma4_bf16(acc, s, *reinterpret_cast<const uint2*>(xr + H));
+            const op_t* xr = x + (size_t)j * ld + c0;
+            fma4_h(acc, s, *reinterpret_cast<const uint2*>(xr));
+            fma4_h(acc, s, *reinterpret_cast<const uint2*>(xr + H));
         }
         const float s = di * (self_w ? self_w[g] : 1.0f) * di;
-        const __nv_bfloat16* xr = x + (size_t)g * ld + c0;
-        fma4_bf16(acc, s, *reinterpret_cast<const uint2*>(xr));
-        fma4_bf16(acc, s, *reinterpret_cast<const uint2*>(xr + H));
+        const op_t* xr = x + (size_t)g * ld + c0;
+        fma4_h(acc, s, *reinterpret_cast<const uint2*>(xr));
+        fma4_h(acc, s, *reinterpret_cast<const uint2*>(xr + H));
         const float v[4] = {acc.x, acc.y, acc.z, acc.w};
-        __align__(8) __nv_bfloat16 hi[4], lo[4];
+        __align__(8) op_t hi[4], lo[4];
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
-            hi[t] = __float2bfloat16(v[t]);
-            lo[t] = __float2bfloat16(v[t] - __bfloat162float(hi[t]));
+            hi[t] = f2op(v[t]);
+            lo[t] = f2op(v[t] - op2f(hi[t]));
         }
-        __nv_bfloat16* o = out + (size_t)g * ld + c0;
+        op_t* o = out + (size_t)g * ld + c0;
         *reinterpret_cast<uint2*>(o) = *reinterpret_cast<const uint2*>(hi);
         *reinterpret_cast<uint2*>(o + H) = *reinterpret_cast<const uint2*>(lo);
         *reinterpret_cast<uint2*>(o + 2 * H) = *reinterpret_cast<const uint2*>(hi);
@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(256) gcn_aggregate_kernel(const __nv_bfloat16*
 
 struct GnnWs {
     float *a_src, *a_dst, *dis, *hid, *emb;
-    __nv_bfloat16 *z, *buf0, *buf1, *emb_h;
+    op_t *z, *buf0, *buf1, *emb_h;
     size_t total;
 };
 static GnnWs carve_gnn(void* ws, const cm_gnn_params* p, int cap) {
@@ -261,11 +261,11 @@ static GnnWs carve_gnn(void* ws, const cm_gnn_params* p, int cap) {
     const size_t n = cap, H = p->hidden;
     r.a_src = c.take<float>(n * p->heads);
     r.a_dst = c.take<float>(n * p->heads);
-    r.z = c.take<__nv_bfloat16>(n * gnn_layout(p).zk);
+    r.z = c.take<op_t>(n * gnn_layout(p).zk);
     r.dis = c.take<float>(n);
-    r.buf0 = c.take<__nv_bfloat16>(n * 3 * H);
-    r.buf1 = c.take<__nv_bfloat16>(n * 3 * H);
-    r.emb_h = c.take<__nv_bfloat16>(n * 3 * H);
+    r.buf0 = c.take<op_t>(n * 3 * H);
+    r.buf1 = c.take<op_t>(n * 3 * H);
+    r.emb_h = c.take<op_t>(n * 3 * H);
     r.hid = c.take<float>(n * 3 * (H / 2));
     r.emb = c.take<float>(n * H);
     r.total = align_up(c.off, 256);
@@ -341,10 +341,10 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
         CM_TIMED("gat_aggregate", st);
         gat_aggregate_kernel<4><<<warps_grid, 256, 0, st>>>(x, C, csr_row_ptr, csr_col, ws.a_src, ws.a_dst, n_nodes_dev, M, ws.z, f.zk);
     }
-    auto W = [&](size_t off) { return reinterpret_cast<const __nv_bfloat16*>(blob + off); };
+    auto W = [&](size_t off) { return reinterpret_cast<const op_t*>(blob + off); };
     Dense d;
     d.M = M; d.m_dev = n_nodes_dev; d.relu = 1;
-    d.A = ws.z; d.lda = f.zk; d.K = f.zk; d.W = W(f.wcat_h); d.bias = blob + f.bias1; d.N = H; d.out_bf16 = ws.buf0; d.ldo_bf16 = 3 * H; d.split_out = 1;
+    d.A = ws.z; d.lda = f.zk; d.K = f.zk; d.W = W(f.wcat_h); d.bias = blob + f.bias1; d.N = H; d.out_h = ws.buf0; d.ldo_h = 3 * H; d.split_out = 1;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     {
         CM_TIMED("gcn_norm", st);
@@ -359,11 +359,11 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
         if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     }
     float* emb = node_emb ? node_emb : (graph_emb ? ws.emb : nullptr);
-    d.A = ws.buf0; d.W = W(f.fcw_h); d.bias = p->fc_shared_bias; d.out_bf16 = ws.emb_h; d.out_f32 = emb; d.ldo_f32 = H;
+    d.A = ws.buf0; d.W = W(f.fcw_h); d.bias = p->fc_shared_bias; d.out_h = ws.emb_h; d.out_f32 = emb; d.ldo_f32 = H;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     if (mask_out || instance_out || edge_out || mask_prob) {
         const int H2 = H / 2;
-        d.A = ws.emb_h; d.W = W(f.head1w_h); d.bias = blob + f.head1b; d.N = 3 * H2; d.out_bf16 = nullptr; d.out_f32 = ws.hid; d.ldo_f32 = 3 * H2;
+        d.A = ws.emb_h; d.W = W(f.head1w_h); d.bias = blob + f.head1b; d.N = 3 * H2; d.out_h = nullptr; d.out_f32 = ws.hid; d.ldo_f32 = 3 * H2;
         if ((rc = launch_dense(d, st)) != CM_OK) return rc;
         Heads2 h2;
         h2.n_heads = 3;

@@ -100,14 +100,14 @@ int cm_csr_from_edge_index(const int64_t* edge_index, int64_t row_stride, const 
                            int n_edges, void* workspace, size_t workspace_bytes, int32_t* csr_row_ptr,
                            int32_t* csr_col, float* csr_w, float* self_w, uint32_t* status, void* stream);
 
-/* Dense-layer building block of A5-A11 on the tcgen05 tensor cores (bf16 operands, fp32 accumulation in TMEM):
+/* Dense-layer building block of A5-A11 on the tcgen05 tensor cores (fp16 operands, fp32 accumulation in TMEM):
  *   out[m,n] = LN?( relu?( alpha * (sum_k a[m,k] w[n,k] + bias[n]) + residual[m,n] ) )
- * a [m,lda] bf16 and w [n,k] bf16 (an nn.Linear weight), k % 8 == 0, lda % 8 == 0, 16-byte aligned; m is a
+ * a [m,lda] fp16 and w [n,k] fp16 (an nn.Linear weight), k % 8 == 0, lda % 8 == 0, 16-byte aligned; m is a
  * capacity and *m_dev (optional) the live row count; bias / ln_gamma / ln_beta fp32 [n] (LayerNorm eps 1e-5,
- * n <= 256); residual bf16 [m,ldr]; out_bf16 and/or out_f32 [m,n]. */
-int cm_linear_bf16(const void* a_bf16, int lda, const void* w_bf16, int m, int n, int k, const int32_t* m_dev,
-                   const float* bias, float alpha, int relu, const void* residual_bf16, int ldr,
-                   const float* ln_gamma, const float* ln_beta, void* out_bf16, float* out_f32, void* stream);
+ * n <= 256); residual fp16 [m,ldr]; out_f16 and/or out_f32 [m,n]. */
+int cm_linear_f16(const void* a_f16, int lda, const void* w_f16, int m, int n, int k, const int32_t* m_dev,
+                   const float* bias, float alpha, int relu, const void* residual_f16, int ldr,
+                   const float* ln_gamma, const float* ln_beta, void* out_f16, float* out_f32, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * A5-A7: RegionGraphGNN forward (extract_rg_embeddings.py:27-135), eval mode.
@@ -176,7 +176,7 @@ typedef struct cm_fusion_params {
 size_t cm_fusion_workspace_bytes(const cm_fusion_params* p, int n_graphs, int node_cap, int n_kg);
 /* Tensor-core path for knowledge-graph rows shared by every image (the reference feeds the same category rows
  * to every sample -- "KG broadcast once"): cm_fusion_fold projects kg [n_kg, kg_dim] through the KG side of both
- * attention blocks once per (weights, kg) pair and stores bf16 copies of the remaining weights; the blob is then
+ * attention blocks once per (weights, kg) pair and stores fp16 copies of the remaining weights; the blob is then
  * passed to cm_fusion_forward, which runs the region-node side as tcgen05 GEMMs.  cm_fusion_folded_bytes returns
  * 0 when the shape has no folded form (late fusion, hidden_dim > 256, num_heads * slots(n_kg) > 128). */
 size_t cm_fusion_folded_bytes(const cm_fusion_params* p, int n_kg);

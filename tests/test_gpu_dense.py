@@ -1,6 +1,6 @@
-"""GPU parity of the tcgen05/TMEM/TMA dense layer (cm_linear_bf16) against a plain PyTorch fp32 reference of the
-same op on the same bf16-rounded operands.  fp32 accumulation => tolerance is fp32 summation noise (1e-3 abs at
-K=512 with O(1) outputs is generous); bf16 outputs additionally carry one bf16 rounding (2^-8 relative)."""
+"""GPU parity of the tcgen05/TMEM/TMA dense layer (cm_linear_f16) against a plain PyTorch fp32 reference of the
+same op on the same fp16-rounded operands.  fp32 accumulation => tolerance is fp32 summation noise (1e-3 abs at
+K=512 with O(1) outputs is generous); fp16 outputs additionally carry one fp16 rounding (2^-11 relative)."""
 import pytest
 import torch
 
@@ -12,18 +12,18 @@ def _run(m, n, k, *, bias=True, alpha=1.0, relu=False, residual=False, ln=False,
     lib = _lib.load()
     g = torch.Generator().manual_seed(seed)
     lda = lda or k
-    a = (torch.randn(m, lda, generator=g) * 0.5).to(torch.bfloat16).cuda()
-    w = (torch.randn(n, k, generator=g) * (1.0 / k ** 0.5)).to(torch.bfloat16).cuda()
+    a = (torch.randn(m, lda, generator=g) * 0.5).to(torch.float16).cuda()
+    w = (torch.randn(n, k, generator=g) * (1.0 / k ** 0.5)).to(torch.float16).cuda()
     b = torch.randn(n, generator=g).cuda() if bias else None
-    r = (torch.randn(m, n, generator=g)).to(torch.bfloat16).cuda() if residual else None
+    r = (torch.randn(m, n, generator=g)).to(torch.float16).cuda() if residual else None
     gam = (1 + 0.1 * torch.randn(n, generator=g)).cuda() if ln else None
     bet = (0.1 * torch.randn(n, generator=g)).cuda() if ln else None
-    out16 = torch.full((m, n), 7.0, dtype=torch.bfloat16, device="cuda")
+    out16 = torch.full((m, n), 7.0, dtype=torch.float16, device="cuda")
     out32 = torch.full((m, n), 7.0, dtype=torch.float32, device="cuda")
     mdev = torch.tensor([live], dtype=torch.int32, device="cuda") if live is not None else None
     p = _lib.ptr
-    _lib.check(lib.cm_linear_bf16(p(a), lda, p(w), m, n, k, p(mdev), p(b), float(alpha), int(relu), p(r), n, p(gam), p(bet),
-                                  p(out16), p(out32), _lib.stream_ptr()), "cm_linear_bf16")
+    _lib.check(lib.cm_linear_f16(p(a), lda, p(w), m, n, k, p(mdev), p(b), float(alpha), int(relu), p(r), n, p(gam), p(bet),
+                                  p(out16), p(out32), _lib.stream_ptr()), "cm_linear_f16")
     torch.cuda.synchronize()
     ref = a[:, :k].float() @ w.float().t()
     if bias:
@@ -40,7 +40,7 @@ def _run(m, n, k, *, bias=True, alpha=1.0, relu=False, residual=False, ln=False,
     err16 = (out16[:rows].float() - ref[:rows]).abs().max().item()
     scale = ref[:rows].abs().max().item()
     assert err32 <= 2e-3, (m, n, k, err32)
-    assert err16 <= 2e-3 + scale * 2 ** -8, (m, n, k, err16)
+    assert err16 <= 2e-3 + scale * 2 ** -11, (m, n, k, err16)
     if rows < m:   # rows past the live count are never written
         assert (out32[rows:] == 7.0).all() and (out16[rows:].float() == 7.0).all()
 

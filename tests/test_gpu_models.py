@@ -1,11 +1,12 @@
 """GPU parity: RegionGraphGNN (A5-A7), fusion + heads (A10-A12) vs the oracle and the reference's golden
 outputs.  Tolerances, max-abs:
-  * RegionGraphGNN (tcgen05 GEMMs in split bf16 precision, fp32 gathers): <= 1e-4 (measured 3e-5);
+  * RegionGraphGNN (tcgen05 GEMMs on split fp16 operands hi+lo, fp32 gathers): <= 1e-4 (measured 6e-6);
   * fusion, general fp32 path (per-image KG rows, late fusion): logits <= 1e-4, attention probabilities <= 1e-5;
-  * fusion, tensor-core path (KG rows shared by the batch; bf16 operands on the region-node side): logits <= 1e-2 --
-    the north star's bound for bf16 mask logits (measured 2.7e-3) -- fused features <= 4e-2 on values up to 8
-    (measured 1.5e-2), attention probabilities <= 1e-3 (measured 5e-5)."""
-TC_LOGITS, TC_FUSED, TC_ATTN = 1e-2, 4e-2, 1e-3
+  * fusion, tensor-core path (KG rows shared by the batch; plain fp16 operands on the region-node side, split fp16 on
+    the KG-side / graph-level rows): logits <= 5e-3 -- half the north star's 1e-2 bound for reduced-precision mask
+    logits (measured 8e-4) -- fused features <= 1e-2 on values up to 8 (measured 2.4e-3), attention probabilities
+    <= 1e-4 (measured 5e-6)."""
+TC_LOGITS, TC_FUSED, TC_ATTN = 5e-3, 1e-2, 1e-4
 import os
 
 import numpy as np
@@ -137,7 +138,7 @@ def test_detector_matches_reference_golden(detector, case):
     for name in ("rg2kg", "kg2rg"):
         assert tuple(attn[name].shape) == z[f"{case}.{name}"].shape
         np.testing.assert_allclose(_np(attn[name]), z[f"{case}.{name}"], rtol=0, atol=tol_a, err_msg=name)
-        np.testing.assert_allclose(_np(attn[name].sum(-1)), 1.0, atol=2e-3 if tc else 1e-5)
+        np.testing.assert_allclose(_np(attn[name].sum(-1)), 1.0, atol=1e-3 if tc else 1e-5)
     out4 = m(rg, kg)
     assert len(out4) == 4 and torch.allclose(out4[0], mask, atol=1e-6)
     fused, aw = m.fusion(rg, kg)
@@ -173,7 +174,7 @@ def test_fusion_errors_and_invariances(detector):
     pn, pk = torch.randperm(rg.shape[1], generator=g).cuda(), torch.randperm(13, generator=g).cuda()
     perm = m(rg[:, pn], kg[:, pk])                                   # node- and KG-order invariance
     for a, b in zip(base, perm):
-        assert torch.allclose(a, b, atol=TC_LOGITS / 2)             # B = 1 -> tensor-core path (bf16 operands)
+        assert torch.allclose(a, b, atol=TC_LOGITS / 2)             # B = 1 -> tensor-core path (fp16 operands)
 
 
 def test_ragged_batch_equals_per_image(detector, golden_dir):
