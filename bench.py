@@ -124,11 +124,11 @@ def kernel_work(name, B, M, E, K):
     # the KG-side rows and the graph-level MLP + heads.  Split-precision layers are counted once, padding not at all.
     hk = 8 * K
     lin_flops = 2.0 * M * (60 * 128 + 3 * 128 * 128 + 128 * 128 + 128 * 192)
-    lin_flops += 2.0 * M * (d * D + D * 2 * hk + D * D + hk * D + D * 2 * D + 2 * D * D)
-    lin_flops += 2.0 * gk * (D * D + 2 * (D * 2 * D))
-    lin_flops += 2.0 * B * (2 * D * D + D * D + 4 * D * (D // 2))
+    node_flops = 2.0 * M * (d * D + D * 2 * hk + D * D + hk * D + D * 2 * D + 2 * D * D)   # fusion_node: one kernel
     table = {
         "dense_tc": ("tensor", lin_flops),
+        "fusion_node": ("tensor", node_flops),
+        "fusion_kgrows": ("tensor", 2.0 * gk * (D * D + 2 * (D * 2 * D))),
         "cast_f16": ("hbm", 768.0 * M),
         "rag_scan": ("hbm", 4.0 * px),
         "rag_compact": ("hbm", 4.0 * B * LABEL_CAP * (4 + 17 + 2)),
@@ -142,7 +142,7 @@ def kernel_work(name, B, M, E, K):
         "gcn_aggregate": ("hbm", 3 * (2 * 512.0 * M + 8.0 * E)),
         "layernorm": ("hbm", 2 * 1024.0 * (M + gk)),
         "attn_rg2kg": ("hbm", 2 * 1024.0 * M),
-        "attn_kg2rg": ("hbm", (4.0 * hk + 512.0) * M + 1536.0 * gk),
+        "kg2rg_partial": ("hbm", (512.0 + 512.0 + 1024.0) * M),
         "segment_mean": ("hbm", 1024.0 * M + 512.0 * M),
     }
     return table.get(name, (None, None))

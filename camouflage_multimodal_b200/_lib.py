@@ -59,7 +59,7 @@ SIGNATURES = {
     "cm_timing_report": (_i, [C.c_char_p, _i]),
     "cm_rag_workspace_bytes": (_sz, [_i, _i]),
     "cm_rag_build": (_i, [_fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp]),
-    "cm_node_features": (_i, [_fp, _fp, _fp, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
+    "cm_node_features": (_i, [_fp, _fp, _fp, _i, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
     "cm_edge_weights": (_i, [_fp, _fp, _fp, _fp, _i, _fp, _fp]),
     "cm_csr_workspace_bytes": (_sz, [_i, _i]),
     "cm_csr_from_edge_index": (_i, [_fp, _i64, _fp, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp]),

@@ -12,125 +12,11 @@
 #include <tuple>
 
 #include "dense_tc.cuh"
+#include "tc_ptx.cuh"
 
 namespace cm {
 
 constexpr int TC_BM = 128, TC_BK = 64, TC_STAGES = 4, TC_THREADS = 320, TC_EPI_THREADS = 256;
-
-// ------------------------------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-// Bounded wait: a broken pipeline traps (launch error) instead of hanging the GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    for (uint32_t spin = 0;; ++spin) {
-        uint32_t done;
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(addr), "r"(parity)
-            : "memory");
-        if (done) return;
-        if (spin > (1u << 26)) __trap();
-    }
-}
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
-            smem_u32(smem_dst)),
-        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, fp16 x fp16 -> fp32, issued by one thread for the CTA
-__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// 32 lanes x 32 columns of fp32: thread t of the warp gets row (lane quarter base + t), columns c..c+31
-__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: 8-row groups 1024 B apart (SBO), LBO unused (1),
-// version 1 (sm_100), layout type 2.  Start address in 16-byte units.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
-    d |= (uint64_t)1 << 16;
-    d |= (uint64_t)(1024 >> 4) << 32;
-    d |= (uint64_t)1 << 46;
-    d |= (uint64_t)2 << 61;
-    return d;
-}
-// Instruction descriptor, kind::f16: D fp32 (bits 4-5 = 1), A = B = fp16 (format 0 at bits 7-9 and 10-12; fp16 would
-// be 1), both K-major, N >> 3 at bits 17-22, M >> 4 at bits 24-28.
-__host__ __device__ constexpr uint32_t umma_idesc_f16(int m, int n) {
-    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
-
-__device__ __forceinline__ uint4 pack8(const float* x) {
-    uint4 pk;
-    op2_t b0 = f2op2(x[0], x[1]), b1 = f2op2(x[2], x[3]);
-    op2_t b2 = f2op2(x[4], x[5]), b3 = f2op2(x[6], x[7]);
-    pk.x = *reinterpret_cast<uint32_t*>(&b0);
-    pk.y = *reinterpret_cast<uint32_t*>(&b1);
-    pk.z = *reinterpret_cast<uint32_t*>(&b2);
-    pk.w = *reinterpret_cast<uint32_t*>(&b3);
-    return pk;
-}
-
-// In-place softmax over each group of GS consecutive slots of a 32-column chunk; only the first `valid` slots of
-// a group are keys (the rest are layout padding and come out as 0).  am[k] accumulates slot k over the groups.
-template <int GS>
-__device__ __forceinline__ void softmax_groups(float (&x)[32], int valid, float (&am)[32]) {
-#pragma unroll
-    for (int g = 0; g < 32 / GS; ++g) {
-        float mx = -INFINITY;
-#pragma unroll
-        for (int k = 0; k < GS; ++k)
-            if (k < valid) mx = fmaxf(mx, x[g * GS + k]);
-        float sum = 0.f;
-#pragma unroll
-        for (int k = 0; k < GS; ++k) {
-            const float e = k < valid ? expf(x[g * GS + k] - mx) : 0.f;
-            x[g * GS + k] = e;
-            sum += e;
-        }
-        const float inv = 1.0f / sum;
-#pragma unroll
-        for (int k = 0; k < GS; ++k) {
-            x[g * GS + k] *= inv;
-            am[k] += x[g * GS + k];
-        }
-    }
-}
 
 template <int BN>
 struct TcSmem {
@@ -438,7 +324,7 @@ static int get_encoder() {
 }
 
 // 2-D fp16 tensor map: inner dim = cols (K), outer = rows; box = 64 x box_rows, 128-byte swizzle, OOB -> 0.
-static int make_map(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+int make_map(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
     using Key = std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t>;
     static std::map<Key, CUtensorMap> cache;
     Key key{ptr, rows, cols, ld, box_rows};

@@ -1,0 +1,391 @@
+// Region-node side of the KG-folded cross-attention fusion as ONE kernel (fusion_model.py:108-120 + the K/V side of
+// :123-129), one CTA per tile of 128 region nodes, all activations resident in shared memory / TMEM:
+//
+//   ph0  r   = x Wr^T + br                         x [128,128] by TMA            -> A1 (smem, fp16, SW128 K-major)
+//   ph1  S   = r [U1;U2]^T + [c1;0]                softmax per head -> P1        -> A2 (smem);  S2 raw -> global fp32
+//   ph2  V2  = r Wv2^T + bv2                                                     -> global fp16
+//   ph3  y0  = LN(r + P1 VO^T + bo1)                                             -> A1 (in place)
+//   ph4  hh0 = relu(y0 W1[0:256]^T + b1)                                         -> A3 (smem)
+//   ph5  Y   = hh0 W2[:,0:256]^T
+//   ph6  hh1 = relu(y0 W1[256:512]^T + b1)                                       -> A3
+//   ph7  Y  += hh1 W2[:,256:512]^T;  y = Y + b2 + y0                             -> global fp32 (mean over nodes follows)
+//
+// Every GEMM is 128 x 256 x K on tcgen05 (fp16 operands, fp32 accumulators in the two 256-column halves T0 / T1 of
+// TMEM), its weight tiles [256 x 64] streamed through a 3-stage TMA ring; the epilogue of phase i (8 warps, one
+// TMEM lane = one node row per thread) overlaps the MMAs of the phases that do not depend on it.
+//   warp 0: TMA producer   warp 1: MMA issuer   warps 2-9: epilogues
+// Dependencies: MMA(ph) waits for the epilogue that produced its A operand and for the epilogue that last read its
+// TMEM half; epilogue(ph) waits for acc_ready[ph] only -- tcgen05.commit covers every earlier MMA, which is also
+// what makes the in-place / aliased shared-memory buffers safe (see the notes at each phase).
+#include <cuda.h>
+#include <math.h>
+
+#include "fusion_node.cuh"
+#include "tc_ptx.cuh"
+
+namespace cm {
+
+constexpr int FN_THREADS = 320, FN_EPI_THREADS = 256, FN_STAGES = 3, FN_PHASES = 8;
+constexpr int FN_A1 = 0, FN_A3 = 65536, FN_X = FN_A3, FN_P1 = FN_A3 + 32768, FN_RING = 131072, FN_STAGE_BYTES = 32768;
+constexpr int FN_BAR = FN_RING + FN_STAGES * FN_STAGE_BYTES;   // 229376
+constexpr int FN_SMEM = FN_BAR + 256 + 1024;                   // + barriers, + 1 KB alignment slack
+constexpr int FN_KB_TILE = 128 * 64 * 2;                       // one [128 x 64] fp16 k-block of an activation tile
+
+// GEMM schedule: A operand (smem offset, k-blocks), weight map index + K offset, TMEM column half, accumulate,
+// epilogue the MMA warp must wait for before issuing (-1: none; phase 0 waits for the x tile instead).
+struct FnPhase {
+    int a_off, a_kb, wmap, w_row0, w_k0, tmem_col, accumulate, wait_epi;
+};
+__constant__ FnPhase fn_phases[2][FN_PHASES] = {
+    {
+        // MODE 0: region-node chain
+        {FN_X, 2, 1, 0, 0, 0, 0, -1},      // r
+        {FN_A1, 4, 2, 0, 0, 256, 0, 0},    // scores        (A1 = r ready after epi0)
+        {FN_A1, 4, 3, 0, 0, 0, 0, 0},      // V2            (T0 drained by epi0)
+        {FN_P1, 2, 4, 0, 0, 256, 0, 1},    // P1 VO^T       (P1 ready, T1 drained after epi1)
+        {FN_A1, 4, 5, 0, 0, 0, 0, 3},      // hh0           (A1 = y0 after epi3; T0 drained by epi2 < epi3)
+        {FN_A3, 4, 6, 0, 0, 256, 0, 4},    // Y  = hh0 ...  (A3 = hh0 after epi4; T1 drained by epi3)
+        {FN_A1, 4, 5, 256, 0, 0, 0, 4},    // hh1           (T0 drained by epi4)
+        {FN_A3, 4, 6, 0, 256, 256, 1, 6},  // Y += hh1 ...  (A3 = hh1 after epi6)
+    },
+    {
+        // MODE 1: KG-row chain (fusion_model.py:130-131): x = ctx2 tile [128,256] in A3
+        {FN_A3, 4, 1, 0, 0, 256, 0, -1},   // ctx2 Wo2^T    -> LN(kp + . + bo2) = z0 -> A1
+        {FN_A1, 4, 2, 0, 0, 0, 0, 0},      // hh0           (A1 = z0 after epi0)
+        {FN_A3, 4, 3, 0, 0, 256, 0, 1},    // Y  = hh0 ...  (A3 = hh0 after epi1; T1 drained by epi0)
+        {FN_A1, 4, 2, 256, 0, 0, 0, 1},    // hh1           (T0 drained by epi1)
+        {FN_A3, 4, 3, 0, 256, 256, 1, 3},  // Y += hh1 ...  (A3 = hh1 after epi3)
+        {0, 0, 0, 0, 0, 0, 0, -1}, {0, 0, 0, 0, 0, 0, 0, -1}, {0, 0, 0, 0, 0, 0, 0, -1},
+    },
+};
+
+__device__ __forceinline__ void st_smem_v4(uint32_t addr, uint4 v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_smem_v4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+// 32 fp32 values of row `row`, columns c0..c0+31, into a K-major SW128 activation tile set starting at `base`
+__device__ __forceinline__ void store_chunk_smem(uint32_t base, int row, int c0, const float* x) {
+    const uint32_t tile = base + (uint32_t)(c0 >> 6) * FN_KB_TILE;
+    const int ch0 = (c0 & 63) >> 3;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) st_smem_v4(tile + sw128_offset(row, ch0 + t), pack8(x + 8 * t));
+}
+__device__ __forceinline__ void add_chunk_smem(uint32_t base, int row, int c0, float* x) {
+    const uint32_t tile = base + (uint32_t)(c0 >> 6) * FN_KB_TILE;
+    const int ch0 = (c0 & 63) >> 3;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const uint4 v = ld_smem_v4(tile + sw128_offset(row, ch0 + t));
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float2 f = op22f(*reinterpret_cast<const op2_t*>(&w[u]));
+            x[8 * t + 2 * u] += f.x;
+            x[8 * t + 2 * u + 1] += f.y;
+        }
+    }
+}
+// x[j] = acc[j] + vec[c0 + j] (vec: fp32 per-column vector in global memory, warp-uniform address -> broadcast)
+__device__ __forceinline__ void load_acc_bias(uint32_t taddr, int c0, const float* __restrict__ vec, float* x) {
+    uint32_t v[32];
+    tc_ld32(taddr + c0, v);
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(vec + c0 + j));
+        x[j] = __uint_as_float(v[j]) + b4.x;
+        x[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
+        x[j + 2] = __uint_as_float(v[j + 2]) + b4.z;
+        x[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid_constant__ FusionNodeArgs a) {
+    constexpr int NPH = MODE == 0 ? 8 : 5, XKB = MODE == 0 ? 2 : 4;
+    extern __shared__ uint8_t smem_raw[];
+    const int m_live = a.m_dev ? min(*a.m_dev, a.M) : a.M;
+    const int m0 = blockIdx.x * 128;
+    if (m0 >= m_live) return;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t sbase = smem_u32(smem);
+    uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + FN_BAR);
+    uint64_t* w_empty = w_full + FN_STAGES;
+    uint64_t* x_full = w_empty + FN_STAGES;
+    uint64_t* acc_ready = x_full + 1;
+    uint64_t* epi_done = acc_ready + FN_PHASES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(epi_done + FN_PHASES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < FN_STAGES; ++s) {
+            mbar_init(w_full + s, 1);
+            mbar_init(w_empty + s, 1);
+        }
+        mbar_init(x_full, 1);
+        for (int i = 0; i < FN_PHASES; ++i) {
+            mbar_init(acc_ready + i, 1);
+            mbar_init(epi_done + i, 8);   // one arrival per epilogue warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            mbar_expect_tx(x_full, XKB * FN_KB_TILE);
+            for (int kb = 0; kb < XKB; ++kb) tma_load_2d(smem + FN_X + kb * FN_KB_TILE, &a.maps[0], x_full, kb * 64, m0);
+            int t = 0;
+            for (int ph = 0; ph < NPH; ++ph) {
+                const FnPhase p = fn_phases[MODE][ph];
+                for (int kb = 0; kb < p.a_kb; ++kb, ++t) {
+                    const int s = t % FN_STAGES, n = t / FN_STAGES;
+                    if (n > 0) mbar_wait(w_empty + s, (n - 1) & 1);
+                    mbar_expect_tx(w_full + s, FN_STAGE_BYTES);
+                    tma_load_2d(smem + FN_RING + s * FN_STAGE_BYTES, &a.maps[p.wmap], w_full + s, p.w_k0 + kb * 64, p.w_row0);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_f16(128, 256);
+            int t = 0;
+            for (int ph = 0; ph < NPH; ++ph) {
+                const FnPhase p = fn_phases[MODE][ph];
+                if (ph == 0) mbar_wait(x_full, 0);
+                else if (p.wait_epi >= 0) mbar_wait(epi_done + p.wait_epi, 0);
+                tc_fence_after();
+                for (int kb = 0; kb < p.a_kb; ++kb, ++t) {
+                    const int s = t % FN_STAGES, n = t / FN_STAGES;
+                    mbar_wait(w_full + s, n & 1);
+                    tc_fence_after();
+                    const uint64_t adesc = umma_desc_sw128(sbase + p.a_off + kb * FN_KB_TILE);
+                    const uint64_t bdesc = umma_desc_sw128(sbase + FN_RING + s * FN_STAGE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        tc_mma_f16(tmem_base + p.tmem_col, adesc + 2 * k, bdesc + 2 * k, idesc, (p.accumulate | kb | k) != 0);
+                    tc_commit(w_empty + s);
+                }
+                tc_commit(acc_ready + ph);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ------------------------------------------------------------------------------ epilogues (warps 2..9)
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int lrow = q * 32 + lane, row = m0 + lrow;
+        const bool row_ok = row < m_live;
+        const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16), t1 = t0 + 256;
+        auto done = [&](int ph) {   // smem writes -> async proxy, TMEM reads retired, then one arrival per warp
+            fence_proxy_async_smem();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(epi_done + ph);
+        };
+        auto wait_acc = [&](int ph) {
+            mbar_wait(acc_ready + ph, 0);
+            __syncwarp();
+            tc_fence_after();
+        };
+        float x[32];
+
+        // y0 = LN(acc + bias + residual) -> A1.  Residual: A1 itself (in place: each thread re-reads and rewrites only
+        // its own (row, chunk) cells, and every MMA that read A1 has completed because acc_ready[ph] covers them) or
+        // fp32 rows from global memory (row % res_mod).  The statistics scratch is the x tile, dead since phase 0.
+        auto epi_ln = [&](int ph, uint32_t taddr, const float* bias, const float* res_rows) {
+            wait_acc(ph);
+            const float* res = res_rows ? res_rows + (size_t)(row % a.res_mod) * 256 : nullptr;
+            auto load = [&](int c0) {
+                load_acc_bias(taddr, c0, bias, x);
+                if (res) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const float4 r4 = __ldg(reinterpret_cast<const float4*>(res + c0 + j));
+                        x[j] += r4.x;
+                        x[j + 1] += r4.y;
+                        x[j + 2] += r4.z;
+                        x[j + 3] += r4.w;
+                    }
+                } else {
+                    add_chunk_smem(sbase + FN_A1, lrow, c0, x);
+                }
+            };
+            float s1 = 0.f, s2 = 0.f;
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load(c0);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    s1 += x[j];
+                    s2 = fmaf(x[j], x[j], s2);
+                }
+            }
+            float2* stat = reinterpret_cast<float2*>(smem + FN_X);
+            stat[half * 128 + lrow] = make_float2(s1, s2);
+            asm volatile("bar.sync 1, %0;" ::"n"(FN_EPI_THREADS) : "memory");
+            const float2 o = stat[(half ^ 1) * 128 + lrow];
+            s1 += o.x;
+            s2 += o.y;
+            const float mean = s1 * (1.0f / 256.f);
+            const float rstd = rsqrtf(fmaxf(s2 * (1.0f / 256.f) - mean * mean, 0.f) + 1e-5f);
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load(c0);
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const float4 g4 = __ldg(reinterpret_cast<const float4*>(a.ln_g + c0 + j));
+                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(a.ln_b + c0 + j));
+                    x[j] = (x[j] - mean) * rstd * g4.x + b4.x;
+                    x[j + 1] = (x[j + 1] - mean) * rstd * g4.y + b4.y;
+                    x[j + 2] = (x[j + 2] - mean) * rstd * g4.z + b4.z;
+                    x[j + 3] = (x[j + 3] - mean) * rstd * g4.w + b4.w;
+                }
+                store_chunk_smem(sbase + FN_A1, lrow, c0, x);
+            }
+            done(ph);   // the scratch is not rewritten before every warp has arrived here (next A3 writer waits on it)
+        };
+        // hh half = relu(acc + b1) -> A3
+        auto epi_relu = [&](int ph, const float* b1) {
+            wait_acc(ph);
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load_acc_bias(t0, c0, b1, x);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+                store_chunk_smem(sbase + FN_A3, lrow, c0, x);
+            }
+            done(ph);
+        };
+        // y = Y + b2 + A1 -> global fp32
+        auto epi_final = [&](int ph) {
+            wait_acc(ph);
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load_acc_bias(t1, c0, a.b_ffn2, x);
+                add_chunk_smem(sbase + FN_A1, lrow, c0, x);
+                if (row_ok) {
+                    float* o = a.y + (size_t)row * 256 + c0;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+                }
+            }
+        };
+
+        if (MODE == 1) {
+            epi_ln(0, t1, a.b_out1, a.res_rows);
+            epi_relu(1, a.b_ffn1);
+            epi_relu(3, a.b_ffn1 + 256);
+            epi_final(4);
+        } else {
+        // ---- epi0: r -> A1
+        wait_acc(0);
+        for (int c0 = half * 32; c0 < 256; c0 += 64) {
+            load_acc_bias(t0, c0, a.b_rgproj, x);
+            store_chunk_smem(sbase + FN_A1, lrow, c0, x);
+        }
+        done(0);
+
+        // ---- epi1: half 0 -> P1 = per-head softmax of the rg->kg scores (A2); half 1 -> raw kg->rg scores (global)
+        wait_acc(1);
+        {
+            float am[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) am[j] = 0.f;
+            for (int c0 = half * 128; c0 < half * 128 + 128; c0 += 32) {
+                load_acc_bias(t1, c0, a.ccat, x);
+                if (half == 0) {
+                    if (a.sm_gs == 16) softmax_groups<16>(x, a.sm_valid, am); else softmax_groups<32>(x, a.sm_valid, am);
+                    store_chunk_smem(sbase + FN_P1, lrow, c0, x);
+                } else if (row_ok) {
+                    float* o = a.s2 + (size_t)row * 128 + (c0 - 128);
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+                }
+            }
+            if (half == 0 && a.attn_mean && row_ok) {
+                const float inv = (float)a.sm_gs / 128.f;   // 1 / heads
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < a.sm_valid) a.attn_mean[(size_t)row * a.sm_valid + j] = am[j] * inv;
+            }
+        }
+        done(1);
+
+        // ---- epi2: V2 -> global fp16
+        wait_acc(2);
+        for (int c0 = half * 32; c0 < 256; c0 += 64) {
+            load_acc_bias(t0, c0, a.b_v2, x);
+            if (row_ok) {
+                op_t* o = a.v2 + (size_t)row * 256 + c0;
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(o + j) = pack8(x + j);
+            }
+        }
+        done(2);
+
+        epi_ln(3, t1, a.b_out1, nullptr);     // y0 = LN(r + P1 VO^T + bo1)
+        epi_relu(4, a.b_ffn1);                // phase 5 has no epilogue: its accumulator stays in T1
+        epi_relu(6, a.b_ffn1 + 256);
+        epi_final(7);                         // y = Y + b2 + y0
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+static void fn_set_attr() {
+    static bool attr = false;
+    if (!attr) {
+        cudaFuncSetAttribute(fusion_node_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, FN_SMEM);
+        cudaFuncSetAttribute(fusion_node_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FN_SMEM);
+        attr = true;
+    }
+}
+
+int launch_fusion_node(FusionNodeArgs& a, const void* x, const void* w_rgproj, const void* wcat, const void* wv2, const void* vot,
+                       const void* ffn1, const void* ffn2, cudaStream_t st) {
+    int rc;
+    if ((rc = make_map(&a.maps[0], x, (uint64_t)a.M, 128, 128, 128)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[1], w_rgproj, 256, 128, 128, 256)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[2], wcat, 256, 256, 256, 256)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[3], wv2, 256, 256, 256, 256)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[4], vot, 256, 128, 128, 256)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[5], ffn1, 512, 256, 256, 256)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[6], ffn2, 256, 512, 512, 256)) != CM_OK) return rc;
+    fn_set_attr();
+    {
+        CM_TIMED("fusion_node", st);
+        fusion_node_kernel<0><<<ceil_div(a.M, 128), FN_THREADS, FN_SMEM, st>>>(a);
+    }
+    return post_launch("fusion_node");
+}
+
+// KG-row chain: z = z0 + FFN(z0), z0 = LN(res_rows[row % res_mod] + x Wo^T + b_out1); x [M,256] fp16, z -> a.y
+int launch_fusion_kgrows(FusionNodeArgs& a, const void* x, const void* wo, const void* ffn1, const void* ffn2, cudaStream_t st) {
+    int rc;
+    if ((rc = make_map(&a.maps[0], x, (uint64_t)a.M, 256, 256, 128)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[1], wo, 256, 256, 256, 256)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[2], ffn1, 512, 256, 256, 256)) != CM_OK) return rc;
+    if ((rc = make_map(&a.maps[3], ffn2, 256, 512, 512, 256)) != CM_OK) return rc;
+    fn_set_attr();
+    {
+        CM_TIMED("fusion_kgrows", st);
+        fusion_node_kernel<1><<<ceil_div(a.M, 128), FN_THREADS, FN_SMEM, st>>>(a);
+    }
+    return post_launch("fusion_kgrows");
+}
+
+}  // namespace cm

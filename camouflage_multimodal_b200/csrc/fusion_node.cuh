@@ -1,0 +1,29 @@
+// Fused region-node side of the KG-folded cross-attention fusion (fusion_node.cu): hidden_dim 256, rg_dim 128,
+// 128 folded key slots.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace cm {
+
+struct FusionNodeArgs {
+    CUtensorMap maps[7];   // x, Wr, [U1;U2], Wv2, VO^T, W1, W2 (filled by launch_fusion_node)
+    int M;                 // row capacity of x (grid size); *m_dev the live rows
+    const int* m_dev;
+    const float *b_rgproj, *ccat, *b_v2, *b_out1, *ln_g, *ln_b, *b_ffn1, *b_ffn2;
+    const float* res_rows = nullptr;   // KG-row chain: fp32 residual rows [res_mod, 256] (projected KG rows)
+    int res_mod = 1;
+    int sm_gs, sm_valid;   // slots per head (16 / 32) and live KG rows
+    float* s2;             // [M,128] raw kg->rg scores
+    op_t* v2;              // [M,256] V of the kg->rg attention
+    float* y;              // [M,256] rg stream after the FFN residual
+    float* attn_mean;      // [M, sm_valid] head-averaged rg->kg probabilities or NULL
+};
+
+int launch_fusion_node(FusionNodeArgs& a, const void* x, const void* w_rgproj, const void* wcat, const void* wv2, const void* vot,
+                       const void* ffn1, const void* ffn2, cudaStream_t st);
+
+int launch_fusion_kgrows(FusionNodeArgs& a, const void* x, const void* wo, const void* ffn1, const void* ffn2, cudaStream_t st);
+
+}  // namespace cm

@@ -16,12 +16,17 @@
 #include <math.h>
 
 #include "dense_tc.cuh"
+#include "fusion_kg.cuh"
+#include "fusion_node.cuh"
 #include "fusion_tc.cuh"
 #include "linear.cuh"
 
 namespace cm {
 
 static size_t al(size_t v) { return (v + 255) / 256 * 256; }
+
+// shapes the single-kernel node side is written for (the reference's configs/multimodal_config.yaml defaults)
+static bool fusion_node_fused_ok(const cm_fusion_params* p) { return p->hidden == 256 && p->rg_dim == 128 && p->rg_proj_w != nullptr; }
 
 bool fusion_fold_supported(const cm_fusion_params* p, int n_kg) {
     if (p->fusion_type != 0) return false;
@@ -48,16 +53,11 @@ FusionFolded fusion_folded_layout(const cm_fusion_params* p, int n_kg) {
     f.vot = take(D * 128 * 2);
     f.ffn1 = take(2 * D * D * 2);
     f.ffn2 = take(2 * D * D * 2);
-    // KG-side and graph-level layers run in split precision: weights stored [hi | hi | lo] along K (3x)
-    f.wo2 = take(3 * D * D * 2);
-    f.kffn1 = take(3 * 2 * D * D * 2);
-    f.kffn2 = take(3 * 2 * D * D * 2);
-    f.fl1 = take(3 * 2 * D * D * 2);
-    f.fl2 = take(3 * D * D * 2);
-    f.hw1 = take(3 * 4 * (D / 2) * D * 2);
-    f.kp_h = take(K * D * 2);
+    // KG-row chain (out-projection, FFN) on the tensor cores; the graph-level layers read the fp32 parameters as stored
+    f.wo2_h = take(D * D * 2);
+    f.kffn1_h = take(2 * D * D * 2);
+    f.kffn2_h = take(2 * D * D * 2);
     f.ccat = take(256 * 4);
-    f.hb1 = take(4 * (D / 2) * 4);
     f.kp = take(K * D * 4);
     f.k1v1 = take(K * 2 * D * 4);
     f.q2 = take(K * D * 4);
@@ -116,110 +116,6 @@ __global__ void fusion_fold_kernel(cm_fusion_params p, int n_kg, int gs, const f
     }
 }
 
-__global__ void concat_heads1_kernel(cm_fusion_params p, op_t* __restrict__ hw1, float* __restrict__ hb1) {
-    const int D = p.hidden, H2 = D / 2;
-    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = tid; i < 4LL * H2 * D; i += stride) {
-        const int t = (int)(i / ((long long)H2 * D)), o = (int)(i / D), c = (int)(i % D);
-        const float v = p.head_w1[t][i - (long long)t * H2 * D];
-        const op_t hi = f2op(v);
-        op_t* w = hw1 + (size_t)o * 3 * D + c;
-        w[0] = hi;
-        w[D] = hi;
-        w[2 * D] = f2op(v - op2f(hi));
-    }
-    for (long long i = tid; i < 4LL * H2; i += stride) hb1[i] = p.head_b1[(int)(i / H2)][i % H2];
-}
-
-// kg -> rg attention on the folded scores: grid (n_graphs, n_kg), one thread per channel c (head h = c / hd).
-//   p2[h][n] = softmax over the image's nodes n of s2[n, h*gs + k];  ctx2[b*K + k, c] = sum_n p2[h(c)][n] v2[n, c]
-// attn (optional) block [n_kg, N_b] at n_kg*node_ptr[b]: mean over heads of p2.
-__global__ void __launch_bounds__(256) attn_kg2rg_fold_kernel(const float* __restrict__ s2, const op_t* __restrict__ v2, int D,
-                                                              int heads, int gs, const int* __restrict__ node_ptr, int n_kg,
-                                                              op_t* __restrict__ ctx2, float* __restrict__ attn) {
-    __shared__ float s_max[32], s_inv[32];
-    __shared__ float s_p[8][33];
-    const int b = blockIdx.x, k = blockIdx.y, c = threadIdx.x;
-    const int warp = c >> 5, lane = c & 31, nwarps = blockDim.x >> 5;
-    const int n0 = node_ptr[b], n1 = node_ptr[b + 1];
-    const int hd = D / heads;
-    for (int h = warp; h < heads; h += nwarps) {
-        const float* col = s2 + h * gs + k;
-        float mx = -INFINITY;
-        for (int n = n0 + lane; n < n1; n += 32) mx = fmaxf(mx, col[(size_t)n * 128]);
-        mx = warp_max(mx);
-        float sum = 0.f;
-        for (int n = n0 + lane; n < n1; n += 32) sum += expf(col[(size_t)n * 128] - mx);
-        sum = warp_sum(sum);
-        if (lane == 0) {
-            s_max[h] = mx;
-            s_inv[h] = n1 > n0 ? 1.0f / sum : 0.f;
-        }
-    }
-    __syncthreads();
-    const int my_h = c / hd;
-    float acc = 0.f;
-    for (int base = n0; base < n1; base += 32) {
-        for (int t = c; t < heads * 32; t += blockDim.x) {
-            const int h = t >> 5, i = t & 31, n = base + i;
-            s_p[h][i] = n < n1 ? expf(s2[(size_t)n * 128 + h * gs + k] - s_max[h]) * s_inv[h] : 0.f;
-        }
-        __syncthreads();
-        const int cnt = min(32, n1 - base);
-        if (c < D)
-            for (int i = 0; i < cnt; ++i) acc = fmaf(s_p[my_h][i], op2f(v2[(size_t)(base + i) * D + c]), acc);
-        if (attn && c < cnt) {
-            float tot = 0.f;
-            for (int h = 0; h < heads; ++h) tot += s_p[h][c];
-            attn[(size_t)n_kg * n0 + (size_t)k * (n1 - n0) + (base - n0) + c] = tot / (float)heads;
-        }
-        __syncthreads();
-    }
-    if (c < D) {   // split row [hi | lo | hi]
-        op_t* o = ctx2 + ((size_t)b * n_kg + k) * 3 * D + c;
-        const op_t hi = f2op(acc);
-        o[0] = hi;
-        o[D] = f2op(acc - op2f(hi));
-        o[2 * D] = hi;
-    }
-}
-
-// out[g, c] = mean over rows seg_ptr[g] .. (or fixed_len rows) of in, written as a split row: thirds of `third`
-// columns [hi | lo | hi], this segment mean landing at column offset col0 of each third
-__global__ void __launch_bounds__(128) segment_mean_split_kernel(const float* __restrict__ in, int dim, const int* __restrict__ seg_ptr,
-                                                                 int fixed_len, op_t* __restrict__ out, int third, int col0) {
-    const int g = blockIdx.x, c = blockIdx.y * 128 + threadIdx.x;
-    if (c >= dim) return;
-    const int a = seg_ptr ? seg_ptr[g] : g * fixed_len;
-    const int z = seg_ptr ? seg_ptr[g + 1] : a + fixed_len;
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    int r = a;
-    for (; r + 3 < z; r += 4) {
-        s0 += in[(size_t)r * dim + c];
-        s1 += in[(size_t)(r + 1) * dim + c];
-        s2 += in[(size_t)(r + 2) * dim + c];
-        s3 += in[(size_t)(r + 3) * dim + c];
-    }
-    for (; r < z; ++r) s0 += in[(size_t)r * dim + c];
-    const int n = z - a;
-    const float v = n > 0 ? ((s0 + s1) + (s2 + s3)) / (float)n : 0.f;
-    op_t* o = out + (size_t)g * 3 * third + col0 + c;
-    const op_t hi = f2op(v);
-    o[0] = hi;
-    o[third] = f2op(v - op2f(hi));
-    o[2 * third] = hi;
-}
-
-static int seg_mean_split(const float* in, int dim, const int* seg_ptr, int fixed_len, int n_seg, op_t* out, int third, int col0,
-                          cudaStream_t st) {
-    dim3 grid(n_seg, ceil_div(dim, 128));
-    {
-        CM_TIMED("segment_mean", st);
-        segment_mean_split_kernel<<<grid, 128, 0, st>>>(in, dim, seg_ptr, fixed_len, out, third, col0);
-    }
-    return post_launch("segment_mean");
-}
-
 int fusion_fold(const cm_fusion_params* p, const float* kg, int n_kg, void* folded, cudaStream_t st) {
     const FusionFolded f = fusion_folded_layout(p, n_kg);
     char* base = reinterpret_cast<char*>(folded);
@@ -250,53 +146,42 @@ int fusion_fold(const cm_fusion_params* p, const float* kg, int n_kg, void* fold
     if ((rc = cast_weight(p->k2r_in_w + (size_t)2 * D * D, base + f.wv2, (size_t)D * D, st)) != CM_OK) return rc;
     if ((rc = cast_weight(p->ffn_rg_w1, base + f.ffn1, (size_t)2 * D * D, st)) != CM_OK) return rc;
     if ((rc = cast_weight(p->ffn_rg_w2, base + f.ffn2, (size_t)2 * D * D, st)) != CM_OK) return rc;
-    auto SW = [&](const float* w, int rows, int cols, size_t off) {
-        return launch_split_weight(w, rows, cols, cols, nullptr, reinterpret_cast<op_t*>(base + off), st);
-    };
-    if ((rc = SW(p->k2r_out_w, D, D, f.wo2)) != CM_OK) return rc;
-    if ((rc = SW(p->ffn_kg_w1, 2 * D, D, f.kffn1)) != CM_OK) return rc;
-    if ((rc = SW(p->ffn_kg_w2, D, 2 * D, f.kffn2)) != CM_OK) return rc;
-    if ((rc = SW(p->fl_w1, D, 2 * D, f.fl1)) != CM_OK) return rc;
-    if ((rc = SW(p->fl_w2, D, D, f.fl2)) != CM_OK) return rc;
-    if ((rc = cast_weight(kp, base + f.kp_h, (size_t)K * D, st)) != CM_OK) return rc;
-    if (p->head_w1[0]) {
-        {
-            CM_TIMED("fusion_fold", st);
-            concat_heads1_kernel<<<64, 256, 0, st>>>(*p, reinterpret_cast<op_t*>(base + f.hw1), reinterpret_cast<float*>(base + f.hb1));
-        }
-        if ((rc = post_launch("fusion_fold(heads)")) != CM_OK) return rc;
-    }
+    if ((rc = cast_weight(p->k2r_out_w, base + f.wo2_h, (size_t)D * D, st)) != CM_OK) return rc;
+    if ((rc = cast_weight(p->ffn_kg_w1, base + f.kffn1_h, (size_t)2 * D * D, st)) != CM_OK) return rc;
+    if ((rc = cast_weight(p->ffn_kg_w2, base + f.kffn2_h, (size_t)2 * D * D, st)) != CM_OK) return rc;
     return CM_OK;
 }
 
 struct FusionTcWs {
-    op_t *rgb, *r, *p1, *v2, *y0, *hh, *ctx2, *z0, *hk, *both, *f1, *fusedb;
-    float *s2, *y, *z, *z0f, *fused, *hid;
+    op_t *rgb, *r, *p1, *v2, *y0, *hh, *ctx2, *z0, *hk;
+    float *s2, *y, *part_m, *part_l, *part_acc, *part_y, *stat, *z, *both;
     size_t total;
 };
 
 static FusionTcWs carve_fusion_tc(void* ws, const cm_fusion_params* p, int G, int M, int Kk) {
     Carver c(ws);
     FusionTcWs w;
-    const size_t D = p->hidden, m = M, gk = (size_t)G * Kk;
+    const size_t D = p->hidden, m = M, gc = (size_t)G * KG_MAX_CHUNKS;
+    const int gs = Kk <= 16 ? 16 : 32;
     w.rgb = c.take<op_t>(m * p->rg_dim);
     w.r = c.take<op_t>(m * D);
     w.p1 = c.take<op_t>(m * 128);
     w.v2 = c.take<op_t>(m * D);
     w.y0 = c.take<op_t>(m * D);
     w.hh = c.take<op_t>(m * 2 * D);
-    w.ctx2 = c.take<op_t>(gk * 3 * D);
-    w.z0 = c.take<op_t>(gk * 3 * D);
-    w.hk = c.take<op_t>(gk * 3 * 2 * D);
-    w.both = c.take<op_t>((size_t)G * 3 * 2 * D);
-    w.f1 = c.take<op_t>((size_t)G * 3 * D);
-    w.fusedb = c.take<op_t>((size_t)G * 3 * D);
-    w.z0f = c.take<float>(gk * D);
     w.s2 = c.take<float>(m * 128);
     w.y = c.take<float>(m * D);
+    w.part_m = c.take<float>(gc * 128);
+    w.part_l = c.take<float>(gc * 128);
+    w.part_acc = c.take<float>(gc * gs * D);
+    w.part_y = c.take<float>(gc * D);
+    w.stat = c.take<float>((size_t)G * 256);
+    const size_t gk = (size_t)G * Kk;
+    w.ctx2 = c.take<op_t>(gk * D);
+    w.z0 = c.take<op_t>(gk * D);
+    w.hk = c.take<op_t>(gk * 2 * D);
     w.z = c.take<float>(gk * D);
-    w.fused = c.take<float>((size_t)G * D);
-    w.hid = c.take<float>((size_t)G * 4 * (D / 2));
+    w.both = c.take<float>((size_t)G * 2 * D);
     w.total = align_up(c.off, 256);
     return w;
 }
@@ -310,12 +195,22 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     const char* base = reinterpret_cast<const char*>(folded);
     auto W = [&](size_t off) { return reinterpret_cast<const op_t*>(base + off); };
     FusionTcWs w = carve_fusion_tc(workspace, p, G, M, Kk);
-    const int D = p->hidden, GK = G * Kk;
+    const int D = p->hidden;
     const int* m_dev = node_ptr + G;
     int rc;
     Dense d;
 
     if ((rc = launch_cast_f16(rg, p->rg_dim, M, p->rg_dim, m_dev, w.rgb, p->rg_dim, st)) != CM_OK) return rc;
+    if (fusion_node_fused_ok(p)) {
+        // the whole region-node side in one kernel (fusion_node.cu)
+        FusionNodeArgs a;
+        a.M = M; a.m_dev = m_dev;
+        a.b_rgproj = p->rg_proj_b; a.ccat = reinterpret_cast<const float*>(base + f.ccat); a.b_v2 = p->k2r_in_b + 2 * D;
+        a.b_out1 = p->r2k_out_b; a.ln_g = p->ln_rg_w; a.ln_b = p->ln_rg_b; a.b_ffn1 = p->ffn_rg_b1; a.b_ffn2 = p->ffn_rg_b2;
+        a.sm_gs = f.gs; a.sm_valid = Kk;
+        a.s2 = w.s2; a.v2 = w.v2; a.y = w.y; a.attn_mean = attn_rg2kg;
+        if ((rc = launch_fusion_node(a, w.rgb, W(f.w_rgproj), W(f.wcat), W(f.wv2), W(f.vot), W(f.ffn1), W(f.ffn2), st)) != CM_OK) return rc;
+    } else {
     const op_t* r = w.rgb;
     if (p->rg_proj_w) {   // fusion_model.py:108
         d = Dense(); d.A = w.rgb; d.lda = p->rg_dim; d.W = W(f.w_rgproj); d.M = M; d.N = D; d.K = p->rg_dim; d.m_dev = m_dev;
@@ -343,54 +238,46 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     d = Dense(); d.A = w.hh; d.lda = 2 * D; d.W = W(f.ffn2); d.M = M; d.N = D; d.K = 2 * D; d.m_dev = m_dev;
     d.bias = p->ffn_rg_b2; d.residual = w.y0; d.ldr = D; d.out_f32 = w.y; d.ldo_f32 = D;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-    if ((rc = seg_mean_split(w.y, D, node_ptr, 0, G, w.both, 2 * D, 0, st)) != CM_OK) return rc;
-
-    // ---- kg attends to rg (:123-131).  From here on rows are per (image, kg row) or per image: few rows whose
-    // rounding errors are not averaged over hundreds of nodes, so these layers run in split precision
-    // (activations [hi | lo | hi] x weights [hi | hi | lo], K tripled).
-    {
-        CM_TIMED("attn_kg2rg", st);
-        attn_kg2rg_fold_kernel<<<dim3(G, Kk), D, 0, st>>>(w.s2, w.v2, D, p->heads, f.gs, node_ptr, Kk, w.ctx2, attn_kg2rg);
     }
-    if ((rc = post_launch("attn_kg2rg")) != CM_OK) return rc;
-    d = Dense(); d.A = w.ctx2; d.lda = 3 * D; d.W = W(f.wo2); d.M = GK; d.N = D; d.K = 3 * D;
-    d.bias = p->k2r_out_b; d.residual_f32 = reinterpret_cast<const float*>(base + f.kp); d.ldr = D; d.res_mod = Kk;
-    d.ln_gamma = p->ln_kg_w; d.ln_beta = p->ln_kg_b; d.out_h = w.z0; d.ldo_h = 3 * D; d.split_out = 1; d.out_f32 = w.z0f; d.ldo_f32 = D;
-    if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-    d = Dense(); d.A = w.z0; d.lda = 3 * D; d.W = W(f.kffn1); d.M = GK; d.N = 2 * D; d.K = 3 * D;
-    d.bias = p->ffn_kg_b1; d.relu = 1; d.out_h = w.hk; d.ldo_h = 6 * D; d.split_out = 1;
-    if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-    d = Dense(); d.A = w.hk; d.lda = 6 * D; d.W = W(f.kffn2); d.M = GK; d.N = D; d.K = 6 * D;
-    d.bias = p->ffn_kg_b2; d.residual_f32 = w.z0f; d.ldr = D; d.out_f32 = w.z; d.ldo_f32 = D;
-    if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-    if ((rc = seg_mean_split(w.z, D, nullptr, Kk, G, w.both, 2 * D, D, st)) != CM_OK) return rc;   // :135
-
-    // ---- fusion layer (:138-139) and the four heads (:239-242)
-    float* fused = fused_out ? fused_out : w.fused;
-    d = Dense(); d.A = w.both; d.lda = 6 * D; d.W = W(f.fl1); d.M = G; d.N = D; d.K = 6 * D;
-    d.bias = p->fl_b1; d.relu = 1; d.out_h = w.f1; d.ldo_h = 3 * D; d.split_out = 1;
-    if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-    d = Dense(); d.A = w.f1; d.lda = 3 * D; d.W = W(f.fl2); d.M = G; d.N = D; d.K = 3 * D;
-    d.bias = p->fl_b2; d.out_h = w.fusedb; d.ldo_h = 3 * D; d.split_out = 1; d.out_f32 = fused; d.ldo_f32 = D;
-    if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-    if (mask_out || instance_out || edge_out || score_out) {
-        const int H2 = D / 2;
-        d = Dense(); d.A = w.fusedb; d.lda = 3 * D; d.W = W(f.hw1); d.M = G; d.N = 4 * H2; d.K = 3 * D;
-        d.bias = reinterpret_cast<const float*>(base + f.hb1); d.relu = 1; d.out_f32 = w.hid; d.ldo_f32 = 4 * H2;
+    // ---- kg attends to rg (:123-131): chunk partials over the nodes, merged per image into ctx2 and the node mean (:134)
+    KgSideArgs ks;
+    ks.s2 = w.s2; ks.v2 = w.v2; ks.y = w.y; ks.part_m = w.part_m; ks.part_l = w.part_l; ks.part_acc = w.part_acc; ks.part_y = w.part_y;
+    ks.attn_kg2rg = attn_kg2rg; ks.node_cap = M;
+    if ((rc = launch_kg2rg_partial(ks, D, p->heads, f.gs, node_ptr, G, st)) != CM_OK) return rc;
+    if ((rc = launch_kg_merge(ks, D, p->heads, f.gs, Kk, node_ptr, G, w.ctx2, w.both, w.stat, st)) != CM_OK) return rc;
+    // ---- KG rows: z0 = LN(kp + ctx2 Wo^T + bo) (:130), z = z0 + FFN(z0) (:131)
+    const int GK = G * Kk;
+    const float* kp = reinterpret_cast<const float*>(base + f.kp);
+    if (D == 256) {
+        FusionNodeArgs a;
+        a.M = GK; a.m_dev = nullptr;
+        a.b_out1 = p->k2r_out_b; a.ln_g = p->ln_kg_w; a.ln_b = p->ln_kg_b; a.b_ffn1 = p->ffn_kg_b1; a.b_ffn2 = p->ffn_kg_b2;
+        a.res_rows = kp; a.res_mod = Kk; a.y = w.z;
+        if ((rc = launch_fusion_kgrows(a, w.ctx2, W(f.wo2_h), W(f.kffn1_h), W(f.kffn2_h), st)) != CM_OK) return rc;
+    } else {
+        d = Dense(); d.A = w.ctx2; d.lda = D; d.W = W(f.wo2_h); d.M = GK; d.N = D; d.K = D;
+        d.bias = p->k2r_out_b; d.residual_f32 = kp; d.ldr = D; d.res_mod = Kk; d.ln_gamma = p->ln_kg_w; d.ln_beta = p->ln_kg_b;
+        d.out_h = w.z0; d.ldo_h = D;
         if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-        Heads2 h2;
-        h2.n_heads = 4;
-        h2.hdim = H2;
-        float* outs[4] = {mask_out, instance_out, edge_out, score_out};
-        for (int t = 0; t < 4; ++t) {
-            h2.w2[t] = p->head_w2[t];
-            h2.b2[t] = p->head_b2[t];
-            h2.cdim[t] = t < 2 ? p->num_classes : 1;
-            h2.out[t] = outs[t];
-        }
-        h2.sigmoid[3] = 1;   // score head ends in nn.Sigmoid (fusion_model.py:229-235)
-        if ((rc = launch_heads2(w.hid, 4 * H2, G, nullptr, h2, st)) != CM_OK) return rc;
+        d = Dense(); d.A = w.z0; d.lda = D; d.W = W(f.kffn1_h); d.M = GK; d.N = 2 * D; d.K = D;
+        d.bias = p->ffn_kg_b1; d.relu = 1; d.out_h = w.hk; d.ldo_h = 2 * D;
+        if ((rc = launch_dense(d, st)) != CM_OK) return rc;
+        d = Dense(); d.A = w.hk; d.lda = 2 * D; d.W = W(f.kffn2_h); d.M = GK; d.N = D; d.K = 2 * D;
+        d.bias = p->ffn_kg_b2; d.residual = w.z0; d.ldr = D; d.out_f32 = w.z; d.ldo_f32 = D;
+        if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     }
+    // ---- mean over kg rows (:135), fusion layer (:138-139), heads (:239-242)
+    GraphTailArgs gt;
+    gt.D = D; gt.n_kg = Kk; gt.num_classes = p->num_classes;
+    gt.want_heads = (mask_out || instance_out || edge_out || score_out) ? 1 : 0;
+    gt.z = w.z; gt.both = w.both;
+    gt.fl1_w = p->fl_w1; gt.fl1_b = p->fl_b1; gt.fl2_w = p->fl_w2; gt.fl2_b = p->fl_b2;
+    for (int t = 0; t < 4; ++t) {
+        gt.hw1[t] = p->head_w1[t]; gt.hb1[t] = p->head_b1[t]; gt.hw2[t] = p->head_w2[t]; gt.hb2[t] = p->head_b2[t];
+        if (gt.want_heads) CM_REQUIRE(p->head_w1[t] && p->head_b1[t] && p->head_w2[t] && p->head_b2[t], "cm_fusion_forward: head %d parameters missing", t);
+    }
+    gt.fused = fused_out; gt.mask_out = mask_out; gt.inst_out = instance_out; gt.edge_out = edge_out; gt.score_out = score_out;
+    if ((rc = launch_graph_tail(gt, G, st)) != CM_OK) return rc;
     return post_launch("cm_fusion_forward(tc)");
 }
 

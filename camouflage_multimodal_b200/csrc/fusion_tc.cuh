@@ -6,7 +6,7 @@ namespace cm {
 
 struct FusionFolded {   // byte offsets into the folded blob
     int gs, n_kg;
-    size_t w_rgproj, wcat, wv2, vot, ffn1, ffn2, wo2, kffn1, kffn2, fl1, fl2, hw1, kp_h, ccat, hb1, kp, k1v1, q2, total;
+    size_t w_rgproj, wcat, wv2, vot, ffn1, ffn2, wo2_h, kffn1_h, kffn2_h, ccat, kp, k1v1, q2, total;
 };
 
 bool fusion_fold_supported(const cm_fusion_params* p, int n_kg);

@@ -71,12 +71,14 @@ class RegionGraphBatch:
 
 def build_region_graphs(images, labels, canny, label_cap: int | None = None, edge_cap: int | None = None,
                         want_edge_index: bool = True, local_ids: bool = False, out: RegionGraphBatch | None = None,
-                        norm_side: float = NORM_SIDE) -> RegionGraphBatch:
+                        norm_side: float = NORM_SIDE, feature_kernel: str = "auto") -> RegionGraphBatch:
     """A1-A4 for a batch: images ``[B,H,W,3]`` f32, labels ``[B,H,W]`` i32, canny ``[B,H,W]`` u8, all CUDA.
 
     ``label_cap`` bounds the label values (labels >= label_cap are reported through ``status``); the default
     reads ``labels.max()+1`` back from the device (one sync) -- pass it to stay asynchronous.  ``edge_cap``
     defaults to 16 directed edges per possible node.  No host synchronisation happens when ``label_cap`` is given.
+    ``feature_kernel``: ``"auto"`` = pixel-parallel kernel with per-label shared-memory tables (falls back by itself
+    when the table does not fit), ``"bbox"`` = one warp per region over its bounding box.
     """
     lib = _lib.load()
     for t, n in ((images, "images"), (labels, "labels"), (canny, "canny")):
@@ -110,6 +112,7 @@ def build_region_graphs(images, labels, canny, label_cap: int | None = None, edg
             batch_vec=torch.empty(node_cap, dtype=torch.int64, device=dev),
             status=torch.zeros(1, **i32), batch=B, label_cap=label_cap, node_cap=node_cap, edge_cap=ecap)
     st = _lib.stream_ptr(dev)
+    tile_cap = 0 if feature_kernel == "bbox" else label_cap
     ws_bytes = lib.cm_rag_workspace_bytes(B, label_cap)
     ws = WORKSPACE.get(dev, "rag", ws_bytes)
     p = _lib.ptr
@@ -117,7 +120,7 @@ def build_region_graphs(images, labels, canny, label_cap: int | None = None, edg
                                 p(g.edge_ptr), p(g.node_label), p(g.node_bbox), p(g.batch_vec), p(g.csr_row_ptr),
                                 p(g.csr_col), p(g.edge_index), 1 if local_ids else 0, g.node_cap, g.edge_cap,
                                 p(g.status), st), "cm_rag_build")
-    _lib.check(lib.cm_node_features(p(images), p(labels), p(canny), B, H, W, p(g.node_ptr), p(g.node_label),
+    _lib.check(lib.cm_node_features(p(images), p(labels), p(canny), B, H, W, tile_cap, p(g.node_ptr), p(g.node_label),
                                     p(g.node_bbox), float(norm_side), p(g.x), g.node_cap, st), "cm_node_features")
     n_dev = g.node_ptr[B:]
     _lib.check(lib.cm_edge_weights(p(g.x), p(g.csr_row_ptr), p(g.csr_col), p(n_dev), g.node_cap, p(g.edge_w), st),

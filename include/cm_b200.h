@@ -80,10 +80,11 @@ int cm_rag_build(const int32_t* labels, int batch, int h, int w, int label_cap, 
 /* A3: the 15 region features (extract_rg_embeddings.py:154-211).
  * image [B,H,W,3] float32 in [0,1]; canny [B,H,W] uint8 (non-zero = edge pixel, the output of
  * skimage.feature.canny(gray, sigma=2), :152); x [node_cap,15] float32 out.
- * norm_side is the reference's hard-coded 256.0 (:172-174). */
+ * norm_side is the reference's hard-coded 256.0 (:172-174).  label_cap = the bound passed to cm_rag_build
+ * (labels >= label_cap are never nodes); 0 selects the bounding-box kernel that needs no per-label table. */
 int cm_node_features(const float* image, const int32_t* labels, const uint8_t* canny, int batch, int h,
-                     int w, const int32_t* node_ptr, const int32_t* node_label, const int32_t* node_bbox,
-                     float norm_side, float* x, int node_cap, void* stream);
+                     int w, int label_cap, const int32_t* node_ptr, const int32_t* node_label,
+                     const int32_t* node_bbox, float norm_side, float* x, int node_cap, void* stream);
 
 /* A4: Gaussian-kernel edge weights (extract_rg_embeddings.py:227-235), one per directed CSR entry,
  * float32 arithmetic.  n_nodes_dev points at the device-side node count (node_ptr + B). */
