@@ -141,13 +141,14 @@ __global__ void __launch_bounds__(256) node_features_kernel(const float* __restr
 // are emitted by the OUTSIDE pixel: it looks at its 12 L1<=2 neighbours and contributes once to every distinct
 // foreign label (the 4-neighbours come first, so a first occurrence among them is a perimeter pixel).  The four
 // partial tables are then summed over distributed shared memory and one thread per node writes the 15 features.
-constexpr int NF_THREADS = 256, NF_CLUSTER = 4, NF_STRIP = 8, NF_NONE = INT_MIN;
+constexpr int NF_THREADS = 512, NF_CLUSTER = 4, NF_NONE = INT_MIN;
 constexpr double NF_S1 = 1099511627776.0, NF_S2 = 17592186044416.0;   // 2^40, 2^44
 
-struct NfTables {
-    unsigned long long* a64;   // [11][cap]: s1 r,g,b | gray | s2 r,g,b | gray^2 | ring r,g,b
-    unsigned int* a32;         // [6][cap]:  count | sum x | sum y | canny | perimeter | ring count
-};
+// Per-label accumulators, all 32-bit so that every update is a native shared-memory ATOMS.ADD (64-bit shared atomics
+// are CAS loops): the 11 fixed-point sums (s1 r,g,b | gray | s2 r,g,b | gray^2 | ring r,g,b) are kept as three 16-bit
+// limbs each -- limb sums stay below 2^32 for up to 65535 pixels per CTA -- rows 3q .. 3q+2 of a32; rows 33..38 hold
+// count | sum x | sum y | canny | perimeter | ring count.
+constexpr int NF_ROWS = 39, NF_CNT = 33;
 
 __device__ __forceinline__ unsigned long long nf_fix(double v, double scale) { return (unsigned long long)__double2ll_rn(v * scale); }
 
@@ -159,16 +160,13 @@ node_features_tile_kernel(const float* __restrict__ image, const int* __restrict
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int rpc = (H + NF_CLUSTER - 1) / NF_CLUSTER, y0 = rank * rpc, y1 = min(H, y0 + rpc), th = rpc + 4;
-    NfTables t;
-    t.a64 = reinterpret_cast<unsigned long long*>(nf_smem);
-    t.a32 = reinterpret_cast<unsigned int*>(t.a64 + 11 * (size_t)cap);
-    int* lab_s = reinterpret_cast<int*>(t.a32 + 6 * (size_t)cap);
+    unsigned int* tab = reinterpret_cast<unsigned int*>(nf_smem);   // [NF_ROWS][cap]
+    int* lab_s = reinterpret_cast<int*>(tab + (NF_ROWS * (size_t)cap + 3) / 4 * 4);   // 16-byte aligned for the int4 row copies
     const int* lab = labels + (size_t)b * H * W;
     const float* img = image + (size_t)b * H * W * 3;
     const uint8_t* can = canny + (size_t)b * H * W;
 
-    for (int i = tid; i < 11 * cap; i += NF_THREADS) t.a64[i] = 0ull;
-    for (int i = tid; i < 6 * cap; i += NF_THREADS) t.a32[i] = 0u;
+    for (int i = tid; i < NF_ROWS * cap; i += NF_THREADS) tab[i] = 0u;
     for (int i = tid; i < th * (W / 4); i += NF_THREADS) {   // label rows y0-2 .. y0+rpc+1; rows outside the image -> NF_NONE
         const int r = i / (W / 4), c4 = (i - r * (W / 4)) * 4, y = y0 - 2 + r;
         int4 v = make_int4(NF_NONE, NF_NONE, NF_NONE, NF_NONE);
@@ -177,100 +175,223 @@ node_features_tile_kernel(const float* __restrict__ image, const int* __restrict
     }
     __syncthreads();
 
-    auto flush = [&](int L, const double* s1, const double* s2, double sg, double sg2, int cnt, int sx, int y, int sc) {
-        if (cnt == 0 || L < 0 || L >= cap) return;
+    // ---- helpers -------------------------------------------------------------------------------------------
+    auto add64 = [&](int q, int L, unsigned long long v) {   // quantity q of label L += v, as three 16-bit limbs
+        atomicAdd(tab + (size_t)(3 * q) * cap + L, (unsigned)(v & 0xffffull));
+        atomicAdd(tab + (size_t)(3 * q + 1) * cap + L, (unsigned)((v >> 16) & 0xffffull));
+        atomicAdd(tab + (size_t)(3 * q + 2) * cap + L, (unsigned)(v >> 32));
+    };
+    // Lanes that hold partial sums for the same label in neighbouring columns are combined with a segmented
+    // inclusive scan (shuffles, no divergence); only the last lane of every run touches the table.
+    auto seg_begin = [&](int key, bool& head, bool& tail) {
+        const int up = __shfl_up_sync(0xffffffffu, key, 1), dn = __shfl_down_sync(0xffffffffu, key, 1);
+        head = lane == 0 || up != key;
+        tail = lane == 31 || dn != key;
+    };
+    auto seg_scan64 = [&](unsigned long long v, bool head) -> unsigned long long {
+        bool f = head;
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            atomicAdd(t.a64 + (size_t)c * cap + L, nf_fix(s1[c], NF_S1));
-            atomicAdd(t.a64 + (size_t)(4 + c) * cap + L, nf_fix(s2[c], NF_S2));
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long vu = __shfl_up_sync(0xffffffffu, v, d);
+            const bool fu = __shfl_up_sync(0xffffffffu, (int)f, d) != 0;
+            if (lane >= d && !f) {
+                v += vu;
+                f = fu;
+            }
         }
-        atomicAdd(t.a64 + (size_t)3 * cap + L, nf_fix(sg, NF_S1));
-        atomicAdd(t.a64 + (size_t)7 * cap + L, nf_fix(sg2, NF_S2));
-        atomicAdd(t.a32 + L, (unsigned)cnt);
-        atomicAdd(t.a32 + (size_t)cap + L, (unsigned)sx);
-        atomicAdd(t.a32 + (size_t)2 * cap + L, (unsigned)(cnt * y));
-        if (sc) atomicAdd(t.a32 + (size_t)3 * cap + L, (unsigned)sc);
+        return v;
+    };
+    auto seg_scan32 = [&](unsigned v, bool head) -> unsigned {
+        bool f = head;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned vu = __shfl_up_sync(0xffffffffu, v, d);
+            const bool fu = __shfl_up_sync(0xffffffffu, (int)f, d) != 0;
+            if (lane >= d && !f) {
+                v += vu;
+                f = fu;
+            }
+        }
+        return v;
+    };
+    struct Member {   // moment sums of one label inside this lane's column segment
+        int L;
+        unsigned long long q[8];   // s1 r,g,b | gray | s2 r,g,b | gray^2 (fixed point)
+        unsigned cs, sx, sy;       // count | canny << 16, sum x, sum y
+    };
+    struct Ring {     // what this lane's pixels contribute to one foreign label
+        int L;
+        unsigned long long q[3];   // rgb (fixed point)
+        unsigned cp;               // ring count | perimeter << 16
+    };
+    auto flush_member = [&](Member& m) {
+        if (!__any_sync(0xffffffffu, m.L != NF_NONE)) return;
+        bool head, tail;
+        seg_begin(m.L, head, tail);
+        unsigned long long tq[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) tq[k] = seg_scan64(m.q[k], head);
+        const unsigned cs = seg_scan32(m.cs, head), sx = seg_scan32(m.sx, head), sy = seg_scan32(m.sy, head);
+        if (tail && m.L != NF_NONE) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) add64(k, m.L, tq[k]);
+            atomicAdd(tab + (size_t)NF_CNT * cap + m.L, cs & 0xffffu);
+            atomicAdd(tab + (size_t)(NF_CNT + 1) * cap + m.L, sx);
+            atomicAdd(tab + (size_t)(NF_CNT + 2) * cap + m.L, sy);
+            if (cs >> 16) atomicAdd(tab + (size_t)(NF_CNT + 3) * cap + m.L, cs >> 16);
+        }
+        m.L = NF_NONE;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) m.q[k] = 0ull;
+        m.cs = m.sx = m.sy = 0u;
+    };
+    auto flush_ring = [&](Ring& r) {
+        if (!__any_sync(0xffffffffu, r.L != NF_NONE)) return;
+        bool head, tail;
+        seg_begin(r.L, head, tail);
+        unsigned long long tq[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) tq[k] = seg_scan64(r.q[k], head);
+        const unsigned cp = seg_scan32(r.cp, head);
+        if (tail && r.L != NF_NONE) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) add64(8 + k, r.L, tq[k]);
+            atomicAdd(tab + (size_t)(NF_CNT + 5) * cap + r.L, cp & 0xffffu);
+            if (cp >> 16) atomicAdd(tab + (size_t)(NF_CNT + 4) * cap + r.L, cp >> 16);
+        }
+        r.L = NF_NONE;
+        r.q[0] = r.q[1] = r.q[2] = 0ull;
+        r.cp = 0u;
     };
 
-    for (int y = y0 + warp; y < y1; y += NF_THREADS / 32) {
-        const int* row = lab_s + (y - y0 + 2) * W;
-        for (int x0 = lane * NF_STRIP; x0 < W; x0 += 32 * NF_STRIP) {
-            float px[3 * NF_STRIP];
-            const float4* ip = reinterpret_cast<const float4*>(img + ((size_t)y * W + x0) * 3);
+    // ---- a warp owns bands of 8 adjacent rows; a lane walks DOWN its column, so the pixels it sees belong to one or
+    // two labels (regions are taller than a few pixels) and their sums stay in registers until the band ends
+    const float S1f = 1099511627776.0f;   // 2^40: float x 2^40 is exact, so is its conversion to a 64-bit integer
+    const int n_bands = (y1 - y0 + 7) / 8;
+    // work item = (band, group of 32 columns), dealt round-robin to the 16 warps
+    const int n_xg = (W + 31) / 32;
+    for (int item = warp; item < n_bands * n_xg; item += NF_THREADS / 32) {
+        const int yb = y0 + (item / n_xg) * 8;
+        {
+            const int x = (item % n_xg) * 32 + lane;
+            const bool in = x < W;
+            Member ma, mb;
+            Ring ra, rb;
+            ma.L = mb.L = ra.L = rb.L = NF_NONE;
 #pragma unroll
-            for (int i = 0; i < 6; ++i) {
-                const float4 v = __ldg(ip + i);
-                px[4 * i] = v.x; px[4 * i + 1] = v.y; px[4 * i + 2] = v.z; px[4 * i + 3] = v.w;
-            }
-            const uint2 cw = __ldg(reinterpret_cast<const uint2*>(can + (size_t)y * W + x0));
-            const unsigned long long cbits = ((unsigned long long)cw.y << 32) | cw.x;
-            double s1[3] = {0, 0, 0}, s2[3] = {0, 0, 0}, sg = 0, sg2 = 0;
-            int curL = NF_NONE, cnt = 0, sx = 0, sc = 0;
+            for (int k = 0; k < 8; ++k) ma.q[k] = mb.q[k] = 0ull;
+            ma.cs = ma.sx = ma.sy = mb.cs = mb.sx = mb.sy = 0u;
+            ra.q[0] = ra.q[1] = ra.q[2] = rb.q[0] = rb.q[1] = rb.q[2] = 0ull;
+            ra.cp = rb.cp = 0u;
+            for (int i = 0; i < 8; ++i) {
+                const int y = yb + i;
+                if (y >= y1) break;
+                const int* row = lab_s + (y - y0 + 2) * W;
+                const size_t p = (size_t)y * W + (in ? x : 0);
+                const int L = in ? row[x] : NF_NONE;
+                const float r = __ldg(img + 3 * p), g = __ldg(img + 3 * p + 1), bl = __ldg(img + 3 * p + 2);
+                const unsigned long long fr = (unsigned long long)__float2ll_rn(r * S1f), fg = (unsigned long long)__float2ll_rn(g * S1f),
+                                         fb = (unsigned long long)__float2ll_rn(bl * S1f);
+                if (in && L >= 0 && L < cap) {
+                    const double dr = r, dg = g, db = bl;
+                    const double gray = dr * 0.2989 + dg * 0.5870 + db * 0.1140;   // :151
+                    unsigned long long t8[8] = {fr, fg, fb, nf_fix(gray, NF_S1), nf_fix(dr * dr, NF_S2), nf_fix(dg * dg, NF_S2),
+                                                nf_fix(db * db, NF_S2), nf_fix(gray * gray, NF_S2)};
+                    const unsigned cs = 1u | (can[p] != 0 ? 0x10000u : 0u);
+                    if (ma.L == NF_NONE) ma.L = L;
+                    if (L == ma.L) {
 #pragma unroll
-            for (int i = 0; i < NF_STRIP; ++i) {
-                const int x = x0 + i, L = row[x];
-                const double dr = px[3 * i], dg = px[3 * i + 1], db = px[3 * i + 2];
-                if (L != curL) {
-                    flush(curL, s1, s2, sg, sg2, cnt, sx, y, sc);
-                    curL = L; cnt = 0; sx = 0; sc = 0; sg = 0; sg2 = 0;
-                    s1[0] = s1[1] = s1[2] = 0; s2[0] = s2[1] = s2[2] = 0;
+                        for (int k = 0; k < 8; ++k) ma.q[k] += t8[k];
+                        ma.cs += cs; ma.sx += (unsigned)x; ma.sy += (unsigned)y;
+                    } else {
+                        if (mb.L == NF_NONE) mb.L = L;
+                        if (L == mb.L) {
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) mb.q[k] += t8[k];
+                            mb.cs += cs; mb.sx += (unsigned)x; mb.sy += (unsigned)y;
+                        } else {   // a third label inside 8 rows of one column: straight to the table
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) add64(k, L, t8[k]);
+                            atomicAdd(tab + (size_t)NF_CNT * cap + L, 1u);
+                            atomicAdd(tab + (size_t)(NF_CNT + 1) * cap + L, (unsigned)x);
+                            atomicAdd(tab + (size_t)(NF_CNT + 2) * cap + L, (unsigned)y);
+                            if (cs >> 16) atomicAdd(tab + (size_t)(NF_CNT + 3) * cap + L, 1u);
+                        }
+                    }
                 }
-                s1[0] += dr; s1[1] += dg; s1[2] += db;
-                s2[0] += dr * dr; s2[1] += dg * dg; s2[2] += db * db;
-                const double gray = dr * 0.2989 + dg * 0.5870 + db * 0.1140;   // :151
-                sg += gray;
-                sg2 += gray * gray;
-                ++cnt;
-                sx += x;
-                sc += ((cbits >> (8 * i)) & 0xffull) != 0ull;
-                // ---- what this pixel contributes to its foreign neighbours' regions
-                int v[12];
-                v[0] = x > 0 ? row[x - 1] : NF_NONE;
-                v[1] = x + 1 < W ? row[x + 1] : NF_NONE;
-                v[2] = row[x - W];
-                v[3] = row[x + W];
-                v[4] = x > 1 ? row[x - 2] : NF_NONE;
-                v[5] = x + 2 < W ? row[x + 2] : NF_NONE;
-                v[6] = row[x - 2 * W];
-                v[7] = row[x + 2 * W];
-                v[8] = x > 0 ? row[x - W - 1] : NF_NONE;
-                v[9] = x + 1 < W ? row[x - W + 1] : NF_NONE;
-                v[10] = x > 0 ? row[x + W - 1] : NF_NONE;
-                v[11] = x + 1 < W ? row[x + W + 1] : NF_NONE;
-                bool any = false;
-#pragma unroll
-                for (int k = 0; k < 12; ++k) any |= (v[k] != L) & (v[k] != NF_NONE);
-                if (any) {
+                // ---- what this pixel contributes to its foreign neighbours' regions: distinct labels among the 12
+                // L1 <= 2 neighbours, the 4-neighbours first (a label first seen there makes this a perimeter pixel)
+                if (in) {
+                    int v[12];
+                    v[0] = x > 0 ? row[x - 1] : NF_NONE;
+                    v[1] = x + 1 < W ? row[x + 1] : NF_NONE;
+                    v[2] = row[x - W];
+                    v[3] = row[x + W];
+                    v[4] = x > 1 ? row[x - 2] : NF_NONE;
+                    v[5] = x + 2 < W ? row[x + 2] : NF_NONE;
+                    v[6] = row[x - 2 * W];
+                    v[7] = row[x + 2 * W];
+                    v[8] = x > 0 ? row[x - W - 1] : NF_NONE;
+                    v[9] = x + 1 < W ? row[x - W + 1] : NF_NONE;
+                    v[10] = x > 0 ? row[x + W - 1] : NF_NONE;
+                    v[11] = x + 1 < W ? row[x + W + 1] : NF_NONE;
+                    // first three distinct foreign labels (near flags in nf); a 4th+ distinct label is rare -> `over`
+                    int u1 = NF_NONE, u2 = NF_NONE, u3 = NF_NONE;
+                    unsigned nf = 0, over = 0;
 #pragma unroll
                     for (int k = 0; k < 12; ++k) {
                         const int u = v[k];
-                        bool first = (u != L) & (u >= 0) & (u < cap);
+                        if ((u != L) & (u >= 0) & (u < cap) & (u != u1) & (u != u2) & (u != u3)) {
+                            if (u1 == NF_NONE) { u1 = u; nf |= k < 4 ? 1u : 0u; }
+                            else if (u2 == NF_NONE) { u2 = u; nf |= k < 4 ? 2u : 0u; }
+                            else if (u3 == NF_NONE) { u3 = u; nf |= k < 4 ? 4u : 0u; }
+                            else over |= 1u << k;
+                        }
+                    }
+                    auto contribute = [&](int u, bool near) {
+                        const unsigned cp = 1u | (near ? 0x10000u : 0u);
+                        if (ra.L == NF_NONE) ra.L = u;
+                        if (u == ra.L) {
+                            ra.q[0] += fr; ra.q[1] += fg; ra.q[2] += fb; ra.cp += cp;
+                        } else {
+                            if (rb.L == NF_NONE) rb.L = u;
+                            if (u == rb.L) {
+                                rb.q[0] += fr; rb.q[1] += fg; rb.q[2] += fb; rb.cp += cp;
+                            } else {
+                                add64(8, u, fr); add64(9, u, fg); add64(10, u, fb);
+                                atomicAdd(tab + (size_t)(NF_CNT + 5) * cap + u, 1u);
+                                if (near) atomicAdd(tab + (size_t)(NF_CNT + 4) * cap + u, 1u);
+                            }
+                        }
+                    };
+                    if (u1 != NF_NONE) contribute(u1, (nf & 1u) != 0);
+                    if (u2 != NF_NONE) contribute(u2, (nf & 2u) != 0);
+                    if (u3 != NF_NONE) contribute(u3, (nf & 4u) != 0);
+                    if (over) {
 #pragma unroll
-                        for (int j = 0; j < k; ++j) first &= v[j] != u;
-                        if (first) {
-                            atomicAdd(t.a32 + (size_t)5 * cap + u, 1u);
-                            atomicAdd(t.a64 + (size_t)8 * cap + u, nf_fix(dr, NF_S1));
-                            atomicAdd(t.a64 + (size_t)9 * cap + u, nf_fix(dg, NF_S1));
-                            atomicAdd(t.a64 + (size_t)10 * cap + u, nf_fix(db, NF_S1));
-                            if (k < 4) atomicAdd(t.a32 + (size_t)4 * cap + u, 1u);
+                        for (int k = 0; k < 12; ++k) {
+                            if (!((over >> k) & 1u)) continue;
+                            bool first = true;
+#pragma unroll
+                            for (int j = 0; j < k; ++j) first &= v[j] != v[k];
+                            if (first) contribute(v[k], k < 4);
                         }
                     }
                 }
             }
-            flush(curL, s1, s2, sg, sg2, cnt, sx, y, sc);
+            flush_member(ma);
+            flush_member(mb);
+            flush_ring(ra);
+            flush_ring(rb);
         }
     }
     cluster.sync();
 
     // ---- one thread per node of the image: sum the four partial tables (DSMEM), then the 15 features
     const int n0 = node_ptr[b], nb = min(node_ptr[b + 1], node_cap) - n0;
-    const unsigned long long* r64[NF_CLUSTER];
-    const unsigned int* r32[NF_CLUSTER];
+    const unsigned int* rt[NF_CLUSTER];
 #pragma unroll
-    for (int r = 0; r < NF_CLUSTER; ++r) {
-        r64[r] = cluster.map_shared_rank(t.a64, r);
-        r32[r] = cluster.map_shared_rank(t.a32, r);
-    }
+    for (int r = 0; r < NF_CLUSTER; ++r) rt[r] = cluster.map_shared_rank(tab, r);
     for (int i = rank * NF_THREADS + tid; i < nb; i += NF_CLUSTER * NF_THREADS) {
         const int g = n0 + i, L = node_label[g];
         unsigned long long q64[11];
@@ -283,9 +404,11 @@ node_features_tile_kernel(const float* __restrict__ image, const int* __restrict
 #pragma unroll
             for (int r = 0; r < NF_CLUSTER; ++r) {
 #pragma unroll
-                for (int k = 0; k < 11; ++k) q64[k] += r64[r][(size_t)k * cap + L];
+                for (int k = 0; k < 11; ++k)
+                    q64[k] += (unsigned long long)rt[r][(size_t)(3 * k) * cap + L] + ((unsigned long long)rt[r][(size_t)(3 * k + 1) * cap + L] << 16) +
+                              ((unsigned long long)rt[r][(size_t)(3 * k + 2) * cap + L] << 32);
 #pragma unroll
-                for (int k = 0; k < 6; ++k) q32[k] += r32[r][(size_t)k * cap + L];
+                for (int k = 0; k < 6; ++k) q32[k] += rt[r][(size_t)(NF_CNT + k) * cap + L];
             }
         }
         float* o = xout + (size_t)g * CM_NODE_FEATURES;
@@ -323,7 +446,7 @@ node_features_tile_kernel(const float* __restrict__ image, const int* __restrict
 
 static size_t nf_tile_smem(int H, int W, int cap) {
     const int rpc = (H + NF_CLUSTER - 1) / NF_CLUSTER;
-    return (size_t)cap * (11 * 8 + 6 * 4) + (size_t)(rpc + 4) * W * 4;
+    return ((size_t)cap * NF_ROWS + 3) / 4 * 16 + (size_t)(rpc + 4) * W * 4;
 }
 
 // one thread per node row; weights for every directed CSR entry
@@ -438,7 +561,7 @@ extern "C" int cm_node_features(const float* image, const int32_t* labels, const
     CM_REQUIRE(batch > 0 && h > 0 && w > 0 && node_cap > 0 && norm_side > 0.f, "cm_node_features: bad sizes");
     cudaStream_t st = as_stream(stream);
     const size_t smem = label_cap > 0 ? nf_tile_smem(h, w, label_cap) : 0;
-    if (label_cap > 0 && w % 8 == 0 && smem <= 200 * 1024 && batch <= 65535) {
+    if (label_cap > 0 && w % 8 == 0 && smem <= 200 * 1024 && batch <= 65535 && (long long)((h + NF_CLUSTER - 1) / NF_CLUSTER) * w <= 65535) {
         static size_t smem_set = 0;
         if (smem > smem_set) {
             cudaFuncSetAttribute(node_features_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -157,34 +157,71 @@ __global__ void __launch_bounds__(1024) kg_merge_kernel(const float* __restrict_
 
 // out[o] = act(sum_k a[k] w[o][k] + bias[o]): one warp per output, lanes stride K in float4 (w rows are contiguous:
 // an nn.Linear weight as stored).  a, out in shared memory; K % 128 == 0 or any K % 4 == 0.
-__device__ __forceinline__ void gemv_warp(const float* a, const float* __restrict__ w, const float* __restrict__ bias, float* out, int N, int K,
-                                          bool relu) {
+template <int KI>   // K == 128 * KI: every weight load of a warp pass (8 outputs x KI float4 per lane) is issued before the first FMA
+__device__ __forceinline__ void gemv_warp_t(const float* a, const float* const* __restrict__ wrows, const float* const* __restrict__ brows,
+                                            int rows_per_mat, float* out, int N, bool relu) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    for (int o0 = warp * 8; o0 < N; o0 += nwarps * 8) {   // 8 outputs per warp pass: 8 independent weight loads in flight
+    constexpr int K = 128 * KI;
+    for (int o0 = warp * 8; o0 < N; o0 += nwarps * 8) {
+        float4 wv[8][KI];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int o = min(o0 + i, N - 1), m = o / rows_per_mat, r = o - m * rows_per_mat;
+            const float* wr = wrows[m] + (size_t)r * K;
+#pragma unroll
+            for (int q = 0; q < KI; ++q) wv[i][q] = __ldg(reinterpret_cast<const float4*>(wr + q * 128 + lane * 4));
+        }
         float s[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) s[i] = 0.f;
-        for (int k = lane * 4; k < K; k += 128) {
-            float4 wv[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
-                wv[i] = o0 + i < N ? __ldg(reinterpret_cast<const float4*>(w + (size_t)(o0 + i) * K + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
-            const float4 av = *reinterpret_cast<const float4*>(a + k);
+        for (int q = 0; q < KI; ++q) {
+            const float4 av = *reinterpret_cast<const float4*>(a + q * 128 + lane * 4);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                s[i] = fmaf(wv[i].x, av.x, s[i]);
-                s[i] = fmaf(wv[i].y, av.y, s[i]);
-                s[i] = fmaf(wv[i].z, av.z, s[i]);
-                s[i] = fmaf(wv[i].w, av.w, s[i]);
+                s[i] = fmaf(wv[i][q].x, av.x, s[i]);
+                s[i] = fmaf(wv[i][q].y, av.y, s[i]);
+                s[i] = fmaf(wv[i][q].z, av.z, s[i]);
+                s[i] = fmaf(wv[i][q].w, av.w, s[i]);
             }
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const float t = warp_sum(s[i]);
-            if (lane == 0 && o0 + i < N) {
-                const float v = t + (bias ? bias[o0 + i] : 0.f);
-                out[o0 + i] = relu ? fmaxf(v, 0.f) : v;
+            const int o = o0 + i;
+            if (lane == 0 && o < N) {
+                const int m = o / rows_per_mat, r = o - m * rows_per_mat;
+                const float v = t + (brows[m] ? brows[m][r] : 0.f);
+                out[o] = relu ? fmaxf(v, 0.f) : v;
             }
+        }
+    }
+}
+
+// out[o] = act(sum_k a[k] w[o][k] + bias[o]) for the rows of n_mat stacked nn.Linear weights ([rows_per_mat, K] each, as
+// stored); one warp per 8 outputs, lanes stride K in float4.  a, out in shared memory; K % 4 == 0.
+__device__ __forceinline__ void gemv_warp(const float* a, const float* const* wrows, const float* const* brows, int rows_per_mat, float* out,
+                                          int N, int K, bool relu) {
+    if (K == 512) return gemv_warp_t<4>(a, wrows, brows, rows_per_mat, out, N, relu);
+    if (K == 256) return gemv_warp_t<2>(a, wrows, brows, rows_per_mat, out, N, relu);
+    if (K == 128) return gemv_warp_t<1>(a, wrows, brows, rows_per_mat, out, N, relu);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int o = warp; o < N; o += nwarps) {
+        const int m = o / rows_per_mat, r = o - m * rows_per_mat;
+        const float* wr = wrows[m] + (size_t)r * K;
+        float s = 0.f;
+        for (int k = lane * 4; k < K; k += 128) {
+            const float4 wv = __ldg(reinterpret_cast<const float4*>(wr + k));
+            const float4 av = *reinterpret_cast<const float4*>(a + k);
+            s = fmaf(wv.x, av.x, s);
+            s = fmaf(wv.y, av.y, s);
+            s = fmaf(wv.z, av.z, s);
+            s = fmaf(wv.w, av.w, s);
+        }
+        s = warp_sum(s);
+        if (lane == 0) {
+            const float v = s + (brows[m] ? brows[m][r] : 0.f);
+            out[o] = relu ? fmaxf(v, 0.f) : v;
         }
     }
 }
@@ -202,15 +239,15 @@ __global__ void __launch_bounds__(1024) graph_tail_kernel(const GraphTailArgs a)
         both[c] = a.both[(size_t)b * 2 * D + c];
     }
     __syncthreads();
-    gemv_warp(both, a.fl1_w, a.fl1_b, f1, D, 2 * D, true);
+    gemv_warp(both, &a.fl1_w, &a.fl1_b, D, f1, D, 2 * D, true);
     __syncthreads();
-    gemv_warp(f1, a.fl2_w, a.fl2_b, fz, D, D, false);
+    gemv_warp(f1, &a.fl2_w, &a.fl2_b, D, fz, D, D, false);
     __syncthreads();
     if (a.fused)
         for (int c = tid; c < D; c += blockDim.x) a.fused[(size_t)b * D + c] = fz[c];
     if (!a.want_heads) return;
     const int H2 = D / 2;
-    for (int t = 0; t < 4; ++t) gemv_warp(fz, a.hw1[t], a.hb1[t], hid + t * H2, H2, D, true);
+    gemv_warp(fz, a.hw1, a.hb1, H2, hid, 4 * H2, D, true);   // first layers of the four heads as one stacked matrix
     __syncthreads();
     int o = 0;
     for (int t = 0; t < 4; ++t) {
