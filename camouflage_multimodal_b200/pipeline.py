@@ -17,8 +17,11 @@ from .region_graph import RegionGraphBatch, build_region_graphs
 
 class EvalPipeline:
     def __init__(self, gnn, detector, kg, label_cap: int = 544, threshold: float = 0.5, label_offset_fix: bool = False,
-                 want_pred_mask: bool = False):
-        """``kg``: ``[K, kg_dim]`` knowledge-graph rows shared by every image (broadcast once)."""
+                 want_pred_mask: bool = False, lane: int = 0):
+        """``kg``: ``[K, kg_dim]`` knowledge-graph rows shared by every image (broadcast once).
+        ``lane``: pipelines with different lanes own disjoint scratch and may run concurrently on different streams
+        (they share the read-only folded weights)."""
+        self.lane = int(lane)
         self.gnn, self.detector = gnn.eval(), detector.eval()
         kg = kg.reshape(-1, kg.shape[-1])
         _lib.require_cuda(kg, "kg")
@@ -52,6 +55,14 @@ class EvalPipeline:
     def run(self, images, labels, canny, gt):
         """Device inputs: images [B,H,W,3] f32, labels [B,H,W] i32, canny [B,H,W] u8, gt [B,H,W] u8.
         Returns a dict of device tensors (valid until the next call)."""
+        from .region_graph import WORKSPACE
+        prev_lane, WORKSPACE.lane = WORKSPACE.lane, self.lane
+        try:
+            return self._run(images, labels, canny, gt)
+        finally:
+            WORKSPACE.lane = prev_lane
+
+    def _run(self, images, labels, canny, gt):
         lib = _lib.load()
         B, H, W, _ = images.shape
         dev = images.device
@@ -136,47 +147,56 @@ class HostStager:
 
 
 class HostPipeline:
-    """Host-facing entry of the evaluation path: batches arrive in pinned host memory, go to the device on a copy
-    stream, through the captured step on the compute stream, and the logits + per-image metrics come back to pinned
-    host memory.  ``slots`` input buffers are rotated so the H2D copy of batch i+1 overlaps the kernels of batch i;
-    the kernels themselves stay serialised on one stream (they share the pipeline's intermediate buffers)."""
+    """Host-facing entry of the evaluation path: batches arrive in pinned host memory and each goes through one
+    *slot* -- its own stream, device input buffers, captured step and pinned result buffers -- as H2D copy ->
+    captured step -> D2H of the logits + per-image metrics.  Slots are rotated, so the copies of one batch overlap
+    the kernels of the others; slots whose pipelines sit on different lanes (``pipes`` list) also overlap their
+    kernels, slots sharing a pipeline are serialised through ``pipe_done`` events (they share its buffers)."""
 
-    def __init__(self, pipe: EvalPipeline, B, H, W, device, slots: int = 2, use_graph: bool = True):
-        self.pipe, self.dev = pipe, device
-        self.copy_stream = torch.cuda.Stream(device)
+    def __init__(self, pipe, B, H, W, device, slots: int = 2, use_graph: bool = True):
+        pipes = list(pipe) if isinstance(pipe, (list, tuple)) else [pipe]
+        self.pipes, self.dev = pipes, device
+        self.pipe_done = [torch.cuda.Event() for _ in pipes]
         self.slots = []
-        for _ in range(slots):
+        for k in range(slots):
             st = HostStager(B, H, W, device)
+            st.pipe_idx = k % len(pipes)
+            st.stream = torch.cuda.Stream(device)
             st.d_labels.fill_(1)
             st.d_images.zero_(); st.d_canny.zero_(); st.d_gt.zero_()
-            st.ev_h2d, st.ev_done = torch.cuda.Event(), torch.cuda.Event()
-            st.graph, st.out = pipe.capture(st.d_images, st.d_labels, st.d_canny, st.d_gt) if use_graph else (None, None)
+            st.ev_done = torch.cuda.Event()
+            st.graph, st.out = pipes[st.pipe_idx].capture(st.d_images, st.d_labels, st.d_canny, st.d_gt) if use_graph else (None, None)
             st.ev_done.record(torch.cuda.current_stream(device))
             self.slots.append(st)
+        for ev in self.pipe_done:
+            ev.record(torch.cuda.current_stream(device))
         self.h2d_bytes, self.d2h_bytes = self.slots[0].h2d_bytes, self.slots[0].d2h_bytes
 
     def submit(self, i, h_images, h_labels, h_canny, h_gt):
         """Queue batch ``i`` (pinned host tensors); returns its slot.  The slot's host results are valid once
         ``slot.ev_done`` has completed and until the slot is reused ``len(slots)`` submissions later."""
         st = self.slots[i % len(self.slots)]
-        main = torch.cuda.current_stream(self.dev)
-        self.copy_stream.wait_event(st.ev_done)            # the slot's previous batch has been consumed
-        with torch.cuda.stream(self.copy_stream):
+        pipe = self.pipes[st.pipe_idx]
+        with torch.cuda.stream(st.stream):
             st.d_images.copy_(h_images, non_blocking=True)
             st.d_labels.copy_(h_labels, non_blocking=True)
             st.d_canny.copy_(h_canny, non_blocking=True)
             st.d_gt.copy_(h_gt, non_blocking=True)
-            st.ev_h2d.record(self.copy_stream)
-        main.wait_event(st.ev_h2d)
-        if st.graph is not None:
-            st.graph.replay()
-            out = st.out
-        else:
-            out = self.pipe.run(st.d_images, st.d_labels, st.d_canny, st.d_gt)
-        st.h_mask_out.copy_(out["mask_out"], non_blocking=True)
-        st.h_per_image.copy_(out["per_image"], non_blocking=True)
-        st.ev_done.record(main)
+            st.stream.wait_event(self.pipe_done[st.pipe_idx])     # another slot may be using this pipeline's buffers
+            if st.graph is not None:
+                st.graph.replay()
+                out = st.out
+            else:
+                out = pipe.run(st.d_images, st.d_labels, st.d_canny, st.d_gt)
+            st.h_mask_out.copy_(out["mask_out"], non_blocking=True)
+            st.h_per_image.copy_(out["per_image"], non_blocking=True)
+            self.pipe_done[st.pipe_idx].record(st.stream)
+            st.ev_done.record(st.stream)
         return st
+
+    def synchronize(self):
+        for st in self.slots:
+            st.ev_done.synchronize()
 
 
 def allreduce_partials(partial: torch.Tensor, confusion: torch.Tensor | None = None):

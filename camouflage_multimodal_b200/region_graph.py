@@ -21,13 +21,15 @@ NORM_SIDE = 256.0   # hard-coded by the reference (extract_rg_embeddings.py:172-
 
 
 class _Workspace:
-    """Grow-only byte buffers per (device, tag): scratch handed to the C ABI."""
+    """Grow-only byte buffers per (device, tag, lane): scratch handed to the C ABI.  ``lane`` separates
+    pipelines that run concurrently on different streams (pipeline.EvalPipeline(lane=...))."""
 
     def __init__(self):
         self._bufs = {}
+        self.lane = 0
 
     def get(self, device, tag: str, nbytes: int) -> torch.Tensor:
-        key = (str(device), tag)
+        key = (str(device), tag, self.lane)
         buf = self._bufs.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
