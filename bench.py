@@ -136,6 +136,8 @@ def kernel_work(name, B, M, E, K):
         "rag_compact": ("hbm", 4.0 * B * LABEL_CAP * (4 + 17 + 2)),
         "rag_emit": ("hbm", 4.0 * B * LABEL_CAP * 17 + 4.0 * E + 28.0 * M),
         "node_features": ("hbm", px * (12.0 + 4.0 + 1.0) + 60.0 * M),
+        "node_features_u8": ("hbm", px * (3.0 + 4.0 + 1.0) + 60.0 * M),
+        "labels_widen": ("hbm", px * (2.0 + 4.0)),
         "edge_weights": ("hbm", 60.0 * M + 8.0 * E),
         "paint_metrics": ("hbm", px * (4.0 + 1.0) + 4.0 * M),
         "gat_logits": ("hbm", 60.0 * M + 32.0 * M),
@@ -155,12 +157,14 @@ def cpu_state_dicts(gnn, det):
             {k: v.detach().cpu().clone() for k, v in det.state_dict().items()})
 
 
-def run_cpu_baseline(gnn_sd, fusion_sd, kg, n_images=6):
+def run_cpu_baseline(gnn_sd, fusion_sd, kg, n_images=6, inp="u8"):
     """The oracle port of the reference's single-threaded per-image loop, timed on this host (1 core for the
     Python region loop; the dense layers use torch's default intra-op threads like the reference would)."""
     from camouflage_multimodal_b200 import synth
     from oracle import cpu_path
     sample = synth.make_batch(0, n_images, seed=1234)
+    if inp == "u8":
+        sample = sample.as_decoded().as_float()
     sec, _ = cpu_path.time_images(sample, gnn_sd, fusion_sd, kg, faithful=True, processes=1)
     return {"value": n_images / sec, "unit": "images/sec", "cores": 1, "kind": "port",
             "sample": f"{n_images} images of the same synthetic set through the oracle restatement of the reference's "
@@ -186,6 +190,8 @@ def reference_arm(args):
     torch.set_num_threads(1)
     total = (args.steps + args.warmup) * per_step
     data = synth.make_batch(0, total, seed=1234)
+    if args.input == "u8":      # the same byte-quantised images the B200 arm receives, as the float array the reference takes
+        data = data.as_decoded().as_float()
     items = [(data.images[i].numpy(), data.labels[i].numpy(), data.canny[i].numpy(), data.gt[i].numpy(), gsd, fsd, kg, True)
              for i in range(total)]
     times = []
@@ -204,19 +210,21 @@ def reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.gpus, kg_src),
+        "config": workload_config(args.gpus, kg_src, 0, args.input),
         "cpu_baseline": {"value": value, "unit": "images/sec", "cores": per_step, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
-def workload_config(n_gpus, kg_src, lanes=1):
+def workload_config(n_gpus, kg_src, lanes=1, inp="u8"):
     return {"workload": f"BASELINE configs[1]: synthetic COD10K-test-shaped set ({SET_SIZE} images, 256x256), batch {BATCH} "
                         f"per GPU: graph build + RG-GNN + RGxKG cross-attention fusion + heads + paint + utils/metrics",
             "batch_per_gpu": BATCH, "global_batch": BATCH * n_gpus, "regions_per_image": "303-530 (empirical histogram)",
             "kg": kg_src, "parallelism": f"dp{n_gpus} (images sharded i mod N, metric partial sums all-reduced once)",
             "l2": "6 distinct input batches per GPU (226 MB) rotated so every step's inputs come from HBM, not L2",
-            "lanes": lanes}
+            "lanes": lanes,
+            "input": ("uint8 RGB images (value = byte/255) + int16 label maps + uint8 canny + uint8 gt: 458 752 B per image"
+                      if inp == "u8" else "float32 images + int32 label maps + uint8 canny + uint8 gt: 1 179 648 B per image")}
 
 
 def b200_arm(args):
@@ -255,7 +263,8 @@ def b200_arm(args):
     pool = []
     for j in range(n_pool):
         first = (j * world + rank) * BATCH
-        pool.append(synth.make_batch(first % max(SET_SIZE - BATCH, 1), BATCH, seed=1234, device=dev))
+        b = synth.make_batch(first % max(SET_SIZE - BATCH, 1), BATCH, seed=1234, device=dev)
+        pool.append(b.as_decoded() if args.input == "u8" else b)
     torch.cuda.synchronize()
 
     def barrier():
@@ -322,7 +331,8 @@ def b200_arm(args):
     summary = summarize(total)
 
     # ---- end to end through the host-facing call: pinned host inputs, H2D + path + D2H every step
-    stager = HostPipeline(pipes, BATCH, H, W, dev, slots=max(2, 2 * lanes), use_graph=not args.no_graph)
+    stager = HostPipeline(pipes, BATCH, H, W, dev, slots=max(2, 2 * lanes), use_graph=not args.no_graph,
+                          image_dtype=pool[0].images.dtype, label_dtype=pool[0].labels.dtype)
     host_pool = [(b.images.cpu().pin_memory(), b.labels.cpu().pin_memory(), b.canny.cpu().pin_memory(), b.gt.cpu().pin_memory())
                  for b in pool]
 
@@ -377,7 +387,7 @@ def b200_arm(args):
         line = {
             "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f16", "data": "synthetic", "config": workload_config(world, kg_src, lanes), "clocks": clk,
+            "dtype": "f16", "data": "synthetic", "config": workload_config(world, kg_src, lanes, args.input), "clocks": clk,
             "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": stager.h2d_bytes,
                     "d2h_bytes_per_step": stager.d2h_bytes},
             "gpu_launches": int(round(launches_per_step * args.steps)),
@@ -386,7 +396,7 @@ def b200_arm(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             gsd, fsd = cpu_state_dicts(gnn, det)
-            line["cpu_baseline"] = run_cpu_baseline(gsd, fsd, kg.cpu(), args.cpu_images)
+            line["cpu_baseline"] = run_cpu_baseline(gsd, fsd, kg.cpu(), args.cpu_images, args.input)
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -399,6 +409,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pool", type=int, default=6, help="distinct input batches rotated per GPU (6 x 37.7 MB > L2)")
+    ap.add_argument("--input", default="u8", choices=["u8", "f32"],
+                    help="u8: uint8 RGB + int16 label maps as a decoder / SLIC hand them over (image value = byte/255); "
+                         "f32: float32 images in [0,1] + int32 labels")
     ap.add_argument("--lanes", type=int, default=3, help="pipelines with disjoint buffers replayed on their own streams")
     ap.add_argument("--cpu-images", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -60,6 +60,8 @@ SIGNATURES = {
     "cm_rag_workspace_bytes": (_sz, [_i, _i]),
     "cm_rag_build": (_i, [_fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp]),
     "cm_node_features": (_i, [_fp, _fp, _fp, _i, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
+    "cm_node_features_u8": (_i, [_fp, _fp, _fp, _i, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
+    "cm_labels_widen_i16": (_i, [_fp, _i64, _fp, _fp]),
     "cm_edge_weights": (_i, [_fp, _fp, _fp, _fp, _i, _fp, _fp]),
     "cm_csr_workspace_bytes": (_sz, [_i, _i]),
     "cm_csr_from_edge_index": (_i, [_fp, _i64, _fp, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp]),

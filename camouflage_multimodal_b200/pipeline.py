@@ -53,7 +53,8 @@ class EvalPipeline:
         }
 
     def run(self, images, labels, canny, gt):
-        """Device inputs: images [B,H,W,3] f32, labels [B,H,W] i32, canny [B,H,W] u8, gt [B,H,W] u8.
+        """Device inputs: images [B,H,W,3] f32 (or uint8 = byte/255), labels [B,H,W] i32 (or int16), canny [B,H,W] u8,
+        gt [B,H,W] u8.
         Returns a dict of device tensors (valid until the next call)."""
         from .region_graph import WORKSPACE
         prev_lane, WORKSPACE.lane = WORKSPACE.lane, self.lane
@@ -67,6 +68,13 @@ class EvalPipeline:
         B, H, W, _ = images.shape
         dev = images.device
         self._alloc(B, H, W, dev)
+        if labels.dtype == torch.int16:     # host-side label maps travel as int16; the kernels read int32
+            l32 = self._bufs.get("labels32")
+            if l32 is None:
+                l32 = self._bufs["labels32"] = torch.empty((B, H, W), dtype=torch.int32, device=dev)
+            _lib.check(lib.cm_labels_widen_i16(_lib.ptr(labels), labels.numel(), _lib.ptr(l32), _lib.stream_ptr(dev)),
+                       "cm_labels_widen_i16")
+            labels = l32
         g = build_region_graphs(images, labels, canny, label_cap=self.label_cap, want_edge_index=False, out=self._graph)
         self._graph = g
         n_dev = g.node_ptr[B:]
@@ -112,15 +120,15 @@ class EvalPipeline:
 class HostStager:
     """Pinned host buffers + device buffers for one batch: the host-facing entry of the pipeline."""
 
-    def __init__(self, B, H, W, device):
+    def __init__(self, B, H, W, device, image_dtype=torch.float32, label_dtype=torch.int32):
         self.dev = device
         pin = dict(pin_memory=True)
-        self.h_images = torch.empty((B, H, W, 3), dtype=torch.float32, **pin)
-        self.h_labels = torch.empty((B, H, W), dtype=torch.int32, **pin)
+        self.h_images = torch.empty((B, H, W, 3), dtype=image_dtype, **pin)
+        self.h_labels = torch.empty((B, H, W), dtype=label_dtype, **pin)
         self.h_canny = torch.empty((B, H, W), dtype=torch.uint8, **pin)
         self.h_gt = torch.empty((B, H, W), dtype=torch.uint8, **pin)
-        self.d_images = torch.empty((B, H, W, 3), dtype=torch.float32, device=device)
-        self.d_labels = torch.empty((B, H, W), dtype=torch.int32, device=device)
+        self.d_images = torch.empty((B, H, W, 3), dtype=image_dtype, device=device)
+        self.d_labels = torch.empty((B, H, W), dtype=label_dtype, device=device)
         self.d_canny = torch.empty((B, H, W), dtype=torch.uint8, device=device)
         self.d_gt = torch.empty((B, H, W), dtype=torch.uint8, device=device)
         self.h_mask_out = torch.empty((B, 2), dtype=torch.float32, **pin)
@@ -153,13 +161,14 @@ class HostPipeline:
     the kernels of the others; slots whose pipelines sit on different lanes (``pipes`` list) also overlap their
     kernels, slots sharing a pipeline are serialised through ``pipe_done`` events (they share its buffers)."""
 
-    def __init__(self, pipe, B, H, W, device, slots: int = 2, use_graph: bool = True):
+    def __init__(self, pipe, B, H, W, device, slots: int = 2, use_graph: bool = True, image_dtype=torch.float32,
+                 label_dtype=torch.int32):
         pipes = list(pipe) if isinstance(pipe, (list, tuple)) else [pipe]
         self.pipes, self.dev = pipes, device
         self.pipe_done = [torch.cuda.Event() for _ in pipes]
         self.slots = []
         for k in range(slots):
-            st = HostStager(B, H, W, device)
+            st = HostStager(B, H, W, device, image_dtype, label_dtype)
             st.pipe_idx = k % len(pipes)
             st.stream = torch.cuda.Stream(device)
             st.d_labels.fill_(1)

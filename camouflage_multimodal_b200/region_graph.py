@@ -74,19 +74,21 @@ class RegionGraphBatch:
 def build_region_graphs(images, labels, canny, label_cap: int | None = None, edge_cap: int | None = None,
                         want_edge_index: bool = True, local_ids: bool = False, out: RegionGraphBatch | None = None,
                         norm_side: float = NORM_SIDE, feature_kernel: str = "auto") -> RegionGraphBatch:
-    """A1-A4 for a batch: images ``[B,H,W,3]`` f32, labels ``[B,H,W]`` i32, canny ``[B,H,W]`` u8, all CUDA.
+    """A1-A4 for a batch: images ``[B,H,W,3]`` f32 in [0,1] or uint8 (value = byte / 255, integer-exact feature
+    kernel), labels ``[B,H,W]`` i32, canny ``[B,H,W]`` u8, all CUDA.
 
     ``label_cap`` bounds the label values (labels >= label_cap are reported through ``status``); the default
     reads ``labels.max()+1`` back from the device (one sync) -- pass it to stay asynchronous.  ``edge_cap``
     defaults to 16 directed edges per possible node.  No host synchronisation happens when ``label_cap`` is given.
     ``feature_kernel``: ``"auto"`` = pixel-parallel kernel with per-label shared-memory tables (falls back by itself
-    when the table does not fit), ``"bbox"`` = one warp per region over its bounding box.
+    when the table does not fit), ``"bbox"`` = one warp per region over its bounding box.  uint8 images default to the
+    region-parallel integer kernel; ``"tile"`` selects their pixel-parallel variant.
     """
     lib = _lib.load()
     for t, n in ((images, "images"), (labels, "labels"), (canny, "canny")):
         _lib.require_cuda(t, n)
-    if images.dim() != 4 or images.shape[-1] != 3 or images.dtype != torch.float32:
-        raise ValueError(f"images must be [B,H,W,3] float32, got {tuple(images.shape)} {images.dtype}")
+    if images.dim() != 4 or images.shape[-1] != 3 or images.dtype not in (torch.float32, torch.uint8):
+        raise ValueError(f"images must be [B,H,W,3] float32 or uint8, got {tuple(images.shape)} {images.dtype}")
     B, H, W, _ = images.shape
     if tuple(labels.shape) != (B, H, W) or labels.dtype != torch.int32:
         raise ValueError(f"labels must be [B,H,W] int32, got {tuple(labels.shape)} {labels.dtype}")
@@ -122,8 +124,13 @@ def build_region_graphs(images, labels, canny, label_cap: int | None = None, edg
                                 p(g.edge_ptr), p(g.node_label), p(g.node_bbox), p(g.batch_vec), p(g.csr_row_ptr),
                                 p(g.csr_col), p(g.edge_index), 1 if local_ids else 0, g.node_cap, g.edge_cap,
                                 p(g.status), st), "cm_rag_build")
-    _lib.check(lib.cm_node_features(p(images), p(labels), p(canny), B, H, W, tile_cap, p(g.node_ptr), p(g.node_label),
-                                    p(g.node_bbox), float(norm_side), p(g.x), g.node_cap, st), "cm_node_features")
+    if images.dtype == torch.uint8:
+        _lib.check(lib.cm_node_features_u8(p(images), p(labels), p(canny), B, H, W, label_cap, p(g.node_ptr), p(g.node_label),
+                                           None if feature_kernel == "tile" else p(g.node_bbox), float(norm_side), p(g.x),
+                                           g.node_cap, st), "cm_node_features_u8")
+    else:
+        _lib.check(lib.cm_node_features(p(images), p(labels), p(canny), B, H, W, tile_cap, p(g.node_ptr), p(g.node_label),
+                                        p(g.node_bbox), float(norm_side), p(g.x), g.node_cap, st), "cm_node_features")
     n_dev = g.node_ptr[B:]
     _lib.check(lib.cm_edge_weights(p(g.x), p(g.csr_row_ptr), p(g.csr_col), p(n_dev), g.node_cap, p(g.edge_w), st),
                "cm_edge_weights")

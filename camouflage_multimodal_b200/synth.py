@@ -181,6 +181,16 @@ class SynthBatch:
     def __len__(self):
         return self.images.shape[0]
 
+    def as_decoded(self):
+        """The same batch in the form a decoder hands over: uint8 RGB (byte = round(255 * value)) and int16 labels."""
+        img = self.images if self.images.dtype == torch.uint8 else (self.images * 255.0).round().clamp_(0, 255).to(torch.uint8)
+        return SynthBatch(img, self.labels.to(torch.int16), self.canny, self.gt, self.n_regions)
+
+    def as_float(self):
+        """uint8 images back to the float [0,1] form ``create_region_graph`` receives (byte / 255)."""
+        img = self.images.to(torch.float32) / 255.0 if self.images.dtype == torch.uint8 else self.images
+        return SynthBatch(img, self.labels.to(torch.int32), self.canny, self.gt, self.n_regions)
+
 
 def make_batch(first: int, count: int, seed: int = 1234, device="cpu", n_regions=None) -> SynthBatch:
     """Images ``first .. first+count-1`` of the seeded COD10K-shaped set."""

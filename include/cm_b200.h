@@ -86,6 +86,22 @@ int cm_node_features(const float* image, const int32_t* labels, const uint8_t* c
                      int w, int label_cap, const int32_t* node_ptr, const int32_t* node_label,
                      const int32_t* node_bbox, float norm_side, float* x, int node_cap, void* stream);
 
+/* A3 on 8-bit images: image_u8 [B,H,W,3] uint8 as a decoder yields it (PIL convert('RGB') + resize,
+ * extract_rg_embeddings.py:260-261); the image value is byte / 255.0, which is what the reference's
+ * ToTensor -> Normalize -> de-normalise -> clip round trip (:263-276) hands create_region_graph up to float32
+ * rounding.  All moments are integers, so the features are exact up to the final fp64 divisions.
+ * node_bbox (from cm_rag_build) selects the region-parallel kernel (one warp per region over its bounding box);
+ * node_bbox == NULL selects the pixel-parallel tile kernel, which requires label_cap > 0 and
+ * (h / 4 or h / 8 rows) * w <= 66051 pixels per CTA (CM_ERR_ARG otherwise). */
+int cm_node_features_u8(const uint8_t* image_u8, const int32_t* labels, const uint8_t* canny, int batch, int h,
+                        int w, int label_cap, const int32_t* node_ptr, const int32_t* node_label,
+                        const int32_t* node_bbox, float norm_side, float* x, int node_cap, void* stream);
+
+/* Label maps arrive from the host as int16 when they fit (SLIC with n_segments=500 yields < 600 labels; the
+ * reference holds them as int64, extract_rg_embeddings.py:144): widen n labels to the int32 the kernels read.
+ * Both buffers 16-byte aligned. */
+int cm_labels_widen_i16(const int16_t* labels16, int64_t n, int32_t* labels32, void* stream);
+
 /* A4: Gaussian-kernel edge weights (extract_rg_embeddings.py:227-235), one per directed CSR entry,
  * float32 arithmetic.  n_nodes_dev points at the device-side node count (node_ptr + B). */
 int cm_edge_weights(const float* x, const int32_t* csr_row_ptr, const int32_t* csr_col,

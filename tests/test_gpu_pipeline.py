@@ -160,3 +160,32 @@ def test_host_pipeline_graph_replay_equals_eager(models):
         out = eager.run(d.images, d.labels, d.canny, d.gt)
         assert torch.equal(got[j][0], out["mask_out"].cpu())
         assert torch.equal(got[j][1], out["per_image"].cpu())
+
+
+def test_lanes_and_decoded_inputs_equal_float_path(models):
+    """Two lanes (disjoint scratch, own streams, captured steps) fed uint8 images + int16 label maps return what one
+    eager pipeline returns for the same values as float32 images + int32 labels: metrics to 1e-6, logits to 1e-3
+    (the two feature kernels agree to ~1e-7; the fp16 tensor-core operands of the dense layers turn a last-bit
+    feature difference into ~1e-4 on logits of magnitude 4 -- the stated tolerance is 1e-2)."""
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, HostPipeline
+    gnn, det, kg, _, _ = models
+    B = 4
+    dev = torch.device("cuda")
+    pipes = [EvalPipeline(gnn, det, kg, label_cap=544, lane=k) for k in range(2)]
+    hp = HostPipeline(pipes, B, 256, 256, dev, slots=4, use_graph=True, image_dtype=torch.uint8, label_dtype=torch.int16)
+    batches = [synth.make_batch(90 + 5 * j, B, seed=1234).as_decoded() for j in range(6)]
+    pinned = [tuple(t.pin_memory() for t in (b.images, b.labels, b.canny, b.gt)) for b in batches]
+    slots = [hp.submit(j, *hb) for j, hb in enumerate(pinned[:4])]       # four batches in flight on two lanes
+    hp.synchronize()
+    got = [(st.h_mask_out.clone(), st.h_per_image.clone()) for st in slots]
+    for j in (4, 5):                                                      # slot reuse
+        st = hp.submit(j, *pinned[j])
+        st.ev_done.synchronize()
+        got.append((st.h_mask_out.clone(), st.h_per_image.clone()))
+    eager = EvalPipeline(gnn, det, kg, label_cap=544, lane=7)
+    for j, b in enumerate(batches):
+        d = b.as_float().to("cuda")
+        out = eager.run(d.images, d.labels, d.canny, d.gt)
+        assert (got[j][0] - out["mask_out"].cpu()).abs().max() <= 1e-3
+        pi = out["per_image"].cpu()
+        assert (got[j][1] - pi).abs().max() <= 1e-6

@@ -151,3 +151,62 @@ def test_feature_kernels_agree():
     assert float((x_tile - x_bbox).abs().max()) <= 1e-6
     g3 = build_region_graphs(b.images, b.labels, b.canny, label_cap=544)
     assert torch.equal(g3.x[:n], x_tile)
+
+
+@pytest.mark.parametrize("kernel", ["auto", "tile"])
+def test_uint8_images_match_oracle_exactly(kernel):
+    """Decoder-form inputs (uint8 RGB, int16 labels): the integer-moment feature kernel against the oracle run on
+    byte/255.0 in float64.  The moments are exact integers, so the only difference left is the final float32
+    rounding of an fp64 value that differs from numpy's in the last few ulps: tolerance 2e-7 (vs 1e-5 for float images)."""
+    from camouflage_multimodal_b200.region_graph import build_region_graphs
+    b = synth.make_batch(20, 3, seed=1234, n_regions=[310, 481, 530]).as_decoded()
+    assert b.images.dtype == torch.uint8 and b.labels.dtype == torch.int16
+    d = b.to("cuda")
+    g = build_region_graphs(d.images, d.labels.to(torch.int32), d.canny, label_cap=544, feature_kernel=kernel)
+    n, e = g.counts()
+    assert n == int(b.n_regions.sum())
+    ptr = g.node_ptr.cpu().numpy()
+    for i in range(3):
+        x, ei, w, _ = _oracle_graph(b.images[i].numpy().astype(np.float64) / 255.0, b.labels[i].numpy(), b.canny[i].numpy())
+        got = g.x[ptr[i]:ptr[i + 1]].cpu().numpy()
+        np.testing.assert_allclose(got, x, rtol=0, atol=2e-7)
+        # counts-only features are bit-exact
+        assert np.array_equal(got[:, 10], x[:, 10]) and np.array_equal(got[:, 13], x[:, 13]) and np.array_equal(got[:, 11], x[:, 11])
+
+
+@pytest.mark.parametrize("kernel", ["auto", "tile"])
+def test_uint8_odd_shapes_and_float_agreement(kernel):
+    """Non-multiple-of-32 width, labels with gaps / zeros / negatives, a constant-colour image (zero variance must
+    come out as exactly 0) -- uint8 path vs the float path on the same values."""
+    from camouflage_multimodal_b200.region_graph import build_region_graphs
+    g0 = torch.Generator().manual_seed(5)
+    H, W = 72, 100
+    img = torch.randint(0, 256, (2, H, W, 3), generator=g0, dtype=torch.uint8)
+    img[1] = 77
+    lab = (torch.arange(H)[:, None] // 9 * 12 + torch.arange(W)[None, :] // 9).to(torch.int32)[None].repeat(2, 1, 1) * 3
+    lab[0, :5, :7] = -4
+    lab[1, 30:40, 50:] = 0
+    can = (torch.rand((2, H, W), generator=g0) < 0.1).to(torch.uint8)
+    cap = int(lab.max()) + 1
+    gu = build_region_graphs(img.cuda(), lab.cuda(), can.cuda(), label_cap=cap, feature_kernel=kernel)
+    xu = gu.x[: gu.counts()[0]].cpu().numpy()
+    gf = build_region_graphs((img.float() / 255.0).cuda(), lab.cuda(), can.cuda(), label_cap=cap)
+    xf = gf.x[: gf.counts()[0]].cpu().numpy()
+    assert xu.shape == xf.shape and xu.shape[0] > 50
+    np.testing.assert_allclose(xu, xf, rtol=0, atol=1e-6)
+    n1 = int(gu.node_ptr[1])
+    assert (xu[n1:, 3:6] == 0).all() and (xu[n1:, 7] == 0).all() and (xu[n1:, 14] == 0).all() and (xu[n1:, 12] == 0).all()
+    for i in range(2):
+        x, _, _, _ = _oracle_graph(img[i].numpy().astype(np.float64) / 255.0, lab[i].numpy(), can[i].numpy())
+        a, z = int(gu.node_ptr[i]), int(gu.node_ptr[i + 1])
+        np.testing.assert_allclose(xu[a:z], x, rtol=0, atol=2e-7)
+
+
+def test_labels_widen_i16():
+    from camouflage_multimodal_b200 import _lib
+    lib = _lib.load()
+    for n in (0, 5, 8, 4099, 256 * 256 * 3 + 3):
+        src = torch.randint(-32768, 32767, (max(n, 1),), dtype=torch.int16, device="cuda")[:n]
+        dst = torch.full((n + 8,), 123456, dtype=torch.int32, device="cuda")
+        _lib.check(lib.cm_labels_widen_i16(_lib.ptr(src) if n else _lib.ptr(dst), n, _lib.ptr(dst), _lib.stream_ptr()), "widen")
+        assert torch.equal(dst[:n], src.to(torch.int32)) and (dst[n:] == 123456).all()
