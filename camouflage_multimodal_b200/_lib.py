@@ -33,6 +33,20 @@ class GnnParams(C.Structure):
     ]
 
 
+class GnnDropout(C.Structure):
+    _fields_ = [("keep", _fp * 7), ("p_conv", C.c_float), ("p_fc", C.c_float)]
+
+
+class GnnGrads(C.Structure):
+    _fields_ = [
+        ("conv1_lin_weight", _fp), ("conv1_att_src", _fp), ("conv1_att_dst", _fp), ("conv1_bias", _fp),
+        ("conv_lin_weight", _fp * 3), ("conv_bias", _fp * 3),
+        ("bn_weight", _fp * 4), ("bn_bias", _fp * 4),
+        ("fc_shared_weight", _fp), ("fc_shared_bias", _fp),
+        ("head1_weight", _fp * 3), ("head1_bias", _fp * 3), ("head2_weight", _fp * 3), ("head2_bias", _fp * 3),
+    ]
+
+
 class FusionParams(C.Structure):
     _fields_ = [
         ("rg_dim", C.c_int), ("kg_dim", C.c_int), ("hidden", C.c_int), ("heads", C.c_int),
@@ -71,6 +85,11 @@ SIGNATURES = {
     "cm_gnn_workspace_bytes": (_sz, [C.POINTER(GnnParams), _i]),
     "cm_gnn_forward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _fp, _i, _fp, _sz,
                             _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "cm_gnn_train_workspace_bytes": (_sz, [C.POINTER(GnnParams), _i, _i]),
+    "cm_gnn_train_forward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _i, _i, C.POINTER(GnnDropout), _fp, _sz,
+                                  _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "cm_gnn_backward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _i, _i, C.POINTER(GnnDropout), _fp, _sz,
+                             _fp, _fp, _fp, _fp, C.POINTER(GnnGrads), _fp]),
     "cm_fusion_workspace_bytes": (_sz, [C.POINTER(FusionParams), _i, _i, _i]),
     "cm_fusion_folded_bytes": (_sz, [C.POINTER(FusionParams), _i]),
     "cm_fusion_fold": (_i, [C.POINTER(FusionParams), _fp, _i, _fp, _sz, _fp]),

@@ -1,0 +1,154 @@
+// Strided fp32 GEMM with deterministic split-K, and column sums with fp64 partials: the dense building blocks of
+// the training-mode passes (see train_common.cuh).
+#include "train_common.cuh"
+
+namespace cm {
+
+constexpr int GB = 64, GK = 16;
+
+template <bool AKC, bool BKC>
+__global__ void __launch_bounds__(256) sgemm_kernel(const float* __restrict__ A, long sam, long sak, const float* __restrict__ B, long sbk,
+                                                    long sbn, float* __restrict__ C, long ldc, int M, int N, int K, int k_chunk,
+                                                    long split_stride, const float* __restrict__ bias, int relu,
+                                                    const uint8_t* __restrict__ keep, float keep_scale, float alpha, int accumulate) {
+    __shared__ float As[GK][GB + 4], Bs[GK][GB + 4];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int m0 = blockIdx.y * GB, n0 = blockIdx.x * GB;
+    const int kb = blockIdx.z * k_chunk, ke = min(K, kb + k_chunk);
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int k0 = kb; k0 < ke; k0 += GK) {
+        if (AKC) {
+            const int m = tid >> 2, kk = (tid & 3) * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int k = k0 + kk + q;
+                As[kk + q][m] = (m0 + m < M && k < ke) ? A[(long)(m0 + m) * sam + (long)k * sak] : 0.f;
+            }
+        } else {
+            const int kk = tid >> 4, m = (tid & 15) * 4, k = k0 + kk;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) As[kk][m + q] = (m0 + m + q < M && k < ke) ? A[(long)(m0 + m + q) * sam + (long)k * sak] : 0.f;
+        }
+        if (BKC) {
+            const int n = tid >> 2, kk = (tid & 3) * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int k = k0 + kk + q;
+                Bs[kk + q][n] = (n0 + n < N && k < ke) ? B[(long)k * sbk + (long)(n0 + n) * sbn] : 0.f;
+            }
+        } else {
+            const int kk = tid >> 4, n = (tid & 15) * 4, k = k0 + kk;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) Bs[kk][n + q] = (n0 + n + q < N && k < ke) ? B[(long)k * sbk + (long)(n0 + n + q) * sbn] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < GK; ++kk) {
+            const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    float* Cz = C + (long)blockIdx.z * split_stride;
+    const bool final = split_stride == 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int m = m0 + ty * 4 + i;
+        if (m >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int n = n0 + tx * 4 + j;
+            if (n >= N) continue;
+            float v = acc[i][j];
+            if (final) {
+                v *= alpha;
+                if (bias) v += bias[n];
+                if (relu) v = fmaxf(v, 0.f);
+                if (keep) v = keep[(long)m * N + n] ? v * keep_scale : 0.f;
+                if (accumulate) v += Cz[(long)m * ldc + n];
+            }
+            Cz[(long)m * ldc + n] = v;
+        }
+    }
+}
+
+__global__ void splitk_reduce_kernel(const float* __restrict__ part, int splits, int M, int N, float* __restrict__ C, long ldc,
+                                     const float* __restrict__ bias, int relu, float alpha, int accumulate) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long)M * N) return;
+    float s = 0.f;
+    for (int z = 0; z < splits; ++z) s += part[(long)z * M * N + i];
+    const int m = (int)(i / N), n = (int)(i - (long)m * N);
+    s *= alpha;
+    if (bias) s += bias[n];
+    if (relu) s = fmaxf(s, 0.f);
+    float* c = C + (long)m * ldc + n;
+    *c = accumulate ? *c + s : s;
+}
+
+int launch_gemm(const Gemm& g, cudaStream_t st, const char* name) {
+    if (g.M <= 0 || g.N <= 0) return CM_OK;
+    const int splits = g.splits > 1 && g.part ? g.splits : 1;
+    const int k_chunk = splits > 1 ? ((g.K + splits - 1) / splits + GK - 1) / GK * GK : (g.K > 0 ? g.K : 1);
+    dim3 grid(ceil_div(g.N, GB), ceil_div(g.M, GB), splits);
+    float* out = splits > 1 ? g.part : g.C;
+    const long ldc = splits > 1 ? g.N : g.ldc, ss = splits > 1 ? (long)g.M * g.N : 0;
+    {
+        CM_TIMED(name, st);
+#define CM_SGEMM(a, b)                                                                                                              \
+    sgemm_kernel<a, b><<<grid, 256, 0, st>>>(g.A, g.sam, g.sak, g.B, g.sbk, g.sbn, out, ldc, g.M, g.N, g.K, k_chunk, ss, g.bias, g.relu, \
+                                             g.keep, g.keep_scale, g.alpha, splits > 1 ? 0 : g.accumulate)
+        if (g.a_k_contig && g.b_k_contig) CM_SGEMM(true, true);
+        else if (g.a_k_contig) CM_SGEMM(true, false);
+        else if (g.b_k_contig) CM_SGEMM(false, true);
+        else CM_SGEMM(false, false);
+#undef CM_SGEMM
+    }
+    if (splits > 1) {
+        CM_TIMED("splitk_reduce", st);
+        splitk_reduce_kernel<<<ceil_div((long)g.M * g.N, 256), 256, 0, st>>>(g.part, splits, g.M, g.N, g.C, g.ldc, g.bias, g.relu, g.alpha,
+                                                                            g.accumulate);
+    }
+    return post_launch(name);
+}
+
+// ---------------------------------------------------------------- column sums
+constexpr int CS_ROWS = 64;   // rows per CTA
+int col_parts(int rows) { return rows > 0 ? ceil_div(rows, CS_ROWS) : 1; }
+
+__global__ void colsum_part_kernel(const float* __restrict__ a, int lda, int rows, int cols, double* __restrict__ part) {
+    const int c = blockIdx.y * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    const int r0 = blockIdx.x * CS_ROWS, r1 = min(rows, r0 + CS_ROWS);
+    double s = 0.0;
+    for (int r = r0; r < r1; ++r) s += (double)a[(long)r * lda + c];
+    part[(long)blockIdx.x * cols + c] = s;
+}
+__global__ void colsum_final_kernel(const double* __restrict__ part, int parts, int cols, float* __restrict__ out, int accumulate) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    double s = 0.0;
+    for (int p = 0; p < parts; ++p) s += part[(long)p * cols + c];
+    out[c] = accumulate ? out[c] + (float)s : (float)s;
+}
+
+int launch_colsum(const float* a, int lda, int rows, int cols, double* part, float* out, int accumulate, cudaStream_t st) {
+    const int parts = col_parts(rows);
+    {
+        CM_TIMED("colsum", st);
+        if (rows > 0) colsum_part_kernel<<<dim3(parts, ceil_div(cols, 128)), 128, 0, st>>>(a, lda, rows, cols, part);
+        colsum_final_kernel<<<ceil_div(cols, 128), 128, 0, st>>>(part, rows > 0 ? parts : 0, cols, out, accumulate);
+    }
+    return post_launch("colsum");
+}
+
+}  // namespace cm

@@ -207,7 +207,9 @@ class _GCNConvParams(nn.Module):
 class RegionGraphGNN(nn.Module):
     """``RegionGraphGNN(in_channels=15, hidden_channels=128, num_classes=2)`` (extract_rg_embeddings.py:27-135).
 
-    Inference (eval mode) runs on the sm_100a kernels through ``cm_gnn_forward``; there is no eager path.
+    Inference (eval mode) runs on the sm_100a kernels through ``cm_gnn_forward``; under ``model.train()``,
+    ``forward`` runs ``cm_gnn_train_forward`` and is differentiable through ``cm_gnn_backward`` (training.py).
+    There is no eager path.
     """
 
     def __init__(self, in_channels=15, hidden_channels=128, num_classes=2):
@@ -361,7 +363,13 @@ class RegionGraphGNN(nn.Module):
                 node_ptr = torch.tensor([0, data.x.shape[0]], dtype=torch.int32, device=data.x.device)
         return self.run(data.x, row_ptr, col, w, self_w, None, node_ptr, n_graphs, want=want)
 
+    # F.dropout probabilities of the reference's forward (extract_rg_embeddings.py:61-85); training mode only
+    p_conv, p_fc = 0.3, 0.2
+
     def forward(self, data):
+        if self.training:   # model.train(): batch-statistics BatchNorm, dropout, autograd through cm_gnn_backward
+            from .training import gnn_train_forward
+            return gnn_train_forward(self, data)[:3]
         r = self._run_data(data, ("mask_out", "instance_out", "edge_out"))
         return r["mask_out"], r["instance_out"], r["edge_out"]
 

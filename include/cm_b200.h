@@ -170,6 +170,41 @@ int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const float* x, c
                    float* instance_out, float* edge_out, float* mask_prob, float* graph_emb, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Training-mode RegionGraphGNN: forward under model.train() and the backward pass
+ * (extract_rg_embeddings.py:54-90; the step is models/region_graph/train.py:345-357).
+ * BatchNorm uses the statistics of ALL nodes in the batch (Batch.from_data_list, train.py:231) and returns them
+ * so the caller can update running_mean / running_var; dropout (F.dropout p=0.3 after bn1..bn3, p=0.2 after
+ * fc_shared and the three head hidden layers) is applied through caller-supplied keep masks -- PyTorch's Philox
+ * stream cannot be reproduced, so the masks are data (NULL = dropout off, which is what gradient parity checks use).
+ * The CSR must be structurally symmetric (every region adjacency is); a missing reverse edge sets
+ * CM_STATUS_EDGE_OVERFLOW in *status.  n_nodes / n_edges are host-side exact counts.
+ * The workspace carries the saved activations from cm_gnn_train_forward to cm_gnn_backward.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct cm_gnn_dropout {
+    const uint8_t* keep[7]; /* [N,H] after bn1, bn2, bn3, fc_shared; [N,H/2] mask, instance, edge head hidden; NULL = keep all */
+    float p_conv, p_fc;     /* 0.3, 0.2 */
+} cm_gnn_dropout;
+typedef struct cm_gnn_grads { /* one buffer per trainable tensor of cm_gnn_params, same shapes; overwritten */
+    float *conv1_lin_weight, *conv1_att_src, *conv1_att_dst, *conv1_bias;
+    float *conv_lin_weight[3], *conv_bias[3];
+    float *bn_weight[4], *bn_bias[4];
+    float *fc_shared_weight, *fc_shared_bias;
+    float *head1_weight[3], *head1_bias[3], *head2_weight[3], *head2_bias[3];
+} cm_gnn_grads;
+size_t cm_gnn_train_workspace_bytes(const cm_gnn_params* p, int n_nodes, int n_edges);
+/* Outputs: mask_out / instance_out [N,num_classes], edge_out [N,1], node_emb [N,hidden] (optional; the shared
+ * embedding after dropout), bn_batch_mean / bn_batch_var [4,hidden] (optional; biased variance). */
+int cm_gnn_train_forward(const cm_gnn_params* p, const float* x, const int32_t* csr_row_ptr, const int32_t* csr_col,
+                         const float* csr_w, const float* self_w, int n_nodes, int n_edges, const cm_gnn_dropout* drop,
+                         void* workspace, size_t workspace_bytes, float* mask_out, float* instance_out, float* edge_out,
+                         float* node_emb, float* bn_batch_mean, float* bn_batch_var, uint32_t* status, void* stream);
+/* d_* are the loss gradients with respect to the forward outputs (NULL = zero). */
+int cm_gnn_backward(const cm_gnn_params* p, const float* x, const int32_t* csr_row_ptr, const int32_t* csr_col,
+                    const float* csr_w, const float* self_w, int n_nodes, int n_edges, const cm_gnn_dropout* drop,
+                    void* workspace, size_t workspace_bytes, const float* d_mask_out, const float* d_instance_out,
+                    const float* d_edge_out, const float* d_node_emb, const cm_gnn_grads* grads, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * A10-A12: CrossAttentionFusion / LateFusion + the four detector heads
  * (models/multimodal/fusion_model.py:16-246), eval mode.  Raw parameters = reference state dict.
  * ------------------------------------------------------------------------------------------------ */

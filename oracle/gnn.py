@@ -130,8 +130,10 @@ def _bn_train(x, p, name, eps=1e-5):
     return (x - mu) / torch.sqrt(var + eps) * p[f"{name}.weight"] + p[f"{name}.bias"]
 
 
-def rg_gnn_forward(p, x, edge_index, edge_attr, batch=None, training_bn=False, heads=4, hidden=128):
-    """All outputs of ``RegionGraphGNN`` from a state dict ``p`` (dropout off).
+def rg_gnn_forward(p, x, edge_index, edge_attr, batch=None, training_bn=False, heads=4, hidden=128, drop=None):
+    """All outputs of ``RegionGraphGNN`` from a state dict ``p``.  ``drop`` (training only): list of 7 keep masks
+    (or None) applied as ``F.dropout`` does -- ``h * keep / (1 - p)`` with p = 0.3 after bn1..bn3 (:61,66,71) and
+    p = 0.2 after fc_shared and the three head hidden layers (:79-90); ``None`` = dropout off.
 
     Follows extract_rg_embeddings.py:54-135: GAT(no edge weights)+BN+ReLU, 3x GCN(edge weights)+BN+ReLU,
     fc_shared+ReLU -> node embeddings; three 2-layer heads; graph embedding = mean pool.
@@ -141,14 +143,22 @@ def rg_gnn_forward(p, x, edge_index, edge_attr, batch=None, training_bn=False, h
     ew = edge_attr.reshape(-1) if edge_attr is not None and edge_attr.numel() > 0 else None   # :56
     lin_w = p["conv1.lin.weight"] if "conv1.lin.weight" in p else p["conv1.lin_src.weight"]
     h = gat_conv(x, edge_index, lin_w, p["conv1.att_src"], p["conv1.att_dst"], p["conv1.bias"], heads, hidden)
-    h = F.relu(bn(h, p, "bn1"))
+    def dr(t, site, pr):
+        if drop is None or drop[site] is None:
+            return t
+        return t * drop[site].to(t.dtype) / (1.0 - pr)
+
+    h = dr(F.relu(bn(h, p, "bn1")), 0, 0.3)
     for k in (2, 3, 4):
         h = gcn_conv(h, edge_index, ew, p[f"conv{k}.lin.weight"], p[f"conv{k}.bias"])
         h = F.relu(bn(h, p, f"bn{k}"))
-    emb = F.relu(F.linear(h, p["fc_shared.weight"], p["fc_shared.bias"]))                       # :120
+        if k < 4:
+            h = dr(h, k - 1, 0.3)
+    emb = dr(F.relu(F.linear(h, p["fc_shared.weight"], p["fc_shared.bias"])), 3, 0.2)           # :120
 
     def head(n):
         t = F.relu(F.linear(emb, p[f"fc_{n}_1.weight"], p[f"fc_{n}_1.bias"]))
+        t = dr(t, {"mask": 4, "instance": 5, "edge": 6}[n], 0.2)
         return F.linear(t, p[f"fc_{n}_2.weight"], p[f"fc_{n}_2.bias"])
 
     if batch is None:
