@@ -63,6 +63,21 @@ class FusionParams(C.Structure):
     ]
 
 
+class FusionDropout(C.Structure):
+    _fields_ = [("keep", _fp * 9), ("p", C.c_float)]
+
+
+FUSION_GRAD_FIELDS = ["rg_proj_w", "rg_proj_b", "kg_proj_w", "kg_proj_b", "r2k_in_w", "r2k_in_b", "r2k_out_w", "r2k_out_b",
+                      "k2r_in_w", "k2r_in_b", "k2r_out_w", "k2r_out_b", "ln_rg_w", "ln_rg_b", "ln_kg_w", "ln_kg_b",
+                      "ffn_rg_w1", "ffn_rg_b1", "ffn_rg_w2", "ffn_rg_b2", "ffn_kg_w1", "ffn_kg_b1", "ffn_kg_w2", "ffn_kg_b2",
+                      "fl_w1", "fl_b1", "fl_w2", "fl_b2"]
+
+
+class FusionGrads(C.Structure):
+    _fields_ = [(n, _fp) for n in FUSION_GRAD_FIELDS] + [("head_w1", _fp * 4), ("head_b1", _fp * 4), ("head_w2", _fp * 4),
+                                                         ("head_b2", _fp * 4)]
+
+
 # name -> (restype, argtypes); the list is also what tests/test_abi.py checks against include/cm_b200.h
 _i, _sz, _f, _i64 = C.c_int, C.c_size_t, C.c_float, C.c_int64
 SIGNATURES = {
@@ -90,6 +105,11 @@ SIGNATURES = {
                                   _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_gnn_backward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _i, _i, C.POINTER(GnnDropout), _fp, _sz,
                              _fp, _fp, _fp, _fp, C.POINTER(GnnGrads), _fp]),
+    "cm_fusion_train_workspace_bytes": (_sz, [C.POINTER(FusionParams), _i, _i, _i]),
+    "cm_fusion_train_forward": (_i, [C.POINTER(FusionParams), _fp, _fp, _i, _i, _fp, _i, C.POINTER(FusionDropout), _fp, _sz,
+                                     _fp, _fp, _fp, _fp, _fp, _fp]),
+    "cm_fusion_backward": (_i, [C.POINTER(FusionParams), _fp, _fp, _i, _i, _fp, _i, C.POINTER(FusionDropout), _fp, _sz,
+                                _fp, _fp, _fp, _fp, _fp, C.POINTER(FusionGrads), _fp, _fp, _fp]),
     "cm_fusion_workspace_bytes": (_sz, [C.POINTER(FusionParams), _i, _i, _i]),
     "cm_fusion_folded_bytes": (_sz, [C.POINTER(FusionParams), _i]),
     "cm_fusion_fold": (_i, [C.POINTER(FusionParams), _fp, _i, _fp, _sz, _fp]),

@@ -151,4 +151,83 @@ int launch_colsum(const float* a, int lda, int rows, int cols, double* part, flo
     return post_launch("colsum");
 }
 
+// ---------------------------------------------------------------- elementwise + LayerNorm
+__global__ void tc_add_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, long count) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) out[i] = a[i] + (b ? b[i] : 0.f);
+}
+int launch_add(const float* a, const float* b, float* out, long count, cudaStream_t st) {
+    if (count <= 0) return CM_OK;
+    CM_TIMED("train_elementwise", st);
+    tc_add_kernel<<<ceil_div(count, 256), 256, 0, st>>>(a, b, out, count);
+    return post_launch("add");
+}
+__global__ void tc_relu_drop_bwd_kernel(const float* __restrict__ act, float scale, long count, float* __restrict__ d) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) d[i] = act[i] > 0.f ? d[i] * scale : 0.f;
+}
+int launch_relu_drop_bwd(const float* act, float scale, long count, float* d, cudaStream_t st) {
+    if (count <= 0) return CM_OK;
+    CM_TIMED("train_elementwise", st);
+    tc_relu_drop_bwd_kernel<<<ceil_div(count, 256), 256, 0, st>>>(act, scale, count, d);
+    return post_launch("relu_drop_bwd");
+}
+
+__global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, int rows, int dim, float* __restrict__ y,
+                                                     float* __restrict__ stats) {
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= rows) return;
+    const float* xr = x + (size_t)r * dim;
+    float s = 0.f;
+    for (int c = lane; c < dim; c += 32) s += xr[c];
+    const float mean = warp_sum(s) / dim;
+    float q = 0.f;
+    for (int c = lane; c < dim; c += 32) {
+        const float d = xr[c] - mean;
+        q = fmaf(d, d, q);
+    }
+    const float rstd = rsqrtf(warp_sum(q) / dim + 1e-5f);
+    for (int c = lane; c < dim; c += 32) y[(size_t)r * dim + c] = (xr[c] - mean) * rstd * gamma[c] + beta[c];
+    if (lane == 0) {
+        stats[2 * r] = mean;
+        stats[2 * r + 1] = rstd;
+    }
+}
+int launch_ln_fwd(const float* x, const float* gamma, const float* beta, int rows, int dim, float* y, float* stats, cudaStream_t st) {
+    if (rows <= 0) return CM_OK;
+    CM_TIMED("train_layernorm", st);
+    ln_fwd_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(x, gamma, beta, rows, dim, y, stats);
+    return post_launch("ln_fwd");
+}
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x, const float* __restrict__ stats,
+                                                     const float* __restrict__ gamma, const float* __restrict__ dy, int rows, int dim,
+                                                     float* __restrict__ dx, float* __restrict__ prod) {
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= rows) return;
+    const float mean = stats[2 * r], rstd = stats[2 * r + 1];
+    const float* xr = x + (size_t)r * dim;
+    const float* dr = dy + (size_t)r * dim;
+    float a = 0.f, b = 0.f;
+    for (int c = lane; c < dim; c += 32) {
+        const float xh = (xr[c] - mean) * rstd, g = dr[c] * gamma[c];
+        a += g;
+        b = fmaf(g, xh, b);
+    }
+    a = warp_sum(a) / dim;
+    b = warp_sum(b) / dim;
+    for (int c = lane; c < dim; c += 32) {
+        const float xh = (xr[c] - mean) * rstd, d = dr[c];
+        prod[(size_t)r * dim + c] = d * xh;
+        dx[(size_t)r * dim + c] = rstd * (d * gamma[c] - a - xh * b);
+    }
+}
+int launch_ln_bwd(const float* x, const float* stats, const float* gamma, const float* dy, int rows, int dim, float* dx, float* prod,
+                  cudaStream_t st) {
+    if (rows <= 0) return CM_OK;
+    CM_TIMED("train_layernorm", st);
+    ln_bwd_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(x, stats, gamma, dy, rows, dim, dx, prod);
+    return post_launch("ln_bwd");
+}
+
 }  // namespace cm

@@ -61,4 +61,14 @@ inline Gemm gemm_tn(const float* dY, int ldy, const float* X, int ldx, float* dW
 int col_parts(int rows);
 int launch_colsum(const float* a, int lda, int rows, int cols, double* part, float* out, int accumulate, cudaStream_t st);
 
+// elementwise helpers
+int launch_add(const float* a, const float* b, float* out, long count, cudaStream_t st);                 // out = a + b (b may be NULL)
+int launch_relu_drop_bwd(const float* act, float scale, long count, float* d, cudaStream_t st);           // d = act > 0 ? d*scale : 0
+
+// LayerNorm over `dim` columns (eps 1e-5, biased variance), one warp per row.  stats [rows,2] = mean, rstd.
+int launch_ln_fwd(const float* x, const float* gamma, const float* beta, int rows, int dim, float* y, float* stats, cudaStream_t st);
+// dx from dy; writes prod = dy * xhat (for dgamma = colsum(prod), dbeta = colsum(dy))
+int launch_ln_bwd(const float* x, const float* stats, const float* gamma, const float* dy, int rows, int dim, float* dx, float* prod,
+                  cudaStream_t st);
+
 }  // namespace cm

@@ -251,6 +251,7 @@ class MultimodalCamouflageDetector(nn.Module):
             final_dim = hidden_dim // 2
         else:
             raise ValueError(f"Unknown fusion_type: {fusion_type}")
+        self.dropout_p = float(dropout)
         self.mask_head = _head(final_dim, num_classes, dropout)
         self.instance_head = _head(final_dim, num_classes, dropout)
         self.edge_head = _head(final_dim, 1, dropout)
@@ -262,12 +263,24 @@ class MultimodalCamouflageDetector(nn.Module):
         """Ragged batch entry: all images' node embeddings as one ``[M, rg_dim]`` block, segments in ``node_ptr``
         (int32, device), ``kg`` ``[1 or n_graphs, K, kg_dim]``.  Returns the dict of ``cm_fusion_forward`` outputs."""
         if self.training:
-            raise NotImplementedError("the B200 fusion path is inference-only for now: call .eval()")
+            return self._train_forward(rg_rows, node_ptr, n_graphs, kg, return_attention)
         return self._runner.run(rg_rows, node_ptr, n_graphs, kg, want_attention=return_attention, want_heads=True, out=out)
+
+    def _train_forward(self, rg_rows, node_ptr, n_graphs, kg, return_attention):
+        """model.train(): dropout + autograd through ``cm_fusion_train_forward`` / ``cm_fusion_backward`` (training.py)."""
+        if self.fusion_type != "cross_attention":
+            raise NotImplementedError("training on the B200 path covers fusion_type='cross_attention' (the YAML default)")
+        if return_attention:
+            raise NotImplementedError("attention maps are an inference output here: call .eval() to get them")
+        from .training import fusion_train_forward
+        fused, mask, inst, edge, score = fusion_train_forward(self, rg_rows, node_ptr, n_graphs, kg)
+        return {"fused": fused, "mask_out": mask, "instance_out": inst, "edge_out": edge, "score_out": score}
 
     def forward(self, rg_embeddings, kg_embeddings, return_attention=False):
         if self.training:
-            raise NotImplementedError("the B200 fusion path is inference-only for now: call .eval()")
+            rows, node_ptr, B, N, kg = _dense_inputs(rg_embeddings, kg_embeddings)
+            res = self._train_forward(rows, node_ptr, B, kg, return_attention)
+            return (res["mask_out"], res["instance_out"], res["edge_out"], res["score_out"])
         attn = None
         if self.fusion_type == "cross_attention":
             rows, node_ptr, B, N, kg = _dense_inputs(rg_embeddings, kg_embeddings)

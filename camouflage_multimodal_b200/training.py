@@ -136,3 +136,112 @@ def update_bn_running_stats(model, batch_mean, batch_var, n):
             bn.running_mean.mul_(1 - m).add_(batch_mean[k], alpha=m)
             bn.running_var.mul_(1 - m).add_(batch_var[k] * (n / max(n - 1, 1)), alpha=m)
             bn.num_batches_tracked += 1
+
+
+# ------------------------------------------------------------------------------------------------ fusion
+def _fusion_param_list(det):
+    """Trainable tensors of a cross-attention ``MultimodalCamouflageDetector`` in ``cm_fusion_grads`` field order;
+    ``None`` where the projection is ``nn.Identity``."""
+    import torch.nn as nn
+    f = det.fusion
+    lin = lambda m: (m.weight, m.bias) if isinstance(m, nn.Linear) else (None, None)
+    out = [*lin(f.rg_proj), *lin(f.kg_proj)]
+    for m in (f.cross_attn_rg2kg, f.cross_attn_kg2rg):
+        out += [m.in_proj_weight, m.in_proj_bias, m.out_proj.weight, m.out_proj.bias]
+    out += [f.ln_rg.weight, f.ln_rg.bias, f.ln_kg.weight, f.ln_kg.bias]
+    for seq in (f.ffn_rg, f.ffn_kg, f.fusion_layer):
+        out += [seq[0].weight, seq[0].bias, seq[3].weight, seq[3].bias]
+    heads = (det.mask_head, det.instance_head, det.edge_head, det.score_head)
+    out += [h[0].weight for h in heads] + [h[0].bias for h in heads] + [h[3].weight for h in heads] + [h[3].bias for h in heads]
+    return out
+
+
+def _fusion_grads_struct(grads):
+    g = _lib.FusionGrads()
+    it = iter(grads)
+    for name in _lib.FUSION_GRAD_FIELDS:
+        t = next(it)
+        setattr(g, name, t.data_ptr() if t is not None else None)
+    for arr in (g.head_w1, g.head_b1, g.head_w2, g.head_b2):
+        for k in range(4):
+            arr[k] = next(it).data_ptr()
+    return g
+
+
+def _fusion_dropout_struct(masks, p):
+    d = _lib.FusionDropout()
+    for k in range(9):
+        d.keep[k] = masks[k].data_ptr() if masks is not None and masks[k] is not None else None
+    d.p = float(p)
+    return d
+
+
+class FusionTrainFunction(torch.autograd.Function):
+    """``(fused, mask_out, instance_out, edge_out, score_out) = f(det, rg_rows, node_ptr, G, kg, masks, *params)``;
+    differentiable in ``rg_rows``, ``kg`` and the parameters."""
+
+    @staticmethod
+    def forward(ctx, det, rg_rows, node_ptr, n_graphs, kg, masks, *params):
+        lib = _lib.load()
+        _lib.require_cuda(rg_rows, "rg_embeddings")
+        _lib.require_cuda(kg, "kg_embeddings")
+        dev = rg_rows.device
+        rg_rows, kg = _lib.f32c(rg_rows), _lib.f32c(kg)
+        G, M, K = int(n_graphs), rg_rows.shape[0], kg.shape[1]
+        if kg.shape[0] != G:
+            raise RuntimeError(f"training step needs one KG copy per image: kg has {kg.shape[0]} graphs, batch has {G}")
+        s, keep = det._runner.params()
+        drop = _fusion_dropout_struct(masks, det.dropout_p)
+        ws_bytes = lib.cm_fusion_train_workspace_bytes(C.byref(s), G, M, K)
+        if ws_bytes == 0:
+            raise ValueError("cm_fusion_train_workspace_bytes: " + lib.cm_last_error().decode())
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        f32 = dict(dtype=torch.float32, device=dev)
+        c = s.num_classes
+        fused = torch.empty((G, s.hidden), **f32)
+        outs = [torch.empty((G, c), **f32), torch.empty((G, c), **f32), torch.empty((G, 1), **f32), torch.empty((G, 1), **f32)]
+        p = _lib.ptr
+        _lib.check(lib.cm_fusion_train_forward(C.byref(s), p(rg_rows), p(node_ptr), G, M, p(kg), K, C.byref(drop), p(ws), ws_bytes,
+                                               p(fused), p(outs[0]), p(outs[1]), p(outs[2]), p(outs[3]), _lib.stream_ptr(dev)),
+                   "cm_fusion_train_forward")
+        ctx.det, ctx.masks, ctx.dims = det, masks, (G, M, K)
+        ctx.held = (rg_rows, node_ptr, kg, ws, keep, [None if t is None else _lib.f32c(t) for t in params])
+        return (fused, *outs)
+
+    @staticmethod
+    def backward(ctx, d_fused, d_mask, d_inst, d_edge, d_score):
+        lib = _lib.load()
+        det = ctx.det
+        rg_rows, node_ptr, kg, ws, keep, held = ctx.held
+        G, M, K = ctx.dims
+        dev = rg_rows.device
+        s, keep2 = det._runner.params()
+        drop = _fusion_dropout_struct(ctx.masks, det.dropout_p)
+        grads = [None if t is None else torch.empty_like(t) for t in held]
+        g = _fusion_grads_struct(grads)
+        ds = [None if d is None else _lib.f32c(d) for d in (d_fused, d_mask, d_inst, d_edge, d_score)]
+        d_rg = torch.empty_like(rg_rows) if ctx.needs_input_grad[1] else None
+        d_kg = torch.empty_like(kg) if ctx.needs_input_grad[4] else None
+        p = _lib.ptr
+        _lib.check(lib.cm_fusion_backward(C.byref(s), p(rg_rows), p(node_ptr), G, M, p(kg), K, C.byref(drop), p(ws), ws.numel(),
+                                          p(ds[0]), p(ds[1]), p(ds[2]), p(ds[3]), p(ds[4]), C.byref(g), p(d_rg), p(d_kg),
+                                          _lib.stream_ptr(dev)), "cm_fusion_backward")
+        return (None, d_rg, None, None, d_kg, None) + tuple(grads)
+
+
+def fusion_train_forward(det, rg_rows, node_ptr, n_graphs, kg, masks="auto"):
+    """Training-mode detector forward on a ragged batch; returns ``(fused, mask, instance, edge, score)``."""
+    G, M, K = int(n_graphs), rg_rows.shape[0], kg.shape[1]
+    if kg.shape[0] == 1 and G > 1:
+        kg = kg.expand(G, -1, -1)
+    kg = kg.contiguous()
+    p_drop = det.dropout_p
+    if masks == "auto":
+        masks = None
+        if p_drop > 0:
+            D, H = det.fusion.hidden_dim, det.fusion.cross_attn_rg2kg.num_heads
+            dev = rg_rows.device
+            shapes = [(M, H, K), (M, 2 * D), (H, K, M), (G * K, 2 * D), (G, D)] + [(G, D // 2)] * 4
+            masks = [(torch.rand(sh, device=dev) >= p_drop).to(torch.uint8) for sh in shapes]
+    params = _fusion_param_list(det)
+    return FusionTrainFunction.apply(det, rg_rows, node_ptr, G, kg, masks, *params)

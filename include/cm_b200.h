@@ -248,6 +248,41 @@ int cm_fusion_forward(const cm_fusion_params* p, const void* folded, const float
                       void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Training-mode CrossAttentionFusion + the four detector heads: forward under model.train() and the backward
+ * pass (fusion_model.py:75-146, 229-246; the step is models/multimodal/train_multimodal.py:232-275).
+ * Ragged batch as in cm_fusion_forward; kg is [n_graphs, n_kg, kg_dim] -- one copy of the KG rows per image,
+ * which is what the reference's expand() feeds the model, so gradients that reach the KG side sum over images.
+ * Dropout (nn.Dropout / attention dropout, all with the model's `dropout`) through caller-supplied keep masks:
+ *   keep[0] rg->kg attention probabilities [M, heads, n_kg]      keep[1] ffn_rg hidden [M, 2*hidden]
+ *   keep[2] kg->rg attention probabilities [heads, n_kg, M]      keep[3] ffn_kg hidden [n_graphs*n_kg, 2*hidden]
+ *   keep[4] fusion_layer hidden [n_graphs, hidden]               keep[5..8] mask / instance / edge / score head hidden
+ * NULL = keep all.  d_rg [M, rg_dim] and d_kg [n_graphs*n_kg, kg_dim] (optional) receive the input gradients, so the
+ * node embeddings can be trained through (cm_gnn_backward's d_node_emb).
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct cm_fusion_dropout {
+    const uint8_t* keep[9];
+    float p;
+} cm_fusion_dropout;
+typedef struct cm_fusion_grads { /* one buffer per trainable tensor of cm_fusion_params (cross attention), overwritten */
+    float *rg_proj_w, *rg_proj_b, *kg_proj_w, *kg_proj_b;
+    float *r2k_in_w, *r2k_in_b, *r2k_out_w, *r2k_out_b;
+    float *k2r_in_w, *k2r_in_b, *k2r_out_w, *k2r_out_b;
+    float *ln_rg_w, *ln_rg_b, *ln_kg_w, *ln_kg_b;
+    float *ffn_rg_w1, *ffn_rg_b1, *ffn_rg_w2, *ffn_rg_b2;
+    float *ffn_kg_w1, *ffn_kg_b1, *ffn_kg_w2, *ffn_kg_b2;
+    float *fl_w1, *fl_b1, *fl_w2, *fl_b2;
+    float *head_w1[4], *head_b1[4], *head_w2[4], *head_b2[4];
+} cm_fusion_grads;
+size_t cm_fusion_train_workspace_bytes(const cm_fusion_params* p, int n_graphs, int n_rows, int n_kg);
+int cm_fusion_train_forward(const cm_fusion_params* p, const float* rg, const int32_t* node_ptr, int n_graphs, int n_rows,
+                            const float* kg, int n_kg, const cm_fusion_dropout* drop, void* workspace, size_t workspace_bytes,
+                            float* fused, float* mask_out, float* instance_out, float* edge_out, float* score_out, void* stream);
+int cm_fusion_backward(const cm_fusion_params* p, const float* rg, const int32_t* node_ptr, int n_graphs, int n_rows,
+                       const float* kg, int n_kg, const cm_fusion_dropout* drop, void* workspace, size_t workspace_bytes,
+                       const float* d_fused, const float* d_mask_out, const float* d_instance_out, const float* d_edge_out,
+                       const float* d_score_out, const cm_fusion_grads* grads, float* d_rg, float* d_kg, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * A8 + A9 (+A13): pixel-mask paint and the metric reductions.
  * Paint: models/region_graph/test.py:241-244 -- pixel with label l gets prob[l] when 0 <= l < N_b (the
  * reference indexes by RAW label); with id_of_label != NULL it gets prob[id_of_label[l]] instead

@@ -130,3 +130,99 @@ def test_gnn_train_step_is_reproducible_and_optimizer_step_reduces_loss():
     with torch.no_grad():
         mask, _, _ = m(data)     # the inference kernels pick up the updated weights and running statistics
     assert torch.isfinite(mask).all()
+
+
+# ----------------------------------------------------------------------------------------------- fusion
+def _fusion_loss(mask, inst, edge, score, y, iy, ey, sy):
+    dt = mask.dtype
+    return (F.cross_entropy(mask, y) + F.cross_entropy(inst, iy) + F.binary_cross_entropy_with_logits(edge.squeeze(-1), ey.to(dt))
+            + F.binary_cross_entropy(score.squeeze(-1), sy.to(dt)))
+
+
+def _detector(seed=2, **cfg):
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
+    torch.manual_seed(seed)
+    det = build_multimodal_model(cfg)
+    with torch.no_grad():
+        for n, p in det.named_parameters():
+            if "ln_" in n and n.endswith("weight"):
+                p.uniform_(0.7, 1.3)
+            elif n.endswith("bias"):
+                p.normal_(0, 0.05)
+    return det.cuda()
+
+
+def _fusion_oracle(det, rows, node_ptr, kg, targets, heads):
+    from oracle import fusion as ofus
+    sd = {k: v.detach().cpu().double().requires_grad_(True) for k, v in det.state_dict().items()}
+    rg = rows.detach().cpu().double().requires_grad_(True)
+    kgd = kg.detach().cpu().double().requires_grad_(True)
+    ptr = node_ptr.cpu().tolist()
+    outs = []
+    for g in range(len(ptr) - 1):
+        m, i, e, s, _, _ = ofus.detector_forward(sd, rg[ptr[g]:ptr[g + 1]][None], kgd[None], heads=heads)
+        outs.append((m, i, e, s))
+    cat = [torch.cat([o[j] for o in outs]) for j in range(4)]
+    loss = _fusion_loss(*cat, *targets)
+    loss.backward()
+    return cat, loss, {k: v.grad for k, v in sd.items()}, rg.grad, kgd.grad
+
+
+@pytest.mark.parametrize("cfg", [dict(), dict(rg_dim=256, kg_dim=64, hidden_dim=256, num_heads=4, num_classes=3)])
+def test_fusion_train_step_gradients_match_autograd_oracle(cfg):
+    """Ragged batch of 3 images against the float64 oracle run per image: every parameter gradient plus the gradients
+    with respect to the region embeddings and the (shared) KG rows.  Second config: Identity rg_proj, head_dim 64."""
+    det = _detector(**cfg).train()
+    det.dropout_p = 0.0
+    gen = torch.Generator().manual_seed(9)
+    sizes = [57, 131, 90]
+    M, G, K = sum(sizes), 3, 13
+    rows = (torch.randn((M, cfg.get("rg_dim", 128)), generator=gen).clamp_min(0) * 0.5).cuda().requires_grad_(True)
+    kg = (torch.randn((K, cfg.get("kg_dim", 128)), generator=gen).clamp_min(0) * 0.25).cuda().requires_grad_(True)
+    node_ptr = torch.tensor([0, 57, 188, 278], dtype=torch.int32, device="cuda")
+    nc = cfg.get("num_classes", 2)
+    targets = (torch.randint(0, nc, (G,), generator=gen), torch.randint(0, nc, (G,), generator=gen),
+               torch.randint(0, 2, (G,), generator=gen).float(), torch.randint(0, 2, (G,), generator=gen).float())
+    res = det.forward_ragged(rows, node_ptr, G, kg[None])
+    outs = (res["mask_out"], res["instance_out"], res["edge_out"], res["score_out"])
+    loss = _fusion_loss(*outs, *[t.cuda() for t in targets])
+    loss.backward()
+    ocat, oloss, og, org, okg = _fusion_oracle(det, rows, node_ptr, kg, targets, cfg.get("num_heads", 8))
+    for got, ref in zip(outs, ocat):
+        np.testing.assert_allclose(got.detach().cpu().numpy(), ref.detach().numpy(), rtol=0, atol=2e-4)
+    assert abs(loss.item() - oloss.item()) <= 1e-4
+    bad = {}
+    named = dict(det.named_parameters())
+    named["<rg rows>"], named["<kg rows>"] = rows, kg
+    og["<rg rows>"], og["<kg rows>"] = org, okg
+    for name, prm in named.items():
+        ref = og[name].numpy()
+        got = prm.grad.detach().cpu().numpy().astype(np.float64)
+        assert got.shape == ref.shape, name
+        tol = 3e-4 * np.abs(ref).max() + 1e-6
+        err = np.abs(got - ref).max() / tol
+        if err > 1.0:
+            bad[name] = err
+    assert not bad, f"gradient mismatch (error / tolerance): {bad}"
+
+
+def test_fusion_train_dense_forward_signature_and_dropout():
+    """The reference's call shape under model.train(): dense [B,N,d] / [B,K,d] inputs, 4 outputs, dropout on:
+    finite gradients for every parameter, different masks give different losses, eval afterwards still works."""
+    det = _detector(4).train()
+    gen = torch.Generator().manual_seed(1)
+    rg = torch.randn((2, 40, 128), generator=gen).clamp_min(0).cuda()
+    kg = torch.randn((1, 13, 128), generator=gen).clamp_min(0).mul(0.25).cuda().expand(2, -1, -1)
+    losses = []
+    for _ in range(2):
+        det.zero_grad()
+        mask, inst, edge, score = det(rg, kg)
+        assert tuple(mask.shape) == (2, 2) and tuple(score.shape) == (2, 1)
+        loss = mask.square().mean() + score.mean() + inst.sum() * 0.1 + edge.sum() * 0.1
+        loss.backward()
+        losses.append(loss.item())
+        assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in det.parameters())
+    assert losses[0] != losses[1]
+    det.eval()
+    with torch.no_grad():
+        assert torch.isfinite(det(rg, kg)[0]).all()
