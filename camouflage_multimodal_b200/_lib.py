@@ -105,6 +105,7 @@ SIGNATURES = {
                                   _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_gnn_backward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _i, _i, C.POINTER(GnnDropout), _fp, _sz,
                              _fp, _fp, _fp, _fp, C.POINTER(GnnGrads), _fp]),
+    "cm_flash_attention_f16": (_i, [_fp, _i, _fp, _i, _fp, _i, _i, _fp, _i, _f, _fp, _i, _fp]),
     "cm_fusion_train_workspace_bytes": (_sz, [C.POINTER(FusionParams), _i, _i, _i]),
     "cm_fusion_train_forward": (_i, [C.POINTER(FusionParams), _fp, _fp, _i, _i, _fp, _i, C.POINTER(FusionDropout), _fp, _sz,
                                      _fp, _fp, _fp, _fp, _fp, _fp]),

@@ -9,6 +9,7 @@
 
 #include <algorithm>
 
+#include "flash_tc.cuh"
 #include "fusion_tc.cuh"
 #include "linear.cuh"
 
@@ -258,6 +259,7 @@ extern "C" size_t cm_fusion_workspace_bytes(const cm_fusion_params* p, int n_gra
     if (!p || n_graphs <= 0 || node_cap <= 0 || n_kg <= 0 || cm::check_fusion(p) != CM_OK) return 0;
     size_t need = cm::carve_fusion(nullptr, p, n_graphs, node_cap, n_kg).total;
     if (cm::fusion_fold_supported(p, n_kg)) need = std::max(need, cm::fusion_tc_workspace_bytes(p, n_graphs, node_cap, n_kg));
+    if (cm::fusion_flash_supported(p, n_kg)) need = std::max(need, cm::fusion_flash_workspace_bytes(p, n_graphs, node_cap, n_kg));
     return need;
 }
 
@@ -333,6 +335,24 @@ extern "C" int cm_fusion_forward(const cm_fusion_params* p, const void* folded, 
         if ((rc = launch_linear(l, st)) != CM_OK) return rc;
         if ((rc = detector_heads(p, fused, D / 2, G, w.hid, mask_out, instance_out, edge_out, score_out, st)) != CM_OK) return rc;
         return post_launch("cm_fusion_forward(late)");
+    }
+
+    // large shared KG vocabularies, attention maps not requested: fused QK^T.softmax.V on the tensor cores (flash_tc.cu)
+    if (kg_graphs == 1 && !attn_rg2kg && !attn_kg2rg && fusion_flash_supported(p, Kk)) {
+        const size_t need = fusion_flash_workspace_bytes(p, G, M, Kk);
+        if (workspace_bytes < need) {
+            set_error("cm_fusion_forward: workspace %zu < %zu bytes", workspace_bytes, need);
+            return CM_ERR_WORKSPACE;
+        }
+        FlashTail t;
+        if ((rc = fusion_forward_flash(p, rg, node_ptr, G, M, kg, Kk, workspace, &t, st)) != CM_OK) return rc;
+        float* fz = fused_out ? fused_out : t.fused;
+        l = Linear(); l.M = G; l.A = t.both; l.lda = 2 * D; l.K = 2 * D; l.W = p->fl_w1; l.bias = p->fl_b1; l.N = D; l.C = t.f1; l.ldc = D; l.relu = 1;
+        if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+        l = Linear(); l.M = G; l.A = t.f1; l.lda = D; l.K = D; l.W = p->fl_w2; l.bias = p->fl_b2; l.N = D; l.C = fz; l.ldc = D;
+        if ((rc = launch_linear(l, st)) != CM_OK) return rc;
+        if ((rc = detector_heads(p, fz, D, G, t.hid, mask_out, instance_out, edge_out, score_out, st)) != CM_OK) return rc;
+        return post_launch("cm_fusion_forward(flash)");
     }
 
     const int heads = p->heads, R = kg_graphs * Kk, GK = G * Kk, shared = kg_graphs == 1;

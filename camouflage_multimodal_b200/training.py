@@ -245,3 +245,46 @@ def fusion_train_forward(det, rg_rows, node_ptr, n_graphs, kg, masks="auto"):
             masks = [(torch.rand(sh, device=dev) >= p_drop).to(torch.uint8) for sh in shapes]
     params = _fusion_param_list(det)
     return FusionTrainFunction.apply(det, rg_rows, node_ptr, G, kg, masks, *params)
+
+
+# ------------------------------------------------------------------------------------------------ data parallel
+def allreduce_gradients(parameters, average: bool = False):
+    """Sum (the reference's fusion step sums per-sample gradients, train_multimodal.py:270) or average the ``.grad``
+    of every parameter over ranks in ONE flat all-reduce (6.2 MB of fp32 for both models: a single NCCL call over
+    NVLink sized for launch latency, not one call per tensor).  No-op without an initialised process group."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return
+    grads = [p.grad for p in parameters if p.grad is not None]
+    if not grads:
+        return
+    flat = torch.cat([g.reshape(-1) for g in grads])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    if average:
+        flat /= dist.get_world_size()
+    off = 0
+    for g in grads:
+        n = g.numel()
+        g.copy_(flat[off:off + n].view_as(g))
+        off += n
+
+
+def joint_train_step(gnn, det, data, node_ptr, n_graphs, kg, loss_fn, optimizer=None, max_norm: float = 1.0,
+                     average_gradients: bool = False):
+    """One data-parallel training step through both models (BASELINE configs[3]): GNN forward (train mode) -> node
+    embeddings -> fusion + heads -> ``loss_fn(node_outputs, image_outputs)`` -> backward through
+    ``cm_fusion_backward`` and ``cm_gnn_backward`` -> gradient all-reduce -> ``clip_grad_norm_`` -> optimizer step
+    (models/region_graph/train.py:345-357, models/multimodal/train_multimodal.py:232-275).  Returns the loss."""
+    params = list(gnn.parameters()) + list(det.parameters())
+    if optimizer is not None:
+        optimizer.zero_grad(set_to_none=True)
+    mask, inst, edge, emb = gnn_train_forward(gnn, data)
+    res = det.forward_ragged(emb, node_ptr, n_graphs, kg)
+    loss = loss_fn((mask, inst, edge), res)
+    loss.backward()
+    allreduce_gradients(params, average=average_gradients)
+    if max_norm is not None:
+        torch.nn.utils.clip_grad_norm_(params, max_norm=max_norm)
+    if optimizer is not None:
+        optimizer.step()
+    return loss

@@ -247,6 +247,15 @@ int cm_fusion_forward(const cm_fusion_params* p, const void* folded, const float
                       float* edge_out, float* score_out, float* attn_rg2kg, float* attn_kg2rg,
                       void* stream);
 
+/* Fused QK^T -> softmax -> PV on the tcgen05 tensor cores for heads of 32 dims (the cross-attention of A10 when the
+ * knowledge graph is large; cm_fusion_forward takes this path by itself for >= 128 shared KG rows when no attention
+ * maps are requested).  q [mq, hidden], k [mk, hidden] row-major fp16; vt [hidden, ldv] = V transposed (ldv % 8 == 0,
+ * columns >= mk finite); hidden % 64 == 0; heads = hidden / 32.  seg_ptr (device, n_seg + 1 ints) gives the key range
+ * of each segment -- one set of output rows per segment: out [n_seg * mq, ldo] fp16 -- or NULL for one segment [0, mk).
+ * scale multiplies the scores (1/sqrt(32) for nn.MultiheadAttention). */
+int cm_flash_attention_f16(const void* q_f16, int mq, const void* k_f16, int mk, const void* vt_f16, int ldv, int hidden,
+                           const int32_t* seg_ptr, int n_seg, float scale, void* out_f16, int ldo, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Training-mode CrossAttentionFusion + the four detector heads: forward under model.train() and the backward
  * pass (fusion_model.py:75-146, 229-246; the step is models/multimodal/train_multimodal.py:232-275).

@@ -152,3 +152,32 @@ def test_sharded_metric_allreduce_gloo(tmp_path):
     for p in procs:
         out, _ = p.communicate(timeout=240)
         assert p.returncode == 0, out.decode()
+
+
+_GRAD_WORKER = r"""
+import sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+rank = int(sys.argv[3])
+dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{sys.argv[2]}", rank=rank, world_size=2)
+from camouflage_multimodal_b200.training import allreduce_gradients
+ps = [torch.nn.Parameter(torch.zeros(3, 5)), torch.nn.Parameter(torch.zeros(7)), torch.nn.Parameter(torch.zeros(2))]
+ps[0].grad = torch.full((3, 5), float(rank + 1))
+ps[1].grad = torch.arange(7.0) * (rank + 1)
+allreduce_gradients(ps)                      # ps[2] has no grad: skipped on both ranks
+assert torch.equal(ps[0].grad, torch.full((3, 5), 3.0)) and torch.equal(ps[1].grad, torch.arange(7.0) * 3) and ps[2].grad is None
+allreduce_gradients(ps, average=True)
+assert torch.equal(ps[0].grad, torch.full((3, 5), 3.0))
+dist.destroy_process_group()
+"""
+
+
+def test_gradient_allreduce_gloo(tmp_path):
+    """The data-parallel training step's only collective: one flat SUM all-reduce of every gradient."""
+    script = tmp_path / "g.py"
+    script.write_text(_GRAD_WORKER)
+    port = str(31500 + os.getpid() % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT) for r in range(2)]
+    for p in procs:
+        out, _ = p.communicate(timeout=240)
+        assert p.returncode == 0, out.decode()

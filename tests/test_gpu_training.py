@@ -226,3 +226,44 @@ def test_fusion_train_dense_forward_signature_and_dropout():
     det.eval()
     with torch.no_grad():
         assert torch.isfinite(det(rg, kg)[0]).all()
+
+
+def test_joint_step_gradients_flow_from_fusion_into_the_gnn():
+    """configs[3] in small: loss on the image-level heads only, so every GNN gradient arrives through
+    cm_fusion_backward's d_rg -> cm_gnn_backward's d_node_emb.  Oracle: autograd through both float64 restatements."""
+    from camouflage_multimodal_b200 import training
+    from oracle import fusion as ofus, gnn as ognn
+    data, y, iy, ey = _batch(2, first=66)
+    gnn = _model(9).train()
+    gnn.p_conv = gnn.p_fc = 0.0
+    det = _detector(6).train()
+    det.dropout_p = 0.0
+    kg = synth.synthetic_kg(13).cuda()
+    ptr = torch.zeros(3, dtype=torch.int32, device="cuda")
+    ptr[1:] = torch.cumsum(torch.bincount(data.batch, minlength=2), 0).to(torch.int32)
+    tg = (torch.tensor([1, 0]), torch.tensor([0, 1]), torch.tensor([1.0, 0.0]), torch.tensor([0.0, 1.0]))
+
+    def loss_fn(node_outs, res):
+        return _fusion_loss(res["mask_out"], res["instance_out"], res["edge_out"], res["score_out"], *[t.cuda() for t in tg])
+
+    loss = training.joint_train_step(gnn, det, data, ptr, 2, kg[None], loss_fn, optimizer=None, max_norm=None)
+    gsd = {k: v.detach().cpu().double().requires_grad_("running" not in k) for k, v in gnn.state_dict().items() if "num_batches" not in k}
+    fsd = {k: v.detach().cpu().double().requires_grad_(True) for k, v in det.state_dict().items()}
+    r = ognn.rg_gnn_forward(gsd, data.x.cpu().double(), data.edge_index.cpu(), data.edge_attr.cpu().double(), training_bn=True)
+    p = ptr.cpu().tolist()
+    outs = [ofus.detector_forward(fsd, r["node_emb"][p[g]:p[g + 1]][None], kg.cpu().double()[None]) for g in range(2)]
+    oloss = _fusion_loss(*[torch.cat([o[j] for o in outs]) for j in range(4)], *tg)
+    oloss.backward()
+    assert abs(loss.item() - oloss.item()) <= 1e-4
+    bad = {}
+    for name, prm in list(gnn.named_parameters()) + list(det.named_parameters()):
+        ref = (gsd[name] if name in gsd else fsd[name]).grad
+        if any(name.startswith(h) for h in ("fc_mask", "fc_instance", "fc_edge")):   # node heads carry no loss here
+            assert prm.grad.abs().max().item() == 0.0
+            continue
+        ref = ref.numpy()
+        got = prm.grad.detach().cpu().numpy().astype(np.float64)
+        tol = 5e-4 * np.abs(ref).max() + 1e-6
+        if np.abs(got - ref).max() > tol:
+            bad[name] = np.abs(got - ref).max() / tol
+    assert not bad, f"gradient mismatch (error / tolerance): {bad}"
