@@ -9,6 +9,8 @@ All buffers are allocated once at capacity; no step synchronises with the host.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _lib, metrics
@@ -32,6 +34,8 @@ class EvalPipeline:
         self._bufs = None
         self._shape = None
         self.total = None      # optional [15] f64 device accumulator of the per-batch metric partial sums
+        self._side = None      # side stream for the paint + metrics branch
+        self.parallel_metrics = os.environ.get("CM_PARALLEL_METRICS", "1") != "0"
 
     def _alloc(self, B, H, W, dev):
         if self._shape == (B, H, W, str(dev)):
@@ -80,19 +84,30 @@ class EvalPipeline:
         n_dev = g.node_ptr[B:]
         r = self.gnn.run(g.x, g.csr_row_ptr, g.csr_col, g.edge_w, None, n_dev, g.node_ptr, B,
                          want=("node_emb", "mask_out", "mask_prob"), out=self._bufs["gnn"])
+        # paint + metrics need only the GNN's mask probabilities: they run on a side stream next to the fusion (inside a
+        # captured step this becomes a parallel branch of the CUDA graph)
+        main = torch.cuda.current_stream(dev)
+        if self._side is None or self._side.device != dev:
+            self._side = torch.cuda.Stream(dev)
+        side = self._side if self.parallel_metrics else main
+        if side is not main:
+            side.wait_stream(main)
+        p = _lib.ptr
+        b = self._bufs
+        with torch.cuda.stream(side):
+            _lib.check(lib.cm_paint_metrics(p(labels), p(gt), B, H, W, p(r["mask_prob"]), p(g.node_ptr),
+                                            p(g.id_of_label) if self.label_offset_fix else None, self.label_cap,
+                                            self.threshold, p(b["pred_mask"]), p(b["counts"]), p(b["abs_err"]),
+                                            _lib.stream_ptr(dev)), "cm_paint_metrics")
+            _lib.check(lib.cm_metrics_finalize(p(b["counts"]), p(b["abs_err"]), B, H * W, p(b["per_image"]), p(b["partial"]),
+                                               _lib.stream_ptr(dev)), "cm_metrics_finalize")
+            if self.total is not None:
+                self.total.add_(b["partial"])
         f = self.detector.forward_ragged(r["node_emb"], g.node_ptr, B, self.kg, return_attention=False,
                                          out=self._bufs["fusion"])
         self._bufs["fusion"] = f
-        p = _lib.ptr
-        b = self._bufs
-        _lib.check(lib.cm_paint_metrics(p(labels), p(gt), B, H, W, p(r["mask_prob"]), p(g.node_ptr),
-                                        p(g.id_of_label) if self.label_offset_fix else None, self.label_cap,
-                                        self.threshold, p(b["pred_mask"]), p(b["counts"]), p(b["abs_err"]),
-                                        _lib.stream_ptr(dev)), "cm_paint_metrics")
-        _lib.check(lib.cm_metrics_finalize(p(b["counts"]), p(b["abs_err"]), B, H * W, p(b["per_image"]), p(b["partial"]),
-                                           _lib.stream_ptr(dev)), "cm_metrics_finalize")
-        if self.total is not None:
-            self.total.add_(b["partial"])
+        if side is not main:
+            main.wait_stream(side)
         return {"graph": g, "node_emb": r["node_emb"], "node_mask_out": r["mask_out"], "mask_prob": r["mask_prob"],
                 "mask_out": f["mask_out"], "instance_out": f["instance_out"], "edge_out": f["edge_out"],
                 "score_out": f["score_out"], "fused": f["fused"], "counts": b["counts"], "abs_err": b["abs_err"],
