@@ -411,9 +411,18 @@ def b200_arm(args):
     launches_per_step = sum(v[0] for v in rep.values()) / args.steps
     top = next(iter(kernels))
     tk = kernels[top]
+    # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture of this same command
+    # (profiles/ncu_traffic.json, written by tools/summarize_ncu.py --json); None when the kernel was not captured
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        for kname, rec in json.load(open(tpath)).items():
+            if kname.startswith(top):
+                traffic = rec["dram_bytes_per_launch"]
+                break
     roofline = {"kernel": top, "bound": tk.get("bound"), "achieved": tk.get("achieved"),
                 "peak": hbm_peak if tk.get("bound") == "hbm" else tf_peak, "unit": tk.get("unit"), "frac": tk.get("frac"),
-                "traffic": None, "peak_source": peak_src, "launches_per_step": tk["launches_per_step"],
+                "traffic": traffic, "peak_source": peak_src, "launches_per_step": tk["launches_per_step"],
                 "ms_per_step": tk["ms_per_step"], "share_of_kernel_time": tk["ms_per_step"] / sum(v["ms_per_step"] for v in kernels.values())}
 
     if rank == 0:
