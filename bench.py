@@ -206,14 +206,14 @@ def reference_arm(args):
     value = args.steps * per_step / sec
     sample = (f"{per_step} images per step (one per worker process, {cores} host cpus) of the same synthetic set, "
               f"oracle port of the reference's per-image CPU loop")
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args.gpus, kg_src, 0, args.input),
         "cpu_baseline": {"value": value, "unit": "images/sec", "cores": per_step, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def workload_config(n_gpus, kg_src, lanes=1, inp="u8"):
@@ -439,12 +439,31 @@ def b200_arm(args):
         if world == 1 and not args.no_cpu_baseline:
             gsd, fsd = cpu_state_dicts(gnn, det)
             line["cpu_baseline"] = run_cpu_baseline(gsd, fsd, kg.cpu(), args.cpu_images, args.input)
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The ONE JSON line of the contract, on the process's real stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    # libraries print to stdout too (NCCL's version banner, NCCL_DEBUG=INFO logs): everything except the JSON line goes
+    # to stderr, so stdout carries exactly one line
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
