@@ -116,6 +116,8 @@ SIGNATURES = {
     "cm_fusion_fold": (_i, [C.POINTER(FusionParams), _fp, _i, _fp, _sz, _fp]),
     "cm_fusion_forward": (_i, [C.POINTER(FusionParams), _fp, _fp, _fp, _i, _i, _fp, _i, _i, _fp, _sz,
                                _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "cm_canny_workspace_bytes": (_sz, [_i, _i, _i]),
+    "cm_canny": (_i, [_fp, _i, _i, _i, _i, C.c_double, C.c_double, C.c_double, _fp, _sz, _fp, _fp]),
     "cm_paint_metrics": (_i, [_fp, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _f, _fp, _fp, _fp, _fp]),
     "cm_metrics_dense": (_i, [_fp, _fp, _i, _i64, _f, _fp, _fp, _fp]),
     "cm_metrics_finalize": (_i, [_fp, _fp, _i, _i64, _fp, _fp, _fp]),

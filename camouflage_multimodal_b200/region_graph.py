@@ -137,6 +137,25 @@ def build_region_graphs(images, labels, canny, label_cap: int | None = None, edg
     return g
 
 
+def canny_edges(images, sigma: float = 2.0, low_threshold: float = 0.1, high_threshold: float = 0.2, out=None):
+    """``skimage.feature.canny(gray, sigma)`` of every image (extract_rg_embeddings.py:151-152) on the device:
+    ``images`` ``[B,H,W,3]`` float32 in [0,1] or uint8 (value = byte/255) -> ``[B,H,W]`` uint8 edge map (0/1).
+    Thresholds are skimage's defaults for float images (0.1 / 0.2 of the gradient magnitude)."""
+    lib = _lib.load()
+    _lib.require_cuda(images, "images")
+    if images.dim() != 4 or images.shape[-1] != 3 or images.dtype not in (torch.float32, torch.uint8):
+        raise ValueError(f"images must be [B,H,W,3] float32 or uint8, got {tuple(images.shape)} {images.dtype}")
+    images = images.contiguous()
+    B, H, W, _ = images.shape
+    dev = images.device
+    edges = out if out is not None else torch.empty((B, H, W), dtype=torch.uint8, device=dev)
+    ws_bytes = lib.cm_canny_workspace_bytes(B, H, W)
+    ws = WORKSPACE.get(dev, "canny", ws_bytes)
+    _lib.check(lib.cm_canny(_lib.ptr(images), 1 if images.dtype == torch.uint8 else 0, B, H, W, float(sigma), float(low_threshold),
+                            float(high_threshold), _lib.ptr(ws), ws_bytes, _lib.ptr(edges), _lib.stream_ptr(dev)), "cm_canny")
+    return edges
+
+
 class _CsrData(Data):
     """``Data`` that also carries the target-keyed CSR the build produced, so the GNN need not rebuild it."""
 
@@ -144,19 +163,20 @@ class _CsrData(Data):
 def create_region_graph(image, n_segments=500, segments=None, edges=None, device=None):
     """Drop-in for ``create_region_graph(image, n_segments) -> (Data, segments)`` (extract_rg_embeddings.py:138).
 
-    ``image``: ``[H,W,3]`` float array in [0,1].  ``segments`` (the SLIC label map, :143-144) and ``edges``
-    (the boolean Canny map, :152) must be supplied: SLIC / Canny are not part of this path yet.  The returned
-    ``Data`` lives on the CUDA device; ``edge_index`` is in canonical (sorted) order and ``edge_attr`` is ``[E,1]``.
+    ``image``: ``[H,W,3]`` float array in [0,1].  ``segments`` (the SLIC label map, :143-144) must be supplied: SLIC is
+    not part of this path yet.  ``edges`` (the boolean Canny map, :152) is computed on the device by
+    ``canny_edges`` (``cm_canny``, sigma 2 like the reference) unless given.  The returned ``Data`` lives on the CUDA
+    device; ``edge_index`` is in canonical (sorted) order and ``edge_attr`` is ``[E,1]``.
     """
-    if segments is None or edges is None:
+    if segments is None:
         raise NotImplementedError(
-            "create_region_graph needs the superpixel label map (`segments`) and the Canny edge map (`edges`): "
-            "SLIC / Canny are upstream of the B200 hot path (SURVEY.md 8f N1/N2)")
+            "create_region_graph needs the superpixel label map (`segments`): SLIC is upstream of the B200 hot path "
+            "(SURVEY.md 8f N1)")
     dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
     img = torch.as_tensor(np.asarray(image), dtype=torch.float32).to(dev)[None]
     seg_np = np.asarray(segments)
     lab = torch.as_tensor(seg_np.astype(np.int32)).to(dev)[None]
-    can = torch.as_tensor(np.asarray(edges).astype(np.uint8)).to(dev)[None]
+    can = canny_edges(img, sigma=2.0) if edges is None else torch.as_tensor(np.asarray(edges).astype(np.uint8)).to(dev)[None]
     cap = max(int(seg_np.max()) + 1, 1) if seg_np.size else 1
     g = build_region_graphs(img, lab, can, label_cap=cap, local_ids=True)
     n, e = g.counts()

@@ -292,6 +292,18 @@ int cm_fusion_backward(const cm_fusion_params* p, const float* rg, const int32_t
                        const float* d_score_out, const cm_fusion_grads* grads, float* d_rg, float* d_kg, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * the Canny edge map behind region feature 13 -- skimage.feature.canny(gray, sigma=2) with
+ * gray = image . [0.2989, 0.5870, 0.1140] (extract_rg_embeddings.py:151-152): Gaussian (mode 'constant', bleed-over
+ * corrected), scipy Sobel (mode 'reflect'), bilinear non-maximum suppression, hysteresis low/high on the float
+ * magnitude (skimage defaults 0.1 / 0.2), all in float64 in scipy's operation order.  Parity unpinned (scikit-image
+ * is not vendored by the reference): checked against the numpy/scipy restatement in oracle/canny.py.
+ * image [B,H,W,3] float32 in [0,1] (image_is_u8 = 0) or uint8 (value = byte/255); edges [B,H,W] uint8 out (0/1).
+ * ------------------------------------------------------------------------------------------------ */
+size_t cm_canny_workspace_bytes(int batch, int h, int w);
+int cm_canny(const void* image, int image_is_u8, int batch, int h, int w, double sigma, double low_threshold,
+             double high_threshold, void* workspace, size_t workspace_bytes, uint8_t* edges, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * A8 + A9 (+A13): pixel-mask paint and the metric reductions.
  * Paint: models/region_graph/test.py:241-244 -- pixel with label l gets prob[l] when 0 <= l < N_b (the
  * reference indexes by RAW label); with id_of_label != NULL it gets prob[id_of_label[l]] instead
