@@ -31,7 +31,12 @@ def to_3d(t: torch.Tensor, name: str) -> torch.Tensor:
     raise ValueError(f"{name} must be 2D/3D/4D tensor, got shape {t.shape}")
 
 
-def mha(p, prefix, query, key, heads):
+def _drop(t, keep, pdrop):
+    """F.dropout with an explicit keep mask (training parity: PyTorch's RNG stream cannot be reproduced)."""
+    return t if keep is None else t * keep.to(t.dtype) / (1.0 - pdrop)
+
+
+def mha(p, prefix, query, key, heads, keep=None, pdrop=0.0):
     """``nn.MultiheadAttention(batch_first=True)`` eval forward with ``need_weights=True,
     average_attn_weights=True`` (fusion_model.py:112-118): packed in-projection rows [q; k; v], q scaled by
     1/sqrt(head_dim), softmax over keys, out-projection; returns (out [B,Lq,D], head-mean probs [B,Lq,Lk])."""
@@ -46,33 +51,36 @@ def mha(p, prefix, query, key, heads):
     k = k.view(bsz, lk, heads, hd).transpose(1, 2)
     v = v.view(bsz, lk, heads, hd).transpose(1, 2)
     prob = torch.softmax(q @ k.transpose(-1, -2), dim=-1)          # [B,H,Lq,Lk]
-    ctx = (prob @ v).transpose(1, 2).reshape(bsz, lq, d)
+    ctx = (_drop(prob, keep, pdrop) @ v).transpose(1, 2).reshape(bsz, lq, d)
     out = F.linear(ctx, p[f"{prefix}.out_proj.weight"], p[f"{prefix}.out_proj.bias"])
     return out, prob.mean(dim=1)
 
 
-def _mlp2(p, prefix, x):
-    """Sequential(Linear, ReLU, Dropout, Linear) in eval: indices 0 and 3."""
-    return F.linear(F.relu(F.linear(x, p[f"{prefix}.0.weight"], p[f"{prefix}.0.bias"])),
+def _mlp2(p, prefix, x, keep=None, pdrop=0.0):
+    """Sequential(Linear, ReLU, Dropout, Linear): indices 0 and 3 (dropout only through an explicit keep mask)."""
+    return F.linear(_drop(F.relu(F.linear(x, p[f"{prefix}.0.weight"], p[f"{prefix}.0.bias"])), keep, pdrop),
                     p[f"{prefix}.3.weight"], p[f"{prefix}.3.bias"])
 
 
-def cross_attention_fusion(p, rg, kg, heads=8, prefix="fusion."):
-    """fusion_model.py:75-146.  ``p`` holds the ``fusion.*`` entries of the detector state dict."""
+def cross_attention_fusion(p, rg, kg, heads=8, prefix="fusion.", drop=None, pdrop=0.0):
+    """fusion_model.py:75-146.  ``p`` holds the ``fusion.*`` entries of the detector state dict.  ``drop`` (training
+    parity only): keep masks ``r2k`` [B,H,N,K], ``ffn_rg`` [B,N,2D], ``k2r`` [B,H,K,N], ``ffn_kg`` [B,K,2D],
+    ``fusion_layer`` [B,D]."""
+    dk = (lambda name: None) if drop is None else drop.get
     rg, kg = to_3d(rg, "rg_embeddings"), to_3d(kg, "kg_embeddings")
     g = lambda k: p[prefix + k]
     r = F.linear(rg, g("rg_proj.weight"), g("rg_proj.bias")) if (prefix + "rg_proj.weight") in p else rg   # :108
     k = F.linear(kg, g("kg_proj.weight"), g("kg_proj.bias")) if (prefix + "kg_proj.weight") in p else kg   # :109
     d = r.shape[-1]
     sub = {kk[len(prefix):]: v for kk, v in p.items() if kk.startswith(prefix)}
-    a, w_rk = mha(sub, "cross_attn_rg2kg", r, k, heads)                                   # :112-118
+    a, w_rk = mha(sub, "cross_attn_rg2kg", r, k, heads, dk("r2k"), pdrop)                 # :112-118
     y = F.layer_norm(r + a, (d,), g("ln_rg.weight"), g("ln_rg.bias"))                    # :119
-    y = y + _mlp2(sub, "ffn_rg", y)                                                       # :120
-    c, w_kr = mha(sub, "cross_attn_kg2rg", k, r, heads)                                   # :123-129
+    y = y + _mlp2(sub, "ffn_rg", y, dk("ffn_rg"), pdrop)                                  # :120
+    c, w_kr = mha(sub, "cross_attn_kg2rg", k, r, heads, dk("k2r"), pdrop)                 # :123-129
     z = F.layer_norm(k + c, (d,), g("ln_kg.weight"), g("ln_kg.bias"))                    # :130
-    z = z + _mlp2(sub, "ffn_kg", z)                                                       # :131
+    z = z + _mlp2(sub, "ffn_kg", z, dk("ffn_kg"), pdrop)                                  # :131
     both = torch.cat([y.mean(dim=1), z.mean(dim=1)], dim=-1)                              # :134-138
-    fused = _mlp2(sub, "fusion_layer", both)                                              # :139
+    fused = _mlp2(sub, "fusion_layer", both, dk("fusion_layer"), pdrop)                   # :139
     return fused, {"rg2kg": w_rk, "kg2rg": w_kr}
 
 
@@ -88,19 +96,20 @@ def late_fusion(p, rg, kg, prefix="fusion."):
     return F.linear(x, p[prefix + "fusion.6.weight"], p[prefix + "fusion.6.bias"]), None
 
 
-def detector_forward(p, rg, kg, heads=8, fusion_type="cross_attention"):
+def detector_forward(p, rg, kg, heads=8, fusion_type="cross_attention", drop=None, pdrop=0.0):
     """``MultimodalCamouflageDetector.forward`` (fusion_model.py:237-246), eval mode.
     Returns (mask_out, instance_out, edge_out, score_out, attention dict or None, fused)."""
     if fusion_type == "cross_attention":
-        fused, attn = cross_attention_fusion(p, rg, kg, heads)
+        fused, attn = cross_attention_fusion(p, rg, kg, heads, drop=drop, pdrop=pdrop)
     elif fusion_type == "late":
         fused, attn = late_fusion(p, rg, kg)
     else:
         raise ValueError(f"Unknown fusion_type: {fusion_type}")
-    mask = _mlp2(p, "mask_head", fused)
-    inst = _mlp2(p, "instance_head", fused)
-    edge = _mlp2(p, "edge_head", fused)
-    score = torch.sigmoid(_mlp2(p, "score_head", fused))                                   # :229-235
+    dk = (lambda name: None) if drop is None else drop.get
+    mask = _mlp2(p, "mask_head", fused, dk("mask_head"), pdrop)
+    inst = _mlp2(p, "instance_head", fused, dk("instance_head"), pdrop)
+    edge = _mlp2(p, "edge_head", fused, dk("edge_head"), pdrop)
+    score = torch.sigmoid(_mlp2(p, "score_head", fused, dk("score_head"), pdrop))          # :229-235
     return mask, inst, edge, score, attn, fused
 
 

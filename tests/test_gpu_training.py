@@ -267,3 +267,54 @@ def test_joint_step_gradients_flow_from_fusion_into_the_gnn():
         if np.abs(got - ref).max() > tol:
             bad[name] = np.abs(got - ref).max() / tol
     assert not bad, f"gradient mismatch (error / tolerance): {bad}"
+
+
+def test_fusion_train_step_with_all_nine_dropout_masks():
+    """Every dropout site of the fusion (both attention-probability dropouts, both FFNs, the fusion MLP, four heads)
+    with explicit keep masks, p = 0.3, against the float64 oracle given the same masks."""
+    from camouflage_multimodal_b200 import training
+    det = _detector(8).train()
+    pd = det.dropout_p
+    assert abs(pd - 0.3) < 1e-9
+    gen = torch.Generator().manual_seed(13)
+    sizes = [44, 71]
+    M, G, K, D, H = sum(sizes), 2, 13, 256, 8
+    rows = (torch.randn((M, 128), generator=gen).clamp_min(0) * 0.5).cuda().requires_grad_(True)
+    kg = (torch.randn((K, 128), generator=gen).clamp_min(0) * 0.25).cuda()
+    node_ptr = torch.tensor([0, 44, 115], dtype=torch.int32, device="cuda")
+    shapes = [(M, H, K), (M, 2 * D), (H, K, M), (G * K, 2 * D), (G, D)] + [(G, D // 2)] * 4
+    masks = [(torch.rand(sh, generator=gen) >= pd).to(torch.uint8).cuda() for sh in shapes]
+    targets = (torch.tensor([1, 0]), torch.tensor([0, 1]), torch.tensor([1.0, 0.0]), torch.tensor([0.0, 1.0]))
+    fused, *outs = training.fusion_train_forward(det, rows, node_ptr, G, kg[None], masks=masks)
+    loss = _fusion_loss(*outs, *[t.cuda() for t in targets])
+    loss.backward()
+    # oracle, image by image, with the same masks sliced to the image
+    from oracle import fusion as ofus
+    sd = {k: v.detach().cpu().double().requires_grad_(True) for k, v in det.state_dict().items()}
+    rg = rows.detach().cpu().double().requires_grad_(True)
+    mk = [m.cpu() for m in masks]
+    ptr = node_ptr.cpu().tolist()
+    res = []
+    for g in range(G):
+        a, b = ptr[g], ptr[g + 1]
+        drop = {"r2k": mk[0][a:b].permute(1, 0, 2)[None], "ffn_rg": mk[1][a:b][None], "k2r": mk[2][:, :, a:b][None],
+                "ffn_kg": mk[3][g * K:(g + 1) * K][None], "fusion_layer": mk[4][g][None], "mask_head": mk[5][g][None],
+                "instance_head": mk[6][g][None], "edge_head": mk[7][g][None], "score_head": mk[8][g][None]}
+        res.append(ofus.detector_forward(sd, rg[a:b][None], kg.cpu().double()[None], drop=drop, pdrop=pd))
+    ocat = [torch.cat([r[j] for r in res]) for j in range(4)]
+    oloss = _fusion_loss(*ocat, *targets)
+    oloss.backward()
+    for got, ref in zip(outs, ocat):
+        np.testing.assert_allclose(got.detach().cpu().numpy(), ref.detach().numpy(), rtol=0, atol=3e-4)
+    bad = {}
+    named = dict(det.named_parameters())
+    named["<rg rows>"] = rows
+    og = {k: v.grad for k, v in sd.items()}
+    og["<rg rows>"] = rg.grad
+    for name, prm in named.items():
+        ref = og[name].numpy()
+        got = prm.grad.detach().cpu().numpy().astype(np.float64)
+        tol = 3e-4 * np.abs(ref).max() + 1e-6
+        if np.abs(got - ref).max() > tol:
+            bad[name] = np.abs(got - ref).max() / tol
+    assert not bad, f"gradient mismatch (error / tolerance): {bad}"
