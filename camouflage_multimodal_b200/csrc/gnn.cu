@@ -9,7 +9,10 @@
 //     BatchNorm folded into its weight and bias) follows as a dense layer.
 // PyG semantics restated: self loops removed then one added per node (GAT); add_remaining_self_loops with
 // weight 1, symmetric normalisation by the weighted in-degree (GCN); softmax denominator + 1e-16.
+#include <cstdlib>
+
 #include "dense_tc.cuh"
+#include "gcn_tc.cuh"
 #include "linear.cuh"
 
 namespace cm {
@@ -344,7 +347,43 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
     auto W = [&](size_t off) { return reinterpret_cast<const op_t*>(blob + off); };
     Dense d;
     d.M = M; d.m_dev = n_nodes_dev; d.relu = 1;
-    d.A = ws.z; d.lda = f.zk; d.K = f.zk; d.W = W(f.wcat_h); d.bias = blob + f.bias1; d.N = H; d.out_h = ws.buf0; d.ldo_h = 3 * H; d.split_out = 1;
+    // hidden == 128 with two classes: the GCN layers run as fused gather + tensor-core kernels (gcn_tc.cu) over fp32
+    // rows, the last one carrying the row-local tail; any other shape takes the aggregate + dense kernels below.
+    static const bool force_general = getenv("CM_GNN_GENERAL") != nullptr;   // test hook: exercise the unfused kernels
+    const bool fused = H == 128 && p->num_classes == 2 && !force_general;
+    float* emb = node_emb ? node_emb : (graph_emb ? ws.emb : nullptr);
+    const bool want_heads = mask_out || instance_out || edge_out || mask_prob;
+    d.A = ws.z; d.lda = f.zk; d.K = f.zk; d.W = W(f.wcat_h); d.bias = blob + f.bias1; d.N = H;
+    if (fused) {
+        float* xa = reinterpret_cast<float*>(ws.buf0);   // [M, 128] fp32 ping-pong inside the fp16 split buffers
+        float* xb = reinterpret_cast<float*>(ws.buf1);
+        d.out_f32 = xa; d.ldo_f32 = H;
+        if ((rc = launch_dense(d, st)) != CM_OK) return rc;
+        {
+            CM_TIMED("gcn_norm", st);
+            gcn_norm_kernel<<<ceil_div(M, 256), 256, 0, st>>>(csr_row_ptr, csr_col, csr_w, self_w, n_nodes_dev, M, ws.dis);
+        }
+        GcnLayer g;
+        g.row_ptr = csr_row_ptr; g.col = csr_col; g.w = csr_w; g.self_w = self_w; g.dis = ws.dis; g.n_dev = n_nodes_dev; g.M = M;
+        for (int k = 0; k < 3; ++k) {
+            g.x = (k & 1) ? xb : xa;
+            g.out = (k & 1) ? xa : xb;
+            g.w_split = W(f.convw_h[k]); g.bias = blob + f.convb[k];
+            if (k == 2) {
+                g.chain = 1; g.out = nullptr;
+                g.fc_split = W(f.fcw_h); g.fc_bias = p->fc_shared_bias; g.emb = emb;
+                g.do_heads = want_heads ? 1 : 0;
+                g.h1_split = W(f.head1w_h); g.h1_bias = blob + f.head1b;
+                for (int t = 0; t < 3; ++t) {
+                    g.w2[t] = p->head2_weight[t];
+                    g.b2[t] = p->head2_bias[t];
+                }
+                g.out_mask = mask_out; g.out_inst = instance_out; g.out_edge = edge_out; g.prob_out = mask_prob;
+            }
+            if ((rc = launch_gcn_layer_tc(g, st)) != CM_OK) return rc;
+        }
+    } else {
+    d.out_h = ws.buf0; d.ldo_h = 3 * H; d.split_out = 1;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     {
         CM_TIMED("gcn_norm", st);
@@ -358,10 +397,9 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
         d.A = ws.buf1; d.lda = 3 * H; d.K = 3 * H; d.W = W(f.convw_h[k]); d.bias = blob + f.convb[k];
         if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     }
-    float* emb = node_emb ? node_emb : (graph_emb ? ws.emb : nullptr);
     d.A = ws.buf0; d.W = W(f.fcw_h); d.bias = p->fc_shared_bias; d.out_h = ws.emb_h; d.out_f32 = emb; d.ldo_f32 = H;
     if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-    if (mask_out || instance_out || edge_out || mask_prob) {
+    if (want_heads) {
         const int H2 = H / 2;
         d.A = ws.emb_h; d.W = W(f.head1w_h); d.bias = blob + f.head1b; d.N = 3 * H2; d.out_h = nullptr; d.out_f32 = ws.hid; d.ldo_f32 = 3 * H2;
         if ((rc = launch_dense(d, st)) != CM_OK) return rc;
@@ -377,6 +415,7 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
         }
         h2.prob_out = mask_prob;
         if ((rc = launch_heads2(ws.hid, 3 * H2, M, n_nodes_dev, h2, st)) != CM_OK) return rc;
+    }
     }
     if (graph_emb) {
         if ((rc = launch_segment_mean(emb, H, node_ptr, 0, n_graphs, graph_emb, H, st)) != CM_OK) return rc;
