@@ -334,6 +334,51 @@ __device__ __forceinline__ void u8_write_features(const U8Moments& m, float norm
     o[14] = (float)gvar;                        // :193
 }
 
+// Same arithmetic as u8_write_features with the moments warp-uniform and the 15 outputs spread over the lanes: every
+// lane runs ONE fp64 division / square root on its own operands instead of lane 0 running sixteen of them in turn.
+__device__ __forceinline__ void u8_write_features_warp(const U8Moments& m, float norm_side, float* __restrict__ o, int lane) {
+    const unsigned full = 0xffffffffu;
+    const double n = (double)m.n, s = 255.0 * n, s2 = s * s, ns = (double)norm_side;
+    const long long ni = (long long)m.n, sr = (long long)m.r, sg = (long long)m.g, sb = (long long)m.b;
+    const double crr = (double)(ni * (long long)m.rr - sr * sr), cgg = (double)(ni * (long long)m.gg - sg * sg),
+                 cbb = (double)(ni * (long long)m.bb - sb * sb), crg = (double)(ni * (long long)m.rg - sr * sg),
+                 crb = (double)(ni * (long long)m.rb - sr * sb), cgb = (double)(ni * (long long)m.gb - sg * sb);
+    const double wr = 0.2989, wg = 0.5870, wb = 0.1140;   // :151
+    const double gnum = wr * (double)sr + wg * (double)sg + wb * (double)sb;
+    const double vnum = wr * wr * crr + wg * wg * cgg + wb * wb * cbb + 2.0 * (wr * wg * crg + wr * wb * crb + wg * wb * cgb);
+    const double per = (double)m.per, rden = m.rn > 0 ? 255.0 * (double)m.rn : 1.0;
+    double num = 0.0, den = 1.0;
+    switch (lane) {
+        case 0: num = (double)sr; den = s; break;
+        case 1: num = (double)sg; den = s; break;
+        case 2: num = (double)sb; den = s; break;
+        case 3: num = crr; den = s2; break;
+        case 4: num = cgg; den = s2; break;
+        case 5: num = cbb; den = s2; break;
+        case 6: num = gnum; den = s; break;
+        case 7: case 14: num = vnum; den = s2; break;
+        case 8: num = (double)m.sx; den = n; break;
+        case 9: num = (double)m.sy; den = n; break;
+        case 10: num = n; den = ns * ns; break;
+        case 11: num = per * per; den = 4.0 * 3.14159265358979323846 * n + 1e-10; break;   // :179
+        case 13: num = (double)m.can; den = n; break;
+        case 16: num = (double)m.xr; den = rden; break;
+        case 17: num = (double)m.xg; den = rden; break;
+        case 18: num = (double)m.xb; den = rden; break;
+        default: break;
+    }
+    double a = num / den;
+    const double a_ns = a / ns;                       // centroids, :172-173
+    if (lane == 8 || lane == 9) a = a_ns;
+    if ((lane >= 3 && lane <= 5) || lane == 7 || lane == 14) a = a > 0.0 ? a : 0.0;
+    const double d = a - __shfl_down_sync(full, a, 16);   // lanes 0..2: mean_c - ring mean_c
+    const double d0 = __shfl_sync(full, d, 0), d1 = __shfl_sync(full, d, 1), d2 = __shfl_sync(full, d, 2);
+    if (lane == 12) a = m.rn > 0 ? __fma_rn(d2, d2, __fma_rn(d1, d1, d0 * d0)) : 0.0;   // :190
+    const double rt = sqrt(a);
+    if ((lane >= 3 && lane <= 5) || lane == 7 || lane == 12) a = rt;
+    if (lane < CM_NODE_FEATURES) o[lane] = (float)a;
+}
+
 __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_t* __restrict__ image, const int* __restrict__ labels,
                                                                     const uint8_t* __restrict__ canny, int batch, int H, int W,
                                                                     const int* __restrict__ node_ptr, const int* __restrict__ node_label,
@@ -355,6 +400,79 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
 
     unsigned n = 0, sx = 0, sy = 0, sc = 0, per = 0, rn = 0, r1 = 0, g1 = 0, b1 = 0, rr = 0, gg = 0, b2 = 0, rg = 0, rb = 0, gb = 0,
              xr = 0, xg = 0, xb = 0;
+    const int wh = wy1 - wy0 + 1;
+    __shared__ unsigned short visit[8][1024];
+    if (ww <= 32 && wh <= 32) {
+        // Window of at most 32 x 32 pixels (every SLIC-sized region).  Lane y keeps row y of the membership mask as
+        // one 32-bit word (ballot over the row's labels); the 4-connected and L1 <= 2 dilations (:177, :185) are
+        // shifts and ORs of the words above / below (shuffles) and the three counts are popc.  The member and ring
+        // pixels are then written as a compact list (row, column, member bit) to shared memory so that the moment
+        // pass keeps all 32 lanes on pixels that count: one label load per window pixel instead of thirteen, and
+        // ~0.7 visits per window pixel instead of one.
+        const unsigned full = 0xffffffffu;
+        const bool colin = lane < ww;
+        const int base = wy0 * W + wx0;
+        const int* lp0 = lab + base + (colin ? lane : 0);
+        unsigned m = 0;
+        for (int y8 = 0; y8 < wh; y8 += 8) {
+            int lw[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) lw[k] = __ldg(lp0 + min(y8 + k, wh - 1) * W);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const unsigned bal = __ballot_sync(full, colin && lw[k] == L);
+                if (lane == y8 + k) m = bal;
+            }
+        }
+        if (lane >= wh) m = 0;
+        unsigned up1 = __shfl_up_sync(full, m, 1), up2 = __shfl_up_sync(full, m, 2);
+        unsigned dn1 = __shfl_down_sync(full, m, 1), dn2 = __shfl_down_sync(full, m, 2);
+        if (lane < 1) up1 = 0;
+        if (lane < 2) up2 = 0;
+        if (lane > 30) dn1 = 0;
+        if (lane > 29) dn2 = 0;
+        const unsigned keep = lane < wh ? (ww == 32 ? full : ((1u << ww) - 1u)) & ~m : 0u;
+        const unsigned h1 = (m << 1) | (m >> 1), v1 = up1 | dn1;
+        const unsigned m1 = keep & (h1 | v1);
+        const unsigned m2 = keep & (h1 | v1 | (m << 2) | (m >> 2) | (v1 << 1) | (v1 >> 1) | up2 | dn2);
+        n = __popc(m);
+        per = __popc(m1);
+        rn = __popc(m2);
+        // compact list of the pixels to visit: exclusive scan of the per-row counts, each lane writes its row
+        unsigned vv = m | m2;
+        int incl = __popc(vv);
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(full, incl, d);
+            if (lane >= d) incl += t;
+        }
+        const int total_px = __shfl_sync(full, incl, 31);
+        unsigned short* lst = visit[threadIdx.x >> 5];
+        int o = incl - __popc(vv);
+        while (vv) {
+            const int bit = __ffs(vv) - 1;
+            vv &= vv - 1;
+            lst[o++] = (unsigned short)((lane << 5) | bit | (((m >> bit) & 1u) << 10));
+        }
+        __syncwarp();
+        const uint8_t* ip0 = img + 3 * (size_t)base;
+        const uint8_t* cp0 = can + base;
+        for (int k = lane; k < total_px; k += 32) {
+            const unsigned e = lst[k];
+            const int yy = (e >> 5) & 31, xx = e & 31;
+            const unsigned mm = e >> 10, q2 = mm ^ 1u;
+            const int off = yy * W + xx;
+            const uint8_t* ip = ip0 + 3 * off;
+            const unsigned r = ip[0], g = ip[1], bl = ip[2];
+            const unsigned cn = cp0[off] != 0 ? mm : 0u;
+            const unsigned rm = r * mm, gm = g * mm, bm = bl * mm;
+            sx += (unsigned)(wx0 + xx) * mm; sy += (unsigned)(wy0 + yy) * mm; sc += cn;
+            r1 += rm; g1 += gm; b1 += bm;
+            rr += r * rm; gg += g * gm; b2 += bl * bm;
+            rg += r * gm; rb += r * bm; gb += g * bm;
+            xr += r * q2; xg += g * q2; xb += bl * q2;
+        }
+    } else
     for (int i = lane; i < npx; i += 32) {
         int yy = __float2int_rz(((float)i + 0.5f) * inv_ww);   // i / ww, fixed up below (npx < 2^22 keeps it within +-1)
         int xx = i - yy * ww;
@@ -397,7 +515,7 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
     m.rr = warp_sum_wide(rr); m.gg = warp_sum_wide(gg); m.bb = warp_sum_wide(b2);
     m.rg = warp_sum_wide(rg); m.rb = warp_sum_wide(rb); m.gb = warp_sum_wide(gb);
     m.xr = warp_sum_wide(xr); m.xg = warp_sum_wide(xg); m.xb = warp_sum_wide(xb);
-    if (lane == 0) u8_write_features(m, norm_side, xout + (size_t)gi * CM_NODE_FEATURES);
+    u8_write_features_warp(m, norm_side, xout + (size_t)gi * CM_NODE_FEATURES, lane);
 }
 
 __global__ void labels_widen_kernel(const short* __restrict__ in, long long n, int* __restrict__ out) {

@@ -65,6 +65,23 @@ __device__ __forceinline__ void gc_load_weight(uint8_t* w_dst, const CUtensorMap
     tma_load_2d(w_dst + 3 * n * 128, map, bar, 2 * GC_H + 64, 0);
 }
 
+#ifdef CM_GC_PROFILE
+__device__ unsigned long long gc_prof[16];
+#define GC_STAMP(i)                                                                   \
+    do {                                                                              \
+        if (blockIdx.x == 3 && threadIdx.x == 0) {                                    \
+            unsigned long long t_;                                                    \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                    \
+            gc_prof[i] = t_;                                                          \
+        }                                                                             \
+    } while (0)
+extern "C" int cm_debug_gcn_profile(unsigned long long* out) {
+    return cudaMemcpyFromSymbol(out, gc_prof, sizeof(gc_prof)) == cudaSuccess ? 0 : 1;
+}
+#else
+#define GC_STAMP(i)
+#endif
+
 template <bool CHAIN>
 __global__ void __launch_bounds__(GC_THREADS, 1)
 gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_fc,
@@ -87,6 +104,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
     uint64_t* acc = w_full + 3;                                          // [3]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc + 3);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    GC_STAMP(0);
 
     if (tid == 0) {
         for (int i = 0; i < 3; ++i) {
@@ -123,6 +141,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    GC_STAMP(1);
 
     // ---------------------------------------------------------------- phase 1: gather, four rows per warp at a time
     // Eight lanes own a row: load t of a lane covers columns [32 t + 4 l8, +4), so every load instruction reads one
@@ -204,6 +223,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
+    GC_STAMP(2);
 
     // ---------------------------------------------------------------- phases 2 + 3, up to three chained products
     const int q = warp & 3, grp = warp >> 2;
@@ -230,6 +250,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
         mbar_wait(acc + stage, 0);
         __syncwarp();
         tc_fence_after();
+        GC_STAMP(3 + 2 * stage);
         const float* sb = stage == 0 ? s_bias : (stage == 1 ? s_fcb : s_h1b);
         for (int c = grp; c < n / 32; c += 4) {
             uint32_t v[32];
@@ -271,6 +292,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
             tc_fence_before();
             __syncthreads();
         }
+        GC_STAMP(4 + 2 * stage);
     }
     if (CHAIN && p.do_heads) {
 #pragma unroll
@@ -293,6 +315,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
     }
     tc_fence_before();
     __syncthreads();
+    GC_STAMP(9);
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
