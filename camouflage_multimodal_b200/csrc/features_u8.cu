@@ -414,12 +414,12 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
         const int base = wy0 * W + wx0;
         const int* lp0 = lab + base + (colin ? lane : 0);
         unsigned m = 0;
-        for (int y8 = 0; y8 < wh; y8 += 8) {
-            int lw[8];
+        for (int y8 = 0; y8 < wh; y8 += 16) {   // sixteen rows of label loads in flight
+            int lw[16];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) lw[k] = __ldg(lp0 + min(y8 + k, wh - 1) * W);
+            for (int k = 0; k < 16; ++k) lw[k] = __ldg(lp0 + min(y8 + k, wh - 1) * W);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
+            for (int k = 0; k < 16; ++k) {
                 const unsigned bal = __ballot_sync(full, colin && lw[k] == L);
                 if (lane == y8 + k) m = bal;
             }
@@ -452,25 +452,34 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
         while (vv) {
             const int bit = __ffs(vv) - 1;
             vv &= vv - 1;
-            lst[o++] = (unsigned short)((lane << 5) | bit | (((m >> bit) & 1u) << 10));
+            lst[o++] = (unsigned short)((lane << 5) | bit | (((m >> bit) & 1u) ? 0x400u : 0x800u));
         }
         __syncwarp();
         const uint8_t* ip0 = img + 3 * (size_t)base;
         const uint8_t* cp0 = can + base;
-        for (int k = lane; k < total_px; k += 32) {
-            const unsigned e = lst[k];
-            const int yy = (e >> 5) & 31, xx = e & 31;
-            const unsigned mm = e >> 10, q2 = mm ^ 1u;
-            const int off = yy * W + xx;
-            const uint8_t* ip = ip0 + 3 * off;
-            const unsigned r = ip[0], g = ip[1], bl = ip[2];
-            const unsigned cn = cp0[off] != 0 ? mm : 0u;
-            const unsigned rm = r * mm, gm = g * mm, bm = bl * mm;
-            sx += (unsigned)(wx0 + xx) * mm; sy += (unsigned)(wy0 + yy) * mm; sc += cn;
-            r1 += rm; g1 += gm; b1 += bm;
-            rr += r * rm; gg += g * gm; b2 += bl * bm;
-            rg += r * gm; rb += r * bm; gb += g * bm;
-            xr += r * q2; xg += g * q2; xb += bl * q2;
+        for (int k0 = 0; k0 < total_px; k0 += 64) {   // two list entries per lane per trip, their loads issued together
+            unsigned e[2], r[2], g[2], bl[2], cb[2];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int k = k0 + 32 * j + lane;
+                e[j] = k < total_px ? lst[k] : 0u;   // 0: pixel (0, 0) of the window with both weights 0
+                const int off = ((e[j] >> 5) & 31) * W + (e[j] & 31);
+                const uint8_t* ip = ip0 + 3 * off;
+                r[j] = ip[0];
+                g[j] = ip[1];
+                bl[j] = ip[2];
+                cb[j] = cp0[off];
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const unsigned mm = (e[j] >> 10) & 1u, q2 = e[j] >> 11;
+                const unsigned rm = r[j] * mm, gm = g[j] * mm, bm = bl[j] * mm;
+                sx += (unsigned)(wx0 + (e[j] & 31)) * mm; sy += (unsigned)(wy0 + ((e[j] >> 5) & 31)) * mm; sc += cb[j] != 0 ? mm : 0u;
+                r1 += rm; g1 += gm; b1 += bm;
+                rr += r[j] * rm; gg += g[j] * gm; b2 += bl[j] * bm;
+                rg += r[j] * gm; rb += r[j] * bm; gb += g[j] * bm;
+                xr += r[j] * q2; xg += g[j] * q2; xb += bl[j] * q2;
+            }
         }
     } else
     for (int i = lane; i < npx; i += 32) {

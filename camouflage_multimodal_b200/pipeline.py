@@ -223,6 +223,32 @@ class HostPipeline:
             st.ev_done.synchronize()
 
 
+def bind_host_to_gpu(device_index: int) -> list[int]:
+    """Pin this process (and the pinned staging buffers it first-touches afterwards) to the CPU cores NVML reports as
+    local to the GPU, so host->device copies do not cross the socket interconnect.  Returns the cores bound to
+    (empty when NVML or the affinity call is unavailable -- the process then keeps its inherited affinity)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(_physical_index(device_index))
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cores = [64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1]
+        allowed = sorted(set(cores) & os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:   # noqa: BLE001 -- placement is an optimisation, never a requirement
+        return []
+
+
+def _physical_index(device_index: int) -> int:
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+    ids = [v for v in vis.split(",") if v.strip()]
+    if ids and device_index < len(ids) and ids[device_index].strip().isdigit():
+        return int(ids[device_index])
+    return device_index
+
+
 def allreduce_partials(partial: torch.Tensor, confusion: torch.Tensor | None = None):
     """Sum the metric partial sums (and image-level confusion counts) over ranks: the only data-path collective
     of the sharded evaluation.  No-op without an initialised process group."""
