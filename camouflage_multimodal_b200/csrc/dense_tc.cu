@@ -395,10 +395,28 @@ __global__ void cast_f16_kernel(const float* __restrict__ in, int ld_in, int row
     }
 }
 
+// dense rows (ld_in == ld_out == cols, cols % 8 == 0, 16-byte aligned): eight values per thread per trip
+__global__ void __launch_bounds__(256) cast_f16_flat_kernel(const float* __restrict__ in, int rows, int cols, const int* rows_dev,
+                                                             op_t* __restrict__ out) {
+    const int live = rows_dev ? min(*rows_dev, rows) : rows;
+    const long long n8 = (long long)live * cols / 8;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+        const float4 a = reinterpret_cast<const float4*>(in)[2 * i], b = reinterpret_cast<const float4*>(in)[2 * i + 1];
+        const float x[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        reinterpret_cast<uint4*>(out)[i] = pack8(x);
+    }
+}
+
 int launch_cast_f16(const float* in, int ld_in, int rows, int cols, const int* rows_dev, op_t* out, int ld_out,
                      cudaStream_t st) {
     if (rows <= 0) return CM_OK;
     const long long total = (long long)rows * ld_out;
+    if (ld_in == cols && ld_out == cols && (cols & 7) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        const int blocks = (int)std::min<long long>((total / 8 + 255) / 256, 148LL * 8);
+        CM_TIMED("cast_f16", st);
+        cast_f16_flat_kernel<<<blocks, 256, 0, st>>>(in, rows, cols, rows_dev, out);
+        return post_launch("cast_f16");
+    }
     int blocks = (int)std::min<long long>((total + 255) / 256, 148LL * 16);
     {
         CM_TIMED("cast_f16", st);

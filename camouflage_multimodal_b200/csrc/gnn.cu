@@ -147,39 +147,60 @@ __global__ void __launch_bounds__(256) gat_aggregate_kernel(const float* __restr
     const int g = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int n = n_dev ? min(*n_dev, cap) : cap;
     if (g >= n) return;
-    const int e0 = row_ptr[g], e1 = row_ptr[g + 1];
+    // Softmax weights: one lane per incoming edge (the added self loop is edge number deg), all heads of that edge in
+    // the lane; maxima and denominators by warp reduction.  Aggregation: lane c owns input feature c and pulls the
+    // edge's neighbour index and weights from the owning lane by shuffle -- the exp is evaluated once per edge and
+    // head, not once per lane.
+    const unsigned full = 0xffffffffu;
+    const int e0 = row_ptr[g], deg = row_ptr[g + 1] - e0;
     float ad[HEADS], mx[HEADS], den[HEADS], acc[HEADS];
 #pragma unroll
     for (int h = 0; h < HEADS; ++h) {
         ad[h] = a_dst[(size_t)g * HEADS + h];
-        float l = a_src[(size_t)g * HEADS + h] + ad[h];   // the added self loop
-        mx[h] = l > 0.f ? l : 0.2f * l;
+        mx[h] = -INFINITY;
         den[h] = 0.f;
         acc[h] = 0.f;
     }
-    for (int e = e0; e < e1; ++e) {
-        const int j = col[e];
-        if (j == g) continue;   // PyG removes existing self loops first
+    auto logits = [&](int idx, int& j, float (&l)[HEADS]) -> bool {
+        j = idx < deg ? col[e0 + idx] : g;
+        const bool ok = idx <= deg && !(idx < deg && j == g);   // PyG removes existing self loops, then appends one
 #pragma unroll
         for (int h = 0; h < HEADS; ++h) {
-            float l = a_src[(size_t)j * HEADS + h] + ad[h];
-            l = l > 0.f ? l : 0.2f * l;
-            mx[h] = fmaxf(mx[h], l);
+            const float t = a_src[(size_t)j * HEADS + h] + ad[h];
+            l[h] = t > 0.f ? t : 0.2f * t;
         }
+        return ok;
+    };
+    for (int base = 0; base <= deg; base += 32) {
+        int j;
+        float l[HEADS];
+        const bool ok = logits(base + lane, j, l);
+#pragma unroll
+        for (int h = 0; h < HEADS; ++h) mx[h] = fmaxf(mx[h], ok ? l[h] : -INFINITY);
     }
-    for (int e = e0; e <= e1; ++e) {   // e == e1 is the self loop (PyG appends it last)
-        const int j = e < e1 ? col[e] : g;
-        if (e < e1 && j == g) continue;
-        const float xv = lane < C ? x[(size_t)j * C + lane] : 0.f;
+#pragma unroll
+    for (int h = 0; h < HEADS; ++h)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx[h] = fmaxf(mx[h], __shfl_xor_sync(full, mx[h], o));
+    for (int base = 0; base <= deg; base += 32) {
+        int j;
+        float l[HEADS], w[HEADS];
+        const bool ok = logits(base + lane, j, l);
 #pragma unroll
         for (int h = 0; h < HEADS; ++h) {
-            float l = a_src[(size_t)j * HEADS + h] + ad[h];
-            l = l > 0.f ? l : 0.2f * l;
-            const float w = expf(l - mx[h]);
-            den[h] += w;
-            acc[h] = fmaf(w, xv, acc[h]);
+            w[h] = ok ? expf(l[h] - mx[h]) : 0.f;
+            den[h] += w[h];
+        }
+        const int cnt = min(32, deg + 1 - base);
+        for (int t = 0; t < cnt; ++t) {
+            const int jt = __shfl_sync(full, j, t);
+            const float xv = lane < C ? x[(size_t)jt * C + lane] : 0.f;
+#pragma unroll
+            for (int h = 0; h < HEADS; ++h) acc[h] = fmaf(__shfl_sync(full, w[h], t), xv, acc[h]);
         }
     }
+#pragma unroll
+    for (int h = 0; h < HEADS; ++h) den[h] = warp_sum(den[h]);
     // z row = [z_hi | z_lo | z_hi], each third padded with zeros to zk/3 columns
     op_t* zr = z + (size_t)g * zk;
     const int third = zk / 3;
