@@ -63,6 +63,18 @@ class FusionParams(C.Structure):
     ]
 
 
+class RgLossConfig(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("mask_pos_weight", "instance_pos_weight", "edge_pos_weight", "task_mask", "task_instance", "task_edge")]
+
+
+class ImageLossConfig(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("alpha", "gamma", "w_focal", "w_instance", "w_edge", "w_score")]
+
+
+class AdamWConfig(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("lr", "beta1", "beta2", "eps", "weight_decay", "max_norm")]
+
+
 class FusionDropout(C.Structure):
     _fields_ = [("keep", _fp * 9), ("p", C.c_float)]
 
@@ -122,6 +134,10 @@ SIGNATURES = {
     "cm_metrics_dense": (_i, [_fp, _fp, _i, _i64, _f, _fp, _fp, _fp]),
     "cm_metrics_finalize": (_i, [_fp, _fp, _i, _i64, _fp, _fp, _fp]),
     "cm_class_confusion": (_i, [_fp, _fp, _i, _i, _fp, _fp]),
+    "cm_region_targets": (_i, [_fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _fp, _fp, _fp, _fp]),
+    "cm_rg_node_loss": (_i, [_fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, C.POINTER(RgLossConfig), _fp, _sz, _fp, _fp, _fp, _fp, _fp]),
+    "cm_image_loss": (_i, [_fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, C.POINTER(ImageLossConfig), _fp, _fp, _fp, _fp, _fp, _fp]),
+    "cm_adamw_step": (_i, [_fp, _fp, _fp, _fp, _fp, _i, _i64, C.POINTER(AdamWConfig), _i, _fp, _fp, _fp]),
 }
 
 _lib = None

@@ -330,6 +330,57 @@ int cm_metrics_finalize(const int64_t* counts, const double* abs_err, int batch,
 int cm_class_confusion(const float* mask_out, const int64_t* true_cls, int n, int num_classes,
                        int64_t* counts4, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * the training-loop pieces around the model passes (device-side, no host synchronisation).
+ * ------------------------------------------------------------------------------------------------ */
+/* Per-region ground-truth targets (models/region_graph/train.py:169-176): the reference thresholds the mean of the
+ * ToTensor'ed masks (byte/255) over the region's pixels at 0.5 / 0.5 / 0.3; with byte masks that is the integer
+ * test 2*S > 255*n (10*S > 765*n for the edge mask).  labels [B,H,W] int32, masks [B,H,W] uint8, node_* from
+ * cm_rag_build.  y / instance_y [node_cap] int64 (what nn.CrossEntropyLoss takes), edge_y [node_cap] float32. */
+int cm_region_targets(const int32_t* labels, const uint8_t* mask, const uint8_t* instance_mask, const uint8_t* edge_mask,
+                      int batch, int h, int w, const int32_t* node_ptr, const int32_t* node_label, const int32_t* node_bbox,
+                      int node_cap, int64_t* y, int64_t* instance_y, float* edge_y, void* stream);
+
+/* Region-node multi-task loss (train.py:325-353): CrossEntropyLoss(weight=[1, mask_pos_weight]) * task_mask +
+ * CrossEntropyLoss(weight=[1, instance_pos_weight]) * task_instance + BCEWithLogitsLoss(pos_weight) * task_edge.
+ * Logits [node_cap, 2] / [node_cap, 2] / [node_cap]; *n_nodes_dev live rows.  loss_out [4] = total, mask, instance,
+ * edge terms; d_* (optional) = d total / d logits (rows past the live count zeroed).  workspace: 40 bytes. */
+typedef struct cm_rg_loss_config {
+    float mask_pos_weight, instance_pos_weight, edge_pos_weight;   /* 5, 4, 3 in the reference */
+    float task_mask, task_instance, task_edge;                     /* 2, 1, 0.5 */
+} cm_rg_loss_config;
+int cm_rg_node_loss(const float* mask_logits, const float* instance_logits, const float* edge_logits, const int64_t* y,
+                    const int64_t* instance_y, const float* edge_y, const int32_t* n_nodes_dev, int node_cap,
+                    const cm_rg_loss_config* cfg, void* workspace, size_t workspace_bytes, float* loss_out, float* d_mask,
+                    float* d_instance, float* d_edge, void* stream);
+
+/* Image-level loss of the multimodal detector (models/multimodal/train_multimodal.py:29-57, 253-268), summed over the
+ * images of the batch (the reference calls backward once per sample):
+ *   w_focal * AggressiveFocalLoss(alpha, gamma)(mask, label) + w_instance * CE(instance, label)
+ *   + w_edge * BCEWithLogits(edge, edge_label) + w_score * (score - score_label)^2
+ * mask / instance logits [G,2], edge logit [G], score [G] (after the sigmoid).  loss_out [1]; d_* optional. */
+typedef struct cm_image_loss_config {
+    float alpha, gamma;                            /* 0.75, 3.0 */
+    float w_focal, w_instance, w_edge, w_score;    /* 3, 1, 0.5, 0.3 */
+} cm_image_loss_config;
+int cm_image_loss(const float* mask_logits, const float* instance_logits, const float* edge_logits, const float* score,
+                  const int64_t* mask_label, const float* edge_label, const float* score_label, int n_graphs,
+                  const cm_image_loss_config* cfg, float* loss_out, float* d_mask, float* d_instance, float* d_edge,
+                  float* d_score, void* stream);
+
+/* torch.nn.utils.clip_grad_norm_(params, max_norm) followed by torch.optim.AdamW.step() (train.py:318,356-357;
+ * train_multimodal.py:276-277) over a table of tensors in two launches + one tiny one: params / grads / exp_avg /
+ * exp_avg_sq are DEVICE arrays of n_tensors device pointers, numel the element counts (device), max_numel the
+ * largest of them (host).  The gradients are scaled in place by min(1, max_norm / (total_norm + 1e-6)) (max_norm <= 0:
+ * no clipping); norm_out [2] = total gradient norm before clipping, clip coefficient.  step counts from 1.
+ * norm_workspace: n_tensors doubles. */
+typedef struct cm_adamw_config {
+    float lr, beta1, beta2, eps, weight_decay, max_norm;
+} cm_adamw_config;
+int cm_adamw_step(float* const* params, const float* const* grads, float* const* exp_avg, float* const* exp_avg_sq,
+                  const int64_t* numel, int n_tensors, int64_t max_numel, const cm_adamw_config* cfg, int step,
+                  double* norm_workspace, float* norm_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
