@@ -125,28 +125,55 @@ int launch_gemm(const Gemm& g, cudaStream_t st, const char* name) {
 constexpr int CS_ROWS = 64;   // rows per CTA
 int col_parts(int rows) { return rows > 0 ? ceil_div(rows, CS_ROWS) : 1; }
 
-__global__ void colsum_part_kernel(const float* __restrict__ a, int lda, int rows, int cols, double* __restrict__ part) {
-    const int c = blockIdx.y * blockDim.x + threadIdx.x;
-    if (c >= cols) return;
+// 32 columns x 8 row lanes per CTA over CS_ROWS rows: eight independent loads in flight per thread, fixed-order tree
+__global__ void __launch_bounds__(256) colsum_part_kernel(const float* __restrict__ a, int lda, int rows, int cols, double* __restrict__ part) {
+    __shared__ double sh[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.y * 32 + tx;
     const int r0 = blockIdx.x * CS_ROWS, r1 = min(rows, r0 + CS_ROWS);
     double s = 0.0;
-    for (int r = r0; r < r1; ++r) s += (double)a[(long)r * lda + c];
-    part[(long)blockIdx.x * cols + c] = s;
+    if (c < cols) {
+        float v[CS_ROWS / 8];
+#pragma unroll
+        for (int k = 0; k < CS_ROWS / 8; ++k) {
+            const int r = r0 + ty + 8 * k;
+            v[k] = r < r1 ? a[(long)r * lda + c] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < CS_ROWS / 8; ++k) s += (double)v[k];
+    }
+    sh[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && c < cols) {
+#pragma unroll
+        for (int k = 1; k < 8; ++k) s += sh[k][tx];
+        part[(long)blockIdx.x * cols + c] = s;
+    }
 }
-__global__ void colsum_final_kernel(const double* __restrict__ part, int parts, int cols, float* __restrict__ out, int accumulate) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cols) return;
+// 32 columns x 8 part lanes per CTA: coalesced reads of the partial rows, fixed-order tree over the 8 lanes (deterministic)
+__global__ void __launch_bounds__(256) colsum_final_kernel(const double* __restrict__ part, int parts, int cols, float* __restrict__ out,
+                                                           int accumulate) {
+    __shared__ double sh[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
     double s = 0.0;
-    for (int p = 0; p < parts; ++p) s += part[(long)p * cols + c];
-    out[c] = accumulate ? out[c] + (float)s : (float)s;
+    if (c < cols)
+        for (int p = ty; p < parts; p += 8) s += part[(long)p * cols + c];
+    sh[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && c < cols) {
+#pragma unroll
+        for (int k = 1; k < 8; ++k) s += sh[k][tx];
+        out[c] = accumulate ? out[c] + (float)s : (float)s;
+    }
 }
 
 int launch_colsum(const float* a, int lda, int rows, int cols, double* part, float* out, int accumulate, cudaStream_t st) {
     const int parts = col_parts(rows);
     {
         CM_TIMED("colsum", st);
-        if (rows > 0) colsum_part_kernel<<<dim3(parts, ceil_div(cols, 128)), 128, 0, st>>>(a, lda, rows, cols, part);
-        colsum_final_kernel<<<ceil_div(cols, 128), 128, 0, st>>>(part, rows > 0 ? parts : 0, cols, out, accumulate);
+        if (rows > 0) colsum_part_kernel<<<dim3(parts, ceil_div(cols, 32)), 256, 0, st>>>(a, lda, rows, cols, part);
+        colsum_final_kernel<<<ceil_div(cols, 32), 256, 0, st>>>(part, rows > 0 ? parts : 0, cols, out, accumulate);
     }
     return post_launch("colsum");
 }

@@ -147,7 +147,14 @@ class FusedAdamW:
         self.lr, self.betas, self.eps, self.weight_decay, self.max_norm = lr, betas, eps, weight_decay, max_norm
         self.exp_avg = [torch.zeros_like(p) for p in self.params]
         self.exp_avg_sq = [torch.zeros_like(p) for p in self.params]
-        self.grads = [torch.zeros_like(p) for p in self.params]   # stable gradient buffers: p.grad is pointed at them
+        # stable gradient buffers, views of ONE flat tensor (zero_grad is one memset, a data-parallel all-reduce one call);
+        # p.grad is pointed at them and autograd accumulates in place
+        offs, total = [], 0
+        for p in self.params:
+            offs.append(total)
+            total += (p.numel() + 3) // 4 * 4
+        self.flat_grad = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.grads = [self.flat_grad[o:o + p.numel()].view_as(p) for o, p in zip(offs, self.params)]
         for p, g in zip(self.params, self.grads):
             p.grad = g
         table = lambda ts: torch.tensor([t.data_ptr() for t in ts], dtype=torch.int64, device=dev)  # noqa: E731
@@ -158,9 +165,20 @@ class FusedAdamW:
         self._norm_out = torch.zeros(2, dtype=torch.float32, device=dev)
         self.step_count = 0
 
-    def zero_grad(self):
-        for g in self.grads:
-            g.zero_()
+    def zero_grad(self, set_to_none: bool = False):
+        """Zeroes the registered buffers (``set_to_none`` is accepted for torch.optim compatibility and ignored: the
+        kernels need stable gradient addresses)."""
+        self.flat_grad.zero_()
+        for p, g in zip(self.params, self.grads):
+            p.grad = g
+
+    def allreduce(self, average: bool = False):
+        """Data-parallel gradient sum (or mean) over the process group: one NCCL call on the flat buffer."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.flat_grad)
+            if average:
+                self.flat_grad.div_(dist.get_world_size())
 
     @property
     def total_norm(self):

@@ -282,7 +282,10 @@ def joint_train_step(gnn, det, data, node_ptr, n_graphs, kg, loss_fn, optimizer=
     res = det.forward_ragged(emb, node_ptr, n_graphs, kg)
     loss = loss_fn((mask, inst, edge), res)
     loss.backward()
-    allreduce_gradients(params, average=average_gradients)
+    if hasattr(optimizer, "allreduce"):     # train_loop.FusedAdamW: gradients already live in one flat buffer
+        optimizer.allreduce(average=average_gradients)
+    else:
+        allreduce_gradients(params, average=average_gradients)
     if max_norm is not None:
         torch.nn.utils.clip_grad_norm_(params, max_norm=max_norm)
     if optimizer is not None:

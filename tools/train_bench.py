@@ -44,27 +44,31 @@ def main():
     B = args.batch
     b = synth.make_batch(rank * B, B, seed=1234, device=dev).as_decoded()
     params = list(gnn.parameters()) + list(det.parameters())
-    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-4)
+    from camouflage_multimodal_b200.train_loop import FusedAdamW, MultimodalLoss, RegionGraphLoss, region_targets
+    # clip_grad_norm_(1.0) + AdamW(lr, weight_decay=1e-4) in cm_adamw_step (train.py:318, 356-357)
+    opt = FusedAdamW(params, lr=1e-4, weight_decay=1e-4, max_norm=1.0)
     gen = torch.Generator().manual_seed(rank)
     img_y = torch.randint(0, 2, (B,), generator=gen).to(dev)
-    w_mask = torch.tensor([1.0, 5.0], device=dev)
+    edge_y = torch.randint(0, 2, (B,), generator=gen).float().to(dev)
+    score_y = torch.rand((B,), generator=gen).to(dev)
+    rg_loss, mm_loss = RegionGraphLoss(), MultimodalLoss()
+    labels32 = b.labels.to(torch.int32)
 
     def step():
         # graph build (inference kernels) is part of the step: the reference builds graphs in its Dataset.__getitem__
-        g = build_region_graphs(b.images, b.labels.to(torch.int32), b.canny, label_cap=544)
+        g = build_region_graphs(b.images, labels32, b.canny, label_cap=544)
         data = batch_to_data(g)
         n = data.x.shape[0]
-        # per-region labels: majority vote of the GT mask over the region (train.py:169-176) -- here the painted label
-        node_y = (data.x[:, 10] > data.x[:, 10].median()).long()
+        # per-region targets from the ground-truth masks (train.py:169-176); the synthetic set has one mask per image,
+        # used for all three maps
+        y, iy, ey = region_targets(g, labels32, b.gt, b.gt, b.gt)
 
         def loss_fn(node_outs, res):
-            lm = F.cross_entropy(node_outs[0], node_y, weight=w_mask)
-            li = F.cross_entropy(node_outs[1], node_y)
-            le = F.binary_cross_entropy_with_logits(node_outs[2].squeeze(-1), node_y.float())
-            lf = F.cross_entropy(res["mask_out"], img_y) + F.binary_cross_entropy(res["score_out"].squeeze(-1), img_y.float())
-            return lm + li + le + lf
+            ln = rg_loss(node_outs[0], node_outs[1], node_outs[2], y[:n], iy[:n], ey[:n])
+            lf = mm_loss(res["mask_out"], res["instance_out"], res["edge_out"], res["score_out"], img_y, edge_y, score_y)
+            return ln + lf
 
-        return training.joint_train_step(gnn, det, data, g.node_ptr, B, kg[None], loss_fn, optimizer=opt, max_norm=1.0), n
+        return training.joint_train_step(gnn, det, data, g.node_ptr, B, kg[None], loss_fn, optimizer=opt, max_norm=None), n
 
     for _ in range(args.warmup):
         step()
