@@ -2,8 +2,9 @@
 
 Mirrors ``models/region_graph/extract_rg_embeddings.py`` of the reference: ``create_region_graph`` (:138-246)
 from the label map onward, and ``RegionGraphGNN`` (:27-135) with the same constructor, methods, return
-arities and PyG state-dict key names (``conv1.lin.weight``, ``conv1.att_src`` ...).  SLIC and Canny are the
-steps before the hot path: the label map and the boolean edge map are inputs here.
+arities and PyG state-dict key names (``conv1.lin.weight``, ``conv1.att_src`` ...).  SLIC is the step before the hot
+path: the label map is an input here.  The Canny edge map (8f N2, ``:152``) is computed on the
+device by ``canny_edges`` / ``cm_canny`` when the caller does not pass one.
 """
 from __future__ import annotations
 
