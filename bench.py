@@ -133,6 +133,8 @@ def kernel_work(name, B, M, E, K):
         # rows are gathered from L2 (the whole activation tensor is 7 MB at batch 32)
         "gcn_layer_tc": ("hbm", 2 * (1024.0 * M + 8.0 * E)),
         "gcn_tail_tc": ("hbm", (1024.0 + 24.0) * M + 8.0 * E),
+        # fused GAT layer: 15-d features + per-head logits + edge list in, fp32 rows + deg^-1/2 out
+        "gat_layer_tc": ("hbm", (60.0 + 32.0 + 512.0 + 4.0) * M + 8.0 * E),
         "fusion_node": ("tensor", node_flops),
         "fusion_kgrows": ("tensor", 2.0 * gk * (D * D + 2 * (D * 2 * D))),
         "cast_f16": ("hbm", 768.0 * M),

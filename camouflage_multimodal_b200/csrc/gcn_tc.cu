@@ -28,6 +28,7 @@ constexpr int GC_VEC_FLOATS = 128 + 128 + 192 + 320 + 8;
 constexpr int GC_OFF_PART = GC_OFF_VEC + GC_VEC_FLOATS * 4;   // head partial sums [4 groups][128 rows][5]
 constexpr int GC_OFF_BAR = GC_OFF_PART + 4 * 128 * 5 * 4;
 constexpr int GC_SMEM = GC_OFF_BAR + 128 + 1024;          // + slack for 1 KB alignment
+constexpr int GC_SMEM_GAT = 4 * GC_A_BLOCK + GC_VEC_FLOATS * 4 + 128 + 1024;
 
 __device__ __forceinline__ void gc_store_split(uint8_t* a_tile, int row, int chunk_base, int kb, const float* x, int n8) {
     // x: n8 groups of 8 consecutive columns starting at 16-byte chunk `chunk_base` of K block kb
@@ -42,10 +43,11 @@ __device__ __forceinline__ void gc_store_split(uint8_t* a_tile, int row, int chu
 }
 
 // A_hi W_hi + A_lo W_hi + A_hi W_lo over K = 128 (two 64-wide K blocks, four UMMA_K = 16 steps each)
-__device__ __forceinline__ void gc_issue(uint32_t tmem, uint32_t a_addr, uint32_t w_addr, int n, uint32_t idesc) {
+__device__ __forceinline__ void gc_issue(uint32_t tmem, uint32_t a_addr, uint32_t w_addr, int n, uint32_t idesc, int nkb = 2) {
     const uint32_t wb = (uint32_t)n * 128;
 #pragma unroll
     for (int kb = 0; kb < 2; ++kb) {
+        if (kb >= nkb) break;
         const uint64_t ahi = umma_desc_sw128(a_addr + kb * GC_A_BLOCK), alo = umma_desc_sw128(a_addr + (2 + kb) * GC_A_BLOCK);
         const uint64_t whi = umma_desc_sw128(w_addr + kb * wb), wlo = umma_desc_sw128(w_addr + (2 + kb) * wb);
 #pragma unroll
@@ -57,6 +59,12 @@ __device__ __forceinline__ void gc_issue(uint32_t tmem, uint32_t a_addr, uint32_
     }
 }
 
+// GAT layer weight [128, 3 x 64]: one K block of W_hi (columns 0..63) and one of W_lo (columns 128..191)
+__device__ __forceinline__ void gc_load_weight_k64(uint8_t* w_dst, const CUtensorMap* map, uint64_t* bar, int n) {
+    mbar_expect_tx(bar, (uint32_t)(2 * n * 128));
+    tma_load_2d(w_dst, map, bar, 0, 0);
+    tma_load_2d(w_dst + 2 * n * 128, map, bar, 128, 0);
+}
 __device__ __forceinline__ void gc_load_weight(uint8_t* w_dst, const CUtensorMap* map, uint64_t* bar, int n) {
     mbar_expect_tx(bar, (uint32_t)(4 * n * 128));
     tma_load_2d(w_dst, map, bar, 0, 0);                          // W_hi, K columns [0, 64)
@@ -82,25 +90,32 @@ extern "C" int cm_debug_gcn_profile(unsigned long long* out) {
 #define GC_STAMP(i)
 #endif
 
-template <bool CHAIN>
+// MODE 0: GCN layer -> fp32 rows;  1: GCN layer + chained fc_shared / heads;  2: GAT layer (softmax-weighted 15-d
+// neighbour sums per head as the A operand, K = 64) -> fp32 rows, also writes the GCN normalisation deg^-1/2
+template <int MODE>
 __global__ void __launch_bounds__(GC_THREADS, 1)
 gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_fc,
                     const __grid_constant__ CUtensorMap map_h1, GcnLayer p) {
+    constexpr bool CHAIN = MODE == 1, GAT = MODE == 2;
     extern __shared__ uint8_t smem_raw[];
     const int n_live = p.n_dev ? min(*p.n_dev, p.M) : p.M;
     const int m0 = blockIdx.x * GC_ROWS;
     if (m0 >= n_live) return;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // GAT mode needs one K block per operand half: A_hi | W_hi | A_lo | W_lo interleaved in the first 64 KB, no edge list
+    constexpr int OFF_W = GAT ? GC_A_BLOCK : GC_OFF_W, OFF_VEC = GAT ? 4 * GC_A_BLOCK : GC_OFF_VEC;
+    constexpr int OFF_BAR = GAT ? OFF_VEC + GC_VEC_FLOATS * 4 : GC_OFF_BAR;
+    constexpr uint32_t TMEM_COLS = CHAIN ? 256u : 128u;
     uint8_t* a_tile = smem + GC_OFF_A;
-    uint8_t* w_tile = smem + GC_OFF_W;
+    uint8_t* w_tile = smem + OFF_W;
     int2* s_edge = reinterpret_cast<int2*>(smem + GC_OFF_EDGE);
-    float* s_bias = reinterpret_cast<float*>(smem + GC_OFF_VEC);
+    float* s_bias = reinterpret_cast<float*>(smem + OFF_VEC);
     float* s_fcb = s_bias + 128;
     float* s_h1b = s_fcb + 128;
     float* s_w2 = s_h1b + 192;
     float* s_b2 = s_w2 + 320;
     float* s_part = reinterpret_cast<float*>(smem + GC_OFF_PART);
-    uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + GC_OFF_BAR);   // [3]
+    uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + OFF_BAR);   // [3]
     uint64_t* acc = w_full + 3;                                          // [3]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc + 3);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -112,18 +127,20 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
             mbar_init(acc + i, 1);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        gc_load_weight(w_tile, &map_w, w_full, GC_H);
+        if (GAT) gc_load_weight_k64(w_tile, &map_w, w_full, GC_H); else gc_load_weight(w_tile, &map_w, w_full, GC_H);
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256u) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     // ---------------------------------------------------------------- phase 0: vectors + the tile's edge list
     const int rows_here = min(GC_ROWS, n_live - m0);
     const int e_lo = p.row_ptr[m0], e_hi = p.row_ptr[m0 + rows_here];
-    for (int e = e_lo + tid; e < min(e_hi, e_lo + GC_EDGE_CAP); e += GC_THREADS) {
-        const int j = p.col[e];
-        s_edge[e - e_lo] = make_int2(j, __float_as_int(p.dis[j] * (p.w ? p.w[e] : 1.0f)));
+    if (!GAT) {
+        for (int e = e_lo + tid; e < min(e_hi, e_lo + GC_EDGE_CAP); e += GC_THREADS) {
+            const int j = p.col[e];
+            s_edge[e - e_lo] = make_int2(j, __float_as_int(p.dis[j] * (p.w ? p.w[e] : 1.0f)));
+        }
     }
     for (int c = tid; c < 128; c += GC_THREADS) s_bias[c] = p.bias[c];
     if (CHAIN) {
@@ -146,7 +163,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
     // ---------------------------------------------------------------- phase 1: gather, four rows per warp at a time
     // Eight lanes own a row: load t of a lane covers columns [32 t + 4 l8, +4), so every load instruction reads one
     // whole 128-byte line per row and a lane keeps 2 edges x 4 loads in flight.
-    {
+    if (!GAT) {
         const int slot = lane >> 3, l8 = lane & 7;
         const float* xc = p.x + l8 * 4;
         for (int i = 0; i < 2; ++i) {
@@ -220,6 +237,93 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
             }
         }
     }
+    // ---------------------------------------------------------------- phase 1 (GAT): one row at a time per warp
+    // Softmax weights with one lane per incoming edge (the added self loop is edge number deg), then lane c owns input
+    // feature c and pulls (j, w_h) by shuffle -- gat_aggregate_kernel's scheme, the row written as fp16 hi / lo into
+    // K block 0 of the A operand (columns h * C + c, zero padded to 64) instead of to HBM.
+    if (GAT) {
+        // sixteen lanes per row, two rows per warp at a time (C <= 16 features; edges beyond 16 take another trip);
+        // loop bounds are the maximum over the two halves so every shuffle runs converged
+        constexpr int HEADS = 4;
+        const unsigned full = 0xffffffffu;
+        const int C = p.gat_c, half = lane >> 4, l16 = lane & 15;
+        for (int i = 0; i < GC_ROWS / 32; ++i) {
+            const int r = warp * (GC_ROWS / 16) + 2 * i + half, g = m0 + r;
+            const bool live = r < rows_here;
+            const int gs = live ? g : m0;
+            float acc[HEADS] = {0.f, 0.f, 0.f, 0.f}, den[HEADS] = {0.f, 0.f, 0.f, 0.f};
+            const int e0 = p.row_ptr[gs], deg = live ? p.row_ptr[gs + 1] - e0 : -1;   // dead rows: no trips count
+            const int deg_max = max(deg, __shfl_xor_sync(full, deg, 16));
+            float ad[HEADS], mx[HEADS];
+#pragma unroll
+            for (int h = 0; h < HEADS; ++h) {
+                ad[h] = p.a_dst[(size_t)gs * HEADS + h];
+                mx[h] = -INFINITY;
+            }
+            float wsum = 0.f;
+            for (int base = 0; base <= deg_max; base += 16) {
+                const int idx = base + l16;
+                const int j = idx < deg ? p.col[e0 + idx] : gs;
+                const bool ok = idx <= deg && !(idx < deg && j == gs);
+                const float4 as = *reinterpret_cast<const float4*>(p.a_src + (size_t)j * HEADS);
+                const float t[HEADS] = {as.x + ad[0], as.y + ad[1], as.z + ad[2], as.w + ad[3]};
+#pragma unroll
+                for (int h = 0; h < HEADS; ++h) mx[h] = fmaxf(mx[h], ok ? (t[h] > 0.f ? t[h] : 0.2f * t[h]) : -INFINITY);
+                if (idx < deg && j != gs) wsum += p.w ? p.w[e0 + idx] : 1.0f;
+            }
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+#pragma unroll
+                for (int h = 0; h < HEADS; ++h) mx[h] = fmaxf(mx[h], __shfl_xor_sync(full, mx[h], o));
+                wsum += __shfl_xor_sync(full, wsum, o);
+            }
+            if (l16 == 0 && live && p.dis_out) {   // gcn_norm: (sum of incoming weights + self weight)^-1/2, inf -> 0
+                const float rs = 1.0f / sqrtf(wsum + (p.self_w ? p.self_w[g] : 1.0f));
+                p.dis_out[g] = isinf(rs) ? 0.f : rs;
+            }
+            for (int base = 0; base <= deg_max; base += 16) {
+                const int idx = base + l16;
+                const int j = idx < deg ? p.col[e0 + idx] : gs;
+                const bool ok = idx <= deg && !(idx < deg && j == gs);
+                const float4 as = *reinterpret_cast<const float4*>(p.a_src + (size_t)j * HEADS);
+                const float t[HEADS] = {as.x + ad[0], as.y + ad[1], as.z + ad[2], as.w + ad[3]};
+                float wv[HEADS];
+#pragma unroll
+                for (int h = 0; h < HEADS; ++h) {
+                    const float l = t[h] > 0.f ? t[h] : 0.2f * t[h];
+                    wv[h] = ok ? expf(l - mx[h]) : 0.f;
+                    den[h] += wv[h];
+                }
+                const int cnt = min(16, deg_max + 1 - base);
+                for (int q = 0; q < cnt; ++q) {   // entries past this half's own edge count carry weight 0 and j = row itself
+                    const int jt = __shfl_sync(full, j, q, 16);
+                    const float xv = l16 < C ? p.x[(size_t)jt * C + l16] : 0.f;
+#pragma unroll
+                    for (int h = 0; h < HEADS; ++h) acc[h] = fmaf(__shfl_sync(full, wv[h], q, 16), xv, acc[h]);
+                }
+            }
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1)
+#pragma unroll
+                for (int h = 0; h < HEADS; ++h) den[h] += __shfl_xor_sync(full, den[h], o);
+            if (l16 < C) {
+#pragma unroll
+                for (int h = 0; h < HEADS; ++h) {
+                    const float v = live ? acc[h] / (den[h] + 1e-16f) : 0.f;
+                    const op_t hi = f2op(v), lo = f2op(v - op2f(hi));
+                    const int k = h * C + l16;
+                    const uint32_t off = sw128_offset(r, k >> 3) + (k & 7) * 2;
+                    *reinterpret_cast<op_t*>(a_tile + off) = hi;
+                    *reinterpret_cast<op_t*>(a_tile + 2 * GC_A_BLOCK + off) = lo;
+                }
+            }
+            for (int k = HEADS * C + l16; k < 64; k += 16) {   // zero padding of the K block
+                const uint32_t off = sw128_offset(r, k >> 3) + (k & 7) * 2;
+                *reinterpret_cast<op_t*>(a_tile + off) = f2op(0.f);
+                *reinterpret_cast<op_t*>(a_tile + 2 * GC_A_BLOCK + off) = f2op(0.f);
+            }
+        }
+    }
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -239,7 +343,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
             mbar_wait(w_full + stage, 0);
             tc_fence_after();
             gc_issue(tmem_base + tcol, smem_u32(a_tile), smem_u32(w_tile), n,
-                     stage == 2 ? umma_idesc_f16(GC_ROWS, 192) : umma_idesc_f16(GC_ROWS, 128));
+                     stage == 2 ? umma_idesc_f16(GC_ROWS, 192) : umma_idesc_f16(GC_ROWS, 128), GAT ? 1 : 2);
             tc_commit(acc + stage);
             if (stage + 1 < n_stage) {   // the weight buffer is free once these products retire
                 mbar_wait(acc + stage, 0);
@@ -318,17 +422,18 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
     GC_STAMP(9);
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
     }
 }
 
 int launch_gcn_layer_tc(const GcnLayer& p, cudaStream_t st) {
     if (p.M <= 0) return CM_OK;
-    CM_REQUIRE(p.x && p.row_ptr && p.col && p.dis && p.bias && p.w_split, "gcn layer: NULL operand");
+    CM_REQUIRE(p.x && p.row_ptr && p.col && p.bias && p.w_split, "gcn layer: NULL operand");
+    CM_REQUIRE(p.gat ? (p.a_src && p.a_dst && p.gat_c > 0 && 4 * p.gat_c <= 64 && p.out) : (p.dis != nullptr), "gcn layer: missing GAT / GCN operand");
     CM_REQUIRE(p.chain || p.out, "gcn layer: no output");
     CM_REQUIRE(!p.chain || (p.fc_split && (!p.do_heads || (p.h1_split && p.h1_bias))), "gcn layer: chained tail needs its weights");
     CUtensorMap mw, mfc, mh1;
-    int rc = make_map(&mw, p.w_split, GC_H, 3 * GC_H, 3 * GC_H, GC_H);
+    int rc = p.gat ? make_map(&mw, p.w_split, GC_H, 192, 192, GC_H) : make_map(&mw, p.w_split, GC_H, 3 * GC_H, 3 * GC_H, GC_H);
     if (rc != CM_OK) return rc;
     mfc = mw;
     mh1 = mw;
@@ -338,17 +443,21 @@ int launch_gcn_layer_tc(const GcnLayer& p, cudaStream_t st) {
     }
     static bool attr = false;
     if (!attr) {
-        cudaFuncSetAttribute(gcn_layer_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GC_SMEM);
-        cudaFuncSetAttribute(gcn_layer_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GC_SMEM);
+        cudaFuncSetAttribute(gcn_layer_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, GC_SMEM);
+        cudaFuncSetAttribute(gcn_layer_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GC_SMEM);
+        cudaFuncSetAttribute(gcn_layer_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GC_SMEM_GAT);
         attr = true;
     }
     const int grid = ceil_div(p.M, GC_ROWS);
-    if (p.chain) {
+    if (p.gat) {
+        CM_TIMED("gat_layer_tc", st);
+        gcn_layer_tc_kernel<2><<<grid, GC_THREADS, GC_SMEM_GAT, st>>>(mw, mfc, mh1, p);
+    } else if (p.chain) {
         CM_TIMED("gcn_tail_tc", st);
-        gcn_layer_tc_kernel<true><<<grid, GC_THREADS, GC_SMEM, st>>>(mw, mfc, mh1, p);
+        gcn_layer_tc_kernel<1><<<grid, GC_THREADS, GC_SMEM, st>>>(mw, mfc, mh1, p);
     } else {
         CM_TIMED("gcn_layer_tc", st);
-        gcn_layer_tc_kernel<false><<<grid, GC_THREADS, GC_SMEM, st>>>(mw, mfc, mh1, p);
+        gcn_layer_tc_kernel<0><<<grid, GC_THREADS, GC_SMEM, st>>>(mw, mfc, mh1, p);
     }
     return post_launch("gcn_layer_tc");
 }

@@ -20,6 +20,12 @@ struct GcnLayer {
     const op_t* w_split = nullptr;     // [128, 384] fp16 = [W_hi | W_hi | W_lo]
     const float* bias = nullptr;       // [128]
     float* out = nullptr;              // [M, 128] fp32 (plain layer)
+    // GAT layer (gat = 1): x is [M, gat_c] fp32 input features, a_src / a_dst [M, 4] the per-head attention logits,
+    // w_split [128, 3 x 64] = [W_hi | W_hi | W_lo] over the 4 x gat_c aggregated columns; dis_out receives deg^-1/2
+    int gat = 0, gat_c = 0;
+    const float* a_src = nullptr;
+    const float* a_dst = nullptr;
+    float* dis_out = nullptr;
     int chain = 0, do_heads = 0;
     const op_t* fc_split = nullptr;    // [128, 384]
     const float* fc_bias = nullptr;    // [128] or NULL

@@ -361,10 +361,6 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
         gat_logits_kernel<<<ceil_div((long long)M * hd, 256), 256, 0, st>>>(x, C, hd, blob + f.u_src, blob + f.u_dst, n_nodes_dev, M,
                                                                            ws.a_src, ws.a_dst);
     }
-    {
-        CM_TIMED("gat_aggregate", st);
-        gat_aggregate_kernel<4><<<warps_grid, 256, 0, st>>>(x, C, csr_row_ptr, csr_col, ws.a_src, ws.a_dst, n_nodes_dev, M, ws.z, f.zk);
-    }
     auto W = [&](size_t off) { return reinterpret_cast<const op_t*>(blob + off); };
     Dense d;
     d.M = M; d.m_dev = n_nodes_dev; d.relu = 1;
@@ -372,15 +368,26 @@ extern "C" int cm_gnn_forward(const cm_gnn_params* p, const void* folded, const 
     // rows, the last one carrying the row-local tail; any other shape takes the aggregate + dense kernels below.
     static const bool force_general = getenv("CM_GNN_GENERAL") != nullptr;   // test hook: exercise the unfused kernels
     const bool fused = H == 128 && p->num_classes == 2 && !force_general;
+    const bool fused_gat = fused && hd == 4 && f.zk == 192;   // GAT layer as gather -> tcgen05 too (gcn_tc.cu, MODE 2)
+    if (!fused_gat) {
+        CM_TIMED("gat_aggregate", st);
+        gat_aggregate_kernel<4><<<warps_grid, 256, 0, st>>>(x, C, csr_row_ptr, csr_col, ws.a_src, ws.a_dst, n_nodes_dev, M, ws.z, f.zk);
+    }
     float* emb = node_emb ? node_emb : (graph_emb ? ws.emb : nullptr);
     const bool want_heads = mask_out || instance_out || edge_out || mask_prob;
     d.A = ws.z; d.lda = f.zk; d.K = f.zk; d.W = W(f.wcat_h); d.bias = blob + f.bias1; d.N = H;
     if (fused) {
         float* xa = reinterpret_cast<float*>(ws.buf0);   // [M, 128] fp32 ping-pong inside the fp16 split buffers
         float* xb = reinterpret_cast<float*>(ws.buf1);
-        d.out_f32 = xa; d.ldo_f32 = H;
-        if ((rc = launch_dense(d, st)) != CM_OK) return rc;
-        {
+        if (fused_gat) {
+            GcnLayer ga;
+            ga.gat = 1; ga.gat_c = C; ga.x = x; ga.a_src = ws.a_src; ga.a_dst = ws.a_dst; ga.dis_out = ws.dis;
+            ga.row_ptr = csr_row_ptr; ga.col = csr_col; ga.w = csr_w; ga.self_w = self_w; ga.n_dev = n_nodes_dev; ga.M = M;
+            ga.w_split = W(f.wcat_h); ga.bias = blob + f.bias1; ga.out = xa;
+            if ((rc = launch_gcn_layer_tc(ga, st)) != CM_OK) return rc;
+        } else {
+            d.out_f32 = xa; d.ldo_f32 = H;
+            if ((rc = launch_dense(d, st)) != CM_OK) return rc;
             CM_TIMED("gcn_norm", st);
             gcn_norm_kernel<<<ceil_div(M, 256), 256, 0, st>>>(csr_row_ptr, csr_col, csr_w, self_w, n_nodes_dev, M, ws.dis);
         }
