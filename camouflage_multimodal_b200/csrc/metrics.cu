@@ -38,20 +38,42 @@ __global__ void __launch_bounds__(256) paint_metrics_kernel(const int* __restric
     const double thr = (double)threshold;
     int tp = 0, sp = 0, sg = 0, eq = 0;
     double ae = 0.0;
-    for (int p = blockIdx.x * 256 + threadIdx.x; p < HW; p += gridDim.x * 256) {
-        const int l = lab[p];
-        int idx = l;
-        if (idm) idx = (l >= 0 && l < cap) ? idm[l] : -1;
-        float pr = 0.f;
-        if (idx >= 0 && idx < nb) pr = mask_prob[n0 + idx];
-        if (pred_mask) pred_mask[(size_t)b * HW + p] = pr;
-        const double gv = (double)g[p] / 255.0;   // test.py:275
+    __shared__ double gt_lut[256];   // byte -> byte / 255.0 (test.py:275), the same fp64 quotient without a division per pixel
+    gt_lut[threadIdx.x] = (double)threadIdx.x / 255.0;
+    __syncthreads();
+    auto account = [&](float pr, unsigned gbyte) {
+        const double gv = gt_lut[gbyte];
         const bool pb = (double)pr > thr, gb = gv > thr;
         tp += pb && gb;
         sp += pb;
         sg += gb;
         eq += pb == gb;
         ae += fabs((double)pr - gv);
+    };
+    auto prob_of = [&](int l) {
+        int idx = l;
+        if (idm) idx = (l >= 0 && l < cap) ? idm[l] : -1;
+        return (idx >= 0 && idx < nb) ? mask_prob[n0 + idx] : 0.f;
+    };
+    if ((HW & 3) == 0 && ((reinterpret_cast<uintptr_t>(lab) | reinterpret_cast<uintptr_t>(g)) & 15) == 0) {
+        // four pixels per thread per trip: one 16-byte label load, one 4-byte gt load, the four dependent
+        // label -> node id -> probability gathers in flight together
+        for (int q = blockIdx.x * 256 + threadIdx.x; q < HW / 4; q += gridDim.x * 256) {
+            const int4 l4 = reinterpret_cast<const int4*>(lab)[q];
+            const unsigned g4 = reinterpret_cast<const unsigned*>(g)[q];
+            const float p0 = prob_of(l4.x), p1 = prob_of(l4.y), p2 = prob_of(l4.z), p3 = prob_of(l4.w);
+            if (pred_mask) reinterpret_cast<float4*>(pred_mask + (size_t)b * HW)[q] = make_float4(p0, p1, p2, p3);
+            account(p0, g4 & 255u);
+            account(p1, (g4 >> 8) & 255u);
+            account(p2, (g4 >> 16) & 255u);
+            account(p3, g4 >> 24);
+        }
+    } else {
+        for (int p = blockIdx.x * 256 + threadIdx.x; p < HW; p += gridDim.x * 256) {
+            const float pr = prob_of(lab[p]);
+            if (pred_mask) pred_mask[(size_t)b * HW + p] = pr;
+            account(pr, g[p]);
+        }
     }
     flush_partials(tp, sp, sg, eq, ae, counts + 4 * (size_t)b, abs_err + b);
 }
