@@ -19,7 +19,7 @@
 
 namespace cm {
 
-constexpr int KG_SUB = 64;   // nodes per shared-memory sub-block
+constexpr int KG_SUB = 64;   // nodes per shared-memory sub-block (32 measured no faster: 25.3 vs 24.8 us)
 
 template <int GS>
 __global__ void __launch_bounds__(256) kg2rg_partial_kernel(const float* __restrict__ s2, const op_t* __restrict__ v2, const float* __restrict__ y,

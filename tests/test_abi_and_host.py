@@ -181,3 +181,60 @@ def test_gradient_allreduce_gloo(tmp_path):
     for p in procs:
         out, _ = p.communicate(timeout=240)
         assert p.returncode == 0, out.decode()
+
+
+def test_embedding_matcher_matches_reference_class_golden():
+    """tests/golden/embedding_matcher.json holds the outputs of the reference's own EmbeddingMatcher
+    (tools/gen_golden_matcher.py); the mirror must reproduce every category choice, id list and tensor."""
+    import json
+    import sys
+    import numpy as np
+    import torch
+    from camouflage_multimodal_b200.embedding_cache import EmbeddingMatcher
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", "tools"))
+    import gen_golden_matcher as gg      # only its seeded input builder is used (no reference import at module level ...)
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "embedding_matcher.json")))
+    rg, kg = gg.inputs()
+    for tag, mapping in (("no_mapping", None), ("mapping", gold["mapping"])):
+        m = EmbeddingMatcher(rg, kg, category_mapping=mapping)
+        case = gold["cases"][tag]
+        for n in gold["names"]:
+            assert m.extract_category_from_filename(n) == case["category_of"][n]
+            e, ids = m.get_kg_embedding_for_image(n, use_all_categories=False)
+            assert ids == case["single"][n]["ids"]
+            np.testing.assert_allclose(e.numpy(), np.array(case["single"][n]["kg"], dtype=np.float32), rtol=0, atol=0)
+        e, ids = m.get_kg_embedding_for_image(gold["names"][0], use_all_categories=True)
+        assert ids == case["all"]["ids"]
+        np.testing.assert_array_equal(e.numpy(), np.array(case["all"]["kg"], dtype=np.float32))
+        for flag in (True, False):
+            md = m.create_matched_dataset(use_all_kg_categories=flag)
+            ref = case[f"matched_{flag}"]
+            assert len(md) == len(ref)
+            for r, g in zip(md, ref):
+                assert sorted(r.keys()) == g["keys"]
+                assert (r["image_name"], r["category_ids"], r["num_rg_nodes"], r["num_kg_categories"]) == \
+                       (g["image_name"], g["category_ids"], g["num_rg_nodes"], g["num_kg_categories"])
+                assert abs(float(r["kg_embeddings"].double().sum()) - g["kg_sum"]) < 1e-12
+                assert abs(float(r["rg_node_embeddings"].double().sum()) - g["rg_sum"]) < 1e-12
+
+
+def test_embedding_cache_files_round_trip(tmp_path):
+    import json
+    import torch
+    from camouflage_multimodal_b200.embedding_cache import EmbeddingMatcher, save_embedding_cache
+    gen = torch.Generator().manual_seed(5)
+    allemb = {f"COD10K-CAM-1-Aquatic-1-Batfish-{i}.jpg": {"node_embeddings": torch.randn((4 + i, 128), generator=gen),
+                                                          "graph_embedding": torch.randn((1, 128), generator=gen), "num_nodes": 4 + i}
+              for i in range(3)}
+    summary = save_embedding_cache(allemb, str(tmp_path))
+    assert summary["total_images"] == 3 and summary["embedding_dim"] == 128
+    loaded = torch.load(tmp_path / "all_rg_embeddings.pt", weights_only=False)
+    assert list(loaded) == list(allemb) and set(loaded[next(iter(loaded))]) == {"node_embeddings", "graph_embedding", "num_nodes"}
+    one = torch.load(tmp_path / "COD10K-CAM-1-Aquatic-1-Batfish-1_embedding.pt", weights_only=False)
+    assert one["num_nodes"] == 5 and one["embedding_dim"] == 128 and one["image_name"].endswith("Batfish-1.jpg")
+    assert json.load(open(tmp_path / "embedding_summary.json"))["images"][one["image_name"]]["node_embedding_shape"] == [5, 128]
+    kg = {"Fish": torch.randn(128, generator=gen), "Bird": torch.randn(128, generator=gen)}
+    torch.save(kg, tmp_path / "kg.pt")
+    m = EmbeddingMatcher(str(tmp_path / "all_rg_embeddings.pt"), str(tmp_path / "kg.pt"))
+    rows, ptr, kgb = m.matched_ragged_batch(list(allemb), device="cpu")
+    assert rows.shape == (4 + 5 + 6, 128) and ptr.tolist() == [0, 4, 9, 15] and kgb.shape == (1, 2, 128)
