@@ -134,6 +134,9 @@ SIGNATURES = {
     "cm_metrics_dense": (_i, [_fp, _fp, _i, _i64, _f, _fp, _fp, _fp]),
     "cm_metrics_finalize": (_i, [_fp, _fp, _i, _i64, _fp, _fp, _fp]),
     "cm_class_confusion": (_i, [_fp, _fp, _i, _i, _fp, _fp]),
+    "cm_slic_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "cm_slic": (_i, [_fp, _i, _i, _i, _i, C.c_double, C.c_double, _i, _fp, _sz, _fp, _fp]),
+    "cm_slic_enforce_connectivity": (_i, [_fp, _i, _i, _i, _i, _i, _i, _fp, _fp, _fp]),
     "cm_region_targets": (_i, [_fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _fp, _fp, _fp, _fp]),
     "cm_rg_node_loss": (_i, [_fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, C.POINTER(RgLossConfig), _fp, _sz, _fp, _fp, _fp, _fp, _fp]),
     "cm_image_loss": (_i, [_fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, C.POINTER(ImageLossConfig), _fp, _fp, _fp, _fp, _fp, _fp]),

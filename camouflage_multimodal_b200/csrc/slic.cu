@@ -1,0 +1,439 @@
+// SLIC superpixels on the device -- skimage.segmentation.slic(img_u8, n_segments, compactness, sigma)
+// as the reference calls it (models/region_graph/extract_rg_embeddings.py:143-144), restated in oracle/slic.py.
+// float64 throughout, every sum in the order of the sequential algorithm (no FMA contraction), so the result equals the
+// oracle's up to libm differences in pow / cbrt:
+//   slic_float_kernel     byte * (1/255), then the singleton z pass of the 3-D Gaussian (sum of all taps on one value)
+//   slic_blur_kernel      scipy correlate1d (symmetric form), mode='reflect', along y then x, per channel
+//   slic_lab_kernel       rgb2lab (sRGB, D65), * 1/compactness
+//   slic_assign_kernel    per pixel: the cluster of least distance among those whose +-2*step window holds the pixel,
+//                         lowest index on ties (the sequential loop's strict '<' in index order)
+//   slic_update_kernel    one thread per cluster walks the OLD window in raster order: sums / count -> new centre
+//   slic_connect_kernel   _enforce_label_connectivity_cython: raster-order BFS, one thread per image (the algorithm is
+//                         sequential by definition: the label a small segment joins depends on the visiting order)
+#include <math.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace cm {
+
+constexpr int SLIC_MAX_RADIUS = 16;
+struct SlicGauss {
+    double w[2 * SLIC_MAX_RADIUS + 1];   // index r + radius
+    int radius;
+};
+struct SlicGrid {
+    int start_y, start_x, seed_step_y, seed_step_x, ny, nx, K;   // seeds
+    int step_y, step_x, step;                                    // window half-extent / spatial weight
+};
+
+__device__ __forceinline__ int slic_reflect(int i, int n) {   // scipy mode='reflect': (d c b a | a b c d | d c b a)
+    while (i < 0 || i >= n) {
+        if (i < 0) i = -i - 1;
+        if (i >= n) i = 2 * n - 1 - i;
+    }
+    return i;
+}
+
+// out [B,H,W,3] f64
+__global__ void slic_float_kernel(const uint8_t* __restrict__ img, long long n, const SlicGauss g, int z_pass, double* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double v = __dmul_rn((double)img[i], 1.0 / 255.0);
+    if (z_pass) {   // every tap of the z axis (length 1, reflect) reads the same value
+        double t = __dmul_rn(v, g.w[g.radius]);
+        for (int j = g.radius; j >= 1; --j) t = __dadd_rn(t, __dmul_rn(__dadd_rn(v, v), g.w[g.radius - j]));
+        v = t;
+    }
+    out[i] = v;
+}
+// axis 0: along y, axis 1: along x; in / out [B,H,W,3]
+__global__ void slic_blur_kernel(const double* __restrict__ in, int H, int W, int axis, const SlicGauss g, double* __restrict__ out) {
+    const int xc = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;   // xc = x * 3 + channel
+    if (xc >= 3 * W) return;
+    const int x = xc / 3, c = xc - 3 * x;
+    const double* p = in + (size_t)b * H * W * 3;
+    auto at = [&](int yy, int xx) { return p[((size_t)yy * W + xx) * 3 + c]; };
+    double t = __dmul_rn(at(y, x), g.w[g.radius]);
+    for (int j = g.radius; j >= 1; --j) {
+        double a, d;
+        if (axis == 0) {
+            a = at(slic_reflect(y - j, H), x);
+            d = at(slic_reflect(y + j, H), x);
+        } else {
+            a = at(y, slic_reflect(x - j, W));
+            d = at(y, slic_reflect(x + j, W));
+        }
+        t = __dadd_rn(t, __dmul_rn(__dadd_rn(a, d), g.w[g.radius - j]));
+    }
+    out[((size_t)b * H + y) * W * 3 + xc] = t;
+}
+// in place: rgb -> Lab * ratio
+__global__ void slic_lab_kernel(double* __restrict__ v, long long npx, double ratio) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npx) return;
+    double c[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double a = v[3 * i + k];
+        c[k] = a > 0.04045 ? pow(__ddiv_rn(__dadd_rn(a, 0.055), 1.055), 2.4) : __ddiv_rn(a, 12.92);
+    }
+    const double M[3][3] = {{0.412453, 0.357580, 0.180423}, {0.212671, 0.715160, 0.072169}, {0.019334, 0.119193, 0.950227}};
+    const double white[3] = {0.95047, 1.0, 1.08883};
+    double f[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        double t = __dadd_rn(__dadd_rn(__dmul_rn(c[0], M[k][0]), __dmul_rn(c[1], M[k][1])), __dmul_rn(c[2], M[k][2]));
+        t = __ddiv_rn(t, white[k]);
+        f[k] = t > 0.008856 ? cbrt(t) : __dadd_rn(__dmul_rn(7.787, t), 16.0 / 116.0);
+    }
+    v[3 * i] = __dmul_rn(__dadd_rn(__dmul_rn(116.0, f[1]), -16.0), ratio);
+    v[3 * i + 1] = __dmul_rn(__dmul_rn(500.0, __dadd_rn(f[0], -f[1])), ratio);
+    v[3 * i + 2] = __dmul_rn(__dmul_rn(200.0, __dadd_rn(f[1], -f[2])), ratio);
+}
+
+// seg [B,K,5] = (y, x, L, a, b)
+__global__ void slic_seed_kernel(SlicGrid g, int batch, double* __restrict__ seg) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= batch * g.K) return;
+    const int k = i % g.K;
+    double* s = seg + (size_t)i * 5;
+    s[0] = (double)(g.start_y + (k / g.nx) * g.seed_step_y);
+    s[1] = (double)(g.start_x + (k % g.nx) * g.seed_step_x);
+    s[2] = s[3] = s[4] = 0.0;
+}
+
+// window of cluster centre c along an axis of length n: [max(c - 2 step, 0), min(c + 2 step + 1, n)) truncated to int
+__device__ __forceinline__ void slic_window(double c, int step, int n, int* lo, int* hi) {
+    if (!isfinite(c)) {   // an emptied cluster (0 / 0): no window
+        *lo = 0;
+        *hi = 0;
+        return;
+    }
+    *lo = (int)fmax(c - 2.0 * step, 0.0);
+    *hi = (int)fmin(c + 2.0 * step + 1.0, (double)n);
+}
+
+// one CTA = 16 x 16 pixel tile; clusters whose window meets the tile are listed in shared memory in index order
+__global__ void __launch_bounds__(256) slic_assign_kernel(const double* __restrict__ feat, const double* __restrict__ seg, SlicGrid g, int H,
+                                                          int W, int* __restrict__ nearest) {
+    __shared__ int s_list[1024];
+    __shared__ int s_count;
+    __shared__ double s_seg[64][5];
+    const int b = blockIdx.z, ty0 = blockIdx.y * 16, tx0 = blockIdx.x * 16;
+    const int tid = threadIdx.x, y = ty0 + (tid >> 4), x = tx0 + (tid & 15);
+    const double* sg = seg + (size_t)b * g.K * 5;
+    // ordered compaction of the candidate clusters (256 at a time, ballot-free: prefix by a serial scan of flags in smem)
+    __shared__ unsigned char s_flag[256];
+    if (tid == 0) s_count = 0;
+    __syncthreads();
+    for (int k0 = 0; k0 < g.K; k0 += 256) {
+        const int k = k0 + tid;
+        bool hit = false;
+        if (k < g.K) {
+            int ylo, yhi, xlo, xhi;
+            slic_window(sg[k * 5], g.step_y, H, &ylo, &yhi);
+            slic_window(sg[k * 5 + 1], g.step_x, W, &xlo, &xhi);
+            hit = ylo < ty0 + 16 && yhi > ty0 && xlo < tx0 + 16 && xhi > tx0;
+        }
+        s_flag[tid] = hit;
+        __syncthreads();
+        if (tid == 0) {
+            int n = s_count;
+            for (int i = 0; i < 256; ++i)
+                if (s_flag[i] && n < 1024) s_list[n++] = k0 + i;
+            s_count = n;
+        }
+        __syncthreads();
+    }
+    const int n_cand = s_count;
+    const bool in = y < H && x < W;
+    double f0 = 0, f1 = 0, f2 = 0;
+    if (in) {
+        const double* p = feat + (((size_t)b * H + y) * W + x) * 3;
+        f0 = p[0];
+        f1 = p[1];
+        f2 = p[2];
+    }
+    const double sw = 1.0 / (double)(g.step * g.step);
+    double best = 1.7976931348623157e308;
+    int best_k = -1;
+    for (int c0 = 0; c0 < n_cand; c0 += 64) {
+        const int nc = min(64, n_cand - c0);
+        __syncthreads();
+        for (int i = tid; i < nc * 5; i += 256) s_seg[i / 5][i % 5] = sg[(size_t)s_list[c0 + i / 5] * 5 + i % 5];
+        __syncthreads();
+        if (in) {
+            for (int i = 0; i < nc; ++i) {
+                const double cy = s_seg[i][0], cx = s_seg[i][1];
+                int ylo, yhi, xlo, xhi;
+                slic_window(cy, g.step_y, H, &ylo, &yhi);
+                slic_window(cx, g.step_x, W, &xlo, &xhi);
+                if (y < ylo || y >= yhi || x < xlo || x >= xhi) continue;
+                const double dy = __dadd_rn(cy, -(double)y), dx = __dadd_rn(cx, -(double)x);
+                double d = __dmul_rn(__dadd_rn(__dmul_rn(dy, dy), __dmul_rn(dx, dx)), sw);
+                const double e0 = __dadd_rn(f0, -s_seg[i][2]), e1 = __dadd_rn(f1, -s_seg[i][3]), e2 = __dadd_rn(f2, -s_seg[i][4]);
+                const double dc = __dadd_rn(__dadd_rn(__dmul_rn(e0, e0), __dmul_rn(e1, e1)), __dmul_rn(e2, e2));
+                d = __dadd_rn(d, dc);
+                if (best > d) {   // strict: the lowest cluster index keeps a tie
+                    best = d;
+                    best_k = s_list[c0 + i];
+                }
+            }
+        }
+    }
+    if (in) nearest[((size_t)b * H + y) * W + x] = best_k;
+}
+
+// one thread per (image, cluster): raster-order sums over the cluster's OLD window (every member lies inside it)
+__global__ void slic_update_kernel(const double* __restrict__ feat, const int* __restrict__ nearest, SlicGrid g, int batch, int H, int W,
+                                   const double* __restrict__ seg_old, double* __restrict__ seg_new) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= batch * g.K) return;
+    const int b = i / g.K, k = i - b * g.K;
+    const double* so = seg_old + (size_t)i * 5;
+    int ylo, yhi, xlo, xhi;
+    slic_window(so[0], g.step_y, H, &ylo, &yhi);
+    slic_window(so[1], g.step_x, W, &xlo, &xhi);
+    double sy = 0, sx = 0, s0 = 0, s1 = 0, s2 = 0, n = 0;
+    for (int y = ylo; y < yhi; ++y)
+        for (int x = xlo; x < xhi; ++x) {
+            const size_t p = ((size_t)b * H + y) * W + x;
+            if (nearest[p] != k) continue;
+            n = __dadd_rn(n, 1.0);
+            sy = __dadd_rn(sy, (double)y);
+            sx = __dadd_rn(sx, (double)x);
+            s0 = __dadd_rn(s0, feat[3 * p]);
+            s1 = __dadd_rn(s1, feat[3 * p + 1]);
+            s2 = __dadd_rn(s2, feat[3 * p + 2]);
+        }
+    double* sn = seg_new + (size_t)i * 5;
+    sn[0] = __ddiv_rn(sy, n);   // 0 / 0 = NaN for an emptied cluster, as in the reference loop
+    sn[1] = __ddiv_rn(sx, n);
+    sn[2] = __ddiv_rn(s0, n);
+    sn[3] = __ddiv_rn(s1, n);
+    sn[4] = __ddiv_rn(s2, n);
+}
+
+// One CTA per image, thread 0 walks (the other lanes only initialise / copy).  `lab` holds any labels (equality is all
+// that matters); the new labels live in shared memory as int16 while the image fits (H*W <= 96K), else in `out` itself.
+// coords [B, max_size] packed y << 16 | x.
+template <bool SMEM>
+__global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict__ labels_in, int H, int W, int min_size, int max_size,
+                                                           int start_label, int* __restrict__ coords, int* __restrict__ out) {
+    extern __shared__ short s_out[];
+    const int b = blockIdx.x, n = H * W;
+    const int* lab = labels_in + (size_t)b * n;
+    int* o = out + (size_t)b * n;
+    int* q = coords + (size_t)b * max(max_size, 1);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        if (SMEM) s_out[i] = -1; else o[i] = -1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        auto get = [&](int i) -> int { return SMEM ? (int)s_out[i] : o[i]; };
+        auto put = [&](int i, int v) { if (SMEM) s_out[i] = (short)v; else o[i] = v; };
+        int cur = start_label;
+        const int ddy[4] = {0, 0, 1, -1}, ddx[4] = {1, -1, 0, 0};
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                if (get(y * W + x) >= 0) continue;
+                int adjacent = 0;
+                const int label = lab[y * W + x];
+                put(y * W + x, cur);
+                int size = 1, visited = 0;
+                q[0] = (y << 16) | x;
+                while (visited < size && size < max_size) {
+                    const int py = q[visited] >> 16, px = q[visited] & 0xffff;
+                    for (int i = 0; i < 4; ++i) {
+                        const int qy = py + ddy[i], qx = px + ddx[i];
+                        if (qy < 0 || qy >= H || qx < 0 || qx >= W) continue;
+                        const int oq = get(qy * W + qx);
+                        if (oq == -1 && lab[qy * W + qx] == label) {
+                            put(qy * W + qx, cur);
+                            q[size++] = (qy << 16) | qx;
+                            if (size >= max_size) break;
+                        } else if (oq >= 0 && oq != cur) {
+                            adjacent = oq;
+                        }
+                    }
+                    ++visited;
+                }
+                if (size < min_size) {
+                    for (int i = 0; i < size; ++i) put((q[i] >> 16) * W + (q[i] & 0xffff), adjacent);
+                } else {
+                    ++cur;
+                }
+            }
+    }
+    __syncthreads();
+    if (SMEM)
+        for (int i = threadIdx.x; i < n; i += blockDim.x) o[i] = s_out[i];
+}
+
+static int launch_slic_connect(const int* labels_in, int batch, int h, int w, int min_size, int max_size, int start_label, int* coords,
+                               int* out, cudaStream_t st) {
+    const size_t smem = (size_t)h * w * sizeof(short);
+    CM_TIMED("slic_connectivity", st);
+    if (smem <= 192 * 1024 && (long long)h * w + start_label < 32767) {
+        static bool attr = false;
+        if (!attr) {
+            cudaFuncSetAttribute(slic_connect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 192 * 1024);
+            attr = true;
+        }
+        slic_connect_kernel<true><<<batch, 256, smem, st>>>(labels_in, h, w, min_size, max_size, start_label, coords, out);
+    } else {
+        slic_connect_kernel<false><<<batch, 256, 0, st>>>(labels_in, h, w, min_size, max_size, start_label, coords, out);
+    }
+    return CM_OK;
+}
+
+// skimage.util.regular_grid for the volume (1, H, W): seed start and step per axis
+static void regular_grid_hw(int H, int W, int n_points, int* start_y, int* start_x, int* step_y, int* step_x) {
+    double dims[3] = {1.0, (double)std::min(H, W), (double)std::max(H, W)};   // ascending
+    double space = dims[0] * dims[1] * dims[2];
+    double st[3];
+    if (space <= (double)n_points) {
+        *start_y = *start_x = 0;
+        *step_y = *step_x = 1;
+        return;
+    }
+    for (int i = 0; i < 3; ++i) st[i] = pow(space / n_points, 1.0 / 3.0);
+    if (dims[0] < st[0] || dims[1] < st[1] || dims[2] < st[2]) {
+        for (int d = 0; d < 3; ++d) {
+            st[d] = dims[d];
+            double rest = 1.0;
+            for (int e = d + 1; e < 3; ++e) rest *= dims[e];
+            for (int e = d + 1; e < 3; ++e) st[e] = pow(rest / n_points, 1.0 / (double)(3 - d - 1));
+            bool ok = true;
+            for (int e = 0; e < 3; ++e) ok = ok && dims[e] >= st[e];
+            if (ok) break;
+        }
+    }
+    int starts[3], steps[3];
+    for (int i = 0; i < 3; ++i) {
+        starts[i] = (int)floor(st[i] / 2.0);
+        steps[i] = (int)nearbyint(st[i]);   // np.round: half to even
+    }
+    const int iy = H <= W ? 1 : 2, ix = H <= W ? 2 : 1;   // position of each axis in the sorted order (ties: y first)
+    *start_y = starts[iy];
+    *step_y = std::max(steps[iy], 1);
+    *start_x = starts[ix];
+    *step_x = std::max(steps[ix], 1);
+}
+
+struct SlicWs {
+    double *a, *b, *seg0, *seg1;
+    int *nearest, *coords;
+    size_t total;
+};
+static SlicWs carve_slic(void* ws, int batch, int h, int w, int K, int max_size) {
+    Carver c(ws);
+    SlicWs r;
+    const size_t n = (size_t)batch * h * w;
+    r.a = c.take<double>(n * 3);
+    r.b = c.take<double>(n * 3);
+    r.seg0 = c.take<double>((size_t)batch * K * 5);
+    r.seg1 = c.take<double>((size_t)batch * K * 5);
+    r.nearest = c.take<int>(n);
+    r.coords = c.take<int>((size_t)batch * std::max(max_size, 1));
+    r.total = align_up(c.off, 256);
+    return r;
+}
+static SlicGrid slic_grid(int h, int w, int n_segments) {
+    SlicGrid g;
+    regular_grid_hw(h, w, n_segments, &g.start_y, &g.start_x, &g.seed_step_y, &g.seed_step_x);
+    g.ny = (h - g.start_y + g.seed_step_y - 1) / g.seed_step_y;
+    g.nx = (w - g.start_x + g.seed_step_x - 1) / g.seed_step_x;
+    g.K = g.ny * g.nx;
+    int sy, sx;
+    regular_grid_hw(h, w, g.K, &sy, &sx, &g.step_y, &g.step_x);   // the clustering loop recomputes its steps from the seed count
+    g.step = std::max(std::max(g.seed_step_y, g.seed_step_x), 1);
+    return g;
+}
+
+}  // namespace cm
+
+extern "C" size_t cm_slic_workspace_bytes(int batch, int h, int w, int n_segments) {
+    if (batch <= 0 || h <= 0 || w <= 0 || n_segments <= 0) return 0;
+    const cm::SlicGrid g = cm::slic_grid(h, w, n_segments);
+    const int max_size = (int)(3.0 * ((double)h * w / g.K));
+    return cm::carve_slic(nullptr, batch, h, w, g.K, max_size).total;
+}
+
+extern "C" int cm_slic(const uint8_t* image_u8, int batch, int h, int w, int n_segments, double compactness, double sigma,
+                       int max_num_iter, void* workspace, size_t workspace_bytes, int32_t* labels, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(image_u8 && workspace && labels, "cm_slic: NULL pointer");
+    CM_REQUIRE(batch > 0 && h > 0 && w > 0 && h < 65536 && w < 65536 && n_segments > 0 && compactness > 0.0 && sigma >= 0.0 && max_num_iter > 0,
+               "cm_slic: bad arguments");
+    const SlicGrid g = slic_grid(h, w, n_segments);
+    const double segment_size = (double)h * w / g.K;
+    const int min_size = (int)(0.5 * segment_size), max_size = (int)(3.0 * segment_size);
+    SlicWs ws = carve_slic(workspace, batch, h, w, g.K, max_size);
+    if (workspace_bytes < ws.total) {
+        set_error("cm_slic: workspace %zu < %zu bytes", workspace_bytes, ws.total);
+        return CM_ERR_WORKSPACE;
+    }
+    SlicGauss gw;
+    gw.radius = 0;
+    gw.w[0] = 1.0;
+    if (sigma > 0.0) {   // scipy _gaussian_kernel1d, truncate = 4
+        gw.radius = (int)(4.0 * sigma + 0.5);
+        CM_REQUIRE(gw.radius <= SLIC_MAX_RADIUS, "cm_slic: sigma %.3f needs a kernel radius above %d", sigma, SLIC_MAX_RADIUS);
+        const int nw = 2 * gw.radius + 1;
+        for (int r = -gw.radius; r <= gw.radius; ++r) gw.w[r + gw.radius] = exp(-0.5 / (sigma * sigma) * (double)(r * r));
+        // phi.sum() in numpy's order: eight running sums over blocks of 8, combined as a tree, then the remainder
+        double sum = 0.0;
+        if (nw < 8) {
+            for (int i = 0; i < nw; ++i) sum += gw.w[i];
+        } else {
+            double r8[8];
+            for (int j = 0; j < 8; ++j) r8[j] = gw.w[j];
+            int i = 8;
+            for (; i < nw - (nw % 8); i += 8)
+                for (int j = 0; j < 8; ++j) r8[j] += gw.w[i + j];
+            sum = ((r8[0] + r8[1]) + (r8[2] + r8[3])) + ((r8[4] + r8[5]) + (r8[6] + r8[7]));
+            for (; i < nw; ++i) sum += gw.w[i];
+        }
+        for (int r = 0; r < nw; ++r) gw.w[r] /= sum;
+    }
+    cudaStream_t st = as_stream(stream);
+    const long long npx = (long long)batch * h * w;
+    {
+        CM_TIMED("slic_preprocess", st);
+        slic_float_kernel<<<ceil_div(npx * 3, 256), 256, 0, st>>>(image_u8, npx * 3, gw, sigma > 0.0 ? 1 : 0, ws.a);
+        if (sigma > 0.0) {
+            dim3 grid(ceil_div(3 * w, 128), h, batch);
+            slic_blur_kernel<<<grid, 128, 0, st>>>(ws.a, h, w, 0, gw, ws.b);
+            slic_blur_kernel<<<grid, 128, 0, st>>>(ws.b, h, w, 1, gw, ws.a);
+        }
+        slic_lab_kernel<<<ceil_div(npx, 256), 256, 0, st>>>(ws.a, npx, 1.0 / compactness);
+        slic_seed_kernel<<<ceil_div(batch * g.K, 256), 256, 0, st>>>(g, batch, ws.seg0);
+    }
+    double *cur = ws.seg0, *nxt = ws.seg1;
+    {
+        CM_TIMED("slic_iterations", st);
+        for (int it = 0; it < max_num_iter; ++it) {
+            slic_assign_kernel<<<dim3(ceil_div(w, 16), ceil_div(h, 16), batch), 256, 0, st>>>(ws.a, cur, g, h, w, ws.nearest);
+            slic_update_kernel<<<ceil_div(batch * g.K, 64), 64, 0, st>>>(ws.a, ws.nearest, g, batch, h, w, cur, nxt);
+            std::swap(cur, nxt);
+        }
+    }
+    // labels = nearest + 1 only shifts every value: equality tests are unchanged, so the BFS reads `nearest` itself
+    launch_slic_connect(ws.nearest, batch, h, w, min_size, max_size, 1, ws.coords, labels, st);
+    return post_launch("cm_slic");
+}
+
+extern "C" int cm_slic_enforce_connectivity(const int32_t* labels_in, int batch, int h, int w, int min_size, int max_size,
+                                            int start_label, int32_t* coords_workspace, int32_t* labels_out, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(labels_in && coords_workspace && labels_out, "cm_slic_enforce_connectivity: NULL pointer");
+    CM_REQUIRE(batch > 0 && h > 0 && w > 0 && h < 65536 && w < 65536 && max_size > 0 && start_label >= 0, "cm_slic_enforce_connectivity: bad arguments");
+    launch_slic_connect(labels_in, batch, h, w, min_size, max_size, start_label, coords_workspace, labels_out, as_stream(stream));
+    return post_launch("cm_slic_enforce_connectivity");
+}

@@ -2,9 +2,9 @@
 
 Mirrors ``models/region_graph/extract_rg_embeddings.py`` of the reference: ``create_region_graph`` (:138-246)
 from the label map onward, and ``RegionGraphGNN`` (:27-135) with the same constructor, methods, return
-arities and PyG state-dict key names (``conv1.lin.weight``, ``conv1.att_src`` ...).  SLIC is the step before the hot
-path: the label map is an input here.  The Canny edge map (8f N2, ``:152``) is computed on the
-device by ``canny_edges`` / ``cm_canny`` when the caller does not pass one.
+arities and PyG state-dict key names (``conv1.lin.weight``, ``conv1.att_src`` ...).  The two steps before the hot
+path -- SLIC (``:143-144``) and Canny (8f N2, ``:152``) -- run on the device too (``slic_segments`` /
+``cm_slic``, ``canny_edges`` / ``cm_canny``) when the caller does not pass a label map / edge map.
 """
 from __future__ import annotations
 
@@ -157,6 +157,25 @@ def canny_edges(images, sigma: float = 2.0, low_threshold: float = 0.1, high_thr
     return edges
 
 
+def slic_segments(images_u8, n_segments: int = 500, compactness: float = 10.0, sigma: float = 1.0, max_num_iter: int = 10, out=None):
+    """``skimage.segmentation.slic(img_u8, n_segments, compactness, sigma)`` of every image
+    (extract_rg_embeddings.py:143-144) on the device: ``images_u8`` ``[B,H,W,3]`` uint8 -> ``[B,H,W]`` int32 labels
+    (from 1, connectivity enforced).  ``cm_slic``; see oracle/slic.py for the restated algorithm (parity unpinned)."""
+    lib = _lib.load()
+    _lib.require_cuda(images_u8, "images")
+    if images_u8.dim() != 4 or images_u8.shape[-1] != 3 or images_u8.dtype != torch.uint8:
+        raise ValueError(f"images must be [B,H,W,3] uint8, got {tuple(images_u8.shape)} {images_u8.dtype}")
+    images_u8 = images_u8.contiguous()
+    B, H, W, _ = images_u8.shape
+    dev = images_u8.device
+    labels = out if out is not None else torch.empty((B, H, W), dtype=torch.int32, device=dev)
+    ws_bytes = lib.cm_slic_workspace_bytes(B, H, W, int(n_segments))
+    ws = WORKSPACE.get(dev, "slic", ws_bytes)
+    _lib.check(lib.cm_slic(_lib.ptr(images_u8), B, H, W, int(n_segments), float(compactness), float(sigma), int(max_num_iter),
+                           _lib.ptr(ws), ws_bytes, _lib.ptr(labels), _lib.stream_ptr(dev)), "cm_slic")
+    return labels
+
+
 class _CsrData(Data):
     """``Data`` that also carries the target-keyed CSR the build produced, so the GNN need not rebuild it."""
 
@@ -164,17 +183,17 @@ class _CsrData(Data):
 def create_region_graph(image, n_segments=500, segments=None, edges=None, device=None):
     """Drop-in for ``create_region_graph(image, n_segments) -> (Data, segments)`` (extract_rg_embeddings.py:138).
 
-    ``image``: ``[H,W,3]`` float array in [0,1].  ``segments`` (the SLIC label map, :143-144) must be supplied: SLIC is
-    not part of this path yet.  ``edges`` (the boolean Canny map, :152) is computed on the device by
-    ``canny_edges`` (``cm_canny``, sigma 2 like the reference) unless given.  The returned ``Data`` lives on the CUDA
+    ``image``: ``[H,W,3]`` float array in [0,1].  ``segments`` (the SLIC label map, :143-144) is computed on the device
+    by ``slic_segments`` (``cm_slic``) from ``(image * 255).astype(uint8)`` like the reference unless given, ``edges``
+    (the boolean Canny map, :152) by ``canny_edges`` (``cm_canny``, sigma 2) unless given.  The returned ``Data`` lives on the CUDA
     device; ``edge_index`` is in canonical (sorted) order and ``edge_attr`` is ``[E,1]``.
     """
-    if segments is None:
-        raise NotImplementedError(
-            "create_region_graph needs the superpixel label map (`segments`): SLIC is upstream of the B200 hot path "
-            "(SURVEY.md 8f N1)")
     dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
     img = torch.as_tensor(np.asarray(image), dtype=torch.float32).to(dev)[None]
+    if segments is None:
+        img_u8 = torch.as_tensor((np.asarray(image) * 255).astype(np.uint8)).to(dev)[None]        # :143
+        lab = slic_segments(img_u8, n_segments=n_segments, compactness=10.0, sigma=1.0)         # :144
+        segments = lab[0].cpu().numpy().astype(np.int64)
     seg_np = np.asarray(segments)
     lab = torch.as_tensor(seg_np.astype(np.int32)).to(dev)[None]
     can = canny_edges(img, sigma=2.0) if edges is None else torch.as_tensor(np.asarray(edges).astype(np.uint8)).to(dev)[None]

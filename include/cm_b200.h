@@ -381,6 +381,22 @@ int cm_adamw_step(float* const* params, const float* const* grads, float* const*
                   const int64_t* numel, int n_tensors, int64_t max_numel, const cm_adamw_config* cfg, int step,
                   double* norm_workspace, float* norm_out, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * SLIC superpixels -- skimage.segmentation.slic(img_u8, n_segments=500, compactness=10, sigma=1) as
+ * called at models/region_graph/extract_rg_embeddings.py:143-144 (img_as_float -> Gaussian (reflect) -> rgb2lab ->
+ * max_num_iter k-means rounds on the regular seed grid -> connectivity enforcement, labels from 1; label 0 can appear
+ * where a first small segment has no labelled neighbour yet, as in skimage).  float64, sequential summation order.
+ * image_u8 [B,H,W,3]; labels [B,H,W] int32 out.
+ * ------------------------------------------------------------------------------------------------ */
+size_t cm_slic_workspace_bytes(int batch, int h, int w, int n_segments);
+int cm_slic(const uint8_t* image_u8, int batch, int h, int w, int n_segments, double compactness, double sigma,
+            int max_num_iter, void* workspace, size_t workspace_bytes, int32_t* labels, void* stream);
+/* The last stage on its own (skimage _enforce_label_connectivity_cython, 4-connected raster-order BFS): segments
+ * smaller than min_size join the last labelled neighbour met, segments are cut at max_size pixels.
+ * coords_workspace: batch * max_size int32. */
+int cm_slic_enforce_connectivity(const int32_t* labels_in, int batch, int h, int w, int min_size, int max_size,
+                                 int start_label, int32_t* coords_workspace, int32_t* labels_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,182 @@
+"""ORACLE (test infrastructure only): CPU restatement of ``skimage.segmentation.slic(img_u8, n_segments=500,
+compactness=10, sigma=1)`` as the reference calls it (models/region_graph/extract_rg_embeddings.py:143-144).
+
+PARITY UNPINNED: scikit-image (requirements: >=0.21.0, not vendored, not installable here) is absent, so this file
+restates the published algorithm of skimage 0.21 (``segmentation/slic_superpixels.py``, ``segmentation/_slic.pyx``,
+``util/_regular_grid.py``, ``color/colorconv.py``) from its documented behaviour:
+  img_as_float (uint8 * (1/255)) -> Gaussian sigma=(1,1,1,0) over the [1,H,W,3] volume, mode='reflect' (scipy
+  ``gaussian_filter``, truncate 4) -> rgb2lab (D65, 2 deg) -> * 1/compactness -> seeds on ``regular_grid`` with colour 0
+  -> max_num_iter = 10 rounds of [assign: clusters in index order, window +-2*step around the truncated centre, strict
+  '<' so the lowest index wins ties; update: raster-order sums / counts] -> labels + 1 ->
+  ``_enforce_label_connectivity_cython`` (raster-order BFS, min_size = 0.5 * HW / K, max_size = 3 * HW / K).
+The only check available is statistical (region counts against the reference's ``embedding_summary.json`` range,
+SURVEY 8f N1) plus the invariants tested in tests/.  Arithmetic is float64 with explicit operation order so the CUDA
+kernels can be compared with it bit for bit up to libm differences in pow / cbrt.
+"""
+import numpy as np
+from scipy import ndimage as ndi
+
+XYZ_FROM_RGB = np.array([[0.412453, 0.357580, 0.180423], [0.212671, 0.715160, 0.072169], [0.019334, 0.119193, 0.950227]])
+WHITE_D65 = np.array([0.95047, 1.0, 1.08883])
+
+
+def regular_grid_steps(shape, n_points):
+    """skimage.util.regular_grid for an ascending-sorted shape like (1, H, W): (starts, steps) per axis."""
+    ar_shape = np.asanyarray(shape)
+    ndim = len(ar_shape)
+    unsort = np.argsort(np.argsort(ar_shape))
+    sorted_dims = np.sort(ar_shape)
+    space_size = float(np.prod(ar_shape))
+    if space_size <= n_points:
+        return [0] * ndim, [1] * ndim
+    stepsizes = np.full(ndim, (space_size / n_points) ** (1.0 / ndim), dtype="float64")
+    if (sorted_dims < stepsizes).any():
+        for dim in range(ndim):
+            stepsizes[dim] = sorted_dims[dim]
+            space_size = float(np.prod(sorted_dims[dim + 1:]))
+            stepsizes[dim + 1:] = (space_size / n_points) ** (1.0 / (ndim - dim - 1))
+            if (sorted_dims >= stepsizes).all():
+                break
+    starts = (stepsizes // 2).astype(int)
+    stepsizes = np.round(stepsizes).astype(int)
+    return list(starts[unsort]), list(stepsizes[unsort])
+
+
+def gaussian_weights(sigma, truncate=4.0):
+    """scipy.ndimage._filters._gaussian_kernel1d (order 0)."""
+    radius = int(truncate * float(sigma) + 0.5)
+    x = np.arange(-radius, radius + 1)
+    phi = np.exp(-0.5 / (sigma * sigma) * x ** 2)
+    return phi / phi.sum()
+
+
+def rgb2lab(rgb):
+    """skimage.color.rgb2lab (sRGB, D65, 2 degree observer), float64 [..., 3]."""
+    arr = rgb.astype(np.float64).copy()
+    m = arr > 0.04045
+    arr[m] = np.power((arr[m] + 0.055) / 1.055, 2.4)
+    arr[~m] /= 12.92
+    r, g, b = arr[..., 0], arr[..., 1], arr[..., 2]
+    M = XYZ_FROM_RGB
+    xyz = np.stack([(r * M[i, 0] + g * M[i, 1]) + b * M[i, 2] for i in range(3)], axis=-1)
+    xyz = xyz / WHITE_D65
+    m = xyz > 0.008856
+    xyz[m] = np.cbrt(xyz[m])
+    xyz[~m] = 7.787 * xyz[~m] + 16.0 / 116.0
+    x, y, z = xyz[..., 0], xyz[..., 1], xyz[..., 2]
+    return np.stack([116.0 * y - 16.0, 500.0 * (x - y), 200.0 * (y - z)], axis=-1)
+
+
+def preprocess(image_u8, sigma=1.0, compactness=10.0):
+    """uint8 [H,W,3] -> the scaled Lab volume [H,W,3] float64 the clustering works on."""
+    img = image_u8.astype(np.float64) * (1.0 / 255.0)
+    vol = img[None]                                                  # [1,H,W,3]
+    if sigma > 0:
+        vol = ndi.gaussian_filter(vol, [sigma, sigma, sigma, 0], mode="reflect")
+    lab = rgb2lab(vol[0])
+    return np.ascontiguousarray(lab * (1.0 / compactness))
+
+
+def cluster(feat, n_segments=500, max_num_iter=10):
+    """_slic_cython on one [H,W,C] float64 image (depth 1, spacing 1).  Returns nearest-segment indices [H,W] (0-based)
+    and the final centroids [K, 2 + C] (y, x, colour)."""
+    H, W, C = feat.shape
+    starts, steps = regular_grid_steps((1, H, W), n_segments)
+    ys = np.arange(starts[1], H, steps[1])
+    xs = np.arange(starts[2], W, steps[2])
+    K = len(ys) * len(xs)
+    _, steps2 = regular_grid_steps((1, H, W), K)        # the cython routine recomputes the steps from the seed count
+    step_y, step_x = int(steps2[1]), int(steps2[2])
+    step = max(int(s) for s in steps)
+    seg = np.zeros((K, 2 + C))
+    seg[:, 0] = np.repeat(ys, len(xs))
+    seg[:, 1] = np.tile(xs, len(ys))
+    sw = 1.0 / float(step * step)
+    nearest = np.full((H, W), -1, dtype=np.int64)
+    yy, xx = np.mgrid[0:H, 0:W]
+    for _ in range(max_num_iter):
+        dist = np.full((H, W), np.finfo(np.float64).max)
+        for k in range(K):
+            cy, cx = seg[k, 0], seg[k, 1]
+            if not (np.isfinite(cy) and np.isfinite(cx)):
+                continue
+            y0, y1 = int(max(cy - 2 * step_y, 0)), int(min(cy + 2 * step_y + 1, H))
+            x0, x1 = int(max(cx - 2 * step_x, 0)), int(min(cx + 2 * step_x + 1, W))
+            if y0 >= y1 or x0 >= x1:
+                continue
+            dy = (cy - yy[y0:y1, x0:x1]) ** 2
+            dx = (cx - xx[y0:y1, x0:x1]) ** 2
+            d = (dy + dx) * sw
+            dc = np.zeros_like(d)
+            for c in range(C):
+                dc = dc + (feat[y0:y1, x0:x1, c] - seg[k, 2 + c]) ** 2
+            d = d + dc
+            sub = dist[y0:y1, x0:x1]
+            better = sub > d
+            sub[better] = d[better]
+            nearest[y0:y1, x0:x1][better] = k
+        # raster-order sums: np.add.at over the flattened image keeps the sequential order per cluster
+        flat = nearest.ravel()
+        live = flat >= 0
+        n = np.bincount(flat[live], minlength=K).astype(np.float64)
+        new = np.zeros_like(seg)
+        for col, vals in ((0, yy.ravel()), (1, xx.ravel())):
+            acc = np.zeros(K)
+            np.add.at(acc, flat[live], vals[live].astype(np.float64))
+            new[:, col] = acc
+        for c in range(C):
+            acc = np.zeros(K)
+            np.add.at(acc, flat[live], feat[..., c].ravel()[live])
+            new[:, 2 + c] = acc
+        with np.errstate(invalid="ignore", divide="ignore"):
+            seg = new / n[:, None]
+    return nearest, seg
+
+
+def enforce_connectivity(labels, min_size, max_size, start_label=1):
+    """_enforce_label_connectivity_cython on one [H,W] label image (depth 1): raster-order BFS, 4-connected."""
+    H, W = labels.shape
+    out = np.full((H, W), -1, dtype=np.int64)
+    cur = start_label
+    coords = np.zeros((max(max_size, 1), 2), dtype=np.int64)
+    ddy = (0, 0, 1, -1)
+    ddx = (1, -1, 0, 0)
+    for y in range(H):
+        for x in range(W):
+            if out[y, x] >= 0:
+                continue
+            adjacent = 0
+            label = labels[y, x]
+            out[y, x] = cur
+            size, visited = 1, 0
+            coords[0] = (y, x)
+            while visited < size < max_size:
+                py, px = coords[visited]
+                for i in range(4):
+                    qy, qx = py + ddy[i], px + ddx[i]
+                    if 0 <= qy < H and 0 <= qx < W:
+                        if labels[qy, qx] == label and out[qy, qx] == -1:
+                            out[qy, qx] = cur
+                            coords[size] = (qy, qx)
+                            size += 1
+                            if size >= max_size:
+                                break
+                        elif out[qy, qx] >= 0 and out[qy, qx] != cur:
+                            adjacent = out[qy, qx]
+                visited += 1
+            if size < min_size:
+                for i in range(size):
+                    out[coords[i, 0], coords[i, 1]] = adjacent
+            else:
+                cur += 1
+    return out
+
+
+def slic(image_u8, n_segments=500, compactness=10.0, sigma=1.0, max_num_iter=10, start_label=1):
+    feat = preprocess(image_u8, sigma, compactness)
+    nearest, seg = cluster(feat, n_segments, max_num_iter)
+    labels = nearest + start_label
+    K = seg.shape[0]
+    H, W = labels.shape
+    segment_size = H * W / K
+    return enforce_connectivity(labels, int(0.5 * segment_size), int(3 * segment_size), start_label)

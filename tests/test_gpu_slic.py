@@ -1,0 +1,58 @@
+"""device SLIC against the CPU restatement (oracle/slic.py; parity with scikit-image itself is
+unpinned -- it is not installable here).  The connectivity stage is an integer algorithm: bit-exact.  The clustering is
+float64 with the oracle's summation order; pow / cbrt differ between CUDA and numpy in the last bit, so a handful of
+near-tie pixels may flip: >= 99.5 % of the pixels must agree and the region count must agree within 1 %."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _images(n, seed=21):
+    from camouflage_multimodal_b200 import synth
+    return synth.make_batch(0, n, seed=seed, device=torch.device("cuda")).as_decoded().images
+
+
+def test_connectivity_stage_is_bit_exact():
+    from camouflage_multimodal_b200 import _lib
+    from oracle import slic as oslic
+    imgs = _images(2).cpu().numpy()
+    near = np.stack([oslic.cluster(oslic.preprocess(im))[0] for im in imgs]) + 1
+    K = 529
+    min_size, max_size = int(0.5 * 65536 / K), int(3 * 65536 / K)
+    lab_in = torch.as_tensor(near.astype(np.int32)).cuda()
+    out = torch.empty_like(lab_in)
+    coords = torch.empty((2, max_size), dtype=torch.int32, device="cuda")
+    lib = _lib.load()
+    _lib.check(lib.cm_slic_enforce_connectivity(_lib.ptr(lab_in), 2, 256, 256, min_size, max_size, 1, _lib.ptr(coords), _lib.ptr(out),
+                                                C.c_void_p(torch.cuda.current_stream().cuda_stream)), "connectivity")
+    for i in range(2):
+        ref = oslic.enforce_connectivity(near[i], min_size, max_size, 1)
+        assert np.array_equal(out[i].cpu().numpy(), ref)
+
+
+def test_slic_matches_oracle_and_invariants():
+    from camouflage_multimodal_b200.region_graph import slic_segments
+    from oracle import slic as oslic
+    imgs = _images(3)
+    lab = slic_segments(imgs, n_segments=500, compactness=10.0, sigma=1.0).cpu().numpy()
+    for i in range(3):
+        ref = oslic.slic(imgs[i].cpu().numpy(), 500, 10.0, 1.0)
+        agree = float((lab[i] == ref).mean())
+        n_dev, n_ref = len(np.unique(lab[i])), len(np.unique(ref))
+        assert agree >= 0.995, f"image {i}: {agree:.4f} of the pixels agree"
+        assert abs(n_dev - n_ref) <= max(1, int(0.01 * n_ref))
+        assert 300 <= n_dev <= 529          # the reference's embedding_summary.json range for n_segments=500
+        assert lab[i].min() >= 0 and lab[i].max() <= 529
+
+
+def test_create_region_graph_runs_from_the_image_alone():
+    from camouflage_multimodal_b200.region_graph import create_region_graph
+    img = _images(1)[0].cpu().numpy().astype(np.float64) / 255.0
+    data, segments = create_region_graph(img, n_segments=500)
+    assert segments.shape == (256, 256) and data.x.shape[1] == 15
+    assert data.x.shape[0] == len(np.unique(segments))
+    assert data.edge_index.shape[0] == 2 and data.edge_index.shape[1] > data.x.shape[0]
