@@ -107,10 +107,12 @@ def test_edge_cases():
     assert g0.counts() == (0, 0)
 
 
-def test_needs_label_map():
+def test_label_map_is_computed_when_not_given():
+    """A tiny uniform image: fewer pixels than n_segments -> every pixel is its own seed; SLIC's connectivity pass then
+    merges the sub-minimum segments, and the graph build runs on whatever comes out."""
     from camouflage_multimodal_b200.region_graph import create_region_graph
-    with pytest.raises(NotImplementedError):
-        create_region_graph(np.zeros((8, 8, 3), np.float32))
+    data, segments = create_region_graph(np.zeros((8, 8, 3), np.float32))
+    assert segments.shape == (8, 8) and data.x.shape[0] == len(np.unique(segments))
 
 
 def test_full_size_properties():

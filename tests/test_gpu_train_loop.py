@@ -54,7 +54,7 @@ def test_rg_node_loss_value_and_gradients():
     om, oi, oe = [t.detach().cpu().double()[:n].requires_grad_(True) for t in (mask, inst, edge)]
     ol, *_ = otl.rg_node_loss(om, oi, oe, y.cpu()[:n], iy.cpu()[:n], ey.cpu()[:n])
     ol.backward()
-    assert abs(float(loss) - float(ol)) <= 2e-6 * abs(float(ol))
+    assert abs(float(loss.detach()) - float(ol.detach())) <= 2e-6 * abs(float(ol.detach()))
     for got, ref in ((mask.grad, om.grad), (inst.grad, oi.grad), (edge.grad, oe.grad)):
         np.testing.assert_allclose(got[:n].cpu().numpy(), ref.numpy(), rtol=2e-5, atol=1e-9)
         assert float(got[n:].abs().max()) == 0.0
@@ -77,7 +77,7 @@ def test_multimodal_loss_and_focal_loss():
     o = [t.detach().cpu().double().requires_grad_(True) for t in (mask, inst, edge, score)]
     ol = otl.multimodal_loss(*o, ml.cpu(), el.cpu(), sl.cpu())
     ol.backward()
-    assert abs(float(loss) - float(ol)) <= 3e-6 * abs(float(ol))
+    assert abs(float(loss.detach()) - float(ol.detach())) <= 3e-6 * abs(float(ol.detach()))
     for got, ref in zip((mask, inst, edge, score), o):
         np.testing.assert_allclose(got.grad.cpu().numpy(), ref.grad.numpy(), rtol=5e-5, atol=2e-7)
     # the focal term alone, batch mean as the reference module reduces it
@@ -88,7 +88,7 @@ def test_multimodal_loss_and_focal_loss():
     zo = z.detach().cpu().double().requires_grad_(True)
     fo = otl.aggressive_focal_loss(zo, t.cpu())
     fo.backward()
-    assert abs(float(fl) - float(fo)) <= 3e-6 * abs(float(fo)) + 1e-9
+    assert abs(float(fl.detach()) - float(fo.detach())) <= 3e-6 * abs(float(fo.detach())) + 1e-9
     np.testing.assert_allclose(z.grad.cpu().numpy(), zo.grad.numpy(), rtol=5e-5, atol=2e-7)
 
 
