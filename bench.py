@@ -347,11 +347,11 @@ def b200_arm(args):
     # ---- end to end through the host-facing call: pinned host inputs, H2D + path + D2H every step
     stager = HostPipeline(pipes, BATCH, H, W, dev, slots=max(2, 2 * lanes), use_graph=not args.no_graph,
                           image_dtype=pool[0].images.dtype, label_dtype=pool[0].labels.dtype)
-    host_pool = [(b.images.cpu().pin_memory(), b.labels.cpu().pin_memory(), b.canny.cpu().pin_memory(), b.gt.cpu().pin_memory())
-                 for b in pool]
+    # host batches in the pipeline's pinned staging layout (images | labels | canny | gt in one allocation): one H2D copy each
+    host_pool = [stager.host_batch().fill(b.images.cpu(), b.labels.cpu(), b.canny.cpu(), b.gt.cpu()) for b in pool]
 
     def e2e_step(s):
-        return stager.submit(s, *host_pool[s % n_pool])
+        return stager.submit(s, host_pool[s % n_pool])
 
     for s in range(n_warm):
         e2e_step(s)

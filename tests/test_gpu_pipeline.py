@@ -178,8 +178,13 @@ def test_lanes_and_decoded_inputs_equal_float_path(models):
     slots = [hp.submit(j, *hb) for j, hb in enumerate(pinned[:4])]       # four batches in flight on two lanes
     hp.synchronize()
     got = [(st.h_mask_out.clone(), st.h_per_image.clone()) for st in slots]
-    for j in (4, 5):                                                      # slot reuse
-        st = hp.submit(j, *pinned[j])
+    for j in (4, 5):                                                      # slot reuse; batch 5 through the one-copy staging layout
+        if j == 5:
+            hb = hp.host_batch().fill(batches[j].images, batches[j].labels, batches[j].canny, batches[j].gt)
+            assert hb.flat.is_pinned() and hb.payload_bytes == hp.h2d_bytes
+            st = hp.submit(j, hb)
+        else:
+            st = hp.submit(j, *pinned[j])
         st.ev_done.synchronize()
         got.append((st.h_mask_out.clone(), st.h_per_image.clone()))
     eager = EvalPipeline(gnn, det, kg, label_cap=544, lane=7)
