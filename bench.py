@@ -115,6 +115,9 @@ def measured_peaks():
     return 6650.0, 1590.0, "fallback (B200_PROFILING.md)"
 
 
+LABEL_BYTES = 4   # 2 when the label maps stay int16 end to end (--input u8)
+
+
 def kernel_work(name, B, M, E, K):
     """Algorithmic work of ONE step's launches of a kernel: ("hbm", bytes) or ("tensor", flops).
     M = nodes, E = directed edges in the batch, K = KG rows.  Figures follow SURVEY.md 8(d) / DESIGN.md."""
@@ -138,14 +141,14 @@ def kernel_work(name, B, M, E, K):
         "fusion_node": ("tensor", node_flops),
         "fusion_kgrows": ("tensor", 2.0 * gk * (D * D + 2 * (D * 2 * D))),
         "cast_f16": ("hbm", 768.0 * M),
-        "rag_scan": ("hbm", 4.0 * px),
+        "rag_scan": ("hbm", float(LABEL_BYTES) * px),
         "rag_compact": ("hbm", 4.0 * B * LABEL_CAP * (4 + 17 + 2)),
         "rag_emit": ("hbm", 4.0 * B * LABEL_CAP * 17 + 4.0 * E + 28.0 * M),
         "node_features": ("hbm", px * (12.0 + 4.0 + 1.0) + 60.0 * M),
-        "node_features_u8": ("hbm", px * (3.0 + 4.0 + 1.0) + 60.0 * M),
+        "node_features_u8": ("hbm", px * (3.0 + LABEL_BYTES + 1.0) + 60.0 * M),
         "labels_widen": ("hbm", px * (2.0 + 4.0)),
         "edge_weights": ("hbm", 60.0 * M + 8.0 * E),
-        "paint_metrics": ("hbm", px * (4.0 + 1.0) + 4.0 * M),
+        "paint_metrics": ("hbm", px * (LABEL_BYTES + 1.0) + 4.0 * M),
         "gat_logits": ("hbm", 60.0 * M + 32.0 * M),
         "gat_aggregate": ("hbm", 60.0 * M + 4.0 * E + 240.0 * M),
         "gcn_norm": ("hbm", 8.0 * E + 4.0 * M),
@@ -259,6 +262,8 @@ def b200_arm(args):
     if world > 1:   # weights and KG rows broadcast once from rank 0
         for t in list(gnn.state_dict().values()) + list(det.state_dict().values()) + [kg]:
             dist.broadcast(t, src=0)
+    global LABEL_BYTES
+    LABEL_BYTES = 2 if args.input == "u8" else 4
     lanes = max(1, args.lanes)
     n_pool = args.pool
     if n_pool % lanes:
@@ -476,7 +481,7 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pool", type=int, default=8, help="distinct input batches rotated per GPU (8 x 14.7 MB of decoded inputs + their intermediates > L2)")

@@ -100,8 +100,10 @@ SIGNATURES = {
     "cm_timing_report": (_i, [C.c_char_p, _i]),
     "cm_rag_workspace_bytes": (_sz, [_i, _i]),
     "cm_rag_build": (_i, [_fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp]),
+    "cm_rag_build_i16": (_i, [_fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp]),
     "cm_node_features": (_i, [_fp, _fp, _fp, _i, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
     "cm_node_features_u8": (_i, [_fp, _fp, _fp, _i, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
+    "cm_node_features_u8_i16": (_i, [_fp, _fp, _fp, _i, _i, _i, _i, _fp, _fp, _fp, _f, _fp, _i, _fp]),
     "cm_labels_widen_i16": (_i, [_fp, _i64, _fp, _fp]),
     "cm_edge_weights": (_i, [_fp, _fp, _fp, _fp, _i, _fp, _fp]),
     "cm_csr_workspace_bytes": (_sz, [_i, _i]),
@@ -131,6 +133,7 @@ SIGNATURES = {
     "cm_canny_workspace_bytes": (_sz, [_i, _i, _i]),
     "cm_canny": (_i, [_fp, _i, _i, _i, _i, C.c_double, C.c_double, C.c_double, _fp, _sz, _fp, _fp]),
     "cm_paint_metrics": (_i, [_fp, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _f, _fp, _fp, _fp, _fp]),
+    "cm_paint_metrics_i16": (_i, [_fp, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _f, _fp, _fp, _fp, _fp]),
     "cm_metrics_dense": (_i, [_fp, _fp, _i, _i64, _f, _fp, _fp, _fp]),
     "cm_metrics_finalize": (_i, [_fp, _fp, _i, _i64, _fp, _fp, _fp]),
     "cm_class_confusion": (_i, [_fp, _fp, _i, _i, _fp, _fp]),

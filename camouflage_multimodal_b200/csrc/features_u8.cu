@@ -379,7 +379,8 @@ __device__ __forceinline__ void u8_write_features_warp(const U8Moments& m, float
     if (lane < CM_NODE_FEATURES) o[lane] = (float)a;
 }
 
-__global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_t* __restrict__ image, const int* __restrict__ labels,
+template <typename LT>
+__global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_t* __restrict__ image, const LT* __restrict__ labels,
                                                                     const uint8_t* __restrict__ canny, int batch, int H, int W,
                                                                     const int* __restrict__ node_ptr, const int* __restrict__ node_label,
                                                                     const int* __restrict__ node_bbox, float norm_side,
@@ -394,7 +395,7 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
     const int wx0 = max(bb.x - 2, 0), wy0 = max(bb.y - 2, 0), wx1 = min(bb.z + 2, W - 1), wy1 = min(bb.w + 2, H - 1);
     const int ww = wx1 - wx0 + 1, npx = ww * (wy1 - wy0 + 1);
     const float inv_ww = 1.0f / (float)ww;
-    const int* lab = labels + (size_t)b * H * W;
+    const LT* lab = labels + (size_t)b * H * W;
     const uint8_t* img = image + (size_t)b * H * W * 3;
     const uint8_t* can = canny + (size_t)b * H * W;
 
@@ -412,7 +413,7 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
         const unsigned full = 0xffffffffu;
         const bool colin = lane < ww;
         const int base = wy0 * W + wx0;
-        const int* lp0 = lab + base + (colin ? lane : 0);
+        const LT* lp0 = lab + base + (colin ? lane : 0);
         unsigned m = 0;
         for (int y8 = 0; y8 < wh; y8 += 16) {   // sixteen rows of label loads in flight
             int lw[16];
@@ -488,7 +489,7 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
         if (xx < 0) { --yy; xx += ww; }
         if (xx >= ww) { ++yy; xx -= ww; }
         const int y = wy0 + yy, x = wx0 + xx;
-        const int* lp = lab + (size_t)y * W + x;
+        const LT* lp = lab + (size_t)y * W + x;
         const size_t p = (size_t)y * W + x;
         // every load of the iteration is issued up front (out-of-image neighbours are clamped onto the pixel itself,
         // whose label is != L whenever the neighbour tests matter): one memory round trip per pixel, not thirteen
@@ -543,9 +544,10 @@ __global__ void labels_widen_kernel(const short* __restrict__ in, long long n, i
 
 }  // namespace cm
 
-extern "C" int cm_node_features_u8(const uint8_t* image_u8, const int32_t* labels, const uint8_t* canny, int batch, int h,
+static int node_features_u8_impl(const uint8_t* image_u8, const void* labels_v, int label_bytes, const uint8_t* canny, int batch, int h,
                                    int w, int label_cap, const int32_t* node_ptr, const int32_t* node_label,
                                    const int32_t* node_bbox, float norm_side, float* x, int node_cap, void* stream) {
+    const int32_t* labels = reinterpret_cast<const int32_t*>(labels_v);
     using namespace cm;
     CM_DEVICE_OR_RETURN();
     CM_REQUIRE(image_u8 && labels && canny && node_ptr && node_label && x, "cm_node_features_u8: NULL pointer");
@@ -553,10 +555,15 @@ extern "C" int cm_node_features_u8(const uint8_t* image_u8, const int32_t* label
     CM_REQUIRE((long long)h * w < (1 << 22), "cm_node_features_u8: images up to 4M pixels");
     if (node_bbox) {
         CM_TIMED("node_features_u8", as_stream(stream));
-        node_features_u8_bbox_kernel<<<ceil_div(node_cap, 8), 256, 0, as_stream(stream)>>>(image_u8, labels, canny, batch, h, w, node_ptr,
-                                                                                          node_label, node_bbox, norm_side, x, node_cap);
+        if (label_bytes == 2)
+            node_features_u8_bbox_kernel<short><<<ceil_div(node_cap, 8), 256, 0, as_stream(stream)>>>(
+                image_u8, reinterpret_cast<const short*>(labels_v), canny, batch, h, w, node_ptr, node_label, node_bbox, norm_side, x, node_cap);
+        else
+            node_features_u8_bbox_kernel<int><<<ceil_div(node_cap, 8), 256, 0, as_stream(stream)>>>(
+                image_u8, labels, canny, batch, h, w, node_ptr, node_label, node_bbox, norm_side, x, node_cap);
         return post_launch("cm_node_features_u8");
     }
+    CM_REQUIRE(label_bytes == 4, "cm_node_features_u8_i16: int16 label maps go through the region kernel (pass node_bbox)");
     CM_REQUIRE(label_cap > 0, "cm_node_features_u8: the tile kernel (node_bbox == NULL) needs label_cap > 0");
     // a CTA's 32-bit sums of squares hold (pixels per CTA) * 255^2 < 2^32; its labels + table must fit in shared memory
     int ncl = 0;
@@ -611,4 +618,16 @@ extern "C" int cm_labels_widen_i16(const int16_t* labels16, int64_t n, int32_t* 
         labels_widen_kernel<<<blocks, 256, 0, st>>>(labels16, (long long)n, labels32);
     }
     return post_launch("cm_labels_widen_i16");
+}
+
+extern "C" int cm_node_features_u8(const uint8_t* image_u8, const int32_t* labels, const uint8_t* canny, int batch, int h,
+                                   int w, int label_cap, const int32_t* node_ptr, const int32_t* node_label,
+                                   const int32_t* node_bbox, float norm_side, float* x, int node_cap, void* stream) {
+    return node_features_u8_impl(image_u8, labels, 4, canny, batch, h, w, label_cap, node_ptr, node_label, node_bbox, norm_side, x, node_cap, stream);
+}
+
+extern "C" int cm_node_features_u8_i16(const uint8_t* image_u8, const int16_t* labels, const uint8_t* canny, int batch, int h,
+                                   int w, int label_cap, const int32_t* node_ptr, const int32_t* node_label,
+                                   const int32_t* node_bbox, float norm_side, float* x, int node_cap, void* stream) {
+    return node_features_u8_impl(image_u8, labels, 2, canny, batch, h, w, label_cap, node_ptr, node_label, node_bbox, norm_side, x, node_cap, stream);
 }

@@ -25,14 +25,20 @@ __device__ __forceinline__ void flush_partials(int tp, int sp, int sg, int eq, d
 }
 
 // grid (chunks, B), block 256; each thread walks pixels with stride gridDim.x*256
-__global__ void __launch_bounds__(256) paint_metrics_kernel(const int* __restrict__ labels, const uint8_t* __restrict__ gt, int HW,
+__device__ __forceinline__ int4 load4_labels(const int* p, int q) { return reinterpret_cast<const int4*>(p)[q]; }
+__device__ __forceinline__ int4 load4_labels(const short* p, int q) {
+    const uint2 a = reinterpret_cast<const uint2*>(p)[q];
+    return make_int4((int)(short)(a.x & 0xffffu), (int)(short)(a.x >> 16), (int)(short)(a.y & 0xffffu), (int)(short)(a.y >> 16));
+}
+template <typename LT>
+__global__ void __launch_bounds__(256) paint_metrics_kernel(const LT* __restrict__ labels, const uint8_t* __restrict__ gt, int HW,
                                                             const float* __restrict__ mask_prob, const int* __restrict__ node_ptr,
                                                             const int* __restrict__ id_of_label, int cap, float threshold,
                                                             float* __restrict__ pred_mask, unsigned long long* __restrict__ counts,
                                                             double* __restrict__ abs_err) {
     const int b = blockIdx.y;
     const int n0 = node_ptr[b], nb = node_ptr[b + 1] - n0;
-    const int* lab = labels + (size_t)b * HW;
+    const LT* lab = labels + (size_t)b * HW;
     const uint8_t* g = gt + (size_t)b * HW;
     const int* idm = id_of_label ? id_of_label + (size_t)b * cap : nullptr;
     const double thr = (double)threshold;
@@ -59,7 +65,7 @@ __global__ void __launch_bounds__(256) paint_metrics_kernel(const int* __restric
         // four pixels per thread per trip: one 16-byte label load, one 4-byte gt load, the four dependent
         // label -> node id -> probability gathers in flight together
         for (int q = blockIdx.x * 256 + threadIdx.x; q < HW / 4; q += gridDim.x * 256) {
-            const int4 l4 = reinterpret_cast<const int4*>(lab)[q];
+            const int4 l4 = load4_labels(lab, q);
             const unsigned g4 = reinterpret_cast<const unsigned*>(g)[q];
             const float p0 = prob_of(l4.x), p1 = prob_of(l4.y), p2 = prob_of(l4.z), p3 = prob_of(l4.w);
             if (pred_mask) reinterpret_cast<float4*>(pred_mask + (size_t)b * HW)[q] = make_float4(p0, p1, p2, p3);
@@ -70,7 +76,7 @@ __global__ void __launch_bounds__(256) paint_metrics_kernel(const int* __restric
         }
     } else {
         for (int p = blockIdx.x * 256 + threadIdx.x; p < HW; p += gridDim.x * 256) {
-            const float pr = prob_of(lab[p]);
+            const float pr = prob_of((int)lab[p]);
             if (pred_mask) pred_mask[(size_t)b * HW + p] = pr;
             account(pr, g[p]);
         }
@@ -186,9 +192,10 @@ static int metric_chunks(long long pixels, int batch) {
 
 }  // namespace cm
 
-extern "C" int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
+static int paint_metrics_impl(const void* labels_v, int label_bytes, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
                                 const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, float threshold,
                                 float* pred_mask, int64_t* counts, double* abs_err, void* stream) {
+    const int32_t* labels = reinterpret_cast<const int32_t*>(labels_v);
     using namespace cm;
     CM_DEVICE_OR_RETURN();
     CM_REQUIRE(labels && gt && mask_prob && node_ptr && counts && abs_err, "cm_paint_metrics: NULL pointer");
@@ -200,8 +207,12 @@ extern "C" int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int ba
     dim3 grid(metric_chunks((long long)h * w, batch), batch);
     {
         CM_TIMED("paint_metrics", st);
-        paint_metrics_kernel<<<grid, 256, 0, st>>>(labels, gt, h * w, mask_prob, node_ptr, id_of_label, label_cap, threshold,
-                                                   pred_mask, reinterpret_cast<unsigned long long*>(counts), abs_err);
+        if (label_bytes == 2)
+            paint_metrics_kernel<short><<<grid, 256, 0, st>>>(reinterpret_cast<const short*>(labels_v), gt, h * w, mask_prob, node_ptr, id_of_label,
+                                                              label_cap, threshold, pred_mask, reinterpret_cast<unsigned long long*>(counts), abs_err);
+        else
+            paint_metrics_kernel<int><<<grid, 256, 0, st>>>(labels, gt, h * w, mask_prob, node_ptr, id_of_label, label_cap, threshold,
+                                                            pred_mask, reinterpret_cast<unsigned long long*>(counts), abs_err);
     }
     return post_launch("cm_paint_metrics");
 }
@@ -249,4 +260,16 @@ extern "C" int cm_class_confusion(const float* mask_out, const int64_t* true_cls
             mask_out, reinterpret_cast<const long long*>(true_cls), n, num_classes, reinterpret_cast<unsigned long long*>(counts4));
     }
     return post_launch("cm_class_confusion");
+}
+
+extern "C" int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
+                                const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, float threshold,
+                                float* pred_mask, int64_t* counts, double* abs_err, void* stream) {
+    return paint_metrics_impl(labels, 4, gt, batch, h, w, mask_prob, node_ptr, id_of_label, label_cap, threshold, pred_mask, counts, abs_err, stream);
+}
+
+extern "C" int cm_paint_metrics_i16(const int16_t* labels, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
+                                const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, float threshold,
+                                float* pred_mask, int64_t* counts, double* abs_err, void* stream) {
+    return paint_metrics_impl(labels, 2, gt, batch, h, w, mask_prob, node_ptr, id_of_label, label_cap, threshold, pred_mask, counts, abs_err, stream);
 }

@@ -134,12 +134,28 @@ __global__ void __launch_bounds__(256) rag_scan_kernel(const int* __restrict__ l
 // branch-free compares and then drained bit by bit, so a warp spends its instructions on ~4 events per thread
 // instead of walking 32 pixel x neighbour sites that almost always diverge.  Same outputs as rag_scan_kernel (the
 // box maxima and the adjacency bit set are order independent).
-__global__ void __launch_bounds__(256) rag_scan8_kernel(const int* __restrict__ labels, int H, int W, int cap, int cw,
+// eight consecutive labels (16-byte aligned run start for int16, two 16-byte loads for int32)
+__device__ __forceinline__ void load8_labels(const int* p, int* v) {
+    const int4 a0 = *reinterpret_cast<const int4*>(p), a1 = *reinterpret_cast<const int4*>(p + 4);
+    v[0] = a0.x; v[1] = a0.y; v[2] = a0.z; v[3] = a0.w; v[4] = a1.x; v[5] = a1.y; v[6] = a1.z; v[7] = a1.w;
+}
+__device__ __forceinline__ void load8_labels(const short* p, int* v) {
+    const uint4 a = *reinterpret_cast<const uint4*>(p);
+    const unsigned w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        v[2 * k] = (int)(short)(w[k] & 0xffffu);
+        v[2 * k + 1] = (int)(short)(w[k] >> 16);
+    }
+}
+
+template <typename LT>
+__global__ void __launch_bounds__(256) rag_scan8_kernel(const LT* __restrict__ labels, int H, int W, int cap, int cw,
                                                         int rows_per_cta, int* __restrict__ box_g,
                                                         uint32_t* __restrict__ adj_g, uint32_t* status) {
     extern __shared__ int sbox[];
     const int b = blockIdx.y;
-    const int* lab = labels + (size_t)b * H * W;
+    const LT* lab = labels + (size_t)b * H * W;
     const int r0 = blockIdx.x * rows_per_cta;
     const int r1 = min(H, r0 + rows_per_cta);
     for (int i = threadIdx.x; i < 4 * cap; i += blockDim.x) sbox[i] = 0;
@@ -151,17 +167,15 @@ __global__ void __launch_bounds__(256) rag_scan8_kernel(const int* __restrict__ 
         const int r = u / upr, x0 = (u - r * upr) << 3, y = r0 + r;
         // v[0] = west of the run, v[1..8] = the run, v[9] = east of it; v[10..19] the same columns one row down
         int v[20];
-        const int* pa = lab + (size_t)y * W + x0;
-        const int4 a0 = *reinterpret_cast<const int4*>(pa), a1 = *reinterpret_cast<const int4*>(pa + 4);
-        v[0] = x0 > 0 ? pa[-1] : -1;
-        v[1] = a0.x; v[2] = a0.y; v[3] = a0.z; v[4] = a0.w; v[5] = a1.x; v[6] = a1.y; v[7] = a1.z; v[8] = a1.w;
-        v[9] = x0 + 8 < W ? pa[8] : -1;
+        const LT* pa = lab + (size_t)y * W + x0;
+        load8_labels(pa, v + 1);
+        v[0] = x0 > 0 ? (int)pa[-1] : -1;
+        v[9] = x0 + 8 < W ? (int)pa[8] : -1;
         if (y + 1 < H) {
-            const int* pb = pa + W;
-            const int4 b0 = *reinterpret_cast<const int4*>(pb), b1 = *reinterpret_cast<const int4*>(pb + 4);
-            v[10] = x0 > 0 ? pb[-1] : -1;
-            v[11] = b0.x; v[12] = b0.y; v[13] = b0.z; v[14] = b0.w; v[15] = b1.x; v[16] = b1.y; v[17] = b1.z; v[18] = b1.w;
-            v[19] = x0 + 8 < W ? pb[8] : -1;
+            const LT* pb = pa + W;
+            load8_labels(pb, v + 11);
+            v[10] = x0 > 0 ? (int)pb[-1] : -1;
+            v[19] = x0 + 8 < W ? (int)pb[8] : -1;
         } else {
 #pragma unroll
             for (int k = 10; k < 20; ++k) v[k] = -1;
@@ -374,7 +388,7 @@ extern "C" size_t cm_rag_workspace_bytes(int batch, int label_cap) {
     return cm::carve_rag(nullptr, batch, label_cap).total;
 }
 
-extern "C" int cm_rag_build(const int32_t* labels, int batch, int h, int w, int label_cap, void* workspace,
+static int rag_build_impl(const void* labels, int label_bytes, int batch, int h, int w, int label_cap, void* workspace,
                             size_t workspace_bytes, int32_t* id_of_label, int32_t* node_ptr, int32_t* edge_ptr,
                             int32_t* node_label, int32_t* node_bbox, int64_t* batch_vec, int32_t* csr_row_ptr,
                             int32_t* csr_col, int64_t* edge_index, int local_ids, int node_cap, int edge_cap,
@@ -403,16 +417,19 @@ extern "C" int cm_rag_build(const int32_t* labels, int batch, int h, int w, int 
     static bool attr_done = false;
     if (!attr_done) {
         cudaFuncSetAttribute(rag_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        cudaFuncSetAttribute(rag_scan8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(rag_scan8_kernel<int>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(rag_scan8_kernel<short>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_done = true;
     }
     dim3 g1(ceil_div(h, rows), batch);
     {
         CM_TIMED("rag_scan", st);
-        if ((w & 7) == 0 && (reinterpret_cast<uintptr_t>(labels) & 15) == 0)
-            rag_scan8_kernel<<<g1, 256, smem, st>>>(labels, h, w, label_cap, cw, rows, ws.box, ws.adj, status);
+        if (label_bytes == 2)
+            rag_scan8_kernel<short><<<g1, 256, smem, st>>>(reinterpret_cast<const short*>(labels), h, w, label_cap, cw, rows, ws.box, ws.adj, status);
+        else if ((w & 7) == 0 && (reinterpret_cast<uintptr_t>(labels) & 15) == 0)
+            rag_scan8_kernel<int><<<g1, 256, smem, st>>>(reinterpret_cast<const int*>(labels), h, w, label_cap, cw, rows, ws.box, ws.adj, status);
         else
-            rag_scan_kernel<<<g1, 256, smem, st>>>(labels, h, w, label_cap, cw, rows, ws.box, ws.adj, status);
+            rag_scan_kernel<<<g1, 256, smem, st>>>(reinterpret_cast<const int*>(labels), h, w, label_cap, cw, rows, ws.box, ws.adj, status);
     }
     {
         CM_TIMED("rag_compact", st);
@@ -430,4 +447,23 @@ extern "C" int cm_rag_build(const int32_t* labels, int batch, int h, int w, int 
                                                             edge_cap);
     }
     return post_launch("cm_rag_build");
+}
+
+extern "C" int cm_rag_build(const int32_t* labels, int batch, int h, int w, int label_cap, void* workspace,
+                            size_t workspace_bytes, int32_t* id_of_label, int32_t* node_ptr, int32_t* edge_ptr,
+                            int32_t* node_label, int32_t* node_bbox, int64_t* batch_vec, int32_t* csr_row_ptr,
+                            int32_t* csr_col, int64_t* edge_index, int local_ids, int node_cap, int edge_cap,
+                            uint32_t* status, void* stream) {
+    return rag_build_impl(labels, 4, batch, h, w, label_cap, workspace, workspace_bytes, id_of_label, node_ptr, edge_ptr, node_label, node_bbox, batch_vec, csr_row_ptr, csr_col, edge_index, local_ids, node_cap, edge_cap, status, stream);
+}
+
+extern "C" int cm_rag_build_i16(const int16_t* labels, int batch, int h, int w, int label_cap, void* workspace,
+                            size_t workspace_bytes, int32_t* id_of_label, int32_t* node_ptr, int32_t* edge_ptr,
+                            int32_t* node_label, int32_t* node_bbox, int64_t* batch_vec, int32_t* csr_row_ptr,
+                            int32_t* csr_col, int64_t* edge_index, int local_ids, int node_cap, int edge_cap,
+                            uint32_t* status, void* stream) {
+    using namespace cm;
+    CM_REQUIRE(labels && (w & 7) == 0 && (reinterpret_cast<uintptr_t>(labels) & 15) == 0,
+               "cm_rag_build_i16: int16 label maps need W % 8 == 0 and a 16-byte aligned buffer (else cm_labels_widen_i16 + cm_rag_build)");
+    return rag_build_impl(labels, 2, batch, h, w, label_cap, workspace, workspace_bytes, id_of_label, node_ptr, edge_ptr, node_label, node_bbox, batch_vec, csr_row_ptr, csr_col, edge_index, local_ids, node_cap, edge_cap, status, stream);
 }

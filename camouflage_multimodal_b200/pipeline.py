@@ -72,9 +72,12 @@ class EvalPipeline:
         B, H, W, _ = images.shape
         dev = images.device
         self._alloc(B, H, W, dev)
-        if labels.dtype == torch.int16:     # host-side label maps travel as int16; the kernels read int32
+        # host-side label maps travel as int16: with uint8 images the int16 kernels read them as they are, otherwise they
+        # are widened once on the device
+        i16_direct = labels.dtype == torch.int16 and images.dtype == torch.uint8 and W % 8 == 0 and labels.data_ptr() % 16 == 0
+        if labels.dtype == torch.int16 and not i16_direct:
             l32 = self._bufs.get("labels32")
-            if l32 is None:
+            if l32 is None or l32.shape != labels.shape:
                 l32 = self._bufs["labels32"] = torch.empty((B, H, W), dtype=torch.int32, device=dev)
             _lib.check(lib.cm_labels_widen_i16(_lib.ptr(labels), labels.numel(), _lib.ptr(l32), _lib.stream_ptr(dev)),
                        "cm_labels_widen_i16")
@@ -95,7 +98,8 @@ class EvalPipeline:
         p = _lib.ptr
         b = self._bufs
         with torch.cuda.stream(side):
-            _lib.check(lib.cm_paint_metrics(p(labels), p(gt), B, H, W, p(r["mask_prob"]), p(g.node_ptr),
+            paint = lib.cm_paint_metrics_i16 if labels.dtype == torch.int16 else lib.cm_paint_metrics
+            _lib.check(paint(p(labels), p(gt), B, H, W, p(r["mask_prob"]), p(g.node_ptr),
                                             p(g.id_of_label) if self.label_offset_fix else None, self.label_cap,
                                             self.threshold, p(b["pred_mask"]), p(b["counts"]), p(b["abs_err"]),
                                             _lib.stream_ptr(dev)), "cm_paint_metrics")

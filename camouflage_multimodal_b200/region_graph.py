@@ -76,7 +76,8 @@ def build_region_graphs(images, labels, canny, label_cap: int | None = None, edg
                         want_edge_index: bool = True, local_ids: bool = False, out: RegionGraphBatch | None = None,
                         norm_side: float = NORM_SIDE, feature_kernel: str = "auto") -> RegionGraphBatch:
     """A1-A4 for a batch: images ``[B,H,W,3]`` f32 in [0,1] or uint8 (value = byte / 255, integer-exact feature
-    kernel), labels ``[B,H,W]`` i32, canny ``[B,H,W]`` u8, all CUDA.
+    kernel), labels ``[B,H,W]`` i32 (or int16: read as they are by the ``*_i16`` kernels when the images are uint8 and
+    ``W % 8 == 0``, widened otherwise), canny ``[B,H,W]`` u8, all CUDA.
 
     ``label_cap`` bounds the label values (labels >= label_cap are reported through ``status``); the default
     reads ``labels.max()+1`` back from the device (one sync) -- pass it to stay asynchronous.  ``edge_cap``
@@ -91,8 +92,8 @@ def build_region_graphs(images, labels, canny, label_cap: int | None = None, edg
     if images.dim() != 4 or images.shape[-1] != 3 or images.dtype not in (torch.float32, torch.uint8):
         raise ValueError(f"images must be [B,H,W,3] float32 or uint8, got {tuple(images.shape)} {images.dtype}")
     B, H, W, _ = images.shape
-    if tuple(labels.shape) != (B, H, W) or labels.dtype != torch.int32:
-        raise ValueError(f"labels must be [B,H,W] int32, got {tuple(labels.shape)} {labels.dtype}")
+    if tuple(labels.shape) != (B, H, W) or labels.dtype not in (torch.int32, torch.int16):
+        raise ValueError(f"labels must be [B,H,W] int32 (or int16), got {tuple(labels.shape)} {labels.dtype}")
     if tuple(canny.shape) != (B, H, W) or canny.dtype != torch.uint8:
         raise ValueError(f"canny must be [B,H,W] uint8, got {tuple(canny.shape)} {canny.dtype}")
     images, labels, canny = images.contiguous(), labels.contiguous(), canny.contiguous()
@@ -121,12 +122,19 @@ def build_region_graphs(images, labels, canny, label_cap: int | None = None, edg
     ws_bytes = lib.cm_rag_workspace_bytes(B, label_cap)
     ws = WORKSPACE.get(dev, "rag", ws_bytes)
     p = _lib.ptr
-    _lib.check(lib.cm_rag_build(p(labels), B, H, W, label_cap, p(ws), ws_bytes, p(g.id_of_label), p(g.node_ptr),
+    # int16 label maps are read as they are (no widened copy) when the int16 kernels apply: uint8 images through the
+    # region feature kernel, W % 8 == 0; any other combination widens first
+    i16 = labels.dtype == torch.int16
+    if i16 and not (images.dtype == torch.uint8 and feature_kernel != "tile" and W % 8 == 0 and labels.data_ptr() % 16 == 0):
+        labels, i16 = labels.to(torch.int32), False
+    rag_build = lib.cm_rag_build_i16 if i16 else lib.cm_rag_build
+    _lib.check(rag_build(p(labels), B, H, W, label_cap, p(ws), ws_bytes, p(g.id_of_label), p(g.node_ptr),
                                 p(g.edge_ptr), p(g.node_label), p(g.node_bbox), p(g.batch_vec), p(g.csr_row_ptr),
                                 p(g.csr_col), p(g.edge_index), 1 if local_ids else 0, g.node_cap, g.edge_cap,
                                 p(g.status), st), "cm_rag_build")
     if images.dtype == torch.uint8:
-        _lib.check(lib.cm_node_features_u8(p(images), p(labels), p(canny), B, H, W, label_cap, p(g.node_ptr), p(g.node_label),
+        feat = lib.cm_node_features_u8_i16 if i16 else lib.cm_node_features_u8
+        _lib.check(feat(p(images), p(labels), p(canny), B, H, W, label_cap, p(g.node_ptr), p(g.node_label),
                                            None if feature_kernel == "tile" else p(g.node_bbox), float(norm_side), p(g.x),
                                            g.node_cap, st), "cm_node_features_u8")
     else:

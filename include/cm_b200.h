@@ -397,6 +397,23 @@ int cm_slic(const uint8_t* image_u8, int batch, int h, int w, int n_segments, do
 int cm_slic_enforce_connectivity(const int32_t* labels_in, int batch, int h, int w, int min_size, int max_size,
                                  int start_label, int32_t* coords_workspace, int32_t* labels_out, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * int16 label maps end to end (SLIC labels are < 32768; the host sends 2 bytes per pixel): the same three entry
+ * points reading int16 directly, so no widened copy is written or re-read.  Semantics are those of cm_rag_build,
+ * cm_node_features_u8 (region kernel: node_bbox required) and cm_paint_metrics.  cm_rag_build_i16 needs W % 8 == 0 and a
+ * 16-byte aligned label buffer; otherwise widen with cm_labels_widen_i16 and use the int32 entry points.
+ * ------------------------------------------------------------------------------------------------ */
+int cm_rag_build_i16(const int16_t* labels, int batch, int h, int w, int label_cap, void* workspace, size_t workspace_bytes,
+                     int32_t* id_of_label, int32_t* node_ptr, int32_t* edge_ptr, int32_t* node_label, int32_t* node_bbox,
+                     int64_t* batch_vec, int32_t* csr_row_ptr, int32_t* csr_col, int64_t* edge_index, int local_ids,
+                     int node_cap, int edge_cap, uint32_t* status, void* stream);
+int cm_node_features_u8_i16(const uint8_t* image_u8, const int16_t* labels, const uint8_t* canny, int batch, int h, int w,
+                            int label_cap, const int32_t* node_ptr, const int32_t* node_label, const int32_t* node_bbox,
+                            float norm_side, float* x, int node_cap, void* stream);
+int cm_paint_metrics_i16(const int16_t* labels, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
+                         const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, float threshold,
+                         float* pred_mask, int64_t* counts, double* abs_err, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

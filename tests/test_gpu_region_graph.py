@@ -212,3 +212,19 @@ def test_labels_widen_i16():
         dst = torch.full((n + 8,), 123456, dtype=torch.int32, device="cuda")
         _lib.check(lib.cm_labels_widen_i16(_lib.ptr(src) if n else _lib.ptr(dst), n, _lib.ptr(dst), _lib.stream_ptr()), "widen")
         assert torch.equal(dst[:n], src.to(torch.int32)) and (dst[n:] == 123456).all()
+
+
+def test_int16_label_maps_are_read_directly_and_give_identical_graphs():
+    """cm_rag_build_i16 / cm_node_features_u8_i16 on int16 labels == the int32 entry points on the widened copy."""
+    from camouflage_multimodal_b200.region_graph import build_region_graphs
+    b = synth.make_batch(40, 3, seed=77, device=torch.device("cuda")).as_decoded()
+    assert b.labels.dtype == torch.int16 and b.images.dtype == torch.uint8
+    g16 = build_region_graphs(b.images, b.labels, b.canny, label_cap=544)
+    g32 = build_region_graphs(b.images, b.labels.to(torch.int32), b.canny, label_cap=544)
+    n, e = g32.counts()
+    assert g16.counts() == (n, e)
+    for f in ("node_ptr", "edge_ptr", "id_of_label"):
+        assert torch.equal(getattr(g16, f), getattr(g32, f)), f
+    assert torch.equal(g16.csr_row_ptr[: n + 1], g32.csr_row_ptr[: n + 1]) and torch.equal(g16.csr_col[:e], g32.csr_col[:e])
+    assert torch.equal(g16.node_bbox[:n], g32.node_bbox[:n]) and torch.equal(g16.x[:n], g32.x[:n])
+    assert torch.equal(g16.edge_w[:e], g32.edge_w[:e])
