@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             mbar_init(w_full + s, 1);
             mbar_init(w_empty + s, 1);
         }
-        mbar_init(x_full, 1);
+        mbar_init(x_full, (MODE == 0 && a.x32) ? 8 : 1);   // one TMA transaction, or one arrival per converting warp
         for (int i = 0; i < FN_PHASES; ++i) {
             mbar_init(acc_ready + i, 1);
             mbar_init(epi_done + i, 8);   // one arrival per epilogue warp
@@ -144,8 +144,10 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
     if (warp == 0) {
         // ------------------------------------------------------------------------------ TMA producer
         if (lane == 0) {
-            mbar_expect_tx(x_full, XKB * FN_KB_TILE);
-            for (int kb = 0; kb < XKB; ++kb) tma_load_2d(smem + FN_X + kb * FN_KB_TILE, &a.maps[0], x_full, kb * 64, m0);
+            if (!(MODE == 0 && a.x32)) {
+                mbar_expect_tx(x_full, XKB * FN_KB_TILE);
+                for (int kb = 0; kb < XKB; ++kb) tma_load_2d(smem + FN_X + kb * FN_KB_TILE, &a.maps[0], x_full, kb * 64, m0);
+            }
             int t = 0;
             for (int ph = 0; ph < NPH; ++ph) {
                 const FnPhase p = fn_phases[MODE][ph];
@@ -201,6 +203,33 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             tc_fence_after();
         };
         float x[32];
+
+        if (MODE == 0 && a.x32) {
+            // fp32 rows -> fp16 A operand of phase 0 (SWIZZLE_128B, two 64-column K blocks): coalesced 16-byte loads,
+            // eight in flight per thread, 8-byte shared-memory stores
+            const int et = threadIdx.x - 64;
+#pragma unroll
+            for (int j0 = 0; j0 < 16; j0 += 8) {
+                float4 v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int i = et + 256 * (j0 + j), r = i >> 5, c4 = i & 31;
+                    v[j] = m0 + r < a.M ? *reinterpret_cast<const float4*>(a.x32 + (size_t)(m0 + r) * 128 + c4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int i = et + 256 * (j0 + j), r = i >> 5, c4 = i & 31;
+                    const op2_t lo = f2op2(v[j].x, v[j].y), hi = f2op2(v[j].z, v[j].w);
+                    uint2 pk;
+                    pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+                    pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+                    *reinterpret_cast<uint2*>(smem + FN_X + (c4 >> 4) * FN_KB_TILE + sw128_offset(r, (c4 & 15) >> 1) + (c4 & 1) * 8) = pk;
+                }
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(x_full);
+        }
 
         // y0 = LN(acc + bias + residual) -> A1.  Residual: A1 itself (in place: each thread re-reads and rewrites only
         // its own (row, chunk) cells, and every MMA that read A1 has completed because acc_ready[ph] covers them) or

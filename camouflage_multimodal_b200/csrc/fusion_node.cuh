@@ -12,6 +12,8 @@ struct FusionNodeArgs {
     int M;                 // row capacity of x (grid size); *m_dev the live rows
     const int* m_dev;
     const float *b_rgproj, *ccat, *b_v2, *b_out1, *ln_g, *ln_b, *b_ffn1, *b_ffn2;
+    const float* x32 = nullptr;        // region-node kernel: fp32 input rows [M,128]; converted to the fp16 A operand in the
+                                       // kernel (no separate cast pass); NULL = fp16 rows through the x tensor map
     const float* res_rows = nullptr;   // KG-row chain: fp32 residual rows [res_mod, 256] (projected KG rows)
     int res_mod = 1;
     int sm_gs, sm_valid;   // slots per head (16 / 32) and live KG rows

@@ -200,7 +200,7 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     int rc;
     Dense d;
 
-    if ((rc = launch_cast_f16(rg, p->rg_dim, M, p->rg_dim, m_dev, w.rgb, p->rg_dim, st)) != CM_OK) return rc;
+    if (!fusion_node_fused_ok(p) && (rc = launch_cast_f16(rg, p->rg_dim, M, p->rg_dim, m_dev, w.rgb, p->rg_dim, st)) != CM_OK) return rc;
     if (fusion_node_fused_ok(p)) {
         // the whole region-node side in one kernel (fusion_node.cu)
         FusionNodeArgs a;
@@ -209,6 +209,7 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
         a.b_out1 = p->r2k_out_b; a.ln_g = p->ln_rg_w; a.ln_b = p->ln_rg_b; a.b_ffn1 = p->ffn_rg_b1; a.b_ffn2 = p->ffn_rg_b2;
         a.sm_gs = f.gs; a.sm_valid = Kk;
         a.s2 = w.s2; a.v2 = w.v2; a.y = w.y; a.attn_mean = attn_rg2kg;
+        a.x32 = rg;   // fp32 node embeddings are converted inside the kernel (rg_dim == 128 here)
         if ((rc = launch_fusion_node(a, w.rgb, W(f.w_rgproj), W(f.wcat), W(f.wv2), W(f.vot), W(f.ffn1), W(f.ffn2), st)) != CM_OK) return rc;
     } else {
     const op_t* r = w.rgb;
