@@ -358,6 +358,19 @@ def b200_arm(args):
     def e2e_step(s):
         return stager.submit(s, host_pool[s % n_pool])
 
+    # what this box's PCIe link copies from pinned memory at the step's transfer size (the roofline of `e2e`)
+    probe_h, probe_d = host_pool[0].flat, torch.empty_like(host_pool[0].flat, device=dev)
+    for _ in range(3):
+        probe_d.copy_(probe_h, non_blocking=True)
+    pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    pe0.record()
+    for _ in range(20):
+        probe_d.copy_(probe_h, non_blocking=True)
+    pe1.record()
+    torch.cuda.synchronize()
+    h2d_probe_gbs = 20 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+    del probe_d
+
     for s in range(n_warm):
         e2e_step(s)
     barrier()
@@ -446,7 +459,10 @@ def b200_arm(args):
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f16", "data": "synthetic", "config": workload_config(world, kg_src, lanes, args.input, n_pool, len(host_cores)), "clocks": clk,
             "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": stager.h2d_bytes,
-                    "d2h_bytes_per_step": stager.d2h_bytes},
+                    "d2h_bytes_per_step": stager.d2h_bytes, "h2d_probe_gbs": h2d_probe_gbs,
+                    "h2d_achieved_gbs": e2e_value / world * stager.h2d_bytes / BATCH / 1e9,
+                    "note": "h2d_probe_gbs = pinned-memory copy rate of this box at the step's transfer size, measured just "
+                            "before the e2e loop; h2d_achieved_gbs / h2d_probe_gbs is the fraction of the PCIe roofline"},
             "gpu_launches": int(round(launches_per_step * args.steps)),
             "roofline": roofline, "kernels": kernels, "kernels_saturated": saturated,
             "nodes_per_step": n_nodes, "edges_per_step": n_edges, "metrics_summary": summary,
