@@ -200,3 +200,27 @@ def test_ragged_batch_equals_per_image(detector, golden_dir):
         np.testing.assert_allclose(_np(res["kg2rg"][13 * off:13 * (off + n)]).reshape(13, n), attn["kg2rg"][0].numpy(),
                                    rtol=0, atol=TC_ATTN)
         off += n
+
+
+def test_gnn_dense_general_graph_vs_oracle(gnn):
+    """A general (non-RAG) graph with ~40 neighbours per node: a 128-node tile of the fused GCN / GAT kernels then holds
+    ~5 000 edges, past the 2 048-entry shared-memory edge list (the overflow reads go to global memory), and rows have
+    more than 16 / 32 incoming edges (several softmax trips per row).  Asymmetric edges, duplicate edges, weights."""
+    from camouflage_multimodal_b200.data import Data
+    from oracle import gnn as ognn
+    m, z = gnn
+    sd = gnn_state_dict(z)
+    gen = torch.Generator().manual_seed(5)
+    n, e = 300, 12000
+    x = torch.rand((n, 15), generator=gen)
+    ei = torch.randint(0, n, (2, e), generator=gen)
+    w = torch.rand((e, 1), generator=gen)
+    d = Data(x=x, edge_index=ei, edge_attr=w)
+    with torch.no_grad():
+        r = ognn.rg_gnn_forward(sd, d.x, d.edge_index, d.edge_attr)
+    mask, inst, edge = m(d.to("cuda"))
+    emb = m.extract_node_embeddings(d.to("cuda"))
+    np.testing.assert_allclose(_np(mask), r["mask_out"].numpy(), rtol=0, atol=2e-4)
+    np.testing.assert_allclose(_np(inst), r["instance_out"].numpy(), rtol=0, atol=2e-4)
+    np.testing.assert_allclose(_np(edge), r["edge_out"].numpy(), rtol=0, atol=2e-4)
+    np.testing.assert_allclose(_np(emb), r["node_emb"].numpy(), rtol=0, atol=2e-4)
