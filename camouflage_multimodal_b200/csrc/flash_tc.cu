@@ -25,8 +25,10 @@
 
 namespace cm {
 
-constexpr int FA_BM = 128, FA_BN = 128, FA_THREADS = 128;
-constexpr int FA_Q = 0, FA_K = 16384, FA_V = 32768, FA_P = 49152, FA_BAR = 81920, FA_SMEM = FA_BAR + 128 + 1024;
+// 64-key blocks, K / V^T double-buffered (the next block is in flight while this one is computed): 66 KB of shared
+// memory and 128 TMEM columns per CTA, three CTAs per SM whose tensor, exp and TMA phases overlap
+constexpr int FA_BM = 128, FA_BN = 64, FA_THREADS = 128;
+constexpr int FA_Q = 0, FA_K = 16384, FA_V = 24576, FA_KV_STRIDE = 16384, FA_P = 49152, FA_BAR = 65536, FA_SMEM = FA_BAR + 128 + 1024;   // K/V double-buffered
 
 __device__ __forceinline__ float fa_ex2(float x) {
     float y;
@@ -34,7 +36,7 @@ __device__ __forceinline__ float fa_ex2(float x) {
     return y;
 }
 
-__global__ void __launch_bounds__(FA_THREADS) flash_attn_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+__global__ void __launch_bounds__(FA_THREADS, 3) flash_attn_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                                                                const __grid_constant__ CUtensorMap map_vt, int Mq, const int* __restrict__ seg_ptr,
                                                                int n_keys, float scale_log2, op_t* __restrict__ out, int ldo) {
     extern __shared__ uint8_t fa_smem_raw[];
@@ -54,30 +56,38 @@ __global__ void __launch_bounds__(FA_THREADS) flash_attn_kernel(const __grid_con
         return;
     }
     uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + FA_BAR);
-    uint64_t *bar_kv = bar_q + 1, *bar_s = bar_q + 2, *bar_o = bar_q + 3;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 4);
+    uint64_t *bar_kv = bar_q + 1, *bar_s = bar_q + 3, *bar_o = bar_q + 4;   // bar_kv[2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 5);
     if (tid == 32) {
         mbar_init(bar_q, 1);
         mbar_init(bar_kv, 1);
+        mbar_init(bar_kv + 1, 1);
         mbar_init(bar_s, 1);
         mbar_init(bar_o, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256u) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(128u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t t_s = tmem_base + ((uint32_t)(warp * 32) << 16), t_o = t_s + 128;   // this warp's lane quarter
+    const uint32_t t_s = tmem_base + ((uint32_t)(warp * 32) << 16), t_o = t_s + FA_BN;   // this warp's lane quarter
     constexpr uint32_t idesc_s = umma_idesc_f16(FA_BM, FA_BN), idesc_o = umma_idesc_f16(FA_BM, 32);
-    const uint32_t aq = smem_u32(smem + FA_Q), ak = smem_u32(smem + FA_K), av = smem_u32(smem + FA_V), ap = smem_u32(smem + FA_P);
+    const uint32_t aq = smem_u32(smem + FA_Q), ap = smem_u32(smem + FA_P);
+    auto load_kv = [&](int blk) {   // thread 0: K rows and V^T columns of key block blk into buffer blk & 1
+        const int kb = key0_al + blk * FA_BN, buf = blk & 1;
+        mbar_expect_tx(bar_kv + buf, 16384);
+        tma_load_2d(smem + FA_K + buf * FA_KV_STRIDE, &map_k, bar_kv + buf, pair * 64, kb);
+        tma_load_2d(smem + FA_V + buf * FA_KV_STRIDE, &map_vt, bar_kv + buf, kb, pair * 64);
+    };
 
     if (tid == 0) {
         mbar_expect_tx(bar_q, 16384);
         tma_load_2d(smem + FA_Q, &map_q, bar_q, pair * 64, q0);
+        load_kv(0);
     }
     float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f}, o[2][32];
 #pragma unroll
@@ -87,13 +97,10 @@ __global__ void __launch_bounds__(FA_THREADS) flash_attn_kernel(const __grid_con
 
     for (int blk = 0; blk < nblk; ++blk) {
         const int kb = key0_al + blk * FA_BN;
-        if (tid == 0) {
-            mbar_expect_tx(bar_kv, 32768);
-            tma_load_2d(smem + FA_K, &map_k, bar_kv, pair * 64, kb);
-            tma_load_2d(smem + FA_V, &map_vt, bar_kv, kb, pair * 64);
-            tma_load_2d(smem + FA_V + 8192, &map_vt, bar_kv, kb + 64, pair * 64);
-        }
-        mbar_wait(bar_kv, blk & 1);
+        // the other buffer was last read by block blk - 1, whose products retired before the barrier that ended it
+        if (tid == 0 && blk + 1 < nblk) load_kv(blk + 1);
+        mbar_wait(bar_kv + (blk & 1), (blk >> 1) & 1);
+        const uint32_t ak = smem_u32(smem + FA_K + (blk & 1) * FA_KV_STRIDE), av = smem_u32(smem + FA_V + (blk & 1) * FA_KV_STRIDE);
         const int n_valid = min(FA_BN, key1 - kb), n_lo = max(0, key0 - kb);   // columns [n_lo, n_valid) are keys of the segment
 #pragma unroll
         for (int hd = 0; hd < 2; ++hd) {
@@ -111,7 +118,7 @@ __global__ void __launch_bounds__(FA_THREADS) flash_attn_kernel(const __grid_con
             float mx = -INFINITY;
             uint32_t v[32];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < FA_BN / 32; ++c) {
                 tc_ld32(t_s + c * 32, v);
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
@@ -122,7 +129,7 @@ __global__ void __launch_bounds__(FA_THREADS) flash_attn_kernel(const __grid_con
             // ---- pass 2: probabilities -> fp16 -> shared memory (two [128 x 64] K-major swizzled sub-tiles)
             float sum = 0.f;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < FA_BN / 32; ++c) {
                 tc_ld32(t_s + c * 32, v);
                 float p[32];
 #pragma unroll
@@ -130,7 +137,7 @@ __global__ void __launch_bounds__(FA_THREADS) flash_attn_kernel(const __grid_con
                     p[j] = (c * 32 + j < n_valid && c * 32 + j >= n_lo) ? fa_ex2(fmaf(__uint_as_float(v[j]), scale_log2, -m_new)) : 0.f;
                     sum += p[j];
                 }
-                uint8_t* pt = smem + FA_P + (c >> 1) * 16384;
+                uint8_t* pt = smem + FA_P;   // one [128 x 64] K-major swizzled tile
 #pragma unroll
                 for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(pt + sw128_offset(tid, (c & 1) * 4 + j)) = pack8(p + 8 * j);
             }
@@ -142,10 +149,10 @@ __global__ void __launch_bounds__(FA_THREADS) flash_attn_kernel(const __grid_con
             if (tid == 0) {
                 tc_fence_after();
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    const uint64_t da = umma_desc_sw128(ap + (k >> 2) * 16384) + 2 * (k & 3);
-                    const uint64_t db = umma_desc_sw128(av + (k >> 2) * 8192 + hd * 4096) + 2 * (k & 3);
-                    tc_mma_f16(tmem_base + 128, da, db, idesc_o, k != 0);
+                for (int k = 0; k < FA_BN / 16; ++k) {
+                    const uint64_t da = umma_desc_sw128(ap) + 2 * k;
+                    const uint64_t db = umma_desc_sw128(av + hd * 4096) + 2 * k;
+                    tc_mma_f16(tmem_base + FA_BN, da, db, idesc_o, k != 0);
                 }
                 tc_commit(bar_o);
             }
@@ -174,7 +181,7 @@ __global__ void __launch_bounds__(FA_THREADS) flash_attn_kernel(const __grid_con
     __syncthreads();
     if (warp == 0) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
     }
 }
 
