@@ -19,6 +19,7 @@
 namespace cm {
 
 constexpr int GC_ROWS = 128, GC_H = 128, GC_THREADS = 512, GC_EDGE_CAP = 2048;
+constexpr bool GC_STAGE_EDGES = false;   // staging the tile's (j, dis_j * w) list in shared memory first measured no faster than reading col / w / dis[j] in the gather (one dependent round trip fewer), so the gather reads them directly
 constexpr int GC_A_BLOCK = GC_ROWS * 128;                 // one K block (64 fp16) of the A tile: 16 KB
 constexpr int GC_OFF_A = 0;                               // A_hi kb0, A_hi kb1, A_lo kb0, A_lo kb1
 constexpr int GC_OFF_W = 4 * GC_A_BLOCK;                  // W_hi kb0, kb1, W_lo kb0, kb1 (N x 128 B each, N <= 192)
@@ -136,7 +137,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
     // ---------------------------------------------------------------- phase 0: vectors + the tile's edge list
     const int rows_here = min(GC_ROWS, n_live - m0);
     const int e_lo = p.row_ptr[m0], e_hi = p.row_ptr[m0 + rows_here];
-    if (!GAT) {
+    if (!GAT && GC_STAGE_EDGES) {
         for (int e = e_lo + tid; e < min(e_hi, e_lo + GC_EDGE_CAP); e += GC_THREADS) {
             const int j = p.col[e];
             s_edge[e - e_lo] = make_int2(j, __float_as_int(p.dis[j] * (p.w ? p.w[e] : 1.0f)));
@@ -186,7 +187,7 @@ gcn_layer_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_cons
                     int j = live ? g : 0;
                     float sc = 0.f;
                     if (e < e1) {
-                        if (e - e_lo < GC_EDGE_CAP) {
+                        if (GC_STAGE_EDGES && e - e_lo < GC_EDGE_CAP) {
                             const int2 ed = s_edge[e - e_lo];
                             j = ed.x;
                             sc = __int_as_float(ed.y);
