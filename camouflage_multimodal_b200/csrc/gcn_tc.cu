@@ -4,10 +4,10 @@
 // tile never leave the SM between the third GCNConv and the logits.
 //
 // One CTA = 128 nodes (CSR rows), 512 threads:
-//   phase 0  thread 0 starts the TMA load of the layer weight ([W_hi | W_lo], 64 KB); all threads stage the tile's
-//            edge list (neighbour index, dis[j] * w_e) in shared memory with coalesced loads
+//   phase 0  thread 0 starts the TMA load of the layer weight ([W_hi | W_lo], 64 KB)
 //   phase 1  eight lanes per row, four rows per warp at a time: sum_j s_ij x_j over fp32 rows [M,128] (L2 resident),
-//            split the sum into fp16 hi + lo and store both into the K-major SWIZZLE_128B A tile
+//            col / w / dis[j] read straight from the CSR arrays; the sum is split into fp16 hi + lo and both halves
+//            are stored into the K-major SWIZZLE_128B A tile
 //   phase 2  thread 0: 24 x tcgen05.mma (A_hi W_hi + A_lo W_hi + A_hi W_lo), fp32 accumulators in TMEM
 //   phase 3  16 warps read TMEM (lane quarter = warp % 4, column chunk = warp / 4): bias + ReLU, then either the
 //            fp32 row store (layers 1, 2) or hi/lo back into the A tile for the next chained product
@@ -19,7 +19,9 @@
 namespace cm {
 
 constexpr int GC_ROWS = 128, GC_H = 128, GC_THREADS = 512, GC_EDGE_CAP = 2048;
-constexpr bool GC_STAGE_EDGES = false;   // staging the tile's (j, dis_j * w) list in shared memory first measured no faster than reading col / w / dis[j] in the gather (one dependent round trip fewer), so the gather reads them directly
+// Staging the tile's (j, dis_j * w_e) list in shared memory before the gather measured no faster than reading
+// col / w / dis[j] in the gather itself (one dependent round trip fewer), so the gather reads them directly.
+constexpr bool GC_STAGE_EDGES = false;
 constexpr int GC_A_BLOCK = GC_ROWS * 128;                 // one K block (64 fp16) of the A tile: 16 KB
 constexpr int GC_OFF_A = 0;                               // A_hi kb0, A_hi kb1, A_lo kb0, A_lo kb1
 constexpr int GC_OFF_W = 4 * GC_A_BLOCK;                  // W_hi kb0, kb1, W_lo kb0, kb1 (N x 128 B each, N <= 192)

@@ -217,9 +217,16 @@ __global__ void slic_update_kernel(const double* __restrict__ feat, const int* _
     sn[4] = __ddiv_rn(s2, n);
 }
 
-// One CTA per image, thread 0 walks (the other lanes only initialise / copy).  `lab` holds any labels (equality is all
-// that matters); the new labels live in shared memory as int16 while the image fits (H*W <= 96K), else in `out` itself.
+// One CTA per image; the walk is sequential by definition (one warp replays it eight queue entries at a time in the
+// shared-memory variant, thread 0 alone in the global-memory fallback; the other threads only initialise / copy).  `lab` holds any labels (equality is all
+// that matters); while the image fits (about H*W <= 88K) the new labels (int16), a 4-bit neighbour-equality mask per pixel
+// and the queue all live in shared memory, else the walk runs on `out` / `labels_in` / `coords` in global memory.
 // coords [B, max_size] packed y << 16 | x.
+#ifndef CM_SLIC_WARP_WALK
+#define CM_SLIC_WARP_WALK 0
+#endif
+constexpr bool SLIC_WARP_WALK = CM_SLIC_WARP_WALK != 0;
+
 template <bool SMEM>
 __global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict__ labels_in, int H, int W, int min_size, int max_size,
                                                            int start_label, int* __restrict__ coords, int* __restrict__ out) {
@@ -228,11 +235,86 @@ __global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict
     const int* lab = labels_in + (size_t)b * n;
     int* o = out + (size_t)b * n;
     int* q = coords + (size_t)b * max(max_size, 1);
+    // SMEM variant: besides the new labels (int16), a 4-bit "same input label as my E / W / S / N neighbour" mask per
+    // pixel (two pixels per byte), built by all threads, so the sequential walk below never leaves shared memory
+    unsigned char* s_same = reinterpret_cast<unsigned char*>(s_out + n);
+    if (SMEM) q = reinterpret_cast<int*>(s_same + ((size_t)n / 2 + 8) / 4 * 4);   // the walk's queue too
+    if (SMEM) {
+        for (int i = threadIdx.x; i < (n + 1) / 2; i += blockDim.x) s_same[i] = 0;
+        __syncthreads();
+    }
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        if (SMEM) s_out[i] = -1; else o[i] = -1;
+        if (SMEM) {
+            s_out[i] = -1;
+            const int y = i / W, x = i - y * W, l = lab[i];
+            unsigned m = 0;
+            if (x + 1 < W && lab[i + 1] == l) m |= 1u;
+            if (x > 0 && lab[i - 1] == l) m |= 2u;
+            if (y + 1 < H && lab[i + W] == l) m |= 4u;
+            if (y > 0 && lab[i - W] == l) m |= 8u;
+            atomicOr(reinterpret_cast<unsigned*>(s_same) + (i >> 3), m << (4 * (i & 7)));
+        } else {
+            o[i] = -1;
+        }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (SMEM && SLIC_WARP_WALK && threadIdx.x < 32) {
+        // One warp replays the sequential walk: lane = (queue entry % 8) * 4 + direction, so eight queue entries are
+        // expanded per step.  Lane order == the order the scalar loop visits (entry, direction) pairs, so "first lane
+        // claims a pixel", "last lane sets adjacent" and "stop at the lane that fills the queue" reproduce it exactly:
+        // a pixel claimed by an earlier lane reads as `cur` for the later ones in the scalar loop, i.e. no effect.
+        const int lane = threadIdx.x, ent = lane >> 2, dir = lane & 3;
+        const int dy = dir == 2 ? 1 : (dir == 3 ? -1 : 0), dx = dir == 0 ? 1 : (dir == 1 ? -1 : 0);
+        const unsigned below = (1u << lane) - 1u;
+        int cur = start_label;
+        for (int base = 0; base < n; base += 32) {
+            unsigned pending = __ballot_sync(~0u, base + lane < n && s_out[base + lane] < 0);
+            while (pending) {
+                const int p0 = base + __ffs(pending) - 1;
+                if (lane == 0) {
+                    s_out[p0] = (short)cur;
+                    q[0] = p0;
+                }
+                __syncwarp();
+                int size = 1, visited = 0, adjacent = 0;
+                while (visited < size && size < max_size) {
+                    const int nent = min(8, size - visited);
+                    const bool act = ent < nent;
+                    const int pi = act ? q[visited + ent] : 0;
+                    const int py = pi / W, px = pi - py * W, qy = py + dy, qx = px + dx;
+                    const bool inb = act && qy >= 0 && qy < H && qx >= 0 && qx < W;
+                    const int qi = inb ? qy * W + qx : 0;
+                    const int oq = inb ? (int)s_out[qi] : cur;
+                    const bool same = inb && ((s_same[pi >> 1] >> (4 * (pi & 1) + dir)) & 1u);
+                    const bool cand = oq == -1 && same;
+                    const unsigned cm = __ballot_sync(~0u, cand);
+                    bool winner = false;
+                    if (cand) winner = (__ffs(__match_any_sync(cm, qi)) - 1) == lane;
+                    const unsigned wm = __ballot_sync(~0u, winner);
+                    const int room = max_size - size, rank = __popc(wm & below);
+                    const unsigned fill = __ballot_sync(~0u, winner && rank == room - 1);   // the append that fills the queue
+                    const int cut = fill ? __ffs(fill) - 1 : 31;
+                    if (winner && lane <= cut) {
+                        s_out[qi] = (short)cur;
+                        q[size + rank] = qi;
+                    }
+                    const unsigned am = __ballot_sync(~0u, inb && !cand && oq >= 0 && oq != cur && lane <= cut);
+                    if (am) adjacent = __shfl_sync(~0u, oq, 31 - __clz(am));
+                    size += min(__popc(wm), room);
+                    visited += nent;
+                    __syncwarp();
+                }
+                if (size < min_size) {
+                    for (int i = lane; i < size; i += 32) s_out[q[i]] = (short)adjacent;
+                } else {
+                    ++cur;
+                }
+                __syncwarp();
+                pending = __ballot_sync(~0u, base + lane < n && s_out[base + lane] < 0);
+            }
+        }
+    }
+    if (!(SMEM && SLIC_WARP_WALK) && threadIdx.x == 0) {
         auto get = [&](int i) -> int { return SMEM ? (int)s_out[i] : o[i]; };
         auto put = [&](int i, int v) { if (SMEM) s_out[i] = (short)v; else o[i] = v; };
         int cur = start_label;
@@ -241,17 +323,19 @@ __global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict
             for (int x = 0; x < W; ++x) {
                 if (get(y * W + x) >= 0) continue;
                 int adjacent = 0;
-                const int label = lab[y * W + x];
+                const int label = SMEM ? 0 : lab[y * W + x];
                 put(y * W + x, cur);
                 int size = 1, visited = 0;
                 q[0] = (y << 16) | x;
                 while (visited < size && size < max_size) {
-                    const int py = q[visited] >> 16, px = q[visited] & 0xffff;
+                    const int py = q[visited] >> 16, px = q[visited] & 0xffff, pi = py * W + px;
+                    const unsigned same = SMEM ? (s_same[pi >> 1] >> (4 * (pi & 1))) & 15u : 0u;
                     for (int i = 0; i < 4; ++i) {
                         const int qy = py + ddy[i], qx = px + ddx[i];
                         if (qy < 0 || qy >= H || qx < 0 || qx >= W) continue;
                         const int oq = get(qy * W + qx);
-                        if (oq == -1 && lab[qy * W + qx] == label) {
+                        const bool same_label = SMEM ? ((same >> i) & 1u) != 0 : lab[qy * W + qx] == label;
+                        if (oq == -1 && same_label) {
                             put(qy * W + qx, cur);
                             q[size++] = (qy << 16) | qx;
                             if (size >= max_size) break;
@@ -275,12 +359,14 @@ __global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict
 
 static int launch_slic_connect(const int* labels_in, int batch, int h, int w, int min_size, int max_size, int start_label, int* coords,
                                int* out, cudaStream_t st) {
-    const size_t smem = (size_t)h * w * sizeof(short);
+    // labels (int16) + 4-bit neighbour masks + the queue; at most n / min_size + 1 labels are ever handed out
+    const size_t smem = (size_t)h * w * sizeof(short) + ((size_t)h * w / 2 + 8) / 4 * 4 + (size_t)std::max(max_size, 1) * sizeof(int);
+    const long long max_label = (long long)start_label + (long long)h * w / std::max(min_size, 1) + 1;
     CM_TIMED("slic_connectivity", st);
-    if (smem <= 192 * 1024 && (long long)h * w + start_label < 32767) {
+    if (smem <= 224 * 1024 && max_label < 32767 && ((size_t)h * w * sizeof(short)) % 4 == 0) {
         static bool attr = false;
         if (!attr) {
-            cudaFuncSetAttribute(slic_connect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 192 * 1024);
+            cudaFuncSetAttribute(slic_connect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
             attr = true;
         }
         slic_connect_kernel<true><<<batch, 256, smem, st>>>(labels_in, h, w, min_size, max_size, start_label, coords, out);

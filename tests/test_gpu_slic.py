@@ -34,6 +34,28 @@ def test_connectivity_stage_is_bit_exact():
         assert np.array_equal(out[i].cpu().numpy(), ref)
 
 
+@pytest.mark.parametrize("h,w,min_size,max_size", [(64, 64, 20, 50), (256, 256, 30, 90), (96, 200, 1, 7), (128, 128, 40, 4000),
+                                                   (256, 256, 0, 5), (40, 24, 500, 2000)])
+def test_connectivity_truncation_and_merges(h, w, min_size, max_size):
+    """Blocky random labels with speckle: most segments are cut at max_size or merged into a neighbour, the cases where
+    the order of the walk matters (queue order, which neighbour is met last, where the cut falls)."""
+    from camouflage_multimodal_b200 import _lib
+    from oracle import slic as oslic
+    rng = np.random.default_rng(h * 1000 + max_size)
+    coarse = rng.integers(0, 4, size=(2, (h + 7) // 8, (w + 7) // 8))
+    lab = np.repeat(np.repeat(coarse, 8, axis=1), 8, axis=2)[:, :h, :w].copy()
+    speck = rng.random(lab.shape) < 0.08
+    lab[speck] = rng.integers(0, 4, size=int(speck.sum()))
+    lab_in = torch.as_tensor(lab.astype(np.int32)).cuda()
+    out = torch.empty_like(lab_in)
+    coords = torch.empty((2, max(max_size, 1)), dtype=torch.int32, device="cuda")
+    _lib.check(_lib.load().cm_slic_enforce_connectivity(_lib.ptr(lab_in), 2, h, w, min_size, max_size, 1, _lib.ptr(coords),
+                                                        _lib.ptr(out), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+               "connectivity")
+    for i in range(2):
+        assert np.array_equal(out[i].cpu().numpy(), oslic.enforce_connectivity(lab[i], min_size, max_size, 1))
+
+
 def test_slic_matches_oracle_and_invariants():
     from camouflage_multimodal_b200.region_graph import slic_segments
     from oracle import slic as oslic
