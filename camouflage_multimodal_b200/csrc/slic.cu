@@ -223,7 +223,7 @@ __global__ void slic_update_kernel(const double* __restrict__ feat, const int* _
 // and the queue all live in shared memory, else the walk runs on `out` / `labels_in` / `coords` in global memory.
 // coords [B, max_size] packed y << 16 | x.
 #ifndef CM_SLIC_WARP_WALK
-#define CM_SLIC_WARP_WALK 0
+#define CM_SLIC_WARP_WALK 1
 #endif
 constexpr bool SLIC_WARP_WALK = CM_SLIC_WARP_WALK != 0;
 
