@@ -7,8 +7,8 @@
 //   slic_lab_kernel       rgb2lab (sRGB, D65), * 1/compactness
 //   slic_assign_kernel    per pixel: the cluster of least distance among those whose +-2*step window holds the pixel,
 //                         lowest index on ties (the sequential loop's strict '<' in index order)
-//   slic_update_kernel    one thread per cluster walks the OLD window in raster order: sums / count -> new centre
-//   slic_connect_kernel   _enforce_label_connectivity_cython: raster-order BFS, one thread per image (the algorithm is
+//   slic_update_kernel    one warp per cluster walks the OLD window in raster order: sums / count -> new centre
+//   slic_connect_kernel   _enforce_label_connectivity_cython: raster-order BFS, one warp per image (the algorithm is
 //                         sequential by definition: the label a small segment joins depends on the visiting order)
 #include <math.h>
 
@@ -188,38 +188,40 @@ __global__ void __launch_bounds__(256) slic_assign_kernel(const double* __restri
 }
 
 // one thread per (image, cluster): raster-order sums over the cluster's OLD window (every member lies inside it)
-__global__ void slic_update_kernel(const double* __restrict__ feat, const int* __restrict__ nearest, SlicGrid g, int batch, int H, int W,
-                                   const double* __restrict__ seg_old, double* __restrict__ seg_new) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) slic_update_kernel(const double* __restrict__ feat, const int* __restrict__ nearest, SlicGrid g, int batch,
+                                                          int H, int W, const double* __restrict__ seg_old, double* __restrict__ seg_new) {
+    // One warp per cluster.  The lanes scan a window row 32 pixels at a time (coalesced) and ballot the members; lane c
+    // then owns running sum c (y, x, three colours) and adds the members in raster order, so every sum is the same
+    // sequence of float64 additions as the scalar loop.  The count is an exact integer either way.
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (i >= batch * g.K) return;
-    const int b = i / g.K, k = i - b * g.K;
+    const int b = i / g.K, k = i - b * g.K, c = min(lane, 4);
     const double* so = seg_old + (size_t)i * 5;
     int ylo, yhi, xlo, xhi;
     slic_window(so[0], g.step_y, H, &ylo, &yhi);
     slic_window(so[1], g.step_x, W, &xlo, &xhi);
-    double sy = 0, sx = 0, s0 = 0, s1 = 0, s2 = 0, n = 0;
-    for (int y = ylo; y < yhi; ++y)
-        for (int x = xlo; x < xhi; ++x) {
-            const size_t p = ((size_t)b * H + y) * W + x;
-            if (nearest[p] != k) continue;
-            n = __dadd_rn(n, 1.0);
-            sy = __dadd_rn(sy, (double)y);
-            sx = __dadd_rn(sx, (double)x);
-            s0 = __dadd_rn(s0, feat[3 * p]);
-            s1 = __dadd_rn(s1, feat[3 * p + 1]);
-            s2 = __dadd_rn(s2, feat[3 * p + 2]);
+    double acc = 0;
+    int cnt = 0;
+    for (int y = ylo; y < yhi; ++y) {
+        const size_t row = ((size_t)b * H + y) * W;
+        for (int x0 = xlo; x0 < xhi; x0 += 32) {
+            const int x = x0 + lane;
+            unsigned m = __ballot_sync(~0u, x < xhi && nearest[row + x] == k);
+            cnt += __popc(m);
+            while (m) {
+                const int xx = x0 + __ffs(m) - 1;
+                m &= m - 1;
+                const double v = c == 0 ? (double)y : (c == 1 ? (double)xx : feat[3 * (row + xx) + (c - 2)]);
+                acc = __dadd_rn(acc, v);
+            }
         }
-    double* sn = seg_new + (size_t)i * 5;
-    sn[0] = __ddiv_rn(sy, n);   // 0 / 0 = NaN for an emptied cluster, as in the reference loop
-    sn[1] = __ddiv_rn(sx, n);
-    sn[2] = __ddiv_rn(s0, n);
-    sn[3] = __ddiv_rn(s1, n);
-    sn[4] = __ddiv_rn(s2, n);
+    }
+    if (lane < 5) seg_new[(size_t)i * 5 + lane] = __ddiv_rn(acc, (double)cnt);   // 0 / 0 = NaN for an emptied cluster, as in the reference loop
 }
 
 // One CTA per image; the walk is sequential by definition (one warp replays it eight queue entries at a time in the
-// shared-memory variant, thread 0 alone in the global-memory fallback; the other threads only initialise / copy).  `lab` holds any labels (equality is all
-// that matters); while the image fits (about H*W <= 88K) the new labels (int16), a 4-bit neighbour-equality mask per pixel
+// shared-memory variant, thread 0 alone in the global-memory fallback; the other threads only initialise / copy).
+// `lab` holds any labels (equality is all that matters); while the image fits (about H*W <= 88K) the new labels (int16), a 4-bit neighbour-equality mask per pixel
 // and the queue all live in shared memory, else the walk runs on `out` / `labels_in` / `coords` in global memory.
 // coords [B, max_size] packed y << 16 | x.
 #ifndef CM_SLIC_WARP_WALK
@@ -505,7 +507,7 @@ extern "C" int cm_slic(const uint8_t* image_u8, int batch, int h, int w, int n_s
         CM_TIMED("slic_iterations", st);
         for (int it = 0; it < max_num_iter; ++it) {
             slic_assign_kernel<<<dim3(ceil_div(w, 16), ceil_div(h, 16), batch), 256, 0, st>>>(ws.a, cur, g, h, w, ws.nearest);
-            slic_update_kernel<<<ceil_div(batch * g.K, 64), 64, 0, st>>>(ws.a, ws.nearest, g, batch, h, w, cur, nxt);
+            slic_update_kernel<<<ceil_div(batch * g.K, 8), 256, 0, st>>>(ws.a, ws.nearest, g, batch, h, w, cur, nxt);
             std::swap(cur, nxt);
         }
     }
