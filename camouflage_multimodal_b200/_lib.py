@@ -149,7 +149,41 @@ SIGNATURES = {
 _lib = None
 
 
-def load() -> C.CDLL:
+class StreamArg(C.c_void_p):
+    """A ``cudaStream_t`` argument that remembers which device it belongs to (see ``_Guarded``)."""
+    device_index = None
+
+
+class _Guarded:
+    """The loaded library with a device guard around every call that takes a stream: the library launches on the
+    CURRENT device, so a call whose stream (``stream_ptr(tensor.device)``) lives on another device makes that device
+    current for the duration of the call -- what a torch op does for its own kernels.  Without it a model on cuda:1
+    called while the current device is 0 would launch on a foreign stream (invalid resource handle)."""
+
+    def __init__(self, cdll):
+        self._cdll = cdll
+        self._fns = {}
+
+    def __getattr__(self, name):
+        fn = self._fns.get(name)
+        if fn is None:
+            raw = getattr(self._cdll, name)
+            takes_stream = name in SIGNATURES and len(SIGNATURES[name][1]) > 0 and SIGNATURES[name][1][-1] is _fp
+
+            def call(*args, _raw=raw):
+                st = args[-1] if args else None
+                idx = getattr(st, "device_index", None)
+                if idx is not None and idx != torch.cuda.current_device():
+                    with torch.cuda.device(idx):
+                        return _raw(*args)
+                return _raw(*args)
+
+            fn = call if takes_stream else raw
+            self._fns[name] = fn
+        return fn
+
+
+def load() -> "_Guarded":
     """Load the shared library (once).  Raises if it has not been built."""
     global _lib
     if _lib is None:
@@ -162,8 +196,28 @@ def load() -> C.CDLL:
             fn = getattr(lib, name)   # AttributeError if the ABI and the binding drift apart
             fn.restype = res
             fn.argtypes = args
-        _lib = lib
+        _lib = _Guarded(lib)
     return _lib
+
+
+# Bumped by everything that writes parameters through raw device pointers (FusedAdamW.step -> cm_adamw_step): torch's
+# Tensor._version does not see such writes, so every cache of folded / converted weights keys on this counter too.
+_param_generation = 0
+
+
+def param_generation() -> int:
+    return _param_generation
+
+
+def bump_param_generation(tensors=()) -> None:
+    """Call after a kernel wrote ``tensors`` in place behind torch's back."""
+    global _param_generation
+    _param_generation += 1
+    for t in tensors:
+        try:
+            torch.autograd.graph.increment_version(t)
+        except Exception:   # the generation counter alone already invalidates this package's caches
+            break
 
 
 class CmError(RuntimeError):
@@ -187,7 +241,12 @@ def ptr(t):
 
 
 def stream_ptr(device=None):
-    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    """The current stream of ``device`` (default: the current device) as a ``cudaStream_t`` argument."""
+    st = StreamArg(torch.cuda.current_stream(device).cuda_stream)
+    if device is not None:
+        device = torch.device(device)
+        st.device_index = device.index if device.index is not None else torch.cuda.current_device()
+    return st
 
 
 def require_cuda(t: torch.Tensor, name: str) -> None:

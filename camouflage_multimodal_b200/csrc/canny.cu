@@ -240,10 +240,9 @@ extern "C" int cm_canny(const void* image, int image_is_u8, int batch, int h, in
     {
         const size_t smem = (size_t)h * w;
         const int use_smem = smem <= 200 * 1024;
-        static bool attr = false;
-        if (!attr) {
+        static PerDeviceOnce attr;
+        if (attr.first()) {
             cudaFuncSetAttribute(canny_hysteresis_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-            attr = true;
         }
         CM_TIMED("canny_hysteresis", st);
         canny_hysteresis_kernel<<<batch, 1024, use_smem ? smem : 0, st>>>(ws.cls, h, w, use_smem, edges);

@@ -48,6 +48,12 @@ int check_device() {
     return CM_OK;
 }
 
+int current_device_slot() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    return dev;
+}
+
 int num_sms() {
     int dev = 0;
     cudaGetDevice(&dev);

@@ -43,6 +43,28 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
         if (_rc != CM_OK) return _rc;               \
     } while (0)
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a PER-DEVICE setting: one flag / high-water mark per device, so
+// the second GPU used by a process gets its opt-in too.
+int current_device_slot();   // cudaGetDevice clamped to [0, 64)
+struct PerDeviceOnce {
+    bool done[64] = {};
+    bool first() {
+        const int d = current_device_slot();
+        if (done[d]) return false;
+        done[d] = true;
+        return true;
+    }
+};
+struct PerDeviceMax {
+    size_t v[64] = {};
+    bool raise(size_t s) {
+        const int d = current_device_slot();
+        if (s <= v[d]) return false;
+        v[d] = s;
+        return true;
+    }
+};
+
 // Carves a caller-provided workspace into aligned slices.
 struct Carver {
     char* base;

@@ -359,10 +359,9 @@ static int launch_dense_bn(const Dense& d, cudaStream_t st) {
     if (rc != CM_OK) return rc;
     rc = make_map(&mw, d.W, (uint64_t)d.N, (uint64_t)d.K, (uint64_t)d.K, BN);
     if (rc != CM_OK) return rc;
-    static bool attr = false;
-    if (!attr) {
+    static PerDeviceOnce attr;
+    if (attr.first()) {
         cudaFuncSetAttribute(dense_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN>::TOTAL);
-        attr = true;
     }
     dim3 grid(ceil_div(d.N, BN), ceil_div(d.M, TC_BM));
     {

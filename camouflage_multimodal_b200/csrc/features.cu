@@ -562,10 +562,9 @@ extern "C" int cm_node_features(const float* image, const int32_t* labels, const
     cudaStream_t st = as_stream(stream);
     const size_t smem = label_cap > 0 ? nf_tile_smem(h, w, label_cap) : 0;
     if (label_cap > 0 && w % 8 == 0 && smem <= 200 * 1024 && batch <= 65535 && (long long)((h + NF_CLUSTER - 1) / NF_CLUSTER) * w <= 65535) {
-        static size_t smem_set = 0;
-        if (smem > smem_set) {
+        static PerDeviceMax smem_set;
+        if (smem_set.raise(smem)) {
             cudaFuncSetAttribute(node_features_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            smem_set = smem;
         }
         {
             CM_TIMED("node_features", st);

@@ -580,10 +580,9 @@ static int node_features_u8_impl(const uint8_t* image_u8, const void* labels_v, 
     CM_REQUIRE(ncl > 0, "cm_node_features_u8: image %dx%d with label_cap %d does not fit the integer tables; use cm_node_features "
                "on float images", h, w, label_cap);
     cudaStream_t st = as_stream(stream);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
+    static PerDeviceMax smem_set;
+    if (smem_set.raise(smem)) {
         cudaFuncSetAttribute(node_features_u8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        smem_set = smem;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(ncl, batch);

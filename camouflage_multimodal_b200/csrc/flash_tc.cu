@@ -197,10 +197,9 @@ int launch_flash(const op_t* Q, int Mq, const op_t* K, int Mk, const op_t* Vt, i
     if ((rc = make_map(&mq, Q, (uint64_t)Mq, (uint64_t)D, (uint64_t)D, FA_BM)) != CM_OK) return rc;
     if ((rc = make_map(&mk, K, (uint64_t)Mk, (uint64_t)D, (uint64_t)D, FA_BN)) != CM_OK) return rc;
     if ((rc = make_map(&mv, Vt, (uint64_t)D, (uint64_t)Mk, (uint64_t)ldv, 64)) != CM_OK) return rc;
-    static bool attr = false;
-    if (!attr) {
+    static PerDeviceOnce attr;
+    if (attr.first()) {
         cudaFuncSetAttribute(flash_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM);
-        attr = true;
     }
     const int segs = seg_ptr ? n_seg : 1;
     CM_REQUIRE(segs >= 1 && segs <= 65535, "flash attention: 1..65535 key segments");

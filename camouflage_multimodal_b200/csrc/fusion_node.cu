@@ -376,11 +376,10 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
 }
 
 static void fn_set_attr() {
-    static bool attr = false;
-    if (!attr) {
+    static PerDeviceOnce attr;
+    if (attr.first()) {
         cudaFuncSetAttribute(fusion_node_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, FN_SMEM);
         cudaFuncSetAttribute(fusion_node_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FN_SMEM);
-        attr = true;
     }
 }
 

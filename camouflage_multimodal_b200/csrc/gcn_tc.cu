@@ -444,12 +444,11 @@ int launch_gcn_layer_tc(const GcnLayer& p, cudaStream_t st) {
         if ((rc = make_map(&mfc, p.fc_split, GC_H, 3 * GC_H, 3 * GC_H, GC_H)) != CM_OK) return rc;
         if (p.do_heads && (rc = make_map(&mh1, p.h1_split, 192, 3 * GC_H, 3 * GC_H, 192)) != CM_OK) return rc;
     }
-    static bool attr = false;
-    if (!attr) {
+    static PerDeviceOnce attr;
+    if (attr.first()) {
         cudaFuncSetAttribute(gcn_layer_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, GC_SMEM);
         cudaFuncSetAttribute(gcn_layer_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GC_SMEM);
         cudaFuncSetAttribute(gcn_layer_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GC_SMEM_GAT);
-        attr = true;
     }
     const int grid = ceil_div(p.M, GC_ROWS);
     if (p.gat) {

@@ -414,12 +414,11 @@ static int rag_build_impl(const void* labels, int label_bytes, int batch, int h,
     int rows = 8;
     while (rows > 1 && (long long)ceil_div(h, rows) * batch < 2LL * num_sms()) rows >>= 1;
     const size_t smem = (size_t)label_cap * 4 * sizeof(int);
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDeviceOnce attr_done;
+    if (attr_done.first()) {
         cudaFuncSetAttribute(rag_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         cudaFuncSetAttribute(rag_scan8_kernel<int>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         cudaFuncSetAttribute(rag_scan8_kernel<short>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_done = true;
     }
     dim3 g1(ceil_div(h, rows), batch);
     {

@@ -2,9 +2,11 @@
 // as the reference calls it (models/region_graph/extract_rg_embeddings.py:143-144), restated in oracle/slic.py.
 // float64 throughout, every sum in the order of the sequential algorithm (no FMA contraction), so the result equals the
 // oracle's up to libm differences in pow / cbrt:
-//   slic_float_kernel     byte * (1/255), then the singleton z pass of the 3-D Gaussian (sum of all taps on one value)
-//   slic_blur_kernel      scipy correlate1d (symmetric form), mode='reflect', along y then x, per channel
-//   slic_lab_kernel       rgb2lab (sRGB, D65), * 1/compactness
+//   slic_minmax_kernel    per-image min / max byte (skimage >= 0.19 rescales the image to [0,1] first)
+//   slic_lab_kernel       byte * (1/255), min-max rescale, rgb2lab (sRGB, D65), then the singleton z pass of the 3-D
+//                         Gaussian (sum of all taps on one value) -- Lab BEFORE the blur, as skimage >= 0.19 does
+//   slic_blur_kernel      scipy correlate1d (symmetric form), mode='reflect', along y then x, per Lab channel; the x pass
+//                         multiplies by 1 / compactness on the way out
 //   slic_assign_kernel    per pixel: the cluster of least distance among those whose +-2*step window holds the pixel,
 //                         lowest index on ties (the sequential loop's strict '<' in index order)
 //   slic_update_kernel    one warp per cluster walks the OLD window in raster order: sums / count -> new centre
@@ -37,20 +39,40 @@ __device__ __forceinline__ int slic_reflect(int i, int n) {   // scipy mode='ref
     return i;
 }
 
-// out [B,H,W,3] f64
-__global__ void slic_float_kernel(const uint8_t* __restrict__ img, long long n, const SlicGauss g, int z_pass, double* __restrict__ out) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    double v = __dmul_rn((double)img[i], 1.0 / 255.0);
-    if (z_pass) {   // every tap of the z axis (length 1, reflect) reads the same value
-        double t = __dmul_rn(v, g.w[g.radius]);
-        for (int j = g.radius; j >= 1; --j) t = __dadd_rn(t, __dmul_rn(__dadd_rn(v, v), g.w[g.radius - j]));
-        v = t;
+__global__ void slic_mm_init_kernel(int* __restrict__ mm, int batch) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < batch) {
+        mm[2 * i] = 255;
+        mm[2 * i + 1] = 0;
     }
-    out[i] = v;
+}
+// per-image min / max byte (skimage >= 0.19 rescales the whole image to [0,1] before anything else); mm [B,2] = (min, max),
+// pre-set to (255, 0)
+__global__ void slic_minmax_kernel(const uint8_t* __restrict__ img, int per_image, int* __restrict__ mm) {
+    const int b = blockIdx.y;
+    const uint8_t* p = img + (size_t)b * per_image;
+    int lo = 255, hi = 0;
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4; i < per_image; i += gridDim.x * blockDim.x * 4) {
+        if (i + 3 < per_image && (reinterpret_cast<uintptr_t>(p + i) & 3) == 0) {
+            const uchar4 v = *reinterpret_cast<const uchar4*>(p + i);
+            lo = min(lo, min(min((int)v.x, (int)v.y), min((int)v.z, (int)v.w)));
+            hi = max(hi, max(max((int)v.x, (int)v.y), max((int)v.z, (int)v.w)));
+        } else {
+            for (int j = i; j < min(i + 4, per_image); ++j) {
+                lo = min(lo, (int)p[j]);
+                hi = max(hi, (int)p[j]);
+            }
+        }
+    }
+    lo = __reduce_min_sync(~0u, lo);
+    hi = __reduce_max_sync(~0u, hi);
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(mm + 2 * b, lo);
+        atomicMax(mm + 2 * b + 1, hi);
+    }
 }
 // axis 0: along y, axis 1: along x; in / out [B,H,W,3]
-__global__ void slic_blur_kernel(const double* __restrict__ in, int H, int W, int axis, const SlicGauss g, double* __restrict__ out) {
+__global__ void slic_blur_kernel(const double* __restrict__ in, int H, int W, int axis, const SlicGauss g, double scale, double* __restrict__ out) {
     const int xc = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;   // xc = x * 3 + channel
     if (xc >= 3 * W) return;
     const int x = xc / 3, c = xc - 3 * x;
@@ -68,16 +90,22 @@ __global__ void slic_blur_kernel(const double* __restrict__ in, int H, int W, in
         }
         t = __dadd_rn(t, __dmul_rn(__dadd_rn(a, d), g.w[g.radius - j]));
     }
-    out[((size_t)b * H + y) * W * 3 + xc] = t;
+    out[((size_t)b * H + y) * W * 3 + xc] = __dmul_rn(t, scale);   // 1.0 (exact) or 1 / compactness after the last pass
 }
-// in place: rgb -> Lab * ratio
-__global__ void slic_lab_kernel(double* __restrict__ v, long long npx, double ratio) {
+// bytes -> img_as_float (* 1/255) -> min-max rescale -> rgb2lab (sRGB, D65) -> the singleton z pass of the 3-D Gaussian
+// (sum of all taps on one value) -> * ratio (1.0 while a blur follows).  out [B,H,W,3] f64
+__global__ void slic_lab_kernel(const uint8_t* __restrict__ img, const int* __restrict__ mm, int hw, long long npx, const SlicGauss g, int z_pass,
+                                double ratio, double* __restrict__ v) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npx) return;
+    const int b = (int)(i / hw);
+    const double imin = __dmul_rn((double)mm[2 * b], 1.0 / 255.0), imax = __dmul_rn((double)mm[2 * b + 1], 1.0 / 255.0);
+    const double range = __dadd_rn(imax, -imin);
     double c[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const double a = v[3 * i + k];
+        double a = __dadd_rn(__dmul_rn((double)img[3 * i + k], 1.0 / 255.0), -imin);
+        if (imax != imin) a = __ddiv_rn(a, range);
         c[k] = a > 0.04045 ? pow(__ddiv_rn(__dadd_rn(a, 0.055), 1.055), 2.4) : __ddiv_rn(a, 12.92);
     }
     const double M[3][3] = {{0.412453, 0.357580, 0.180423}, {0.212671, 0.715160, 0.072169}, {0.019334, 0.119193, 0.950227}};
@@ -89,9 +117,17 @@ __global__ void slic_lab_kernel(double* __restrict__ v, long long npx, double ra
         t = __ddiv_rn(t, white[k]);
         f[k] = t > 0.008856 ? cbrt(t) : __dadd_rn(__dmul_rn(7.787, t), 16.0 / 116.0);
     }
-    v[3 * i] = __dmul_rn(__dadd_rn(__dmul_rn(116.0, f[1]), -16.0), ratio);
-    v[3 * i + 1] = __dmul_rn(__dmul_rn(500.0, __dadd_rn(f[0], -f[1])), ratio);
-    v[3 * i + 2] = __dmul_rn(__dmul_rn(200.0, __dadd_rn(f[1], -f[2])), ratio);
+    double lab[3] = {__dadd_rn(__dmul_rn(116.0, f[1]), -16.0), __dmul_rn(500.0, __dadd_rn(f[0], -f[1])), __dmul_rn(200.0, __dadd_rn(f[1], -f[2]))};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        double x = lab[k];
+        if (z_pass) {   // every tap of the z axis (length 1, reflect) reads the same value
+            double t = __dmul_rn(x, g.w[g.radius]);
+            for (int j = g.radius; j >= 1; --j) t = __dadd_rn(t, __dmul_rn(__dadd_rn(x, x), g.w[g.radius - j]));
+            x = t;
+        }
+        v[3 * i + k] = __dmul_rn(x, ratio);
+    }
 }
 
 // seg [B,K,5] = (y, x, L, a, b)
@@ -278,7 +314,7 @@ __global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict
                     q[0] = p0;
                 }
                 __syncwarp();
-                int size = 1, visited = 0, adjacent = 0;
+                int size = 1, visited = 0, adjacent = start_label;   // no labelled neighbour yet: join the first label (oracle/slic.py)
                 while (visited < size && size < max_size) {
                     const int nent = min(8, size - visited);
                     const bool act = ent < nent;
@@ -324,7 +360,7 @@ __global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict
         for (int y = 0; y < H; ++y)
             for (int x = 0; x < W; ++x) {
                 if (get(y * W + x) >= 0) continue;
-                int adjacent = 0;
+                int adjacent = start_label;
                 const int label = SMEM ? 0 : lab[y * W + x];
                 put(y * W + x, cur);
                 int size = 1, visited = 0;
@@ -366,10 +402,9 @@ static int launch_slic_connect(const int* labels_in, int batch, int h, int w, in
     const long long max_label = (long long)start_label + (long long)h * w / std::max(min_size, 1) + 1;
     CM_TIMED("slic_connectivity", st);
     if (smem <= 224 * 1024 && max_label < 32767 && ((size_t)h * w * sizeof(short)) % 4 == 0) {
-        static bool attr = false;
-        if (!attr) {
+        static PerDeviceOnce attr;
+        if (attr.first()) {
             cudaFuncSetAttribute(slic_connect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
-            attr = true;
         }
         slic_connect_kernel<true><<<batch, 256, smem, st>>>(labels_in, h, w, min_size, max_size, start_label, coords, out);
     } else {
@@ -414,7 +449,7 @@ static void regular_grid_hw(int H, int W, int n_points, int* start_y, int* start
 
 struct SlicWs {
     double *a, *b, *seg0, *seg1;
-    int *nearest, *coords;
+    int *nearest, *coords, *mm;
     size_t total;
 };
 static SlicWs carve_slic(void* ws, int batch, int h, int w, int K, int max_size) {
@@ -427,6 +462,7 @@ static SlicWs carve_slic(void* ws, int batch, int h, int w, int K, int max_size)
     r.seg1 = c.take<double>((size_t)batch * K * 5);
     r.nearest = c.take<int>(n);
     r.coords = c.take<int>((size_t)batch * std::max(max_size, 1));
+    r.mm = c.take<int>((size_t)batch * 2);
     r.total = align_up(c.off, 256);
     return r;
 }
@@ -493,13 +529,14 @@ extern "C" int cm_slic(const uint8_t* image_u8, int batch, int h, int w, int n_s
     const long long npx = (long long)batch * h * w;
     {
         CM_TIMED("slic_preprocess", st);
-        slic_float_kernel<<<ceil_div(npx * 3, 256), 256, 0, st>>>(image_u8, npx * 3, gw, sigma > 0.0 ? 1 : 0, ws.a);
-        if (sigma > 0.0) {
+        slic_mm_init_kernel<<<ceil_div(batch, 256), 256, 0, st>>>(ws.mm, batch);
+        slic_minmax_kernel<<<dim3(std::min(ceil_div((long long)h * w * 3, 1024), 64), batch), 256, 0, st>>>(image_u8, h * w * 3, ws.mm);
+        slic_lab_kernel<<<ceil_div(npx, 256), 256, 0, st>>>(image_u8, ws.mm, h * w, npx, gw, sigma > 0.0 ? 1 : 0, sigma > 0.0 ? 1.0 : 1.0 / compactness, ws.a);
+        if (sigma > 0.0) {   // scipy gaussian_filter over the Lab volume: y pass, then x pass (* 1 / compactness on the way out)
             dim3 grid(ceil_div(3 * w, 128), h, batch);
-            slic_blur_kernel<<<grid, 128, 0, st>>>(ws.a, h, w, 0, gw, ws.b);
-            slic_blur_kernel<<<grid, 128, 0, st>>>(ws.b, h, w, 1, gw, ws.a);
+            slic_blur_kernel<<<grid, 128, 0, st>>>(ws.a, h, w, 0, gw, 1.0, ws.b);
+            slic_blur_kernel<<<grid, 128, 0, st>>>(ws.b, h, w, 1, gw, 1.0 / compactness, ws.a);
         }
-        slic_lab_kernel<<<ceil_div(npx, 256), 256, 0, st>>>(ws.a, npx, 1.0 / compactness);
         slic_seed_kernel<<<ceil_div(batch * g.K, 256), 256, 0, st>>>(g, batch, ws.seg0);
     }
     double *cur = ws.seg0, *nxt = ws.seg1;

@@ -51,7 +51,7 @@ class _FusionRunner:
 
     def params(self):
         ts = self._tensors()
-        key = tuple((t.data_ptr(), t._version) for t in ts)
+        key = tuple((t.data_ptr(), t._version) for t in ts) + (_lib.param_generation(),)
         if key == self._key:
             return self._struct
         for t in ts:

@@ -59,7 +59,10 @@ class EvalPipeline:
     def run(self, images, labels, canny, gt):
         """Device inputs: images [B,H,W,3] f32 (or uint8 = byte/255), labels [B,H,W] i32 (or int16), canny [B,H,W] u8,
         gt [B,H,W] u8.
-        Returns a dict of device tensors (valid until the next call)."""
+        Returns a dict of device tensors (valid until the next call).  ``out["status"]`` is the graph build's overflow
+        word ([1] i32, non-zero = a label >= label_cap was dropped or the node / edge capacity truncated the graph, see
+        ``check_status``): the run itself never synchronises, so the caller reads it with its results --
+        ``HostPipeline`` copies it back with the logits and raises in ``synchronize()``."""
         from .region_graph import WORKSPACE
         prev_lane, WORKSPACE.lane = WORKSPACE.lane, self.lane
         try:
@@ -112,7 +115,7 @@ class EvalPipeline:
         self._bufs["fusion"] = f
         if side is not main:
             main.wait_stream(side)
-        return {"graph": g, "node_emb": r["node_emb"], "node_mask_out": r["mask_out"], "mask_prob": r["mask_prob"],
+        return {"graph": g, "status": g.status, "node_emb": r["node_emb"], "node_mask_out": r["mask_out"], "mask_prob": r["mask_prob"],
                 "mask_out": f["mask_out"], "instance_out": f["instance_out"], "edge_out": f["edge_out"],
                 "score_out": f["score_out"], "fused": f["fused"], "counts": b["counts"], "abs_err": b["abs_err"],
                 "per_image": b["per_image"], "partial": b["partial"], "pred_mask": b["pred_mask"]}
@@ -134,6 +137,16 @@ class EvalPipeline:
         with torch.cuda.graph(graph):
             out = self.run(images, labels, canny, gt)
         return graph, out
+
+
+def check_status(status: int, what: str = "region-graph build") -> None:
+    """Raise when the overflow word of a graph build is non-zero: the logits / metrics of that batch are not valid."""
+    status = int(status)
+    if status:
+        names = ", ".join(n for b, n in ((_lib.STATUS_LABEL_OVERFLOW, "label >= label_cap (region dropped)"),
+                                         (_lib.STATUS_NODE_OVERFLOW, "nodes > node_cap"), (_lib.STATUS_EDGE_OVERFLOW, "edges > edge_cap"))
+                          if status & b)
+        raise _lib.CmError(f"{what} overflow (status {status}): {names}")
 
 
 class BatchBuffer:
@@ -183,8 +196,9 @@ class HostStager:
                                                                  self.d_batch.gt)
         self.h_mask_out = torch.empty((B, 2), dtype=torch.float32, **pin)
         self.h_per_image = torch.empty((B, 7), dtype=torch.float64, **pin)
+        self.h_status = torch.zeros(1, dtype=torch.int32, **pin)
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in (self.h_images, self.h_labels, self.h_canny, self.h_gt))
-        self.d2h_bytes = sum(t.numel() * t.element_size() for t in (self.h_mask_out, self.h_per_image))
+        self.d2h_bytes = sum(t.numel() * t.element_size() for t in (self.h_mask_out, self.h_per_image, self.h_status))
 
     def fill(self, batch):
         self.h_images.copy_(batch.images)
@@ -198,7 +212,12 @@ class HostStager:
         out = pipe.run(self.d_images, self.d_labels, self.d_canny, self.d_gt)
         self.h_mask_out.copy_(out["mask_out"], non_blocking=True)
         self.h_per_image.copy_(out["per_image"], non_blocking=True)
+        self.h_status.copy_(out["status"], non_blocking=True)
         return out
+
+    def check(self):
+        """After the step's stream work has completed: raise if the graph build overflowed."""
+        check_status(self.h_status.item())
 
 
 class HostPipeline:
@@ -256,13 +275,17 @@ class HostPipeline:
                 out = pipe.run(st.d_images, st.d_labels, st.d_canny, st.d_gt)
             st.h_mask_out.copy_(out["mask_out"], non_blocking=True)
             st.h_per_image.copy_(out["per_image"], non_blocking=True)
+            st.h_status.copy_(out["status"], non_blocking=True)
             self.pipe_done[st.pipe_idx].record(st.stream)
             st.ev_done.record(st.stream)
         return st
 
     def synchronize(self):
+        """Wait for every slot, then raise if any batch's graph build overflowed (its logits / metrics are invalid)."""
         for st in self.slots:
             st.ev_done.synchronize()
+        for st in self.slots:
+            st.check()
 
 
 def bind_host_to_gpu(device_index: int) -> list[int]:

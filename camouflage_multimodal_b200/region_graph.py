@@ -215,6 +215,51 @@ def create_region_graph(image, n_segments=500, segments=None, edges=None, device
     return d, segments
 
 
+# ---------------------------------------------------------------------------- the reference's single-image front end
+IMAGENET_MEAN = (0.485, 0.456, 0.406)
+IMAGENET_STD = (0.229, 0.224, 0.225)
+
+
+def denormalised_image(image_u8):
+    """The float image ``extract_embeddings_from_image`` hands to ``create_region_graph``
+    (extract_rg_embeddings.py:263-276) from the decoded ``[H,W,3]`` uint8 array: torchvision ``ToTensor`` (float32
+    ``/255``) + ``Normalize`` (float32 ``sub(mean).div(std)``), then ``* std + mean`` in float64 and ``clip(0, 1)``.
+    The round trip is not the identity: ``(image * 255).astype(uint8)`` (:143) lands one below the decoder's byte
+    wherever the float64 result falls just short of it, so SLIC sees those bytes -- reproduced here operation for
+    operation (host code: eleven flops per pixel on a 256 x 256 image)."""
+    u8 = np.array(image_u8, dtype=np.uint8, order="C")      # a writable copy
+    t = torch.from_numpy(u8).permute(2, 0, 1).contiguous().to(torch.float32).div(255)
+    mean = torch.tensor(IMAGENET_MEAN, dtype=torch.float32).view(3, 1, 1)
+    std = torch.tensor(IMAGENET_STD, dtype=torch.float32).view(3, 1, 1)
+    a = t.sub(mean).div(std).numpy().transpose(1, 2, 0)
+    return np.clip(a * np.array(IMAGENET_STD) + np.array(IMAGENET_MEAN), 0, 1)
+
+
+def load_image_256(image_path):
+    """``Image.open(path).convert('RGB').resize((256, 256))`` (:260-261) -> ``[256,256,3]`` uint8.  Decode and resample
+    stay on the host (PIL), as in the reference."""
+    from PIL import Image
+    return np.asarray(Image.open(image_path).convert("RGB").resize((256, 256)), dtype=np.uint8)
+
+
+def extract_embeddings_from_image(model, image_path, device, n_segments=500):
+    """Drop-in for ``extract_embeddings_from_image(model, image_path, device, n_segments=500)``
+    (extract_rg_embeddings.py:249-288): -> ``(node_embeddings [N,128] cpu, graph_embedding [1,128] cpu, graph_data cpu,
+    segments [256,256] numpy)``.  The reference's ``predict_single_image`` (models/multimodal/test_multimodal.py:83-106)
+    runs on top of it unchanged.  SLIC, Canny, the graph build and the GNN run on ``device`` (which must be a CUDA
+    device: there is no CPU path); the GNN runs once for both embeddings (the reference runs it twice, :285-286)."""
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise _lib.CmError("extract_embeddings_from_image: the B200 path needs a CUDA device, got %r" % (device,))
+    img_np = denormalised_image(load_image_256(image_path))
+    graph_data, segments = create_region_graph(img_np, n_segments=n_segments, device=dev)
+    graph_data = graph_data.to(dev)
+    model.eval()                                                 # :283 (left in eval mode, as the reference does)
+    with torch.no_grad():
+        r = model._run_data(graph_data, ("node_emb", "graph_emb"))
+    return r["node_emb"].cpu(), r["graph_emb"].cpu(), graph_data.cpu(), segments
+
+
 def batch_to_data(g: RegionGraphBatch) -> Batch:
     """Exact-size PyG-style ``Batch`` view of a batched build (one device->host read for the sizes)."""
     n, e = g.counts()
@@ -322,7 +367,7 @@ class RegionGraphGNN(nn.Module):
     def _prepared(self, device):
         """(params struct, folded blob); refolded whenever a parameter or buffer changed."""
         tensors = list(self.parameters()) + [b for b in self.buffers()]
-        key = tuple((t.data_ptr(), t._version) for t in tensors) + (str(device),)
+        key = tuple((t.data_ptr(), t._version) for t in tensors) + (str(device), _lib.param_generation())
         if self._folded_key != key:
             lib = _lib.load()
             for t in tensors:

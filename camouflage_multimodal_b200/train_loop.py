@@ -18,8 +18,9 @@ import torch
 from . import _lib
 
 
-def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+def _stream(t=None):
+    """Current stream of the device ``t`` lives on (the library call is then made with that device current)."""
+    return _lib.stream_ptr(t.device if t is not None else None)
 
 
 def region_targets(graph, labels, mask, instance_mask, edge_mask):
@@ -36,7 +37,7 @@ def region_targets(graph, labels, mask, instance_mask, edge_mask):
     lib = _lib.load()
     _lib.check(lib.cm_region_targets(_lib.ptr(labels.contiguous()), _lib.ptr(mask.contiguous()), _lib.ptr(instance_mask.contiguous()),
                                      _lib.ptr(edge_mask.contiguous()), b, h, w, _lib.ptr(graph.node_ptr), _lib.ptr(graph.node_label),
-                                     _lib.ptr(graph.node_bbox), graph.node_cap, _lib.ptr(y), _lib.ptr(iy), _lib.ptr(ey), _stream()),
+                                     _lib.ptr(graph.node_bbox), graph.node_cap, _lib.ptr(y), _lib.ptr(iy), _lib.ptr(ey), _stream(y)),
                "cm_region_targets")
     return y, iy, ey
 
@@ -51,7 +52,7 @@ class _RgLossFn(torch.autograd.Function):
         dm, di, de = torch.empty_like(mask), torch.empty_like(inst), torch.empty_like(edge)
         _lib.check(_lib.load().cm_rg_node_loss(_lib.ptr(mask), _lib.ptr(inst), _lib.ptr(edge), _lib.ptr(y), _lib.ptr(iy), _lib.ptr(ey),
                                                _lib.ptr(n_dev) if n_dev is not None else None, cap, C.byref(cfg), _lib.ptr(ws), 40,
-                                               _lib.ptr(out), _lib.ptr(dm), _lib.ptr(di), _lib.ptr(de), _stream()), "cm_rg_node_loss")
+                                               _lib.ptr(out), _lib.ptr(dm), _lib.ptr(di), _lib.ptr(de), _stream(mask)), "cm_rg_node_loss")
         ctx.save_for_backward(dm, di, de)
         ctx.edge_shape = None
         ctx.terms = out
@@ -91,7 +92,7 @@ class _ImageLossFn(torch.autograd.Function):
         dm, di, de, ds = torch.empty_like(mask), torch.empty_like(inst), torch.empty_like(edge), torch.empty_like(score)
         _lib.check(_lib.load().cm_image_loss(_lib.ptr(mask), _lib.ptr(inst), _lib.ptr(edge), _lib.ptr(score), _lib.ptr(mask_label),
                                              _lib.ptr(edge_label), _lib.ptr(score_label), g, C.byref(cfg), _lib.ptr(out),
-                                             _lib.ptr(dm), _lib.ptr(di), _lib.ptr(de), _lib.ptr(ds), _stream()), "cm_image_loss")
+                                             _lib.ptr(dm), _lib.ptr(di), _lib.ptr(de), _lib.ptr(ds), _stream(mask)), "cm_image_loss")
         ctx.save_for_backward(dm, di, de, ds)
         return out[0]
 
@@ -197,4 +198,7 @@ class FusedAdamW:
                                self.max_norm if self.max_norm is not None else 0.0)
         _lib.check(_lib.load().cm_adamw_step(_lib.ptr(self._p), _lib.ptr(self._g), _lib.ptr(self._m), _lib.ptr(self._v),
                                              _lib.ptr(self._numel), len(self.params), self._max_numel, C.byref(cfg), self.step_count,
-                                             _lib.ptr(self._norm_ws), _lib.ptr(self._norm_out), _stream()), "cm_adamw_step")
+                                             _lib.ptr(self._norm_ws), _lib.ptr(self._norm_out), _stream(self.flat_grad)), "cm_adamw_step")
+        # the kernel wrote every parameter through its raw pointer: torch's version counters did not move, so tell the
+        # caches of folded / converted weights (fusion_model._FusionRunner, RegionGraphGNN._prepared) explicitly
+        _lib.bump_param_generation(self.params)

@@ -194,3 +194,47 @@ def test_lanes_and_decoded_inputs_equal_float_path(models):
         assert (got[j][0] - out["mask_out"].cpu()).abs().max() <= 1e-3
         pi = out["per_image"].cpu()
         assert (got[j][1] - pi).abs().max() <= 1e-6
+
+
+def test_host_pipeline_raises_on_graph_overflow(models):
+    """a label >= label_cap is dropped by the build; the status word now comes back with the results and
+    HostPipeline.synchronize() raises instead of returning metrics of a truncated graph."""
+    from camouflage_multimodal_b200 import _lib
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, HostPipeline
+    gnn, det, kg, _, _ = models
+    B = 2
+    dev = torch.device("cuda")
+    b = synth.make_batch(3, B, seed=77, n_regions=[200, 210])
+    ok = EvalPipeline(gnn, det, kg, label_cap=256)
+    hp = HostPipeline(ok, B, 256, 256, dev, slots=1, use_graph=True)
+    st = hp.submit(0, *(t.pin_memory() for t in (b.images, b.labels, b.canny, b.gt)))
+    hp.synchronize()                                                  # fits: no exception
+    assert int(st.h_status.item()) == 0
+    small = EvalPipeline(gnn, det, kg, label_cap=128)                 # labels 128..210 do not fit
+    hp2 = HostPipeline(small, B, 256, 256, dev, slots=1, use_graph=True)
+    hp2.submit(0, *(t.pin_memory() for t in (b.images, b.labels, b.canny, b.gt)))
+    with pytest.raises(_lib.CmError, match="label >= label_cap"):
+        hp2.synchronize()
+    d = b.to("cuda")
+    out = small.run(d.images, d.labels, d.canny, d.gt)
+    assert int(out["status"].item()) & _lib.STATUS_LABEL_OVERFLOW
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_second_device_with_current_device_left_at_zero(models):
+    """per-device kernel attributes + a device guard around every library call -- a pipeline on cuda:1 while
+    the current device stays 0 gives what cuda:0 gives."""
+    import copy
+    from camouflage_multimodal_b200.pipeline import EvalPipeline
+    gnn, det, kg, _, _ = models
+    b = synth.make_batch(11, 2, seed=5)
+    d0 = b.to("cuda:0")
+    out0 = EvalPipeline(gnn, det, kg, label_cap=544, lane=11).run(d0.images, d0.labels, d0.canny, d0.gt)
+    ref = out0["mask_out"].cpu(), out0["per_image"].cpu()
+    torch.cuda.set_device(0)
+    gnn1, det1 = copy.deepcopy(gnn).to("cuda:1"), copy.deepcopy(det).to("cuda:1")
+    d1 = b.to("cuda:1")
+    out1 = EvalPipeline(gnn1, det1, kg.to("cuda:1"), label_cap=544, lane=12).run(d1.images, d1.labels, d1.canny, d1.gt)
+    assert torch.cuda.current_device() == 0
+    torch.cuda.synchronize(1)
+    assert torch.equal(out1["mask_out"].cpu(), ref[0]) and torch.equal(out1["per_image"].cpu(), ref[1])

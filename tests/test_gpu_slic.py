@@ -1,5 +1,6 @@
-"""device SLIC against the CPU restatement (oracle/slic.py; parity with scikit-image itself is
-unpinned -- it is not installable here).  The connectivity stage is an integer algorithm: bit-exact.  The clustering is
+"""device SLIC against the CPU restatement (oracle/slic.py) and against the REFERENCE's recorded region
+counts (tests/golden/slic_images_u8.npz: inputs + embedding_summary.json num_nodes; the oracle reproduces 240 / 240 of
+them, tests/test_oracle_slic.py).  The connectivity stage is an integer algorithm: bit-exact.  The clustering is
 float64 with the oracle's summation order; pow / cbrt differ between CUDA and numpy in the last bit, so a handful of
 near-tie pixels may flip: >= 99.5 % of the pixels must agree and the region count must agree within 1 %."""
 import ctypes as C
@@ -69,6 +70,37 @@ def test_slic_matches_oracle_and_invariants():
         assert abs(n_dev - n_ref) <= max(1, int(0.01 * n_ref))
         assert 300 <= n_dev <= 529          # the reference's embedding_summary.json range for n_segments=500
         assert lab[i].min() >= 0 and lab[i].max() <= 529
+
+
+def test_cm_slic_reproduces_the_references_recorded_region_counts(golden_dir):
+    """cm_slic on the reference's own COD10K inputs: region count == what the reference's scikit-image run recorded
+    (embedding_summary.json) on >= 90 % of the 64 images, the rest within 1 (pow / cbrt last-bit near-ties), and the
+    label maps equal the oracle's on >= 99.5 % of the pixels."""
+    import os
+    from camouflage_multimodal_b200.region_graph import slic_segments
+    from oracle import slic as oslic
+    z = np.load(os.path.join(golden_dir, "slic_images_u8.npz"))
+    images, expected = z["images"], z["expected"]
+    lab = slic_segments(torch.as_tensor(images).cuda(), n_segments=500, compactness=10.0, sigma=1.0).cpu().numpy()
+    got = np.array([len(np.unique(l)) for l in lab])
+    err = got - expected
+    assert np.abs(err).max() <= 1, err.tolist()
+    assert (err == 0).mean() >= 0.9, err.tolist()
+    assert lab.min() >= 1                                           # no stray label 0 (oracle/slic.py enforce_connectivity)
+    for i in range(0, len(images), 8):
+        assert float((lab[i] == oslic.slic(images[i])).mean()) >= 0.995
+
+
+def test_low_contrast_image_is_rescaled():
+    """skimage >= 0.19's min-max rescale: an image squeezed into [50, 101] segments exactly like its stretched copy."""
+    from camouflage_multimodal_b200.region_graph import slic_segments
+    rng = np.random.default_rng(5)
+    base = np.repeat(np.repeat(rng.integers(0, 52, size=(1, 32, 32, 3)), 8, axis=1), 8, axis=2)
+    base[0, 0, 0, 0], base[0, 0, 0, 1] = 0, 51
+    lo, hi = (base + 50).astype(np.uint8), (base * 5).astype(np.uint8)
+    a = slic_segments(torch.as_tensor(lo).cuda()).cpu().numpy()
+    b = slic_segments(torch.as_tensor(hi).cuda()).cpu().numpy()
+    assert float((a == b).mean()) >= 0.995
 
 
 def test_create_region_graph_runs_from_the_image_alone():

@@ -116,3 +116,54 @@ def test_fused_adamw_matches_torch_clip_and_adamw(max_norm):
                 np.testing.assert_allclose(p.grad.cpu().numpy(), q.grad.numpy(), rtol=3e-6, atol=1e-9)
         for p, q in zip(dev_p, ref_p):
             np.testing.assert_allclose(p.detach().cpu().numpy(), q.detach().numpy(), rtol=2e-6, atol=2e-7)
+
+
+def test_eval_after_fused_adamw_uses_the_updated_weights():
+    """cm_adamw_step writes parameters through raw pointers, so Tensor._version never moves; the
+    caches of folded / converted weights (detector: cm_fusion_fold blob, GNN: cm_gnn_fold blob) must still refresh.
+    Train-mode steps with FusedAdamW, then eval() output against the oracle on the UPDATED state dict."""
+    from camouflage_multimodal_b200 import synth
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
+    from camouflage_multimodal_b200.region_graph import RegionGraphGNN
+    from camouflage_multimodal_b200.train_loop import FusedAdamW
+    from oracle import fusion as ofus
+    from oracle import gnn as ognn
+    torch.manual_seed(5)
+    det = build_multimodal_model({}).cuda()
+    kg = synth.synthetic_kg(13).cuda()
+    gen = torch.Generator().manual_seed(3)
+    rg = torch.relu(torch.randn((2, 150, 128), generator=gen)).cuda()
+    det.eval()
+    with torch.no_grad():
+        before = det(rg, kg[None].expand(2, -1, -1))[0].clone()          # builds the folded-weight cache
+    opt = FusedAdamW(det.parameters(), lr=5e-2, weight_decay=1e-4, max_norm=1.0)
+    for _ in range(3):
+        opt.zero_grad()
+        for p, g in zip(opt.params, opt.grads):
+            g.copy_(torch.randn(p.shape, generator=gen).cuda())
+        opt.step()
+    with torch.no_grad():
+        after = det(rg, kg[None].expand(2, -1, -1))[0]
+    fsd = {k: v.detach().cpu() for k, v in det.state_dict().items()}
+    with torch.no_grad():
+        ref = ofus.detector_forward(fsd, rg.cpu(), kg.cpu()[None].expand(2, -1, -1))[0]
+    assert float((after - before).abs().max()) > 1e-2                     # the step really moved the output
+    np.testing.assert_allclose(after.cpu().numpy(), ref.numpy(), rtol=0, atol=1e-2)
+    # the same for the GNN's folded weights (no BatchNorm buffer is touched between the two eval passes)
+    gnn = RegionGraphGNN(15, 128, 2).cuda().eval()
+    hb = synth.make_batch(0, 1, seed=9, n_regions=[120])
+    from camouflage_multimodal_b200.region_graph import create_region_graph
+    data, _ = create_region_graph(hb.images[0].numpy().astype(np.float64), segments=hb.labels[0].numpy(), edges=hb.canny[0].numpy())
+    with torch.no_grad():
+        g_before = gnn(data)[0].clone()
+    gopt = FusedAdamW(gnn.parameters(), lr=5e-2, weight_decay=0.0, max_norm=None)
+    for p, g in zip(gopt.params, gopt.grads):
+        g.copy_(torch.randn(p.shape, generator=gen).cuda())
+    gopt.step()
+    with torch.no_grad():
+        g_after = gnn(data)[0]
+    gsd = {k: v.detach().cpu() for k, v in gnn.state_dict().items()}
+    with torch.no_grad():
+        r = ognn.rg_gnn_forward(gsd, data.x.cpu(), data.edge_index.cpu(), data.edge_attr.cpu())
+    assert float((g_after - g_before).abs().max()) > 1e-3
+    np.testing.assert_allclose(g_after.cpu().numpy(), r["mask_out"].numpy(), rtol=0, atol=2e-3)
