@@ -1,0 +1,533 @@
+// A9': S-measure, E-measure, F-measure (beta^2 = 0.3) and weighted F-measure as device reductions.
+//
+// NOT IN THE REFERENCE (utils/metrics.py:9-92 stops at IoU / Dice / P / R / F1 / MAE / accuracy); BASELINE.json's
+// north_star names them, so the published definitions are restated in oracle/sod_metrics.py (parity unpinned) and
+// computed here on the same conventions: pred [B,H,W] float32 in [0,1] used as it is, GT foreground = byte >= 128
+// (gt / 255 > 0.5, utils/metrics.py:12), 8-bit quantisation q = floor(pred * 255) for the threshold curves.
+//
+//   sod_pass1   one pass: GT count / centroid sums, object-term moments of S, mean(pred), the two 256-bin histograms
+//   sod_pass2   needs the centroid + adaptive threshold from pass 1: SSIM moments of the four quadrants (shifted by each
+//               quadrant's corner pixel so a constant quadrant gives exactly 0 variance), adaptive-threshold counts
+//   sod_edt_cols / sod_edt_rows   exact Euclidean feature transform of the GT (nearest foreground pixel, ties to the
+//               lexicographically smallest (y, x)) for the weighted F-measure
+//   sod_wf      pixel dependency (7x7 Gaussian, sigma 5, zero border) + pixel importance -> weighted error sums
+//   sod_finalize / sod_partial   closed forms per image, curves, batch partial sums
+// Every float64 sum is a per-thread running sum -> warp shuffle tree -> fixed-order block / chunk combination: the
+// result does not depend on scheduling (no floating-point atomics).  Bound: HBM/L2 on pred (4 B) + gt (1 B) per pixel,
+// read three times (the second and third from L2 at batch 32: 10 MB).
+#include <math.h>
+
+#include "common.cuh"
+
+namespace cm {
+
+constexpr int SOD_CHUNKS = 16;   // blocks per image in the two pixel passes
+constexpr int SOD_P1 = 8;        // doubles per chunk, pass 1
+constexpr int SOD_P2 = 18;       // doubles per chunk, pass 2
+constexpr int SOD_KEYS = 8;
+constexpr int SOD_PARTIAL = 2 * SOD_KEYS + 512;
+constexpr double SOD_EPS = 2.220446049250313e-16;
+
+struct SodWs {
+    double *p1, *p2, *p4, *curves, *shift;
+    int* hist;
+    short *col_d, *col_y;
+    int *d2, *near;
+    size_t total;
+    int wf_tiles;
+};
+static SodWs carve_sod(void* ws, int batch, int h, int w) {
+    Carver c(ws);
+    SodWs r;
+    const size_t n = (size_t)batch * h * w;
+    r.wf_tiles = ceil_div(w, 32) * ceil_div(h, 8);
+    r.p1 = c.take<double>((size_t)batch * SOD_CHUNKS * SOD_P1);
+    r.p2 = c.take<double>((size_t)batch * SOD_CHUNKS * SOD_P2);
+    r.p4 = c.take<double>((size_t)batch * r.wf_tiles * 2);
+    r.curves = c.take<double>((size_t)batch * 512);
+    r.shift = c.take<double>((size_t)batch * 4);
+    r.hist = c.take<int>((size_t)batch * 512);
+    r.col_d = c.take<short>(n);
+    r.col_y = c.take<short>(n);
+    r.d2 = c.take<int>(n);
+    r.near = c.take<int>(n);
+    r.total = align_up(c.off, 256);
+    return r;
+}
+
+// block-wide sum of NV doubles per thread, result valid in thread 0 (fixed order: lanes by shuffle tree, warps 0..7 serially)
+template <int NV>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* s_red /* [8 * NV] */) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const double t = warp_sum(v[k]);
+        if (lane == 0) s_red[wid * NV + k] = t;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            double t = 0.0;
+            for (int wi = 0; wi < (int)(blockDim.x >> 5); ++wi) t += s_red[wi * NV + k];
+            v[k] = t;
+        }
+    }
+}
+
+// grid (SOD_CHUNKS, B), block 256
+__global__ void __launch_bounds__(256) sod_pass1_kernel(const float* __restrict__ pred, const uint8_t* __restrict__ gt, int H, int W,
+                                                        double* __restrict__ p1, int* __restrict__ hist) {
+    __shared__ int s_hist[512];
+    __shared__ double s_red[8 * SOD_P1];
+    const int b = blockIdx.y, HW = H * W;
+    const float* pr = pred + (size_t)b * HW;
+    const uint8_t* g = gt + (size_t)b * HW;
+    for (int i = threadIdx.x; i < 512; i += 256) s_hist[i] = 0;
+    __syncthreads();
+    // v: n_fg, sum y_fg, sum x_fg, sum p (fg), sum p^2 (fg), sum (1-p) (bg), sum (1-p)^2 (bg), sum p
+    double v[SOD_P1] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int n_fg = 0;
+    long long sy = 0, sx = 0;
+    const int per = (HW + SOD_CHUNKS - 1) / SOD_CHUNKS, i0 = blockIdx.x * per, i1 = min(i0 + per, HW);
+    for (int i = i0 + threadIdx.x; i < i1; i += 256) {
+        const double p = (double)pr[i];
+        const bool fg = g[i] >= 128;
+        int q = (int)(p * 255.0);
+        q = min(max(q, 0), 255);
+        atomicAdd(&s_hist[(fg ? 0 : 256) + q], 1);
+        v[7] += p;
+        if (fg) {
+            const int y = i / W;
+            ++n_fg;
+            sy += y;
+            sx += i - y * W;
+            v[3] += p;
+            v[4] += p * p;
+        } else {
+            const double o = 1.0 - p;
+            v[5] += o;
+            v[6] += o * o;
+        }
+    }
+    v[0] = (double)n_fg;
+    v[1] = (double)sy;
+    v[2] = (double)sx;
+    block_sum<SOD_P1>(v, s_red);
+    if (threadIdx.x == 0) {
+        double* o = p1 + ((size_t)b * SOD_CHUNKS + blockIdx.x) * SOD_P1;
+#pragma unroll
+        for (int k = 0; k < SOD_P1; ++k) o[k] = v[k];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 512; i += 256)
+        if (s_hist[i]) atomicAdd(&hist[(size_t)b * 512 + i], s_hist[i]);
+}
+
+// image totals of pass 1 (fixed chunk order)
+__device__ __forceinline__ void sod_totals(const double* __restrict__ p1, int b, double (&t)[SOD_P1]) {
+#pragma unroll
+    for (int k = 0; k < SOD_P1; ++k) t[k] = 0.0;
+    for (int c = 0; c < SOD_CHUNKS; ++c)
+#pragma unroll
+        for (int k = 0; k < SOD_P1; ++k) t[k] += p1[((size_t)b * SOD_CHUNKS + c) * SOD_P1 + k];
+}
+// GT centroid the way the published code rounds it: round-half-even of the mean, + 1; image centre when the GT is empty
+__device__ __forceinline__ void sod_centroid(const double (&t)[SOD_P1], int H, int W, int* cx, int* cy) {
+    if (t[0] == 0.0) {
+        *cx = (int)rint((double)W / 2.0) + 1;
+        *cy = (int)rint((double)H / 2.0) + 1;
+    } else {
+        *cy = (int)rint(t[1] / t[0]) + 1;
+        *cx = (int)rint(t[2] / t[0]) + 1;
+    }
+}
+
+// grid (SOD_CHUNKS, B), block 256.  Per quadrant k (LT, RT, LB, RB): sum p', sum p'^2, sum p' g (p' = p - corner pixel),
+// sum g; then adaptive-threshold tp, fp.
+__global__ void __launch_bounds__(256) sod_pass2_kernel(const float* __restrict__ pred, const uint8_t* __restrict__ gt, int H, int W,
+                                                        const double* __restrict__ p1, double* __restrict__ p2, double* __restrict__ shift) {
+    __shared__ double s_red[8 * SOD_P2];
+    __shared__ double s_shift[4];
+    __shared__ int s_c[2];
+    __shared__ double s_thr;
+    const int b = blockIdx.y, HW = H * W;
+    const float* pr = pred + (size_t)b * HW;
+    const uint8_t* g = gt + (size_t)b * HW;
+    if (threadIdx.x == 0) {
+        double t[SOD_P1];
+        sod_totals(p1, b, t);
+        int cx, cy;
+        sod_centroid(t, H, W, &cx, &cy);
+        s_c[0] = cx;
+        s_c[1] = cy;
+        s_thr = fmin(2.0 * (t[7] / (double)HW), 1.0);
+        s_shift[0] = (double)pr[0];
+        s_shift[1] = cx < W ? (double)pr[cx] : 0.0;
+        s_shift[2] = cy < H ? (double)pr[(size_t)cy * W] : 0.0;
+        s_shift[3] = (cx < W && cy < H) ? (double)pr[(size_t)cy * W + cx] : 0.0;
+        if (blockIdx.x == 0)
+            for (int k = 0; k < 4; ++k) shift[(size_t)b * 4 + k] = s_shift[k];
+    }
+    __syncthreads();
+    const int cx = s_c[0], cy = s_c[1];
+    const double thr = s_thr;
+    double v[SOD_P2];
+#pragma unroll
+    for (int k = 0; k < SOD_P2; ++k) v[k] = 0.0;
+    int gq[4] = {0, 0, 0, 0}, tpa = 0, fpa = 0;
+    const int per = (HW + SOD_CHUNKS - 1) / SOD_CHUNKS, i0 = blockIdx.x * per, i1 = min(i0 + per, HW);
+    for (int i = i0 + threadIdx.x; i < i1; i += 256) {
+        const double p = (double)pr[i];
+        const bool fg = g[i] >= 128;
+        const int y = i / W, x = i - y * W;
+        const int k = (y >= cy ? 2 : 0) + (x >= cx ? 1 : 0);
+        const double d = p - s_shift[k];
+        // branch-free scatter into the quadrant's slots
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double m = (j == k) ? 1.0 : 0.0;
+            v[3 * j] += m * d;
+            v[3 * j + 1] += m * d * d;
+            v[3 * j + 2] += (fg && j == k) ? d : 0.0;
+            gq[j] += (fg && j == k);
+        }
+        if (p >= thr) {
+            tpa += fg;
+            fpa += !fg;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[12 + j] = (double)gq[j];
+    v[16] = (double)tpa;
+    v[17] = (double)fpa;
+    block_sum<SOD_P2>(v, s_red);
+    if (threadIdx.x == 0) {
+        double* o = p2 + ((size_t)b * SOD_CHUNKS + blockIdx.x) * SOD_P2;
+#pragma unroll
+        for (int k = 0; k < SOD_P2; ++k) o[k] = v[k];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- weighted F: feature transform
+constexpr short SOD_NONE = 0x7fff;
+// one thread per (image, column): nearest foreground row in the column (distance, row), the upper one on ties
+__global__ void sod_edt_cols_kernel(const uint8_t* __restrict__ gt, int batch, int H, int W, short* __restrict__ col_d, short* __restrict__ col_y) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= batch * W) return;
+    const int b = i / W, x = i - b * W;
+    const uint8_t* g = gt + (size_t)b * H * W + x;
+    short* cd = col_d + (size_t)b * H * W + x;
+    short* cyy = col_y + (size_t)b * H * W + x;
+    int last = -1;
+    for (int y = 0; y < H; ++y) {   // nearest at or above
+        if (g[(size_t)y * W] >= 128) last = y;
+        cd[(size_t)y * W] = last >= 0 ? (short)(y - last) : SOD_NONE;
+        cyy[(size_t)y * W] = (short)max(last, 0);
+    }
+    last = -1;
+    for (int y = H - 1; y >= 0; --y) {   // nearest below wins only when strictly closer
+        if (g[(size_t)y * W] >= 128) last = y;
+        if (last >= 0 && (last - y) < (int)cd[(size_t)y * W]) {
+            cd[(size_t)y * W] = (short)(last - y);
+            cyy[(size_t)y * W] = (short)last;
+        }
+    }
+}
+// one block per (row, image): each thread owns pixels x, searches columns outward from x while they can still win
+__global__ void __launch_bounds__(256) sod_edt_rows_kernel(const short* __restrict__ col_d, const short* __restrict__ col_y, int H, int W,
+                                                           int* __restrict__ d2_out, int* __restrict__ near_out) {
+    extern __shared__ short s_row[];   // [W] distances, [W] rows
+    short* s_d = s_row;
+    short* s_y = s_row + W;
+    const int y = blockIdx.x, b = blockIdx.y;
+    const size_t base = ((size_t)b * H + y) * W;
+    for (int x = threadIdx.x; x < W; x += blockDim.x) {
+        s_d[x] = col_d[base + x];
+        s_y[x] = col_y[base + x];
+    }
+    __syncthreads();
+    for (int x = threadIdx.x; x < W; x += blockDim.x) {
+        long long best = (long long)1 << 40;
+        int key = 0x7fffffff;
+        auto consider = [&](int xx) {
+            const int cd = s_d[xx];
+            if (cd == SOD_NONE) return;
+            const long long d = (long long)(x - xx) * (x - xx) + (long long)cd * cd;
+            const int k = (int)s_y[xx] * W + xx;
+            if (d < best || (d == best && k < key)) {
+                best = d;
+                key = k;
+            }
+        };
+        consider(x);
+        for (int k = 1; k < W && (long long)k * k <= best; ++k) {
+            if (x - k >= 0) consider(x - k);
+            if (x + k < W) consider(x + k);
+        }
+        d2_out[base + x] = best >= ((long long)1 << 40) ? -1 : (int)best;
+        near_out[base + x] = key == 0x7fffffff ? 0 : key;
+    }
+}
+
+struct Gauss7 {
+    double k[49];
+};
+// block = 32 x 8 pixel tile; Et with a 3-pixel halo in shared memory (zero outside the image)
+__global__ void __launch_bounds__(256) sod_wf_kernel(const float* __restrict__ pred, const uint8_t* __restrict__ gt, const int* __restrict__ d2,
+                                                     const int* __restrict__ near, int H, int W, const Gauss7 gk, double* __restrict__ p4) {
+    __shared__ double s_et[14][38];
+    __shared__ double s_red[8 * 2];
+    const int b = blockIdx.z, tx0 = blockIdx.x * 32, ty0 = blockIdx.y * 8;
+    const size_t off = (size_t)b * H * W;
+    for (int i = threadIdx.x; i < 14 * 38; i += 256) {
+        const int ly = i / 38, lx = i - ly * 38, y = ty0 + ly - 3, x = tx0 + lx - 3;
+        double et = 0.0;
+        if (y >= 0 && y < H && x >= 0 && x < W) {
+            const size_t p = off + (size_t)y * W + x;
+            if (gt[p] >= 128) {
+                et = fabs((double)pred[p] - 1.0);
+            } else {
+                et = fabs((double)pred[off + near[p]] - 1.0);   // the error of the nearest foreground pixel
+            }
+        }
+        s_et[ly][lx] = et;
+    }
+    __syncthreads();
+    const int lx = threadIdx.x & 31, ly = threadIdx.x >> 5, x = tx0 + lx, y = ty0 + ly;
+    double v[2] = {0.0, 0.0};   // sum Ew over GT, sum Ew over background
+    if (x < W && y < H) {
+        const size_t p = off + (size_t)y * W + x;
+        const bool fg = gt[p] >= 128;
+        const double e = fabs((double)pred[p] - (fg ? 1.0 : 0.0));
+        double ea = 0.0;
+#pragma unroll
+        for (int dy = 0; dy < 7; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 7; ++dx) ea += gk.k[dy * 7 + dx] * s_et[ly + dy][lx + dx];
+        if (fg) {
+            v[0] = ea < e ? ea : e;
+        } else {
+            const double dst = sqrt((double)d2[p]);
+            v[1] = e * (2.0 - exp(log(0.5) / 5.0 * dst));
+        }
+    }
+    block_sum<2>(v, s_red);
+    if (threadIdx.x == 0) {
+        double* o = p4 + ((size_t)b * gridDim.x * gridDim.y + (size_t)blockIdx.y * gridDim.x + blockIdx.x) * 2;
+        o[0] = v[0];
+        o[1] = v[1];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- closed forms
+__device__ __forceinline__ double sod_e_from_counts(double tp, double fp, double n_fg, double n) {
+    const double pf = tp + fp, pb = n - pf;
+    double s;
+    if (n_fg == 0.0) {
+        s = pb;
+    } else if (n_fg == n) {
+        s = pf;
+    } else {
+        const double fn = n_fg - tp, tn = pb - fn, mp = pf / n, mg = n_fg / n;
+        const double cnt[4] = {tp, fp, fn, tn};
+        const double a[4] = {1.0 - mp, 1.0 - mp, 0.0 - mp, 0.0 - mp}, c[4] = {1.0 - mg, 0.0 - mg, 1.0 - mg, 0.0 - mg};
+        s = 0.0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const double align = 2.0 * (a[k] * c[k]) / (a[k] * a[k] + c[k] * c[k] + SOD_EPS);
+            s = s + (align + 1.0) * (align + 1.0) / 4.0 * cnt[k];
+        }
+    }
+    return s / (n - 1.0 + SOD_EPS);
+}
+__device__ __forceinline__ double sod_f_from_counts(double tp, double fp, double n_fg, double beta2) {
+    double ps = tp + fp;
+    if (ps == 0.0) ps = 1.0;
+    const double prec = tp / ps, rec = tp / fmax(n_fg, 1.0);
+    double den = beta2 * prec + rec;
+    if (den == 0.0) den = 1.0;
+    return (1.0 + beta2) * prec * rec / den;
+}
+__device__ __forceinline__ double sod_s_object(double sum, double sum2, double n) {
+    const double x = sum / n;
+    double sigma = 0.0;
+    if (n > 1.0) sigma = sqrt(fmax((sum2 - n * x * x) / (n - 1.0), 0.0));
+    return 2.0 * x / (x * x + 1.0 + sigma + SOD_EPS);
+}
+
+// one block of 256 threads per image: thread t owns curve entry t (threshold q >= 255 - t)
+__global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restrict__ p1, const double* __restrict__ p2, const double* __restrict__ shift,
+                                                           const double* __restrict__ p4, int wf_tiles, const int* __restrict__ hist, int H, int W,
+                                                           double beta2_f, double beta2_wf, double* __restrict__ per_image,
+                                                           double* __restrict__ curves) {
+    __shared__ int s_tp[256], s_fp[256];
+    __shared__ double s_f[256], s_e[256];
+    const int b = blockIdx.x, t = threadIdx.x;
+    const double n = (double)H * (double)W;
+    s_tp[t] = hist[(size_t)b * 512 + 255 - t];
+    s_fp[t] = hist[(size_t)b * 512 + 256 + 255 - t];
+    __syncthreads();
+    for (int o = 1; o < 256; o <<= 1) {   // inclusive scan (integers: order-free)
+        const int a = t >= o ? s_tp[t - o] : 0, c = t >= o ? s_fp[t - o] : 0;
+        __syncthreads();
+        s_tp[t] += a;
+        s_fp[t] += c;
+        __syncthreads();
+    }
+    double tot[SOD_P1];
+    sod_totals(p1, b, tot);
+    const double n_fg = tot[0];
+    const double f = sod_f_from_counts((double)s_tp[t], (double)s_fp[t], n_fg, beta2_f);
+    const double e = sod_e_from_counts((double)s_tp[t], (double)s_fp[t], n_fg, n);
+    curves[(size_t)b * 512 + t] = f;
+    curves[(size_t)b * 512 + 256 + t] = e;
+    s_f[t] = f;
+    s_e[t] = e;
+    __syncthreads();
+    if (t != 0) return;
+    double fsum = 0.0, esum = 0.0, fmx = s_f[0], emx = s_e[0];
+    for (int i = 0; i < 256; ++i) {
+        fsum += s_f[i];
+        esum += s_e[i];
+        fmx = fmax(fmx, s_f[i]);
+        emx = fmax(emx, s_e[i]);
+    }
+    double q[SOD_P2];
+#pragma unroll
+    for (int k = 0; k < SOD_P2; ++k) q[k] = 0.0;
+    for (int c = 0; c < SOD_CHUNKS; ++c)
+#pragma unroll
+        for (int k = 0; k < SOD_P2; ++k) q[k] += p2[((size_t)b * SOD_CHUNKS + c) * SOD_P2 + k];
+    // ---- S-measure (alpha = 0.5)
+    double sm;
+    const double mean_p = tot[7] / n;
+    if (n_fg == 0.0) {
+        sm = 1.0 - mean_p;
+    } else if (n_fg == n) {
+        sm = mean_p;
+    } else {
+        const double yv = n_fg / n;
+        const double so = yv * sod_s_object(tot[3], tot[4], n_fg) + (1.0 - yv) * sod_s_object(tot[5], tot[6], n - n_fg);
+        int cx, cy;
+        sod_centroid(tot, H, W, &cx, &cy);
+        const double w1 = (double)cx * cy / n, w2 = (double)cy * (W - cx) / n, w3 = (double)(H - cy) * cx / n, w4 = 1.0 - w1 - w2 - w3;
+        const double wq[4] = {w1, w2, w3, w4};
+        const double nq[4] = {(double)cx * cy, (double)(W - cx) * cy, (double)cx * (H - cy), (double)(W - cx) * (H - cy)};
+        double sr = 0.0;
+        for (int k = 0; k < 4; ++k) {
+            const double nn = nq[k];
+            if (nn <= 0.0) continue;   // centroid on the last row / column: empty quadrant of weight 0
+            const double nm1 = fmax(nn - 1.0, 1.0);
+            const double md = q[3 * k] / nn, x = shift[(size_t)b * 4 + k] + md, y = q[12 + k] / nn;
+            const double sx = fmax((q[3 * k + 1] - nn * md * md) / nm1, 0.0);
+            const double sy = fmax(q[12 + k] * (1.0 - y) / nm1, 0.0);   // g is 0/1: sum (g - y)^2 = sum g - n y^2
+            const double sxy = (q[3 * k + 2] - nn * md * y) / nm1;
+            const double alpha = 4.0 * x * y * sxy, beta = (x * x + y * y) * (sx + sy);
+            double score;
+            if (alpha != 0.0) {
+                score = alpha / (beta + SOD_EPS);
+            } else {
+                score = beta == 0.0 ? 1.0 : 0.0;
+            }
+            sr += wq[k] * score;
+        }
+        sm = fmax(0.0, 0.5 * so + 0.5 * sr);
+    }
+    // ---- adaptive threshold
+    const double tpa = q[16], fpa = q[17];
+    const double fa = tpa == 0.0 ? 0.0 : sod_f_from_counts(tpa, fpa, n_fg, beta2_f);
+    const double ea = sod_e_from_counts(tpa, fpa, n_fg, n);
+    // ---- weighted F
+    double wf = 0.0;
+    if (n_fg > 0.0) {
+        double ew_fg = 0.0, ew_bg = 0.0;
+        for (int i = 0; i < wf_tiles; ++i) {
+            ew_fg += p4[((size_t)b * wf_tiles + i) * 2];
+            ew_bg += p4[((size_t)b * wf_tiles + i) * 2 + 1];
+        }
+        const double tpw = n_fg - ew_fg, fpw = ew_bg, r = 1.0 - ew_fg / n_fg, pw = tpw / (tpw + fpw + SOD_EPS);
+        wf = (1.0 + beta2_wf) * r * pw / (r + beta2_wf * pw + SOD_EPS);
+    }
+    double* o = per_image + (size_t)b * SOD_KEYS;
+    o[0] = sm;
+    o[1] = ea;
+    o[2] = esum / 256.0;
+    o[3] = emx;
+    o[4] = fa;
+    o[5] = fsum / 256.0;
+    o[6] = fmx;
+    o[7] = wf;
+}
+
+// partial [16 + 512]: sum and sum of squares of the 8 keys over the batch, then the batch sums of the F and E curves
+__global__ void sod_partial_kernel(const double* __restrict__ per_image, const double* __restrict__ curves, int batch, double* __restrict__ partial) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= SOD_PARTIAL) return;
+    double s = 0.0;
+    if (i < 2 * SOD_KEYS) {
+        const int k = i % SOD_KEYS;
+        for (int b = 0; b < batch; ++b) {
+            const double v = per_image[(size_t)b * SOD_KEYS + k];
+            s += i < SOD_KEYS ? v : v * v;
+        }
+    } else {
+        for (int b = 0; b < batch; ++b) s += curves[(size_t)b * 512 + (i - 2 * SOD_KEYS)];
+    }
+    partial[i] = s;
+}
+
+}  // namespace cm
+
+extern "C" size_t cm_sod_workspace_bytes(int batch, int h, int w) {
+    if (batch <= 0 || h <= 0 || w <= 0) return 0;
+    return cm::carve_sod(nullptr, batch, h, w).total;
+}
+
+extern "C" int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, int h, int w, void* workspace, size_t workspace_bytes,
+                              double* per_image, double* partial, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(pred && gt && workspace && per_image && partial, "cm_sod_metrics: NULL pointer");
+    CM_REQUIRE(batch > 0 && batch <= 65535 && h > 0 && w > 0 && h < 32767 && w < 32767 && (long long)h * w < (1ll << 30), "cm_sod_metrics: bad shape");
+    SodWs ws = carve_sod(workspace, batch, h, w);
+    if (workspace_bytes < ws.total) {
+        set_error("cm_sod_metrics: workspace %zu < %zu bytes", workspace_bytes, ws.total);
+        return CM_ERR_WORKSPACE;
+    }
+    cudaStream_t st = as_stream(stream);
+    Gauss7 gk;   // Matlab fspecial('gaussian', 7, 5)
+    {
+        double sum = 0.0;
+        for (int dy = -3; dy <= 3; ++dy)
+            for (int dx = -3; dx <= 3; ++dx) {
+                gk.k[(dy + 3) * 7 + dx + 3] = exp(-(double)(dy * dy + dx * dx) / (2.0 * 5.0 * 5.0));
+                sum += gk.k[(dy + 3) * 7 + dx + 3];
+            }
+        for (int i = 0; i < 49; ++i) gk.k[i] /= sum;
+    }
+    cudaMemsetAsync(ws.hist, 0, (size_t)batch * 512 * sizeof(int), st);
+    {
+        CM_TIMED("sod_pass1", st);
+        sod_pass1_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(pred, gt, h, w, ws.p1, ws.hist);
+    }
+    {
+        CM_TIMED("sod_pass2", st);
+        sod_pass2_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(pred, gt, h, w, ws.p1, ws.p2, ws.shift);
+    }
+    {
+        CM_TIMED("sod_edt", st);
+        sod_edt_cols_kernel<<<ceil_div((long long)batch * w, 128), 128, 0, st>>>(gt, batch, h, w, ws.col_d, ws.col_y);
+        sod_edt_rows_kernel<<<dim3(h, batch), 256, 2 * (size_t)w * sizeof(short), st>>>(ws.col_d, ws.col_y, h, w, ws.d2, ws.near);
+    }
+    {
+        CM_TIMED("sod_wf", st);
+        sod_wf_kernel<<<dim3(ceil_div(w, 32), ceil_div(h, 8), batch), 256, 0, st>>>(pred, gt, ws.d2, ws.near, h, w, gk, ws.p4);
+    }
+    {
+        CM_TIMED("sod_finalize", st);
+        sod_finalize_kernel<<<batch, 256, 0, st>>>(ws.p1, ws.p2, ws.shift, ws.p4, ws.wf_tiles, ws.hist, h, w, 0.3, 1.0, per_image, ws.curves);
+        sod_partial_kernel<<<ceil_div(SOD_PARTIAL, 128), 128, 0, st>>>(per_image, ws.curves, batch, partial);
+    }
+    return post_launch("cm_sod_metrics");
+}

@@ -12,6 +12,9 @@ import torch
 from . import _lib
 
 KEYS = ("iou", "dice", "precision", "recall", "f1", "mae", "accuracy")
+# A9' (not in the reference; published definitions, see csrc/sod_metrics.cu / oracle/sod_metrics.py)
+SOD_KEYS = ("s_measure", "e_adaptive", "e_mean", "e_max", "f_adaptive", "f_mean", "f_max", "wf_measure")
+SOD_PARTIAL = 2 * len(SOD_KEYS) + 512
 
 
 def _device():
@@ -136,3 +139,90 @@ def f1_from_confusion(tp, fp, fn, tn):
     p0, r0 = tn / (tn + fn + eps), tn / (tn + fp + eps)
     f1_0 = 2 * (p0 * r0) / (p0 + r0 + eps)
     return {"f1_class_0": f1_0, "f1_class_1": f1_1, "f1_avg": (f1_0 + f1_1) / 2, "precision_1": p1, "recall_1": r1}
+
+
+# ---------------------------------------------------------------------------------------------------- A9'
+def sod_metrics(pred: torch.Tensor, gt_u8: torch.Tensor, per_image=None, partial=None):
+    """Device entry: ``pred`` ``[B,H,W]`` f32 in [0,1], ``gt_u8`` ``[B,H,W]`` uint8 (foreground = byte >= 128), CUDA ->
+    (per_image ``[B,8]`` f64 in ``SOD_KEYS`` order, partial ``[528]`` f64: sums, sums of squares, summed F / E curves)."""
+    from .region_graph import WORKSPACE
+    lib = _lib.load()
+    _lib.require_cuda(pred, "pred")
+    _lib.require_cuda(gt_u8, "gt")
+    if pred.dim() != 3 or pred.shape != gt_u8.shape or gt_u8.dtype != torch.uint8:
+        raise ValueError(f"pred {tuple(pred.shape)} f32 and gt {tuple(gt_u8.shape)} uint8 must both be [B,H,W]")
+    pred, gt_u8 = _lib.f32c(pred), gt_u8.contiguous()
+    B, H, W = pred.shape
+    dev = pred.device
+    if per_image is None:
+        per_image = torch.empty((B, len(SOD_KEYS)), dtype=torch.float64, device=dev)
+    if partial is None:
+        partial = torch.empty(SOD_PARTIAL, dtype=torch.float64, device=dev)
+    ws_bytes = lib.cm_sod_workspace_bytes(B, H, W)
+    ws = WORKSPACE.get(dev, "sod", ws_bytes)
+    _lib.check(lib.cm_sod_metrics(_lib.ptr(pred), _lib.ptr(gt_u8), B, H, W, _lib.ptr(ws), ws_bytes, _lib.ptr(per_image),
+                                  _lib.ptr(partial), _lib.stream_ptr(dev)), "cm_sod_metrics")
+    return per_image, partial
+
+
+def _sod_inputs(pred_mask, gt_mask):
+    dev = _device()
+    p = pred_mask if torch.is_tensor(pred_mask) else torch.as_tensor(np.asarray(pred_mask))
+    g = gt_mask if torch.is_tensor(gt_mask) else torch.as_tensor(np.asarray(gt_mask))
+    if p.dim() == 2:
+        p, g = p[None], g[None]
+    p = p.to(device=dev, dtype=torch.float32)
+    if g.dtype != torch.uint8:                       # float GT in [0,1] (np.array(PIL 'L') / 255.0): foreground = > 0.5
+        g = (g.to(dev) > 0.5).to(torch.uint8) * 255
+    return p, g.to(dev)
+
+
+def evaluate_sod(pred_mask, gt_mask):
+    """S- / E- / F- / weighted-F-measure of one ``[H,W]`` prediction in [0,1] -> dict with the eight ``SOD_KEYS``."""
+    p, g = _sod_inputs(pred_mask, gt_mask)
+    per, _ = sod_metrics(p, g)
+    return dict(zip(SOD_KEYS, per[0].tolist()))
+
+
+def calculate_s_measure(pred_mask, gt_mask):
+    return evaluate_sod(pred_mask, gt_mask)["s_measure"]
+
+
+def calculate_e_measure(pred_mask, gt_mask):
+    """Adaptive-threshold E-measure of one image."""
+    return evaluate_sod(pred_mask, gt_mask)["e_adaptive"]
+
+
+def calculate_f_measure(pred_mask, gt_mask):
+    """Adaptive-threshold F-measure (beta^2 = 0.3) of one image."""
+    return evaluate_sod(pred_mask, gt_mask)["f_adaptive"]
+
+
+def calculate_weighted_f_measure(pred_mask, gt_mask):
+    return evaluate_sod(pred_mask, gt_mask)["wf_measure"]
+
+
+def sod_summary_from_partial(partial, n_images) -> dict:
+    """Dataset-level numbers from the 528-element partial vector (after any cross-rank all-reduce) the way the
+    literature reports them: mean (and population std) of the per-image values, and ``f_max / f_mean / e_max / e_mean``
+    taken over the dataset-AVERAGED threshold curves."""
+    v = np.asarray(partial.detach().cpu() if torch.is_tensor(partial) else partial, dtype=np.float64)
+    n = float(n_images)
+    k = len(SOD_KEYS)
+    out = {}
+    for i, name in enumerate(SOD_KEYS):
+        mean = v[i] / n
+        out[name + "_per_image"] = float(mean)
+        out[name + "_per_image_std"] = float(np.sqrt(max(v[k + i] / n - mean * mean, 0.0)))
+    fc, ec = v[2 * k:2 * k + 256] / n, v[2 * k + 256:2 * k + 512] / n
+    for name in ("s_measure", "e_adaptive", "f_adaptive", "wf_measure"):
+        out[name] = out[name + "_per_image"]
+    out.update({"f_max": float(fc.max()), "f_mean": float(fc.mean()), "e_max": float(ec.max()), "e_mean": float(ec.mean())})
+    return out
+
+
+def batch_evaluate_sod(pred_masks, gt_masks):
+    p = torch.cat([_sod_inputs(a, b)[0] for a, b in zip(pred_masks, gt_masks)], 0)
+    g = torch.cat([_sod_inputs(a, b)[1] for a, b in zip(pred_masks, gt_masks)], 0)
+    _, part = sod_metrics(p, g)
+    return sod_summary_from_partial(part, p.shape[0])

@@ -19,11 +19,14 @@ from .region_graph import RegionGraphBatch, build_region_graphs
 
 class EvalPipeline:
     def __init__(self, gnn, detector, kg, label_cap: int = 544, threshold: float = 0.5, label_offset_fix: bool = False,
-                 want_pred_mask: bool = False, lane: int = 0):
+                 want_pred_mask: bool = False, lane: int = 0, sod_metrics: bool = True):
         """``kg``: ``[K, kg_dim]`` knowledge-graph rows shared by every image (broadcast once).
         ``lane``: pipelines with different lanes own disjoint scratch and may run concurrently on different streams
-        (they share the read-only folded weights)."""
+        (they share the read-only folded weights).
+        ``sod_metrics``: also compute S- / E- / F- / weighted-F-measure (``metrics.SOD_KEYS``; north_star's "S/E/F-measure",
+        not in the reference) on the painted mask: ``out["per_image_sod"]`` ``[B,8]``, ``out["partial_sod"]`` ``[528]``."""
         self.lane = int(lane)
+        self.sod_metrics = bool(sod_metrics)
         self.gnn, self.detector = gnn.eval(), detector.eval()
         kg = kg.reshape(-1, kg.shape[-1])
         _lib.require_cuda(kg, "kg")
@@ -34,6 +37,7 @@ class EvalPipeline:
         self._bufs = None
         self._shape = None
         self.total = None      # optional [15] f64 device accumulator of the per-batch metric partial sums
+        self.total_sod = None  # optional [528] f64 accumulator of the S/E/F partial sums
         self._side = None      # side stream for the paint + metrics branch
         self.parallel_metrics = os.environ.get("CM_PARALLEL_METRICS", "1") != "0"
 
@@ -53,7 +57,9 @@ class EvalPipeline:
             "abs_err": torch.empty(B, dtype=torch.float64, device=dev),
             "per_image": torch.empty((B, 7), dtype=torch.float64, device=dev),
             "partial": torch.empty(15, dtype=torch.float64, device=dev),
-            "pred_mask": torch.empty((B, H, W), **f32) if self.want_pred_mask else None,
+            "pred_mask": torch.empty((B, H, W), **f32) if (self.want_pred_mask or self.sod_metrics) else None,
+            "per_image_sod": torch.empty((B, len(metrics.SOD_KEYS)), dtype=torch.float64, device=dev) if self.sod_metrics else None,
+            "partial_sod": torch.empty(metrics.SOD_PARTIAL, dtype=torch.float64, device=dev) if self.sod_metrics else None,
         }
 
     def run(self, images, labels, canny, gt):
@@ -108,8 +114,12 @@ class EvalPipeline:
                                             _lib.stream_ptr(dev)), "cm_paint_metrics")
             _lib.check(lib.cm_metrics_finalize(p(b["counts"]), p(b["abs_err"]), B, H * W, p(b["per_image"]), p(b["partial"]),
                                                _lib.stream_ptr(dev)), "cm_metrics_finalize")
+            if self.sod_metrics:
+                metrics.sod_metrics(b["pred_mask"], gt, per_image=b["per_image_sod"], partial=b["partial_sod"])
             if self.total is not None:
                 self.total.add_(b["partial"])
+                if self.total_sod is not None and self.sod_metrics:
+                    self.total_sod.add_(b["partial_sod"])
         f = self.detector.forward_ragged(r["node_emb"], g.node_ptr, B, self.kg, return_attention=False,
                                          out=self._bufs["fusion"])
         self._bufs["fusion"] = f
@@ -118,7 +128,8 @@ class EvalPipeline:
         return {"graph": g, "status": g.status, "node_emb": r["node_emb"], "node_mask_out": r["mask_out"], "mask_prob": r["mask_prob"],
                 "mask_out": f["mask_out"], "instance_out": f["instance_out"], "edge_out": f["edge_out"],
                 "score_out": f["score_out"], "fused": f["fused"], "counts": b["counts"], "abs_err": b["abs_err"],
-                "per_image": b["per_image"], "partial": b["partial"], "pred_mask": b["pred_mask"]}
+                "per_image": b["per_image"], "partial": b["partial"], "pred_mask": b["pred_mask"],
+                "per_image_sod": b["per_image_sod"], "partial_sod": b["partial_sod"]}
 
 
     def capture(self, images, labels, canny, gt):
@@ -197,8 +208,9 @@ class HostStager:
         self.h_mask_out = torch.empty((B, 2), dtype=torch.float32, **pin)
         self.h_per_image = torch.empty((B, 7), dtype=torch.float64, **pin)
         self.h_status = torch.zeros(1, dtype=torch.int32, **pin)
+        self.h_per_image_sod = torch.empty((B, len(metrics.SOD_KEYS)), dtype=torch.float64, **pin)
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in (self.h_images, self.h_labels, self.h_canny, self.h_gt))
-        self.d2h_bytes = sum(t.numel() * t.element_size() for t in (self.h_mask_out, self.h_per_image, self.h_status))
+        self.d2h_bytes = sum(t.numel() * t.element_size() for t in (self.h_mask_out, self.h_per_image, self.h_status, self.h_per_image_sod))
 
     def fill(self, batch):
         self.h_images.copy_(batch.images)
@@ -213,6 +225,8 @@ class HostStager:
         self.h_mask_out.copy_(out["mask_out"], non_blocking=True)
         self.h_per_image.copy_(out["per_image"], non_blocking=True)
         self.h_status.copy_(out["status"], non_blocking=True)
+        if out["per_image_sod"] is not None:
+            self.h_per_image_sod.copy_(out["per_image_sod"], non_blocking=True)
         return out
 
     def check(self):
@@ -276,6 +290,8 @@ class HostPipeline:
             st.h_mask_out.copy_(out["mask_out"], non_blocking=True)
             st.h_per_image.copy_(out["per_image"], non_blocking=True)
             st.h_status.copy_(out["status"], non_blocking=True)
+            if out["per_image_sod"] is not None:
+                st.h_per_image_sod.copy_(out["per_image_sod"], non_blocking=True)
             self.pipe_done[st.pipe_idx].record(st.stream)
             st.ev_done.record(st.stream)
         return st
@@ -314,15 +330,22 @@ def _physical_index(device_index: int) -> int:
     return device_index
 
 
-def allreduce_partials(partial: torch.Tensor, confusion: torch.Tensor | None = None):
-    """Sum the metric partial sums (and image-level confusion counts) over ranks: the only data-path collective
-    of the sharded evaluation.  No-op without an initialised process group."""
+def allreduce_partials(partial: torch.Tensor, confusion: torch.Tensor | None = None, partial_sod: torch.Tensor | None = None):
+    """Sum the metric partial sums (and image-level confusion counts, and the S/E/F partial vector) over ranks: the
+    only data-path collective of the sharded evaluation.  No-op without an initialised process group.
+    Returns ``(partial, confusion)`` -- plus ``partial_sod`` when one was given."""
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-        dist.all_reduce(partial, op=dist.ReduceOp.SUM)
+        if partial_sod is not None:      # one collective for both float64 vectors
+            both = torch.cat([partial, partial_sod])
+            dist.all_reduce(both, op=dist.ReduceOp.SUM)
+            partial.copy_(both[:partial.numel()])
+            partial_sod.copy_(both[partial.numel():])
+        else:
+            dist.all_reduce(partial, op=dist.ReduceOp.SUM)
         if confusion is not None:
             dist.all_reduce(confusion, op=dist.ReduceOp.SUM)
-    return partial, confusion
+    return (partial, confusion) if partial_sod is None else (partial, confusion, partial_sod)
 
 
 def shard_indices(n_items: int, rank: int, world: int):

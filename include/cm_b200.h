@@ -325,6 +325,21 @@ int cm_metrics_dense(const float* pred, const float* gt, int batch, int64_t pixe
  * and from which batch_evaluate's mean / population std follow (utils/metrics.py:78-92). */
 int cm_metrics_finalize(const int64_t* counts, const double* abs_err, int batch, int64_t pixels,
                         double* per_image, double* partial, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A9': S-measure (Fan et al. ICCV'17), E-measure (Fan et al. IJCAI'18), F-measure (beta^2 = 0.3) and weighted
+ * F-measure (Margolin et al. CVPR'14).  NOT IN THE REFERENCE (utils/metrics.py:9-92 has none of them; BASELINE.json's
+ * north_star names them): the published definitions, restated in oracle/sod_metrics.py -- parity unpinned.
+ * pred [B,H,W] float32 in [0,1] (e.g. cm_paint_metrics' pred_mask), gt [B,H,W] uint8 (foreground = byte >= 128).
+ * per_image [B,8] float64 out: s_measure, e_adaptive, e_mean, e_max, f_adaptive, f_mean, f_max, wf_measure
+ * (adaptive threshold min(2 mean(pred), 1); mean / max over the image's own 256-threshold curve).
+ * partial [528] float64 out: sum of the 8 keys, sum of their squares, then the batch sums of the F curve [256] and the
+ * E curve [256] (entry i = threshold floor(255 pred) >= 255 - i) -- the vector to all-reduce next to
+ * cm_metrics_finalize's: dataset-level max / mean F and E are taken over the dataset-AVERAGED curves.
+ * ------------------------------------------------------------------------------------------------ */
+size_t cm_sod_workspace_bytes(int batch, int h, int w);
+int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, int h, int w, void* workspace, size_t workspace_bytes,
+                   double* per_image, double* partial, void* stream);
 /* A13: image-level confusion counts tp, fp, fn, tn (models/multimodal/train_multimodal.py:197-220) from
  * predicted class = argmax(mask_out) and true class ids.  counts4 [4] int64 accumulated (caller zeroes). */
 int cm_class_confusion(const float* mask_out, const int64_t* true_cls, int n, int num_classes,
