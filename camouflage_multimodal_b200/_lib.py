@@ -87,7 +87,7 @@ FUSION_GRAD_FIELDS = ["rg_proj_w", "rg_proj_b", "kg_proj_w", "kg_proj_b", "r2k_i
 
 class FusionGrads(C.Structure):
     _fields_ = [(n, _fp) for n in FUSION_GRAD_FIELDS] + [("head_w1", _fp * 4), ("head_b1", _fp * 4), ("head_w2", _fp * 4),
-                                                         ("head_b2", _fp * 4)]
+                                                         ("head_b2", _fp * 4), ("late_w", _fp * 3), ("late_b", _fp * 3)]
 
 
 # name -> (restype, argtypes); the list is also what tests/test_abi.py checks against include/cm_b200.h

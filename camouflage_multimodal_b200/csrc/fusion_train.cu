@@ -370,6 +370,168 @@ __global__ void ft_sigmoid_bwd_kernel(const float* __restrict__ s, const float* 
 static float fdrop_scale(const cm_fusion_dropout* d, int site) { return d && d->keep[site] ? 1.f / (1.f - d->p) : 1.f; }
 static const uint8_t* fdrop_keep(const cm_fusion_dropout* d, int site) { return d ? d->keep[site] : nullptr; }
 
+// ------------------------------------------------------------------------------------------------ late fusion
+// LateFusion under model.train() (fusion_model.py:149-171 + the detector heads :208-246 with final_dim = hidden / 2):
+// mean over nodes / KG rows -> cat -> Linear ReLU Dropout -> Linear ReLU Dropout -> Linear -> heads.  Dropout sites:
+// keep[0] [G, hidden], keep[1] [G, hidden/2], keep[5..8] the four head hidden layers [G, hidden/4].
+struct LateTrainWs {
+    float *cat, *h1, *h2, *fused, *hh[4], *score;
+    float *dfused, *dhh, *dh2, *dh1, *dcat, *dsig;
+    double* part_d;
+    size_t total;
+};
+static LateTrainWs carve_late_train(void* ws, const cm_fusion_params* p, int G) {
+    Carver c(ws);
+    LateTrainWs w;
+    const size_t g = (size_t)(G > 0 ? G : 1), D = p->hidden, FD = D / 2, HD = FD / 2, in = (size_t)p->rg_dim + p->kg_dim;
+    w.cat = c.take<float>(g * in);
+    w.h1 = c.take<float>(g * D);
+    w.h2 = c.take<float>(g * FD);
+    w.fused = c.take<float>(g * FD);
+    for (int t = 0; t < 4; ++t) w.hh[t] = c.take<float>(g * HD);
+    w.score = c.take<float>(g);
+    w.dfused = c.take<float>(g * FD);
+    w.dhh = c.take<float>(g * HD);
+    w.dh2 = c.take<float>(g * FD);
+    w.dh1 = c.take<float>(g * D);
+    w.dcat = c.take<float>(g * in);
+    w.dsig = c.take<float>(g);
+    w.part_d = c.take<double>((size_t)col_parts((int)g) * (D > in ? D : in));
+    w.total = align_up(c.off, 256);
+    return w;
+}
+static int check_late_train(const cm_fusion_params* p, const char* who) {
+    if (!p || p->fusion_type != 1 || p->hidden <= 0 || p->hidden % 4 || p->rg_dim <= 0 || p->kg_dim <= 0 || p->num_classes <= 0 ||
+        !p->late_w[0] || !p->late_w[1] || !p->late_w[2]) {
+        set_error("%s: late fusion needs hidden %% 4 == 0 and its three Linear layers", who);
+        return CM_ERR_ARG;
+    }
+    return CM_OK;
+}
+// heads on `fused` [G, FD] (hidden layer FD / 2): shared by both fusion types
+static void heads_train_forward(const cm_fusion_params* p, const cm_fusion_dropout* drop, const float* fusedp, int FD, int G, float* const* hh,
+                                float* score_ws, float* mask_out, float* instance_out, float* edge_out, float* score_out, cudaStream_t st) {
+    const int HD = FD / 2;
+    float* outs[4] = {mask_out, instance_out, edge_out, score_out};
+    const int cdim[4] = {p->num_classes, p->num_classes, 1, 1};
+    for (int t = 0; t < 4; ++t) {
+        if (!p->head_w1[t]) continue;   // a bare fusion module (CrossAttentionFusion / LateFusion on its own) has no heads
+        Gemm g = gemm_nt(fusedp, FD, p->head_w1[t], hh[t], HD, G, HD, FD, p->head_b1[t], 1);
+        g.keep = fdrop_keep(drop, 5 + t);
+        g.keep_scale = fdrop_scale(drop, 5 + t);
+        launch_gemm(g, st, "train_linear");
+        float* o = t == 3 ? score_ws : outs[t];
+        if (!o) continue;
+        launch_gemm(gemm_nt(hh[t], HD, p->head_w2[t], o, cdim[t], G, cdim[t], HD, p->head_b2[t], 0), st, "train_linear");
+        if (t == 3) {
+            CM_TIMED("train_elementwise", st);
+            ft_sigmoid_kernel<<<ceil_div(G, 128), 128, 0, st>>>(score_ws, G);   // :233
+            if (score_out) cudaMemcpyAsync(score_out, score_ws, sizeof(float) * G, cudaMemcpyDeviceToDevice, st);
+        }
+    }
+}
+// accumulates the heads' contribution into dfused [G, FD] (pre-set by the caller) and writes the head gradients
+static void heads_backward(const cm_fusion_params* p, const cm_fusion_dropout* drop, const cm_fusion_grads* gr, const float* fusedp, int FD, int G,
+                           float* const* hh, const float* score_ws, const float* const* douts, float* dsig, float* dhh, double* part_d,
+                           float* dfused, cudaStream_t st) {
+    const int HD = FD / 2;
+    const int cdim[4] = {p->num_classes, p->num_classes, 1, 1};
+    for (int t = 0; t < 4; ++t) {
+        if (!p->head_w1[t]) continue;
+        if (!douts[t]) {
+            cudaMemsetAsync(gr->head_w2[t], 0, sizeof(float) * cdim[t] * HD, st);
+            cudaMemsetAsync(gr->head_b2[t], 0, sizeof(float) * cdim[t], st);
+            cudaMemsetAsync(gr->head_w1[t], 0, sizeof(float) * HD * FD, st);
+            cudaMemsetAsync(gr->head_b1[t], 0, sizeof(float) * HD, st);
+            continue;
+        }
+        const float* dout = douts[t];
+        if (t == 3) {   // through the sigmoid
+            CM_TIMED("train_elementwise", st);
+            ft_sigmoid_bwd_kernel<<<ceil_div(G, 128), 128, 0, st>>>(score_ws, douts[3], G, dsig);
+            dout = dsig;
+        }
+        launch_gemm(gemm_tn(dout, cdim[t], hh[t], HD, gr->head_w2[t], G, cdim[t], HD, nullptr, 1), st, "train_wgrad");
+        launch_colsum(dout, cdim[t], G, cdim[t], part_d, gr->head_b2[t], 0, st);
+        launch_gemm(gemm_nn(dout, cdim[t], p->head_w2[t], dhh, HD, G, cdim[t], HD), st, "train_dgrad");
+        launch_relu_drop_bwd(hh[t], fdrop_scale(drop, 5 + t), (long)G * HD, dhh, st);
+        launch_gemm(gemm_tn(dhh, HD, fusedp, FD, gr->head_w1[t], G, HD, FD, nullptr, 1), st, "train_wgrad");
+        launch_colsum(dhh, HD, G, HD, part_d, gr->head_b1[t], 0, st);
+        Gemm g = gemm_nn(dhh, HD, p->head_w1[t], dfused, FD, G, HD, FD);
+        g.accumulate = 1;
+        launch_gemm(g, st, "train_dgrad");
+    }
+}
+
+static int late_train_forward(const cm_fusion_params* p, const float* rg, const int32_t* node_ptr, int G, int M, const float* kg, int K,
+                              const cm_fusion_dropout* drop, void* workspace, size_t workspace_bytes, float* fused, float* mask_out,
+                              float* instance_out, float* edge_out, float* score_out, cudaStream_t st) {
+    (void)M;
+    const int D = p->hidden, FD = D / 2, in = p->rg_dim + p->kg_dim;
+    LateTrainWs w = carve_late_train(workspace, p, G);
+    if (workspace_bytes < w.total) {
+        set_error("cm_fusion_train_forward: workspace %zu < %zu bytes", workspace_bytes, w.total);
+        return CM_ERR_WORKSPACE;
+    }
+    {
+        CM_TIMED("train_pool", st);
+        ft_mean_pool_kernel<<<G, 256, 0, st>>>(rg, p->rg_dim, node_ptr, 0, G, w.cat, in, 0);          // :165-166
+        ft_mean_pool_kernel<<<G, 256, 0, st>>>(kg, p->kg_dim, nullptr, K, G, w.cat, in, p->rg_dim);   // :167-168
+    }
+    {
+        Gemm g = gemm_nt(w.cat, in, p->late_w[0], w.h1, D, G, D, in, p->late_b[0], 1);
+        g.keep = fdrop_keep(drop, 0);
+        g.keep_scale = fdrop_scale(drop, 0);
+        launch_gemm(g, st, "train_linear");
+    }
+    {
+        Gemm g = gemm_nt(w.h1, D, p->late_w[1], w.h2, FD, G, FD, D, p->late_b[1], 1);
+        g.keep = fdrop_keep(drop, 1);
+        g.keep_scale = fdrop_scale(drop, 1);
+        launch_gemm(g, st, "train_linear");
+    }
+    launch_gemm(gemm_nt(w.h2, FD, p->late_w[2], w.fused, FD, G, FD, FD, p->late_b[2], 0), st, "train_linear");
+    if (fused) cudaMemcpyAsync(fused, w.fused, sizeof(float) * G * FD, cudaMemcpyDeviceToDevice, st);
+    heads_train_forward(p, drop, w.fused, FD, G, w.hh, w.score, mask_out, instance_out, edge_out, score_out, st);
+    return post_launch("cm_fusion_train_forward");
+}
+
+static int late_backward(const cm_fusion_params* p, const float* rg, const int32_t* node_ptr, int G, int M, const float* kg, int K,
+                         const cm_fusion_dropout* drop, void* workspace, size_t workspace_bytes, const float* d_fused, const float* const* douts,
+                         const cm_fusion_grads* gr, float* d_rg, float* d_kg, cudaStream_t st) {
+    (void)rg;
+    (void)kg;
+    const int D = p->hidden, FD = D / 2, in = p->rg_dim + p->kg_dim;
+    CM_REQUIRE(gr->late_w[0] && gr->late_w[1] && gr->late_w[2] && gr->late_b[0] && gr->late_b[1] && gr->late_b[2],
+               "cm_fusion_backward: late fusion needs the late_w / late_b gradient buffers");
+    LateTrainWs w = carve_late_train(workspace, p, G);
+    if (workspace_bytes < w.total) {
+        set_error("cm_fusion_backward: workspace %zu < %zu bytes", workspace_bytes, w.total);
+        return CM_ERR_WORKSPACE;
+    }
+    if (d_fused) cudaMemcpyAsync(w.dfused, d_fused, sizeof(float) * G * FD, cudaMemcpyDeviceToDevice, st);
+    else cudaMemsetAsync(w.dfused, 0, sizeof(float) * G * FD, st);
+    heads_backward(p, drop, gr, w.fused, FD, G, w.hh, w.score, douts, w.dsig, w.dhh, w.part_d, w.dfused, st);
+    launch_gemm(gemm_tn(w.dfused, FD, w.h2, FD, gr->late_w[2], G, FD, FD, nullptr, 1), st, "train_wgrad");
+    launch_colsum(w.dfused, FD, G, FD, w.part_d, gr->late_b[2], 0, st);
+    launch_gemm(gemm_nn(w.dfused, FD, p->late_w[2], w.dh2, FD, G, FD, FD), st, "train_dgrad");
+    launch_relu_drop_bwd(w.h2, fdrop_scale(drop, 1), (long)G * FD, w.dh2, st);
+    launch_gemm(gemm_tn(w.dh2, FD, w.h1, D, gr->late_w[1], G, FD, D, nullptr, 1), st, "train_wgrad");
+    launch_colsum(w.dh2, FD, G, FD, w.part_d, gr->late_b[1], 0, st);
+    launch_gemm(gemm_nn(w.dh2, FD, p->late_w[1], w.dh1, D, G, FD, D), st, "train_dgrad");
+    launch_relu_drop_bwd(w.h1, fdrop_scale(drop, 0), (long)G * D, w.dh1, st);
+    launch_gemm(gemm_tn(w.dh1, D, w.cat, in, gr->late_w[0], G, D, in, nullptr, 1), st, "train_wgrad");
+    launch_colsum(w.dh1, D, G, D, w.part_d, gr->late_b[0], 0, st);
+    launch_gemm(gemm_nn(w.dh1, D, p->late_w[0], w.dcat, in, G, D, in), st, "train_dgrad");
+    {
+        CM_TIMED("train_pool", st);
+        if (d_rg) ft_mean_pool_bwd_kernel<<<ceil_div((long)M * p->rg_dim, 256), 256, 0, st>>>(w.dcat, in, 0, p->rg_dim, node_ptr, 0, G, M, d_rg);
+        if (d_kg)
+            ft_mean_pool_bwd_kernel<<<ceil_div((long)G * K * p->kg_dim, 256), 256, 0, st>>>(w.dcat, in, p->rg_dim, p->kg_dim, nullptr, K, G, G * K, d_kg);
+    }
+    return post_launch("cm_fusion_backward");
+}
+
 static int check_fusion_train(const cm_fusion_params* p, const char* who) {
     if (!p || p->fusion_type != 0 || p->hidden <= 0 || p->heads <= 0 || p->hidden % p->heads || p->hidden / p->heads > 32 * FT_MAX_DPL ||
         p->hidden % 2 || p->num_classes <= 0) {
@@ -382,6 +544,10 @@ static int check_fusion_train(const cm_fusion_params* p, const char* who) {
 }  // namespace cm
 
 extern "C" size_t cm_fusion_train_workspace_bytes(const cm_fusion_params* p, int n_graphs, int n_rows, int n_kg) {
+    if (p && p->fusion_type == 1) {
+        if (cm::check_late_train(p, "cm_fusion_train_workspace_bytes") != CM_OK || n_graphs <= 0) return 0;
+        return cm::carve_late_train(nullptr, p, n_graphs).total;
+    }
     if (cm::check_fusion_train(p, "cm_fusion_train_workspace_bytes") != CM_OK || n_graphs <= 0 || n_rows < 0 || n_kg <= 0) return 0;
     return cm::carve_fusion_train(nullptr, p, n_graphs, n_rows, n_kg).total;
 }
@@ -391,9 +557,15 @@ extern "C" int cm_fusion_train_forward(const cm_fusion_params* p, const float* r
                                        float* fused, float* mask_out, float* instance_out, float* edge_out, float* score_out, void* stream) {
     using namespace cm;
     CM_DEVICE_OR_RETURN();
+    if (p && p->fusion_type == 1) {
+        if (int rc = check_late_train(p, "cm_fusion_train_forward")) return rc;
+        CM_REQUIRE(rg && node_ptr && kg && workspace && n_graphs > 0 && n_rows > 0 && n_kg > 0, "cm_fusion_train_forward: bad arguments");
+        return late_train_forward(p, rg, node_ptr, n_graphs, n_rows, kg, n_kg, drop, workspace, workspace_bytes, fused, mask_out, instance_out,
+                                  edge_out, score_out, as_stream(stream));
+    }
     if (int rc = check_fusion_train(p, "cm_fusion_train_forward")) return rc;
     CM_REQUIRE(rg && node_ptr && kg && workspace && n_graphs > 0 && n_rows > 0 && n_kg > 0, "cm_fusion_train_forward: bad arguments");
-    const int G = n_graphs, M = n_rows, K = n_kg, D = p->hidden, H = p->heads, GK = G * K, D2 = D / 2;
+    const int G = n_graphs, M = n_rows, K = n_kg, D = p->hidden, H = p->heads, GK = G * K;
     FusionTrainWs w = carve_fusion_train(workspace, p, G, M, K);
     if (workspace_bytes < w.total) {
         set_error("cm_fusion_train_forward: workspace %zu < %zu bytes", workspace_bytes, w.total);
@@ -458,22 +630,7 @@ extern "C" int cm_fusion_train_forward(const cm_fusion_params* p, const float* r
     }
     launch_gemm(gemm_nt(w.Fh, D, p->fl_w2, w.fused, D, G, D, D, p->fl_b2, 0), st, "train_linear");
     if (fused) cudaMemcpyAsync(fused, w.fused, sizeof(float) * G * D, cudaMemcpyDeviceToDevice, st);
-    float* outs[4] = {mask_out, instance_out, edge_out, score_out};
-    const int cdim[4] = {p->num_classes, p->num_classes, 1, 1};
-    for (int t = 0; t < 4; ++t) {
-        Gemm g = gemm_nt(w.fused, D, p->head_w1[t], w.hh[t], D2, G, D2, D, p->head_b1[t], 1);
-        g.keep = fdrop_keep(drop, 5 + t);
-        g.keep_scale = fdrop_scale(drop, 5 + t);
-        launch_gemm(g, st, "train_linear");
-        float* o = t == 3 ? w.score : outs[t];
-        if (!o) continue;
-        launch_gemm(gemm_nt(w.hh[t], D2, p->head_w2[t], o, cdim[t], G, cdim[t], D2, p->head_b2[t], 0), st, "train_linear");
-        if (t == 3) {
-            CM_TIMED("train_elementwise", st);
-            ft_sigmoid_kernel<<<ceil_div(G, 128), 128, 0, st>>>(w.score, G);   // :233
-            if (score_out) cudaMemcpyAsync(score_out, w.score, sizeof(float) * G, cudaMemcpyDeviceToDevice, st);
-        }
-    }
+    heads_train_forward(p, drop, w.fused, D, G, w.hh, w.score, mask_out, instance_out, edge_out, score_out, st);
     return post_launch("cm_fusion_train_forward");
 }
 
@@ -483,9 +640,16 @@ extern "C" int cm_fusion_backward(const cm_fusion_params* p, const float* rg, co
                                   const float* d_score_out, const cm_fusion_grads* gr, float* d_rg, float* d_kg, void* stream) {
     using namespace cm;
     CM_DEVICE_OR_RETURN();
+    const float* douts[4] = {d_mask_out, d_instance_out, d_edge_out, d_score_out};
+    if (p && p->fusion_type == 1) {
+        if (int rc = check_late_train(p, "cm_fusion_backward")) return rc;
+        CM_REQUIRE(rg && node_ptr && kg && workspace && gr && n_graphs > 0 && n_rows > 0 && n_kg > 0, "cm_fusion_backward: bad arguments");
+        return late_backward(p, rg, node_ptr, n_graphs, n_rows, kg, n_kg, drop, workspace, workspace_bytes, d_fused, douts, gr, d_rg, d_kg,
+                             as_stream(stream));
+    }
     if (int rc = check_fusion_train(p, "cm_fusion_backward")) return rc;
     CM_REQUIRE(rg && node_ptr && kg && workspace && gr && n_graphs > 0 && n_rows > 0 && n_kg > 0, "cm_fusion_backward: bad arguments");
-    const int G = n_graphs, M = n_rows, K = n_kg, D = p->hidden, H = p->heads, GK = G * K, D2 = D / 2;
+    const int G = n_graphs, M = n_rows, K = n_kg, D = p->hidden, H = p->heads, GK = G * K;
     FusionTrainWs w = carve_fusion_train(workspace, p, G, M, K);
     if (workspace_bytes < w.total) {
         set_error("cm_fusion_backward: workspace %zu < %zu bytes", workspace_bytes, w.total);
@@ -499,32 +663,7 @@ extern "C" int cm_fusion_backward(const cm_fusion_params* p, const float* rg, co
     // ---- heads -> dfused
     if (d_fused) cudaMemcpyAsync(w.dfused, d_fused, sizeof(float) * G * D, cudaMemcpyDeviceToDevice, st);
     else cudaMemsetAsync(w.dfused, 0, sizeof(float) * G * D, st);
-    const float* douts[4] = {d_mask_out, d_instance_out, d_edge_out, d_score_out};
-    const int cdim[4] = {p->num_classes, p->num_classes, 1, 1};
-    for (int t = 0; t < 4; ++t) {
-        if (!douts[t]) {
-            cudaMemsetAsync(gr->head_w2[t], 0, sizeof(float) * cdim[t] * D2, st);
-            cudaMemsetAsync(gr->head_b2[t], 0, sizeof(float) * cdim[t], st);
-            cudaMemsetAsync(gr->head_w1[t], 0, sizeof(float) * D2 * D, st);
-            cudaMemsetAsync(gr->head_b1[t], 0, sizeof(float) * D2, st);
-            continue;
-        }
-        const float* dout = douts[t];
-        if (t == 3) {   // through the sigmoid
-            CM_TIMED("train_elementwise", st);
-            ft_sigmoid_bwd_kernel<<<ceil_div(G, 128), 128, 0, st>>>(w.score, d_score_out, G, w.dcat);
-            dout = w.dcat;
-        }
-        launch_gemm(gemm_tn(dout, cdim[t], w.hh[t], D2, gr->head_w2[t], G, cdim[t], D2, nullptr, 1), st, "train_wgrad");
-        launch_colsum(dout, cdim[t], G, cdim[t], w.part_d, gr->head_b2[t], 0, st);
-        launch_gemm(gemm_nn(dout, cdim[t], p->head_w2[t], w.dhh, D2, G, cdim[t], D2), st, "train_dgrad");
-        launch_relu_drop_bwd(w.hh[t], fdrop_scale(drop, 5 + t), (long)G * D2, w.dhh, st);
-        launch_gemm(gemm_tn(w.dhh, D2, w.fused, D, gr->head_w1[t], G, D2, D, nullptr, 1), st, "train_wgrad");
-        launch_colsum(w.dhh, D2, G, D2, w.part_d, gr->head_b1[t], 0, st);
-        Gemm g = gemm_nn(w.dhh, D2, p->head_w1[t], w.dfused, D, G, D2, D);
-        g.accumulate = 1;
-        launch_gemm(g, st, "train_dgrad");
-    }
+    heads_backward(p, drop, gr, w.fused, D, G, w.hh, w.score, douts, w.dcat, w.dhh, w.part_d, w.dfused, st);
     // ---- fusion_layer
     launch_gemm(gemm_tn(w.dfused, D, w.Fh, D, gr->fl_w2, G, D, D, nullptr, 1), st, "train_wgrad");
     launch_colsum(w.dfused, D, G, D, w.part_d, gr->fl_b2, 0, st);

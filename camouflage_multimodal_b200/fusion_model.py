@@ -173,6 +173,7 @@ class CrossAttentionFusion(nn.Module):
     def __init__(self, rg_dim=128, kg_dim=128, hidden_dim=256, num_heads=8, dropout=0.3):
         super().__init__()
         self.rg_dim, self.kg_dim, self.hidden_dim = rg_dim, kg_dim, hidden_dim
+        self.dropout_p = float(dropout)
         self.rg_proj = nn.Linear(rg_dim, hidden_dim) if rg_dim != hidden_dim else nn.Identity()
         self.kg_proj = nn.Linear(kg_dim, hidden_dim) if kg_dim != hidden_dim else nn.Identity()
         self.cross_attn_rg2kg = nn.MultiheadAttention(embed_dim=hidden_dim, num_heads=num_heads, dropout=dropout, batch_first=True)
@@ -188,11 +189,19 @@ class CrossAttentionFusion(nn.Module):
         self._runner = _FusionRunner(self)
 
     def forward(self, rg_embeddings, kg_embeddings):
-        if self.training:
-            raise NotImplementedError("the B200 fusion path is inference-only for now: call .eval()")
         rows, node_ptr, B, N, kg = _dense_inputs(rg_embeddings, kg_embeddings)
-        res = self._runner.run(rows, node_ptr, B, kg, want_attention=True, want_heads=False)
         K = kg.shape[1]
+        if self.training:
+            # model.train(): ``fused`` is differentiable through cm_fusion_train_forward / cm_fusion_backward (dropout
+            # masks drawn here).  The attention maps are a detached side output: the head-averaged probabilities WITHOUT
+            # the attention dropout nn.MultiheadAttention applies to the weights it returns in training mode (those are
+            # one random draw; nothing downstream of the reference reads them while training).
+            from .training import fusion_train_forward
+            fused = fusion_train_forward(self, rows, node_ptr, B, kg)
+            with torch.no_grad():
+                res = self._runner.run(rows.detach(), node_ptr, B, kg.detach(), want_attention=True, want_heads=False)
+            return fused, {"rg2kg": res["rg2kg"].view(B, N, K), "kg2rg": res["kg2rg"].view(B, K, N)}
+        res = self._runner.run(rows, node_ptr, B, kg, want_attention=True, want_heads=False)
         return res["fused"], {"rg2kg": res["rg2kg"].view(B, N, K), "kg2rg": res["kg2rg"].view(B, K, N)}
 
 
@@ -202,6 +211,7 @@ class LateFusion(nn.Module):
     def __init__(self, rg_dim=128, kg_dim=128, hidden_dim=256, dropout=0.3):
         super().__init__()
         self.rg_dim, self.kg_dim, self.hidden_dim = rg_dim, kg_dim, hidden_dim
+        self.dropout_p = float(dropout)
         self.fusion = nn.Sequential(nn.Linear(rg_dim + kg_dim, hidden_dim), nn.ReLU(), nn.Dropout(dropout),
                                     nn.Linear(hidden_dim, hidden_dim // 2), nn.ReLU(), nn.Dropout(dropout),
                                     nn.Linear(hidden_dim // 2, hidden_dim // 2))
@@ -221,9 +231,10 @@ class LateFusion(nn.Module):
         return rg.reshape(B * N, rg.shape[-1]), node_ptr, B, kg
 
     def forward(self, rg_embeddings, kg_embeddings):
-        if self.training:
-            raise NotImplementedError("the B200 fusion path is inference-only for now: call .eval()")
         rows, node_ptr, B, kg = self._inputs(rg_embeddings, kg_embeddings)
+        if self.training:   # dropout + autograd through cm_fusion_train_forward / cm_fusion_backward (fusion_type 1)
+            from .training import fusion_train_forward
+            return fusion_train_forward(self, rows, node_ptr, B, kg), None
         res = self._runner.run(rows, node_ptr, B, kg, want_attention=False, want_heads=False)
         return res["fused"], None
 
@@ -268,19 +279,29 @@ class MultimodalCamouflageDetector(nn.Module):
 
     def _train_forward(self, rg_rows, node_ptr, n_graphs, kg, return_attention):
         """model.train(): dropout + autograd through ``cm_fusion_train_forward`` / ``cm_fusion_backward`` (training.py)."""
-        if self.fusion_type != "cross_attention":
-            raise NotImplementedError("training on the B200 path covers fusion_type='cross_attention' (the YAML default)")
-        if return_attention:
-            raise NotImplementedError("attention maps are an inference output here: call .eval() to get them")
         from .training import fusion_train_forward
         fused, mask, inst, edge, score = fusion_train_forward(self, rg_rows, node_ptr, n_graphs, kg)
-        return {"fused": fused, "mask_out": mask, "instance_out": inst, "edge_out": edge, "score_out": score}
+        res = {"fused": fused, "mask_out": mask, "instance_out": inst, "edge_out": edge, "score_out": score}
+        if return_attention and self.fusion_type == "cross_attention":   # detached, dropout-free maps (see CrossAttentionFusion.forward)
+            with torch.no_grad():
+                a = self._runner.run(rg_rows.detach(), node_ptr, n_graphs, kg.detach(), want_attention=True, want_heads=False)
+            res["rg2kg"], res["kg2rg"] = a["rg2kg"], a["kg2rg"]
+        return res
 
     def forward(self, rg_embeddings, kg_embeddings, return_attention=False):
         if self.training:
-            rows, node_ptr, B, N, kg = _dense_inputs(rg_embeddings, kg_embeddings)
+            if self.fusion_type == "cross_attention":
+                rows, node_ptr, B, N, kg = _dense_inputs(rg_embeddings, kg_embeddings)
+            else:
+                rows, node_ptr, B, kg = LateFusion._inputs(rg_embeddings, kg_embeddings)
             res = self._train_forward(rows, node_ptr, B, kg, return_attention)
-            return (res["mask_out"], res["instance_out"], res["edge_out"], res["score_out"])
+            outs = (res["mask_out"], res["instance_out"], res["edge_out"], res["score_out"])
+            if return_attention:
+                K = kg.shape[1]
+                attn = ({"rg2kg": res["rg2kg"].view(B, N, K), "kg2rg": res["kg2rg"].view(B, K, N)}
+                        if self.fusion_type == "cross_attention" else None)
+                return outs + (attn,)
+            return outs
         attn = None
         if self.fusion_type == "cross_attention":
             rows, node_ptr, B, N, kg = _dense_inputs(rg_embeddings, kg_embeddings)

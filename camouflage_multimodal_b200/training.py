@@ -139,32 +139,45 @@ def update_bn_running_stats(model, batch_mean, batch_var, n):
 
 
 # ------------------------------------------------------------------------------------------------ fusion
-def _fusion_param_list(det):
-    """Trainable tensors of a cross-attention ``MultimodalCamouflageDetector`` in ``cm_fusion_grads`` field order;
-    ``None`` where the projection is ``nn.Identity``."""
+def _fusion_param_list(runner):
+    """Trainable tensors behind a ``_FusionRunner`` (a detector, or a bare CrossAttentionFusion / LateFusion) in
+    ``cm_fusion_grads`` field order: the 28 cross-attention tensors, the 16 head tensors, the 6 late-fusion tensors;
+    ``None`` where the module has no such tensor (``nn.Identity`` projection, no heads, the other fusion type)."""
     import torch.nn as nn
-    f = det.fusion
+    from .fusion_model import CrossAttentionFusion
+    f = runner.fusion
     lin = lambda m: (m.weight, m.bias) if isinstance(m, nn.Linear) else (None, None)
-    out = [*lin(f.rg_proj), *lin(f.kg_proj)]
-    for m in (f.cross_attn_rg2kg, f.cross_attn_kg2rg):
-        out += [m.in_proj_weight, m.in_proj_bias, m.out_proj.weight, m.out_proj.bias]
-    out += [f.ln_rg.weight, f.ln_rg.bias, f.ln_kg.weight, f.ln_kg.bias]
-    for seq in (f.ffn_rg, f.ffn_kg, f.fusion_layer):
-        out += [seq[0].weight, seq[0].bias, seq[3].weight, seq[3].bias]
-    heads = (det.mask_head, det.instance_head, det.edge_head, det.score_head)
-    out += [h[0].weight for h in heads] + [h[0].bias for h in heads] + [h[3].weight for h in heads] + [h[3].bias for h in heads]
-    return out
+    if isinstance(f, CrossAttentionFusion):
+        out = [*lin(f.rg_proj), *lin(f.kg_proj)]
+        for m in (f.cross_attn_rg2kg, f.cross_attn_kg2rg):
+            out += [m.in_proj_weight, m.in_proj_bias, m.out_proj.weight, m.out_proj.bias]
+        out += [f.ln_rg.weight, f.ln_rg.bias, f.ln_kg.weight, f.ln_kg.bias]
+        for seq in (f.ffn_rg, f.ffn_kg, f.fusion_layer):
+            out += [seq[0].weight, seq[0].bias, seq[3].weight, seq[3].bias]
+        late = [None] * 6
+    else:
+        out = [None] * len(_lib.FUSION_GRAD_FIELDS)
+        late = [f.fusion[i].weight for i in (0, 3, 6)] + [f.fusion[i].bias for i in (0, 3, 6)]
+    heads = runner.heads
+    if heads is not None:
+        out += [h[0].weight for h in heads] + [h[0].bias for h in heads] + [h[3].weight for h in heads] + [h[3].bias for h in heads]
+    else:
+        out += [None] * 16
+    return out + late
 
 
 def _fusion_grads_struct(grads):
     g = _lib.FusionGrads()
     it = iter(grads)
+    dp = lambda t: t.data_ptr() if t is not None else None
     for name in _lib.FUSION_GRAD_FIELDS:
-        t = next(it)
-        setattr(g, name, t.data_ptr() if t is not None else None)
+        setattr(g, name, dp(next(it)))
     for arr in (g.head_w1, g.head_b1, g.head_w2, g.head_b2):
         for k in range(4):
-            arr[k] = next(it).data_ptr()
+            arr[k] = dp(next(it))
+    for arr in (g.late_w, g.late_b):
+        for k in range(3):
+            arr[k] = dp(next(it))
     return g
 
 
@@ -177,11 +190,12 @@ def _fusion_dropout_struct(masks, p):
 
 
 class FusionTrainFunction(torch.autograd.Function):
-    """``(fused, mask_out, instance_out, edge_out, score_out) = f(det, rg_rows, node_ptr, G, kg, masks, *params)``;
-    differentiable in ``rg_rows``, ``kg`` and the parameters."""
+    """``(fused[, mask_out, instance_out, edge_out, score_out]) = f(runner, p_drop, rg_rows, node_ptr, G, kg, masks,
+    *params)``; differentiable in ``rg_rows``, ``kg`` and the parameters.  ``runner``: the ``_FusionRunner`` of a
+    detector (five outputs) or of a bare fusion module (``fused`` only); either fusion type."""
 
     @staticmethod
-    def forward(ctx, det, rg_rows, node_ptr, n_graphs, kg, masks, *params):
+    def forward(ctx, runner, p_drop, rg_rows, node_ptr, n_graphs, kg, masks, *params):
         lib = _lib.load()
         _lib.require_cuda(rg_rows, "rg_embeddings")
         _lib.require_cuda(kg, "kg_embeddings")
@@ -190,61 +204,80 @@ class FusionTrainFunction(torch.autograd.Function):
         G, M, K = int(n_graphs), rg_rows.shape[0], kg.shape[1]
         if kg.shape[0] != G:
             raise RuntimeError(f"training step needs one KG copy per image: kg has {kg.shape[0]} graphs, batch has {G}")
-        s, keep = det._runner.params()
-        drop = _fusion_dropout_struct(masks, det.dropout_p)
+        s, keep = runner.params()
+        drop = _fusion_dropout_struct(masks, p_drop)
         ws_bytes = lib.cm_fusion_train_workspace_bytes(C.byref(s), G, M, K)
         if ws_bytes == 0:
             raise ValueError("cm_fusion_train_workspace_bytes: " + lib.cm_last_error().decode())
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         f32 = dict(dtype=torch.float32, device=dev)
         c = s.num_classes
-        fused = torch.empty((G, s.hidden), **f32)
-        outs = [torch.empty((G, c), **f32), torch.empty((G, c), **f32), torch.empty((G, 1), **f32), torch.empty((G, 1), **f32)]
+        final = s.hidden if s.fusion_type == 0 else s.hidden // 2
+        fused = torch.empty((G, final), **f32)
+        has_heads = runner.heads is not None
+        outs = ([torch.empty((G, c), **f32), torch.empty((G, c), **f32), torch.empty((G, 1), **f32), torch.empty((G, 1), **f32)]
+                if has_heads else [None] * 4)
         p = _lib.ptr
         _lib.check(lib.cm_fusion_train_forward(C.byref(s), p(rg_rows), p(node_ptr), G, M, p(kg), K, C.byref(drop), p(ws), ws_bytes,
                                                p(fused), p(outs[0]), p(outs[1]), p(outs[2]), p(outs[3]), _lib.stream_ptr(dev)),
                    "cm_fusion_train_forward")
-        ctx.det, ctx.masks, ctx.dims = det, masks, (G, M, K)
+        ctx.runner, ctx.p_drop, ctx.masks, ctx.dims, ctx.has_heads = runner, p_drop, masks, (G, M, K), has_heads
         ctx.held = (rg_rows, node_ptr, kg, ws, keep, [None if t is None else _lib.f32c(t) for t in params])
-        return (fused, *outs)
+        return (fused, *outs) if has_heads else fused
 
     @staticmethod
-    def backward(ctx, d_fused, d_mask, d_inst, d_edge, d_score):
+    def backward(ctx, d_fused, *d_heads):
         lib = _lib.load()
-        det = ctx.det
         rg_rows, node_ptr, kg, ws, keep, held = ctx.held
         G, M, K = ctx.dims
         dev = rg_rows.device
-        s, keep2 = det._runner.params()
-        drop = _fusion_dropout_struct(ctx.masks, det.dropout_p)
+        s, keep2 = ctx.runner.params()
+        drop = _fusion_dropout_struct(ctx.masks, ctx.p_drop)
         grads = [None if t is None else torch.empty_like(t) for t in held]
         g = _fusion_grads_struct(grads)
-        ds = [None if d is None else _lib.f32c(d) for d in (d_fused, d_mask, d_inst, d_edge, d_score)]
-        d_rg = torch.empty_like(rg_rows) if ctx.needs_input_grad[1] else None
-        d_kg = torch.empty_like(kg) if ctx.needs_input_grad[4] else None
+        d_heads = tuple(d_heads) + (None,) * (4 - len(d_heads))
+        ds = [None if d is None else _lib.f32c(d) for d in (d_fused, *d_heads)]
+        d_rg = torch.empty_like(rg_rows) if ctx.needs_input_grad[2] else None
+        d_kg = torch.empty_like(kg) if ctx.needs_input_grad[5] else None
         p = _lib.ptr
         _lib.check(lib.cm_fusion_backward(C.byref(s), p(rg_rows), p(node_ptr), G, M, p(kg), K, C.byref(drop), p(ws), ws.numel(),
                                           p(ds[0]), p(ds[1]), p(ds[2]), p(ds[3]), p(ds[4]), C.byref(g), p(d_rg), p(d_kg),
                                           _lib.stream_ptr(dev)), "cm_fusion_backward")
-        return (None, d_rg, None, None, d_kg, None) + tuple(grads)
+        return (None, None, d_rg, None, None, d_kg, None) + tuple(grads)
+
+
+def fusion_dropout_masks(runner, p_drop, G, M, K, device):
+    """Fresh keep masks (uint8) for every dropout site of the module behind ``runner`` (``None`` when p = 0): cross
+    attention -- attention rg->kg [M,H,K], FFN_rg [M,2D], attention kg->rg [H,K,M], FFN_kg [G*K,2D], fusion MLP [G,D],
+    four head hidden layers [G,D/2]; late -- [G,D], [G,D/2], then the four head hidden layers [G,D/4] at 5..8."""
+    if p_drop <= 0:
+        return None
+    from .fusion_model import CrossAttentionFusion
+    f = runner.fusion
+    D = f.hidden_dim
+    if isinstance(f, CrossAttentionFusion):
+        H = f.cross_attn_rg2kg.num_heads
+        shapes = [(M, H, K), (M, 2 * D), (H, K, M), (G * K, 2 * D), (G, D)] + [(G, D // 2)] * 4
+    else:
+        shapes = [(G, D), (G, D // 2), None, None, None] + [(G, D // 4)] * 4
+    if runner.heads is None:
+        shapes = shapes[:5] + [None] * 4
+    return [None if sh is None else (torch.rand(sh, device=device) >= p_drop).to(torch.uint8) for sh in shapes]
 
 
 def fusion_train_forward(det, rg_rows, node_ptr, n_graphs, kg, masks="auto"):
-    """Training-mode detector forward on a ragged batch; returns ``(fused, mask, instance, edge, score)``."""
+    """Training-mode forward on a ragged batch of a detector -> ``(fused, mask, instance, edge, score)``, or of a bare
+    fusion module (``CrossAttentionFusion`` / ``LateFusion``) -> ``fused``."""
+    runner = det._runner
     G, M, K = int(n_graphs), rg_rows.shape[0], kg.shape[1]
     if kg.shape[0] == 1 and G > 1:
         kg = kg.expand(G, -1, -1)
     kg = kg.contiguous()
     p_drop = det.dropout_p
     if masks == "auto":
-        masks = None
-        if p_drop > 0:
-            D, H = det.fusion.hidden_dim, det.fusion.cross_attn_rg2kg.num_heads
-            dev = rg_rows.device
-            shapes = [(M, H, K), (M, 2 * D), (H, K, M), (G * K, 2 * D), (G, D)] + [(G, D // 2)] * 4
-            masks = [(torch.rand(sh, device=dev) >= p_drop).to(torch.uint8) for sh in shapes]
-    params = _fusion_param_list(det)
-    return FusionTrainFunction.apply(det, rg_rows, node_ptr, G, kg, masks, *params)
+        masks = fusion_dropout_masks(runner, p_drop, G, M, K, rg_rows.device)
+    params = _fusion_param_list(runner)
+    return FusionTrainFunction.apply(runner, p_drop, rg_rows, node_ptr, G, kg, masks, *params)
 
 
 # ------------------------------------------------------------------------------------------------ data parallel

@@ -280,7 +280,8 @@ typedef struct cm_fusion_grads { /* one buffer per trainable tensor of cm_fusion
     float *ffn_rg_w1, *ffn_rg_b1, *ffn_rg_w2, *ffn_rg_b2;
     float *ffn_kg_w1, *ffn_kg_b1, *ffn_kg_w2, *ffn_kg_b2;
     float *fl_w1, *fl_b1, *fl_w2, *fl_b2;
-    float *head_w1[4], *head_b1[4], *head_w2[4], *head_b2[4];
+    float *head_w1[4], *head_b1[4], *head_w2[4], *head_b2[4];   /* NULL-able together with cm_fusion_params' heads */
+    float *late_w[3], *late_b[3];                                /* fusion_type 1 (LateFusion) */
 } cm_fusion_grads;
 size_t cm_fusion_train_workspace_bytes(const cm_fusion_params* p, int n_graphs, int n_rows, int n_kg);
 int cm_fusion_train_forward(const cm_fusion_params* p, const float* rg, const int32_t* node_ptr, int n_graphs, int n_rows,

@@ -84,15 +84,17 @@ def cross_attention_fusion(p, rg, kg, heads=8, prefix="fusion.", drop=None, pdro
     return fused, {"rg2kg": w_rk, "kg2rg": w_kr}
 
 
-def late_fusion(p, rg, kg, prefix="fusion."):
-    """fusion_model.py:164-171: mean over nodes if 3-D, concat, Linear-ReLU-Linear-ReLU-Linear (0, 3, 6)."""
+def late_fusion(p, rg, kg, prefix="fusion.", drop=None, pdrop=0.0):
+    """fusion_model.py:164-171: mean over nodes if 3-D, concat, Linear-ReLU-Linear-ReLU-Linear (0, 3, 6).  ``drop``
+    (training parity only): keep masks ``late_0`` [B,D] and ``late_1`` [B,D/2] of the two nn.Dropout sites (2, 5)."""
+    dk = (lambda name: None) if drop is None else drop.get
     if rg.dim() == 3:
         rg = rg.mean(dim=1)
     if kg.dim() == 3:
         kg = kg.mean(dim=1)
     x = torch.cat([rg, kg], dim=-1)
-    x = F.relu(F.linear(x, p[prefix + "fusion.0.weight"], p[prefix + "fusion.0.bias"]))
-    x = F.relu(F.linear(x, p[prefix + "fusion.3.weight"], p[prefix + "fusion.3.bias"]))
+    x = _drop(F.relu(F.linear(x, p[prefix + "fusion.0.weight"], p[prefix + "fusion.0.bias"])), dk("late_0"), pdrop)
+    x = _drop(F.relu(F.linear(x, p[prefix + "fusion.3.weight"], p[prefix + "fusion.3.bias"])), dk("late_1"), pdrop)
     return F.linear(x, p[prefix + "fusion.6.weight"], p[prefix + "fusion.6.bias"]), None
 
 
@@ -102,7 +104,7 @@ def detector_forward(p, rg, kg, heads=8, fusion_type="cross_attention", drop=Non
     if fusion_type == "cross_attention":
         fused, attn = cross_attention_fusion(p, rg, kg, heads, drop=drop, pdrop=pdrop)
     elif fusion_type == "late":
-        fused, attn = late_fusion(p, rg, kg)
+        fused, attn = late_fusion(p, rg, kg, drop=drop, pdrop=pdrop)
     else:
         raise ValueError(f"Unknown fusion_type: {fusion_type}")
     dk = (lambda name: None) if drop is None else drop.get

@@ -318,3 +318,100 @@ def test_fusion_train_step_with_all_nine_dropout_masks():
         if np.abs(got - ref).max() > tol:
             bad[name] = np.abs(got - ref).max() / tol
     assert not bad, f"gradient mismatch (error / tolerance): {bad}"
+
+
+def _grad_check(named, og, rel=3e-4):
+    bad = {}
+    for name, prm in named.items():
+        ref = og[name].numpy()
+        got = prm.grad.detach().cpu().numpy().astype(np.float64)
+        tol = rel * np.abs(ref).max() + 1e-6
+        if np.abs(got - ref).max() > tol:
+            bad[name] = np.abs(got - ref).max() / tol
+    assert not bad, f"gradient mismatch (error / tolerance): {bad}"
+
+
+def test_late_fusion_detector_trains():
+    """fusion_type='late' (configs/multimodal_config.yaml: fusion_type) under model.train(): forward with explicit
+    dropout masks on both nn.Dropout sites + the four heads, gradients against float64 autograd over the oracle."""
+    from camouflage_multimodal_b200 import training
+    from oracle import fusion as ofus
+    det = _detector(4, fusion_type="late").train()
+    pd = det.dropout_p
+    gen = torch.Generator().manual_seed(31)
+    sizes = [37, 90, 5]
+    M, G, K, D = sum(sizes), 3, 13, 256
+    rows = (torch.randn((M, 128), generator=gen).clamp_min(0) * 0.5).cuda().requires_grad_(True)
+    kg = (torch.randn((K, 128), generator=gen).clamp_min(0) * 0.25).cuda()
+    node_ptr = torch.tensor([0, 37, 127, 132], dtype=torch.int32, device="cuda")
+    shapes = [(G, D), (G, D // 2), None, None, None] + [(G, D // 4)] * 4
+    masks = [None if sh is None else (torch.rand(sh, generator=gen) >= pd).to(torch.uint8).cuda() for sh in shapes]
+    tg = (torch.tensor([1, 0, 1]), torch.tensor([0, 1, 1]), torch.tensor([1.0, 0.0, 1.0]), torch.tensor([0.0, 1.0, 0.5]))
+    fused, *outs = training.fusion_train_forward(det, rows, node_ptr, G, kg[None], masks=masks)
+    assert fused.shape == (G, D // 2)
+    loss = _fusion_loss(*outs, *[t.cuda() for t in tg])
+    loss.backward()
+    sd = {k: v.detach().cpu().double().requires_grad_(True) for k, v in det.state_dict().items()}
+    rg = rows.detach().cpu().double().requires_grad_(True)
+    mk = [None if m is None else m.cpu() for m in masks]
+    ptr = node_ptr.cpu().tolist()
+    res = []
+    for g in range(G):
+        drop = {"late_0": mk[0][g][None], "late_1": mk[1][g][None], "mask_head": mk[5][g][None], "instance_head": mk[6][g][None],
+                "edge_head": mk[7][g][None], "score_head": mk[8][g][None]}
+        res.append(ofus.detector_forward(sd, rg[ptr[g]:ptr[g + 1]][None], kg.cpu().double()[None], fusion_type="late", drop=drop, pdrop=pd))
+    ocat = [torch.cat([r[j] for r in res]) for j in range(4)]
+    _fusion_loss(*ocat, *tg).backward()
+    for got, ref in zip(outs, ocat):
+        np.testing.assert_allclose(got.detach().cpu().numpy(), ref.detach().numpy(), rtol=0, atol=1e-4)
+    named = dict(det.named_parameters())
+    named["<rg rows>"] = rows
+    og = {k: v.grad for k, v in sd.items()}
+    og["<rg rows>"] = rg.grad
+    _grad_check(named, og)
+    # the module-level forward (reference signature) trains too and draws its own masks
+    det.zero_grad()
+    out = det(rows.detach().view(1, M, 128), kg[None])
+    assert len(out) == 4 and out[0].requires_grad
+    out[0].sum().backward()
+    assert det.fusion.fusion[0].weight.grad.abs().sum() > 0
+
+
+@pytest.mark.parametrize("kind", ["cross_attention", "late"])
+def test_standalone_fusion_modules_train(kind):
+    """CrossAttentionFusion / LateFusion on their own (fusion_model.py:16-171 are ordinary trainable modules): train-mode
+    forward returns a differentiable ``fused``; dropout off -> gradients against float64 autograd over the oracle."""
+    from camouflage_multimodal_b200.fusion_model import CrossAttentionFusion, LateFusion
+    from oracle import fusion as ofus
+    torch.manual_seed(12)
+    mod = (CrossAttentionFusion(128, 128, 256, 8, dropout=0.0) if kind == "cross_attention" else LateFusion(128, 128, 256, dropout=0.0)).cuda().train()
+    gen = torch.Generator().manual_seed(4)
+    B, N, K = 2, 50, 13
+    rg = (torch.randn((B, N, 128), generator=gen).clamp_min(0) * 0.5).cuda().requires_grad_(True)
+    kg = (torch.randn((B, K, 128), generator=gen).clamp_min(0) * 0.25).cuda().requires_grad_(True)
+    fused, attn = mod(rg, kg)
+    w = torch.randn(fused.shape, generator=gen).cuda()
+    (fused * w).sum().backward()
+    sd = {"fusion." + k: v.detach().cpu().double().requires_grad_(True) for k, v in mod.state_dict().items()}
+    rgo, kgo = rg.detach().cpu().double().requires_grad_(True), kg.detach().cpu().double().requires_grad_(True)
+    if kind == "cross_attention":
+        f_ref, a_ref = ofus.cross_attention_fusion(sd, rgo, kgo, 8)
+        assert attn["rg2kg"].shape == (B, N, K) and not attn["rg2kg"].requires_grad
+        np.testing.assert_allclose(attn["rg2kg"].cpu().numpy(), a_ref["rg2kg"].detach().numpy(), rtol=0, atol=1e-3)
+    else:
+        f_ref, _ = ofus.late_fusion(sd, rgo, kgo)
+        assert attn is None
+    (f_ref * w.cpu().double()).sum().backward()
+    np.testing.assert_allclose(fused.detach().cpu().numpy(), f_ref.detach().numpy(), rtol=0, atol=2e-4)
+    named = {"fusion." + k: v for k, v in mod.named_parameters()}
+    named["<rg>"], named["<kg>"] = rg, kg
+    og = {k: v.grad for k, v in sd.items()}
+    og["<rg>"], og["<kg>"] = rgo.grad, kgo.grad
+    _grad_check(named, og)
+    # with dropout on, the forward still runs and differs from the eval output
+    mod.dropout_p = 0.3
+    f2, _ = mod(rg.detach(), kg.detach())
+    mod.eval()
+    with torch.no_grad():
+        f3, _ = mod(rg.detach(), kg.detach())
+    assert torch.isfinite(f2).all() and (f2 - f3).abs().max() > 1e-4
