@@ -115,6 +115,7 @@ SIGNATURES = {
     "cm_gnn_forward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _fp, _i, _fp, _sz,
                             _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_gnn_train_workspace_bytes": (_sz, [C.POINTER(GnnParams), _i, _i]),
+    "cm_set_bn_sync": (_i, [C.c_void_p, _fp, _fp, _i]),
     "cm_gnn_train_forward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _i, _i, C.POINTER(GnnDropout), _fp, _sz,
                                   _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_gnn_backward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _i, _i, C.POINTER(GnnDropout), _fp, _sz,
@@ -147,6 +148,8 @@ SIGNATURES = {
     "cm_image_loss": (_i, [_fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, C.POINTER(ImageLossConfig), _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_adamw_step": (_i, [_fp, _fp, _fp, _fp, _fp, _i, _i64, C.POINTER(AdamWConfig), _i, _fp, _fp, _fp]),
 }
+
+BN_SYNC_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_void_p)
 
 _lib = None
 

@@ -20,6 +20,7 @@ struct GnnTrainWs {
     float *asrc, *adst, *gmax, *gden, *z;
     float *y[4], *a[4], *g[3], *dis, *e, *t[3];
     float *mean, *invstd;   // [4][H]
+    double *bn_sums, *bn_n;  // [2H + 1] column sums (+ row count) of the layer in flight; [4] global row count per layer
     int* rev;
     // backward scratch
     float *dA, *dB, *dT, *dz, *dpre_edge, *dpre_self, *dasrc, *dadst, *du, *dwf, *s1, *s2;
@@ -51,6 +52,8 @@ static GnnTrainWs carve_gnn_train(void* ws, const cm_gnn_params* p, int n, int e
     for (int k = 0; k < 3; ++k) w.t[k] = c.take<float>(N * H2);
     w.mean = c.take<float>(4 * H);
     w.invstd = c.take<float>(4 * H);
+    w.bn_sums = c.take<double>(2 * H + 1);
+    w.bn_n = c.take<double>(4);
     w.rev = c.take<int>(E);
     w.dA = c.take<float>(N * H);
     w.dB = c.take<float>(N * H);
@@ -320,6 +323,25 @@ __global__ void __launch_bounds__(256) gcn_agg_train_kernel(const float* __restr
     }
 }
 
+// ---------------------------------------------------------------- data-parallel BatchNorm hook
+// One process per GPU: when set, every BatchNorm layer's column sums are copied to `buf`, the hook is called (the host
+// all-reduces buf[0..count) over the ranks ON THE GIVEN STREAM) and the statistics are taken from the reduced sums.
+static cm_bn_sync_fn g_bn_sync = nullptr;
+static void* g_bn_sync_user = nullptr;
+static double* g_bn_sync_buf = nullptr;
+static int g_bn_sync_cap = 0;
+static int bn_sync(double* sums, int count, cudaStream_t st) {
+    if (!g_bn_sync) return CM_OK;
+    if (count > g_bn_sync_cap) {
+        set_error("BatchNorm sync buffer holds %d doubles, layer needs %d", g_bn_sync_cap, count);
+        return CM_ERR_ARG;
+    }
+    cudaMemcpyAsync(g_bn_sync_buf, sums, sizeof(double) * count, cudaMemcpyDeviceToDevice, st);
+    g_bn_sync(g_bn_sync_user, count, (void*)st);
+    cudaMemcpyAsync(sums, g_bn_sync_buf, sizeof(double) * count, cudaMemcpyDeviceToDevice, st);
+    return CM_OK;
+}
+
 // ---------------------------------------------------------------- BatchNorm (batch statistics) + ReLU + dropout
 constexpr int BN_ROWS = 64;
 __global__ void bn_fwd_part_kernel(const float* __restrict__ y, int n, int H, double* __restrict__ part) {
@@ -335,17 +357,28 @@ __global__ void bn_fwd_part_kernel(const float* __restrict__ y, int n, int H, do
     part[((size_t)blockIdx.x * 2) * H + c] = s;
     part[((size_t)blockIdx.x * 2 + 1) * H + c] = q;
 }
-__global__ void bn_fwd_final_kernel(const double* __restrict__ part, int parts, int n, int H, float eps, float* __restrict__ mean,
-                                    float* __restrict__ invstd, float* __restrict__ batch_mean, float* __restrict__ batch_var) {
+// sums [2H + 1] = column sums of the parts (fixed order) and, in the last slot, the number of rows
+__global__ void bn_reduce_parts_kernel(const double* __restrict__ part, int parts, int n, int H, double* __restrict__ sums) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c == 0) sums[2 * H] = (double)n;
     if (c >= H) return;
     double s = 0.0, q = 0.0;
     for (int p = 0; p < parts; ++p) {
         s += part[((size_t)p * 2) * H + c];
         q += part[((size_t)p * 2 + 1) * H + c];
     }
-    const double m = s / n;
-    double v = q / n - m * m;   // biased variance (BatchNorm1d training normalisation)
+    sums[c] = s;
+    sums[H + c] = q;
+}
+// sums = (sum x, sum x^2, n) of ALL rows of the batch -- this rank's, or every rank's after the data-parallel hook
+__global__ void bn_fwd_final_kernel(const double* __restrict__ sums, int H, float eps, float* __restrict__ mean, float* __restrict__ invstd,
+                                    float* __restrict__ batch_mean, float* __restrict__ batch_var, double* __restrict__ n_out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= H) return;
+    const double n = sums[2 * H];
+    if (c == 0) *n_out = n;
+    const double m = sums[c] / n;
+    double v = sums[H + c] / n - m * m;   // biased variance (BatchNorm1d training normalisation)
     v = v > 0.0 ? v : 0.0;
     mean[c] = (float)m;
     invstd[c] = (float)(1.0 / sqrt(v + (double)eps));
@@ -384,19 +417,21 @@ __global__ void bn_bwd_part_kernel(const float* __restrict__ y, const float* __r
     part[((size_t)blockIdx.x * 2) * H + c] = s;
     part[((size_t)blockIdx.x * 2 + 1) * H + c] = q;
 }
-__global__ void bn_bwd_final_kernel(const double* __restrict__ part, int parts, int n, int H, float* __restrict__ dgamma,
-                                    float* __restrict__ dbeta, float* __restrict__ s1, float* __restrict__ s2) {
+// dgamma / dbeta are THIS rank's sums (the gradient all-reduce adds the ranks up like every other gradient)
+__global__ void bn_bwd_grads_kernel(const double* __restrict__ sums, int H, float* __restrict__ dgamma, float* __restrict__ dbeta) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= H) return;
-    double s = 0.0, q = 0.0;
-    for (int p = 0; p < parts; ++p) {
-        s += part[((size_t)p * 2) * H + c];
-        q += part[((size_t)p * 2 + 1) * H + c];
-    }
-    dbeta[c] = (float)s;
-    dgamma[c] = (float)q;
-    s1[c] = (float)(s / n);
-    s2[c] = (float)(q / n);
+    dbeta[c] = (float)sums[c];
+    dgamma[c] = (float)sums[H + c];
+}
+// s1, s2 = the two batch means of the BatchNorm backward over ALL rows (after the data-parallel hook: every rank's)
+__global__ void bn_bwd_final_kernel(const double* __restrict__ sums, const double* __restrict__ n_glob, int H, float* __restrict__ s1,
+                                    float* __restrict__ s2) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= H) return;
+    const double n = *n_glob;
+    s1[c] = (float)(sums[c] / n);
+    s2[c] = (float)(sums[H + c] / n);
 }
 __global__ void bn_bwd_apply_kernel(const float* __restrict__ y, const float* __restrict__ mean, const float* __restrict__ invstd,
                                     const float* __restrict__ gamma, const float* __restrict__ dpre, const float* __restrict__ s1,
@@ -446,6 +481,18 @@ static int check_train_params(const cm_gnn_params* p, const char* who) {
 }
 
 }  // namespace cm
+
+extern "C" int cm_set_bn_sync(cm_bn_sync_fn fn, void* user, double* device_buf, int capacity) {
+    if (fn && (!device_buf || capacity <= 0)) {
+        cm::set_error("cm_set_bn_sync: a hook needs a device buffer");
+        return CM_ERR_ARG;
+    }
+    cm::g_bn_sync = fn;
+    cm::g_bn_sync_user = user;
+    cm::g_bn_sync_buf = fn ? device_buf : nullptr;
+    cm::g_bn_sync_cap = fn ? capacity : 0;
+    return CM_OK;
+}
 
 extern "C" size_t cm_gnn_train_workspace_bytes(const cm_gnn_params* p, int n_nodes, int n_edges) {
     if (!p || n_nodes < 0 || n_edges < 0 || cm::check_train_params(p, "cm_gnn_train_workspace_bytes") != CM_OK) return 0;
@@ -505,9 +552,11 @@ extern "C" int cm_gnn_train_forward(const cm_gnn_params* p, const float* x, cons
         {
             CM_TIMED("train_bn", st);
             bn_fwd_part_kernel<<<dim3(parts, ceil_div(H, 128)), 128, 0, st>>>(w.y[k], N, H, w.part_d);
-            bn_fwd_final_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.part_d, parts, N, H, p->bn_eps, w.mean + k * H, w.invstd + k * H,
+            bn_reduce_parts_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.part_d, parts, N, H, w.bn_sums);
+            if (int rc = bn_sync(w.bn_sums, 2 * H + 1, st)) return rc;   // data parallel: (sum x, sum x^2, n) over every rank's nodes
+            bn_fwd_final_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, H, p->bn_eps, w.mean + k * H, w.invstd + k * H,
                                                                   bn_batch_mean ? bn_batch_mean + k * H : nullptr,
-                                                                  bn_batch_var ? bn_batch_var + k * H : nullptr);
+                                                                  bn_batch_var ? bn_batch_var + k * H : nullptr, w.bn_n + k);
             bn_fwd_apply_kernel<<<ceil_div(NH, 256), 256, 0, st>>>(w.y[k], w.mean + k * H, w.invstd + k * H, p->bn_weight[k], p->bn_bias[k],
                                                                    k < 3 ? drop_keep(drop, k) : nullptr, k < 3 ? drop_scale(drop, k) : 1.f,
                                                                    NH, H, w.a[k]);
@@ -593,7 +642,10 @@ extern "C" int cm_gnn_backward(const cm_gnn_params* p, const float* x, const int
             bn_bwd_part_kernel<<<dim3(parts, ceil_div(H, 128)), 128, 0, st>>>(w.y[k], w.mean + k * H, w.invstd + k * H, p->bn_weight[k],
                                                                               p->bn_bias[k], k < 3 ? drop_keep(drop, k) : nullptr,
                                                                               k < 3 ? drop_scale(drop, k) : 1.f, dcur, N, H, w.part_d);
-            bn_bwd_final_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.part_d, parts, N, H, gr->bn_weight[k], gr->bn_bias[k], w.s1, w.s2);
+            bn_reduce_parts_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.part_d, parts, N, H, w.bn_sums);
+            bn_bwd_grads_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, H, gr->bn_weight[k], gr->bn_bias[k]);
+            if (int rc = bn_sync(w.bn_sums, 2 * H, st)) return rc;       // (sum dy, sum dy xhat) over every rank's nodes
+            bn_bwd_final_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, w.bn_n + k, H, w.s1, w.s2);
             bn_bwd_apply_kernel<<<ceil_div(NH, 256), 256, 0, st>>>(w.y[k], w.mean + k * H, w.invstd + k * H, p->bn_weight[k], dcur, w.s1, w.s2,
                                                                    NH, H, dtmp);
         }

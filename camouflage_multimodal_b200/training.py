@@ -86,7 +86,11 @@ class GnnTrainFunction(torch.autograd.Function):
                                             p(status), _lib.stream_ptr(dev)), "cm_gnn_train_forward")
         ctx.model, ctx.n_edges, ctx.masks = model, n_edges, masks
         ctx.held = (x, row_ptr, col, w, self_w, ws, keep, held, status)
-        update_bn_running_stats(model, bmean, bvar, n)
+        sync = BatchNormSync.active
+        if sync is not None:
+            sync.raise_pending()
+        # running statistics use the number of rows the statistics were taken over: every rank's under BatchNormSync
+        update_bn_running_stats(model, bmean, bvar, sync.global_rows(h) if sync is not None else n)
         return mask_out, inst_out, edge_out, emb
 
     @staticmethod
@@ -106,6 +110,8 @@ class GnnTrainFunction(torch.autograd.Function):
         _lib.check(lib.cm_gnn_backward(C.byref(s), p(x), p(row_ptr), p(col), p(w), p(self_w), x.shape[0], ctx.n_edges,
                                        C.byref(drop), p(ws), ws.numel(), p(ds[0]), p(ds[1]), p(ds[2]), p(ds[3]), C.byref(g),
                                        _lib.stream_ptr(dev)), "cm_gnn_backward")
+        if BatchNormSync.active is not None:
+            BatchNormSync.active.raise_pending()
         return (None,) * 8 + tuple(grads)
 
 
@@ -130,12 +136,78 @@ def gnn_train_forward(model, data):
 
 
 def update_bn_running_stats(model, batch_mean, batch_var, n):
+    """``nn.BatchNorm1d``'s running-statistics update (momentum 0.1, unbiased variance).  ``n``: rows the batch statistics
+    were taken over -- a Python int, or a 0-dim device tensor (the all-reduced row count under ``BatchNormSync``)."""
     with torch.no_grad():
+        if torch.is_tensor(n):
+            n = n.to(torch.float32)
+            unbias = n / torch.clamp(n - 1, min=1)
+        else:
+            unbias = n / max(n - 1, 1)
         for k, bn in enumerate((model.bn1, model.bn2, model.bn3, model.bn4)):
             m = bn.momentum if bn.momentum is not None else 0.1
             bn.running_mean.mul_(1 - m).add_(batch_mean[k], alpha=m)
-            bn.running_var.mul_(1 - m).add_(batch_var[k] * (n / max(n - 1, 1)), alpha=m)
+            bn.running_var.mul_(1 - m).add_(batch_var[k] * unbias * m)
             bn.num_batches_tracked += 1
+
+
+def allreduce_bn_sums(sums: torch.Tensor, group=None):
+    """SUM-all-reduce of a BatchNorm statistics vector -- ``(sum x [H], sum x^2 [H], n)`` in the forward, ``(sum dy [H],
+    sum dy*xhat [H])`` in the backward, float64 -- over the ranks, in place.  The per-layer exchange that makes a sharded
+    batch normalise like the single-process reference (``Batch.from_data_list`` + BatchNorm over all nodes, train.py:231,
+    241-250).  No-op without an initialised process group."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    return sums
+
+
+class BatchNormSync:
+    """Installs the library's data-parallel BatchNorm hook (``cm_set_bn_sync``) for the current process: while active,
+    every BatchNorm layer of ``cm_gnn_train_forward`` / ``cm_gnn_backward`` hands its float64 column sums to ``reduce``
+    (default ``allreduce_bn_sums``: one small NCCL all-reduce per layer and direction, on the launching stream) and
+    normalises with the reduced sums, so N ranks with B/N images each compute exactly what one process computes on B
+    images.  Use as a context manager around the training step, or ``install()`` / ``remove()``.  One per process."""
+    active = None
+
+    def __init__(self, device, hidden: int = 128, reduce=None, group=None):
+        self.buf = torch.zeros(2 * hidden + 1, dtype=torch.float64, device=device)
+        self.reduce = reduce if reduce is not None else (lambda t: allreduce_bn_sums(t, group))
+        self._pending = None
+        self._cb = _lib.BN_SYNC_FN(self._call)          # keeps the trampoline alive as long as the object lives
+        self.calls = 0
+
+    def _call(self, _user, count, _stream):
+        try:   # the library has queued the copy into self.buf on torch's current stream of this device
+            self.calls += 1
+            self.reduce(self.buf[:count])
+        except BaseException as e:   # noqa: BLE001 -- a ctypes callback cannot propagate: re-raised after the library call
+            self._pending = e
+
+    def raise_pending(self):
+        e, self._pending = self._pending, None
+        if e is not None:
+            raise e
+
+    def global_rows(self, hidden):
+        """0-dim device tensor: the all-reduced row count of the last forward."""
+        return self.buf[2 * hidden].clone()
+
+    def install(self):
+        _lib.check(_lib.load().cm_set_bn_sync(C.cast(self._cb, C.c_void_p), None, _lib.ptr(self.buf), self.buf.numel()), "cm_set_bn_sync")
+        BatchNormSync.active = self
+        return self
+
+    def remove(self):
+        _lib.check(_lib.load().cm_set_bn_sync(None, None, None, 0), "cm_set_bn_sync")
+        if BatchNormSync.active is self:
+            BatchNormSync.active = None
+
+    __enter__ = install
+
+    def __exit__(self, *exc):
+        self.remove()
+        return False
 
 
 # ------------------------------------------------------------------------------------------------ fusion

@@ -192,6 +192,15 @@ typedef struct cm_gnn_grads { /* one buffer per trainable tensor of cm_gnn_param
     float *head1_weight[3], *head1_bias[3], *head2_weight[3], *head2_bias[3];
 } cm_gnn_grads;
 size_t cm_gnn_train_workspace_bytes(const cm_gnn_params* p, int n_nodes, int n_edges);
+/* Data-parallel BatchNorm: the reference normalises over ALL nodes of the batch (train.py:231,241-250), so
+ * when the batch is sharded over ranks every BatchNorm layer must see every rank's (sum x, sum x^2, n), and its backward
+ * every rank's (sum dy, sum dy xhat).  With a hook set, cm_gnn_train_forward / cm_gnn_backward copy those column sums
+ * (float64, 2 * hidden + 1 / 2 * hidden values) to device_buf, call fn(user, count, stream) -- the host sums
+ * device_buf[0..count) over the ranks on that stream (ncclAllReduce through torch.distributed) -- and read them back.
+ * bn_weight / bn_bias gradients stay this rank's partial sums (the gradient all-reduce adds them like the rest).
+ * fn == NULL clears the hook (single-process statistics).  One hook per process (one process per GPU). */
+typedef void (*cm_bn_sync_fn)(void* user, int count, void* stream);
+int cm_set_bn_sync(cm_bn_sync_fn fn, void* user, double* device_buf, int capacity);
 /* Outputs: mask_out / instance_out [N,num_classes], edge_out [N,1], node_emb [N,hidden] (optional; the shared
  * embedding after dropout), bn_batch_mean / bn_batch_var [4,hidden] (optional; biased variance). */
 int cm_gnn_train_forward(const cm_gnn_params* p, const float* x, const int32_t* csr_row_ptr, const int32_t* csr_col,

@@ -183,6 +183,45 @@ def test_gradient_allreduce_gloo(tmp_path):
         assert p.returncode == 0, out.decode()
 
 
+_BN_WORKER = r"""
+import sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+rank = int(sys.argv[3])
+dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{sys.argv[2]}", rank=rank, world_size=2)
+from camouflage_multimodal_b200.training import allreduce_bn_sums
+from camouflage_multimodal_b200.pipeline import allreduce_partials
+torch.manual_seed(0)
+x = torch.randn(37, 16, dtype=torch.float64) * 2 + 1          # pre-BatchNorm rows of the whole batch
+mine = x[:15] if rank == 0 else x[15:]                        # uneven shards
+sums = torch.cat([mine.sum(0), (mine * mine).sum(0), torch.tensor([float(mine.shape[0])], dtype=torch.float64)])
+allreduce_bn_sums(sums)
+n = sums[-1]
+mean, var = sums[:16] / n, sums[16:32] / n - (sums[:16] / n) ** 2
+bn = torch.nn.BatchNorm1d(16, momentum=1.0).double().train()  # momentum 1: running stats = this batch's
+bn(x)
+assert n.item() == 37 and torch.allclose(mean, bn.running_mean, atol=1e-12)
+assert torch.allclose(var * n / (n - 1), bn.running_var, atol=1e-12)
+# the S/E/F partial vector rides the same collective as the 15-element one
+part, sod = torch.full((15,), float(rank + 1), dtype=torch.float64), torch.arange(528, dtype=torch.float64) * (rank + 1)
+part, conf, sod = allreduce_partials(part, None, sod)
+assert part.tolist() == [3.0] * 15 and torch.equal(sod, torch.arange(528, dtype=torch.float64) * 3) and conf is None
+dist.destroy_process_group()
+"""
+
+
+def test_batchnorm_sums_allreduce_gloo(tmp_path):
+    """Data-parallel BatchNorm: all-reduced (sum x, sum x^2, n) of uneven shards give the statistics
+    nn.BatchNorm1d takes over the whole batch; the GPU side of the hook is tests/test_gpu_dist_training.py."""
+    script = tmp_path / "b.py"
+    script.write_text(_BN_WORKER)
+    port = str(33500 + os.getpid() % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT) for r in range(2)]
+    for p in procs:
+        out, _ = p.communicate(timeout=240)
+        assert p.returncode == 0, out.decode()
+
+
 def test_embedding_matcher_matches_reference_class_golden():
     """tests/golden/embedding_matcher.json holds the outputs of the reference's own EmbeddingMatcher
     (tools/gen_golden_matcher.py); the mirror must reproduce every category choice, id list and tensor."""
