@@ -8,7 +8,8 @@ images, batch 32 forward + metrics) on N B200s, with the kernel roofline and the
 A step = one batch of 32 images per GPU through: label map -> adjacency/edge list -> 15-d region features ->
 edge weights -> RG-GNN -> RGxKG cross-attention fusion + heads -> pixel-mask paint -> metric reductions.
 Images shard by index across ranks (weak scaling); KG rows and weights are broadcast once; the only
-data-path collective is one all-reduce of the 15-element metric partial-sum vector at the end.
+data-path collective is one all-reduce of the metric partial-sum vectors (15 + 528 float64) at the end of a timed region.
+The line also carries `train`: BASELINE configs[3] (one training step at batch 16 per GPU) measured in the same run.
 """
 from __future__ import annotations
 
@@ -174,16 +175,17 @@ def run_cpu_baseline(gnn_sd, fusion_sd, kg, n_images=6, inp="u8"):
     sample = synth.make_batch(0, n_images, seed=1234)
     if inp == "u8":
         sample = sample.as_decoded().as_float()
-    sec, _ = cpu_path.time_images(sample, gnn_sd, fusion_sd, kg, faithful=True, processes=1)
+    sec, _ = cpu_path.time_images(sample, gnn_sd, fusion_sd, kg, faithful=True, processes=1, sod=True)
     return {"value": n_images / sec, "unit": "images/sec", "cores": 1, "kind": "port",
             "sample": f"{n_images} images of the same synthetic set through the oracle restatement of the reference's "
-                      f"per-image CPU loop (full-frame per-region masks as in extract_rg_embeddings.py:154-211), {sec:.1f} s",
+                      f"per-image CPU loop (full-frame per-region masks as in extract_rg_embeddings.py:154-211) incl. S/E/F-measure, {sec:.1f} s",
             "host_cpus": os.cpu_count(), "torch_threads": torch.get_num_threads()}
 
 
 def reference_arm(args):
     """--impl reference: the reference's CPU implementation of the path (oracle port -- the reference's own
-    files need scikit-image / torch-geometric, which are not installable here) on all host cores."""
+    files need scikit-image / torch-geometric, which are not installable here) on all host cores.  A step is one
+    batch of BATCH = 32 images, exactly as in the B200 arm, spread over one worker process per host core."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -195,47 +197,124 @@ def reference_arm(args):
     gsd, fsd = cpu_state_dicts(gnn, det)
     kg, kg_src = load_kg()
     cores = os.cpu_count() or 1
-    per_step = max(1, min(cores, BATCH))
+    workers = max(1, min(cores, BATCH))
     torch.set_num_threads(1)
-    distinct = min(args.steps + args.warmup, 8)   # steps cycle through 8 distinct samples of the set (bounds host memory)
-    total = distinct * per_step
+    distinct = min(args.steps + args.warmup, 4)   # steps cycle through 4 distinct batches of the set (bounds host memory)
+    total = distinct * BATCH
     data = synth.make_batch(0, total, seed=1234)
     if args.input == "u8":      # the same byte-quantised images the B200 arm receives, as the float array the reference takes
         data = data.as_decoded().as_float()
-    items = [(data.images[i].numpy(), data.labels[i].numpy(), data.canny[i].numpy(), data.gt[i].numpy(), gsd, fsd, kg, True)
+    items = [(data.images[i].numpy(), data.labels[i].numpy(), data.canny[i].numpy(), data.gt[i].numpy(), gsd, fsd, kg, True, True)
              for i in range(total)]
     times = []
-    with mp.get_context("fork").Pool(per_step) as pool:
+    with mp.get_context("fork").Pool(workers) as pool:
         for s in range(args.steps + args.warmup):
             t0 = time.perf_counter()
-            pool.map(cpu_path._worker, items[(s % distinct) * per_step:(s % distinct + 1) * per_step], chunksize=1)
+            pool.map(cpu_path._worker, items[(s % distinct) * BATCH:(s % distinct + 1) * BATCH], chunksize=1)
             dt = time.perf_counter() - t0
             if s >= args.warmup:
                 times.append(dt)
     sec = sum(times)
-    value = args.steps * per_step / sec
-    sample = (f"{per_step} images per step (one per worker process, {cores} host cpus) of the same synthetic set, "
-              f"oracle port of the reference's per-image CPU loop")
+    value = args.steps * BATCH / sec
+    sample = (f"{BATCH} images per step over {workers} worker processes ({cores} host cpus) of the same synthetic set, "
+              f"oracle port of the reference's per-image CPU loop incl. S/E/F-measure")
     emit({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.gpus, kg_src, 0, args.input),
-        "cpu_baseline": {"value": value, "unit": "images/sec", "cores": per_step, "kind": "port", "sample": sample},
+        "config": workload_config(args.gpus, kg_src, args.input, arm={"impl": "reference (CPU port)", "workers": workers, "host_cpus": cores,
+                                                                     "images_per_step": BATCH, "distinct_batches": distinct}),
+        "cpu_baseline": {"value": value, "unit": "images/sec", "cores": workers, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     })
 
 
-def workload_config(n_gpus, kg_src, lanes=1, inp="u8", pool=8, host_cores=0):
+def workload_config(n_gpus, kg_src, inp="u8", arm=None):
+    """The workload, identical for both arms; whatever differs between them (lanes, workers, ...) sits under ``arm``."""
     return {"workload": f"BASELINE configs[1]: synthetic COD10K-test-shaped set ({SET_SIZE} images, 256x256), batch {BATCH} "
-                        f"per GPU: graph build + RG-GNN + RGxKG cross-attention fusion + heads + paint + utils/metrics",
+                        f"per GPU: graph build + RG-GNN + RGxKG cross-attention fusion + heads + paint + utils/metrics + S/E/F-measure",
             "batch_per_gpu": BATCH, "global_batch": BATCH * n_gpus, "regions_per_image": "303-530 (empirical histogram)",
             "kg": kg_src, "parallelism": f"dp{n_gpus} (images sharded i mod N, metric partial sums all-reduced once)",
-            "l2": f"{pool} distinct input batches per GPU ({pool * BATCH * (458752 if inp == 'u8' else 1179648) / 1e6:.0f} MB > 126 MB L2) "
-                  "rotated so every step's inputs come from HBM, not L2",
-            "lanes": lanes, "host_cores_bound": host_cores,
+            "metrics": "utils/metrics.py's 7 keys + S-measure, E-measure, F-measure (beta2 0.3), weighted F (not in the reference)",
             "input": ("uint8 RGB images (value = byte/255) + int16 label maps + uint8 canny + uint8 gt: 458 752 B per image"
-                      if inp == "u8" else "float32 images + int32 label maps + uint8 canny + uint8 gt: 1 179 648 B per image")}
+                      if inp == "u8" else "float32 images + int32 label maps + uint8 canny + uint8 gt: 1 179 648 B per image"),
+            "arm": arm or {}}
+
+
+def train_block(args, dev, world, rank):
+    """BASELINE configs[3]: one training step at batch 16 per GPU -- graph build, per-region targets, RG-GNN forward
+    (batch-statistics BatchNorm, all-reduced over ranks), fusion forward, both criteria, backward through both models,
+    gradient SUM all-reduce, clip + AdamW -- random-init weights, synthetic data.  -> dict for the bench line."""
+    import torch.distributed as dist
+
+    from camouflage_multimodal_b200 import _lib, synth, training
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
+    from camouflage_multimodal_b200.region_graph import RegionGraphGNN, batch_to_data, build_region_graphs
+    from camouflage_multimodal_b200.train_loop import FusedAdamW, MultimodalLoss, RegionGraphLoss, region_targets
+    torch.manual_seed(0)
+    gnn = RegionGraphGNN(15, 128, 2).to(dev).train()
+    det = build_multimodal_model({}).to(dev).train()
+    kg, _ = load_kg()
+    kg = kg.to(dev)
+    if world > 1:
+        for t in list(gnn.state_dict().values()) + list(det.state_dict().values()):
+            dist.broadcast(t, src=0)
+    B = args.train_batch
+    b = synth.make_batch(rank * B, B, seed=1234, device=dev).as_decoded()
+    opt = FusedAdamW(list(gnn.parameters()) + list(det.parameters()), lr=1e-4, weight_decay=1e-4, max_norm=1.0)
+    gen = torch.Generator().manual_seed(rank)
+    img_y = torch.randint(0, 2, (B,), generator=gen).to(dev)
+    edge_y = torch.randint(0, 2, (B,), generator=gen).float().to(dev)
+    score_y = torch.rand((B,), generator=gen).to(dev)
+    rg_loss, mm_loss = RegionGraphLoss(), MultimodalLoss()
+    labels32 = b.labels.to(torch.int32)
+    sync = training.BatchNormSync(dev, 128) if world > 1 else None
+
+    def step():
+        g = build_region_graphs(b.images, labels32, b.canny, label_cap=LABEL_CAP)
+        data = batch_to_data(g)
+        n = data.x.shape[0]
+        y, iy, ey = region_targets(g, labels32, b.gt, b.gt, b.gt)
+
+        def loss_fn(node_outs, res):
+            return (rg_loss(node_outs[0], node_outs[1], node_outs[2], y[:n], iy[:n], ey[:n])
+                    + mm_loss(res["mask_out"], res["instance_out"], res["edge_out"], res["score_out"], img_y, edge_y, score_y))
+
+        return training.joint_train_step(gnn, det, data, g.node_ptr, B, kg[None], loss_fn, optimizer=opt, max_norm=None)
+
+    if sync is not None:
+        sync.install()
+    try:
+        steps = max(3, min(args.steps, 20))
+        for _ in range(max(3, min(args.warmup, 5))):
+            step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            loss = step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        _lib.timing_enable(True)
+        step()
+        torch.cuda.synchronize()
+        rep = _lib.timing_report()
+        _lib.timing_enable(False)
+    finally:
+        if sync is not None:
+            sync.remove()
+    top = sorted(rep.items(), key=lambda kv: -kv[1][1])[:8]
+    return {"workload": f"BASELINE configs[3]: training step, batch {B} per GPU (graph build + targets + fwd/bwd both models + both criteria "
+                        "+ BatchNorm-statistics and gradient all-reduce + clip + AdamW)",
+            "value": steps * B * world / (float(ms.item()) / 1e3), "unit": "images/sec", "ms_per_step": float(ms.item()) / steps,
+            "steps": steps, "batch_per_gpu": B, "n_gpus": world, "loss": float(loss), "launches_per_step": int(sum(v[0] for v in rep.values())),
+            "kernel_ms_per_step": sum(v[1] for v in rep.values()), "bn_sync": sync is not None,
+            "kernels": {k: round(v[1], 4) for k, v in top}}
 
 
 def b200_arm(args):
@@ -287,16 +366,18 @@ def b200_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    from camouflage_multimodal_b200 import metrics as gm
     accs = [torch.zeros(15, dtype=torch.float64, device=dev) for _ in range(lanes)]
-    for pl, a in zip(pipes, accs):
-        pl.total = a           # every step adds its metric partial sums (inside the captured step)
+    accs_sod = [torch.zeros(gm.SOD_PARTIAL, dtype=torch.float64, device=dev) for _ in range(lanes)]
+    for pl, a, a2 in zip(pipes, accs, accs_sod):
+        pl.total, pl.total_sod = a, a2    # every step adds its metric partial sums (inside the captured step)
     graphs = None
     if not args.no_graph:      # one captured step per input batch of the pool (a CUDA graph bakes its pointers in)
         graphs = [pipes[j % lanes].capture(b.images, b.labels, b.canny, b.gt) for j, b in enumerate(pool)]
 
-    def step(s):
+    def step(s, stream=None):
         j = s % n_pool
-        with torch.cuda.stream(lane_streams[j % lanes]):
+        with torch.cuda.stream(stream if stream is not None else lane_streams[j % lanes]):
             if graphs is not None:
                 g, out = graphs[j]
                 g.replay()
@@ -314,40 +395,74 @@ def b200_arm(args):
         for st in lane_streams:
             main.wait_stream(st)
 
-    # warm-up: at least W steps, and enough of them that every captured graph has been replayed a few times (its first
-    # launch uploads it) and the clocks have left idle -- a 20-step timed region is only ~6 ms long
-    n_warm = max(args.warmup, 4 * n_pool, 48)
+    def reduce_partials():
+        total = torch.stack(accs).sum(0)
+        total_sod = torch.stack(accs_sod).sum(0)
+        allreduce_partials(total, None, total_sod)
+        return total, total_sod
+
+    # prewarm (untimed, reported): every captured graph is uploaded by its first replay and the collective's kernels are
+    # loaded (lazy module loading); then exactly --warmup steps
+    n_prewarm = 2 * n_pool
     clocks = ClockSampler(local)
     clocks.start()
     fork()
-    for s in range(n_warm):
+    for s in range(n_prewarm):
         step(s)
     join()
-    allreduce_partials(torch.stack(accs).sum(0))   # first use loads these kernels (lazy module loading): not in the timed region
-    for a in accs:
-        a.zero_()
-    torch.cuda.profiler.start()      # ncu --profile-from-start off: the launch list starts at the timed region
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
+    reduce_partials()
     fork()
-    for s in range(args.steps):
-        out = step(s)
+    for s in range(args.warmup):
+        step(s)
     join()
-    total = torch.stack(accs).sum(0)
-    allreduce_partials(total)
-    e1.record()
     barrier()
+
+    def timed_region(single_lane=False):
+        """EXACTLY --steps steps + the metric all-reduce between two barrier + synchronize pairs -> ms (max over ranks
+        is taken over the whole vector of repeats afterwards)."""
+        for a in accs + accs_sod:
+            a.zero_()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        if single_lane:
+            for s in range(args.steps):
+                out = step(s, main)
+        else:
+            fork()
+            for s in range(args.steps):
+                out = step(s)
+            join()
+        total, total_sod = reduce_partials()
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1), out, total, total_sod
+
+    torch.cuda.profiler.start()      # ncu --profile-from-start off: the launch list starts at the timed regions
+    ms0, out, total, total_sod = timed_region()
+    # repeat the K-step region until >= 25 repeats AND >= 100 ms of timed window (a 20-step region is ~4 ms): the value is
+    # the median repeat, min / max are reported
+    repeats = args.repeats if args.repeats > 0 else int(min(max(25, -(-100.0 // max(ms0, 1e-3))), 500))
+    rep_ms = [ms0] + [timed_region()[0] for _ in range(repeats - 1)]
     torch.cuda.profiler.stop()
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms.item())
+    lane1_ms = [timed_region(single_lane=True)[0] for _ in range(min(repeats, 11))]
+
+    def over_ranks(v):
+        t = torch.tensor(v, dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.tolist()
+
+    rep_ms, lane1_ms = over_ranks(rep_ms), over_ranks(lane1_ms)
+    ms_total = statistics.median(rep_ms)
     value = args.steps * BATCH * world / (ms_total / 1e3)
+    value_min, value_max = (args.steps * BATCH * world / (m / 1e3) for m in (max(rep_ms), min(rep_ms)))
+    value_single_lane = args.steps * BATCH * world / (statistics.median(lane1_ms) / 1e3)
     status = int(out["graph"].status.item())
     if status:
         raise SystemExit(f"graph build overflow status {status}")
     summary = summarize(total)
+    summary.update(gm.sod_summary_from_partial(total_sod, float(total[0].item())))
 
     # ---- end to end through the host-facing call: pinned host inputs, H2D + path + D2H every step
     stager = HostPipeline(pipes, BATCH, H, W, dev, slots=max(2, 2 * lanes), use_graph=not args.no_graph,
@@ -371,17 +486,22 @@ def b200_arm(args):
     h2d_probe_gbs = 20 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
     del probe_d
 
-    for s in range(n_warm):
+    for s in range(n_prewarm + args.warmup):
         e2e_step(s)
-    barrier()
-    t0 = time.perf_counter()
-    for s in range(args.steps):
-        e2e_step(s)
-    torch.cuda.synchronize()          # the D2H result of the last step has landed
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = args.steps * BATCH * world / float(e2e_s.item())
+    stager.synchronize()
+
+    def e2e_region():
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(args.steps):
+            e2e_step(s)
+        stager.synchronize()          # every step's D2H results have landed (and no graph build overflowed)
+        return time.perf_counter() - t0
+
+    e2e_reps = int(min(max(repeats, 25), 200))
+    e2e_s = over_ranks([e2e_region() for _ in range(e2e_reps)])
+    e2e_value = args.steps * BATCH * world / statistics.median(e2e_s)
+    e2e_min, e2e_max = (args.steps * BATCH * world / t for t in (max(e2e_s), min(e2e_s)))
     clk = clocks.stop()
 
     # ---- per-kernel durations: CUDA events around every launch, on the launching stream (separate pass)
@@ -441,31 +561,41 @@ def b200_arm(args):
     tk = kernels[top]
     # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture of this same command
     # (profiles/ncu_traffic.json, written by tools/summarize_ncu.py --json); None when the kernel was not captured
-    traffic = None
+    traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.exists(tpath):
-        for kname, rec in json.load(open(tpath)).items():
-            if kname.startswith(top):
+        tj = json.load(open(tpath))
+        for kname, rec in tj.items():
+            if isinstance(rec, dict) and kname.startswith(top):
                 traffic = rec["dram_bytes_per_launch"]
+                traffic_src = "profiles/ncu_traffic.json: ncu --set full capture at " + str(tj.get("_captured_at", "an earlier commit of this round"))
                 break
     roofline = {"kernel": top, "bound": tk.get("bound"), "achieved": tk.get("achieved"),
                 "peak": hbm_peak if tk.get("bound") == "hbm" else tf_peak, "unit": tk.get("unit"), "frac": tk.get("frac"),
-                "traffic": traffic, "peak_source": peak_src, "launches_per_step": tk["launches_per_step"],
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "launches_per_step": tk["launches_per_step"],
                 "ms_per_step": tk["ms_per_step"], "share_of_kernel_time": tk["ms_per_step"] / sum(v["ms_per_step"] for v in kernels.values())}
 
+    train = None if args.no_train else train_block(args, dev, world, rank)
+
     if rank == 0:
+        arm = {"impl": "b200", "lanes": lanes, "host_cores_bound": len(host_cores), "cuda_graph": not args.no_graph,
+               "l2": f"{n_pool} distinct input batches per GPU ({n_pool * BATCH * (458752 if args.input == 'u8' else 1179648) / 1e6:.0f} MB of inputs, "
+                     "~300 MB with their intermediates > 126 MB L2) rotated so every step's inputs come from HBM, not L2"}
         line = {
-            "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": n_warm,
+            "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "prewarm": n_prewarm, "repeats": len(rep_ms), "timed_window_ms": sum(rep_ms), "value_min": value_min, "value_max": value_max,
+            "value_single_lane": value_single_lane,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f16", "data": "synthetic", "config": workload_config(world, kg_src, lanes, args.input, n_pool, len(host_cores)), "clocks": clk,
+            "dtype": "f16", "data": "synthetic", "config": workload_config(world, kg_src, args.input, arm), "clocks": clk,
             "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": stager.h2d_bytes,
-                    "d2h_bytes_per_step": stager.d2h_bytes, "h2d_probe_gbs": h2d_probe_gbs,
+                    "d2h_bytes_per_step": stager.d2h_bytes, "repeats": len(e2e_s), "value_min": e2e_min, "value_max": e2e_max,
+                    "timed_window_ms": 1e3 * sum(e2e_s), "h2d_probe_gbs": h2d_probe_gbs,
                     "h2d_achieved_gbs": e2e_value / world * stager.h2d_bytes / BATCH / 1e9,
                     "note": "h2d_probe_gbs = pinned-memory copy rate of this box at the step's transfer size, measured just "
                             "before the e2e loop; h2d_achieved_gbs / h2d_probe_gbs is the fraction of the PCIe roofline"},
             "gpu_launches": int(round(launches_per_step * args.steps)),
             "roofline": roofline, "kernels": kernels, "kernels_saturated": saturated,
-            "nodes_per_step": n_nodes, "edges_per_step": n_edges, "metrics_summary": summary,
+            "nodes_per_step": n_nodes, "edges_per_step": n_edges, "metrics_summary": summary, "train": train,
         }
         if world == 1 and not args.no_cpu_baseline:
             gsd, fsd = cpu_state_dicts(gnn, det)
@@ -497,7 +627,7 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pool", type=int, default=8, help="distinct input batches rotated per GPU (8 x 14.7 MB of decoded inputs + their intermediates > L2)")
@@ -510,6 +640,9 @@ def main():
     ap.add_argument("--cpu-images", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying CUDA graphs")
+    ap.add_argument("--repeats", type=int, default=0, help="timed regions of --steps steps each (0 = at least 25 and at least 100 ms in total)")
+    ap.add_argument("--no-train", action="store_true", help="skip the configs[3] training-step block")
+    ap.add_argument("--train-batch", type=int, default=16)
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -138,7 +138,8 @@ SIGNATURES = {
     "cm_metrics_dense": (_i, [_fp, _fp, _i, _i64, _f, _fp, _fp, _fp]),
     "cm_metrics_finalize": (_i, [_fp, _fp, _i, _i64, _fp, _fp, _fp]),
     "cm_sod_workspace_bytes": (_sz, [_i, _i, _i]),
-    "cm_sod_metrics": (_i, [_fp, _fp, _i, _i, _i, _fp, _sz, _fp, _fp, _fp]),
+    "cm_sod_metrics": (_i, [_fp, _fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp]),
+    "cm_sod_metrics_painted": (_i, [_fp, _i, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _i, _fp, _sz, _fp, _fp, _fp]),
     "cm_class_confusion": (_i, [_fp, _fp, _i, _i, _fp, _fp]),
     "cm_slic_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "cm_slic": (_i, [_fp, _i, _i, _i, _i, C.c_double, C.c_double, _i, _fp, _sz, _fp, _fp]),

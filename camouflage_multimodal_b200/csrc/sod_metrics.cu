@@ -12,6 +12,9 @@
 //               lexicographically smallest (y, x)) for the weighted F-measure
 //   sod_wf      pixel dependency (7x7 Gaussian, sigma 5, zero border) + pixel importance -> weighted error sums
 //   sod_finalize / sod_partial   closed forms per image, curves, batch partial sums
+// The prediction is either a dense float map or PAINTED on the fly from the label map and the per-node probabilities
+// (models/region_graph/test.py:241-244, the same gather cm_paint_metrics does) -- the pipeline never writes the mask.
+// The weighted F-measure (feature transform + 7x7 filter: the expensive part) is optional.
 // Every float64 sum is a per-thread running sum -> warp shuffle tree -> fixed-order block / chunk combination: the
 // result does not depend on scheduling (no floating-point atomics).  Bound: HBM/L2 on pred (4 B) + gt (1 B) per pixel,
 // read three times (the second and third from L2 at batch 32: 10 MB).
@@ -21,7 +24,8 @@
 
 namespace cm {
 
-constexpr int SOD_CHUNKS = 16;   // blocks per image in the two pixel passes
+constexpr int SOD_CHUNKS = 64;   // blocks per image in the two pixel passes (256 x 256: four pixels per thread, all in flight together)
+constexpr int SOD_ILP = 4;
 constexpr int SOD_P1 = 8;        // doubles per chunk, pass 1
 constexpr int SOD_P2 = 18;       // doubles per chunk, pass 2
 constexpr int SOD_KEYS = 8;
@@ -55,6 +59,47 @@ static SodWs carve_sod(void* ws, int batch, int h, int w) {
     return r;
 }
 
+
+// Where a pixel's prediction comes from: a dense float map, or the paint of test.py:241-244 through the label map.
+struct SodSrc {
+    const float* pred;        // dense [B,H,W] or NULL
+    const void* labels;       // [B,H,W] int32 / int16
+    int label_bytes;
+    const float* mask_prob;   // [nodes]
+    const int* node_ptr;      // [B+1]
+    const int* id_of_label;   // [B,cap] or NULL (raw-label indexing, the reference's quirk)
+    int cap;
+};
+struct SodPix {
+    const float* pr;
+    const int* l32;
+    const short* l16;
+    const float* prob;
+    const int* idm;
+    int nb, cap;
+    __device__ __forceinline__ SodPix(const SodSrc& s, int b, size_t HW) {
+        pr = s.pred ? s.pred + (size_t)b * HW : nullptr;
+        l32 = (!s.pred && s.label_bytes == 4) ? reinterpret_cast<const int*>(s.labels) + (size_t)b * HW : nullptr;
+        l16 = (!s.pred && s.label_bytes == 2) ? reinterpret_cast<const short*>(s.labels) + (size_t)b * HW : nullptr;
+        nb = 0;
+        prob = nullptr;
+        idm = nullptr;
+        cap = s.cap;
+        if (!s.pred) {
+            const int n0 = s.node_ptr[b];
+            nb = s.node_ptr[b + 1] - n0;
+            prob = s.mask_prob + n0;
+            idm = s.id_of_label ? s.id_of_label + (size_t)b * s.cap : nullptr;
+        }
+    }
+    __device__ __forceinline__ float at(int i) const {
+        if (pr) return pr[i];
+        int l = l32 ? l32[i] : (int)l16[i];
+        if (idm) l = (l >= 0 && l < cap) ? idm[l] : -1;
+        return (l >= 0 && l < nb) ? prob[l] : 0.f;
+    }
+};
+
 // block-wide sum of NV doubles per thread, result valid in thread 0 (fixed order: lanes by shuffle tree, warps 0..7 serially)
 template <int NV>
 __device__ __forceinline__ void block_sum(double (&v)[NV], double* s_red /* [8 * NV] */) {
@@ -76,12 +121,12 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* s_red /* [8 *
 }
 
 // grid (SOD_CHUNKS, B), block 256
-__global__ void __launch_bounds__(256) sod_pass1_kernel(const float* __restrict__ pred, const uint8_t* __restrict__ gt, int H, int W,
-                                                        double* __restrict__ p1, int* __restrict__ hist) {
+__global__ void __launch_bounds__(256) sod_pass1_kernel(const SodSrc src, const uint8_t* __restrict__ gt, int H, int W, double* __restrict__ p1,
+                                                        int* __restrict__ hist) {
     __shared__ int s_hist[512];
     __shared__ double s_red[8 * SOD_P1];
-    const int b = blockIdx.y, HW = H * W;
-    const float* pr = pred + (size_t)b * HW;
+    const int b = blockIdx.y, HW = H * W, lane = threadIdx.x & 31;
+    const SodPix px(src, b, (size_t)HW);
     const uint8_t* g = gt + (size_t)b * HW;
     for (int i = threadIdx.x; i < 512; i += 256) s_hist[i] = 0;
     __syncthreads();
@@ -90,24 +135,41 @@ __global__ void __launch_bounds__(256) sod_pass1_kernel(const float* __restrict_
     int n_fg = 0;
     long long sy = 0, sx = 0;
     const int per = (HW + SOD_CHUNKS - 1) / SOD_CHUNKS, i0 = blockIdx.x * per, i1 = min(i0 + per, HW);
-    for (int i = i0 + threadIdx.x; i < i1; i += 256) {
-        const double p = (double)pr[i];
-        const bool fg = g[i] >= 128;
-        int q = (int)(p * 255.0);
-        q = min(max(q, 0), 255);
-        atomicAdd(&s_hist[(fg ? 0 : 256) + q], 1);
-        v[7] += p;
-        if (fg) {
-            const int y = i / W;
-            ++n_fg;
-            sy += y;
-            sx += i - y * W;
-            v[3] += p;
-            v[4] += p * p;
-        } else {
-            const double o = 1.0 - p;
-            v[5] += o;
-            v[6] += o * o;
+    for (int base = i0; base < i1; base += 256 * SOD_ILP) {   // whole warps stay in the loop: the histogram vote needs all lanes
+        float pv[SOD_ILP];
+        unsigned char gv[SOD_ILP];
+#pragma unroll
+        for (int u = 0; u < SOD_ILP; ++u) {   // the label -> node -> probability gathers of SOD_ILP pixels in flight together
+            const int i = base + u * 256 + threadIdx.x;
+            pv[u] = i < i1 ? px.at(i) : 0.f;
+            gv[u] = i < i1 ? g[i] : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < SOD_ILP; ++u) {
+            const int i = base + u * 256 + threadIdx.x;
+            const bool in = i < i1;
+            const double p = (double)pv[u];
+            const bool fg = in && gv[u] >= 128;
+            int q = (int)(p * 255.0);
+            q = min(max(q, 0), 255);
+            // a painted mask is constant over runs of pixels: one shared-memory atomic per distinct (class, bin) of the warp
+            const int key = in ? (fg ? 0 : 256) + q : -1;
+            const unsigned peers = __match_any_sync(0xffffffffu, key);
+            if (in && lane == __ffs(peers) - 1) atomicAdd(&s_hist[key], __popc(peers));
+            if (!in) continue;
+            v[7] += p;
+            if (fg) {
+                const int y = i / W;
+                ++n_fg;
+                sy += y;
+                sx += i - y * W;
+                v[3] += p;
+                v[4] += p * p;
+            } else {
+                const double o = 1.0 - p;
+                v[5] += o;
+                v[6] += o * o;
+            }
         }
     }
     v[0] = (double)n_fg;
@@ -124,16 +186,19 @@ __global__ void __launch_bounds__(256) sod_pass1_kernel(const float* __restrict_
         if (s_hist[i]) atomicAdd(&hist[(size_t)b * 512 + i], s_hist[i]);
 }
 
-// image totals of pass 1 (fixed chunk order)
-__device__ __forceinline__ void sod_totals(const double* __restrict__ p1, int b, double (&t)[SOD_P1]) {
-#pragma unroll
-    for (int k = 0; k < SOD_P1; ++k) t[k] = 0.0;
-    for (int c = 0; c < SOD_CHUNKS; ++c)
-#pragma unroll
-        for (int k = 0; k < SOD_P1; ++k) t[k] += p1[((size_t)b * SOD_CHUNKS + c) * SOD_P1 + k];
+// image totals of pass 1 (fixed chunk order), computed by the first NV threads of the block into shared memory:
+// thread k sums value k over the chunks (NV independent chains of SOD_CHUNKS loads instead of one chain of NV * SOD_CHUNKS)
+template <int NV>
+__device__ __forceinline__ void sod_chunk_totals(const double* __restrict__ part, int b, double* s_tot) {
+    if (threadIdx.x < NV) {
+        double t = 0.0;
+        for (int c = 0; c < SOD_CHUNKS; ++c) t += part[((size_t)b * SOD_CHUNKS + c) * NV + threadIdx.x];
+        s_tot[threadIdx.x] = t;
+    }
+    __syncthreads();
 }
 // GT centroid the way the published code rounds it: round-half-even of the mean, + 1; image centre when the GT is empty
-__device__ __forceinline__ void sod_centroid(const double (&t)[SOD_P1], int H, int W, int* cx, int* cy) {
+__device__ __forceinline__ void sod_centroid(const double* t, int H, int W, int* cx, int* cy) {
     if (t[0] == 0.0) {
         *cx = (int)rint((double)W / 2.0) + 1;
         *cy = (int)rint((double)H / 2.0) + 1;
@@ -145,56 +210,61 @@ __device__ __forceinline__ void sod_centroid(const double (&t)[SOD_P1], int H, i
 
 // grid (SOD_CHUNKS, B), block 256.  Per quadrant k (LT, RT, LB, RB): sum p', sum p'^2, sum p' g (p' = p - corner pixel),
 // sum g; then adaptive-threshold tp, fp.
-__global__ void __launch_bounds__(256) sod_pass2_kernel(const float* __restrict__ pred, const uint8_t* __restrict__ gt, int H, int W,
+__global__ void __launch_bounds__(256) sod_pass2_kernel(const SodSrc src, const uint8_t* __restrict__ gt, int H, int W,
                                                         const double* __restrict__ p1, double* __restrict__ p2, double* __restrict__ shift) {
     __shared__ double s_red[8 * SOD_P2];
+    __shared__ double s_tot[SOD_P1];
     __shared__ double s_shift[4];
-    __shared__ int s_c[2];
-    __shared__ double s_thr;
     const int b = blockIdx.y, HW = H * W;
-    const float* pr = pred + (size_t)b * HW;
+    const SodPix px(src, b, (size_t)HW);
     const uint8_t* g = gt + (size_t)b * HW;
-    if (threadIdx.x == 0) {
-        double t[SOD_P1];
-        sod_totals(p1, b, t);
-        int cx, cy;
-        sod_centroid(t, H, W, &cx, &cy);
-        s_c[0] = cx;
-        s_c[1] = cy;
-        s_thr = fmin(2.0 * (t[7] / (double)HW), 1.0);
-        s_shift[0] = (double)pr[0];
-        s_shift[1] = cx < W ? (double)pr[cx] : 0.0;
-        s_shift[2] = cy < H ? (double)pr[(size_t)cy * W] : 0.0;
-        s_shift[3] = (cx < W && cy < H) ? (double)pr[(size_t)cy * W + cx] : 0.0;
-        if (blockIdx.x == 0)
-            for (int k = 0; k < 4; ++k) shift[(size_t)b * 4 + k] = s_shift[k];
+    sod_chunk_totals<SOD_P1>(p1, b, s_tot);
+    int cx, cy;
+    sod_centroid(s_tot, H, W, &cx, &cy);
+    const double thr = fmin(2.0 * (s_tot[7] / (double)HW), 1.0);
+    if (threadIdx.x < 4) {   // the corner pixel of quadrant k
+        const int k = threadIdx.x, y0 = (k & 2) ? cy : 0, x0 = (k & 1) ? cx : 0;
+        const double sh = (y0 < H && x0 < W) ? (double)px.at(y0 * W + x0) : 0.0;
+        s_shift[k] = sh;
+        if (blockIdx.x == 0) shift[(size_t)b * 4 + k] = sh;
     }
     __syncthreads();
-    const int cx = s_c[0], cy = s_c[1];
-    const double thr = s_thr;
     double v[SOD_P2];
 #pragma unroll
     for (int k = 0; k < SOD_P2; ++k) v[k] = 0.0;
     int gq[4] = {0, 0, 0, 0}, tpa = 0, fpa = 0;
     const int per = (HW + SOD_CHUNKS - 1) / SOD_CHUNKS, i0 = blockIdx.x * per, i1 = min(i0 + per, HW);
-    for (int i = i0 + threadIdx.x; i < i1; i += 256) {
-        const double p = (double)pr[i];
-        const bool fg = g[i] >= 128;
-        const int y = i / W, x = i - y * W;
-        const int k = (y >= cy ? 2 : 0) + (x >= cx ? 1 : 0);
-        const double d = p - s_shift[k];
-        // branch-free scatter into the quadrant's slots
+    for (int base = i0; base < i1; base += 256 * SOD_ILP) {
+        float pv[SOD_ILP];
+        unsigned char gv[SOD_ILP];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const double m = (j == k) ? 1.0 : 0.0;
-            v[3 * j] += m * d;
-            v[3 * j + 1] += m * d * d;
-            v[3 * j + 2] += (fg && j == k) ? d : 0.0;
-            gq[j] += (fg && j == k);
+        for (int u = 0; u < SOD_ILP; ++u) {
+            const int i = base + u * 256 + threadIdx.x;
+            pv[u] = i < i1 ? px.at(i) : 0.f;
+            gv[u] = i < i1 ? g[i] : 0;
         }
-        if (p >= thr) {
-            tpa += fg;
-            fpa += !fg;
+#pragma unroll
+        for (int u = 0; u < SOD_ILP; ++u) {
+            const int i = base + u * 256 + threadIdx.x;
+            if (i >= i1) continue;
+            const double p = (double)pv[u];
+            const bool fg = gv[u] >= 128;
+            const int y = i / W, x = i - y * W;
+            const int k = (y >= cy ? 2 : 0) + (x >= cx ? 1 : 0);
+            const double d = p - s_shift[k];
+            // branch-free scatter into the quadrant's slots
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const double m = (j == k) ? 1.0 : 0.0;
+                v[3 * j] += m * d;
+                v[3 * j + 1] += m * d * d;
+                v[3 * j + 2] += (fg && j == k) ? d : 0.0;
+                gq[j] += (fg && j == k);
+            }
+            if (p >= thr) {
+                tpa += fg;
+                fpa += !fg;
+            }
         }
     }
 #pragma unroll
@@ -274,21 +344,25 @@ struct Gauss7 {
     double k[49];
 };
 // block = 32 x 8 pixel tile; Et with a 3-pixel halo in shared memory (zero outside the image)
-__global__ void __launch_bounds__(256) sod_wf_kernel(const float* __restrict__ pred, const uint8_t* __restrict__ gt, const int* __restrict__ d2,
-                                                     const int* __restrict__ near, int H, int W, const Gauss7 gk, double* __restrict__ p4) {
+__global__ void __launch_bounds__(256) sod_wf_kernel(const SodSrc src, const uint8_t* __restrict__ gtb, const int* __restrict__ d2b,
+                                                     const int* __restrict__ nearb, int H, int W, const Gauss7 gk, double* __restrict__ p4) {
     __shared__ double s_et[14][38];
     __shared__ double s_red[8 * 2];
     const int b = blockIdx.z, tx0 = blockIdx.x * 32, ty0 = blockIdx.y * 8;
-    const size_t off = (size_t)b * H * W;
+    const size_t off0 = (size_t)b * H * W, off = 0;
+    const SodPix pred(src, b, (size_t)H * W);
+    const uint8_t* gt = gtb + off0;
+    const int* d2 = d2b + off0;
+    const int* near = nearb + off0;
     for (int i = threadIdx.x; i < 14 * 38; i += 256) {
         const int ly = i / 38, lx = i - ly * 38, y = ty0 + ly - 3, x = tx0 + lx - 3;
         double et = 0.0;
         if (y >= 0 && y < H && x >= 0 && x < W) {
             const size_t p = off + (size_t)y * W + x;
             if (gt[p] >= 128) {
-                et = fabs((double)pred[p] - 1.0);
+                et = fabs((double)pred.at((int)p) - 1.0);
             } else {
-                et = fabs((double)pred[off + near[p]] - 1.0);   // the error of the nearest foreground pixel
+                et = fabs((double)pred.at(near[p]) - 1.0);   // the error of the nearest foreground pixel
             }
         }
         s_et[ly][lx] = et;
@@ -299,7 +373,7 @@ __global__ void __launch_bounds__(256) sod_wf_kernel(const float* __restrict__ p
     if (x < W && y < H) {
         const size_t p = off + (size_t)y * W + x;
         const bool fg = gt[p] >= 128;
-        const double e = fabs((double)pred[p] - (fg ? 1.0 : 0.0));
+        const double e = fabs((double)pred.at((int)p) - (fg ? 1.0 : 0.0));
         double ea = 0.0;
 #pragma unroll
         for (int dy = 0; dy < 7; ++dy)
@@ -362,12 +436,14 @@ __global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restr
                                                            double beta2_f, double beta2_wf, double* __restrict__ per_image,
                                                            double* __restrict__ curves) {
     __shared__ int s_tp[256], s_fp[256];
-    __shared__ double s_f[256], s_e[256];
+    __shared__ double s_f[256], s_e[256], s_fm[256], s_em[256];
+    __shared__ double s_tot[SOD_P1], s_q[SOD_P2], s_wf[2];
     const int b = blockIdx.x, t = threadIdx.x;
     const double n = (double)H * (double)W;
     s_tp[t] = hist[(size_t)b * 512 + 255 - t];
     s_fp[t] = hist[(size_t)b * 512 + 256 + 255 - t];
-    __syncthreads();
+    sod_chunk_totals<SOD_P1>(p1, b, s_tot);   // (syncs)
+    sod_chunk_totals<SOD_P2>(p2, b, s_q);
     for (int o = 1; o < 256; o <<= 1) {   // inclusive scan (integers: order-free)
         const int a = t >= o ? s_tp[t - o] : 0, c = t >= o ? s_fp[t - o] : 0;
         __syncthreads();
@@ -375,30 +451,70 @@ __global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restr
         s_fp[t] += c;
         __syncthreads();
     }
-    double tot[SOD_P1];
-    sod_totals(p1, b, tot);
-    const double n_fg = tot[0];
+    const double n_fg = s_tot[0];
     const double f = sod_f_from_counts((double)s_tp[t], (double)s_fp[t], n_fg, beta2_f);
     const double e = sod_e_from_counts((double)s_tp[t], (double)s_fp[t], n_fg, n);
     curves[(size_t)b * 512 + t] = f;
     curves[(size_t)b * 512 + 256 + t] = e;
     s_f[t] = f;
     s_e[t] = e;
+    s_fm[t] = f;
+    s_em[t] = e;
+    // weighted-F tile sums: threads 0 / 1 own the two columns, strided partial sums combined in a fixed order below
+    if (p4) {
+        double a = 0.0, c = 0.0;
+        for (int i = t; i < wf_tiles; i += 256) {
+            a += p4[((size_t)b * wf_tiles + i) * 2];
+            c += p4[((size_t)b * wf_tiles + i) * 2 + 1];
+        }
+        __syncthreads();
+        // reuse the tree below: stash in registers until the curve reduction is done
+        for (int o = 128; o > 0; o >>= 1) {   // curve sums / maxima first (fixed tree)
+            __syncthreads();
+            if (t < o) {
+                s_f[t] += s_f[t + o];
+                s_e[t] += s_e[t + o];
+                s_fm[t] = fmax(s_fm[t], s_fm[t + o]);
+                s_em[t] = fmax(s_em[t], s_em[t + o]);
+            }
+        }
+        __syncthreads();
+        const double fsum = s_f[0], esum = s_e[0], fmx = s_fm[0], emx = s_em[0];
+        __syncthreads();
+        s_f[t] = a;
+        s_e[t] = c;
+        for (int o = 128; o > 0; o >>= 1) {
+            __syncthreads();
+            if (t < o) {
+                s_f[t] += s_f[t + o];
+                s_e[t] += s_e[t + o];
+            }
+        }
+        __syncthreads();
+        if (t == 0) {
+            s_wf[0] = s_f[0];
+            s_wf[1] = s_e[0];
+            s_f[0] = fsum;
+            s_e[0] = esum;
+            s_fm[0] = fmx;
+            s_em[0] = emx;
+        }
+    } else {
+        for (int o = 128; o > 0; o >>= 1) {
+            __syncthreads();
+            if (t < o) {
+                s_f[t] += s_f[t + o];
+                s_e[t] += s_e[t + o];
+                s_fm[t] = fmax(s_fm[t], s_fm[t + o]);
+                s_em[t] = fmax(s_em[t], s_em[t + o]);
+            }
+        }
+    }
     __syncthreads();
     if (t != 0) return;
-    double fsum = 0.0, esum = 0.0, fmx = s_f[0], emx = s_e[0];
-    for (int i = 0; i < 256; ++i) {
-        fsum += s_f[i];
-        esum += s_e[i];
-        fmx = fmax(fmx, s_f[i]);
-        emx = fmax(emx, s_e[i]);
-    }
-    double q[SOD_P2];
-#pragma unroll
-    for (int k = 0; k < SOD_P2; ++k) q[k] = 0.0;
-    for (int c = 0; c < SOD_CHUNKS; ++c)
-#pragma unroll
-        for (int k = 0; k < SOD_P2; ++k) q[k] += p2[((size_t)b * SOD_CHUNKS + c) * SOD_P2 + k];
+    const double fsum = s_f[0], esum = s_e[0], fmx = s_fm[0], emx = s_em[0];
+    const double* tot = s_tot;
+    const double* q = s_q;
     // ---- S-measure (alpha = 0.5)
     double sm;
     const double mean_p = tot[7] / n;
@@ -438,14 +554,10 @@ __global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restr
     const double tpa = q[16], fpa = q[17];
     const double fa = tpa == 0.0 ? 0.0 : sod_f_from_counts(tpa, fpa, n_fg, beta2_f);
     const double ea = sod_e_from_counts(tpa, fpa, n_fg, n);
-    // ---- weighted F
-    double wf = 0.0;
-    if (n_fg > 0.0) {
-        double ew_fg = 0.0, ew_bg = 0.0;
-        for (int i = 0; i < wf_tiles; ++i) {
-            ew_fg += p4[((size_t)b * wf_tiles + i) * 2];
-            ew_bg += p4[((size_t)b * wf_tiles + i) * 2 + 1];
-        }
+    // ---- weighted F (NaN when it was not asked for)
+    double wf = p4 ? 0.0 : nan("");
+    if (p4 && n_fg > 0.0) {
+        const double ew_fg = s_wf[0], ew_bg = s_wf[1];
         const double tpw = n_fg - ew_fg, fpw = ew_bg, r = 1.0 - ew_fg / n_fg, pw = tpw / (tpw + fpw + SOD_EPS);
         wf = (1.0 + beta2_wf) * r * pw / (r + beta2_wf * pw + SOD_EPS);
     }
@@ -484,20 +596,29 @@ extern "C" size_t cm_sod_workspace_bytes(int batch, int h, int w) {
     return cm::carve_sod(nullptr, batch, h, w).total;
 }
 
-extern "C" int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, int h, int w, void* workspace, size_t workspace_bytes,
-                              double* per_image, double* partial, void* stream) {
+static int sod_metrics_impl(const cm::SodSrc& src, const uint8_t* gt, int batch, int h, int w, int with_weighted_f, void* workspace,
+                            size_t workspace_bytes, double* per_image, double* partial, void* stream, const char* who) {
     using namespace cm;
     CM_DEVICE_OR_RETURN();
-    CM_REQUIRE(pred && gt && workspace && per_image && partial, "cm_sod_metrics: NULL pointer");
-    CM_REQUIRE(batch > 0 && batch <= 65535 && h > 0 && w > 0 && h < 32767 && w < 32767 && (long long)h * w < (1ll << 30), "cm_sod_metrics: bad shape");
+    CM_REQUIRE(gt && workspace && per_image && partial, "%s: NULL pointer", who);
+    CM_REQUIRE(batch > 0 && batch <= 65535 && h > 0 && w > 0 && h < 32767 && w < 32767 && (long long)h * w < (1ll << 30), "%s: bad shape", who);
     SodWs ws = carve_sod(workspace, batch, h, w);
     if (workspace_bytes < ws.total) {
-        set_error("cm_sod_metrics: workspace %zu < %zu bytes", workspace_bytes, ws.total);
+        set_error("%s: workspace %zu < %zu bytes", who, workspace_bytes, ws.total);
         return CM_ERR_WORKSPACE;
     }
     cudaStream_t st = as_stream(stream);
-    Gauss7 gk;   // Matlab fspecial('gaussian', 7, 5)
+    cudaMemsetAsync(ws.hist, 0, (size_t)batch * 512 * sizeof(int), st);
     {
+        CM_TIMED("sod_pass1", st);
+        sod_pass1_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.p1, ws.hist);
+    }
+    {
+        CM_TIMED("sod_pass2", st);
+        sod_pass2_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.p1, ws.p2, ws.shift);
+    }
+    if (with_weighted_f) {
+        Gauss7 gk;   // Matlab fspecial('gaussian', 7, 5)
         double sum = 0.0;
         for (int dy = -3; dy <= 3; ++dy)
             for (int dx = -3; dx <= 3; ++dx) {
@@ -505,29 +626,49 @@ extern "C" int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, i
                 sum += gk.k[(dy + 3) * 7 + dx + 3];
             }
         for (int i = 0; i < 49; ++i) gk.k[i] /= sum;
-    }
-    cudaMemsetAsync(ws.hist, 0, (size_t)batch * 512 * sizeof(int), st);
-    {
-        CM_TIMED("sod_pass1", st);
-        sod_pass1_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(pred, gt, h, w, ws.p1, ws.hist);
-    }
-    {
-        CM_TIMED("sod_pass2", st);
-        sod_pass2_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(pred, gt, h, w, ws.p1, ws.p2, ws.shift);
-    }
-    {
-        CM_TIMED("sod_edt", st);
-        sod_edt_cols_kernel<<<ceil_div((long long)batch * w, 128), 128, 0, st>>>(gt, batch, h, w, ws.col_d, ws.col_y);
-        sod_edt_rows_kernel<<<dim3(h, batch), 256, 2 * (size_t)w * sizeof(short), st>>>(ws.col_d, ws.col_y, h, w, ws.d2, ws.near);
-    }
-    {
-        CM_TIMED("sod_wf", st);
-        sod_wf_kernel<<<dim3(ceil_div(w, 32), ceil_div(h, 8), batch), 256, 0, st>>>(pred, gt, ws.d2, ws.near, h, w, gk, ws.p4);
+        {
+            CM_TIMED("sod_edt", st);
+            sod_edt_cols_kernel<<<ceil_div((long long)batch * w, 128), 128, 0, st>>>(gt, batch, h, w, ws.col_d, ws.col_y);
+            sod_edt_rows_kernel<<<dim3(h, batch), 256, 2 * (size_t)w * sizeof(short), st>>>(ws.col_d, ws.col_y, h, w, ws.d2, ws.near);
+        }
+        {
+            CM_TIMED("sod_wf", st);
+            sod_wf_kernel<<<dim3(ceil_div(w, 32), ceil_div(h, 8), batch), 256, 0, st>>>(src, gt, ws.d2, ws.near, h, w, gk, ws.p4);
+        }
     }
     {
         CM_TIMED("sod_finalize", st);
-        sod_finalize_kernel<<<batch, 256, 0, st>>>(ws.p1, ws.p2, ws.shift, ws.p4, ws.wf_tiles, ws.hist, h, w, 0.3, 1.0, per_image, ws.curves);
+        sod_finalize_kernel<<<batch, 256, 0, st>>>(ws.p1, ws.p2, ws.shift, with_weighted_f ? ws.p4 : nullptr, ws.wf_tiles, ws.hist, h, w, 0.3, 1.0,
+                                                   per_image, ws.curves);
         sod_partial_kernel<<<ceil_div(SOD_PARTIAL, 128), 128, 0, st>>>(per_image, ws.curves, batch, partial);
     }
-    return post_launch("cm_sod_metrics");
+    return post_launch(who);
+}
+
+extern "C" int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, int h, int w, int with_weighted_f, void* workspace,
+                              size_t workspace_bytes, double* per_image, double* partial, void* stream) {
+    if (!pred) {
+        cm::set_error("cm_sod_metrics: NULL pointer");
+        return CM_ERR_ARG;
+    }
+    cm::SodSrc src = {};
+    src.pred = pred;
+    return sod_metrics_impl(src, gt, batch, h, w, with_weighted_f, workspace, workspace_bytes, per_image, partial, stream, "cm_sod_metrics");
+}
+
+extern "C" int cm_sod_metrics_painted(const void* labels, int label_bytes, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
+                                      const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, int with_weighted_f, void* workspace,
+                                      size_t workspace_bytes, double* per_image, double* partial, void* stream) {
+    if (!labels || !mask_prob || !node_ptr || (label_bytes != 2 && label_bytes != 4) || (id_of_label && label_cap <= 0)) {
+        cm::set_error("cm_sod_metrics_painted: NULL pointer or label_bytes not 2 / 4");
+        return CM_ERR_ARG;
+    }
+    cm::SodSrc src = {};
+    src.labels = labels;
+    src.label_bytes = label_bytes;
+    src.mask_prob = mask_prob;
+    src.node_ptr = node_ptr;
+    src.id_of_label = id_of_label;
+    src.cap = label_cap;
+    return sod_metrics_impl(src, gt, batch, h, w, with_weighted_f, workspace, workspace_bytes, per_image, partial, stream, "cm_sod_metrics_painted");
 }

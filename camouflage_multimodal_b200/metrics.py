@@ -142,9 +142,10 @@ def f1_from_confusion(tp, fp, fn, tn):
 
 
 # ---------------------------------------------------------------------------------------------------- A9'
-def sod_metrics(pred: torch.Tensor, gt_u8: torch.Tensor, per_image=None, partial=None):
+def sod_metrics(pred: torch.Tensor, gt_u8: torch.Tensor, per_image=None, partial=None, weighted_f: bool = True):
     """Device entry: ``pred`` ``[B,H,W]`` f32 in [0,1], ``gt_u8`` ``[B,H,W]`` uint8 (foreground = byte >= 128), CUDA ->
-    (per_image ``[B,8]`` f64 in ``SOD_KEYS`` order, partial ``[528]`` f64: sums, sums of squares, summed F / E curves)."""
+    (per_image ``[B,8]`` f64 in ``SOD_KEYS`` order, partial ``[528]`` f64: sums, sums of squares, summed F / E curves).
+    ``weighted_f=False`` skips the weighted F-measure (NaN in its slot)."""
     from .region_graph import WORKSPACE
     lib = _lib.load()
     _lib.require_cuda(pred, "pred")
@@ -160,8 +161,33 @@ def sod_metrics(pred: torch.Tensor, gt_u8: torch.Tensor, per_image=None, partial
         partial = torch.empty(SOD_PARTIAL, dtype=torch.float64, device=dev)
     ws_bytes = lib.cm_sod_workspace_bytes(B, H, W)
     ws = WORKSPACE.get(dev, "sod", ws_bytes)
-    _lib.check(lib.cm_sod_metrics(_lib.ptr(pred), _lib.ptr(gt_u8), B, H, W, _lib.ptr(ws), ws_bytes, _lib.ptr(per_image),
-                                  _lib.ptr(partial), _lib.stream_ptr(dev)), "cm_sod_metrics")
+    _lib.check(lib.cm_sod_metrics(_lib.ptr(pred), _lib.ptr(gt_u8), B, H, W, 1 if weighted_f else 0, _lib.ptr(ws), ws_bytes,
+                                  _lib.ptr(per_image), _lib.ptr(partial), _lib.stream_ptr(dev)), "cm_sod_metrics")
+    return per_image, partial
+
+
+def sod_metrics_painted(labels, gt_u8, mask_prob, node_ptr, id_of_label=None, label_cap=0, per_image=None, partial=None,
+                        weighted_f: bool = False):
+    """The same reductions on the mask PAINTED from ``labels`` ``[B,H,W]`` (int32 / int16) and the per-node probabilities
+    (``cm_paint_metrics``' gather, models/region_graph/test.py:241-244) without writing the mask."""
+    from .region_graph import WORKSPACE
+    lib = _lib.load()
+    for t, n in ((labels, "labels"), (gt_u8, "gt"), (mask_prob, "mask_prob"), (node_ptr, "node_ptr")):
+        _lib.require_cuda(t, n)
+    if labels.dtype not in (torch.int32, torch.int16) or gt_u8.dtype != torch.uint8 or labels.shape != gt_u8.shape or labels.dim() != 3:
+        raise ValueError("labels [B,H,W] int32 / int16 and gt [B,H,W] uint8 expected")
+    B, H, W = labels.shape
+    dev = labels.device
+    if per_image is None:
+        per_image = torch.empty((B, len(SOD_KEYS)), dtype=torch.float64, device=dev)
+    if partial is None:
+        partial = torch.empty(SOD_PARTIAL, dtype=torch.float64, device=dev)
+    ws_bytes = lib.cm_sod_workspace_bytes(B, H, W)
+    ws = WORKSPACE.get(dev, "sod", ws_bytes)
+    p = _lib.ptr
+    _lib.check(lib.cm_sod_metrics_painted(p(labels.contiguous()), labels.element_size(), p(gt_u8.contiguous()), B, H, W, p(_lib.f32c(mask_prob)),
+                                          p(node_ptr), p(id_of_label), int(label_cap), 1 if weighted_f else 0, p(ws), ws_bytes, p(per_image),
+                                          p(partial), _lib.stream_ptr(dev)), "cm_sod_metrics_painted")
     return per_image, partial
 
 
@@ -217,6 +243,9 @@ def sod_summary_from_partial(partial, n_images) -> dict:
     fc, ec = v[2 * k:2 * k + 256] / n, v[2 * k + 256:2 * k + 512] / n
     for name in ("s_measure", "e_adaptive", "f_adaptive", "wf_measure"):
         out[name] = out[name + "_per_image"]
+    if np.isnan(out["wf_measure"]):          # the weighted F-measure was not asked for
+        for name in [k for k in out if k.startswith("wf_measure")]:
+            del out[name]
     out.update({"f_max": float(fc.max()), "f_mean": float(fc.mean()), "e_max": float(ec.max()), "e_mean": float(ec.mean())})
     return out
 

@@ -19,14 +19,16 @@ from .region_graph import RegionGraphBatch, build_region_graphs
 
 class EvalPipeline:
     def __init__(self, gnn, detector, kg, label_cap: int = 544, threshold: float = 0.5, label_offset_fix: bool = False,
-                 want_pred_mask: bool = False, lane: int = 0, sod_metrics: bool = True):
+                 want_pred_mask: bool = False, lane: int = 0, sod_metrics: bool = True, weighted_f: bool = False):
         """``kg``: ``[K, kg_dim]`` knowledge-graph rows shared by every image (broadcast once).
         ``lane``: pipelines with different lanes own disjoint scratch and may run concurrently on different streams
         (they share the read-only folded weights).
         ``sod_metrics``: also compute S- / E- / F- / weighted-F-measure (``metrics.SOD_KEYS``; north_star's "S/E/F-measure",
-        not in the reference) on the painted mask: ``out["per_image_sod"]`` ``[B,8]``, ``out["partial_sod"]`` ``[528]``."""
+        not in the reference) on the painted mask: ``out["per_image_sod"]`` ``[B,8]``, ``out["partial_sod"]`` ``[528]``.
+        ``weighted_f``: also Margolin's weighted F-measure (an exact Euclidean feature transform of every GT mask: several
+        times the cost of the other seven; its slot is NaN when off)."""
         self.lane = int(lane)
-        self.sod_metrics = bool(sod_metrics)
+        self.sod_metrics, self.weighted_f = bool(sod_metrics), bool(weighted_f)
         self.gnn, self.detector = gnn.eval(), detector.eval()
         kg = kg.reshape(-1, kg.shape[-1])
         _lib.require_cuda(kg, "kg")
@@ -57,7 +59,7 @@ class EvalPipeline:
             "abs_err": torch.empty(B, dtype=torch.float64, device=dev),
             "per_image": torch.empty((B, 7), dtype=torch.float64, device=dev),
             "partial": torch.empty(15, dtype=torch.float64, device=dev),
-            "pred_mask": torch.empty((B, H, W), **f32) if (self.want_pred_mask or self.sod_metrics) else None,
+            "pred_mask": torch.empty((B, H, W), **f32) if self.want_pred_mask else None,
             "per_image_sod": torch.empty((B, len(metrics.SOD_KEYS)), dtype=torch.float64, device=dev) if self.sod_metrics else None,
             "partial_sod": torch.empty(metrics.SOD_PARTIAL, dtype=torch.float64, device=dev) if self.sod_metrics else None,
         }
@@ -114,8 +116,10 @@ class EvalPipeline:
                                             _lib.stream_ptr(dev)), "cm_paint_metrics")
             _lib.check(lib.cm_metrics_finalize(p(b["counts"]), p(b["abs_err"]), B, H * W, p(b["per_image"]), p(b["partial"]),
                                                _lib.stream_ptr(dev)), "cm_metrics_finalize")
-            if self.sod_metrics:
-                metrics.sod_metrics(b["pred_mask"], gt, per_image=b["per_image_sod"], partial=b["partial_sod"])
+            if self.sod_metrics:    # on the painted mask, without materialising it
+                metrics.sod_metrics_painted(labels, gt, r["mask_prob"], g.node_ptr, g.id_of_label if self.label_offset_fix else None,
+                                            self.label_cap, per_image=b["per_image_sod"], partial=b["partial_sod"],
+                                            weighted_f=self.weighted_f)
             if self.total is not None:
                 self.total.add_(b["partial"])
                 if self.total_sod is not None and self.sod_metrics:

@@ -348,8 +348,16 @@ int cm_metrics_finalize(const int64_t* counts, const double* abs_err, int batch,
  * cm_metrics_finalize's: dataset-level max / mean F and E are taken over the dataset-AVERAGED curves.
  * ------------------------------------------------------------------------------------------------ */
 size_t cm_sod_workspace_bytes(int batch, int h, int w);
-int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, int h, int w, void* workspace, size_t workspace_bytes,
-                   double* per_image, double* partial, void* stream);
+/* with_weighted_f = 0 skips the weighted F-measure (it needs an exact Euclidean feature transform of the GT and a 7x7
+ * filter per image -- several times the cost of everything else here); its slot in per_image / partial is then NaN. */
+int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, int h, int w, int with_weighted_f, void* workspace,
+                   size_t workspace_bytes, double* per_image, double* partial, void* stream);
+/* The same on the PAINTED prediction of cm_paint_metrics (pixel with label l gets mask_prob[l], or
+ * mask_prob[id_of_label[l]] with the offset fix; models/region_graph/test.py:241-244) without materialising the mask:
+ * labels [B,H,W] int32 (label_bytes 4) or int16 (2); the other arguments as in cm_paint_metrics. */
+int cm_sod_metrics_painted(const void* labels, int label_bytes, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
+                           const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, int with_weighted_f, void* workspace,
+                           size_t workspace_bytes, double* per_image, double* partial, void* stream);
 /* A13: image-level confusion counts tp, fp, fn, tn (models/multimodal/train_multimodal.py:197-220) from
  * predicted class = argmax(mask_out) and true class ids.  counts4 [4] int64 accumulated (caller zeroes). */
 int cm_class_confusion(const float* mask_out, const int64_t* true_cls, int n, int num_classes,

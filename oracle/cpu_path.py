@@ -20,8 +20,9 @@ from . import metrics as om
 from . import region_graph as org
 
 
-def run_image(image, labels, canny, gt_u8, gnn_sd, fusion_sd, kg, faithful=True):
-    """-> (mask logits [2], metrics dict) for one image; ``kg`` is ``[K,128]``."""
+def run_image(image, labels, canny, gt_u8, gnn_sd, fusion_sd, kg, faithful=True, sod=False):
+    """-> (mask logits [2], metrics dict) for one image; ``kg`` is ``[K,128]``.  ``sod``: also S- / E- / F- / weighted
+    F-measure of the painted mask (oracle/sod_metrics.py; not in the reference)."""
     x, ei, w, _ = org.build_region_graph(np.asarray(image, np.float64), np.asarray(labels, np.int64),
                                          np.asarray(canny).astype(bool), faithful=faithful)
     with torch.no_grad():
@@ -29,6 +30,9 @@ def run_image(image, labels, canny, gt_u8, gnn_sd, fusion_sd, kg, faithful=True)
         mask, _, _, _, _, _ = ofus.detector_forward(fusion_sd, r["node_emb"][None], kg[None])
     pred = om.paint_mask(r["mask_out"].numpy(), np.asarray(labels))
     m = om.evaluate_segmentation(pred, np.asarray(gt_u8) / 255.0)
+    if sod:
+        from . import sod_metrics as osod
+        m.update(osod.evaluate_sod(pred, np.asarray(gt_u8) / 255.0)[0])
     return mask[0].numpy(), m
 
 
@@ -37,11 +41,11 @@ def _worker(args):
     return run_image(*args)
 
 
-def time_images(batch, gnn_sd, fusion_sd, kg, faithful=True, processes=1):
+def time_images(batch, gnn_sd, fusion_sd, kg, faithful=True, processes=1, sod=False):
     """Seconds to push every image of ``batch`` (a synth.SynthBatch on the CPU) through the path, using
     ``processes`` worker processes (the reference itself is a single-threaded Python loop)."""
     items = [(batch.images[i].numpy(), batch.labels[i].numpy(), batch.canny[i].numpy(), batch.gt[i].numpy(),
-              gnn_sd, fusion_sd, kg, faithful) for i in range(len(batch))]
+              gnn_sd, fusion_sd, kg, faithful, sod) for i in range(len(batch))]
     t0 = time.perf_counter()
     if processes <= 1:
         out = [run_image(*it) for it in items]

@@ -113,9 +113,12 @@ def test_pipeline_reports_sod_metrics_on_the_painted_mask():
     det = build_multimodal_model({}).eval()
     hb = synth.make_batch(0, 2, seed=99, n_regions=[150, 180])
     d = hb.to("cuda")
-    pipe = EvalPipeline(gnn.cuda(), det.cuda(), synth.synthetic_kg(13).cuda(), label_cap=256, want_pred_mask=True)
+    pipe = EvalPipeline(gnn.cuda(), det.cuda(), synth.synthetic_kg(13).cuda(), label_cap=256, want_pred_mask=True, weighted_f=True)
     out = pipe.run(d.images, d.labels, d.canny, d.gt)
     per = out["per_image_sod"].cpu().numpy()
+    fast = EvalPipeline(gnn, det, synth.synthetic_kg(13).cuda(), label_cap=256, lane=3).run(d.images, d.labels, d.canny, d.gt)
+    assert torch.isnan(fast["per_image_sod"][:, 7]).all()                       # weighted F is opt-in
+    assert torch.equal(fast["per_image_sod"][:, :7].cpu(), out["per_image_sod"][:, :7].cpu())
     for i in range(2):
         gt = hb.gt[i].numpy() / 255.0
         own, _, _ = osod.evaluate_sod(out["pred_mask"][i].cpu().numpy().astype(np.float64), gt)
