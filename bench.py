@@ -466,7 +466,7 @@ def b200_arm(args):
 
     # ---- end to end through the host-facing call: pinned host inputs, H2D + path + D2H every step
     stager = HostPipeline(pipes, BATCH, H, W, dev, slots=max(2, 2 * lanes), use_graph=not args.no_graph,
-                          image_dtype=pool[0].images.dtype, label_dtype=pool[0].labels.dtype)
+                          image_dtype=pool[0].images.dtype, label_dtype=pool[0].labels.dtype, packed_masks=not args.byte_masks)
     # host batches in the pipeline's pinned staging layout (images | labels | canny | gt in one allocation): one H2D copy each
     host_pool = [stager.host_batch().fill(b.images.cpu(), b.labels.cpu(), b.canny.cpu(), b.gt.cpu()) for b in pool]
 
@@ -590,6 +590,9 @@ def b200_arm(args):
             "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": stager.h2d_bytes,
                     "d2h_bytes_per_step": stager.d2h_bytes, "repeats": len(e2e_s), "value_min": e2e_min, "value_max": e2e_max,
                     "timed_window_ms": 1e3 * sum(e2e_s), "h2d_probe_gbs": h2d_probe_gbs,
+                    "host_format": ("uint8 RGB + int16 labels + 1-bit canny + 1-bit gt (binary masks bit-packed on the host, "
+                                    "cm_unpack_bits on the device): 5.25 B/pixel" if not args.byte_masks else
+                                    "uint8 RGB + int16 labels + uint8 canny + uint8 gt: 7 B/pixel") if args.input == "u8" else "float32 / int32 form",
                     "h2d_achieved_gbs": e2e_value / world * stager.h2d_bytes / BATCH / 1e9,
                     "note": "h2d_probe_gbs = pinned-memory copy rate of this box at the step's transfer size, measured just "
                             "before the e2e loop; h2d_achieved_gbs / h2d_probe_gbs is the fraction of the PCIe roofline"},
@@ -642,6 +645,8 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying CUDA graphs")
     ap.add_argument("--repeats", type=int, default=0, help="timed regions of --steps steps each (0 = at least 25 and at least 100 ms in total)")
     ap.add_argument("--no-train", action="store_true", help="skip the configs[3] training-step block")
+    ap.add_argument("--byte-masks", action="store_true",
+                    help="e2e: send the Canny map and the ground truth one BYTE per pixel (default: one bit per pixel, unpacked on the device)")
     ap.add_argument("--train-batch", type=int, default=16)
     args = ap.parse_args()
     if args.warmup < 3:

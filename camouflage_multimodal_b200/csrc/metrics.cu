@@ -181,6 +181,17 @@ __global__ void class_confusion_kernel(const float* __restrict__ mask_out, const
     }
 }
 
+// one thread per packed byte: bit i (little-endian bit order) -> byte 8 * idx + i = one_value or 0, one 8-byte store
+__global__ void unpack_bits_kernel(const uint8_t* __restrict__ bits, long long n_bytes, unsigned one_value, uint8_t* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_bytes) return;
+    const unsigned b = bits[i];
+    uint2 v;
+    v.x = ((b & 1u) ? one_value : 0u) | ((b & 2u) ? one_value << 8 : 0u) | ((b & 4u) ? one_value << 16 : 0u) | ((b & 8u) ? one_value << 24 : 0u);
+    v.y = ((b & 16u) ? one_value : 0u) | ((b & 32u) ? one_value << 8 : 0u) | ((b & 64u) ? one_value << 16 : 0u) | ((b & 128u) ? one_value << 24 : 0u);
+    reinterpret_cast<uint2*>(out)[i] = v;
+}
+
 static int metric_chunks(long long pixels, int batch) {
     // about four CTAs per SM over the whole batch, at least 1 per image, at most one per 256 pixels
     long long want = (4LL * num_sms() + batch - 1) / batch;
@@ -215,6 +226,18 @@ static int paint_metrics_impl(const void* labels_v, int label_bytes, const uint8
                                                             pred_mask, reinterpret_cast<unsigned long long*>(counts), abs_err);
     }
     return post_launch("cm_paint_metrics");
+}
+
+extern "C" int cm_unpack_bits(const uint8_t* bits, int64_t n_bytes, int one_value, uint8_t* out, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(bits && out && n_bytes > 0 && one_value >= 0 && one_value <= 255, "cm_unpack_bits: bad arguments");
+    CM_REQUIRE((reinterpret_cast<uintptr_t>(out) & 7) == 0, "cm_unpack_bits: the output must be 8-byte aligned");
+    {
+        CM_TIMED("unpack_bits", as_stream(stream));
+        unpack_bits_kernel<<<ceil_div(n_bytes, 256), 256, 0, as_stream(stream)>>>(bits, n_bytes, (unsigned)one_value, out);
+    }
+    return post_launch("cm_unpack_bits");
 }
 
 extern "C" int cm_metrics_dense(const float* pred, const float* gt, int batch, int64_t pixels, float threshold,

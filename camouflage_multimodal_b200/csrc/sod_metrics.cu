@@ -24,7 +24,7 @@
 
 namespace cm {
 
-constexpr int SOD_CHUNKS = 64;   // blocks per image in the two pixel passes (256 x 256: four pixels per thread, all in flight together)
+constexpr int SOD_CHUNKS = 16;   // blocks per image in the two pixel passes (256 x 256: sixteen pixels per thread, four in flight together)
 constexpr int SOD_ILP = 4;
 constexpr int SOD_P1 = 8;        // doubles per chunk, pass 1
 constexpr int SOD_P2 = 18;       // doubles per chunk, pass 2
@@ -33,8 +33,8 @@ constexpr int SOD_PARTIAL = 2 * SOD_KEYS + 512;
 constexpr double SOD_EPS = 2.220446049250313e-16;
 
 struct SodWs {
-    double *p1, *p2, *p4, *curves, *shift;
-    int* hist;
+    double *p1, *p2, *p4, *curves, *shift, *tot1, *tot2;
+    int* hist;   // [B,512] histograms, then [2B + 1] completion counters (zeroed together)
     short *col_d, *col_y;
     int *d2, *near;
     size_t total;
@@ -50,7 +50,9 @@ static SodWs carve_sod(void* ws, int batch, int h, int w) {
     r.p4 = c.take<double>((size_t)batch * r.wf_tiles * 2);
     r.curves = c.take<double>((size_t)batch * 512);
     r.shift = c.take<double>((size_t)batch * 4);
-    r.hist = c.take<int>((size_t)batch * 512);
+    r.tot1 = c.take<double>((size_t)batch * SOD_P1);
+    r.tot2 = c.take<double>((size_t)batch * SOD_P2);
+    r.hist = c.take<int>((size_t)batch * 512 + 2 * (size_t)batch + 1);
     r.col_d = c.take<short>(n);
     r.col_y = c.take<short>(n);
     r.d2 = c.take<int>(n);
@@ -120,9 +122,28 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* s_red /* [8 *
     }
 }
 
+// The block that finishes an image's last chunk adds the chunk partials up in chunk order (so the result does not
+// depend on which block that is) and publishes the image totals.  `counter` is zeroed before the launch.
+template <int NV>
+__device__ __forceinline__ void sod_publish_totals(const double* __restrict__ part, int b, int* counter, double* __restrict__ tot) {
+    __shared__ int s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(counter, 1) == SOD_CHUNKS - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x < NV) {
+        double t = 0.0;
+#pragma unroll 4
+        for (int c = 0; c < SOD_CHUNKS; ++c) t += __ldcg(part + ((size_t)b * SOD_CHUNKS + c) * NV + threadIdx.x);
+        tot[(size_t)b * NV + threadIdx.x] = t;
+    }
+}
+
 // grid (SOD_CHUNKS, B), block 256
 __global__ void __launch_bounds__(256) sod_pass1_kernel(const SodSrc src, const uint8_t* __restrict__ gt, int H, int W, double* __restrict__ p1,
-                                                        int* __restrict__ hist) {
+                                                        int* __restrict__ hist, int* __restrict__ counters, double* __restrict__ tot1) {
     __shared__ int s_hist[512];
     __shared__ double s_red[8 * SOD_P1];
     const int b = blockIdx.y, HW = H * W, lane = threadIdx.x & 31;
@@ -132,8 +153,7 @@ __global__ void __launch_bounds__(256) sod_pass1_kernel(const SodSrc src, const 
     __syncthreads();
     // v: n_fg, sum y_fg, sum x_fg, sum p (fg), sum p^2 (fg), sum (1-p) (bg), sum (1-p)^2 (bg), sum p
     double v[SOD_P1] = {0, 0, 0, 0, 0, 0, 0, 0};
-    int n_fg = 0;
-    long long sy = 0, sx = 0;
+    int n_fg = 0, sy = 0, sx = 0;   // a chunk holds < 2^31 / max(H, W) pixels
     const int per = (HW + SOD_CHUNKS - 1) / SOD_CHUNKS, i0 = blockIdx.x * per, i1 = min(i0 + per, HW);
     for (int base = i0; base < i1; base += 256 * SOD_ILP) {   // whole warps stay in the loop: the histogram vote needs all lanes
         float pv[SOD_ILP];
@@ -152,24 +172,25 @@ __global__ void __launch_bounds__(256) sod_pass1_kernel(const SodSrc src, const 
             const bool fg = in && gv[u] >= 128;
             int q = (int)(p * 255.0);
             q = min(max(q, 0), 255);
-            // a painted mask is constant over runs of pixels: one shared-memory atomic per distinct (class, bin) of the warp
+            // a painted mask is constant over runs of pixels: one shared-memory atomic per run of equal (class, bin) keys
             const int key = in ? (fg ? 0 : 256) + q : -1;
-            const unsigned peers = __match_any_sync(0xffffffffu, key);
-            if (in && lane == __ffs(peers) - 1) atomicAdd(&s_hist[key], __popc(peers));
-            if (!in) continue;
-            v[7] += p;
-            if (fg) {
-                const int y = i / W;
-                ++n_fg;
-                sy += y;
-                sx += i - y * W;
-                v[3] += p;
-                v[4] += p * p;
-            } else {
-                const double o = 1.0 - p;
-                v[5] += o;
-                v[6] += o * o;
+            const int prev = __shfl_up_sync(0xffffffffu, key, 1);
+            const unsigned heads = __ballot_sync(0xffffffffu, lane == 0 || key != prev);
+            if (key >= 0 && ((heads >> lane) & 1u)) {
+                const unsigned later = lane == 31 ? 0u : heads >> (lane + 1);
+                atomicAdd(&s_hist[key], later ? __ffs(later) : 32 - lane);
             }
+            if (!in) continue;
+            const int y = i / W;
+            v[7] += p;
+            n_fg += fg;
+            sy += fg ? y : 0;
+            sx += fg ? i - y * W : 0;
+            v[3] += fg ? p : 0.0;
+            v[4] += fg ? p * p : 0.0;
+            const double o = 1.0 - p;
+            v[5] += fg ? 0.0 : o;
+            v[6] += fg ? 0.0 : o * o;
         }
     }
     v[0] = (double)n_fg;
@@ -184,19 +205,9 @@ __global__ void __launch_bounds__(256) sod_pass1_kernel(const SodSrc src, const 
     __syncthreads();
     for (int i = threadIdx.x; i < 512; i += 256)
         if (s_hist[i]) atomicAdd(&hist[(size_t)b * 512 + i], s_hist[i]);
+    sod_publish_totals<SOD_P1>(p1, b, counters + b, tot1);
 }
 
-// image totals of pass 1 (fixed chunk order), computed by the first NV threads of the block into shared memory:
-// thread k sums value k over the chunks (NV independent chains of SOD_CHUNKS loads instead of one chain of NV * SOD_CHUNKS)
-template <int NV>
-__device__ __forceinline__ void sod_chunk_totals(const double* __restrict__ part, int b, double* s_tot) {
-    if (threadIdx.x < NV) {
-        double t = 0.0;
-        for (int c = 0; c < SOD_CHUNKS; ++c) t += part[((size_t)b * SOD_CHUNKS + c) * NV + threadIdx.x];
-        s_tot[threadIdx.x] = t;
-    }
-    __syncthreads();
-}
 // GT centroid the way the published code rounds it: round-half-even of the mean, + 1; image centre when the GT is empty
 __device__ __forceinline__ void sod_centroid(const double* t, int H, int W, int* cx, int* cy) {
     if (t[0] == 0.0) {
@@ -211,14 +222,16 @@ __device__ __forceinline__ void sod_centroid(const double* t, int H, int W, int*
 // grid (SOD_CHUNKS, B), block 256.  Per quadrant k (LT, RT, LB, RB): sum p', sum p'^2, sum p' g (p' = p - corner pixel),
 // sum g; then adaptive-threshold tp, fp.
 __global__ void __launch_bounds__(256) sod_pass2_kernel(const SodSrc src, const uint8_t* __restrict__ gt, int H, int W,
-                                                        const double* __restrict__ p1, double* __restrict__ p2, double* __restrict__ shift) {
+                                                        const double* __restrict__ tot1, double* __restrict__ p2, double* __restrict__ shift, int* __restrict__ counters,
+                                                        double* __restrict__ tot2) {
     __shared__ double s_red[8 * SOD_P2];
     __shared__ double s_tot[SOD_P1];
     __shared__ double s_shift[4];
     const int b = blockIdx.y, HW = H * W;
     const SodPix px(src, b, (size_t)HW);
     const uint8_t* g = gt + (size_t)b * HW;
-    sod_chunk_totals<SOD_P1>(p1, b, s_tot);
+    if (threadIdx.x < SOD_P1) s_tot[threadIdx.x] = tot1[(size_t)b * SOD_P1 + threadIdx.x];
+    __syncthreads();
     int cx, cy;
     sod_centroid(s_tot, H, W, &cx, &cy);
     const double thr = fmin(2.0 * (s_tot[7] / (double)HW), 1.0);
@@ -251,15 +264,13 @@ __global__ void __launch_bounds__(256) sod_pass2_kernel(const SodSrc src, const 
             const bool fg = gv[u] >= 128;
             const int y = i / W, x = i - y * W;
             const int k = (y >= cy ? 2 : 0) + (x >= cx ? 1 : 0);
-            const double d = p - s_shift[k];
-            // branch-free scatter into the quadrant's slots
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const double m = (j == k) ? 1.0 : 0.0;
-                v[3 * j] += m * d;
-                v[3 * j + 1] += m * d * d;
-                v[3 * j + 2] += (fg && j == k) ? d : 0.0;
-                gq[j] += (fg && j == k);
+            const double d = p - s_shift[k], dd = d * d, dg = fg ? d : 0.0;
+            // a warp's 32 consecutive pixels share the quadrant except where they straddle cx: near-uniform branches
+            switch (k) {
+                case 0: v[0] += d; v[1] += dd; v[2] += dg; gq[0] += fg; break;
+                case 1: v[3] += d; v[4] += dd; v[5] += dg; gq[1] += fg; break;
+                case 2: v[6] += d; v[7] += dd; v[8] += dg; gq[2] += fg; break;
+                default: v[9] += d; v[10] += dd; v[11] += dg; gq[3] += fg; break;
             }
             if (p >= thr) {
                 tpa += fg;
@@ -277,6 +288,7 @@ __global__ void __launch_bounds__(256) sod_pass2_kernel(const SodSrc src, const 
 #pragma unroll
         for (int k = 0; k < SOD_P2; ++k) o[k] = v[k];
     }
+    sod_publish_totals<SOD_P2>(p2, b, counters + b, tot2);
 }
 
 // ---------------------------------------------------------------------------------------------- weighted F: feature transform
@@ -431,25 +443,35 @@ __device__ __forceinline__ double sod_s_object(double sum, double sum2, double n
 }
 
 // one block of 256 threads per image: thread t owns curve entry t (threshold q >= 255 - t)
-__global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restrict__ p1, const double* __restrict__ p2, const double* __restrict__ shift,
+__global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restrict__ tot1, const double* __restrict__ tot2, const double* __restrict__ shift,
                                                            const double* __restrict__ p4, int wf_tiles, const int* __restrict__ hist, int H, int W,
                                                            double beta2_f, double beta2_wf, double* __restrict__ per_image,
-                                                           double* __restrict__ curves) {
-    __shared__ int s_tp[256], s_fp[256];
+                                                           double* __restrict__ curves, int* __restrict__ done_counter, int batch,
+                                                           double* __restrict__ partial) {
+    __shared__ int s_tp[256], s_fp[256], s_wtp[8], s_wfp[8], s_last;
     __shared__ double s_f[256], s_e[256], s_fm[256], s_em[256];
     __shared__ double s_tot[SOD_P1], s_q[SOD_P2], s_wf[2];
     const int b = blockIdx.x, t = threadIdx.x;
     const double n = (double)H * (double)W;
     s_tp[t] = hist[(size_t)b * 512 + 255 - t];
     s_fp[t] = hist[(size_t)b * 512 + 256 + 255 - t];
-    sod_chunk_totals<SOD_P1>(p1, b, s_tot);   // (syncs)
-    sod_chunk_totals<SOD_P2>(p2, b, s_q);
-    for (int o = 1; o < 256; o <<= 1) {   // inclusive scan (integers: order-free)
-        const int a = t >= o ? s_tp[t - o] : 0, c = t >= o ? s_fp[t - o] : 0;
+    if (t < SOD_P1) s_tot[t] = tot1[(size_t)b * SOD_P1 + t];
+    if (t >= 32 && t < 32 + SOD_P2) s_q[t - 32] = tot2[(size_t)b * SOD_P2 + t - 32];
+    {   // inclusive scan of the two histograms (integers: order-free): warp scans + the warp totals
+        const int lane = t & 31, wid = t >> 5;
+        int a = warp_scan_incl(s_tp[t], lane), c = warp_scan_incl(s_fp[t], lane);
+        if (lane == 31) {
+            s_wtp[wid] = a;
+            s_wfp[wid] = c;
+        }
         __syncthreads();
-        s_tp[t] += a;
-        s_fp[t] += c;
+        for (int wi = 0; wi < wid; ++wi) {
+            a += s_wtp[wi];
+            c += s_wfp[wi];
+        }
         __syncthreads();
+        s_tp[t] = a;
+        s_fp[t] = c;
     }
     const double n_fg = s_tot[0];
     const double f = sod_f_from_counts((double)s_tp[t], (double)s_fp[t], n_fg, beta2_f);
@@ -511,7 +533,7 @@ __global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restr
         }
     }
     __syncthreads();
-    if (t != 0) return;
+    if (t == 0) {
     const double fsum = s_f[0], esum = s_e[0], fmx = s_fm[0], emx = s_em[0];
     const double* tot = s_tot;
     const double* q = s_q;
@@ -570,23 +592,27 @@ __global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restr
     o[5] = fsum / 256.0;
     o[6] = fmx;
     o[7] = wf;
-}
-
-// partial [16 + 512]: sum and sum of squares of the 8 keys over the batch, then the batch sums of the F and E curves
-__global__ void sod_partial_kernel(const double* __restrict__ per_image, const double* __restrict__ curves, int batch, double* __restrict__ partial) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= SOD_PARTIAL) return;
-    double s = 0.0;
-    if (i < 2 * SOD_KEYS) {
-        const int k = i % SOD_KEYS;
-        for (int b = 0; b < batch; ++b) {
-            const double v = per_image[(size_t)b * SOD_KEYS + k];
-            s += i < SOD_KEYS ? v : v * v;
-        }
-    } else {
-        for (int b = 0; b < batch; ++b) s += curves[(size_t)b * 512 + (i - 2 * SOD_KEYS)];
     }
-    partial[i] = s;
+    // ---- the last image's block adds the batch up in image order: partial [16 + 512]
+    __threadfence();
+    __syncthreads();
+    if (t == 0) s_last = atomicAdd(done_counter, 1) == batch - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (int i = t; i < SOD_PARTIAL; i += 256) {
+        double sum = 0.0;
+        if (i < 2 * SOD_KEYS) {
+            const int k = i % SOD_KEYS;
+            for (int bb = 0; bb < batch; ++bb) {
+                const double v = __ldcg(per_image + (size_t)bb * SOD_KEYS + k);
+                sum += i < SOD_KEYS ? v : v * v;
+            }
+        } else {
+            for (int bb = 0; bb < batch; ++bb) sum += __ldcg(curves + (size_t)bb * 512 + (i - 2 * SOD_KEYS));
+        }
+        partial[i] = sum;
+    }
 }
 
 }  // namespace cm
@@ -602,20 +628,22 @@ static int sod_metrics_impl(const cm::SodSrc& src, const uint8_t* gt, int batch,
     CM_DEVICE_OR_RETURN();
     CM_REQUIRE(gt && workspace && per_image && partial, "%s: NULL pointer", who);
     CM_REQUIRE(batch > 0 && batch <= 65535 && h > 0 && w > 0 && h < 32767 && w < 32767 && (long long)h * w < (1ll << 30), "%s: bad shape", who);
+    CM_REQUIRE(((long long)h * w / SOD_CHUNKS + 1) * (h > w ? h : w) < (1ll << 31), "%s: image too large for the 32-bit centroid sums of a chunk", who);
     SodWs ws = carve_sod(workspace, batch, h, w);
     if (workspace_bytes < ws.total) {
         set_error("%s: workspace %zu < %zu bytes", who, workspace_bytes, ws.total);
         return CM_ERR_WORKSPACE;
     }
     cudaStream_t st = as_stream(stream);
-    cudaMemsetAsync(ws.hist, 0, (size_t)batch * 512 * sizeof(int), st);
+    cudaMemsetAsync(ws.hist, 0, ((size_t)batch * 512 + 2 * (size_t)batch + 1) * sizeof(int), st);
+    int* counters = ws.hist + (size_t)batch * 512;   // [B] pass 1, [B] pass 2, [1] finalize
     {
         CM_TIMED("sod_pass1", st);
-        sod_pass1_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.p1, ws.hist);
+        sod_pass1_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.p1, ws.hist, counters, ws.tot1);
     }
     {
         CM_TIMED("sod_pass2", st);
-        sod_pass2_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.p1, ws.p2, ws.shift);
+        sod_pass2_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.tot1, ws.p2, ws.shift, counters + batch, ws.tot2);
     }
     if (with_weighted_f) {
         Gauss7 gk;   // Matlab fspecial('gaussian', 7, 5)
@@ -638,9 +666,8 @@ static int sod_metrics_impl(const cm::SodSrc& src, const uint8_t* gt, int batch,
     }
     {
         CM_TIMED("sod_finalize", st);
-        sod_finalize_kernel<<<batch, 256, 0, st>>>(ws.p1, ws.p2, ws.shift, with_weighted_f ? ws.p4 : nullptr, ws.wf_tiles, ws.hist, h, w, 0.3, 1.0,
-                                                   per_image, ws.curves);
-        sod_partial_kernel<<<ceil_div(SOD_PARTIAL, 128), 128, 0, st>>>(per_image, ws.curves, batch, partial);
+        sod_finalize_kernel<<<batch, 256, 0, st>>>(ws.tot1, ws.tot2, ws.shift, with_weighted_f ? ws.p4 : nullptr, ws.wf_tiles, ws.hist, h, w, 0.3, 1.0,
+                                                   per_image, ws.curves, counters + 2 * batch, batch, partial);
     }
     return post_launch(who);
 }

@@ -66,7 +66,8 @@ class EvalPipeline:
 
     def run(self, images, labels, canny, gt):
         """Device inputs: images [B,H,W,3] f32 (or uint8 = byte/255), labels [B,H,W] i32 (or int16), canny [B,H,W] u8,
-        gt [B,H,W] u8.
+        gt [B,H,W] u8.  ``canny`` / ``gt`` may instead be bit-packed ``[B, H*W/8]`` uint8 (one bit per pixel,
+        ``pack_mask_bits``; a set gt bit means 255): they are unpacked on the device first (``cm_unpack_bits``).
         Returns a dict of device tensors (valid until the next call).  ``out["status"]`` is the graph build's overflow
         word ([1] i32, non-zero = a label >= label_cap was dropped or the node / edge capacity truncated the graph, see
         ``check_status``): the run itself never synchronises, so the caller reads it with its results --
@@ -83,6 +84,20 @@ class EvalPipeline:
         B, H, W, _ = images.shape
         dev = images.device
         self._alloc(B, H, W, dev)
+        if canny.dim() == 2 or gt.dim() == 2:      # bit-packed masks: one bit per pixel over PCIe, bytes again here
+            for name, t, one in (("canny", canny, 1), ("gt", gt, 255)):
+                if t.dim() != 2:
+                    continue
+                if (H * W) % 8 or tuple(t.shape) != (B, H * W // 8) or t.dtype != torch.uint8:
+                    raise ValueError(f"packed {name} must be [B, H*W/8] uint8, got {tuple(t.shape)} {t.dtype}")
+                buf = self._bufs.get("unpacked_" + name)
+                if buf is None or buf.shape != (B, H, W):
+                    buf = self._bufs["unpacked_" + name] = torch.empty((B, H, W), dtype=torch.uint8, device=dev)
+                _lib.check(lib.cm_unpack_bits(_lib.ptr(t.contiguous()), t.numel(), one, _lib.ptr(buf), _lib.stream_ptr(dev)), "cm_unpack_bits")
+                if name == "canny":
+                    canny = buf
+                else:
+                    gt = buf
         # host-side label maps travel as int16: with uint8 images the int16 kernels read them as they are, otherwise they
         # are widened once on the device
         i16_direct = labels.dtype == torch.int16 and images.dtype == torch.uint8 and W % 8 == 0 and labels.data_ptr() % 16 == 0
@@ -164,13 +179,27 @@ def check_status(status: int, what: str = "region-graph build") -> None:
         raise _lib.CmError(f"{what} overflow (status {status}): {names}")
 
 
+def pack_mask_bits(mask: torch.Tensor) -> torch.Tensor:
+    """``[B,H,W]`` mask (any non-zero = set) -> ``[B, H*W/8]`` uint8, bit i of byte j = pixel 8 j + i (little-endian bit
+    order, what ``cm_unpack_bits`` reads).  Host-side helper for binary masks (a Canny map, a {0,255} ground truth)."""
+    import numpy as np
+    m = mask.detach().cpu().numpy() != 0
+    return torch.from_numpy(np.packbits(m.reshape(m.shape[0], -1), axis=1, bitorder="little"))
+
+
 class BatchBuffer:
     """The four inputs of one batch as views of ONE flat byte buffer (pinned host memory or device memory), each at a
     256-byte aligned offset: a host batch laid out like this goes to the device as a single copy (54.7 GB/s for
-    14.7 MB on this machine's PCIe link against 50-54 GB/s for four separate 2-6 MB copies)."""
+    14.7 MB on this machine's PCIe link against 50-54 GB/s for four separate 2-6 MB copies).  ``packed_masks``: the
+    Canny map and the ground truth travel one bit per pixel (``[B, H*W/8]`` uint8; 7 -> 5.25 bytes per pixel with uint8
+    images + int16 labels) -- for binary masks only: a set gt bit is read as 255."""
 
-    def __init__(self, B, H, W, image_dtype=torch.float32, label_dtype=torch.int32, device=None):
-        shapes = (((B, H, W, 3), image_dtype), ((B, H, W), label_dtype), ((B, H, W), torch.uint8), ((B, H, W), torch.uint8))
+    def __init__(self, B, H, W, image_dtype=torch.float32, label_dtype=torch.int32, device=None, packed_masks=False):
+        self.packed_masks = bool(packed_masks)
+        mshape = (B, H * W // 8) if packed_masks else (B, H, W)
+        if packed_masks and (H * W) % 8:
+            raise ValueError("packed masks need H*W % 8 == 0")
+        shapes = (((B, H, W, 3), image_dtype), ((B, H, W), label_dtype), (mshape, torch.uint8), (mshape, torch.uint8))
         offs, total = [], 0
         for shp, dt in shapes:
             offs.append(total)
@@ -190,21 +219,22 @@ class BatchBuffer:
         self.payload_bytes = sum(v.numel() * v.element_size() for v in views)
 
     def fill(self, images, labels, canny, gt):
+        """Copy a batch in; with ``packed_masks`` byte masks ``[B,H,W]`` are bit-packed on the way (host work)."""
         self.images.copy_(images)
         self.labels.copy_(labels)
-        self.canny.copy_(canny)
-        self.gt.copy_(gt)
+        self.canny.copy_(pack_mask_bits(canny) if self.packed_masks and canny.dim() == 3 else canny)
+        self.gt.copy_(pack_mask_bits(gt) if self.packed_masks and gt.dim() == 3 else gt)
         return self
 
 
 class HostStager:
     """Pinned host buffers + device buffers for one batch: the host-facing entry of the pipeline."""
 
-    def __init__(self, B, H, W, device, image_dtype=torch.float32, label_dtype=torch.int32):
+    def __init__(self, B, H, W, device, image_dtype=torch.float32, label_dtype=torch.int32, packed_masks=False):
         self.dev = device
         pin = dict(pin_memory=True)
-        self.h_batch = BatchBuffer(B, H, W, image_dtype, label_dtype)
-        self.d_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, device=device)
+        self.h_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, packed_masks=packed_masks)
+        self.d_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, device=device, packed_masks=packed_masks)
         self.h_images, self.h_labels, self.h_canny, self.h_gt = (self.h_batch.images, self.h_batch.labels, self.h_batch.canny,
                                                                  self.h_batch.gt)
         self.d_images, self.d_labels, self.d_canny, self.d_gt = (self.d_batch.images, self.d_batch.labels, self.d_batch.canny,
@@ -217,10 +247,7 @@ class HostStager:
         self.d2h_bytes = sum(t.numel() * t.element_size() for t in (self.h_mask_out, self.h_per_image, self.h_status, self.h_per_image_sod))
 
     def fill(self, batch):
-        self.h_images.copy_(batch.images)
-        self.h_labels.copy_(batch.labels)
-        self.h_canny.copy_(batch.canny)
-        self.h_gt.copy_(batch.gt)
+        self.h_batch.fill(batch.images, batch.labels, batch.canny, batch.gt)
 
     def step(self, pipe: EvalPipeline):
         """One end-to-end step from pinned host memory: H2D (one copy), the whole path, D2H of logits + metrics."""
@@ -246,13 +273,13 @@ class HostPipeline:
     kernels, slots sharing a pipeline are serialised through ``pipe_done`` events (they share its buffers)."""
 
     def __init__(self, pipe, B, H, W, device, slots: int = 2, use_graph: bool = True, image_dtype=torch.float32,
-                 label_dtype=torch.int32):
+                 label_dtype=torch.int32, packed_masks: bool = False):
         pipes = list(pipe) if isinstance(pipe, (list, tuple)) else [pipe]
         self.pipes, self.dev = pipes, device
         self.pipe_done = [torch.cuda.Event() for _ in pipes]
         self.slots = []
         for k in range(slots):
-            st = HostStager(B, H, W, device, image_dtype, label_dtype)
+            st = HostStager(B, H, W, device, image_dtype, label_dtype, packed_masks=packed_masks)
             st.pipe_idx = k % len(pipes)
             st.stream = torch.cuda.Stream(device)
             st.d_labels.fill_(1)
@@ -269,7 +296,7 @@ class HostPipeline:
         """A pinned host batch in the layout of the device slots: fill its ``images / labels / canny / gt`` views (e.g.
         decode straight into them) and pass it to ``submit`` -- it then crosses PCIe as ONE copy."""
         st = self.slots[0]
-        return BatchBuffer(*st.h_images.shape[:3], st.h_images.dtype, st.h_labels.dtype)
+        return BatchBuffer(*st.h_images.shape[:3], st.h_images.dtype, st.h_labels.dtype, packed_masks=st.h_batch.packed_masks)
 
     def submit(self, i, h_images, h_labels=None, h_canny=None, h_gt=None):
         """Queue batch ``i``: a ``BatchBuffer`` from ``host_batch()`` (one H2D copy) or four pinned host tensors (four

@@ -326,6 +326,10 @@ int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int batch, int h,
                      const float* mask_prob, const int32_t* node_ptr, const int32_t* id_of_label,
                      int label_cap, float threshold, float* pred_mask, int64_t* counts, double* abs_err,
                      void* stream);
+/* Binary masks that crossed PCIe one BIT per pixel (the Canny map and a {0,255} ground-truth mask are 2 of the 7 bytes
+ * per pixel of the host -> device transfer; packed they are 0.25): bit i of byte j (little-endian bit order,
+ * numpy.packbits(bitorder="little")) -> out[8 j + i] = one_value or 0.  out 8-byte aligned, 8 * n_bytes bytes. */
+int cm_unpack_bits(const uint8_t* bits, int64_t n_bytes, int one_value, uint8_t* out, void* stream);
 /* Same reductions for a caller-supplied float prediction and float ground truth (the literal signature of
  * utils/metrics.py:evaluate_segmentation: two arrays, one threshold). */
 int cm_metrics_dense(const float* pred, const float* gt, int batch, int64_t pixels, float threshold,

@@ -238,3 +238,26 @@ def test_second_device_with_current_device_left_at_zero(models):
     assert torch.cuda.current_device() == 0
     torch.cuda.synchronize(1)
     assert torch.equal(out1["mask_out"].cpu(), ref[0]) and torch.equal(out1["per_image"].cpu(), ref[1])
+
+
+def test_bit_packed_masks_equal_byte_masks(models):
+    """Canny + ground truth sent one bit per pixel (BatchBuffer(packed_masks=True) -> cm_unpack_bits inside the captured
+    step) give bit-identical results to the byte form."""
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, HostPipeline, pack_mask_bits
+    gnn, det, kg, _, _ = models
+    B = 4
+    dev = torch.device("cuda")
+    b = synth.make_batch(21, B, seed=1234).as_decoded()
+    d = b.to("cuda")
+    ref = EvalPipeline(gnn, det, kg, label_cap=544, lane=20).run(d.images, d.labels, d.canny, d.gt)
+    ref_mask, ref_per, ref_sod = ref["mask_out"].cpu(), ref["per_image"].cpu(), ref["per_image_sod"].cpu()
+    packed = EvalPipeline(gnn, det, kg, label_cap=544, lane=21).run(d.images, d.labels, pack_mask_bits(b.canny).cuda(), pack_mask_bits(b.gt).cuda())
+    assert torch.equal(packed["mask_out"].cpu(), ref_mask) and torch.equal(packed["per_image"].cpu(), ref_per)
+    hp = HostPipeline(EvalPipeline(gnn, det, kg, label_cap=544, lane=22), B, 256, 256, dev, slots=2, use_graph=True,
+                      image_dtype=torch.uint8, label_dtype=torch.int16, packed_masks=True)
+    hb = hp.host_batch().fill(b.images, b.labels, b.canny, b.gt)
+    assert hb.payload_bytes == B * 65536 * (3 + 2) + 2 * B * 8192
+    st = hp.submit(0, hb)
+    hp.synchronize()
+    assert torch.equal(st.h_mask_out, ref_mask) and torch.equal(st.h_per_image, ref_per)
+    assert torch.equal(st.h_per_image_sod[:, :7], ref_sod[:, :7])
