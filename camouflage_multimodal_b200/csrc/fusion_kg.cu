@@ -11,6 +11,7 @@
 //                  consecutive outputs.
 //   kg2rg_weights  (only when the caller asked for attention maps) head-averaged probabilities from S2 and the
 //                  merged statistics.
+#include <cooperative_groups.h>
 #include <math.h>
 
 #include <algorithm>
@@ -265,6 +266,256 @@ __global__ void __launch_bounds__(1024) graph_tail_kernel(const GraphTailArgs a)
     }
 }
 
+// ------------------------------------------------------------------------------------------------ fused KG-side tail
+// A cluster of 4 CTAs per image for everything after the node-side kernel: merge of the kg->rg chunk partials -> ctx2
+// [K,256]; z0 = LN(kp + ctx2 Wo^T + bo); z = z0 + W2 relu(W1 z0 + b1) + b2 (fusion_model.py:130-131); mean over the K
+// rows (:135); fusion MLP (:138-139); the four heads (:239-242).  Each CTA owns a quarter of every layer's OUTPUT columns
+// (so a quarter of its weights: the layer chain is bound by how fast one SM can pull weights out of L2) and broadcasts
+// its slice of the activations into the shared memory of its three peers (DSMEM), one cluster barrier per layer.
+// The three K-row GEMMs are 16-row problems (K <= 16 rows, zero padded): warp-level mma.sync m16n8k16 tiles -- a
+// 128-row tcgen05 tile would be 90 % padding -- with the activations split into fp16 hi + lo parts (two MMAs against
+// the same fp16 weight fragment, fp32 accumulation) and the weight fragments read straight from the folded fp16 copies
+// in L2.  Replaces kg_merge + fusion_kgrows + graph_tail (19 + 37 + 30 us per batch of 32).
+namespace cg = cooperative_groups;
+constexpr int KT_CL = 4, KT_THREADS = 256, KT_LDA = 256 + 8, KT_LDH = 512 + 8;   // +8 halves: rows land on different banks
+struct KtSmem {
+    float sc[KG_MAX_CHUNKS * 128];
+    float z[16 * 256];                 // pre-LN rows, then z0 (fp32), then this CTA's columns of z
+    __half a_hi[16 * KT_LDA], a_lo[16 * KT_LDA];
+    __half h_hi[16 * KT_LDH], h_lo[16 * KT_LDH];
+    float both[512], f1[256], fz[256], hid[128];
+};
+
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void split2(float v0, float v1, __half2* hi, __half2* lo) {
+    const __half h0 = __float2half_rn(v0), h1 = __float2half_rn(v1);
+    *hi = __halves2half2(h0, h1);
+    *lo = __halves2half2(__float2half_rn(v0 - __half2float(h0)), __float2half_rn(v1 - __half2float(h1)));
+}
+// C[16, n) += A[16, KD] W[n, KD]^T for the n-tiles nt0 + warp, nt0 + warp + nwarps, ... < nt1; A = hi + lo in shared
+// memory (row stride lda halves), W fp16 [N, KD] row-major in global memory.  epi(row, col, v0, v1) gets column pairs.
+template <int KD, typename Epi>
+__device__ __forceinline__ void kt_gemm16(const __half* a_hi, const __half* a_lo, int lda, const op_t* __restrict__ W, int nt0, int nt1, Epi epi) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5, g = lane >> 2, t = lane & 3;
+    for (int nt = nt0 + warp; nt < nt1; nt += nwarps) {
+        const uint32_t* wrow = reinterpret_cast<const uint32_t*>(W + (size_t)(nt * 8 + g) * KD);
+        float c[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int kb = 0; kb < KD / 256; ++kb) {   // 256 columns of K at a time: 32 weight fragments in flight before the first MMA
+            uint32_t b[16][2];
+#pragma unroll
+            for (int ks = 0; ks < 16; ++ks) {
+                b[ks][0] = __ldg(wrow + (kb * 16 + ks) * 8 + t);
+                b[ks][1] = __ldg(wrow + (kb * 16 + ks) * 8 + 4 + t);
+            }
+#pragma unroll
+            for (int ks = 0; ks < 16; ++ks) {
+                const int k0 = (kb * 16 + ks) * 16 + 2 * t;
+                uint32_t ah[4], al[4];
+                ah[0] = *reinterpret_cast<const uint32_t*>(a_hi + g * lda + k0);
+                ah[1] = *reinterpret_cast<const uint32_t*>(a_hi + (g + 8) * lda + k0);
+                ah[2] = *reinterpret_cast<const uint32_t*>(a_hi + g * lda + k0 + 8);
+                ah[3] = *reinterpret_cast<const uint32_t*>(a_hi + (g + 8) * lda + k0 + 8);
+                al[0] = *reinterpret_cast<const uint32_t*>(a_lo + g * lda + k0);
+                al[1] = *reinterpret_cast<const uint32_t*>(a_lo + (g + 8) * lda + k0);
+                al[2] = *reinterpret_cast<const uint32_t*>(a_lo + g * lda + k0 + 8);
+                al[3] = *reinterpret_cast<const uint32_t*>(a_lo + (g + 8) * lda + k0 + 8);
+                mma16816(c, ah, b[ks][0], b[ks][1]);
+                mma16816(c, al, b[ks][0], b[ks][1]);
+            }
+        }
+        epi(g, nt * 8 + 2 * t, c[0], c[1]);
+        epi(g + 8, nt * 8 + 2 * t, c[2], c[3]);
+    }
+}
+
+__global__ void __cluster_dims__(KT_CL, 1, 1) __launch_bounds__(KT_THREADS) kg_tail_kernel(const KgTailArgs a) {
+    extern __shared__ __align__(16) uint8_t kt_raw[];
+    KtSmem& sm = *reinterpret_cast<KtSmem*>(kt_raw);
+    cg::cluster_group cluster = cg::this_cluster();
+    constexpr int D = 256, QD = D / KT_CL;   // this CTA's 64 columns of every 256-wide layer
+    const int q = (int)cluster.block_rank(), b = blockIdx.y, tid = threadIdx.x, nt = blockDim.x, warp = tid >> 5, lane = tid & 31;
+    KtSmem* peer[KT_CL];
+#pragma unroll
+    for (int r = 0; r < KT_CL; ++r) peer[r] = cluster.map_shared_rank(&sm, r);
+    const int K = a.n_kg, gs = a.gs, heads = a.heads, n_chunks = KG_MAX_CHUNKS;
+    const int n0 = a.node_ptr[b], nb = a.node_ptr[b + 1] - n0;
+    const int per = ((nb + n_chunks - 1) / n_chunks + KG_SUB - 1) / KG_SUB * KG_SUB;
+    const int nch = nb > 0 ? (nb + per - 1) / per : 0;
+    const size_t slot0 = (size_t)b * n_chunks;
+    // ---- merge statistics of the chunk partials per folded key slot (every CTA: 128 threads, 2 x 16 loads)
+    if (tid < 128) {
+        float pm[KG_MAX_CHUNKS], pl[KG_MAX_CHUNKS];
+#pragma unroll
+        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) {
+            pm[ch] = ch < nch ? a.part_m[(slot0 + ch) * 128 + tid] : -INFINITY;
+            pl[ch] = ch < nch ? a.part_l[(slot0 + ch) * 128 + tid] : 0.f;
+        }
+        float M = -INFINITY;
+#pragma unroll
+        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) M = fmaxf(M, pm[ch]);
+        float L = 0.f;
+#pragma unroll
+        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch)
+            if (ch < nch) L += pl[ch] * expf(pm[ch] - M);
+        const float inv = L > 0.f ? 1.0f / L : 0.f;
+#pragma unroll
+        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) sm.sc[ch * 128 + tid] = ch < nch ? expf(pm[ch] - M) * inv : 0.f;
+        if (a.stat && q == 0) {
+            a.stat[((size_t)b * 128 + tid) * 2] = M;
+            a.stat[((size_t)b * 128 + tid) * 2 + 1] = inv;
+        }
+    }
+    __syncthreads();
+    // ---- this CTA's 64 columns of ctx2 [16, 256] (rows >= K zero) as fp16 hi / lo, broadcast; its columns of mean_n y
+    const int hd = D / heads;
+    for (int i = tid; i < 16 * (QD / 2); i += nt) {
+        const int k = i / (QD / 2), c = q * QD + (i - k * (QD / 2)) * 2;
+        float s0 = 0.f, s1 = 0.f;
+        if (k < K) {
+            const int j = (c / hd) * gs + k;   // c and c + 1 lie in the same head (hd is even)
+            float2 pv[KG_MAX_CHUNKS];
+#pragma unroll
+            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch)
+                pv[ch] = ch < nch ? *reinterpret_cast<const float2*>(a.part_acc + ((slot0 + ch) * gs + k) * D + c) : make_float2(0.f, 0.f);
+#pragma unroll
+            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) {
+                s0 = fmaf(sm.sc[ch * 128 + j], pv[ch].x, s0);
+                s1 = fmaf(sm.sc[ch * 128 + j], pv[ch].y, s1);
+            }
+        }
+        __half2 hi, lo;
+        split2(s0, s1, &hi, &lo);
+#pragma unroll
+        for (int r = 0; r < KT_CL; ++r) {
+            *reinterpret_cast<__half2*>(peer[r]->a_hi + k * KT_LDA + c) = hi;
+            *reinterpret_cast<__half2*>(peer[r]->a_lo + k * KT_LDA + c) = lo;
+        }
+    }
+    if (tid < QD) {
+        const int c = q * QD + tid;
+        float s = 0.f;
+#pragma unroll
+        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) s += ch < nch ? a.part_y[(slot0 + ch) * D + c] : 0.f;
+        s = nb > 0 ? s / (float)nb : 0.f;
+#pragma unroll
+        for (int r = 0; r < KT_CL; ++r) peer[r]->both[c] = s;
+    }
+    cluster.sync();
+    // ---- pre-LN rows kp + ctx2 Wo^T + bo: this CTA's 64 columns, broadcast
+    kt_gemm16<256>(sm.a_hi, sm.a_lo, KT_LDA, a.wo2, q * (QD / 8), (q + 1) * (QD / 8), [&](int row, int col, float v0, float v1) {
+        const float2 bo = *reinterpret_cast<const float2*>(a.bo2 + col);
+        float2 kp = make_float2(0.f, 0.f);
+        if (row < K) kp = *reinterpret_cast<const float2*>(a.kp + (size_t)row * D + col);
+        const float2 v = make_float2(v0 + bo.x + kp.x, v1 + bo.y + kp.y);
+#pragma unroll
+        for (int r = 0; r < KT_CL; ++r) *reinterpret_cast<float2*>(peer[r]->z + row * D + col) = v;
+    });
+    cluster.sync();
+    // ---- z0 = LayerNorm(row) (eps 1e-5, biased variance): every CTA normalises all 16 rows for itself, one warp per row
+    for (int row = warp; row < 16; row += nt >> 5) {
+        float x[8], s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            x[j] = sm.z[row * D + lane * 8 + j];
+            s1 += x[j];
+        }
+        s1 = warp_sum(s1);
+        const float mean = s1 * (1.0f / 256.f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s2 = fmaf(x[j] - mean, x[j] - mean, s2);
+        s2 = warp_sum(s2);
+        const float rstd = rsqrtf(s2 * (1.0f / 256.f) + 1e-5f);
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) {
+            const int c = lane * 8 + j;
+            float v0 = 0.f, v1 = 0.f;
+            if (row < K) {
+                v0 = (x[j] - mean) * rstd * a.ln_g[c] + a.ln_b[c];
+                v1 = (x[j + 1] - mean) * rstd * a.ln_g[c + 1] + a.ln_b[c + 1];
+            }
+            sm.z[row * D + c] = v0;
+            sm.z[row * D + c + 1] = v1;
+            split2(v0, v1, reinterpret_cast<__half2*>(sm.a_hi + row * KT_LDA + c), reinterpret_cast<__half2*>(sm.a_lo + row * KT_LDA + c));
+        }
+    }
+    __syncthreads();
+    // ---- hk = relu(z0 W1^T + b1) [16, 512]: this CTA's 128 columns, broadcast as hi / lo
+    kt_gemm16<256>(sm.a_hi, sm.a_lo, KT_LDA, a.w1, q * (2 * QD / 8), (q + 1) * (2 * QD / 8), [&](int row, int col, float v0, float v1) {
+        const float2 b1 = *reinterpret_cast<const float2*>(a.b1 + col);
+        __half2 hi, lo;
+        split2(fmaxf(v0 + b1.x, 0.f), fmaxf(v1 + b1.y, 0.f), &hi, &lo);
+#pragma unroll
+        for (int r = 0; r < KT_CL; ++r) {
+            *reinterpret_cast<__half2*>(peer[r]->h_hi + row * KT_LDH + col) = hi;
+            *reinterpret_cast<__half2*>(peer[r]->h_lo + row * KT_LDH + col) = lo;
+        }
+    });
+    cluster.sync();
+    // ---- z = z0 + hk W2^T + b2, this CTA's 64 columns (in place: each cell is read and written by the same thread)
+    kt_gemm16<512>(sm.h_hi, sm.h_lo, KT_LDH, a.w2, q * (QD / 8), (q + 1) * (QD / 8), [&](int row, int col, float v0, float v1) {
+        const float2 b2 = *reinterpret_cast<const float2*>(a.b2 + col);
+        float2* cell = reinterpret_cast<float2*>(sm.z + row * D + col);
+        const float2 z0 = *cell;
+        *cell = make_float2(z0.x + v0 + b2.x, z0.y + v1 + b2.y);
+    });
+    __syncthreads();
+    if (tid < QD) {   // mean over the KG rows (:135) of this CTA's columns, broadcast
+        const int c = q * QD + tid;
+        float s = 0.f;
+        for (int r = 0; r < K; ++r) s += sm.z[r * D + c];
+        s /= (float)K;
+#pragma unroll
+        for (int r = 0; r < KT_CL; ++r) peer[r]->both[D + c] = s;
+    }
+    cluster.sync();
+    // ---- fusion layer (:138-139): this CTA's 64 outputs of each Linear, fp32 as stored, broadcast
+    const GraphTailArgs& gta = a.gt;
+    {
+        const float* wq = gta.fl1_w + (size_t)q * QD * 2 * D;
+        const float* bq = gta.fl1_b + q * QD;
+        gemv_warp(sm.both, &wq, &bq, QD, sm.hid, QD, 2 * D, true);
+        __syncthreads();
+        if (tid < QD) {
+#pragma unroll
+            for (int r = 0; r < KT_CL; ++r) peer[r]->f1[q * QD + tid] = sm.hid[tid];
+        }
+    }
+    cluster.sync();
+    {
+        const float* wq = gta.fl2_w + (size_t)q * QD * D;
+        const float* bq = gta.fl2_b + q * QD;
+        gemv_warp(sm.f1, &wq, &bq, QD, sm.hid, QD, D, false);
+        __syncthreads();
+        if (tid < QD) {
+            const float v = sm.hid[tid];
+            if (gta.fused) gta.fused[(size_t)b * D + q * QD + tid] = v;
+#pragma unroll
+            for (int r = 0; r < KT_CL; ++r) peer[r]->fz[q * QD + tid] = v;
+        }
+    }
+    cluster.sync();   // the last remote writes: after this barrier a CTA only touches its own shared memory
+    if (!gta.want_heads) return;
+    // ---- head q (:239-242): mask, instance, edge, score -- one head per CTA of the cluster
+    const int H2 = D / 2, nwarps = nt >> 5;
+    gemv_warp(sm.fz, &gta.hw1[q], &gta.hb1[q], H2, sm.hid, H2, D, true);
+    __syncthreads();
+    const int cdim = q < 2 ? gta.num_classes : 1;
+    for (int j = warp; j < cdim; j += nwarps) {
+        const float* wrow = gta.hw2[q] + (size_t)j * H2;
+        float s = 0.f;
+        for (int k = lane; k < H2; k += 32) s = fmaf(sm.hid[k], wrow[k], s);
+        s = warp_sum(s) + gta.hb2[q][j];
+        if (q == 3) s = 1.0f / (1.0f + expf(-s));   // score head ends in nn.Sigmoid (fusion_model.py:229-235)
+        float* out = q == 0 ? gta.mask_out : q == 1 ? gta.inst_out : q == 2 ? gta.edge_out : gta.score_out;
+        if (lane == 0 && out) out[(size_t)b * cdim + j] = s;
+    }
+}
+
 // attn block of image b: [n_kg, N_b] at n_kg * node_ptr[b]; one thread per (node, kg row)
 __global__ void kg2rg_weights_kernel(const float* __restrict__ s2, const float* __restrict__ stat, const int* __restrict__ node_ptr, int n_graphs,
                                      int n_kg, int heads, int gs, float* __restrict__ attn) {
@@ -309,6 +560,23 @@ int launch_kg_merge(const KgSideArgs& k, int D, int heads, int gs, int n_kg, con
     {
         CM_TIMED("kg2rg_weights", st);
         kg2rg_weights_kernel<<<ceil_div((long long)k.node_cap * n_kg, 256), 256, 0, st>>>(k.s2, stat, node_ptr, n_graphs, n_kg, heads, gs, k.attn_kg2rg);
+    }
+    return post_launch("kg2rg_weights");
+}
+
+int launch_kg_tail(const KgTailArgs& a, const KgSideArgs& k, int n_graphs, cudaStream_t st) {
+    static PerDeviceOnce attr;
+    if (attr.first()) cudaFuncSetAttribute(kg_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(KtSmem));
+    {
+        CM_TIMED("kg_tail", st);
+        kg_tail_kernel<<<dim3(KT_CL, n_graphs), KT_THREADS, sizeof(KtSmem), st>>>(a);
+    }
+    int rc = post_launch("kg_tail");
+    if (rc != CM_OK || !k.attn_kg2rg) return rc;
+    {
+        CM_TIMED("kg2rg_weights", st);
+        kg2rg_weights_kernel<<<ceil_div((long long)k.node_cap * a.n_kg, 256), 256, 0, st>>>(k.s2, a.stat, a.node_ptr, n_graphs, a.n_kg, a.heads, a.gs,
+                                                                                           k.attn_kg2rg);
     }
     return post_launch("kg2rg_weights");
 }

@@ -26,6 +26,18 @@ struct GraphTailArgs {
     float *fused, *mask_out, *inst_out, *edge_out, *score_out;
 };
 
+// the fused tail (kg_tail_kernel): hidden 256, K <= 16 rows
+struct KgTailArgs {
+    const float *part_m, *part_l, *part_acc, *part_y;
+    const int* node_ptr;
+    int n_kg, gs, heads;
+    const op_t *wo2, *w1, *w2;            // fp16 [256,256], [512,256], [256,512] (nn.Linear layout)
+    const float *kp, *bo2, *ln_g, *ln_b, *b1, *b2;
+    float* stat;                          // [G,128,2] merged softmax statistics (for the attention map) or NULL
+    GraphTailArgs gt;                     // fusion MLP + heads (z / both unused)
+};
+int launch_kg_tail(const KgTailArgs& a, const KgSideArgs& k, int n_graphs, cudaStream_t st);
+
 int launch_kg2rg_partial(const KgSideArgs& k, int D, int heads, int gs, const int* node_ptr, int n_graphs, cudaStream_t st);
 // ctx2 [G * n_kg, D] fp16, both [G, 2D] (first half), stat [G,128,2] (needed only for the attention map)
 int launch_kg_merge(const KgSideArgs& k, int D, int heads, int gs, int n_kg, const int* node_ptr, int n_graphs, op_t* ctx2, float* both, float* stat,

@@ -14,6 +14,7 @@
 // of a 128-column block, GS = 16 or 32 slots per head, so the fold needs heads * GS <= 128 and n_kg <= GS; other
 // shapes (per-image KG, large KG vocabularies, late fusion) take the general path in fusion.cu.
 #include <math.h>
+#include <stdlib.h>
 
 #include "dense_tc.cuh"
 #include "fusion_kg.cuh"
@@ -245,10 +246,32 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     ks.s2 = w.s2; ks.v2 = w.v2; ks.y = w.y; ks.part_m = w.part_m; ks.part_l = w.part_l; ks.part_acc = w.part_acc; ks.part_y = w.part_y;
     ks.attn_kg2rg = attn_kg2rg; ks.node_cap = M;
     if ((rc = launch_kg2rg_partial(ks, D, p->heads, f.gs, node_ptr, G, st)) != CM_OK) return rc;
+    // ---- mean over kg rows (:135), fusion layer (:138-139), heads (:239-242)
+    GraphTailArgs gt;
+    gt.D = D; gt.n_kg = Kk; gt.num_classes = p->num_classes;
+    gt.want_heads = (mask_out || instance_out || edge_out || score_out) ? 1 : 0;
+    gt.z = w.z; gt.both = w.both;
+    gt.fl1_w = p->fl_w1; gt.fl1_b = p->fl_b1; gt.fl2_w = p->fl_w2; gt.fl2_b = p->fl_b2;
+    for (int t = 0; t < 4; ++t) {
+        gt.hw1[t] = p->head_w1[t]; gt.hb1[t] = p->head_b1[t]; gt.hw2[t] = p->head_w2[t]; gt.hb2[t] = p->head_b2[t];
+        if (gt.want_heads) CM_REQUIRE(p->head_w1[t] && p->head_b1[t] && p->head_w2[t] && p->head_b2[t], "cm_fusion_forward: head %d parameters missing", t);
+    }
+    gt.fused = fused_out; gt.mask_out = mask_out; gt.inst_out = instance_out; gt.edge_out = edge_out; gt.score_out = score_out;
+    const float* kp = reinterpret_cast<const float*>(base + f.kp);
+    if (D == 256 && Kk <= 16 && !getenv("CM_FUSION_UNFUSED_TAIL")) {
+        // one CTA per image: merge + KG-row chain (mma.sync 16-row tiles) + fusion MLP + heads (fusion_kg.cu)
+        KgTailArgs kt;
+        kt.part_m = w.part_m; kt.part_l = w.part_l; kt.part_acc = w.part_acc; kt.part_y = w.part_y; kt.node_ptr = node_ptr;
+        kt.n_kg = Kk; kt.gs = f.gs; kt.heads = p->heads;
+        kt.wo2 = W(f.wo2_h); kt.w1 = W(f.kffn1_h); kt.w2 = W(f.kffn2_h);
+        kt.kp = kp; kt.bo2 = p->k2r_out_b; kt.ln_g = p->ln_kg_w; kt.ln_b = p->ln_kg_b; kt.b1 = p->ffn_kg_b1; kt.b2 = p->ffn_kg_b2;
+        kt.stat = w.stat; kt.gt = gt;
+        if ((rc = launch_kg_tail(kt, ks, G, st)) != CM_OK) return rc;
+        return post_launch("cm_fusion_forward(tc)");
+    }
     if ((rc = launch_kg_merge(ks, D, p->heads, f.gs, Kk, node_ptr, G, w.ctx2, w.both, w.stat, st)) != CM_OK) return rc;
     // ---- KG rows: z0 = LN(kp + ctx2 Wo^T + bo) (:130), z = z0 + FFN(z0) (:131)
     const int GK = G * Kk;
-    const float* kp = reinterpret_cast<const float*>(base + f.kp);
     if (D == 256) {
         FusionNodeArgs a;
         a.M = GK; a.m_dev = nullptr;
@@ -267,17 +290,6 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
         d.bias = p->ffn_kg_b2; d.residual = w.z0; d.ldr = D; d.out_f32 = w.z; d.ldo_f32 = D;
         if ((rc = launch_dense(d, st)) != CM_OK) return rc;
     }
-    // ---- mean over kg rows (:135), fusion layer (:138-139), heads (:239-242)
-    GraphTailArgs gt;
-    gt.D = D; gt.n_kg = Kk; gt.num_classes = p->num_classes;
-    gt.want_heads = (mask_out || instance_out || edge_out || score_out) ? 1 : 0;
-    gt.z = w.z; gt.both = w.both;
-    gt.fl1_w = p->fl_w1; gt.fl1_b = p->fl_b1; gt.fl2_w = p->fl_w2; gt.fl2_b = p->fl_b2;
-    for (int t = 0; t < 4; ++t) {
-        gt.hw1[t] = p->head_w1[t]; gt.hb1[t] = p->head_b1[t]; gt.hw2[t] = p->head_w2[t]; gt.hb2[t] = p->head_b2[t];
-        if (gt.want_heads) CM_REQUIRE(p->head_w1[t] && p->head_b1[t] && p->head_w2[t] && p->head_b2[t], "cm_fusion_forward: head %d parameters missing", t);
-    }
-    gt.fused = fused_out; gt.mask_out = mask_out; gt.inst_out = instance_out; gt.edge_out = edge_out; gt.score_out = score_out;
     if ((rc = launch_graph_tail(gt, G, st)) != CM_OK) return rc;
     return post_launch("cm_fusion_forward(tc)");
 }
