@@ -115,6 +115,7 @@ SIGNATURES = {
     "cm_gnn_forward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _fp, _i, _fp, _sz,
                             _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_gnn_train_workspace_bytes": (_sz, [C.POINTER(GnnParams), _i, _i]),
+    "cm_train_gemm_f32": (_i, [_fp, _fp, _fp, _i, _i, _i, _i, _fp, _fp]),
     "cm_set_bn_sync": (_i, [C.c_void_p, _fp, _fp, _i]),
     "cm_gnn_train_forward": (_i, [C.POINTER(GnnParams), _fp, _fp, _fp, _fp, _fp, _i, _i, C.POINTER(GnnDropout), _fp, _sz,
                                   _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),

@@ -43,7 +43,11 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint64_t* acc_ready = empty + TC_STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int num_kb = (p.K + TC_BK - 1) / TC_BK;
+    const int all_kb = (p.K + TC_BK - 1) / TC_BK;
+    const int kb_per = p.k_splits > 1 ? (all_kb + p.k_splits - 1) / p.k_splits : all_kb;
+    const int kb_first = p.k_splits > 1 ? blockIdx.z * kb_per : 0;
+    const int num_kb = max(min(all_kb, kb_first + kb_per) - kb_first, 0);   // k-blocks of this CTA's slice (>= 1: the launcher sizes k_splits)
+    if (p.k_splits > 1) p.out_f32 += (size_t)blockIdx.z * p.split_stride;
 
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < TC_STAGES; ++s) {
@@ -71,14 +75,14 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 if (n > 0) mbar_wait(empty + s, (n - 1) & 1);
                 mbar_expect_tx(full + s, S::STAGE_BYTES);
                 uint8_t* a_dst = smem + s * S::STAGE_BYTES;
-                tma_load_2d(a_dst, &map_a, full + s, kb * TC_BK, m0);
-                tma_load_2d(a_dst + S::A_BYTES, &map_w, full + s, kb * TC_BK, n0);
+                tma_load_2d(a_dst, &map_a, full + s, (kb_first + kb) * TC_BK, m0);
+                tma_load_2d(a_dst + S::A_BYTES, &map_w, full + s, (kb_first + kb) * TC_BK, n0);
             }
             __syncwarp();
         }
     } else if (warp == 1) {
         // ---------------------------------------------------------------- MMA issuer
-        constexpr uint32_t idesc = umma_idesc_f16(TC_BM, BN);
+        const uint32_t idesc = umma_idesc_f16(TC_BM, BN) | (p.bf16_operands ? ((1u << 7) | (1u << 10)) : 0u);   // A / B format: 0 fp16, 1 bf16
         for (int kb = 0; kb < num_kb; ++kb) {
             if (lane == 0) {
                 const int s = kb % TC_STAGES, n = kb / TC_STAGES;
@@ -363,7 +367,7 @@ static int launch_dense_bn(const Dense& d, cudaStream_t st) {
     if (attr.first()) {
         cudaFuncSetAttribute(dense_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN>::TOTAL);
     }
-    dim3 grid(ceil_div(d.N, BN), ceil_div(d.M, TC_BM));
+    dim3 grid(ceil_div(d.N, BN), ceil_div(d.M, TC_BM), d.k_splits > 1 ? d.k_splits : 1);
     {
         CM_TIMED("dense_tc", st);
         dense_tc_kernel<BN><<<grid, TC_THREADS, TcSmem<BN>::TOTAL, st>>>(ma, mw, d);
@@ -377,6 +381,13 @@ int launch_dense(const Dense& d, cudaStream_t st) {
     CM_REQUIRE(d.K % 8 == 0 && d.lda % 8 == 0 && d.lda >= d.K, "dense: K=%d / lda=%d must be multiples of 8", d.K, d.lda);
     CM_REQUIRE((reinterpret_cast<uintptr_t>(d.A) & 15) == 0 && (reinterpret_cast<uintptr_t>(d.W) & 15) == 0, "dense: operands must be 16-byte aligned");
     CM_REQUIRE(!d.ln_gamma || d.N <= 256, "dense: fused LayerNorm needs N <= 256 (N=%d)", d.N);
+    CM_REQUIRE(!d.bf16_operands || (!d.out_h && !d.residual), "dense: bf16 operands go with fp32 outputs only");
+    if (d.k_splits > 1) {
+        const int all_kb = (d.K + TC_BK - 1) / TC_BK, per = (all_kb + d.k_splits - 1) / d.k_splits;
+        CM_REQUIRE(d.out_f32 && !d.out_h && !d.bias && !d.residual && !d.residual_f32 && !d.ln_gamma && !d.relu && !d.sm_gs && d.alpha == 1.f &&
+                       !d.m_dev && (long long)per * (d.k_splits - 1) < all_kb,
+                   "dense: split-K writes raw fp32 partial tiles only, every slice non-empty");
+    }
     CM_REQUIRE(!d.sm_gs || ((d.sm_gs == 16 || d.sm_gs == 32) && d.N == 256 && d.out_h && d.out_f32 && !d.ln_gamma &&
                             d.sm_valid >= 1 && d.sm_valid <= d.sm_gs),
                "dense: scores mode needs N == 256, group size 16/32, fp16 + f32 outputs");

@@ -36,6 +36,14 @@ struct Dense {
     // to out_f32 [M,128]; attn_mean [M, sm_valid] (optional) = mean over the head groups of the probabilities.
     int sm_gs = 0, sm_valid = 0;
     float* attn_mean = nullptr;
+    // split-K (training weight gradients: few output tiles, a reduction over every row of the batch): grid.z = k_splits,
+    // slice z covers the k-blocks [z * ceil(num_kb / k_splits), ...) and writes its raw fp32 partial tile (no bias / alpha /
+    // residual) to out_f32 + z * split_stride; the caller sums the slices in a fixed order.
+    int k_splits = 1;
+    size_t split_stride = 0;
+    // operands are bf16 instead of fp16 (same 2-byte K-major layout; kind::f16 takes either): the training GEMMs use it --
+    // gradients span far more than fp16's exponent range.  fp32 outputs only.
+    int bf16_operands = 0;
 };
 
 int launch_dense(const Dense& d, cudaStream_t st);

@@ -1,10 +1,183 @@
 // Strided fp32 GEMM with deterministic split-K, and column sums with fp64 partials: the dense building blocks of
 // the training-mode passes (see train_common.cuh).
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include <cuda_bf16.h>
+
+#include "dense_tc.cuh"
 #include "train_common.cuh"
 
 namespace cm {
 
 constexpr int GB = 64, GK = 16;
+
+// ---------------------------------------------------------------- tensor-core path of launch_gemm
+// The training GEMMs (forward linears, dgrad, wgrad of both models) on the tcgen05 dense kernel (dense_tc.cu) with
+// near-fp32 accuracy: both operands are rewritten as 16-bit thirds along the reduction dimension,
+//   A' = [A_hi | A_lo | A_hi],  B' = [B_hi | B_hi | B_lo]   (hi = round16(v), lo = round16(v - hi)),
+// so that one 16-bit GEMM with fp32 accumulation over 3 K computes A_hi B_hi + A_lo B_hi + A_hi B_lo.  Forward layers use
+// fp16 parts (22 mantissa bits per operand: 5e-7 of the output scale, like the inference GNN layers), the backward GEMMs
+// bf16 parts (16 bits, fp32's exponent range: gradients of a mean loss sit at 1e-6 .. 1e-9; 5e-6 .. 3e-5 of the scale).  Operands of any stride pattern (NT forward,
+// NN dgrad, TN wgrad) are brought to K-major by the split kernels; wgrad runs split-K with a fixed-order reduction.
+// k contiguous in the source: out[r, t * kp + c], thread per (r, c)
+// hi / lo 16-bit parts of v as raw bits: fp16 (22 mantissa bits together, fp16's exponent range) or bf16 (16 bits, fp32's range)
+__device__ __forceinline__ void split_parts(float v, int bf16, unsigned short* hi, unsigned short* lo) {
+    if (bf16) {
+        const __nv_bfloat16 h = __float2bfloat16_rn(v), l = __float2bfloat16_rn(v - __bfloat162float(h));
+        *hi = __bfloat16_as_ushort(h);
+        *lo = __bfloat16_as_ushort(l);
+    } else {
+        const op_t h = f2op(v), l = f2op(v - op2f(h));
+        *hi = __half_as_ushort(h);
+        *lo = __half_as_ushort(l);
+    }
+}
+__global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict__ src, long s_row, int rows, int K, int kp, int b_pattern, int bf16,
+                                                         unsigned short* __restrict__ out) {
+    const long total = (long)rows * kp;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int r = (int)(i / kp), c = (int)(i - (long)r * kp);
+        const float v = c < K ? src[(long)r * s_row + c] : 0.f;
+        unsigned short hi, lo;
+        split_parts(v, bf16, &hi, &lo);
+        unsigned short* o = out + (size_t)r * 3 * kp + c;
+        o[0] = hi;
+        o[kp] = b_pattern ? hi : lo;
+        o[2 * kp] = b_pattern ? lo : hi;
+    }
+}
+// rows contiguous in the source (element (r, k) at src[k * s_k + r]): 32 x 32 tiles through shared memory
+__global__ void __launch_bounds__(256) split_cols_kernel(const float* __restrict__ src, long s_k, int rows, int K, int kp, int b_pattern, int bf16,
+                                                         unsigned short* __restrict__ out) {
+    __shared__ float t[32][33];
+    const int r0 = blockIdx.x * 32, k0 = blockIdx.y * 32, tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8) {
+        const int k = k0 + j, r = r0 + tx;
+        t[j][tx] = (k < K && r < rows) ? src[(long)k * s_k + r] : 0.f;
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int r = r0 + j, k = k0 + tx;
+        if (r >= rows || k >= kp) continue;
+        const float v = t[tx][j];
+        unsigned short hi, lo;
+        split_parts(v, bf16, &hi, &lo);
+        unsigned short* o = out + (size_t)r * 3 * kp + k;
+        o[0] = hi;
+        o[kp] = b_pattern ? hi : lo;
+        o[2 * kp] = b_pattern ? lo : hi;
+    }
+}
+static int split_operand(const float* src, long s_row, long s_k, int rows, int K, int kp, int b_pattern, int bf16, unsigned short* out, cudaStream_t st) {
+    CM_TIMED("train_split_operand", st);
+    if (s_k == 1) {
+        const long total = (long)rows * kp;
+        split_rows_kernel<<<(int)std::min<long>((total + 255) / 256, 148L * 16), 256, 0, st>>>(src, s_row, rows, K, kp, b_pattern, bf16, out);
+    } else {
+        split_cols_kernel<<<dim3(ceil_div(rows, 32), ceil_div(kp, 32)), 256, 0, st>>>(src, s_k, rows, K, kp, b_pattern, bf16, out);
+    }
+    return post_launch("split_operand");
+}
+__global__ void gemm_epilogue_kernel(const float* __restrict__ raw, int M, int N, float* __restrict__ C, long ldc, const float* __restrict__ bias,
+                                     int relu, const uint8_t* __restrict__ keep, float keep_scale, float alpha, int accumulate) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long)M * N) return;
+    const int m = (int)(i / N), n = (int)(i - (long)m * N);
+    float v = raw[i] * alpha;
+    if (bias) v += bias[n];
+    if (relu) v = fmaxf(v, 0.f);
+    if (keep) v = keep[i] ? v * keep_scale : 0.f;
+    float* c = C + (long)m * ldc + n;
+    *c = accumulate ? *c + v : v;
+}
+__global__ void splitk_reduce_kernel(const float* __restrict__ part, int splits, int M, int N, float* __restrict__ C, long ldc,
+                                     const float* __restrict__ bias, int relu, float alpha, int accumulate);
+
+static bool tc_gemm_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("CM_TRAIN_GEMM");
+        on = !(e && e[0] == 'f');   // CM_TRAIN_GEMM=fp32 keeps the CUDA-core tiles
+    }
+    return on == 1;
+}
+static void* scratch_alloc(size_t bytes, cudaStream_t st) {
+    static PerDeviceOnce pool_once;
+    if (pool_once.first()) {   // keep freed blocks in the stream-ordered pool instead of returning them to the driver
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+    }
+    void* p = nullptr;
+    if (cudaMallocAsync(&p, bytes, st) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+// -> CM_OK when the GEMM ran on the tensor cores, 1 when the shape is not worth it (caller falls back), < 0 on error
+static int launch_gemm_tc(const Gemm& g, cudaStream_t st, const char* name) {
+    if (!tc_gemm_enabled() || g.K < 64 || g.N < 16 || (long)g.M * g.N * g.K < (1L << 22)) return 1;
+    if (g.sak != 1 && g.sam != 1) return 1;
+    if (g.sbk != 1 && g.sbn != 1) return 1;
+    if (const char* skip = getenv("CM_TC_SKIP")) {   // debugging aid: keep one access pattern on the fp32 tiles
+        if (strstr(skip, "nn") && g.sak == 1 && g.sbk != 1) return 1;
+        if (strstr(skip, "tn") && g.sak != 1) return 1;
+        if (strstr(skip, "nt") && g.sak == 1 && g.sbk == 1) return 1;
+        if (strstr(skip, "keep") && (g.keep || g.accumulate)) return 1;
+        if (strstr(skip, "split") && g.splits > 1) return 1;
+    }
+    const int kp = (g.K + 7) / 8 * 8, K3 = 3 * kp;
+    const size_t a_bytes = align_up((size_t)g.M * K3 * sizeof(op_t), 256), b_bytes = align_up((size_t)g.N * K3 * sizeof(op_t), 256);
+    // split-K only where the caller provided the partial buffer (wgrad); every slice gets at least four k-blocks
+    int splits = 1;
+    if (g.splits > 1 && g.part) splits = std::max(1, std::min(g.splits, (K3 / 64) / 4));
+    const bool direct = splits == 1 && !g.keep && !g.accumulate;
+    const size_t raw_bytes = (splits == 1 && !direct) ? align_up((size_t)g.M * g.N * sizeof(float), 256) : 0;
+    char* buf = reinterpret_cast<char*>(scratch_alloc(a_bytes + b_bytes + raw_bytes, st));
+    if (!buf) return 1;
+    unsigned short* a3 = reinterpret_cast<unsigned short*>(buf);
+    unsigned short* b3 = reinterpret_cast<unsigned short*>(buf + a_bytes);
+    // forward layers (both operands k-contiguous: activations x weights, O(1) values) keep fp16 thirds: 22 mantissa bits,
+    // so ReLU gates and BatchNorm statistics match the fp32 reference; dgrad / wgrad take gradients (1e-6 .. 1e-9 under a
+    // mean loss, below fp16's range) and use bf16 thirds
+    const int bf16 = !(g.sak == 1 && g.sbk == 1);
+    float* raw = reinterpret_cast<float*>(buf + a_bytes + b_bytes);
+    int rc = split_operand(g.A, g.sam, g.sak, g.M, g.K, kp, 0, bf16, a3, st);
+    if (rc == CM_OK) rc = split_operand(g.B, g.sbn, g.sbk, g.N, g.K, kp, 1, bf16, b3, st);
+    if (rc == CM_OK) {
+        Dense d;
+        d.A = reinterpret_cast<const op_t*>(a3); d.lda = K3; d.W = reinterpret_cast<const op_t*>(b3); d.M = g.M; d.N = g.N; d.K = K3;
+        d.bf16_operands = bf16;
+        if (splits > 1) {
+            d.out_f32 = g.part; d.ldo_f32 = g.N; d.k_splits = splits; d.split_stride = (size_t)g.M * g.N;
+        } else if (direct) {
+            d.out_f32 = g.C; d.ldo_f32 = (int)g.ldc; d.bias = g.bias; d.relu = g.relu; d.alpha = g.alpha;
+        } else {
+            d.out_f32 = raw; d.ldo_f32 = g.N;
+        }
+        rc = launch_dense(d, st);
+    }
+    if (rc == CM_OK && splits > 1) {
+        CM_TIMED("splitk_reduce", st);
+        splitk_reduce_kernel<<<ceil_div((long)g.M * g.N, 256), 256, 0, st>>>(g.part, splits, g.M, g.N, g.C, g.ldc, g.bias, g.relu, g.alpha, g.accumulate);
+    } else if (rc == CM_OK && !direct) {
+        CM_TIMED("train_elementwise", st);
+        gemm_epilogue_kernel<<<ceil_div((long)g.M * g.N, 256), 256, 0, st>>>(raw, g.M, g.N, g.C, g.ldc, g.bias, g.relu, g.keep, g.keep_scale, g.alpha,
+                                                                            g.accumulate);
+    }
+    cudaFreeAsync(buf, st);
+    if (rc != CM_OK) return rc;
+    return post_launch(name);
+}
 
 template <bool AKC, bool BKC>
 __global__ void __launch_bounds__(256) sgemm_kernel(const float* __restrict__ A, long sam, long sak, const float* __restrict__ B, long sbk,
@@ -97,6 +270,10 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ part, int splits,
 
 int launch_gemm(const Gemm& g, cudaStream_t st, const char* name) {
     if (g.M <= 0 || g.N <= 0) return CM_OK;
+    {
+        const int rc = launch_gemm_tc(g, st, name);   // tcgen05 (split fp16 thirds); 1 = shape not worth it / unsupported strides
+        if (rc <= 0) return rc;
+    }
     const int splits = g.splits > 1 && g.part ? g.splits : 1;
     const int k_chunk = splits > 1 ? ((g.K + splits - 1) / splits + GK - 1) / GK * GK : (g.K > 0 ? g.K : 1);
     dim3 grid(ceil_div(g.N, GB), ceil_div(g.M, GB), splits);
@@ -258,3 +435,18 @@ int launch_ln_bwd(const float* x, const float* stats, const float* gamma, const 
 }
 
 }  // namespace cm
+
+// Exported building block / unit-test hook of the training GEMM (include/cm_b200.h): C[M,N] = A[M,K] W[N,K]^T (+ bias).
+extern "C" int cm_train_gemm_f32(const float* a, const float* w, const float* bias, int m, int n, int k, int transposed_a, float* c, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(a && w && c && m > 0 && n > 0 && k > 0, "cm_train_gemm_f32: bad arguments");
+    Gemm g = gemm_nt(a, k, w, c, n, m, n, k, bias, 0);
+    if (transposed_a) {   // a is [K, M] (the wgrad pattern: reduction over the rows of the stored matrix)
+        g.sam = 1;
+        g.sak = m;
+        g.a_k_contig = false;
+    }
+    return launch_gemm(g, as_stream(stream), "train_linear");
+}
+

@@ -199,6 +199,12 @@ size_t cm_gnn_train_workspace_bytes(const cm_gnn_params* p, int n_nodes, int n_e
  * device_buf[0..count) over the ranks on that stream (ncclAllReduce through torch.distributed) -- and read them back.
  * bn_weight / bn_bias gradients stay this rank's partial sums (the gradient all-reduce adds them like the rest).
  * fn == NULL clears the hook (single-process statistics).  One hook per process (one process per GPU). */
+/* The dense building block of the training passes (also their unit-test hook): c [m,n] = a w^T (+ bias), fp32 in and out.
+ * a is [m,k] row-major, or [k,m] with transposed_a (the weight-gradient access pattern); w is [n,k] (nn.Linear layout).
+ * Large shapes run on the tcgen05 dense kernel with both operands split into 16-bit thirds (hi | lo | hi against
+ * hi | hi | lo, fp32 accumulation; fp16 parts for the forward pattern, bf16 parts with transposed_a); small ones on fp32
+ * CUDA-core tiles. */
+int cm_train_gemm_f32(const float* a, const float* w, const float* bias, int m, int n, int k, int transposed_a, float* c, void* stream);
 typedef void (*cm_bn_sync_fn)(void* user, int count, void* stream);
 int cm_set_bn_sync(cm_bn_sync_fn fn, void* user, double* device_buf, int capacity);
 /* Outputs: mask_out / instance_out [N,num_classes], edge_out [N,1], node_emb [N,hidden] (optional; the shared
