@@ -72,14 +72,13 @@ __global__ void __launch_bounds__(256) split_cols_kernel(const float* __restrict
     }
 }
 static int split_operand(const float* src, long s_row, long s_k, int rows, int K, int kp, int b_pattern, int bf16, unsigned short* out, cudaStream_t st) {
-    CM_TIMED("train_split_operand", st);
     if (s_k == 1) {
         const long total = (long)rows * kp;
         split_rows_kernel<<<(int)std::min<long>((total + 255) / 256, 148L * 16), 256, 0, st>>>(src, s_row, rows, K, kp, b_pattern, bf16, out);
     } else {
         split_cols_kernel<<<dim3(ceil_div(rows, 32), ceil_div(kp, 32)), 256, 0, st>>>(src, s_k, rows, K, kp, b_pattern, bf16, out);
     }
-    return post_launch("split_operand");
+    return CM_OK;
 }
 __global__ void gemm_epilogue_kernel(const float* __restrict__ raw, int M, int N, float* __restrict__ C, long ldc, const float* __restrict__ bias,
                                      int relu, const uint8_t* __restrict__ keep, float keep_scale, float alpha, int accumulate) {
@@ -104,6 +103,14 @@ static bool tc_gemm_enabled() {
     }
     return on == 1;
 }
+static long tc_gemm_threshold() {
+    static long t = -1;
+    if (t < 0) {
+        const char* e = getenv("CM_TRAIN_GEMM_MIN");   // multiply-adds
+        t = e ? atol(e) : (1L << 24);
+    }
+    return t;
+}
 static void* scratch_alloc(size_t bytes, cudaStream_t st) {
     static PerDeviceOnce pool_once;
     if (pool_once.first()) {   // keep freed blocks in the stream-ordered pool instead of returning them to the driver
@@ -125,7 +132,9 @@ static void* scratch_alloc(size_t bytes, cudaStream_t st) {
 
 // -> CM_OK when the GEMM ran on the tensor cores, 1 when the shape is not worth it (caller falls back), < 0 on error
 static int launch_gemm_tc(const Gemm& g, cudaStream_t st, const char* name) {
-    if (!tc_gemm_enabled() || g.K < 64 || g.N < 16 || (long)g.M * g.N * g.K < (1L << 22)) return 1;
+    // below ~2^24 multiply-adds the fp32 tile kernel (one launch) is as fast as split + tcgen05 (three launches): KG-row and
+    // graph-level layers stay there, the region-node layers of both models and every weight gradient over them come here
+    if (!tc_gemm_enabled() || g.K < 64 || g.N < 16 || (long)g.M * g.N * g.K < tc_gemm_threshold()) return 1;
     if (g.sak != 1 && g.sam != 1) return 1;
     if (g.sbk != 1 && g.sbn != 1) return 1;
     if (const char* skip = getenv("CM_TC_SKIP")) {   // debugging aid: keep one access pattern on the fp32 tiles
@@ -151,8 +160,13 @@ static int launch_gemm_tc(const Gemm& g, cudaStream_t st, const char* name) {
     // mean loss, below fp16's range) and use bf16 thirds
     const int bf16 = !(g.sak == 1 && g.sbk == 1);
     float* raw = reinterpret_cast<float*>(buf + a_bytes + b_bytes);
-    int rc = split_operand(g.A, g.sam, g.sak, g.M, g.K, kp, 0, bf16, a3, st);
-    if (rc == CM_OK) rc = split_operand(g.B, g.sbn, g.sbk, g.N, g.K, kp, 1, bf16, b3, st);
+    int rc;
+    {
+        CM_TIMED("train_split_operand", st);
+        split_operand(g.A, g.sam, g.sak, g.M, g.K, kp, 0, bf16, a3, st);
+        split_operand(g.B, g.sbn, g.sbk, g.N, g.K, kp, 1, bf16, b3, st);
+        rc = post_launch("split_operand");
+    }
     if (rc == CM_OK) {
         Dense d;
         d.A = reinterpret_cast<const op_t*>(a3); d.lda = K3; d.W = reinterpret_cast<const op_t*>(b3); d.M = g.M; d.N = g.N; d.K = K3;
