@@ -224,15 +224,19 @@ def test_host_pipeline_raises_on_graph_overflow(models):
 def test_second_device_with_current_device_left_at_zero(models):
     """per-device kernel attributes + a device guard around every library call -- a pipeline on cuda:1 while
     the current device stays 0 gives what cuda:0 gives."""
-    import copy
+    from camouflage_multimodal_b200.fusion_model import build_multimodal_model
     from camouflage_multimodal_b200.pipeline import EvalPipeline
+    from camouflage_multimodal_b200.region_graph import RegionGraphGNN
     gnn, det, kg, _, _ = models
     b = synth.make_batch(11, 2, seed=5)
     d0 = b.to("cuda:0")
     out0 = EvalPipeline(gnn, det, kg, label_cap=544, lane=11).run(d0.images, d0.labels, d0.canny, d0.gt)
     ref = out0["mask_out"].cpu(), out0["per_image"].cpu()
     torch.cuda.set_device(0)
-    gnn1, det1 = copy.deepcopy(gnn).to("cuda:1"), copy.deepcopy(det).to("cuda:1")
+    gnn1, det1 = RegionGraphGNN(15, 128, 2), build_multimodal_model({})
+    gnn1.load_state_dict(gnn.state_dict())
+    det1.load_state_dict(det.state_dict())
+    gnn1, det1 = gnn1.to("cuda:1").eval(), det1.to("cuda:1").eval()
     d1 = b.to("cuda:1")
     out1 = EvalPipeline(gnn1, det1, kg.to("cuda:1"), label_cap=544, lane=12).run(d1.images, d1.labels, d1.canny, d1.gt)
     assert torch.cuda.current_device() == 0
