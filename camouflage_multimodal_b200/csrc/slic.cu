@@ -13,6 +13,7 @@
 //   slic_connect_kernel   _enforce_label_connectivity_cython: raster-order BFS, one warp per image (the algorithm is
 //                         sequential by definition: the label a small segment joins depends on the visiting order)
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <vector>
@@ -267,9 +268,11 @@ constexpr bool SLIC_WARP_WALK = CM_SLIC_WARP_WALK != 0;
 
 template <bool SMEM>
 __global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict__ labels_in, int H, int W, int min_size, int max_size,
-                                                           int start_label, int* __restrict__ coords, int* __restrict__ out) {
+                                                           int start_label, int* __restrict__ coords, const int* __restrict__ only_if,
+                                                           int* __restrict__ out) {
     extern __shared__ short s_out[];
     const int b = blockIdx.x, n = H * W;
+    if (only_if && !only_if[b]) return;   // fallback pass behind the parallel kernel: only the images it could not finish
     const int* lab = labels_in + (size_t)b * n;
     int* o = out + (size_t)b * n;
     int* q = coords + (size_t)b * max(max_size, 1);
@@ -395,21 +398,313 @@ __global__ void __launch_bounds__(256) slic_connect_kernel(const int* __restrict
         for (int i = threadIdx.x; i < n; i += blockDim.x) o[i] = s_out[i];
 }
 
-static int launch_slic_connect(const int* labels_in, int batch, int h, int w, int min_size, int max_size, int start_label, int* coords,
-                               int* out, cudaStream_t st) {
+// ------------------------------------------------------------------------------------------------ parallel exact connectivity
+// The same result as the sequential walk (oracle/slic.py enforce_connectivity), computed from its structure instead of
+// replaying it pixel by pixel.  A "unit" is what one BFS of the walk labels.  For a 4-connected component of equal input
+// labels with at most max_size pixels the unit is the whole component, found by a union-find in shared memory; a larger
+// component is carved into units by replaying the walk's BFS on that component alone (it only ever expands into
+// unlabelled pixels of its own component, so the rest of the image does not matter) -- rare, and done by one warp.
+// Units are processed by the walk in the order of their first pixel, so
+//   * kept units (size >= min_size) are numbered start_label, start_label + 1, ... by a prefix count over first pixels;
+//   * a small unit takes `adjacent`: the label of the last neighbour pixel its BFS meets (queue order, directions
+//     E W S N) that belongs to a unit with an EARLIER first pixel (later units are still unlabelled at that time) --
+//     found by replaying the BFS of that one small unit (< min_size pixels) -- or start_label if there is none; small
+//     units that point at small units are resolved by following the (strictly earlier) pointers.
+// One CTA per image, H*W <= 65536 (16-bit pixel indices): parent table 128 KB + 4-bit neighbour-equality masks 32 KB +
+// carve bits 8 KB of shared memory; unit sizes / pointers / labels in a global scratch area.
+constexpr int CC_THREADS = 1024;
+struct CcScratch {   // per image, all indexed by a unit's first pixel
+    int* usz;              // [n] unit size (0 = not a unit start)
+    unsigned short* adj;   // [n] small unit -> first pixel of the unit it joins (CC_NONE: none)
+    int* fin;              // [n] final label of the unit
+    unsigned short* queue; // [n] BFS queue of the carving warp
+};
+constexpr unsigned short CC_NONE = 0xffff;
+
+__device__ __forceinline__ unsigned cc_same(const unsigned char* s_same, int i) { return (s_same[i >> 1] >> (4 * (i & 1))) & 15u; }
+__device__ __forceinline__ int cc_find(const unsigned short* par, int x) {
+    int p = par[x];
+    while (p != x) {
+        x = p;
+        p = par[x];
+    }
+    return x;
+}
+__device__ __forceinline__ void cc_unite(unsigned short* par, int a, int b) {
+    while (true) {
+        a = cc_find(par, a);
+        b = cc_find(par, b);
+        if (a == b) return;
+        if (a > b) {
+            const int t = a;
+            a = b;
+            b = t;
+        }
+        const unsigned short old = atomicCAS(par + b, (unsigned short)b, (unsigned short)a);   // the larger root goes under the smaller
+        if (old == (unsigned short)b) return;
+        b = old;
+    }
+}
+
+__global__ void __launch_bounds__(CC_THREADS) slic_connect_ccl_kernel(const int* __restrict__ labels_in, int H, int W, int min_size, int max_size,
+                                                                      int start_label, int* __restrict__ usz_all, unsigned short* __restrict__ adj_all,
+                                                                      int* __restrict__ fin_all, unsigned short* __restrict__ queue_all,
+                                                                      int* __restrict__ fallback, int* __restrict__ out) {
+    extern __shared__ unsigned short cc_par[];
+    const int b = blockIdx.x, n = H * W, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned short* par = cc_par;
+    unsigned char* s_same = reinterpret_cast<unsigned char*>(par + ((n + 7) & ~7));
+    unsigned* s_done = reinterpret_cast<unsigned*>(s_same + (((n + 1) / 2 + 15) & ~15));   // one bit per pixel (carving only)
+    __shared__ int s_cut[64], s_ncut, s_scan[CC_THREADS / 32], s_over;
+    const int* lab = labels_in + (size_t)b * n;
+    int* o = out + (size_t)b * n;
+    int* usz = usz_all + (size_t)b * n;
+    unsigned short* adj = adj_all + (size_t)b * n;
+    int* fin = fin_all + (size_t)b * n;
+    unsigned short* queue = queue_all + (size_t)b * n;
+    // ---- neighbour-equality masks (E W S N = bits 0..3), parents, cleared tables
+    for (int i = tid; i < (n + 1) / 2; i += CC_THREADS) s_same[i] = 0;
+    for (int i = tid; i < (n + 31) / 32; i += CC_THREADS) s_done[i] = 0;
+    if (tid == 0) {
+        s_ncut = 0;
+        s_over = 0;
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += CC_THREADS) {
+        const int y = i / W, x = i - y * W, l = lab[i];
+        unsigned m = 0;
+        if (x + 1 < W && lab[i + 1] == l) m |= 1u;
+        if (x > 0 && lab[i - 1] == l) m |= 2u;
+        if (y + 1 < H && lab[i + W] == l) m |= 4u;
+        if (y > 0 && lab[i - W] == l) m |= 8u;
+        atomicOr(reinterpret_cast<unsigned*>(s_same) + (i >> 3), m << (4 * (i & 7)));
+        par[i] = (unsigned short)i;
+        usz[i] = 0;
+    }
+    __syncthreads();
+    // ---- union-find over the E and S links; the root of a component is its first pixel in raster order
+    for (int i = tid; i < n; i += CC_THREADS) {
+        const unsigned m = cc_same(s_same, i);
+        if (m & 1u) cc_unite(par, i, i + 1);
+        if (m & 4u) cc_unite(par, i, i + W);
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += CC_THREADS) par[i] = (unsigned short)cc_find(par, i);   // flatten (roots are fixed points)
+    __syncthreads();
+    // ---- component sizes: one atomic per run of equal roots inside a warp's 32 consecutive pixels
+    for (int base = 0; base < n; base += CC_THREADS) {
+        const int i = base + tid;
+        const int r = i < n ? (int)par[i] : -1;
+        const int prev = __shfl_up_sync(0xffffffffu, r, 1);
+        const unsigned heads = __ballot_sync(0xffffffffu, lane == 0 || r != prev);
+        if (r >= 0 && ((heads >> lane) & 1u)) {
+            const unsigned later = lane == 31 ? 0u : heads >> (lane + 1);
+            atomicAdd(usz + r, later ? __ffs(later) : 32 - lane);
+        }
+    }
+    __syncthreads();
+    // ---- components larger than max_size are carved by the walk itself
+    for (int i = tid; i < n; i += CC_THREADS)
+        if (par[i] == i && usz[i] > max_size) {
+            const int k = atomicAdd(&s_ncut, 1);
+            if (k < 64) s_cut[k] = i; else s_over = 1;
+        }
+    __syncthreads();
+    if (tid == 0) fallback[b] = 0;
+    if (s_over) {   // more oversized components than the list holds: this image goes through the sequential walk kernel
+        if (tid == 0) fallback[b] = 1;
+        return;
+    }
+    if (warp == 0 && s_ncut > 0) {
+        // The walk on one component: BFS from its first unlabelled pixel (eight queue entries x four directions per step,
+        // lane order = visiting order, cut at the append that fills the queue), repeated until the component is used up.
+        const int ent = lane >> 2, dir = lane & 3;
+        const int dy = dir == 2 ? 1 : (dir == 3 ? -1 : 0), dx = dir == 0 ? 1 : (dir == 1 ? -1 : 0);
+        const unsigned below = (1u << lane) - 1u;
+        for (int c = 0; c < s_ncut; ++c) {
+            const int root = s_cut[c];
+            int remaining = usz[root], scan_from = root;
+            while (remaining > 0) {
+                // first pixel of the component that is still unlabelled, in raster order
+                int p0 = -1;
+                for (int base = scan_from & ~31; base < n && p0 < 0; base += 32) {
+                    const int i = base + lane;
+                    const bool hit = i < n && i >= scan_from && par[i] == root && !((s_done[i >> 5] >> (i & 31)) & 1u);
+                    const unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (m) p0 = base + __ffs(m) - 1;
+                }
+                if (p0 < 0) break;
+                scan_from = p0 + 1;
+                if (lane == 0) {
+                    atomicOr(&s_done[p0 >> 5], 1u << (p0 & 31));
+                    queue[0] = (unsigned short)p0;
+                }
+                __syncwarp();
+                int size = 1, visited = 0;
+                while (visited < size && size < max_size) {
+                    const int nent = min(8, size - visited);
+                    const bool act = ent < nent;
+                    const int pi = act ? (int)queue[visited + ent] : 0;
+                    const int py = pi / W, px = pi - py * W, qy = py + dy, qx = px + dx;
+                    const bool inb = act && qy >= 0 && qy < H && qx >= 0 && qx < W;
+                    const int qi = inb ? qy * W + qx : 0;
+                    const bool same = inb && ((cc_same(s_same, pi) >> dir) & 1u);
+                    const bool cand = same && !((s_done[qi >> 5] >> (qi & 31)) & 1u);
+                    const unsigned cm = __ballot_sync(0xffffffffu, cand);
+                    bool winner = false;
+                    if (cand) winner = (__ffs(__match_any_sync(cm, qi)) - 1) == lane;
+                    const unsigned wm = __ballot_sync(0xffffffffu, winner);
+                    const int room = max_size - size, rank = __popc(wm & below);
+                    const unsigned fill = __ballot_sync(0xffffffffu, winner && rank == room - 1);
+                    const int cut = fill ? __ffs(fill) - 1 : 31;
+                    if (winner && lane <= cut) {
+                        atomicOr(&s_done[qi >> 5], 1u << (qi & 31));
+                        queue[size + rank] = (unsigned short)qi;
+                    }
+                    size += min(__popc(wm), room);
+                    visited += nent;
+                    __syncwarp();
+                }
+                for (int i = lane; i < size; i += 32) par[queue[i]] = (unsigned short)p0;   // the unit's first pixel names it
+                if (lane == 0) usz[p0] = size;
+                remaining -= size;
+                __syncwarp();
+            }
+        }
+    }
+    __syncthreads();
+    // ---- small units: replay their own BFS (< min_size pixels) for `adjacent`
+    for (int s = tid; s < n; s += CC_THREADS) {
+        if (par[s] != s) continue;
+        const int sz = usz[s];
+        if (sz >= min_size) continue;
+        unsigned short q[64];
+        const bool local = sz <= 64;
+        unsigned short* qq = local ? q : nullptr;   // min_size > 64 falls back to the thread-serial global queue below
+        int last = CC_NONE;
+        if (local) {
+            int size = 1, visited = 0;
+            qq[0] = (unsigned short)s;
+            while (visited < size) {
+                const int pi = qq[visited], py = pi / W, px = pi - py * W;
+                const unsigned m = cc_same(s_same, pi);
+#pragma unroll
+                for (int d = 0; d < 4; ++d) {
+                    const int qy = py + (d == 2 ? 1 : (d == 3 ? -1 : 0)), qx = px + (d == 0 ? 1 : (d == 1 ? -1 : 0));
+                    if (qy < 0 || qy >= H || qx < 0 || qx >= W) continue;
+                    const int qi = qy * W + qx, u = par[qi];
+                    if (((m >> d) & 1u) && u == s) {
+                        bool seen = false;
+                        for (int t = 0; t < size; ++t) seen |= qq[t] == (unsigned short)qi;
+                        if (!seen) qq[size++] = (unsigned short)qi;
+                    } else if (u != s && u < s) {
+                        last = u;   // already labelled when this unit is walked: its unit starts earlier
+                    }
+                }
+                ++visited;
+            }
+        } else {
+            last = -1;
+        }
+        adj[s] = (unsigned short)(last < 0 ? CC_NONE : last);
+        if (last == -1) s_over = 2;
+    }
+    __syncthreads();
+    if (s_over) {   // a small unit above the local queue (min_size > 64): sequential walk for this image
+        if (tid == 0) fallback[b] = 1;
+        return;
+    }
+    // ---- kept units numbered by first pixel: prefix count over raster order (bit per pixel, 64 pixels per thread)
+    for (int i = tid; i < (n + 31) / 32; i += CC_THREADS) s_done[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += CC_THREADS)
+        if (par[i] == i && usz[i] >= min_size) atomicOr(&s_done[i >> 5], 1u << (i & 31));
+    __syncthreads();
+    {
+        const int words = (n + 31) / 32, wper = (words + CC_THREADS - 1) / CC_THREADS, w0 = tid * wper, w1 = min(words, w0 + wper);
+        int cnt = 0;
+        for (int w = w0; w < w1; ++w) cnt += __popc(s_done[w]);
+        const int incl = warp_scan_incl(cnt, lane);
+        if (lane == 31) s_scan[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const int v = s_scan[lane], sc = warp_scan_incl(v, lane);
+            s_scan[lane] = sc - v;
+        }
+        __syncthreads();
+        int run = start_label + s_scan[warp] + incl - cnt;
+        for (int w = w0; w < w1; ++w) {
+            unsigned m = s_done[w];
+            while (m) {
+                fin[w * 32 + __ffs(m) - 1] = run++;
+                m &= m - 1;
+            }
+        }
+    }
+    __syncthreads();
+    // ---- small units follow their pointers to a kept unit (strictly earlier first pixels: the chain ends)
+    for (int s = tid; s < n; s += CC_THREADS) {
+        if (par[s] != s || usz[s] >= min_size) continue;
+        int u = adj[s], l = start_label;
+        while (u != CC_NONE) {
+            if (usz[u] >= min_size) {
+                l = fin[u];
+                break;
+            }
+            u = adj[u];
+        }
+        fin[s] = l;   // chains read `adj` and the kept units' labels only, never another small unit's `fin`
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += CC_THREADS) {
+        o[i] = fin[par[i]];
+    }
+}
+
+static int launch_slic_walk(const int* labels_in, int batch, int h, int w, int min_size, int max_size, int start_label, int* coords,
+                            const int* only_if, int* out, cudaStream_t st) {
     // labels (int16) + 4-bit neighbour masks + the queue; at most n / min_size + 1 labels are ever handed out
     const size_t smem = (size_t)h * w * sizeof(short) + ((size_t)h * w / 2 + 8) / 4 * 4 + (size_t)std::max(max_size, 1) * sizeof(int);
     const long long max_label = (long long)start_label + (long long)h * w / std::max(min_size, 1) + 1;
-    CM_TIMED("slic_connectivity", st);
     if (smem <= 224 * 1024 && max_label < 32767 && ((size_t)h * w * sizeof(short)) % 4 == 0) {
         static PerDeviceOnce attr;
         if (attr.first()) {
             cudaFuncSetAttribute(slic_connect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
         }
-        slic_connect_kernel<true><<<batch, 256, smem, st>>>(labels_in, h, w, min_size, max_size, start_label, coords, out);
+        slic_connect_kernel<true><<<batch, 256, smem, st>>>(labels_in, h, w, min_size, max_size, start_label, coords, only_if, out);
     } else {
-        slic_connect_kernel<false><<<batch, 256, 0, st>>>(labels_in, h, w, min_size, max_size, start_label, coords, out);
+        slic_connect_kernel<false><<<batch, 256, 0, st>>>(labels_in, h, w, min_size, max_size, start_label, coords, only_if, out);
     }
+    return CM_OK;
+}
+
+#ifndef CM_SLIC_PARALLEL_CONNECT
+#define CM_SLIC_PARALLEL_CONNECT 1
+#endif
+static int launch_slic_connect(const int* labels_in, int batch, int h, int w, int min_size, int max_size, int start_label, int* coords,
+                               int* out, cudaStream_t st) {
+    CM_TIMED("slic_connectivity", st);
+    const size_t n = (size_t)h * w;
+    const bool parallel = CM_SLIC_PARALLEL_CONNECT && n <= 65536 && min_size >= 0 && max_size >= 1 && !getenv("CM_SLIC_SEQUENTIAL_WALK");
+    if (!parallel) return launch_slic_walk(labels_in, batch, h, w, min_size, max_size, start_label, coords, nullptr, out, st);
+    // scratch of the parallel kernel, stream-ordered: unit sizes / final labels (int32), pointers / carving queue (uint16), fallback flags
+    const size_t per = n * (4 + 4 + 2 + 2), flags_off = align_up(per * batch, 256), bytes = flags_off + sizeof(int) * batch;
+    char* buf = nullptr;
+    if (cudaMallocAsync(reinterpret_cast<void**>(&buf), bytes, st) != cudaSuccess) {
+        cudaGetLastError();
+        return launch_slic_walk(labels_in, batch, h, w, min_size, max_size, start_label, coords, nullptr, out, st);
+    }
+    int* usz = reinterpret_cast<int*>(buf);
+    int* fin = usz + n * batch;
+    unsigned short* adj = reinterpret_cast<unsigned short*>(fin + n * batch);
+    unsigned short* queue = adj + n * batch;
+    int* fallback = reinterpret_cast<int*>(buf + flags_off);
+    const size_t smem = (((n + 7) & ~(size_t)7) * 2) + ((((n + 1) / 2) + 15) & ~(size_t)15) + ((n + 31) / 32) * 4;
+    static PerDeviceOnce attr;
+    if (attr.first()) cudaFuncSetAttribute(slic_connect_ccl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    slic_connect_ccl_kernel<<<batch, CC_THREADS, smem, st>>>(labels_in, h, w, min_size, max_size, start_label, usz, adj, fin, queue, fallback, out);
+    launch_slic_walk(labels_in, batch, h, w, min_size, max_size, start_label, coords, fallback, out, st);   // exits at once unless flagged
+    cudaFreeAsync(buf, st);
     return CM_OK;
 }
 
