@@ -153,39 +153,34 @@ __device__ __forceinline__ void slic_window(double c, int step, int n, int* lo, 
     *hi = (int)fmin(c + 2.0 * step + 1.0, (double)n);
 }
 
-// one CTA = 16 x 16 pixel tile; clusters whose window meets the tile are listed in shared memory in index order
+// one CTA = 16 x 16 pixel tile; the clusters whose window meets the tile are compacted into shared memory (any order:
+// the pixel keeps the lexicographically smallest (distance, cluster index), which is what the sequential loop's strict
+// '<' in index order leaves behind), their centres and integer windows staged 64 at a time
+constexpr int SLIC_CAND_CAP = 1024;
 __global__ void __launch_bounds__(256) slic_assign_kernel(const double* __restrict__ feat, const double* __restrict__ seg, SlicGrid g, int H,
                                                           int W, int* __restrict__ nearest) {
-    __shared__ int s_list[1024];
+    __shared__ int s_list[SLIC_CAND_CAP];
     __shared__ int s_count;
     __shared__ double s_seg[64][5];
+    __shared__ int s_win[64][4];
+    __shared__ int s_k[64];
     const int b = blockIdx.z, ty0 = blockIdx.y * 16, tx0 = blockIdx.x * 16;
     const int tid = threadIdx.x, y = ty0 + (tid >> 4), x = tx0 + (tid & 15);
     const double* sg = seg + (size_t)b * g.K * 5;
-    // ordered compaction of the candidate clusters (256 at a time, ballot-free: prefix by a serial scan of flags in smem)
-    __shared__ unsigned char s_flag[256];
     if (tid == 0) s_count = 0;
     __syncthreads();
-    for (int k0 = 0; k0 < g.K; k0 += 256) {
-        const int k = k0 + tid;
-        bool hit = false;
-        if (k < g.K) {
-            int ylo, yhi, xlo, xhi;
-            slic_window(sg[k * 5], g.step_y, H, &ylo, &yhi);
-            slic_window(sg[k * 5 + 1], g.step_x, W, &xlo, &xhi);
-            hit = ylo < ty0 + 16 && yhi > ty0 && xlo < tx0 + 16 && xhi > tx0;
+    for (int k = tid; k < g.K; k += 256) {
+        int ylo, yhi, xlo, xhi;
+        slic_window(sg[k * 5], g.step_y, H, &ylo, &yhi);
+        slic_window(sg[k * 5 + 1], g.step_x, W, &xlo, &xhi);
+        if (ylo < ty0 + 16 && yhi > ty0 && xlo < tx0 + 16 && xhi > tx0) {
+            const int idx = atomicAdd(&s_count, 1);
+            if (idx < SLIC_CAND_CAP) s_list[idx] = k;
         }
-        s_flag[tid] = hit;
-        __syncthreads();
-        if (tid == 0) {
-            int n = s_count;
-            for (int i = 0; i < 256; ++i)
-                if (s_flag[i] && n < 1024) s_list[n++] = k0 + i;
-            s_count = n;
-        }
-        __syncthreads();
     }
-    const int n_cand = s_count;
+    __syncthreads();
+    const bool listed = s_count <= SLIC_CAND_CAP;   // otherwise (more than 1024 overlapping windows) every cluster is tested
+    const int n_cand = listed ? s_count : g.K;
     const bool in = y < H && x < W;
     double f0 = 0, f1 = 0, f2 = 0;
     if (in) {
@@ -200,23 +195,27 @@ __global__ void __launch_bounds__(256) slic_assign_kernel(const double* __restri
     for (int c0 = 0; c0 < n_cand; c0 += 64) {
         const int nc = min(64, n_cand - c0);
         __syncthreads();
-        for (int i = tid; i < nc * 5; i += 256) s_seg[i / 5][i % 5] = sg[(size_t)s_list[c0 + i / 5] * 5 + i % 5];
+        if (tid < nc) {
+            const int k = listed ? s_list[c0 + tid] : c0 + tid;
+            s_k[tid] = k;
+#pragma unroll
+            for (int j = 0; j < 5; ++j) s_seg[tid][j] = sg[(size_t)k * 5 + j];
+            slic_window(s_seg[tid][0], g.step_y, H, &s_win[tid][0], &s_win[tid][1]);
+            slic_window(s_seg[tid][1], g.step_x, W, &s_win[tid][2], &s_win[tid][3]);
+        }
         __syncthreads();
         if (in) {
             for (int i = 0; i < nc; ++i) {
-                const double cy = s_seg[i][0], cx = s_seg[i][1];
-                int ylo, yhi, xlo, xhi;
-                slic_window(cy, g.step_y, H, &ylo, &yhi);
-                slic_window(cx, g.step_x, W, &xlo, &xhi);
-                if (y < ylo || y >= yhi || x < xlo || x >= xhi) continue;
-                const double dy = __dadd_rn(cy, -(double)y), dx = __dadd_rn(cx, -(double)x);
+                if (y < s_win[i][0] || y >= s_win[i][1] || x < s_win[i][2] || x >= s_win[i][3]) continue;
+                const double dy = __dadd_rn(s_seg[i][0], -(double)y), dx = __dadd_rn(s_seg[i][1], -(double)x);
                 double d = __dmul_rn(__dadd_rn(__dmul_rn(dy, dy), __dmul_rn(dx, dx)), sw);
                 const double e0 = __dadd_rn(f0, -s_seg[i][2]), e1 = __dadd_rn(f1, -s_seg[i][3]), e2 = __dadd_rn(f2, -s_seg[i][4]);
                 const double dc = __dadd_rn(__dadd_rn(__dmul_rn(e0, e0), __dmul_rn(e1, e1)), __dmul_rn(e2, e2));
                 d = __dadd_rn(d, dc);
-                if (best > d) {   // strict: the lowest cluster index keeps a tie
+                const int k = s_k[i];
+                if (d < best || (d == best && k < best_k)) {   // the lowest cluster index keeps a tie
                     best = d;
-                    best_k = s_list[c0 + i];
+                    best_k = k;
                 }
             }
         }
@@ -224,12 +223,13 @@ __global__ void __launch_bounds__(256) slic_assign_kernel(const double* __restri
     if (in) nearest[((size_t)b * H + y) * W + x] = best_k;
 }
 
-// one thread per (image, cluster): raster-order sums over the cluster's OLD window (every member lies inside it)
+// One warp per (image, cluster): raster-order sums over the cluster's OLD window (every member lies inside it).  The
+// lanes load a window row 32 pixels at a time (coalesced: position + three colours per lane) and ballot the members;
+// lane c then owns running sum c (y, x, three colours) and adds the members in raster order -- the values come from the
+// member's lane by shuffle, so the chain of float64 additions never waits for memory -- the same sequence of additions
+// as the scalar loop.  The count is an exact integer either way.
 __global__ void __launch_bounds__(256) slic_update_kernel(const double* __restrict__ feat, const int* __restrict__ nearest, SlicGrid g, int batch,
                                                           int H, int W, const double* __restrict__ seg_old, double* __restrict__ seg_new) {
-    // One warp per cluster.  The lanes scan a window row 32 pixels at a time (coalesced) and ballot the members; lane c
-    // then owns running sum c (y, x, three colours) and adds the members in raster order, so every sum is the same
-    // sequence of float64 additions as the scalar loop.  The count is an exact integer either way.
     const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (i >= batch * g.K) return;
     const int b = i / g.K, k = i - b * g.K, c = min(lane, 4);
@@ -243,12 +243,22 @@ __global__ void __launch_bounds__(256) slic_update_kernel(const double* __restri
         const size_t row = ((size_t)b * H + y) * W;
         for (int x0 = xlo; x0 < xhi; x0 += 32) {
             const int x = x0 + lane;
-            unsigned m = __ballot_sync(~0u, x < xhi && nearest[row + x] == k);
+            const bool mine = x < xhi && nearest[row + x] == k;
+            unsigned m = __ballot_sync(~0u, mine);
+            if (!m) continue;
             cnt += __popc(m);
+            double v2 = 0, v3 = 0, v4 = 0;
+            if (mine) {
+                const double* p = feat + 3 * (row + x);
+                v2 = p[0];
+                v3 = p[1];
+                v4 = p[2];
+            }
             while (m) {
-                const int xx = x0 + __ffs(m) - 1;
+                const int src = __ffs(m) - 1;
                 m &= m - 1;
-                const double v = c == 0 ? (double)y : (c == 1 ? (double)xx : feat[3 * (row + xx) + (c - 2)]);
+                const double a2 = __shfl_sync(~0u, v2, src), a3 = __shfl_sync(~0u, v3, src), a4 = __shfl_sync(~0u, v4, src);
+                const double v = c == 0 ? (double)y : (c == 1 ? (double)(x0 + src) : (c == 2 ? a2 : (c == 3 ? a3 : a4)));
                 acc = __dadd_rn(acc, v);
             }
         }
@@ -573,20 +583,26 @@ __global__ void __launch_bounds__(CC_THREADS) slic_connect_ccl_kernel(const int*
         }
     }
     __syncthreads();
-    // ---- small units: replay their own BFS (< min_size pixels) for `adjacent`
-    for (int s = tid; s < n; s += CC_THREADS) {
-        if (par[s] != s) continue;
-        const int sz = usz[s];
-        if (sz >= min_size) continue;
+    // ---- small units: replay their own BFS (< min_size pixels) for `adjacent`.  Their first pixels are compacted into a
+    // list (one unit per thread, no idle lanes between them); the carve bits become the units' visited marks.
+    for (int i = tid; i < (n + 31) / 32; i += CC_THREADS) s_done[i] = 0;
+    if (tid == 0) s_ncut = 0;
+    __syncthreads();
+    unsigned short* small = queue;   // the carving queue is free again: list of small-unit first pixels
+    for (int i = tid; i < n; i += CC_THREADS)
+        if (par[i] == i && usz[i] < min_size) small[atomicAdd(&s_ncut, 1)] = (unsigned short)i;
+    __syncthreads();
+    const int n_small = s_ncut;
+    for (int k = tid; k < n_small; k += CC_THREADS) {
+        const int s = small[k], sz = usz[s];
         unsigned short q[64];
-        const bool local = sz <= 64;
-        unsigned short* qq = local ? q : nullptr;   // min_size > 64 falls back to the thread-serial global queue below
         int last = CC_NONE;
-        if (local) {
+        if (sz <= 64) {
             int size = 1, visited = 0;
-            qq[0] = (unsigned short)s;
+            q[0] = (unsigned short)s;
+            atomicOr(&s_done[s >> 5], 1u << (s & 31));
             while (visited < size) {
-                const int pi = qq[visited], py = pi / W, px = pi - py * W;
+                const int pi = q[visited], py = pi / W, px = pi - py * W;
                 const unsigned m = cc_same(s_same, pi);
 #pragma unroll
                 for (int d = 0; d < 4; ++d) {
@@ -594,9 +610,10 @@ __global__ void __launch_bounds__(CC_THREADS) slic_connect_ccl_kernel(const int*
                     if (qy < 0 || qy >= H || qx < 0 || qx >= W) continue;
                     const int qi = qy * W + qx, u = par[qi];
                     if (((m >> d) & 1u) && u == s) {
-                        bool seen = false;
-                        for (int t = 0; t < size; ++t) seen |= qq[t] == (unsigned short)qi;
-                        if (!seen) qq[size++] = (unsigned short)qi;
+                        if (!((s_done[qi >> 5] >> (qi & 31)) & 1u)) {   // only this thread ever marks pixels of unit s
+                            atomicOr(&s_done[qi >> 5], 1u << (qi & 31));
+                            q[size++] = (unsigned short)qi;
+                        }
                     } else if (u != s && u < s) {
                         last = u;   // already labelled when this unit is walked: its unit starts earlier
                     }
@@ -604,10 +621,9 @@ __global__ void __launch_bounds__(CC_THREADS) slic_connect_ccl_kernel(const int*
                 ++visited;
             }
         } else {
-            last = -1;
+            s_over = 2;   // min_size > 64: above the local queue
         }
-        adj[s] = (unsigned short)(last < 0 ? CC_NONE : last);
-        if (last == -1) s_over = 2;
+        adj[s] = (unsigned short)last;
     }
     __syncthreads();
     if (s_over) {   // a small unit above the local queue (min_size > 64): sequential walk for this image
