@@ -15,6 +15,7 @@
 // image and of the all-ones mask, horizontal blur + bleed-over division, Sobel + magnitude, NMS + thresholds, then
 // one CTA per image grows the strong pixels through the weak ones in shared memory until nothing changes.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -192,6 +193,67 @@ __global__ void __launch_bounds__(1024) canny_hysteresis_kernel(uint8_t* __restr
     for (int i = tid; i < n; i += blockDim.x) edges[(size_t)b * n + i] = s[i] == 2 ? 1 : 0;
 }
 
+// hysteresis as connected components: union-find (16-bit pixel indices in shared memory, H*W <= 65536) over the pixels
+// >= low under 8-connectivity, one bit per component root that holds a pixel >= high, then every weak pixel looks its
+// root up.  Same fixed point as growing the strong pixels sweep by sweep, without the sweeps.
+__device__ __forceinline__ int hy_find(const unsigned short* par, int x) {
+    int p = par[x];
+    while (p != x) {
+        x = p;
+        p = par[x];
+    }
+    return x;
+}
+__device__ __forceinline__ void hy_unite(unsigned short* par, int a, int b) {
+    while (true) {
+        a = hy_find(par, a);
+        b = hy_find(par, b);
+        if (a == b) return;
+        if (a > b) {
+            const int t = a;
+            a = b;
+            b = t;
+        }
+        const unsigned short old = atomicCAS(par + b, (unsigned short)b, (unsigned short)a);
+        if (old == (unsigned short)b) return;
+        b = old;
+    }
+}
+__global__ void __launch_bounds__(1024) canny_hysteresis_uf_kernel(const uint8_t* __restrict__ cls, int H, int W, uint8_t* __restrict__ edges) {
+    extern __shared__ unsigned short hy_par[];
+    const int b = blockIdx.x, n = H * W, tid = threadIdx.x;
+    const uint8_t* g = cls + (size_t)b * n;
+    unsigned* strong = reinterpret_cast<unsigned*>(hy_par + ((n + 7) & ~7));
+    for (int i = tid; i < n; i += blockDim.x) hy_par[i] = (unsigned short)i;
+    for (int i = tid; i < (n + 31) / 32; i += blockDim.x) strong[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x) {
+        if (!g[i]) continue;
+        const int y = i / W, x = i - y * W;
+        if (x + 1 < W && g[i + 1]) hy_unite(hy_par, i, i + 1);
+        if (y + 1 < H) {
+            if (g[i + W]) hy_unite(hy_par, i, i + W);
+            if (x > 0 && g[i + W - 1]) hy_unite(hy_par, i, i + W - 1);
+            if (x + 1 < W && g[i + W + 1]) hy_unite(hy_par, i, i + W + 1);
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x)
+        if (g[i] == 2) {
+            const int r = hy_find(hy_par, i);
+            atomicOr(&strong[r >> 5], 1u << (r & 31));
+        }
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x) {
+        uint8_t e = 0;
+        if (g[i]) {
+            const int r = hy_find(hy_par, i);
+            e = (strong[r >> 5] >> (r & 31)) & 1u;
+        }
+        edges[(size_t)b * n + i] = e;
+    }
+}
+
 }  // namespace cm
 
 extern "C" size_t cm_canny_workspace_bytes(int batch, int h, int w) {
@@ -237,7 +299,13 @@ extern "C" int cm_canny(const void* image, int image_is_u8, int batch, int h, in
         canny_sobel_kernel<<<grid, 128, 0, st>>>(ws.smooth, h, w, ws.isob, ws.jsob, ws.mag);
         canny_nms_kernel<<<grid, 128, 0, st>>>(ws.isob, ws.jsob, ws.mag, h, w, low_threshold, high_threshold, ws.cls);
     }
-    {
+    if ((size_t)h * w <= 65536 && !getenv("CM_CANNY_SWEEP_HYSTERESIS")) {
+        const size_t n = (size_t)h * w, smem = ((n + 7) & ~(size_t)7) * 2 + ((n + 31) / 32) * 4;
+        static PerDeviceOnce attr2;
+        if (attr2.first()) cudaFuncSetAttribute(canny_hysteresis_uf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
+        CM_TIMED("canny_hysteresis", st);
+        canny_hysteresis_uf_kernel<<<batch, 1024, smem, st>>>(ws.cls, h, w, edges);
+    } else {
         const size_t smem = (size_t)h * w;
         const int use_smem = smem <= 200 * 1024;
         static PerDeviceOnce attr;

@@ -237,6 +237,8 @@ __global__ void __launch_bounds__(256) slic_update_kernel(const double* __restri
     int ylo, yhi, xlo, xhi;
     slic_window(so[0], g.step_y, H, &ylo, &yhi);
     slic_window(so[1], g.step_x, W, &xlo, &xhi);
+    __shared__ double s_val[8][32][3];   // per warp: the three colours of the chunk's member pixels
+    double (*sv)[3] = s_val[threadIdx.x >> 5];
     double acc = 0;
     int cnt = 0;
     for (int y = ylo; y < yhi; ++y) {
@@ -247,20 +249,22 @@ __global__ void __launch_bounds__(256) slic_update_kernel(const double* __restri
             unsigned m = __ballot_sync(~0u, mine);
             if (!m) continue;
             cnt += __popc(m);
-            double v2 = 0, v3 = 0, v4 = 0;
             if (mine) {
                 const double* p = feat + 3 * (row + x);
-                v2 = p[0];
-                v3 = p[1];
-                v4 = p[2];
+                sv[lane][0] = p[0];
+                sv[lane][1] = p[1];
+                sv[lane][2] = p[2];
             }
-            while (m) {
+            __syncwarp();
+            const int cc = max(c - 2, 0);
+            const double yv = (double)y;
+            while (m) {   // one pass for all five sums: the colour comes from the staging rows, y / x are known without memory
                 const int src = __ffs(m) - 1;
                 m &= m - 1;
-                const double a2 = __shfl_sync(~0u, v2, src), a3 = __shfl_sync(~0u, v3, src), a4 = __shfl_sync(~0u, v4, src);
-                const double v = c == 0 ? (double)y : (c == 1 ? (double)(x0 + src) : (c == 2 ? a2 : (c == 3 ? a3 : a4)));
-                acc = __dadd_rn(acc, v);
+                const double col = sv[src][cc];
+                acc = __dadd_rn(acc, c == 0 ? yv : (c == 1 ? (double)(x0 + src) : col));
             }
+            __syncwarp();
         }
     }
     if (lane < 5) seg_new[(size_t)i * 5 + lane] = __ddiv_rn(acc, (double)cnt);   // 0 / 0 = NaN for an emptied cluster, as in the reference loop
