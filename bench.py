@@ -317,6 +317,70 @@ def train_block(args, dev, world, rank):
             "kernels": {k: round(v[1], 4) for k, v in top}}
 
 
+def image_in_block(args, dev, world, gnn, det, kg, pool, barrier, over_ranks):
+    """The path as the reference ships it, from the IMAGE: SLIC superpixels + Canny edge map on the device (cm_slic,
+    cm_canny), then the same graph build / GNN / fusion / metrics.  Only uint8 RGB + a bit-packed ground truth cross PCIe
+    (3.125 B/pixel).  Device-resident and host-to-host throughput at batch 32 per GPU."""
+    from camouflage_multimodal_b200 import _lib
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, HostPipeline
+    lanes = 2
+    pipes = [EvalPipeline(gnn, det, kg, label_cap=LABEL_CAP, lane=40 + k) for k in range(lanes)]
+    streams = [torch.cuda.Stream(dev) for _ in range(lanes)]
+    main = torch.cuda.current_stream(dev)
+    n = min(len(pool), 4)
+    graphs = [pipes[j % lanes].capture(pool[j].images, None, None, pool[j].gt) for j in range(n)]
+    steps = max(4, min(args.steps, 10))
+
+    def region():
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for st in streams:
+            st.wait_stream(main)
+        for s in range(steps):
+            with torch.cuda.stream(streams[s % n % lanes]):
+                graphs[s % n][0].replay()
+        for st in streams:
+            main.wait_stream(st)
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1)
+
+    region()
+    ms = over_ranks([region() for _ in range(7)])
+    status = int(graphs[0][1]["status"].item())
+    if status:
+        raise SystemExit(f"image-in graph build overflow status {status}")
+    stager = HostPipeline(pipes, BATCH, H, W, dev, slots=2 * lanes, use_graph=True, image_dtype=torch.uint8, packed_masks=True, image_only=True)
+    host = [stager.host_batch().fill(pool[j].images.cpu(), None, None, pool[j].gt.cpu()) for j in range(n)]
+    for s in range(2 * lanes):
+        stager.submit(s, host[s % n])
+    stager.synchronize()
+
+    def e2e_region():
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(steps):
+            stager.submit(s, host[s % n])
+        stager.synchronize()
+        return time.perf_counter() - t0
+
+    e2e_s = over_ranks([e2e_region() for _ in range(7)])
+    _lib.timing_enable(True)
+    pipes[0].run(pool[0].images, None, None, pool[0].gt)
+    torch.cuda.synchronize()
+    rep = _lib.timing_report()
+    _lib.timing_enable(False)
+    front = {k: round(v[1] * 1e3, 1) for k, v in rep.items() if k.startswith("slic_") or k.startswith("canny_")}
+    return {"workload": "BASELINE configs[0] in batch form: uint8 image in -> device SLIC (n_segments 500, compactness 10, sigma 1, 10 iterations, "
+                        "connectivity enforced) + Canny (sigma 2) -> graph build -> RG-GNN -> fusion + heads -> paint -> metrics",
+            "value": steps * BATCH * world / (statistics.median(ms) / 1e3), "unit": "images/sec", "ms_per_step": statistics.median(ms) / steps,
+            "steps": steps, "repeats": len(ms), "lanes": lanes,
+            "e2e": {"value": steps * BATCH * world / statistics.median(e2e_s), "unit": "images/sec", "h2d_bytes_per_step": stager.h2d_bytes,
+                    "d2h_bytes_per_step": stager.d2h_bytes, "host_format": "uint8 RGB + 1-bit gt: 3.125 B/pixel"},
+            "front_end_us_per_step": front}
+
+
 def b200_arm(args):
     import torch.distributed as dist
 
@@ -575,6 +639,7 @@ def b200_arm(args):
                 "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "launches_per_step": tk["launches_per_step"],
                 "ms_per_step": tk["ms_per_step"], "share_of_kernel_time": tk["ms_per_step"] / sum(v["ms_per_step"] for v in kernels.values())}
 
+    image_in = None if (args.no_image_in or args.input != "u8") else image_in_block(args, dev, world, gnn, det, kg, pool, barrier, over_ranks)
     train = None if args.no_train else train_block(args, dev, world, rank)
 
     if rank == 0:
@@ -598,7 +663,7 @@ def b200_arm(args):
                             "before the e2e loop; h2d_achieved_gbs / h2d_probe_gbs is the fraction of the PCIe roofline"},
             "gpu_launches": int(round(launches_per_step * args.steps)),
             "roofline": roofline, "kernels": kernels, "kernels_saturated": saturated,
-            "nodes_per_step": n_nodes, "edges_per_step": n_edges, "metrics_summary": summary, "train": train,
+            "nodes_per_step": n_nodes, "edges_per_step": n_edges, "metrics_summary": summary, "image_in": image_in, "train": train,
         }
         if world == 1 and not args.no_cpu_baseline:
             gsd, fsd = cpu_state_dicts(gnn, det)
@@ -645,6 +710,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying CUDA graphs")
     ap.add_argument("--repeats", type=int, default=0, help="timed regions of --steps steps each (0 = at least 25 and at least 100 ms in total)")
     ap.add_argument("--no-train", action="store_true", help="skip the configs[3] training-step block")
+    ap.add_argument("--no-image-in", action="store_true", help="skip the image-in block (device SLIC + Canny in front of the path)")
     ap.add_argument("--byte-masks", action="store_true",
                     help="e2e: send the Canny map and the ground truth one BYTE per pixel (default: one bit per pixel, unpacked on the device)")
     ap.add_argument("--train-batch", type=int, default=16)

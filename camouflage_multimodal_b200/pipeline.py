@@ -29,6 +29,7 @@ class EvalPipeline:
         times the cost of the other seven; its slot is NaN when off)."""
         self.lane = int(lane)
         self.sod_metrics, self.weighted_f = bool(sod_metrics), bool(weighted_f)
+        self.n_segments = 500   # create_region_graph(image, n_segments=500), extract_rg_embeddings.py:138
         self.gnn, self.detector = gnn.eval(), detector.eval()
         kg = kg.reshape(-1, kg.shape[-1])
         _lib.require_cuda(kg, "kg")
@@ -66,7 +67,10 @@ class EvalPipeline:
 
     def run(self, images, labels, canny, gt):
         """Device inputs: images [B,H,W,3] f32 (or uint8 = byte/255), labels [B,H,W] i32 (or int16), canny [B,H,W] u8,
-        gt [B,H,W] u8.  ``canny`` / ``gt`` may instead be bit-packed ``[B, H*W/8]`` uint8 (one bit per pixel,
+        gt [B,H,W] u8.  ``labels=None`` / ``canny=None`` (uint8 images): the front end of the reference's path as shipped runs
+        on the device first -- SLIC superpixels (``cm_slic``: n_segments 500, compactness 10, sigma 1,
+        extract_rg_embeddings.py:143-144) and the Canny edge map (``cm_canny``, sigma 2, :151-152) -- so only the image
+        and the ground truth cross PCIe.  ``canny`` / ``gt`` may instead be bit-packed ``[B, H*W/8]`` uint8 (one bit per pixel,
         ``pack_mask_bits``; a set gt bit means 255): they are unpacked on the device first (``cm_unpack_bits``).
         Returns a dict of device tensors (valid until the next call).  ``out["status"]`` is the graph build's overflow
         word ([1] i32, non-zero = a label >= label_cap was dropped or the node / edge capacity truncated the graph, see
@@ -84,6 +88,20 @@ class EvalPipeline:
         B, H, W, _ = images.shape
         dev = images.device
         self._alloc(B, H, W, dev)
+        if labels is None or canny is None:     # image-only input: device SLIC / Canny
+            from .region_graph import canny_edges, slic_segments
+            if images.dtype != torch.uint8:
+                raise ValueError("the device front end takes uint8 images (the reference hands skimage.slic (image * 255).astype(uint8))")
+            if labels is None:
+                buf = self._bufs.get("slic_labels")
+                if buf is None or buf.shape != (B, H, W):
+                    buf = self._bufs["slic_labels"] = torch.empty((B, H, W), dtype=torch.int32, device=dev)
+                labels = slic_segments(images, n_segments=self.n_segments, compactness=10.0, sigma=1.0, out=buf)
+            if canny is None:
+                buf = self._bufs.get("canny_map")
+                if buf is None or buf.shape != (B, H, W):
+                    buf = self._bufs["canny_map"] = torch.empty((B, H, W), dtype=torch.uint8, device=dev)
+                canny = canny_edges(images, sigma=2.0, out=buf)
         if canny.dim() == 2 or gt.dim() == 2:      # bit-packed masks: one bit per pixel over PCIe, bytes again here
             for name, t, one in (("canny", canny, 1), ("gt", gt, 255)):
                 if t.dim() != 2:
@@ -194,14 +212,19 @@ class BatchBuffer:
     Canny map and the ground truth travel one bit per pixel (``[B, H*W/8]`` uint8; 7 -> 5.25 bytes per pixel with uint8
     images + int16 labels) -- for binary masks only: a set gt bit is read as 255."""
 
-    def __init__(self, B, H, W, image_dtype=torch.float32, label_dtype=torch.int32, device=None, packed_masks=False):
-        self.packed_masks = bool(packed_masks)
+    def __init__(self, B, H, W, image_dtype=torch.float32, label_dtype=torch.int32, device=None, packed_masks=False, image_only=False):
+        """``image_only``: no label / Canny views -- the device front end (cm_slic, cm_canny) derives both from the image,
+        so a batch is uint8 RGB + the ground truth (3.125 bytes per pixel with a bit-packed mask)."""
+        self.packed_masks, self.image_only = bool(packed_masks), bool(image_only)
         mshape = (B, H * W // 8) if packed_masks else (B, H, W)
         if packed_masks and (H * W) % 8:
             raise ValueError("packed masks need H*W % 8 == 0")
-        shapes = (((B, H, W, 3), image_dtype), ((B, H, W), label_dtype), (mshape, torch.uint8), (mshape, torch.uint8))
+        shapes = [("images", (B, H, W, 3), image_dtype)]
+        if not image_only:
+            shapes += [("labels", (B, H, W), label_dtype), ("canny", mshape, torch.uint8)]
+        shapes.append(("gt", mshape, torch.uint8))
         offs, total = [], 0
-        for shp, dt in shapes:
+        for _, shp, dt in shapes:
             offs.append(total)
             n = 1
             for d in shp:
@@ -209,20 +232,23 @@ class BatchBuffer:
             total += (n * torch.empty((), dtype=dt).element_size() + 255) // 256 * 256
         self.flat = (torch.empty(total, dtype=torch.uint8, pin_memory=True) if device is None
                      else torch.empty(total, dtype=torch.uint8, device=device))
-        views = []
-        for (shp, dt), o in zip(shapes, offs):
+        self.images = self.labels = self.canny = self.gt = None
+        self.payload_bytes = 0
+        for (name, shp, dt), o in zip(shapes, offs):
             n = 1
             for d in shp:
                 n *= d
-            views.append(self.flat[o:o + n * torch.empty((), dtype=dt).element_size()].view(dt).view(shp))
-        self.images, self.labels, self.canny, self.gt = views
-        self.payload_bytes = sum(v.numel() * v.element_size() for v in views)
+            v = self.flat[o:o + n * torch.empty((), dtype=dt).element_size()].view(dt).view(shp)
+            setattr(self, name, v)
+            self.payload_bytes += v.numel() * v.element_size()
 
     def fill(self, images, labels, canny, gt):
-        """Copy a batch in; with ``packed_masks`` byte masks ``[B,H,W]`` are bit-packed on the way (host work)."""
+        """Copy a batch in; with ``packed_masks`` byte masks ``[B,H,W]`` are bit-packed on the way (host work); with
+        ``image_only`` the label and Canny maps are ignored."""
         self.images.copy_(images)
-        self.labels.copy_(labels)
-        self.canny.copy_(pack_mask_bits(canny) if self.packed_masks and canny.dim() == 3 else canny)
+        if not self.image_only:
+            self.labels.copy_(labels)
+            self.canny.copy_(pack_mask_bits(canny) if self.packed_masks and canny.dim() == 3 else canny)
         self.gt.copy_(pack_mask_bits(gt) if self.packed_masks and gt.dim() == 3 else gt)
         return self
 
@@ -230,11 +256,11 @@ class BatchBuffer:
 class HostStager:
     """Pinned host buffers + device buffers for one batch: the host-facing entry of the pipeline."""
 
-    def __init__(self, B, H, W, device, image_dtype=torch.float32, label_dtype=torch.int32, packed_masks=False):
+    def __init__(self, B, H, W, device, image_dtype=torch.float32, label_dtype=torch.int32, packed_masks=False, image_only=False):
         self.dev = device
         pin = dict(pin_memory=True)
-        self.h_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, packed_masks=packed_masks)
-        self.d_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, device=device, packed_masks=packed_masks)
+        self.h_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, packed_masks=packed_masks, image_only=image_only)
+        self.d_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, device=device, packed_masks=packed_masks, image_only=image_only)
         self.h_images, self.h_labels, self.h_canny, self.h_gt = (self.h_batch.images, self.h_batch.labels, self.h_batch.canny,
                                                                  self.h_batch.gt)
         self.d_images, self.d_labels, self.d_canny, self.d_gt = (self.d_batch.images, self.d_batch.labels, self.d_batch.canny,
@@ -243,7 +269,7 @@ class HostStager:
         self.h_per_image = torch.empty((B, 7), dtype=torch.float64, **pin)
         self.h_status = torch.zeros(1, dtype=torch.int32, **pin)
         self.h_per_image_sod = torch.empty((B, len(metrics.SOD_KEYS)), dtype=torch.float64, **pin)
-        self.h2d_bytes = sum(t.numel() * t.element_size() for t in (self.h_images, self.h_labels, self.h_canny, self.h_gt))
+        self.h2d_bytes = self.h_batch.payload_bytes
         self.d2h_bytes = sum(t.numel() * t.element_size() for t in (self.h_mask_out, self.h_per_image, self.h_status, self.h_per_image_sod))
 
     def fill(self, batch):
@@ -273,17 +299,18 @@ class HostPipeline:
     kernels, slots sharing a pipeline are serialised through ``pipe_done`` events (they share its buffers)."""
 
     def __init__(self, pipe, B, H, W, device, slots: int = 2, use_graph: bool = True, image_dtype=torch.float32,
-                 label_dtype=torch.int32, packed_masks: bool = False):
+                 label_dtype=torch.int32, packed_masks: bool = False, image_only: bool = False):
         pipes = list(pipe) if isinstance(pipe, (list, tuple)) else [pipe]
         self.pipes, self.dev = pipes, device
         self.pipe_done = [torch.cuda.Event() for _ in pipes]
         self.slots = []
         for k in range(slots):
-            st = HostStager(B, H, W, device, image_dtype, label_dtype, packed_masks=packed_masks)
+            st = HostStager(B, H, W, device, image_dtype, label_dtype, packed_masks=packed_masks, image_only=image_only)
             st.pipe_idx = k % len(pipes)
             st.stream = torch.cuda.Stream(device)
-            st.d_labels.fill_(1)
-            st.d_images.zero_(); st.d_canny.zero_(); st.d_gt.zero_()
+            st.d_batch.flat.zero_()
+            if st.d_labels is not None:
+                st.d_labels.fill_(1)
             st.ev_done = torch.cuda.Event()
             st.graph, st.out = pipes[st.pipe_idx].capture(st.d_images, st.d_labels, st.d_canny, st.d_gt) if use_graph else (None, None)
             st.ev_done.record(torch.cuda.current_stream(device))
@@ -296,7 +323,8 @@ class HostPipeline:
         """A pinned host batch in the layout of the device slots: fill its ``images / labels / canny / gt`` views (e.g.
         decode straight into them) and pass it to ``submit`` -- it then crosses PCIe as ONE copy."""
         st = self.slots[0]
-        return BatchBuffer(*st.h_images.shape[:3], st.h_images.dtype, st.h_labels.dtype, packed_masks=st.h_batch.packed_masks)
+        return BatchBuffer(*st.h_images.shape[:3], st.h_images.dtype, st.h_labels.dtype if st.h_labels is not None else torch.int32,
+                           packed_masks=st.h_batch.packed_masks, image_only=st.h_batch.image_only)
 
     def submit(self, i, h_images, h_labels=None, h_canny=None, h_gt=None):
         """Queue batch ``i``: a ``BatchBuffer`` from ``host_batch()`` (one H2D copy) or four pinned host tensors (four
@@ -309,8 +337,9 @@ class HostPipeline:
                 st.d_batch.flat.copy_(h_images.flat, non_blocking=True)
             else:
                 st.d_images.copy_(h_images, non_blocking=True)
-                st.d_labels.copy_(h_labels, non_blocking=True)
-                st.d_canny.copy_(h_canny, non_blocking=True)
+                if st.d_labels is not None:
+                    st.d_labels.copy_(h_labels, non_blocking=True)
+                    st.d_canny.copy_(h_canny, non_blocking=True)
                 st.d_gt.copy_(h_gt, non_blocking=True)
             st.stream.wait_event(self.pipe_done[st.pipe_idx])     # another slot may be using this pipeline's buffers
             if st.graph is not None:

@@ -265,3 +265,30 @@ def test_bit_packed_masks_equal_byte_masks(models):
     hp.synchronize()
     assert torch.equal(st.h_mask_out, ref_mask) and torch.equal(st.h_per_image, ref_per)
     assert torch.equal(st.h_per_image_sod[:, :7], ref_sod[:, :7])
+
+
+def test_image_only_pipeline_equals_explicit_front_end(models):
+    """configs[0] "as shipped" in batch form: only uint8 images + ground truth go in, cm_slic / cm_canny run on the device
+    inside the (captured) step; identical to running the front end by hand and feeding its maps to the pipeline."""
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, HostPipeline
+    from camouflage_multimodal_b200.region_graph import canny_edges, slic_segments
+    gnn, det, kg, _, _ = models
+    B = 4
+    dev = torch.device("cuda")
+    b = synth.make_batch(31, B, seed=1234).as_decoded()
+    d = b.to("cuda")
+    lab = slic_segments(d.images)
+    can = canny_edges(d.images)
+    ref = EvalPipeline(gnn, det, kg, label_cap=544, lane=30).run(d.images, lab, can, d.gt)
+    ref_mask, ref_per = ref["mask_out"].cpu(), ref["per_image"].cpu()
+    got = EvalPipeline(gnn, det, kg, label_cap=544, lane=31).run(d.images, None, None, d.gt)
+    assert torch.equal(got["mask_out"].cpu(), ref_mask) and torch.equal(got["per_image"].cpu(), ref_per)
+    assert int(got["status"].item()) == 0
+    hp = HostPipeline(EvalPipeline(gnn, det, kg, label_cap=544, lane=32), B, 256, 256, dev, slots=2, use_graph=True,
+                      image_dtype=torch.uint8, packed_masks=True, image_only=True)
+    hb = hp.host_batch().fill(b.images, None, None, b.gt)
+    assert hb.payload_bytes == B * 65536 * 3 + B * 8192 and hb.labels is None
+    for j in range(3):                     # slot reuse through the captured graphs
+        st = hp.submit(j, hb)
+    hp.synchronize()
+    assert torch.equal(st.h_mask_out, ref_mask) and torch.equal(st.h_per_image, ref_per)
