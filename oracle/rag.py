@@ -4,9 +4,13 @@ PARITY UNPINNED: the reference calls ``skimage.graph.rag_mean_color(image_for_sl
 (models/region_graph/extract_rg_embeddings.py:216) and reads only ``rag.edges()`` (:220).
 scikit-image (>=0.21.0, unpinned, models/region_graph/requirements.txt:4) is not installed, so this
 restates its published algorithm: ``graph.RAG(labels, connectivity=2)`` runs
-``scipy.ndimage.generic_filter`` over the label image with the full 3x3 footprint
-(``generate_binary_structure(2, 2)``), ``mode='nearest'``, and its callback adds an undirected
+``scipy.ndimage.generic_filter`` over the label image with the 3x3 footprint of
+``generate_binary_structure(2, 2)``, ``mode='nearest'``, and its callback adds an undirected
 networkx edge ``(centre, v)`` for every footprint value ``v != centre`` not yet present.
+scikit-image zeroes the "backward" half of that footprint before filtering (each unordered pixel pair
+is then visited once, from its raster-earlier pixel); this restatement keeps the FULL 3x3 footprint.
+The edge SET is identical -- a pair of touching labels is found from either side -- only networkx's
+insertion order can differ, and everything downstream compares on the canonical sorted order.
 """
 from __future__ import annotations
 
