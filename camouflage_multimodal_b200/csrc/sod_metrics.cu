@@ -15,12 +15,14 @@
 // The prediction is either a dense float map or PAINTED on the fly from the label map and the per-node probabilities
 // (models/region_graph/test.py:241-244, the same gather cm_paint_metrics does) -- the pipeline never writes the mask.
 // The weighted F-measure (feature transform + 7x7 filter: the expensive part) is optional.
+// (A single cluster-of-8 launch per batch -- pass 1, cluster barrier, pass 2, barrier, closed forms -- was built and measured
+// slower in the pipeline: 151 us against 78 us for these three small launches, and the step fell from 151 k to 116 k img/s,
+// because eight co-scheduled CTAs per image have to wait for SMs that fusion_node's full-shared-memory CTAs hold, whereas
+// independent small CTAs slip into the gaps.)
 // Every float64 sum is a per-thread running sum -> warp shuffle tree -> fixed-order block / chunk combination: the
 // result does not depend on scheduling (no floating-point atomics).  Bound: HBM/L2 on pred (4 B) + gt (1 B) per pixel,
 // read three times (the second and third from L2 at batch 32: 10 MB).
-#include <cooperative_groups.h>
 #include <math.h>
-#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -445,15 +447,15 @@ __device__ __forceinline__ double sod_s_object(double sum, double sum2, double n
 }
 
 // one block of 256 threads per image: thread t owns curve entry t (threshold q >= 255 - t)
-__device__ __forceinline__ void sod_finalize_body(int b, const double* __restrict__ tot1, const double* __restrict__ tot2,
-                                                  const double* __restrict__ shift, const double* __restrict__ p4, int wf_tiles,
-                                                  const int* __restrict__ hist, int H, int W, double beta2_f, double beta2_wf,
-                                                  double* __restrict__ per_image, double* __restrict__ curves, int* __restrict__ done_counter,
-                                                  int batch, double* __restrict__ partial) {
+__global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restrict__ tot1, const double* __restrict__ tot2, const double* __restrict__ shift,
+                                                           const double* __restrict__ p4, int wf_tiles, const int* __restrict__ hist, int H, int W,
+                                                           double beta2_f, double beta2_wf, double* __restrict__ per_image,
+                                                           double* __restrict__ curves, int* __restrict__ done_counter, int batch,
+                                                           double* __restrict__ partial) {
     __shared__ int s_tp[256], s_fp[256], s_wtp[8], s_wfp[8], s_last;
     __shared__ double s_f[256], s_e[256], s_fm[256], s_em[256];
     __shared__ double s_tot[SOD_P1], s_q[SOD_P2], s_wf[2];
-    const int t = threadIdx.x;
+    const int b = blockIdx.x, t = threadIdx.x;
     const double n = (double)H * (double)W;
     s_tp[t] = hist[(size_t)b * 512 + 255 - t];
     s_fp[t] = hist[(size_t)b * 512 + 256 + 255 - t];
@@ -616,170 +618,6 @@ __device__ __forceinline__ void sod_finalize_body(int b, const double* __restric
         partial[i] = sum;
     }
 }
-__global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restrict__ tot1, const double* __restrict__ tot2, const double* __restrict__ shift,
-                                                           const double* __restrict__ p4, int wf_tiles, const int* __restrict__ hist, int H, int W,
-                                                           double beta2_f, double beta2_wf, double* __restrict__ per_image,
-                                                           double* __restrict__ curves, int* __restrict__ done_counter, int batch,
-                                                           double* __restrict__ partial) {
-    sod_finalize_body(blockIdx.x, tot1, tot2, shift, p4, wf_tiles, hist, H, W, beta2_f, beta2_wf, per_image, curves, done_counter, batch, partial);
-}
-
-// ------------------------------------------------------------------------------------------------ fused: one launch per batch
-// Images of at most 65 536 pixels: a cluster of 8 CTAs owns one image and runs pass 1 -> cluster barrier (the image
-// totals: centroid, adaptive threshold) -> pass 2 -> cluster barrier -> closed forms (CTA 0) in ONE launch; the second
-// pass re-reads its pixels from L2.  (Keeping the 32 pixels of a thread in registers across the barrier was measured
-// slower: 159 registers = one CTA per SM, so the 256 CTAs of a batch of 32 no longer fit one wave.)
-// The chunk partials go through global memory (p1 / p2, fixed summation order), fenced before each barrier.
-constexpr int SF_CL = 8;
-__global__ void __cluster_dims__(SF_CL, 1, 1) __launch_bounds__(256, 3)
-    sod_fused_kernel(const SodSrc src, const uint8_t* __restrict__ gt, int H, int W, double* __restrict__ p1, double* __restrict__ p2,
-                     double* __restrict__ tot1, double* __restrict__ tot2, double* __restrict__ shift, int* __restrict__ hist,
-                     const double* __restrict__ p4, int wf_tiles, double* __restrict__ per_image, double* __restrict__ curves,
-                     int* __restrict__ done_counter, int batch, double* __restrict__ partial) {
-    namespace cg = cooperative_groups;
-    cg::cluster_group cluster = cg::this_cluster();
-    __shared__ int s_hist[512];
-    __shared__ double s_red[8 * SOD_P2];
-    __shared__ double s_tot[SOD_P1], s_shift[4];
-    const int b = blockIdx.y, c = blockIdx.x, HW = H * W, lane = threadIdx.x & 31;
-    const SodPix px(src, b, (size_t)HW);
-    const uint8_t* g = gt + (size_t)b * HW;
-    const int per = (HW + SF_CL - 1) / SF_CL, i0 = c * per, i1 = min(i0 + per, HW);
-    for (int i = threadIdx.x; i < 512; i += 256) s_hist[i] = 0;
-    __syncthreads();
-    // ---- pass 1 (as sod_pass1_kernel)
-    {
-        double v[SOD_P1] = {0, 0, 0, 0, 0, 0, 0, 0};
-        int n_fg = 0, sy = 0, sx = 0;
-        for (int base = i0; base < i1; base += 256 * SOD_ILP) {
-            float pv[SOD_ILP];
-            unsigned char gv[SOD_ILP];
-#pragma unroll
-            for (int u = 0; u < SOD_ILP; ++u) {
-                const int i = base + u * 256 + threadIdx.x;
-                pv[u] = i < i1 ? px.at(i) : 0.f;
-                gv[u] = i < i1 ? g[i] : 0;
-            }
-#pragma unroll
-            for (int u = 0; u < SOD_ILP; ++u) {
-                const int i = base + u * 256 + threadIdx.x;
-                const bool in = i < i1;
-                const double p = (double)pv[u];
-                const bool fg = in && gv[u] >= 128;
-                int q = (int)(p * 255.0);
-                q = min(max(q, 0), 255);
-                const int key = in ? (fg ? 0 : 256) + q : -1;
-                const int prev = __shfl_up_sync(0xffffffffu, key, 1);
-                const unsigned heads = __ballot_sync(0xffffffffu, lane == 0 || key != prev);
-                if (key >= 0 && ((heads >> lane) & 1u)) {
-                    const unsigned later = lane == 31 ? 0u : heads >> (lane + 1);
-                    atomicAdd(&s_hist[key], later ? __ffs(later) : 32 - lane);
-                }
-                if (!in) continue;
-                const int y = i / W;
-                v[7] += p;
-                n_fg += fg;
-                sy += fg ? y : 0;
-                sx += fg ? i - y * W : 0;
-                v[3] += fg ? p : 0.0;
-                v[4] += fg ? p * p : 0.0;
-                const double o = 1.0 - p;
-                v[5] += fg ? 0.0 : o;
-                v[6] += fg ? 0.0 : o * o;
-            }
-        }
-        v[0] = (double)n_fg;
-        v[1] = (double)sy;
-        v[2] = (double)sx;
-        block_sum<SOD_P1>(v, s_red);
-        if (threadIdx.x == 0) {
-            double* o = p1 + ((size_t)b * SF_CL + c) * SOD_P1;
-#pragma unroll
-            for (int k = 0; k < SOD_P1; ++k) o[k] = v[k];
-        }
-        __syncthreads();
-        for (int i = threadIdx.x; i < 512; i += 256)
-            if (s_hist[i]) atomicAdd(&hist[(size_t)b * 512 + i], s_hist[i]);
-    }
-    __threadfence();
-    cluster.sync();
-    // ---- image totals (every CTA, same chunk order), centroid, adaptive threshold, corner pixels
-    if (threadIdx.x < SOD_P1) {
-        double t = 0.0;
-        for (int k = 0; k < SF_CL; ++k) t += __ldcg(p1 + ((size_t)b * SF_CL + k) * SOD_P1 + threadIdx.x);
-        s_tot[threadIdx.x] = t;
-        if (c == 0) tot1[(size_t)b * SOD_P1 + threadIdx.x] = t;
-    }
-    __syncthreads();
-    int cx, cy;
-    sod_centroid(s_tot, H, W, &cx, &cy);
-    const double thr = fmin(2.0 * (s_tot[7] / (double)HW), 1.0);
-    if (threadIdx.x < 4) {
-        const int k = threadIdx.x, y0 = (k & 2) ? cy : 0, x0 = (k & 1) ? cx : 0;
-        const double sh = (y0 < H && x0 < W) ? (double)px.at(y0 * W + x0) : 0.0;
-        s_shift[k] = sh;
-        if (c == 0) shift[(size_t)b * 4 + k] = sh;
-    }
-    __syncthreads();
-    // ---- pass 2 (as sod_pass2_kernel): the pixels come back from L2
-    {
-        double v[SOD_P2];
-#pragma unroll
-        for (int k = 0; k < SOD_P2; ++k) v[k] = 0.0;
-        int gq[4] = {0, 0, 0, 0}, tpa = 0, fpa = 0;
-        for (int base = i0; base < i1; base += 256 * SOD_ILP) {
-            float pv[SOD_ILP];
-            unsigned char gv[SOD_ILP];
-#pragma unroll
-            for (int u = 0; u < SOD_ILP; ++u) {
-                const int i = base + u * 256 + threadIdx.x;
-                pv[u] = i < i1 ? px.at(i) : 0.f;
-                gv[u] = i < i1 ? g[i] : 0;
-            }
-#pragma unroll
-            for (int u = 0; u < SOD_ILP; ++u) {
-                const int i = base + u * 256 + threadIdx.x;
-                if (i >= i1) continue;
-                const double p = (double)pv[u];
-                const bool fg = gv[u] >= 128;
-                const int y = i / W, x = i - y * W;
-                const int k = (y >= cy ? 2 : 0) + (x >= cx ? 1 : 0);
-                const double d = p - s_shift[k], dd = d * d, dg = fg ? d : 0.0;
-                switch (k) {
-                    case 0: v[0] += d; v[1] += dd; v[2] += dg; gq[0] += fg; break;
-                    case 1: v[3] += d; v[4] += dd; v[5] += dg; gq[1] += fg; break;
-                    case 2: v[6] += d; v[7] += dd; v[8] += dg; gq[2] += fg; break;
-                    default: v[9] += d; v[10] += dd; v[11] += dg; gq[3] += fg; break;
-                }
-                if (p >= thr) {
-                    tpa += fg;
-                    fpa += !fg;
-                }
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) v[12 + j] = (double)gq[j];
-        v[16] = (double)tpa;
-        v[17] = (double)fpa;
-        block_sum<SOD_P2>(v, s_red);
-        if (threadIdx.x == 0) {
-            double* o = p2 + ((size_t)b * SF_CL + c) * SOD_P2;
-#pragma unroll
-            for (int k = 0; k < SOD_P2; ++k) o[k] = v[k];
-        }
-    }
-    __threadfence();
-    cluster.sync();
-    if (c != 0) return;
-    if (threadIdx.x < SOD_P2) {
-        double t = 0.0;
-        for (int k = 0; k < SF_CL; ++k) t += __ldcg(p2 + ((size_t)b * SF_CL + k) * SOD_P2 + threadIdx.x);
-        tot2[(size_t)b * SOD_P2 + threadIdx.x] = t;
-    }
-    __threadfence();
-    __syncthreads();
-    sod_finalize_body(b, tot1, tot2, shift, p4, wf_tiles, hist, H, W, 0.3, 1.0, per_image, curves, done_counter, batch, partial);
-}
 
 }  // namespace cm
 
@@ -803,16 +641,13 @@ static int sod_metrics_impl(const cm::SodSrc& src, const uint8_t* gt, int batch,
     cudaStream_t st = as_stream(stream);
     cudaMemsetAsync(ws.hist, 0, ((size_t)batch * 512 + 2 * (size_t)batch + 1) * sizeof(int), st);
     int* counters = ws.hist + (size_t)batch * 512;   // [B] pass 1, [B] pass 2, [1] finalize
-    const bool fused = (long long)h * w <= 65536 && !getenv("CM_SOD_UNFUSED");
-    if (!fused) {
-        {
-            CM_TIMED("sod_pass1", st);
-            sod_pass1_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.p1, ws.hist, counters, ws.tot1);
-        }
-        {
-            CM_TIMED("sod_pass2", st);
-            sod_pass2_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.tot1, ws.p2, ws.shift, counters + batch, ws.tot2);
-        }
+    {
+        CM_TIMED("sod_pass1", st);
+        sod_pass1_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.p1, ws.hist, counters, ws.tot1);
+    }
+    {
+        CM_TIMED("sod_pass2", st);
+        sod_pass2_kernel<<<dim3(SOD_CHUNKS, batch), 256, 0, st>>>(src, gt, h, w, ws.tot1, ws.p2, ws.shift, counters + batch, ws.tot2);
     }
     if (with_weighted_f) {
         Gauss7 gk;   // Matlab fspecial('gaussian', 7, 5)
@@ -833,12 +668,7 @@ static int sod_metrics_impl(const cm::SodSrc& src, const uint8_t* gt, int batch,
             sod_wf_kernel<<<dim3(ceil_div(w, 32), ceil_div(h, 8), batch), 256, 0, st>>>(src, gt, ws.d2, ws.near, h, w, gk, ws.p4);
         }
     }
-    if (fused) {
-        CM_TIMED("sod_fused", st);
-        sod_fused_kernel<<<dim3(SF_CL, batch), 256, 0, st>>>(src, gt, h, w, ws.p1, ws.p2, ws.tot1, ws.tot2, ws.shift, ws.hist,
-                                                            with_weighted_f ? ws.p4 : nullptr, ws.wf_tiles, per_image, ws.curves, counters + 2 * batch,
-                                                            batch, partial);
-    } else {
+    {
         CM_TIMED("sod_finalize", st);
         sod_finalize_kernel<<<batch, 256, 0, st>>>(ws.tot1, ws.tot2, ws.shift, with_weighted_f ? ws.p4 : nullptr, ws.wf_tiles, ws.hist, h, w, 0.3, 1.0,
                                                    per_image, ws.curves, counters + 2 * batch, batch, partial);
