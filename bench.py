@@ -317,7 +317,7 @@ def train_block(args, dev, world, rank):
     return {"workload": f"BASELINE configs[3]: training step, batch {B} per GPU (graph build + targets + fwd/bwd both models + both criteria "
                         "+ BatchNorm-statistics and gradient all-reduce + clip + AdamW)",
             "value": steps * B * world / (float(ms.item()) / 1e3), "unit": "images/sec", "ms_per_step": float(ms.item()) / steps,
-            "steps": steps, "batch_per_gpu": B, "n_gpus": world, "loss": float(loss), "launches_per_step": int(sum(v[0] for v in rep.values())),
+            "steps": steps, "batch_per_gpu": B, "n_gpus": world, "loss": float(loss.detach()), "launches_per_step": int(sum(v[0] for v in rep.values())),
             "kernel_ms_per_step": sum(v[1] for v in rep.values()), "bn_sync": sync is not None,
             "kernels": {k: round(v[1], 4) for k, v in top}}
 

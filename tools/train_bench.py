@@ -93,7 +93,7 @@ def main():
         tot = sum(v[1] for v in rep.values())
         print(json.dumps({"metric": "training images/sec (GNN + fusion forward+backward, grad all-reduce, clip, AdamW)",
                           "value": args.steps * B * world / (ms.item() / 1e3), "unit": "images/sec", "n_gpus": world,
-                          "ms_per_step": ms.item() / args.steps, "batch_per_gpu": B, "nodes_per_step": n, "loss": float(loss),
+                          "ms_per_step": ms.item() / args.steps, "batch_per_gpu": B, "nodes_per_step": n, "loss": float(loss.detach()),
                           "dtype": "f32", "kernel_ms_per_step": tot, "launches_per_step": sum(v[0] for v in rep.values()),
                           "kernels": {k: round(v[1], 4) for k, v in sorted(rep.items(), key=lambda kv: -kv[1][1])[:12]}}))
     if world > 1:
