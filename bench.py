@@ -403,6 +403,9 @@ def b200_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _lib.check(_lib.load().cm_device_check(), "cm_device_check")
+    # configs[3] first: the training step is host-launch-bound (280 launches), so it is measured before the evaluation
+    # pipelines have created their streams, captured graphs and pinned buffers (12.6 ms per step after them, 6.9 before)
+    train = None if args.no_train else train_block(args, dev, world, rank)
 
     gnn, det = make_models()
     kg, kg_src = load_kg()
@@ -645,7 +648,6 @@ def b200_arm(args):
                 "ms_per_step": tk["ms_per_step"], "share_of_kernel_time": tk["ms_per_step"] / sum(v["ms_per_step"] for v in kernels.values())}
 
     image_in = None if (args.no_image_in or args.input != "u8") else image_in_block(args, dev, world, gnn, det, kg, pool, barrier, over_ranks)
-    train = None if args.no_train else train_block(args, dev, world, rank)
 
     if rank == 0:
         arm = {"impl": "b200", "lanes": lanes, "host_cores_bound": len(host_cores), "cuda_graph": not args.no_graph,
