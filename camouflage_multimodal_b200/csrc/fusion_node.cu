@@ -136,6 +136,24 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    if (warp >= 2) {
+        // the per-column vectors the epilogues add (biases, LayerNorm gamma / beta: 10 KB; shared memory is full) are pulled
+        // into L1 now, so the __ldg of every epilogue chunk hits L1 instead of stalling the phase chain on L2
+        const int t = threadIdx.x - 64;   // 0..255: one 128-byte line each
+        auto pf = [&](const float* v, int n_floats) {
+            if (v && t * 32 < n_floats) asm volatile("prefetch.global.L1 [%0];" ::"l"(v + t * 32));
+        };
+        if (MODE == 0) {
+            pf(a.b_rgproj, 256);
+            pf(a.ccat, 256);
+            pf(a.b_v2, 256);
+        }
+        pf(a.b_out1, 256);
+        pf(a.ln_g, 256);
+        pf(a.ln_b, 256);
+        pf(a.b_ffn1, 512);
+        pf(a.b_ffn2, 256);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
