@@ -97,6 +97,7 @@ SIGNATURES = {
     "cm_abi_version": (_i, []),
     "cm_device_check": (_i, []),
     "cm_timing_enable": (None, [_i]),
+    "cm_debug_fusion_phase_stamps": (None, [_fp]),
     "cm_timing_report": (_i, [C.c_char_p, _i]),
     "cm_rag_workspace_bytes": (_sz, [_i, _i]),
     "cm_rag_build": (_i, [_fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp]),

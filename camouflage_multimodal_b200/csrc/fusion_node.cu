@@ -67,6 +67,18 @@ __device__ __forceinline__ uint4 ld_smem_v4(uint32_t addr) {
     asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
     return v;
 }
+// 256-bit global stores (sm_100): a lane writes one full 32-byte sector per instruction.  The row-per-thread epilogues
+// store 128 B (fp32) / 64 B (fp16) pieces at a 512 B / 1 KB stride, so with 16-byte stores every sector was written twice.
+__device__ __forceinline__ void st_global_f32x8(float* p, const float* x) {
+    asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(x[0]), "f"(x[1]), "f"(x[2]), "f"(x[3]), "f"(x[4]),
+                 "f"(x[5]), "f"(x[6]), "f"(x[7])
+                 : "memory");
+}
+__device__ __forceinline__ void st_global_b32x8(void* p, uint4 a, uint4 b) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y),
+                 "r"(b.z), "r"(b.w)
+                 : "memory");
+}
 // 32 fp32 values of row `row`, columns c0..c0+31, into a K-major SW128 activation tile set starting at `base`
 __device__ __forceinline__ void store_chunk_smem(uint32_t base, int row, int c0, const float* x) {
     const uint32_t tile = base + (uint32_t)(c0 >> 6) * FN_KB_TILE;
@@ -158,6 +170,13 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    const bool stamp = a.dbg != nullptr && blockIdx.x == 0;
+    auto now = [] {
+        long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        return t;
+    };
+    if (stamp && threadIdx.x == 0) a.dbg[32] = now();
 
     if (warp == 0) {
         // ------------------------------------------------------------------------------ TMA producer
@@ -185,9 +204,11 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             int t = 0;
             for (int ph = 0; ph < NPH; ++ph) {
                 const FnPhase p = fn_phases[MODE][ph];
+                if (stamp) a.dbg[ph] = now();
                 if (ph == 0) mbar_wait(x_full, 0);
                 else if (p.wait_epi >= 0) mbar_wait(epi_done + p.wait_epi, 0);
                 tc_fence_after();
+                if (stamp) a.dbg[8 + ph] = now();
                 for (int kb = 0; kb < p.a_kb; ++kb, ++t) {
                     const int s = t % FN_STAGES, n = t / FN_STAGES;
                     mbar_wait(w_full + s, n & 1);
@@ -214,11 +235,13 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(epi_done + ph);
+            if (stamp && threadIdx.x == 64) a.dbg[24 + ph] = now();
         };
         auto wait_acc = [&](int ph) {
             mbar_wait(acc_ready + ph, 0);
             __syncwarp();
             tc_fence_after();
+            if (stamp && threadIdx.x == 64) a.dbg[16 + ph] = now();
         };
         float x[32];
 
@@ -322,7 +345,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
                 if (row_ok) {
                     float* o = a.y + (size_t)row * 256 + c0;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+                    for (int j = 0; j < 32; j += 8) st_global_f32x8(o + j, x + j);
                 }
             }
         };
@@ -349,15 +372,24 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             for (int j = 0; j < 32; ++j) am[j] = 0.f;
             for (int c0 = half * 128; c0 < half * 128 + 128; c0 += 32) {
                 load_acc_bias(t1, c0, a.ccat, x);
+                if (stamp && threadIdx.x == 64 && c0 == 0) a.dbg[35] = now();
                 if (half == 0) {
-                    if (a.sm_gs == 16) softmax_groups<16>(x, a.sm_valid, am); else softmax_groups<32>(x, a.sm_valid, am);
+                    if (a.attn_mean) {
+                        if (a.sm_gs == 16) softmax_groups<16, true>(x, a.sm_valid, am); else softmax_groups<32, true>(x, a.sm_valid, am);
+                    } else {
+                        if (a.sm_gs == 16) softmax_groups<16, false>(x, a.sm_valid, am); else softmax_groups<32, false>(x, a.sm_valid, am);
+                    }
+                    if (stamp && threadIdx.x == 64 && c0 == 0) a.dbg[36] = now();
                     store_chunk_smem(sbase + FN_P1, lrow, c0, x);
+                    if (stamp && threadIdx.x == 64 && c0 == 0) a.dbg[37] = now();
                 } else if (row_ok) {
                     float* o = a.s2 + (size_t)row * 128 + (c0 - 128);
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+                    for (int j = 0; j < 32; j += 8) st_global_f32x8(o + j, x + j);
                 }
             }
+            if (stamp && threadIdx.x == 64) a.dbg[33] = now();
+            if (stamp && threadIdx.x == 192) a.dbg[34] = now();
             if (half == 0 && a.attn_mean && row_ok) {
                 const float inv = (float)a.sm_gs / 128.f;   // 1 / heads
 #pragma unroll
@@ -374,7 +406,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             if (row_ok) {
                 op_t* o = a.v2 + (size_t)row * 256 + c0;
 #pragma unroll
-                for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(o + j) = pack8(x + j);
+                for (int j = 0; j < 32; j += 16) st_global_b32x8(o + j, pack8(x + j), pack8(x + j + 8));
             }
         }
         done(2);

@@ -21,6 +21,7 @@ struct FusionNodeArgs {
     op_t* v2;              // [M,256] V of the kg->rg attention
     float* y;              // [M,256] rg stream after the FFN residual
     float* attn_mean;      // [M, sm_valid] head-averaged rg->kg probabilities or NULL
+    long long* dbg = nullptr;   // phase time stamps of CTA 0 (tools/fusion_phase_profile.py): [0..7] MMA issue, [8..15] MMA waited-for, [16..23] epilogue start, [24..31] epilogue done, [32] kernel start
 };
 
 int launch_fusion_node(FusionNodeArgs& a, const void* x, const void* w_rgproj, const void* wcat, const void* wv2, const void* vot,

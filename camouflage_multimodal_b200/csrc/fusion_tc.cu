@@ -25,6 +25,7 @@
 namespace cm {
 
 static size_t al(size_t v) { return (v + 255) / 256 * 256; }
+long long* g_fusion_phase_dbg = nullptr;   // profiling aid (cm_debug_fusion_phase_stamps): 40 device int64 or NULL
 
 // shapes the single-kernel node side is written for (the reference's configs/multimodal_config.yaml defaults)
 static bool fusion_node_fused_ok(const cm_fusion_params* p) { return p->hidden == 256 && p->rg_dim == 128 && p->rg_proj_w != nullptr; }
@@ -211,6 +212,7 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
         a.sm_gs = f.gs; a.sm_valid = Kk;
         a.s2 = w.s2; a.v2 = w.v2; a.y = w.y; a.attn_mean = attn_rg2kg;
         a.x32 = rg;   // fp32 node embeddings are converted inside the kernel (rg_dim == 128 here)
+        a.dbg = g_fusion_phase_dbg;
         if ((rc = launch_fusion_node(a, w.rgb, W(f.w_rgproj), W(f.wcat), W(f.wv2), W(f.vot), W(f.ffn1), W(f.ffn2), st)) != CM_OK) return rc;
     } else {
     const op_t* r = w.rgb;
@@ -295,3 +297,8 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
 }
 
 }  // namespace cm
+
+// Profiling aid (tools/fusion_phase_profile.py): CTA 0 of fusion_node writes globaltimer stamps of every phase into buf
+// (40 int64 on the device) while set; NULL turns it off.  Not part of the product path.
+extern "C" void cm_debug_fusion_phase_stamps(long long* device_buf) { cm::g_fusion_phase_dbg = device_buf; }
+

@@ -96,27 +96,37 @@ __device__ __forceinline__ uint4 pack8(const float* x) {
 }
 
 // In-place softmax over each group of GS consecutive slots of a 32-column chunk; only the first `valid` slots of
-// a group are keys (the rest are layout padding and come out as 0).  am[k] accumulates slot k over the groups.
-template <int GS>
+// a group are keys (the rest are layout padding and come out as 0).  am[k] accumulates slot k over the groups when
+// WANT_MEAN (the head-averaged attention map was asked for).  The epilogue warps that run this are two per scheduler, so
+// it is written for latency, not instruction count alone: exp through ex2.approx on pre-scaled arguments (2 instructions;
+// relative error 2^-22, the probabilities leave as fp16 / 1e-4 maps), maximum and sum as four interleaved chains,
+// reciprocal by rcp.approx + one Newton step.
+template <int GS, bool WANT_MEAN = true>
 __device__ __forceinline__ void softmax_groups(float (&x)[32], int valid, float (&am)[32]) {
+    constexpr float LOG2E = 1.4426950408889634f;
 #pragma unroll
     for (int g = 0; g < 32 / GS; ++g) {
-        float mx = -INFINITY;
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int k = 0; k < GS; ++k)
-            if (k < valid) mx = fmaxf(mx, x[g * GS + k]);
-        float sum = 0.f;
+            if (k < valid) m4[k & 3] = fmaxf(m4[k & 3], x[g * GS + k]);
+        const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * LOG2E;
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int k = 0; k < GS; ++k) {
-            const float e = k < valid ? expf(x[g * GS + k] - mx) : 0.f;
+            float e = 0.f;
+            if (k < valid) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(x[g * GS + k], LOG2E, -mx)));
             x[g * GS + k] = e;
-            sum += e;
+            s4[k & 3] += e;
         }
-        const float inv = 1.0f / sum;
+        const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        float inv;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(sum));
+        inv = inv * (2.0f - sum * inv);
 #pragma unroll
         for (int k = 0; k < GS; ++k) {
             x[g * GS + k] *= inv;
-            am[k] += x[g * GS + k];
+            if (WANT_MEAN) am[k] += x[g * GS + k];
         }
     }
 }

@@ -262,6 +262,10 @@ int cm_fusion_forward(const cm_fusion_params* p, const void* folded, const float
                       float* edge_out, float* score_out, float* attn_rg2kg, float* attn_kg2rg,
                       void* stream);
 
+/* Profiling aid: while buf (40 int64 on the device) is set, CTA 0 of the fused node kernel records a %globaltimer stamp at
+ * every phase's MMA issue / epilogue start / epilogue end (tools/fusion_phase_profile.py).  NULL turns it off. */
+void cm_debug_fusion_phase_stamps(long long* device_buf);
+
 /* Fused QK^T -> softmax -> PV on the tcgen05 tensor cores for heads of 32 dims (the cross-attention of A10 when the
  * knowledge graph is large; cm_fusion_forward takes this path by itself for >= 128 shared KG rows when no attention
  * maps are requested).  q [mq, hidden], k [mk, hidden] row-major fp16; vt [hidden, ldv] = V transposed (ldv % 8 == 0,
