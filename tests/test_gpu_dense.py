@@ -61,3 +61,23 @@ def test_epilogues():
     _run(400, 256, 64, live=1, lda=64)
     _run(260, 128, 64, lda=72, bias=False)
     _run(640, 512, 256, relu=True, live=600)
+
+
+@pytest.mark.parametrize("m,n,k,scale,ta", [(1000, 256, 256, 1.0, 0), (300, 128, 300, 1.0, 0), (256, 256, 4000, 1.0, 1), (256, 128, 7000, 1e-5, 1),
+                                            (512, 256, 236, 1e-7, 1), (777, 192, 60, 1.0, 0), (37, 5, 19, 1.0, 0)])
+def test_training_gemm_building_block(m, n, k, scale, ta):
+    """cm_train_gemm_f32 (the dense block of the training passes) against float64: large shapes run on tcgen05 with 16-bit
+    thirds (fp16 parts for the forward pattern, bf16 parts + split-K for the weight-gradient pattern, whose operand may be
+    tiny), small ones on fp32 tiles; either way <= 5e-5 of the output scale."""
+    from camouflage_multimodal_b200 import _lib
+    lib = _lib.load()
+    gen = torch.Generator().manual_seed(m + k)
+    a = (torch.randn((m, k), generator=gen) * scale).cuda()
+    w = torch.randn((n, k), generator=gen).cuda()
+    b = (torch.randn(n, generator=gen) * scale).cuda()
+    c = torch.full((m, n), float("nan"), device="cuda")
+    aa = a.t().contiguous() if ta else a
+    _lib.check(lib.cm_train_gemm_f32(_lib.ptr(aa), _lib.ptr(w), _lib.ptr(b), m, n, k, ta, _lib.ptr(c), _lib.stream_ptr(a.device)), "cm_train_gemm_f32")
+    ref = a.double() @ w.double().t() + b.double()
+    assert torch.isfinite(c).all()
+    assert float((c.double() - ref).abs().max() / ref.abs().max()) <= 5e-5

@@ -74,3 +74,21 @@ def test_preprocess_order_and_rescale():
     stretched = ((lo.astype(np.int64) - 50) * 5).astype(np.uint8)
     a, b = oslic.preprocess(lo), oslic.preprocess(stretched)
     assert np.abs(a - b).max() < 1e-9
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/data/COD10K/images"), reason="the reference tree only exists in the build container")
+def test_oracle_counts_straight_from_the_reference_files():
+    """Build container only: a different sample than the committed table (every 251st image from an offset), decoded and
+    preprocessed from the reference's own files, against embedding_summary.json."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", "tools"))
+    from check_slic_counts import REF, reference_uint8
+    summ = json.load(open(f"{REF}/models/region_graph/rg_embeddings/embedding_summary.json"))["images"]
+    names = sorted(summ)[17::251]
+    bad = []
+    for n in names:
+        _, u8 = reference_uint8(f"{REF}/data/COD10K/images/{n}")
+        got = len(np.unique(oslic.slic(u8)))
+        if got != summ[n]["num_nodes"]:
+            bad.append((n, summ[n]["num_nodes"], got))
+    assert len(names) >= 20 and len(bad) <= len(names) // 10 and all(abs(e - g) <= 1 for _, e, g in bad), bad
