@@ -115,33 +115,11 @@ __device__ __forceinline__ void load_acc_bias(uint32_t taddr, int c0, const floa
     }
 }
 
-// the same from registers a pipelined TMEM load already delivered
-__device__ __forceinline__ void acc_bias(const uint32_t (&v)[32], int c0, const float* __restrict__ vec, float* x) {
-#pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-        const float4 b4 = __ldg(reinterpret_cast<const float4*>(vec + c0 + j));
-        x[j] = __uint_as_float(v[j]) + b4.x;
-        x[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
-        x[j + 2] = __uint_as_float(v[j + 2]) + b4.z;
-        x[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
-    }
-}
-// Four 32-column chunks of an accumulator (columns cbase, cbase + cstep, ...): the TMEM load of chunk i + 1 is in flight
-// while body(c0, registers of chunk i) runs.
-template <typename Body>
-__device__ __forceinline__ void for_chunks4(uint32_t taddr, int cbase, int cstep, Body&& body) {
-    uint32_t v[2][32];
-    tc_ld32_issue(taddr + cbase, v[0]);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        tc_ld_wait();
-        if (i + 1 < 4) tc_ld32_issue(taddr + cbase + (i + 1) * cstep, v[(i + 1) & 1]);
-        body(cbase + i * cstep, v[i & 1]);
-    }
-}
-
+// Measured and dropped: keeping the next chunk's TMEM load in flight while the current chunk is processed (tc_ld32_issue /
+// tc_ld_wait in tc_ptx.cuh) needs 32 more live registers; a 320-thread CTA is capped at 168 (three warps per 16 K-register
+// sub-partition), and the spills cost more than the hidden latency (43 -> 58 us).
 template <int MODE>
-__global__ void __maxnreg__(200) fusion_node_kernel(const __grid_constant__ FusionNodeArgs a) {
+__global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid_constant__ FusionNodeArgs a) {
     constexpr int NPH = MODE == 0 ? 8 : 5, XKB = MODE == 0 ? 2 : 4;
     extern __shared__ uint8_t smem_raw[];
     const int m_live = a.m_dev ? min(*a.m_dev, a.M) : a.M;
@@ -303,8 +281,8 @@ __global__ void __maxnreg__(200) fusion_node_kernel(const __grid_constant__ Fusi
         auto epi_ln = [&](int ph, uint32_t taddr, const float* bias, const float* res_rows) {
             wait_acc(ph);
             const float* res = res_rows ? res_rows + (size_t)(row % a.res_mod) * 256 : nullptr;
-            auto load = [&](int c0, const uint32_t (&v)[32]) {
-                acc_bias(v, c0, bias, x);
+            auto load = [&](int c0) {
+                load_acc_bias(taddr, c0, bias, x);
                 if (res) {
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) {
@@ -319,19 +297,14 @@ __global__ void __maxnreg__(200) fusion_node_kernel(const __grid_constant__ Fusi
                 }
             };
             float s1 = 0.f, s2 = 0.f;
-            for_chunks4(taddr, half * 32, 64, [&](int c0, const uint32_t (&v)[32]) {
-                load(c0, v);
-                float p1 = 0.f, p2 = 0.f, q1 = 0.f, q2 = 0.f;   // two interleaved chains per statistic
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load(c0);
 #pragma unroll
-                for (int j = 0; j < 32; j += 2) {
-                    p1 += x[j];
-                    q1 += x[j + 1];
-                    p2 = fmaf(x[j], x[j], p2);
-                    q2 = fmaf(x[j + 1], x[j + 1], q2);
+                for (int j = 0; j < 32; ++j) {
+                    s1 += x[j];
+                    s2 = fmaf(x[j], x[j], s2);
                 }
-                s1 += p1 + q1;
-                s2 += p2 + q2;
-            });
+            }
             float2* stat = reinterpret_cast<float2*>(smem + FN_X);
             stat[half * 128 + lrow] = make_float2(s1, s2);
             asm volatile("bar.sync 1, %0;" ::"n"(FN_EPI_THREADS) : "memory");
@@ -340,8 +313,8 @@ __global__ void __maxnreg__(200) fusion_node_kernel(const __grid_constant__ Fusi
             s2 += o.y;
             const float mean = s1 * (1.0f / 256.f);
             const float rstd = rsqrtf(fmaxf(s2 * (1.0f / 256.f) - mean * mean, 0.f) + 1e-5f);
-            for_chunks4(taddr, half * 32, 64, [&](int c0, const uint32_t (&v)[32]) {
-                load(c0, v);
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load(c0);
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) {
                     const float4 g4 = __ldg(reinterpret_cast<const float4*>(a.ln_g + c0 + j));
@@ -352,32 +325,32 @@ __global__ void __maxnreg__(200) fusion_node_kernel(const __grid_constant__ Fusi
                     x[j + 3] = (x[j + 3] - mean) * rstd * g4.w + b4.w;
                 }
                 store_chunk_smem(sbase + FN_A1, lrow, c0, x);
-            });
+            }
             done(ph);   // the scratch is not rewritten before every warp has arrived here (next A3 writer waits on it)
         };
         // hh half = relu(acc + b1) -> A3
         auto epi_relu = [&](int ph, const float* b1) {
             wait_acc(ph);
-            for_chunks4(t0, half * 32, 64, [&](int c0, const uint32_t (&v)[32]) {
-                acc_bias(v, c0, b1, x);
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load_acc_bias(t0, c0, b1, x);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
                 store_chunk_smem(sbase + FN_A3, lrow, c0, x);
-            });
+            }
             done(ph);
         };
         // y = Y + b2 + A1 -> global fp32
         auto epi_final = [&](int ph) {
             wait_acc(ph);
-            for_chunks4(t1, half * 32, 64, [&](int c0, const uint32_t (&v)[32]) {
-                acc_bias(v, c0, a.b_ffn2, x);
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load_acc_bias(t1, c0, a.b_ffn2, x);
                 add_chunk_smem(sbase + FN_A1, lrow, c0, x);
                 if (row_ok) {
                     float* o = a.y + (size_t)row * 256 + c0;
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) st_global_f32x8(o + j, x + j);
                 }
-            });
+            }
         };
 
         if (MODE == 1) {
@@ -388,10 +361,10 @@ __global__ void __maxnreg__(200) fusion_node_kernel(const __grid_constant__ Fusi
         } else {
         // ---- epi0: r -> A1
         wait_acc(0);
-        for_chunks4(t0, half * 32, 64, [&](int c0, const uint32_t (&v)[32]) {
-            acc_bias(v, c0, a.b_rgproj, x);
+        for (int c0 = half * 32; c0 < 256; c0 += 64) {
+            load_acc_bias(t0, c0, a.b_rgproj, x);
             store_chunk_smem(sbase + FN_A1, lrow, c0, x);
-        });
+        }
         done(0);
 
         // ---- epi1: half 0 -> P1 = per-head softmax of the rg->kg scores (A2); half 1 -> raw kg->rg scores (global)
@@ -400,21 +373,24 @@ __global__ void __maxnreg__(200) fusion_node_kernel(const __grid_constant__ Fusi
             float am[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) am[j] = 0.f;
-            for_chunks4(t1, half * 128, 32, [&](int c0, const uint32_t (&v)[32]) {
-                acc_bias(v, c0, a.ccat, x);
+            for (int c0 = half * 128; c0 < half * 128 + 128; c0 += 32) {
+                load_acc_bias(t1, c0, a.ccat, x);
+                if (stamp && threadIdx.x == 64 && c0 == 0) a.dbg[35] = now();
                 if (half == 0) {
                     if (a.attn_mean) {
                         if (a.sm_gs == 16) softmax_groups<16, true>(x, a.sm_valid, am); else softmax_groups<32, true>(x, a.sm_valid, am);
                     } else {
                         if (a.sm_gs == 16) softmax_groups<16, false>(x, a.sm_valid, am); else softmax_groups<32, false>(x, a.sm_valid, am);
                     }
+                    if (stamp && threadIdx.x == 64 && c0 == 0) a.dbg[36] = now();
                     store_chunk_smem(sbase + FN_P1, lrow, c0, x);
+                    if (stamp && threadIdx.x == 64 && c0 == 0) a.dbg[37] = now();
                 } else if (row_ok) {
                     float* o = a.s2 + (size_t)row * 128 + (c0 - 128);
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) st_global_f32x8(o + j, x + j);
                 }
-            });
+            }
             if (stamp && threadIdx.x == 64) a.dbg[33] = now();
             if (stamp && threadIdx.x == 192) a.dbg[34] = now();
             if (half == 0 && a.attn_mean && row_ok) {
@@ -428,14 +404,14 @@ __global__ void __maxnreg__(200) fusion_node_kernel(const __grid_constant__ Fusi
 
         // ---- epi2: V2 -> global fp16
         wait_acc(2);
-        for_chunks4(t0, half * 32, 64, [&](int c0, const uint32_t (&v)[32]) {
-            acc_bias(v, c0, a.b_v2, x);
+        for (int c0 = half * 32; c0 < 256; c0 += 64) {
+            load_acc_bias(t0, c0, a.b_v2, x);
             if (row_ok) {
                 op_t* o = a.v2 + (size_t)row * 256 + c0;
 #pragma unroll
                 for (int j = 0; j < 32; j += 16) st_global_b32x8(o + j, pack8(x + j), pack8(x + j + 8));
             }
-        });
+        }
         done(2);
 
         epi_ln(3, t1, a.b_out1, nullptr);     // y0 = LN(r + P1 VO^T + bo1)
