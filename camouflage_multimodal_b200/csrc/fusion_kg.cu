@@ -371,6 +371,7 @@ __global__ void __cluster_dims__(KT_CL, 1, 1) __launch_bounds__(KT_THREADS) kg_t
         }
     }
     __syncthreads();
+    cluster.sync();   // every CTA of the cluster is running before the first write into a peer's shared memory
     // ---- this CTA's 64 columns of ctx2 [16, 256] (rows >= K zero) as fp16 hi / lo, broadcast; its columns of mean_n y
     const int hd = D / heads;
     for (int i = tid; i < 16 * (QD / 2); i += nt) {
