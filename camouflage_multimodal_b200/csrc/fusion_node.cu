@@ -101,18 +101,26 @@ __device__ __forceinline__ void add_chunk_smem(uint32_t base, int row, int c0, f
         }
     }
 }
-// x[j] = acc[j] + vec[c0 + j] (vec: fp32 per-column vector in global memory, warp-uniform address -> broadcast)
-__device__ __forceinline__ void load_acc_bias(uint32_t taddr, int c0, const float* __restrict__ vec, float* x) {
+// Per-column vectors (biases, LayerNorm gamma / beta) without a memory access on the epilogue's critical path: a thread's
+// four 32-column chunks take the same columns in every lane of the warp (one row per lane), so lane l fetches element
+// c0 + l of each chunk BEFORE the wait for the accumulator (the loads fly during the MMA) and the chunk code broadcasts
+// element j from lane j by shuffle.  (The 10 KB of vectors have no room in shared memory next to the activations and
+// the weight ring; with __ldg in the chunk loop every epilogue spent ~1.5 us of its ~2.2 us waiting for L1 / L2.)
+struct VecSlice {
+    float r[4];
+};
+__device__ __forceinline__ VecSlice vec_slice(const float* __restrict__ vec, int cbase, int cstep, int lane) {
+    VecSlice s;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s.r[i] = __ldg(vec + cbase + i * cstep + lane);
+    return s;
+}
+// x[j] = acc[j] + vec[c0 + j], the vector element coming from lane j's slice register
+__device__ __forceinline__ void load_acc_bias_s(uint32_t taddr, int c0, float breg, float* x) {
     uint32_t v[32];
     tc_ld32(taddr + c0, v);
 #pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-        const float4 b4 = __ldg(reinterpret_cast<const float4*>(vec + c0 + j));
-        x[j] = __uint_as_float(v[j]) + b4.x;
-        x[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
-        x[j + 2] = __uint_as_float(v[j + 2]) + b4.z;
-        x[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
-    }
+    for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) + __shfl_sync(0xffffffffu, breg, j);
 }
 
 // Measured and dropped: keeping the next chunk's TMEM load in flight while the current chunk is processed (tc_ld32_issue /
@@ -279,10 +287,12 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         // its own (row, chunk) cells, and every MMA that read A1 has completed because acc_ready[ph] covers them) or
         // fp32 rows from global memory (row % res_mod).  The statistics scratch is the x tile, dead since phase 0.
         auto epi_ln = [&](int ph, uint32_t taddr, const float* bias, const float* res_rows) {
+            const VecSlice bs = vec_slice(bias, half * 32, 64, lane), gs = vec_slice(a.ln_g, half * 32, 64, lane),
+                           es = vec_slice(a.ln_b, half * 32, 64, lane);
             wait_acc(ph);
             const float* res = res_rows ? res_rows + (size_t)(row % a.res_mod) * 256 : nullptr;
             auto load = [&](int c0) {
-                load_acc_bias(taddr, c0, bias, x);
+                load_acc_bias_s(taddr, c0, bs.r[c0 >> 6], x);
                 if (res) {
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) {
@@ -315,24 +325,20 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             const float rstd = rsqrtf(fmaxf(s2 * (1.0f / 256.f) - mean * mean, 0.f) + 1e-5f);
             for (int c0 = half * 32; c0 < 256; c0 += 64) {
                 load(c0);
+                const float gr = gs.r[c0 >> 6], er = es.r[c0 >> 6];
 #pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    const float4 g4 = __ldg(reinterpret_cast<const float4*>(a.ln_g + c0 + j));
-                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(a.ln_b + c0 + j));
-                    x[j] = (x[j] - mean) * rstd * g4.x + b4.x;
-                    x[j + 1] = (x[j + 1] - mean) * rstd * g4.y + b4.y;
-                    x[j + 2] = (x[j + 2] - mean) * rstd * g4.z + b4.z;
-                    x[j + 3] = (x[j + 3] - mean) * rstd * g4.w + b4.w;
-                }
+                for (int j = 0; j < 32; ++j)
+                    x[j] = (x[j] - mean) * rstd * __shfl_sync(0xffffffffu, gr, j) + __shfl_sync(0xffffffffu, er, j);
                 store_chunk_smem(sbase + FN_A1, lrow, c0, x);
             }
             done(ph);   // the scratch is not rewritten before every warp has arrived here (next A3 writer waits on it)
         };
         // hh half = relu(acc + b1) -> A3
         auto epi_relu = [&](int ph, const float* b1) {
+            const VecSlice bs = vec_slice(b1, half * 32, 64, lane);
             wait_acc(ph);
             for (int c0 = half * 32; c0 < 256; c0 += 64) {
-                load_acc_bias(t0, c0, b1, x);
+                load_acc_bias_s(t0, c0, bs.r[c0 >> 6], x);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
                 store_chunk_smem(sbase + FN_A3, lrow, c0, x);
@@ -341,9 +347,10 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         };
         // y = Y + b2 + A1 -> global fp32
         auto epi_final = [&](int ph) {
+            const VecSlice bs = vec_slice(a.b_ffn2, half * 32, 64, lane);
             wait_acc(ph);
             for (int c0 = half * 32; c0 < 256; c0 += 64) {
-                load_acc_bias(t1, c0, a.b_ffn2, x);
+                load_acc_bias_s(t1, c0, bs.r[c0 >> 6], x);
                 add_chunk_smem(sbase + FN_A1, lrow, c0, x);
                 if (row_ok) {
                     float* o = a.y + (size_t)row * 256 + c0;
@@ -360,21 +367,23 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             epi_final(4);
         } else {
         // ---- epi0: r -> A1
+        const VecSlice b0s = vec_slice(a.b_rgproj, half * 32, 64, lane);
         wait_acc(0);
         for (int c0 = half * 32; c0 < 256; c0 += 64) {
-            load_acc_bias(t0, c0, a.b_rgproj, x);
+            load_acc_bias_s(t0, c0, b0s.r[c0 >> 6], x);
             store_chunk_smem(sbase + FN_A1, lrow, c0, x);
         }
         done(0);
 
         // ---- epi1: half 0 -> P1 = per-head softmax of the rg->kg scores (A2); half 1 -> raw kg->rg scores (global)
+        const VecSlice c1s = vec_slice(a.ccat, half * 128, 32, lane);
         wait_acc(1);
         {
             float am[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) am[j] = 0.f;
             for (int c0 = half * 128; c0 < half * 128 + 128; c0 += 32) {
-                load_acc_bias(t1, c0, a.ccat, x);
+                load_acc_bias_s(t1, c0, c1s.r[(c0 >> 5) & 3], x);
                 if (stamp && threadIdx.x == 64 && c0 == 0) a.dbg[35] = now();
                 if (half == 0) {
                     if (a.attn_mean) {
@@ -403,9 +412,10 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         done(1);
 
         // ---- epi2: V2 -> global fp16
+        const VecSlice b2s = vec_slice(a.b_v2, half * 32, 64, lane);
         wait_acc(2);
         for (int c0 = half * 32; c0 < 256; c0 += 64) {
-            load_acc_bias(t0, c0, a.b_v2, x);
+            load_acc_bias_s(t0, c0, b2s.r[c0 >> 6], x);
             if (row_ok) {
                 op_t* o = a.v2 + (size_t)row * 256 + c0;
 #pragma unroll
