@@ -150,8 +150,8 @@ def kernel_work(name, B, M, E, K):
         "labels_widen": ("hbm", px * (2.0 + 4.0)),
         "edge_weights": ("hbm", 60.0 * M + 8.0 * E),
         "paint_metrics": ("hbm", px * (LABEL_BYTES + 1.0) + 4.0 * M),
-        # S/E/F reductions on the painted mask: labels + gt read once (cluster-fused kernel keeps the pixels in registers)
-        "sod_fused": ("hbm", px * (LABEL_BYTES + 1.0) + 4.0 * M),
+        # labels x gt contingency table (the metrics' only pixel pass): labels once, the ground truth twice (centroid, then table)
+        "region_gt_table": ("hbm", px * (LABEL_BYTES + 2.0) + 32.0 * B * (LABEL_CAP + 1)),
         # one launch for everything after the node kernel: chunk partials in, weights of the KG-row chain + fusion MLP + heads
         # (1.9 MB, L2-resident after the first cluster) -- latency-bound by design at 13 rows per image
         "unpack_bits": ("hbm", px * (2.0 / 8.0 + 2.0)),

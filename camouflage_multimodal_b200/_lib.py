@@ -143,6 +143,9 @@ SIGNATURES = {
     "cm_sod_workspace_bytes": (_sz, [_i, _i, _i]),
     "cm_sod_metrics": (_i, [_fp, _fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp]),
     "cm_sod_metrics_painted": (_i, [_fp, _i, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _i, _fp, _sz, _fp, _fp, _fp]),
+    "cm_region_table_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "cm_region_table_build": (_i, [_fp, _i, _fp, _i, _i, _i, _i, _i, _fp, _sz, _fp]),
+    "cm_region_table_metrics": (_i, [_fp, _i, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _f, _fp, _sz, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "cm_class_confusion": (_i, [_fp, _fp, _i, _i, _fp, _fp]),
     "cm_slic_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "cm_slic": (_i, [_fp, _i, _i, _i, _i, C.c_double, C.c_double, _i, _fp, _sz, _fp, _fp]),

@@ -24,7 +24,10 @@
 // read three times (the second and third from L2 at batch 32: 10 MB).
 #include <math.h>
 
+#include <algorithm>
+
 #include "common.cuh"
+#include "metrics_body.cuh"
 
 namespace cm {
 
@@ -446,12 +449,14 @@ __device__ __forceinline__ double sod_s_object(double sum, double sum2, double n
     return 2.0 * x / (x * x + 1.0 + sigma + SOD_EPS);
 }
 
-// one block of 256 threads per image: thread t owns curve entry t (threshold q >= 255 - t)
-__global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restrict__ tot1, const double* __restrict__ tot2, const double* __restrict__ shift,
-                                                           const double* __restrict__ p4, int wf_tiles, const int* __restrict__ hist, int H, int W,
-                                                           double beta2_f, double beta2_wf, double* __restrict__ per_image,
-                                                           double* __restrict__ curves, int* __restrict__ done_counter, int batch,
-                                                           double* __restrict__ partial) {
+// one block of 256 threads per image: thread t owns curve entry t (threshold q >= 255 - t).  Returns true in the block that
+// finished last (it has written the batch partial).  tot1 / tot2 / shift / hist may have been written by this very block
+// (the fused region-table kernel): plain loads after a __syncthreads().
+__device__ __forceinline__ bool sod_finalize_body(const double* tot1, const double* tot2, const double* shift,
+                                                  const double* __restrict__ p4, int wf_tiles, const int* hist, int H, int W,
+                                                  double beta2_f, double beta2_wf, double* __restrict__ per_image,
+                                                  double* __restrict__ curves, int* __restrict__ done_counter, int batch,
+                                                  double* __restrict__ partial) {
     __shared__ int s_tp[256], s_fp[256], s_wtp[8], s_wfp[8], s_last;
     __shared__ double s_f[256], s_e[256], s_fm[256], s_em[256];
     __shared__ double s_tot[SOD_P1], s_q[SOD_P2], s_wf[2];
@@ -602,7 +607,7 @@ __global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restr
     __syncthreads();
     if (t == 0) s_last = atomicAdd(done_counter, 1) == batch - 1;
     __syncthreads();
-    if (!s_last) return;
+    if (!s_last) return false;
     __threadfence();
     for (int i = t; i < SOD_PARTIAL; i += 256) {
         double sum = 0.0;
@@ -616,6 +621,357 @@ __global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restr
             for (int bb = 0; bb < batch; ++bb) sum += __ldcg(curves + (size_t)bb * 512 + (i - 2 * SOD_KEYS));
         }
         partial[i] = sum;
+    }
+    return true;
+}
+__global__ void __launch_bounds__(256) sod_finalize_kernel(const double* __restrict__ tot1, const double* __restrict__ tot2, const double* __restrict__ shift,
+                                                           const double* __restrict__ p4, int wf_tiles, const int* __restrict__ hist, int H, int W,
+                                                           double beta2_f, double beta2_wf, double* __restrict__ per_image,
+                                                           double* __restrict__ curves, int* __restrict__ done_counter, int batch,
+                                                           double* __restrict__ partial) {
+    sod_finalize_body(tot1, tot2, shift, p4, wf_tiles, hist, H, W, beta2_f, beta2_wf, per_image, curves, done_counter, batch, partial);
+}
+
+
+// ---------------------------------------------------------------------------------------------- region x ground-truth table
+// A painted prediction is constant over a region, so every pixel sum of A9 / A9' factors through the contingency table
+//   c[label][fg][quadrant] = pixels of that label, ground-truth class and S-measure quadrant
+// (quadrants are cut at the GROUND TRUTH's centroid, so the table needs nothing from the model): confusion counts,
+// |pred - gt|, the object / quadrant moments of S, both 256-bin histograms and the adaptive-threshold counts are sums over
+// <= label_cap + 1 table rows of count x f(probability).  The table is built from labels + gt only, i.e. NEXT TO the graph
+// build instead of after the model (rt_table_kernel), and what remains behind the GNN is one block per image
+// (rt_metrics_kernel: table rows x probabilities, the closed forms, the batch sums) -- the three pixel passes
+// (paint_metrics, sod_pass1, sod_pass2: 7 B/pixel each) and two finalize launches leave the step.
+// Exactness: counts are integers; the float64 sums differ from the pixel-order sums by rounding only (tests: <= 1e-12
+// relative).  |pred - gt| needs gt in {0, 255}: the table kernel counts the other bytes per image, and for an image that has
+// any (a resized mask with soft borders) its block of rt_metrics_kernel walks that image's pixels for the A9 counts / MAE
+// exactly as paint_metrics does.  Labels outside [0, label_cap) share the last row (probability 0, like SodPix::at /
+// paint_metrics).
+constexpr int RT_MAX_SPLITS = 16, RT_SPLIT_PIXELS = 1 << 18, RT_THREADS = 1024;
+
+struct RtWs {
+    long long* gtstat;   // [B,4] n_fg, sum y, sum x, bytes outside {0, 255}
+    int* part;           // [B, splits, (cap + 1) * 8]
+    double *curves, *shift, *tot1, *tot2;
+    int* hist;           // [B,512] + [1] finalize counter
+    int splits;
+    size_t total;
+};
+static int rt_splits(int h, int w) {
+    const long long hw = (long long)h * w;
+    return (int)std::min<long long>(RT_MAX_SPLITS, (hw + RT_SPLIT_PIXELS - 1) / RT_SPLIT_PIXELS);
+}
+static RtWs carve_rt(void* ws, int batch, int h, int w, int cap) {
+    Carver c(ws);
+    RtWs r;
+    r.splits = rt_splits(h, w);
+    r.gtstat = c.take<long long>((size_t)batch * 4);
+    r.part = c.take<int>((size_t)batch * r.splits * (cap + 1) * 8);
+    r.curves = c.take<double>((size_t)batch * 512);
+    r.shift = c.take<double>((size_t)batch * 4);
+    r.tot1 = c.take<double>((size_t)batch * SOD_P1);
+    r.tot2 = c.take<double>((size_t)batch * SOD_P2);
+    r.hist = c.take<int>((size_t)batch * 512 + 1);
+    r.total = align_up(c.off, 256);
+    return r;
+}
+
+// foreground bits of eight consecutive pixels starting at pixel 8 * q (gt: one byte or one bit per pixel), and how many
+// of the eight bytes are neither 0 nor 255
+template <bool PACKED>
+__device__ __forceinline__ unsigned rt_fg8(const uint8_t* __restrict__ g, int q, int* gray) {
+    if (PACKED) return g[q];
+    const uint2 w = reinterpret_cast<const uint2*>(g)[q];
+    const unsigned hx = (w.x >> 7) & 0x01010101u, hy = (w.y >> 7) & 0x01010101u;
+    *gray += (__popc(__vcmpne4(w.x, hx * 255u)) + __popc(__vcmpne4(w.y, hy * 255u))) >> 3;
+    return ((hx * 0x01020408u) >> 24) | (((hy * 0x01020408u) >> 24) << 4);
+}
+template <bool PACKED>
+__device__ __forceinline__ unsigned rt_fg1(const uint8_t* __restrict__ g, int i, int* gray) {
+    if (PACKED) return (g[i >> 3] >> (i & 7)) & 1u;
+    const unsigned v = g[i];
+    *gray += v != 0u && v != 255u;
+    return v >> 7;
+}
+__device__ __forceinline__ void rt_load8(const int* __restrict__ lab, int q, int* l) {
+    const int4 a = reinterpret_cast<const int4*>(lab)[2 * q], c = reinterpret_cast<const int4*>(lab)[2 * q + 1];
+    l[0] = a.x; l[1] = a.y; l[2] = a.z; l[3] = a.w; l[4] = c.x; l[5] = c.y; l[6] = c.z; l[7] = c.w;
+}
+__device__ __forceinline__ void rt_load8(const short* __restrict__ lab, int q, int* l) {
+    const uint4 a = reinterpret_cast<const uint4*>(lab)[q];
+    const unsigned w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        l[2 * j] = (int)(short)(w[j] & 0xffffu);
+        l[2 * j + 1] = (int)(short)(w[j] >> 16);
+    }
+}
+
+// grid (splits, B), block 1024, dynamic shared memory (cap + 1) * 8 ints.  Phase 1: the image's ground-truth count /
+// centroid sums / non-binary bytes (every split block computes them for the whole image -- the ground truth is 1 B or
+// 1 bit per pixel -- so no block waits for another).  Phase 2: this block's slice of the pixels -> its own table (plain
+// stores: no zeroing, no global atomics).  A thread takes 16 consecutive pixels (one 32-byte sector of int16 labels);
+// runs of equal (label, class, quadrant) inside them cost one shared-memory atomic, and neighbouring lanes are 16 pixels
+// apart -- wider than most superpixels, so same-address conflicts inside a warp stay rare.
+template <typename LT, bool PACKED>
+__global__ void __launch_bounds__(RT_THREADS) rt_table_kernel(const LT* __restrict__ labels, const uint8_t* __restrict__ gt, int H, int W, int cap,
+                                                              long long* __restrict__ gtstat, int* __restrict__ part, int* __restrict__ done_counter) {
+    extern __shared__ int s_tab[];
+    __shared__ long long s_red[32][4];
+    __shared__ long long s_stat[4];
+    const int b = blockIdx.y, HW = H * W, nt = (cap + 1) * 8, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const LT* lab = labels + (size_t)b * HW;
+    const uint8_t* g = gt + (PACKED ? (size_t)b * (HW >> 3) : (size_t)b * HW);
+    for (int i = threadIdx.x; i < nt; i += RT_THREADS) s_tab[i] = 0;
+    // ---- phase 1
+    long long n = 0, sy = 0, sx = 0;
+    int gray = 0;
+    const bool vec8 = (W & 7) == 0 && (PACKED || (reinterpret_cast<uintptr_t>(g) & 7) == 0);
+    if (vec8) {
+#pragma unroll 4
+        for (int q = threadIdx.x; q < (HW >> 3); q += RT_THREADS) {
+            const unsigned m = rt_fg8<PACKED>(g, q, &gray);
+            const int i = q << 3, y = i / W, x0 = i - y * W, c = __popc(m);
+            n += c;
+            sy += (long long)y * c;
+            sx += (long long)x0 * c + __popc(m & 0xaau) + 2 * __popc(m & 0xccu) + 4 * __popc(m & 0xf0u);
+        }
+    } else {
+        for (int i = threadIdx.x; i < HW; i += RT_THREADS) {
+            const unsigned f = rt_fg1<PACKED>(g, i, &gray);
+            const int y = i / W;
+            n += f;
+            sy += f ? y : 0;
+            sx += f ? i - y * W : 0;
+        }
+    }
+    {
+        long long v[4] = {n, sy, sx, (long long)gray};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+            if (lane == 0) s_red[wid][k] = v[k];
+        }
+        __syncthreads();
+        if (threadIdx.x < 4) {
+            long long t = 0;
+            for (int wi = 0; wi < RT_THREADS / 32; ++wi) t += s_red[wi][threadIdx.x];
+            s_stat[threadIdx.x] = t;
+            if (blockIdx.x == 0) {
+                gtstat[(size_t)b * 4 + threadIdx.x] = t;
+                if (threadIdx.x == 1 && b == 0) *done_counter = 0;
+            }
+        }
+        __syncthreads();
+    }
+    int cx, cy;
+    {
+        const double t[3] = {(double)s_stat[0], (double)s_stat[1], (double)s_stat[2]};
+        sod_centroid(t, H, W, &cx, &cy);
+    }
+    // ---- phase 2
+    int dummy = 0;
+    if ((W & 15) == 0 && ((reinterpret_cast<uintptr_t>(lab) | (PACKED ? (uintptr_t)0 : reinterpret_cast<uintptr_t>(g))) & 31) == 0) {
+        const int nq = HW >> 4, per = (nq + gridDim.x - 1) / gridDim.x, q0 = blockIdx.x * per, q1 = min(q0 + per, nq);
+        for (int q = q0 + threadIdx.x; q < q1; q += RT_THREADS) {
+            int l[16];
+            rt_load8(lab, 2 * q, l);
+            rt_load8(lab, 2 * q + 1, l + 8);
+            const unsigned m = rt_fg8<PACKED>(g, 2 * q, &dummy) | (rt_fg8<PACKED>(g, 2 * q + 1, &dummy) << 8);
+            const int i = q << 4, y = i / W, x0 = i - y * W, ky = y >= cy ? 2 : 0;
+            int prev = -1, cnt = 0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const int lb = (l[j] >= 0 && l[j] < cap) ? l[j] : cap;
+                const int key = (lb << 3) | (int)(((m >> j) & 1u) << 2) | ky | (x0 + j >= cx ? 1 : 0);
+                if (key != prev) {
+                    if (cnt) atomicAdd(&s_tab[prev], cnt);
+                    prev = key;
+                    cnt = 0;
+                }
+                ++cnt;
+            }
+            atomicAdd(&s_tab[prev], cnt);
+        }
+    } else {
+        const int per = (HW + gridDim.x - 1) / gridDim.x, i0 = blockIdx.x * per, i1 = min(i0 + per, HW);
+        for (int i = i0 + threadIdx.x; i < i1; i += RT_THREADS) {
+            const int l = (int)lab[i], y = i / W, x = i - y * W;
+            const int lb = (l >= 0 && l < cap) ? l : cap;
+            atomicAdd(&s_tab[(lb << 3) | (int)(rt_fg1<PACKED>(g, i, &dummy) << 2) | (y >= cy ? 2 : 0) | (x >= cx ? 1 : 0)], 1);
+        }
+    }
+    __syncthreads();
+    int* o = part + ((size_t)b * gridDim.x + blockIdx.x) * nt;
+    for (int i = threadIdx.x; i < nt; i += RT_THREADS) o[i] = s_tab[i];
+}
+
+// one block of 256 threads per image, after the model: table rows x node probabilities -> everything sod_pass1 /
+// sod_pass2 / paint_metrics would have summed over the pixels, then the closed forms of sod_finalize and (last block)
+// the batch sums of both metric families.  Dynamic shared memory: (cap + 1) * 8 ints + (cap + 1) floats.
+__global__ void __launch_bounds__(256) rt_metrics_kernel(const int* __restrict__ part, int splits, int cap, const long long* __restrict__ gtstat,
+                                                         const void* __restrict__ labels, int label_bytes, const float* __restrict__ mask_prob,
+                                                         const int* __restrict__ node_ptr, const int* __restrict__ id_of_label, float threshold,
+                                                         int H, int W, const uint8_t* __restrict__ gt_bytes,
+                                                         unsigned long long* __restrict__ counts, double* __restrict__ abs_err,
+                                                         double* tot1, double* tot2, double* shift, int* hist, double* __restrict__ curves,
+                                                         int* __restrict__ done_counter, int batch, double* __restrict__ per_image,
+                                                         double* __restrict__ partial, double* __restrict__ per_image_sod,
+                                                         double* __restrict__ partial_sod) {
+    extern __shared__ int s_dyn[];
+    __shared__ int s_hist[512];
+    __shared__ double s_red[8 * SOD_P2];
+    __shared__ double s_shift[4], s_thr;
+    const int b = blockIdx.x, t = threadIdx.x, HW = H * W, rows = cap + 1, nt = rows * 8;
+    int* s_tab = s_dyn;
+    float* s_p = reinterpret_cast<float*>(s_dyn + nt);
+    const int n0 = node_ptr[b], nb = node_ptr[b + 1] - n0;
+    const float* prob = mask_prob + n0;
+    const int* idm = id_of_label ? id_of_label + (size_t)b * cap : nullptr;
+    auto prob_of = [&](int l) {
+        int idx = (l >= 0 && l < cap) ? l : -1;
+        if (idm && idx >= 0) idx = idm[idx];
+        return (idx >= 0 && idx < nb) ? prob[idx] : 0.f;
+    };
+    for (int i = t; i < 512; i += 256) s_hist[i] = 0;
+    int cx, cy;
+    const long long gray = gtstat[(size_t)b * 4 + 3];
+    const double gt3[3] = {(double)gtstat[(size_t)b * 4], (double)gtstat[(size_t)b * 4 + 1], (double)gtstat[(size_t)b * 4 + 2]};
+    sod_centroid(gt3, H, W, &cx, &cy);
+    if (t < 4) {   // the corner pixel of quadrant k (sod_pass2)
+        const int y0 = (t & 2) ? cy : 0, x0 = (t & 1) ? cx : 0;
+        double sh = 0.0;
+        if (y0 < H && x0 < W) {
+            const size_t p = (size_t)b * HW + (size_t)y0 * W + x0;
+            sh = (double)prob_of(label_bytes == 2 ? (int)reinterpret_cast<const short*>(labels)[p] : reinterpret_cast<const int*>(labels)[p]);
+        }
+        s_shift[t] = sh;
+        shift[(size_t)b * 4 + t] = sh;
+    }
+    // the slices' tables added up, each row's probability next to it
+    const int* pb = part + (size_t)b * splits * nt;
+    for (int i = t; i < nt / 4; i += 256) {
+        int4 a = reinterpret_cast<const int4*>(pb)[i];
+        for (int s = 1; s < splits; ++s) {
+            const int4 c = reinterpret_cast<const int4*>(pb + (size_t)s * nt)[i];
+            a.x += c.x; a.y += c.y; a.z += c.z; a.w += c.w;
+        }
+        reinterpret_cast<int4*>(s_tab)[i] = a;
+    }
+    for (int l = t; l < rows; l += 256) s_p[l] = prob_of(l);
+    __syncthreads();
+    // ---- pass-1 sums, the two histograms, the A9 counts
+    const double thr = (double)threshold;
+    double v[SOD_P2];
+#pragma unroll
+    for (int k = 0; k < SOD_P2; ++k) v[k] = 0.0;
+    long long tp = 0, sp = 0, eq = 0;
+    double ae = 0.0;
+    for (int l = t; l < rows; l += 256) {
+        const int* c = s_tab + l * 8;
+        const int cb = c[0] + c[1] + c[2] + c[3], cf = c[4] + c[5] + c[6] + c[7];
+        if ((cb | cf) == 0) continue;
+        const double p = (double)s_p[l], o = 1.0 - p;
+        v[3] += p * cf;
+        v[4] += p * p * cf;
+        v[5] += o * cb;
+        v[6] += o * o * cb;
+        v[7] += p * (cb + cf);
+        int q = (int)(p * 255.0);
+        q = min(max(q, 0), 255);
+        if (cf) atomicAdd(&s_hist[q], cf);
+        if (cb) atomicAdd(&s_hist[256 + q], cb);
+        const bool pos = p > thr;
+        tp += pos ? cf : 0;
+        sp += pos ? cb + cf : 0;
+        eq += pos ? cf : cb;
+        ae += o * cf + p * cb;   // |p - 1| on the foreground, |p - 0| on the background
+    }
+    double sg = gt3[0];
+    if (gray != 0 && gt_bytes) {
+        // non-binary ground truth: |p - g / 255| does not factor through the table -- this image's pixels once more, the
+        // way paint_metrics accounts them (utils/metrics.py:11-12, 47, 52: both masks thresholded at `threshold`)
+        tp = sp = eq = 0;
+        ae = 0.0;
+        long long sgi = 0;
+        const uint8_t* g = gt_bytes + (size_t)b * HW;
+        for (int i = t; i < HW; i += 256) {
+            const size_t p = (size_t)b * HW + i;
+            const double pr = (double)prob_of(label_bytes == 2 ? (int)reinterpret_cast<const short*>(labels)[p] : reinterpret_cast<const int*>(labels)[p]);
+            const double gv = (double)g[i] / 255.0;
+            const bool pb = pr > thr, gb = gv > thr;
+            tp += pb && gb;
+            sp += pb;
+            sgi += gb;
+            eq += pb == gb;
+            ae += fabs(pr - gv);
+        }
+        v[9] = (double)sgi;
+    }
+    v[0] = (double)tp;
+    v[1] = (double)sp;
+    v[2] = (double)eq;
+    v[8] = ae;
+    block_sum<SOD_P2>(v, s_red);
+    if (gray != 0 && gt_bytes) sg = v[9];
+    if (t == 0) {
+        double* o1 = tot1 + (size_t)b * SOD_P1;
+        o1[0] = gt3[0];
+        o1[1] = gt3[1];
+        o1[2] = gt3[2];
+#pragma unroll
+        for (int k = 3; k < SOD_P1; ++k) o1[k] = v[k];
+        s_thr = fmin(2.0 * (v[7] / (double)HW), 1.0);
+        counts[4 * (size_t)b] = (unsigned long long)v[0];
+        counts[4 * (size_t)b + 1] = (unsigned long long)v[1];
+        counts[4 * (size_t)b + 2] = (unsigned long long)sg;
+        counts[4 * (size_t)b + 3] = (unsigned long long)v[2];
+        abs_err[b] = v[8];
+    }
+    __syncthreads();
+    for (int i = t; i < 512; i += 256) hist[(size_t)b * 512 + i] = s_hist[i];
+    // ---- pass-2 sums: quadrant moments about the corner pixel's value, adaptive-threshold counts
+    const double athr = s_thr;
+#pragma unroll
+    for (int k = 0; k < SOD_P2; ++k) v[k] = 0.0;
+    long long gq[4] = {0, 0, 0, 0}, tpa = 0, fpa = 0;
+    for (int l = t; l < rows; l += 256) {
+        const int* c = s_tab + l * 8;
+        const double p = (double)s_p[l];
+        int cb = 0, cf = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int b0 = c[k], f0 = c[4 + k];
+            cb += b0;
+            cf += f0;
+            if ((b0 | f0) == 0) continue;
+            const double d = p - s_shift[k];
+            v[3 * k] += d * (b0 + f0);
+            v[3 * k + 1] += d * d * (b0 + f0);
+            v[3 * k + 2] += d * f0;
+            gq[k] += f0;
+        }
+        if (p >= athr) {
+            tpa += cf;
+            fpa += cb;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[12 + j] = (double)gq[j];
+    v[16] = (double)tpa;
+    v[17] = (double)fpa;
+    __syncthreads();
+    block_sum<SOD_P2>(v, s_red);
+    if (t == 0) {
+#pragma unroll
+        for (int k = 0; k < SOD_P2; ++k) tot2[(size_t)b * SOD_P2 + k] = v[k];
+    }
+    __syncthreads();
+    // ---- closed forms (sod_finalize) and, in the block that finishes last, the batch sums of both families
+    const bool last = sod_finalize_body(tot1, tot2, shift, nullptr, 0, hist, H, W, 0.3, 1.0, per_image_sod, curves, done_counter, batch, partial_sod);
+    if (last) {
+        __syncthreads();
+        metrics_finalize_block(counts, abs_err, batch, (long long)HW, per_image, partial, reinterpret_cast<double(*)[14]>(s_red));
     }
 }
 
@@ -702,4 +1058,80 @@ extern "C" int cm_sod_metrics_painted(const void* labels, int label_bytes, const
     src.id_of_label = id_of_label;
     src.cap = label_cap;
     return sod_metrics_impl(src, gt, batch, h, w, with_weighted_f, workspace, workspace_bytes, per_image, partial, stream, "cm_sod_metrics_painted");
+}
+
+extern "C" size_t cm_region_table_workspace_bytes(int batch, int h, int w, int label_cap) {
+    if (batch <= 0 || h <= 0 || w <= 0 || label_cap <= 0) return 0;
+    return cm::carve_rt(nullptr, batch, h, w, label_cap).total;
+}
+
+static const int RT_MAX_CAP = 6000;   // (cap + 1) * 36 bytes of shared memory per block
+
+extern "C" int cm_region_table_build(const void* labels, int label_bytes, const uint8_t* gt, int gt_packed, int batch, int h, int w, int label_cap,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(labels && gt && workspace && (label_bytes == 2 || label_bytes == 4), "cm_region_table_build: NULL pointer or label_bytes not 2 / 4");
+    CM_REQUIRE(batch > 0 && batch <= 65535 && h > 0 && w > 0 && h < 32767 && w < 32767 && (long long)h * w < (1ll << 30), "cm_region_table_build: bad shape");
+    CM_REQUIRE(label_cap > 0 && label_cap <= RT_MAX_CAP, "cm_region_table_build: label_cap must be in 1..%d", RT_MAX_CAP);
+    CM_REQUIRE(!gt_packed || ((long long)h * w) % 8 == 0, "cm_region_table_build: a bit-packed ground truth needs H*W divisible by 8");
+    RtWs ws = carve_rt(workspace, batch, h, w, label_cap);
+    if (workspace_bytes < ws.total) {
+        set_error("cm_region_table_build: workspace %zu < %zu bytes", workspace_bytes, ws.total);
+        return CM_ERR_WORKSPACE;
+    }
+    cudaStream_t st = as_stream(stream);
+    const size_t smem = (size_t)(label_cap + 1) * 8 * sizeof(int);
+    const int v = (label_bytes == 2 ? 0 : 2) + (gt_packed ? 1 : 0);
+    {
+        static PerDeviceMax smem_set[4];
+        if (smem > 40 * 1024 && smem_set[v].raise(smem)) {
+            const void* f = v == 0 ? (const void*)rt_table_kernel<short, false> : v == 1 ? (const void*)rt_table_kernel<short, true>
+                          : v == 2 ? (const void*)rt_table_kernel<int, false> : (const void*)rt_table_kernel<int, true>;
+            cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        }
+    }
+    {
+        CM_TIMED("region_gt_table", st);
+        const dim3 grid(ws.splits, batch);
+        int* done = ws.hist + (size_t)batch * 512;
+        if (v == 0) rt_table_kernel<short, false><<<grid, RT_THREADS, smem, st>>>(reinterpret_cast<const short*>(labels), gt, h, w, label_cap, ws.gtstat, ws.part, done);
+        else if (v == 1) rt_table_kernel<short, true><<<grid, RT_THREADS, smem, st>>>(reinterpret_cast<const short*>(labels), gt, h, w, label_cap, ws.gtstat, ws.part, done);
+        else if (v == 2) rt_table_kernel<int, false><<<grid, RT_THREADS, smem, st>>>(reinterpret_cast<const int*>(labels), gt, h, w, label_cap, ws.gtstat, ws.part, done);
+        else rt_table_kernel<int, true><<<grid, RT_THREADS, smem, st>>>(reinterpret_cast<const int*>(labels), gt, h, w, label_cap, ws.gtstat, ws.part, done);
+    }
+    return post_launch("cm_region_table_build");
+}
+
+extern "C" int cm_region_table_metrics(const void* labels, int label_bytes, const uint8_t* gt_bytes, int batch, int h, int w, const float* mask_prob,
+                                       const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, float threshold, void* workspace,
+                                       size_t workspace_bytes, int64_t* counts, double* abs_err, double* per_image, double* partial,
+                                       double* per_image_sod, double* partial_sod, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(labels && workspace && mask_prob && node_ptr && counts && abs_err && per_image_sod && partial_sod && (per_image || partial),
+               "cm_region_table_metrics: NULL pointer");
+    CM_REQUIRE(label_bytes == 2 || label_bytes == 4, "cm_region_table_metrics: label_bytes not 2 / 4");
+    CM_REQUIRE(batch > 0 && batch <= 65535 && h > 0 && w > 0 && (long long)h * w < (1ll << 30), "cm_region_table_metrics: bad shape");
+    CM_REQUIRE(label_cap > 0 && label_cap <= RT_MAX_CAP, "cm_region_table_metrics: label_cap must be in 1..%d", RT_MAX_CAP);
+    CM_REQUIRE(threshold >= 0.f && threshold < 1.f, "cm_region_table_metrics: threshold must be in [0, 1)");
+    RtWs ws = carve_rt(workspace, batch, h, w, label_cap);
+    if (workspace_bytes < ws.total) {
+        set_error("cm_region_table_metrics: workspace %zu < %zu bytes", workspace_bytes, ws.total);
+        return CM_ERR_WORKSPACE;
+    }
+    cudaStream_t st = as_stream(stream);
+    const size_t smem = (size_t)(label_cap + 1) * (8 * sizeof(int) + sizeof(float));
+    {
+        static PerDeviceMax smem_set;
+        if (smem > 32 * 1024 && smem_set.raise(smem)) cudaFuncSetAttribute(rt_metrics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    }
+    {
+        CM_TIMED("region_table_metrics", st);
+        rt_metrics_kernel<<<batch, 256, smem, st>>>(ws.part, ws.splits, label_cap, ws.gtstat, labels, label_bytes, mask_prob, node_ptr, id_of_label, threshold,
+                                                    h, w, gt_bytes, reinterpret_cast<unsigned long long*>(counts), abs_err, ws.tot1,
+                                                    ws.tot2, ws.shift, ws.hist, ws.curves, ws.hist + (size_t)batch * 512, batch, per_image, partial,
+                                                    per_image_sod, partial_sod);
+    }
+    return post_launch("cm_region_table_metrics");
 }

@@ -191,6 +191,74 @@ def sod_metrics_painted(labels, gt_u8, mask_prob, node_ptr, id_of_label=None, la
     return per_image, partial
 
 
+RT_MAX_LABEL_CAP = 6000
+
+
+class RegionTable:
+    """A8 + A9 + A9' of a painted mask through the region x ground-truth contingency table (``cm_region_table_*``): the
+    pixel pass needs labels + gt only, so it runs next to the graph build; behind the model one small block per image turns
+    table rows x node probabilities into the same counts / sums the pixel kernels (``cm_paint_metrics``,
+    ``cm_sod_metrics_painted``) give.  Weighted F is not part of it (it needs the pixel-level distance transform).
+
+    ``build(labels, gt)`` -- labels ``[B,H,W]`` int32 / int16, gt ``[B,H,W]`` uint8 or bit-packed ``[B,H*W/8]`` uint8;
+    ``metrics(mask_prob, node_ptr, ...)`` -- after the model, on the same stream or one that waited for ``build``."""
+
+    def __init__(self, label_cap: int, lane_key: str = "region_table"):
+        if not 0 < int(label_cap) <= RT_MAX_LABEL_CAP:
+            raise ValueError(f"label_cap must be in 1..{RT_MAX_LABEL_CAP}")
+        self.label_cap = int(label_cap)
+        self._key = lane_key
+        self._built = None
+
+    def build(self, labels, gt):
+        from .region_graph import WORKSPACE
+        lib = _lib.load()
+        _lib.require_cuda(labels, "labels")
+        _lib.require_cuda(gt, "gt")
+        if labels.dtype not in (torch.int32, torch.int16) or labels.dim() != 3 or gt.dtype != torch.uint8:
+            raise ValueError("labels [B,H,W] int32 / int16 and gt uint8 expected")
+        B, H, W = labels.shape
+        packed = gt.dim() == 2
+        if packed and ((H * W) % 8 or tuple(gt.shape) != (B, H * W // 8)):
+            raise ValueError(f"packed gt must be [B, H*W/8] uint8, got {tuple(gt.shape)}")
+        if not packed and gt.shape != labels.shape:
+            raise ValueError("gt [B,H,W] uint8 expected")
+        labels, gt = labels.contiguous(), gt.contiguous()
+        dev = labels.device
+        ws_bytes = lib.cm_region_table_workspace_bytes(B, H, W, self.label_cap)
+        ws = WORKSPACE.get(dev, self._key, ws_bytes)
+        p = _lib.ptr
+        _lib.check(lib.cm_region_table_build(p(labels), labels.element_size(), p(gt), 1 if packed else 0, B, H, W, self.label_cap, p(ws), ws_bytes,
+                                             _lib.stream_ptr(dev)), "cm_region_table_build")
+        self._built = (labels, None if packed else gt, ws, ws_bytes, (B, H, W))
+        return self
+
+    def metrics(self, mask_prob, node_ptr, id_of_label=None, threshold: float = 0.5, counts=None, abs_err=None, per_image=None, partial=None,
+                per_image_sod=None, partial_sod=None):
+        """-> dict(counts [B,4] i64, abs_err [B], per_image [B,7], partial [15], per_image_sod [B,8], partial_sod [528])."""
+        if self._built is None:
+            raise RuntimeError("RegionTable.metrics before build")
+        lib = _lib.load()
+        labels, gt_bytes, ws, ws_bytes, (B, H, W) = self._built
+        dev = labels.device
+        _lib.require_cuda(mask_prob, "mask_prob")
+        _lib.require_cuda(node_ptr, "node_ptr")
+        f64 = dict(dtype=torch.float64, device=dev)
+        counts = torch.empty((B, 4), dtype=torch.int64, device=dev) if counts is None else counts
+        abs_err = torch.empty(B, **f64) if abs_err is None else abs_err
+        per_image = torch.empty((B, 7), **f64) if per_image is None else per_image
+        partial = torch.empty(15, **f64) if partial is None else partial
+        per_image_sod = torch.empty((B, len(SOD_KEYS)), **f64) if per_image_sod is None else per_image_sod
+        partial_sod = torch.empty(SOD_PARTIAL, **f64) if partial_sod is None else partial_sod
+        p = _lib.ptr
+        _lib.check(lib.cm_region_table_metrics(p(labels), labels.element_size(), p(gt_bytes), B, H, W, p(_lib.f32c(mask_prob)), p(node_ptr),
+                                               p(id_of_label), self.label_cap, float(threshold), p(ws), ws_bytes, p(counts), p(abs_err),
+                                               p(per_image), p(partial), p(per_image_sod), p(partial_sod), _lib.stream_ptr(dev)),
+                   "cm_region_table_metrics")
+        return {"counts": counts, "abs_err": abs_err, "per_image": per_image, "partial": partial, "per_image_sod": per_image_sod,
+                "partial_sod": partial_sod}
+
+
 def _sod_inputs(pred_mask, gt_mask):
     dev = _device()
     p = pred_mask if torch.is_tensor(pred_mask) else torch.as_tensor(np.asarray(pred_mask))

@@ -19,15 +19,23 @@ from .region_graph import RegionGraphBatch, build_region_graphs
 
 class EvalPipeline:
     def __init__(self, gnn, detector, kg, label_cap: int = 544, threshold: float = 0.5, label_offset_fix: bool = False,
-                 want_pred_mask: bool = False, lane: int = 0, sod_metrics: bool = True, weighted_f: bool = False):
+                 want_pred_mask: bool = False, lane: int = 0, sod_metrics: bool = True, weighted_f: bool = False,
+                 table_metrics: bool = True):
         """``kg``: ``[K, kg_dim]`` knowledge-graph rows shared by every image (broadcast once).
         ``lane``: pipelines with different lanes own disjoint scratch and may run concurrently on different streams
         (they share the read-only folded weights).
         ``sod_metrics``: also compute S- / E- / F- / weighted-F-measure (``metrics.SOD_KEYS``; north_star's "S/E/F-measure",
         not in the reference) on the painted mask: ``out["per_image_sod"]`` ``[B,8]``, ``out["partial_sod"]`` ``[528]``.
         ``weighted_f``: also Margolin's weighted F-measure (an exact Euclidean feature transform of every GT mask: several
-        times the cost of the other seven; its slot is NaN when off)."""
+        times the cost of the other seven; its slot is NaN when off).
+        ``table_metrics``: compute the metrics through the region x ground-truth contingency table (``metrics.RegionTable``:
+        the pixel pass moves next to the graph build, behind the model only one small block per image remains) instead of
+        three pixel passes behind the GNN; same numbers.  Used when the S/E/F metrics are on and neither the painted mask nor
+        the weighted F-measure is asked for."""
         self.lane = int(lane)
+        self.table_metrics = bool(table_metrics) and os.environ.get("CM_TABLE_METRICS", "1") != "0"
+        self._table = None
+        self._side2 = None
         self.sod_metrics, self.weighted_f = bool(sod_metrics), bool(weighted_f)
         self.n_segments = 500   # create_region_graph(image, n_segments=500), extract_rg_embeddings.py:138
         self.gnn, self.detector = gnn.eval(), detector.eval()
@@ -102,9 +110,11 @@ class EvalPipeline:
                 if buf is None or buf.shape != (B, H, W):
                     buf = self._bufs["canny_map"] = torch.empty((B, H, W), dtype=torch.uint8, device=dev)
                 canny = canny_edges(images, sigma=2.0, out=buf)
+        use_table = (self.table_metrics and self.sod_metrics and not self.weighted_f and not self.want_pred_mask
+                     and self.label_cap <= metrics.RT_MAX_LABEL_CAP and 0.0 <= self.threshold < 1.0)
         if canny.dim() == 2 or gt.dim() == 2:      # bit-packed masks: one bit per pixel over PCIe, bytes again here
             for name, t, one in (("canny", canny, 1), ("gt", gt, 255)):
-                if t.dim() != 2:
+                if t.dim() != 2 or (name == "gt" and use_table):    # the region table reads the packed ground truth as it is
                     continue
                 if (H * W) % 8 or tuple(t.shape) != (B, H * W // 8) or t.dtype != torch.uint8:
                     raise ValueError(f"packed {name} must be [B, H*W/8] uint8, got {tuple(t.shape)} {t.dtype}")
@@ -126,6 +136,17 @@ class EvalPipeline:
             _lib.check(lib.cm_labels_widen_i16(_lib.ptr(labels), labels.numel(), _lib.ptr(l32), _lib.stream_ptr(dev)),
                        "cm_labels_widen_i16")
             labels = l32
+        main = torch.cuda.current_stream(dev)
+        if use_table:      # labels x gt contingency table: needs nothing from the model, runs next to the graph build
+            if self._table is None:
+                self._table = metrics.RegionTable(self.label_cap)
+            if self._side2 is None or self._side2.device != dev:
+                self._side2 = torch.cuda.Stream(dev)
+            side2 = self._side2 if self.parallel_metrics else main
+            if side2 is not main:
+                side2.wait_stream(main)
+            with torch.cuda.stream(side2):
+                self._table.build(labels, gt)
         g = build_region_graphs(images, labels, canny, label_cap=self.label_cap, want_edge_index=False, out=self._graph)
         self._graph = g
         n_dev = g.node_ptr[B:]
@@ -133,30 +154,41 @@ class EvalPipeline:
                          want=("node_emb", "mask_out", "mask_prob"), out=self._bufs["gnn"])
         # paint + metrics need only the GNN's mask probabilities: they run on a side stream next to the fusion (inside a
         # captured step this becomes a parallel branch of the CUDA graph)
-        main = torch.cuda.current_stream(dev)
         if self._side is None or self._side.device != dev:
             self._side = torch.cuda.Stream(dev)
         side = self._side if self.parallel_metrics else main
         if side is not main:
             side.wait_stream(main)
+            if use_table:
+                side.wait_stream(self._side2)
         p = _lib.ptr
         b = self._bufs
-        with torch.cuda.stream(side):
-            paint = lib.cm_paint_metrics_i16 if labels.dtype == torch.int16 else lib.cm_paint_metrics
-            _lib.check(paint(p(labels), p(gt), B, H, W, p(r["mask_prob"]), p(g.node_ptr),
-                                            p(g.id_of_label) if self.label_offset_fix else None, self.label_cap,
-                                            self.threshold, p(b["pred_mask"]), p(b["counts"]), p(b["abs_err"]),
-                                            _lib.stream_ptr(dev)), "cm_paint_metrics")
-            _lib.check(lib.cm_metrics_finalize(p(b["counts"]), p(b["abs_err"]), B, H * W, p(b["per_image"]), p(b["partial"]),
-                                               _lib.stream_ptr(dev)), "cm_metrics_finalize")
-            if self.sod_metrics:    # on the painted mask, without materialising it
-                metrics.sod_metrics_painted(labels, gt, r["mask_prob"], g.node_ptr, g.id_of_label if self.label_offset_fix else None,
-                                            self.label_cap, per_image=b["per_image_sod"], partial=b["partial_sod"],
-                                            weighted_f=self.weighted_f)
-            if self.total is not None:
-                self.total.add_(b["partial"])
-                if self.total_sod is not None and self.sod_metrics:
-                    self.total_sod.add_(b["partial_sod"])
+        if use_table:
+            with torch.cuda.stream(side):
+                self._table.metrics(r["mask_prob"], g.node_ptr, g.id_of_label if self.label_offset_fix else None, self.threshold,
+                                    counts=b["counts"], abs_err=b["abs_err"], per_image=b["per_image"], partial=b["partial"],
+                                    per_image_sod=b["per_image_sod"], partial_sod=b["partial_sod"])
+                if self.total is not None:
+                    self.total.add_(b["partial"])
+                    if self.total_sod is not None:
+                        self.total_sod.add_(b["partial_sod"])
+        else:
+            with torch.cuda.stream(side):
+                paint = lib.cm_paint_metrics_i16 if labels.dtype == torch.int16 else lib.cm_paint_metrics
+                _lib.check(paint(p(labels), p(gt), B, H, W, p(r["mask_prob"]), p(g.node_ptr),
+                                                p(g.id_of_label) if self.label_offset_fix else None, self.label_cap,
+                                                self.threshold, p(b["pred_mask"]), p(b["counts"]), p(b["abs_err"]),
+                                                _lib.stream_ptr(dev)), "cm_paint_metrics")
+                _lib.check(lib.cm_metrics_finalize(p(b["counts"]), p(b["abs_err"]), B, H * W, p(b["per_image"]), p(b["partial"]),
+                                                   _lib.stream_ptr(dev)), "cm_metrics_finalize")
+                if self.sod_metrics:    # on the painted mask, without materialising it
+                    metrics.sod_metrics_painted(labels, gt, r["mask_prob"], g.node_ptr, g.id_of_label if self.label_offset_fix else None,
+                                                self.label_cap, per_image=b["per_image_sod"], partial=b["partial_sod"],
+                                                weighted_f=self.weighted_f)
+                if self.total is not None:
+                    self.total.add_(b["partial"])
+                    if self.total_sod is not None and self.sod_metrics:
+                        self.total_sod.add_(b["partial_sod"])
         f = self.detector.forward_ragged(r["node_emb"], g.node_ptr, B, self.kg, return_attention=False,
                                          out=self._bufs["fusion"])
         self._bufs["fusion"] = f

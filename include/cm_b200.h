@@ -372,6 +372,27 @@ int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, int h, int w
 int cm_sod_metrics_painted(const void* labels, int label_bytes, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
                            const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, int with_weighted_f, void* workspace,
                            size_t workspace_bytes, double* per_image, double* partial, void* stream);
+/* A8 + A9 + A9' on a painted mask WITHOUT a pixel pass behind the model.  A painted prediction is constant over a region, so
+ * every pixel sum of utils/metrics.py:9-92 and of the S- / E- / F-measures factors through the contingency table
+ * count[label][gt class][S-measure quadrant]; the quadrants are cut at the ground truth's centroid, so the table depends on
+ * labels + gt only.
+ *   cm_region_table_build    labels [B,H,W] int32 / int16 (label_bytes 4 / 2), gt [B,H,W] uint8, or bit-packed [B,H*W/8] with
+ *                            gt_packed != 0 (bit i of byte j = pixel 8 j + i, a set bit = 255): builds the table in `workspace`.
+ *                            Needs nothing from the model: run it next to the graph build.
+ *   cm_region_table_metrics  the same workspace + the per-node probabilities: counts [B,4] / abs_err [B] / per_image [B,7] /
+ *                            partial [15] exactly as cm_paint_metrics + cm_metrics_finalize give them, per_image_sod [B,8] /
+ *                            partial_sod [528] as cm_sod_metrics_painted (weighted F = NaN).  gt_bytes: the byte ground truth
+ *                            again, or NULL when it was bit-packed; |pred - gt| only factors for gt in {0, 255}, so for an
+ *                            image where the build found other bytes that image's block walks its pixels for the A9 counts / MAE
+ *                            the way cm_paint_metrics does (decided on the device, no synchronisation).  threshold in [0, 1).  label_cap <= 6000; labels outside [0, label_cap)
+ *                            paint probability 0 as in cm_paint_metrics. */
+size_t cm_region_table_workspace_bytes(int batch, int h, int w, int label_cap);
+int cm_region_table_build(const void* labels, int label_bytes, const uint8_t* gt, int gt_packed, int batch, int h, int w, int label_cap,
+                          void* workspace, size_t workspace_bytes, void* stream);
+int cm_region_table_metrics(const void* labels, int label_bytes, const uint8_t* gt_bytes, int batch, int h, int w, const float* mask_prob,
+                            const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, float threshold, void* workspace,
+                            size_t workspace_bytes, int64_t* counts, double* abs_err, double* per_image, double* partial,
+                            double* per_image_sod, double* partial_sod, void* stream);
 /* A13: image-level confusion counts tp, fp, fn, tn (models/multimodal/train_multimodal.py:197-220) from
  * predicted class = argmax(mask_out) and true class ids.  counts4 [4] int64 accumulated (caller zeroes). */
 int cm_class_confusion(const float* mask_out, const int64_t* true_cls, int n, int num_classes,
