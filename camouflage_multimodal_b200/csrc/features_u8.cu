@@ -279,13 +279,20 @@ node_features_u8_kernel(const uint8_t* __restrict__ image, const int* __restrict
 // no shared memory, ~1.7 pixel visits per pixel for compact superpixels.  Label and image windows are small and
 // re-read through L1/L2; DRAM sees each byte once.  ~9x fewer instructions than the tile kernel on SLIC-shaped
 // regions; the tile kernel remains the better choice for a few huge regions.
-__device__ __forceinline__ int u8_find_image(const int* __restrict__ node_ptr, int batch, int g) {
-    int lo = 0, hi = batch;   // largest b with node_ptr[b] <= g
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (node_ptr[mid] <= g) lo = mid; else hi = mid;
+// the image b with node_ptr[b] <= g < node_ptr[b + 1].  Images hold about the same number of regions, so the proportional
+// guess is right or one off: two independent loads instead of the log2(batch) dependent ones of a bisection.
+__device__ __forceinline__ int u8_find_image(const int* __restrict__ node_ptr, int batch, int g, int total) {
+    int b = min(__float2int_rz((float)g * (float)batch / (float)total), batch - 1);
+    int lo = node_ptr[b], hi = node_ptr[b + 1];
+    while (lo > g) {
+        hi = lo;
+        lo = node_ptr[--b];
     }
-    return lo;
+    while (hi <= g) {
+        lo = hi;
+        hi = node_ptr[++b + 1];
+    }
+    return b;
 }
 // warp sum of 32 values < 2^32 whose total may exceed 2^32
 __device__ __forceinline__ unsigned long long warp_sum_wide(unsigned v) {
@@ -389,7 +396,7 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
     const int gi = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int total = min(node_ptr[batch], node_cap);
     if (gi >= total) return;
-    const int b = u8_find_image(node_ptr, batch, gi);
+    const int b = u8_find_image(node_ptr, batch, gi, node_ptr[batch]);
     const int L = node_label[gi];
     const int4 bb = *reinterpret_cast<const int4*>(node_bbox + 4 * (size_t)gi);
     const int wx0 = max(bb.x - 2, 0), wy0 = max(bb.y - 2, 0), wx1 = min(bb.z + 2, W - 1), wy1 = min(bb.w + 2, H - 1);
@@ -415,14 +422,23 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
         const int base = wy0 * W + wx0;
         const LT* lp0 = lab + base + (colin ? lane : 0);
         unsigned m = 0;
-        for (int y8 = 0; y8 < wh; y8 += 16) {   // sixteen rows of label loads in flight
+        for (int y8 = 0; y8 < wh; y8 += 16) {   // up to sixteen rows of label loads in flight; rows past the window are skipped
             int lw[16];
+            const LT* lp = lp0 + y8 * W;
 #pragma unroll
-            for (int k = 0; k < 16; ++k) lw[k] = __ldg(lp0 + min(y8 + k, wh - 1) * W);
+            for (int k4 = 0; k4 < 16; k4 += 4) {
+                if (y8 + k4 >= wh) break;       // warp-uniform
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                const unsigned bal = __ballot_sync(full, colin && lw[k] == L);
-                if (lane == y8 + k) m = bal;
+                for (int k = k4; k < k4 + 4; ++k) lw[k] = __ldg(lp + min(k, wh - 1 - y8) * W);
+            }
+#pragma unroll
+            for (int k4 = 0; k4 < 16; k4 += 4) {
+                if (y8 + k4 >= wh) break;
+#pragma unroll
+                for (int k = k4; k < k4 + 4; ++k) {
+                    const unsigned bal = __ballot_sync(full, colin && lw[k] == L);
+                    if (lane == y8 + k) m = bal;
+                }
             }
         }
         if (lane >= wh) m = 0;
@@ -516,6 +532,18 @@ __global__ void __launch_bounds__(256) node_features_u8_bbox_kernel(const uint8_
         rn += m2; xr += r * m2; xg += g * m2; xb += bl * m2;
     }
     U8Moments m;
+    if (ww <= 32 && wh <= 32) {
+        // at most 1024 pixels of 8-bit values: every warp total is below 2^27 -- one redux each, no 16-bit halves
+        m.n = __reduce_add_sync(0xffffffffu, n); m.can = __reduce_add_sync(0xffffffffu, sc);
+        m.per = __reduce_add_sync(0xffffffffu, per); m.rn = __reduce_add_sync(0xffffffffu, rn);
+        m.sx = __reduce_add_sync(0xffffffffu, sx); m.sy = __reduce_add_sync(0xffffffffu, sy);
+        m.r = __reduce_add_sync(0xffffffffu, r1); m.g = __reduce_add_sync(0xffffffffu, g1); m.b = __reduce_add_sync(0xffffffffu, b1);
+        m.rr = __reduce_add_sync(0xffffffffu, rr); m.gg = __reduce_add_sync(0xffffffffu, gg); m.bb = __reduce_add_sync(0xffffffffu, b2);
+        m.rg = __reduce_add_sync(0xffffffffu, rg); m.rb = __reduce_add_sync(0xffffffffu, rb); m.gb = __reduce_add_sync(0xffffffffu, gb);
+        m.xr = __reduce_add_sync(0xffffffffu, xr); m.xg = __reduce_add_sync(0xffffffffu, xg); m.xb = __reduce_add_sync(0xffffffffu, xb);
+        u8_write_features_warp(m, norm_side, xout + (size_t)gi * CM_NODE_FEATURES, lane);
+        return;
+    }
     m.n = __reduce_add_sync(0xffffffffu, n);
     m.can = __reduce_add_sync(0xffffffffu, sc);
     m.per = __reduce_add_sync(0xffffffffu, per);
