@@ -123,6 +123,11 @@ __device__ __forceinline__ void load_acc_bias_s(uint32_t taddr, int c0, float br
     for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) + __shfl_sync(0xffffffffu, breg, j);
 }
 
+// Measured and dropped: four more warps (448 threads) for the two epilogues that only feed global memory (raw kg->rg scores,
+// V2), the softmax split over both halves.  The chain gets its accumulator halves back sooner, but the tile was slower both
+// with row-per-thread st.global in the side warps (26.5 -> 30.2 us) and with 16 KB staged tiles handed to TMA stores
+// (30.7 us); with the side warps only waiting it was 27.7 us: the softmax / LayerNorm epilogues of the chain warps stretch
+// by what the side work would have saved (the register file allows 128 registers per thread at 448 threads).
 // Measured and dropped: keeping the next chunk's TMEM load in flight while the current chunk is processed (tc_ld32_issue /
 // tc_ld_wait in tc_ptx.cuh) needs 32 more live registers; a 320-thread CTA is capped at 168 (three warps per 16 K-register
 // sub-partition), and the spills cost more than the hidden latency (43 -> 58 us).
