@@ -142,6 +142,8 @@ SIGNATURES = {
     "cm_metrics_finalize": (_i, [_fp, _fp, _i, _i64, _fp, _fp, _fp]),
     "cm_sod_workspace_bytes": (_sz, [_i, _i, _i]),
     "cm_sod_metrics": (_i, [_fp, _fp, _i, _i, _i, _i, _fp, _sz, _fp, _fp, _fp]),
+    "cm_sod_metrics_static_max_bytes": (_sz, []),
+    "cm_sod_metrics_static": (_i, [_fp, _fp, _i, _i, _i, _fp, _fp, _fp]),
     "cm_sod_metrics_painted": (_i, [_fp, _i, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _i, _fp, _sz, _fp, _fp, _fp]),
     "cm_region_table_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "cm_region_table_build": (_i, [_fp, _i, _fp, _i, _i, _i, _i, _i, _fp, _sz, _fp]),

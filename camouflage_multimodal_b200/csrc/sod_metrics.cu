@@ -1043,6 +1043,57 @@ extern "C" int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, i
     return sod_metrics_impl(src, gt, batch, h, w, with_weighted_f, workspace, workspace_bytes, per_image, partial, stream, "cm_sod_metrics");
 }
 
+// ---------------------------------------------------------------------------------------------- no-allocation variant
+// cm_sod_metrics (without the weighted F-measure) for callers that cannot allocate: the workspace is a file-scope device
+// array that every GPU loading the library holds until exit.  All calls on a device share it (and find the previous call's
+// contents there: the histogram / counter block is cleared by sod_metrics_impl as for any workspace) -- calls that overlap on
+// the GPU race.
+constexpr size_t SOD_STATIC_BYTES = 2u << 20;   // 2 MiB: ~170 images of 256 x 256 per call
+static __device__ __align__(256) unsigned char g_sod_static_scratch[SOD_STATIC_BYTES];
+
+// workspace bytes of the S / E / F passes alone: carve_sod lays the weighted-F arrays (col_d onwards) out last
+static size_t sod_bytes_without_wf(int batch, int h, int w) {
+    const cm::SodWs ws = cm::carve_sod(nullptr, batch, h, w);
+    return cm::align_up((size_t)reinterpret_cast<uintptr_t>(ws.col_d), 256);
+}
+
+extern "C" size_t cm_sod_metrics_static_max_bytes(void) { return SOD_STATIC_BYTES; }
+
+extern "C" int cm_sod_metrics_static(const float* pred, const uint8_t* gt, int batch, int h, int w, double* per_image, double* partial,
+                                     void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    if (!pred) {
+        set_error("cm_sod_metrics_static: NULL pointer");
+        return CM_ERR_ARG;
+    }
+    CM_REQUIRE(batch > 0 && h > 0 && w > 0 && batch <= 65535 && (long long)h * w < (1ll << 30), "cm_sod_metrics_static: bad shape");
+    const size_t need = sod_bytes_without_wf(batch, h, w);
+    if (need > SOD_STATIC_BYTES) {
+        set_error("cm_sod_metrics_static: batch %d of %d x %d needs %zu bytes of scratch, the built-in array holds %zu -- use cm_sod_metrics "
+                  "with a caller workspace", batch, h, w, need, (size_t)SOD_STATIC_BYTES);
+        return CM_ERR_WORKSPACE;
+    }
+    // the array's name is a host-side stand-in here: its device address, looked up once per device with that device current
+    static void* dev_ptr[64] = {};
+    const int slot = current_device_slot();
+    if (!dev_ptr[slot]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_sod_static_scratch);
+        if (e != cudaSuccess || !p) {
+            set_error("cm_sod_metrics_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+            return CM_ERR_LAUNCH;
+        }
+        dev_ptr[slot] = p;
+    }
+    SodSrc src = {};
+    src.pred = pred;
+    // passing `need` as the size would fail carve_sod's full-size check: the weighted-F slices (unused with with_weighted_f = 0)
+    // lie beyond the array and are never touched
+    return sod_metrics_impl(src, gt, batch, h, w, 0, dev_ptr[slot], carve_sod(nullptr, batch, h, w).total, per_image, partial, stream,
+                            "cm_sod_metrics_static");
+}
+
 extern "C" int cm_sod_metrics_painted(const void* labels, int label_bytes, const uint8_t* gt, int batch, int h, int w, const float* mask_prob,
                                       const int32_t* node_ptr, const int32_t* id_of_label, int label_cap, int with_weighted_f, void* workspace,
                                       size_t workspace_bytes, double* per_image, double* partial, void* stream) {

@@ -366,6 +366,16 @@ size_t cm_sod_workspace_bytes(int batch, int h, int w);
  * filter per image -- several times the cost of everything else here); its slot in per_image / partial is then NaN. */
 int cm_sod_metrics(const float* pred, const uint8_t* gt, int batch, int h, int w, int with_weighted_f, void* workspace,
                    size_t workspace_bytes, double* per_image, double* partial, void* stream);
+/* No counterpart in the reference: added for callers that cannot allocate device memory
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  cm_sod_metrics without the
+ * weighted F-measure (its slot is NaN) and without a workspace argument: the scratch is a 2 MiB array built into the library
+ * (cm_sod_metrics_static_max_bytes; every GPU that loads the library holds it until exit; ~170 images of 256 x 256 per
+ * call).  A batch that needs more is rejected with CM_ERR_WORKSPACE.  The call allocates nothing (no cudaMalloc / cudaFree /
+ * allocating library routine).  Every call on a device shares the array: calls that overlap on the GPU (different streams
+ * without ordering) race -- serialise them.  Inputs / outputs as in cm_sod_metrics. */
+size_t cm_sod_metrics_static_max_bytes(void);
+int cm_sod_metrics_static(const float* pred, const uint8_t* gt, int batch, int h, int w, double* per_image, double* partial,
+                          void* stream);
 /* The same on the PAINTED prediction of cm_paint_metrics (pixel with label l gets mask_prob[l], or
  * mask_prob[id_of_label[l]] with the offset fix; models/region_graph/test.py:241-244) without materialising the mask:
  * labels [B,H,W] int32 (label_bytes 4) or int16 (2); the other arguments as in cm_paint_metrics. */
