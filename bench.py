@@ -154,6 +154,9 @@ def kernel_work(name, B, M, E, K):
         "region_gt_table": ("hbm", px * (LABEL_BYTES + 2.0) + 32.0 * B * (LABEL_CAP + 1)),
         # one launch for everything after the node kernel: chunk partials in, weights of the KG-row chain + fusion MLP + heads
         # (1.9 MB, L2-resident after the first cluster) -- latency-bound by design at 13 rows per image
+        "kg_tail": ("hbm", (M / 64.0 + B / 2.0) * 4608.0 * 4.0 + 1.9e6),
+        # table rows x node probabilities -> every metric: the per-image tables + the probabilities in, a few hundred bytes out
+        "region_table_metrics": ("hbm", 32.0 * B * (LABEL_CAP + 1) + 4.0 * M + 2048.0 * B),
         "unpack_bits": ("hbm", px * (2.0 / 8.0 + 2.0)),
         "gat_logits": ("hbm", 60.0 * M + 32.0 * M),
         "gat_aggregate": ("hbm", 60.0 * M + 4.0 * E + 240.0 * M),

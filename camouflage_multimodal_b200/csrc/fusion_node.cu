@@ -135,6 +135,11 @@ template <int MODE>
 __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid_constant__ FusionNodeArgs a) {
     constexpr int NPH = MODE == 0 ? 8 : 5, XKB = MODE == 0 ? 2 : 4;
     extern __shared__ uint8_t smem_raw[];
+    if (a.dbg && threadIdx.x == 0) {   // every CTA: first instruction / last (the buffer holds 40 + 2 x grid stamps)
+        long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.dbg[40 + 2 * blockIdx.x] = t;
+    }
     const int m_live = a.m_dev ? min(*a.m_dev, a.M) : a.M;
     const int m0 = blockIdx.x * 128;
     if (m0 >= m_live) return;
@@ -438,8 +443,10 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
     }
     __syncthreads();
     if (warp == 0) {
+        if (stamp && lane == 0) a.dbg[38] = now();
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        if (a.dbg && lane == 0) a.dbg[41 + 2 * blockIdx.x] = now();
     }
 }
 

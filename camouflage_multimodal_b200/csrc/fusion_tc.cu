@@ -25,7 +25,7 @@
 namespace cm {
 
 static size_t al(size_t v) { return (v + 255) / 256 * 256; }
-long long* g_fusion_phase_dbg = nullptr;   // profiling aid (cm_debug_fusion_phase_stamps): 40 device int64 or NULL
+long long* g_fusion_phase_dbg = nullptr;   // profiling aid (cm_debug_fusion_phase_stamps): 40 + 2 x grid device int64 or NULL
 
 // shapes the single-kernel node side is written for (the reference's configs/multimodal_config.yaml defaults)
 static bool fusion_node_fused_ok(const cm_fusion_params* p) { return p->hidden == 256 && p->rg_dim == 128 && p->rg_proj_w != nullptr; }
@@ -299,6 +299,6 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
 }  // namespace cm
 
 // Profiling aid (tools/fusion_phase_profile.py): CTA 0 of fusion_node writes globaltimer stamps of every phase into buf
-// (40 int64 on the device) while set; NULL turns it off.  Not part of the product path.
+// and every CTA its start / end at [40 + 2 b], [41 + 2 b] (40 + 2 x grid int64 on the device) while set; NULL turns it off.  Not part of the product path.
 extern "C" void cm_debug_fusion_phase_stamps(long long* device_buf) { cm::g_fusion_phase_dbg = device_buf; }
 

@@ -542,29 +542,25 @@ __device__ __forceinline__ bool sod_finalize_body(const double* tot1, const doub
         }
     }
     __syncthreads();
-    if (t == 0) {
+    if (t < 32) {
+    // The closed forms are ~40 dependent float64 divisions / square roots: spread over the lanes of warp 0 (one quadrant of
+    // the region term per lane 0..3, the two object terms on lanes 4 / 5, the adaptive-threshold F / E on 6 / 7, weighted F
+    // on 8) and gathered by lane 0 in the order a single thread would have added them.
+    const unsigned full = 0xffffffffu;
     const double fsum = s_f[0], esum = s_e[0], fmx = s_fm[0], emx = s_em[0];
     const double* tot = s_tot;
     const double* q = s_q;
-    // ---- S-measure (alpha = 0.5)
-    double sm;
     const double mean_p = tot[7] / n;
-    if (n_fg == 0.0) {
-        sm = 1.0 - mean_p;
-    } else if (n_fg == n) {
-        sm = mean_p;
-    } else {
-        const double yv = n_fg / n;
-        const double so = yv * sod_s_object(tot[3], tot[4], n_fg) + (1.0 - yv) * sod_s_object(tot[5], tot[6], n - n_fg);
+    const bool mixed = n_fg != 0.0 && n_fg != n;
+    double piece = 0.0;
+    if (mixed && t < 4) {            // ---- S-measure, region term of quadrant t
+        const int k = t;
         int cx, cy;
         sod_centroid(tot, H, W, &cx, &cy);
         const double w1 = (double)cx * cy / n, w2 = (double)cy * (W - cx) / n, w3 = (double)(H - cy) * cx / n, w4 = 1.0 - w1 - w2 - w3;
-        const double wq[4] = {w1, w2, w3, w4};
-        const double nq[4] = {(double)cx * cy, (double)(W - cx) * cy, (double)cx * (H - cy), (double)(W - cx) * (H - cy)};
-        double sr = 0.0;
-        for (int k = 0; k < 4; ++k) {
-            const double nn = nq[k];
-            if (nn <= 0.0) continue;   // centroid on the last row / column: empty quadrant of weight 0
+        const double wk = k == 0 ? w1 : k == 1 ? w2 : k == 2 ? w3 : w4;
+        const double nn = k == 0 ? (double)cx * cy : k == 1 ? (double)(W - cx) * cy : k == 2 ? (double)cx * (H - cy) : (double)(W - cx) * (H - cy);
+        if (nn > 0.0) {              // centroid on the last row / column: empty quadrant of weight 0
             const double nm1 = fmax(nn - 1.0, 1.0);
             const double md = q[3 * k] / nn, x = shift[(size_t)b * 4 + k] + md, y = q[12 + k] / nn;
             const double sx = fmax((q[3 * k + 1] - nn * md * md) / nm1, 0.0);
@@ -577,30 +573,51 @@ __device__ __forceinline__ bool sod_finalize_body(const double* tot1, const doub
             } else {
                 score = beta == 0.0 ? 1.0 : 0.0;
             }
-            sr += wq[k] * score;
+            piece = wk * score;
         }
-        sm = fmax(0.0, 0.5 * so + 0.5 * sr);
+    } else if (mixed && t == 4) {    // ---- S-measure, object terms
+        piece = sod_s_object(tot[3], tot[4], n_fg);
+    } else if (mixed && t == 5) {
+        piece = sod_s_object(tot[5], tot[6], n - n_fg);
+    } else if (t == 6) {             // ---- adaptive threshold
+        piece = q[16] == 0.0 ? 0.0 : sod_f_from_counts(q[16], q[17], n_fg, beta2_f);
+    } else if (t == 7) {
+        piece = sod_e_from_counts(q[16], q[17], n_fg, n);
+    } else if (t == 8) {             // ---- weighted F (NaN when it was not asked for)
+        piece = p4 ? 0.0 : nan("");
+        if (p4 && n_fg > 0.0) {
+            const double ew_fg = s_wf[0], ew_bg = s_wf[1];
+            const double tpw = n_fg - ew_fg, fpw = ew_bg, r = 1.0 - ew_fg / n_fg, pw = tpw / (tpw + fpw + SOD_EPS);
+            piece = (1.0 + beta2_wf) * r * pw / (r + beta2_wf * pw + SOD_EPS);
+        }
     }
-    // ---- adaptive threshold
-    const double tpa = q[16], fpa = q[17];
-    const double fa = tpa == 0.0 ? 0.0 : sod_f_from_counts(tpa, fpa, n_fg, beta2_f);
-    const double ea = sod_e_from_counts(tpa, fpa, n_fg, n);
-    // ---- weighted F (NaN when it was not asked for)
-    double wf = p4 ? 0.0 : nan("");
-    if (p4 && n_fg > 0.0) {
-        const double ew_fg = s_wf[0], ew_bg = s_wf[1];
-        const double tpw = n_fg - ew_fg, fpw = ew_bg, r = 1.0 - ew_fg / n_fg, pw = tpw / (tpw + fpw + SOD_EPS);
-        wf = (1.0 + beta2_wf) * r * pw / (r + beta2_wf * pw + SOD_EPS);
+    double pc[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) pc[k] = __shfl_sync(full, piece, k);
+    if (t == 0) {
+        double sm;
+        if (n_fg == 0.0) {
+            sm = 1.0 - mean_p;
+        } else if (n_fg == n) {
+            sm = mean_p;
+        } else {
+            const double yv = n_fg / n;
+            const double so = yv * pc[4] + (1.0 - yv) * pc[5];
+            double sr = 0.0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) sr += pc[k];
+            sm = fmax(0.0, 0.5 * so + 0.5 * sr);
+        }
+        double* o = per_image + (size_t)b * SOD_KEYS;
+        o[0] = sm;
+        o[1] = pc[7];
+        o[2] = esum / 256.0;
+        o[3] = emx;
+        o[4] = pc[6];
+        o[5] = fsum / 256.0;
+        o[6] = fmx;
+        o[7] = pc[8];
     }
-    double* o = per_image + (size_t)b * SOD_KEYS;
-    o[0] = sm;
-    o[1] = ea;
-    o[2] = esum / 256.0;
-    o[3] = emx;
-    o[4] = fa;
-    o[5] = fsum / 256.0;
-    o[6] = fmx;
-    o[7] = wf;
     }
     // ---- the last image's block adds the batch up in image order: partial [16 + 512]
     __threadfence();
