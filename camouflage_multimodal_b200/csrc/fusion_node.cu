@@ -123,6 +123,13 @@ __device__ __forceinline__ void load_acc_bias_s(uint32_t taddr, int c0, float br
     for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) + __shfl_sync(0xffffffffu, breg, j);
 }
 
+// Measured and dropped: a node-pooled FFN.  The rg stream is used only through its mean over the image's nodes
+// (fusion_model.py:134) and the mean commutes with the FFN's second layer, so ph5 / ph7, the y epilogue and the 1 KB per node
+// of y can go: the y0 / hh epilogues add their columns up per image (warp transpose-reduce) and the KG-side tail applies W2 to
+// one 512-vector per image.  Built and measured (the parity suite was not run on it): this kernel 41.0 -> 37.6 us (the column sums cost ~0.35 us per 32-column
+// chunk, eating half of what the two GEMM phases and the 15.6 MB store saved), kg2rg_partial unchanged (it is latency-bound,
+// not bound by the y bytes it no longer read), kg_tail 40.6 -> 45.5 us (the GEMV and the block sums sit on its critical
+// path): nothing gained over the step, so the full FFN stayed.
 // Measured and dropped: four more warps (448 threads) for the two epilogues that only feed global memory (raw kg->rg scores,
 // V2), the softmax split over both halves.  The chain gets its accumulator halves back sooner, but the tile was slower both
 // with row-per-thread st.global in the side warps (26.5 -> 30.2 us) and with 16 KB staged tiles handed to TMA stores
