@@ -334,6 +334,10 @@ class HostPipeline:
                  label_dtype=torch.int32, packed_masks: bool = False, image_only: bool = False):
         pipes = list(pipe) if isinstance(pipe, (list, tuple)) else [pipe]
         self.pipes, self.dev = pipes, device
+        # One stream carries every host->device copy, in submission order: each batch crosses PCIe at the link's full rate and
+        # the batch that is needed first arrives first.  (With the copy on the slot's own stream the copies of several slots
+        # share the link and all of them finish late.)  CM_E2E_COPY_STREAM=0: the copy on the slot's stream.
+        self.copy_stream = torch.cuda.Stream(device) if os.environ.get("CM_E2E_COPY_STREAM", "1") != "0" else None
         self.pipe_done = [torch.cuda.Event() for _ in pipes]
         self.slots = []
         for k in range(slots):
@@ -344,8 +348,10 @@ class HostPipeline:
             if st.d_labels is not None:
                 st.d_labels.fill_(1)
             st.ev_done = torch.cuda.Event()
+            st.ev_copied, st.ev_consumed = torch.cuda.Event(), torch.cuda.Event()
             st.graph, st.out = pipes[st.pipe_idx].capture(st.d_images, st.d_labels, st.d_canny, st.d_gt) if use_graph else (None, None)
             st.ev_done.record(torch.cuda.current_stream(device))
+            st.ev_consumed.record(torch.cuda.current_stream(device))
             self.slots.append(st)
         for ev in self.pipe_done:
             ev.record(torch.cuda.current_stream(device))
@@ -364,7 +370,10 @@ class HostPipeline:
         the slot is reused ``len(slots)`` submissions later."""
         st = self.slots[i % len(self.slots)]
         pipe = self.pipes[st.pipe_idx]
-        with torch.cuda.stream(st.stream):
+        cs = self.copy_stream if self.copy_stream is not None else st.stream
+        with torch.cuda.stream(cs):
+            if cs is not st.stream:
+                cs.wait_event(st.ev_consumed)      # the slot's previous step has read its device inputs
             if isinstance(h_images, BatchBuffer):
                 st.d_batch.flat.copy_(h_images.flat, non_blocking=True)
             else:
@@ -373,6 +382,11 @@ class HostPipeline:
                     st.d_labels.copy_(h_labels, non_blocking=True)
                     st.d_canny.copy_(h_canny, non_blocking=True)
                 st.d_gt.copy_(h_gt, non_blocking=True)
+            if cs is not st.stream:
+                st.ev_copied.record(cs)
+        with torch.cuda.stream(st.stream):
+            if cs is not st.stream:
+                st.stream.wait_event(st.ev_copied)
             st.stream.wait_event(self.pipe_done[st.pipe_idx])     # another slot may be using this pipeline's buffers
             if st.graph is not None:
                 st.graph.replay()
@@ -385,6 +399,7 @@ class HostPipeline:
             if out["per_image_sod"] is not None:
                 st.h_per_image_sod.copy_(out["per_image_sod"], non_blocking=True)
             self.pipe_done[st.pipe_idx].record(st.stream)
+            st.ev_consumed.record(st.stream)
             st.ev_done.record(st.stream)
         return st
 
