@@ -559,6 +559,23 @@ def b200_arm(args):
     pe1.record()
     torch.cuda.synchronize()
     h2d_probe_gbs = 20 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+
+    # the same copy rate with the device busy: rotating over every host buffer of the pool on a copy stream while the
+    # device-resident steps run on the lane streams (on some boxes of the pool copies slow down under compute; e2e follows)
+    cstream = torch.cuda.Stream(dev)
+    fork()
+    for s in range(4 * n_pool):
+        step(s)
+    with torch.cuda.stream(cstream):
+        pe0.record(cstream)
+        for j in range(20):
+            probe_d.copy_(host_pool[j % n_pool].flat, non_blocking=True)
+        pe1.record(cstream)
+    for s in range(8 * n_pool):
+        step(s)
+    join()
+    torch.cuda.synchronize()
+    h2d_probe_busy_gbs = 20 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
     del probe_d
 
     for s in range(n_prewarm + args.warmup):
@@ -679,6 +696,8 @@ def b200_arm(args):
                     "d2h_bytes_per_step": stager.d2h_bytes, "repeats": len(e2e_s), "value_min": e2e_min, "value_max": e2e_max,
                     "timed_window_ms": 1e3 * sum(e2e_s), "h2d_probe_gbs": h2d_probe_gbs,
                     "host_submit_us_per_step": 1e6 * statistics.median(submit_s) / args.steps,
+                    "ingest": stager.ingest, "ingest_calibration_steps_per_s": stager.ingest_rates,
+                    "h2d_probe_busy_gbs": h2d_probe_busy_gbs,
                     "host_format": ("uint8 RGB + int16 labels + 1-bit canny + 1-bit gt (binary masks bit-packed on the host, "
                                     "cm_unpack_bits on the device): 5.25 B/pixel" if not args.byte_masks else
                                     "uint8 RGB + int16 labels + uint8 canny + uint8 gt: 7 B/pixel") if args.input == "u8" else "float32 / int32 form",

@@ -155,6 +155,22 @@ __global__ void unpack_bits_kernel(const uint8_t* __restrict__ bits, long long n
     reinterpret_cast<uint2*>(out)[i] = v;
 }
 
+// Host -> device staging by the SMs: `src` is pinned host memory the device can address (cudaHostAlloc under unified
+// addressing), read with 16-byte loads, eight per thread in flight, by a fixed small grid -- the copy is then a node of
+// the captured step like any other kernel: no copy-engine channel to schedule next to the compute channels, no extra call.
+__global__ void __launch_bounds__(256) ingest_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, long long n16) {
+    const long long stride = (long long)gridDim.x * 256;
+    long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    for (; i + 7 * stride < n16; i += 8 * stride) {
+        uint4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = __ldcv(src + i + u * stride);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) dst[i + u * stride] = v[u];
+    }
+    for (; i < n16; i += stride) dst[i] = __ldcv(src + i);
+}
+
 static int metric_chunks(long long pixels, int batch) {
     // about four CTAs per SM over the whole batch, at least 1 per image, at most one per 256 pixels
     long long want = (4LL * num_sms() + batch - 1) / batch;
@@ -201,6 +217,19 @@ extern "C" int cm_unpack_bits(const uint8_t* bits, int64_t n_bytes, int one_valu
         unpack_bits_kernel<<<ceil_div(n_bytes, 256), 256, 0, as_stream(stream)>>>(bits, n_bytes, (unsigned)one_value, out);
     }
     return post_launch("cm_unpack_bits");
+}
+
+extern "C" int cm_ingest_copy(const void* host_src, void* dst, int64_t n_bytes, int ctas, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(host_src && dst && n_bytes > 0 && n_bytes % 16 == 0, "cm_ingest_copy: NULL pointer or a size that is not a multiple of 16");
+    CM_REQUIRE(((reinterpret_cast<uintptr_t>(host_src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0, "cm_ingest_copy: pointers must be 16-byte aligned");
+    if (ctas <= 0) ctas = 32;
+    {
+        CM_TIMED("ingest_copy", as_stream(stream));
+        ingest_copy_kernel<<<ctas, 256, 0, as_stream(stream)>>>(reinterpret_cast<const uint4*>(host_src), reinterpret_cast<uint4*>(dst), n_bytes / 16);
+    }
+    return post_launch("cm_ingest_copy");
 }
 
 extern "C" int cm_metrics_dense(const float* pred, const float* gt, int batch, int64_t pixels, float threshold,

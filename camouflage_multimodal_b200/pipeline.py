@@ -331,7 +331,12 @@ class HostPipeline:
     kernels, slots sharing a pipeline are serialised through ``pipe_done`` events (they share its buffers)."""
 
     def __init__(self, pipe, B, H, W, device, slots: int = 2, use_graph: bool = True, image_dtype=torch.float32,
-                 label_dtype=torch.int32, packed_masks: bool = False, image_only: bool = False):
+                 label_dtype=torch.int32, packed_masks: bool = False, image_only: bool = False, ingest: str | None = None):
+        """``ingest``: how a ``BatchBuffer`` crosses PCIe -- ``"ce"`` (cudaMemcpyAsync: a copy engine), ``"sm"``
+        (``cm_ingest_copy``: a 64-block kernel reading the pinned buffer) or ``"auto"`` (default; env ``CM_E2E_INGEST``): both are
+        timed at construction on this machine, under the load of the slots' own captured steps, and the faster one is kept.  A
+        copy engine is the faster path on an idle link (53 against 47 GB/s here), but on some machines its copies fall to
+        two thirds of that while kernels run, and the kernel path does not (``tools/ingest_probe.py``)."""
         pipes = list(pipe) if isinstance(pipe, (list, tuple)) else [pipe]
         self.pipes, self.dev = pipes, device
         # One stream carries every host->device copy, in submission order: each batch crosses PCIe at the link's full rate and
@@ -356,6 +361,51 @@ class HostPipeline:
         for ev in self.pipe_done:
             ev.record(torch.cuda.current_stream(device))
         self.h2d_bytes, self.d2h_bytes = self.slots[0].h2d_bytes, self.slots[0].d2h_bytes
+        ingest = ingest or os.environ.get("CM_E2E_INGEST", "auto")
+        if ingest not in ("ce", "sm", "auto"):
+            raise ValueError("ingest must be 'ce', 'sm' or 'auto'")
+        flat = self.slots[0].d_batch.flat
+        sm_ok = flat.numel() % 16 == 0 and flat.data_ptr() % 16 == 0 and self.slots[0].h_batch.flat.data_ptr() % 16 == 0
+        self.ingest_rates = None
+        if ingest == "auto":
+            ingest = self._calibrate() if (sm_ok and use_graph) else "ce"
+        self.ingest = ingest if sm_ok else "ce"
+
+    def _stage(self, stream, h_flat, d_flat, mode):
+        """Queue the host -> device transfer of one flat batch on ``stream`` (current stream = ``stream``)."""
+        if mode == "sm":
+            lib = _lib.load()
+            _lib.check(lib.cm_ingest_copy(h_flat.data_ptr(), _lib.ptr(d_flat), d_flat.numel(), 64, _lib.stream_ptr(self.dev)), "cm_ingest_copy")
+        else:
+            d_flat.copy_(h_flat, non_blocking=True)
+
+    def _calibrate(self, rounds: int = 3) -> str:
+        """Time ``rounds * slots`` end-to-end submissions with each transfer mode.  The transfers land in a scratch buffer, so
+        the slots' device inputs (valid data from the capture) are not disturbed while their captured steps run as the load."""
+        import time
+        scratch = torch.empty_like(self.slots[0].d_batch.flat)
+        rates = {}
+        for mode in ("ce", "sm", "ce", "sm"):
+            torch.cuda.synchronize(self.dev)
+            t0 = time.perf_counter()
+            for i in range(rounds * len(self.slots)):
+                st = self.slots[i % len(self.slots)]
+                cs = self.copy_stream if self.copy_stream is not None else st.stream
+                with torch.cuda.stream(cs):
+                    cs.wait_event(st.ev_consumed)
+                    self._stage(cs, st.h_batch.flat, scratch, mode)
+                    st.ev_copied.record(cs)
+                with torch.cuda.stream(st.stream):
+                    st.stream.wait_event(st.ev_copied)
+                    st.stream.wait_event(self.pipe_done[st.pipe_idx])
+                    st.graph.replay()
+                    self.pipe_done[st.pipe_idx].record(st.stream)
+                    st.ev_consumed.record(st.stream)
+                    st.ev_done.record(st.stream)
+            torch.cuda.synchronize(self.dev)
+            rates[mode] = max(rates.get(mode, 0.0), rounds * len(self.slots) / (time.perf_counter() - t0))   # steps / s, best of two
+        self.ingest_rates = rates
+        return "sm" if rates["sm"] > 1.10 * rates["ce"] else "ce"
 
     def host_batch(self) -> BatchBuffer:
         """A pinned host batch in the layout of the device slots: fill its ``images / labels / canny / gt`` views (e.g.
@@ -375,7 +425,7 @@ class HostPipeline:
             if cs is not st.stream:
                 cs.wait_event(st.ev_consumed)      # the slot's previous step has read its device inputs
             if isinstance(h_images, BatchBuffer):
-                st.d_batch.flat.copy_(h_images.flat, non_blocking=True)
+                self._stage(cs, h_images.flat, st.d_batch.flat, self.ingest if h_images.flat.data_ptr() % 16 == 0 else "ce")
             else:
                 st.d_images.copy_(h_images, non_blocking=True)
                 if st.d_labels is not None:

@@ -340,6 +340,11 @@ int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int batch, int h,
  * per pixel of the host -> device transfer; packed they are 0.25): bit i of byte j (little-endian bit order,
  * numpy.packbits(bitorder="little")) -> out[8 j + i] = one_value or 0.  out 8-byte aligned, 8 * n_bytes bytes. */
 int cm_unpack_bits(const uint8_t* bits, int64_t n_bytes, int one_value, uint8_t* out, void* stream);
+/* Host -> device staging of a batch by a kernel instead of a copy engine (the front end's hand-over; the
+ * reference's `.to(device)`, models/multimodal/test_multimodal.py:96-99): host_src is PINNED host memory (cudaHostAlloc /
+ * torch pin_memory: device-addressable under unified addressing), n_bytes a multiple of 16, both pointers 16-byte aligned;
+ * `ctas` blocks of 256 threads (<= 0: 32) read it with 16-byte loads.  Being a kernel it can sit inside a captured step. */
+int cm_ingest_copy(const void* host_src, void* dst, int64_t n_bytes, int ctas, void* stream);
 /* Same reductions for a caller-supplied float prediction and float ground truth (the literal signature of
  * utils/metrics.py:evaluate_segmentation: two arrays, one threshold). */
 int cm_metrics_dense(const float* pred, const float* gt, int batch, int64_t pixels, float threshold,
