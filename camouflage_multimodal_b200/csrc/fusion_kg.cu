@@ -344,53 +344,83 @@ __global__ void __cluster_dims__(KT_CL, 1, 1) __launch_bounds__(KT_THREADS) kg_t
     for (int r = 0; r < KT_CL; ++r) peer[r] = cluster.map_shared_rank(&sm, r);
     const int K = a.n_kg, gs = a.gs, heads = a.heads, n_chunks = KG_MAX_CHUNKS;
     const int n0 = a.node_ptr[b], nb = a.node_ptr[b + 1] - n0;
-    const int per = ((nb + n_chunks - 1) / n_chunks + KG_SUB - 1) / KG_SUB * KG_SUB;
-    const int nch = nb > 0 ? (nb + per - 1) / per : 0;
-    const size_t slot0 = (size_t)b * n_chunks;
-    // ---- merge statistics of the chunk partials per folded key slot (every CTA: 128 threads, 2 x 16 loads)
+    // the image's partials: slots slot0 .. slot0 + nch - 1
+    size_t slot0;
+    int nch;
+    if (a.tile_partials) {
+        slot0 = (size_t)(n0 >> 7) + b;
+        nch = nb > 0 ? ((n0 + nb - 1) >> 7) - (n0 >> 7) + 1 : 0;
+    } else {
+        const int per = ((nb + n_chunks - 1) / n_chunks + KG_SUB - 1) / KG_SUB * KG_SUB;
+        slot0 = (size_t)b * n_chunks;
+        nch = nb > 0 ? (nb + per - 1) / per : 0;
+    }
+    // ---- merge statistics of the partials per folded key slot (every CTA: 128 threads); groups of KG_MAX_CHUNKS partials,
+    // one group unless an image spans more than 16 tiles
+    float M = -INFINITY, inv = 0.f;
     if (tid < 128) {
-        float pm[KG_MAX_CHUNKS], pl[KG_MAX_CHUNKS];
+        for (int g0 = 0; g0 < nch; g0 += KG_MAX_CHUNKS) {
+            float pm[KG_MAX_CHUNKS];
 #pragma unroll
-        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) {
-            pm[ch] = ch < nch ? a.part_m[(slot0 + ch) * 128 + tid] : -INFINITY;
-            pl[ch] = ch < nch ? a.part_l[(slot0 + ch) * 128 + tid] : 0.f;
+            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) pm[ch] = g0 + ch < nch ? a.part_m[(slot0 + g0 + ch) * 128 + tid] : -INFINITY;
+#pragma unroll
+            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) M = fmaxf(M, pm[ch]);
         }
-        float M = -INFINITY;
-#pragma unroll
-        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) M = fmaxf(M, pm[ch]);
         float L = 0.f;
+        for (int g0 = 0; g0 < nch; g0 += KG_MAX_CHUNKS) {
+            float pm[KG_MAX_CHUNKS], pl[KG_MAX_CHUNKS];
 #pragma unroll
-        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch)
-            if (ch < nch) L += pl[ch] * expf(pm[ch] - M);
-        const float inv = L > 0.f ? 1.0f / L : 0.f;
+            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) {
+                pm[ch] = g0 + ch < nch ? a.part_m[(slot0 + g0 + ch) * 128 + tid] : -INFINITY;
+                pl[ch] = g0 + ch < nch ? a.part_l[(slot0 + g0 + ch) * 128 + tid] : 0.f;
+            }
 #pragma unroll
-        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) sm.sc[ch * 128 + tid] = ch < nch ? expf(pm[ch] - M) * inv : 0.f;
+            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch)
+                if (g0 + ch < nch) L += pl[ch] * expf(pm[ch] - M);
+        }
+        inv = L > 0.f ? 1.0f / L : 0.f;
         if (a.stat && q == 0) {
             a.stat[((size_t)b * 128 + tid) * 2] = M;
             a.stat[((size_t)b * 128 + tid) * 2 + 1] = inv;
         }
     }
-    __syncthreads();
     cluster.sync();   // every CTA of the cluster is running before the first write into a peer's shared memory
     // ---- this CTA's 64 columns of ctx2 [16, 256] (rows >= K zero) as fp16 hi / lo, broadcast; its columns of mean_n y
     const int hd = D / heads;
-    for (int i = tid; i < 16 * (QD / 2); i += nt) {
-        const int k = i / (QD / 2), c = q * QD + (i - k * (QD / 2)) * 2;
-        float s0 = 0.f, s1 = 0.f;
-        if (k < K) {
-            const int j = (c / hd) * gs + k;   // c and c + 1 lie in the same head (hd is even)
-            float2 pv[KG_MAX_CHUNKS];
+    constexpr int ITEMS = 16 * (QD / 2) / KT_THREADS;   // (row, column pair) items per thread
+    float s0[ITEMS], s1[ITEMS];
+#pragma unroll
+    for (int it = 0; it < ITEMS; ++it) s0[it] = s1[it] = 0.f;
+    for (int g0 = 0; g0 < nch || g0 == 0; g0 += KG_MAX_CHUNKS) {
+        if (g0 > 0) __syncthreads();              // the previous group's factors have been consumed
+        if (tid < 128) {
 #pragma unroll
             for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch)
-                pv[ch] = ch < nch ? *reinterpret_cast<const float2*>(a.part_acc + ((slot0 + ch) * gs + k) * D + c) : make_float2(0.f, 0.f);
+                sm.sc[ch * 128 + tid] = g0 + ch < nch ? expf(a.part_m[(slot0 + g0 + ch) * 128 + tid] - M) * inv : 0.f;
+        }
+        __syncthreads();
 #pragma unroll
-            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) {
-                s0 = fmaf(sm.sc[ch * 128 + j], pv[ch].x, s0);
-                s1 = fmaf(sm.sc[ch * 128 + j], pv[ch].y, s1);
+        for (int it = 0; it < ITEMS; ++it) {
+            const int i = tid + it * KT_THREADS, k = i / (QD / 2), c = q * QD + (i - k * (QD / 2)) * 2;
+            if (k < K) {
+                const int jj = (c / hd) * gs + k;   // c and c + 1 lie in the same head (hd is even)
+                float2 pv[KG_MAX_CHUNKS];
+#pragma unroll
+                for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch)
+                    pv[ch] = g0 + ch < nch ? *reinterpret_cast<const float2*>(a.part_acc + ((slot0 + g0 + ch) * gs + k) * D + c) : make_float2(0.f, 0.f);
+#pragma unroll
+                for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) {
+                    s0[it] = fmaf(sm.sc[ch * 128 + jj], pv[ch].x, s0[it]);
+                    s1[it] = fmaf(sm.sc[ch * 128 + jj], pv[ch].y, s1[it]);
+                }
             }
         }
+    }
+#pragma unroll
+    for (int it = 0; it < ITEMS; ++it) {
+        const int i = tid + it * KT_THREADS, k = i / (QD / 2), c = q * QD + (i - k * (QD / 2)) * 2;
         __half2 hi, lo;
-        split2(s0, s1, &hi, &lo);
+        split2(s0[it], s1[it], &hi, &lo);
 #pragma unroll
         for (int r = 0; r < KT_CL; ++r) {
             *reinterpret_cast<__half2*>(peer[r]->a_hi + k * KT_LDA + c) = hi;
@@ -400,8 +430,13 @@ __global__ void __cluster_dims__(KT_CL, 1, 1) __launch_bounds__(KT_THREADS) kg_t
     if (tid < QD) {
         const int c = q * QD + tid;
         float s = 0.f;
+        for (int g0 = 0; g0 < nch; g0 += KG_MAX_CHUNKS) {
+            float pv[KG_MAX_CHUNKS];
 #pragma unroll
-        for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) s += ch < nch ? a.part_y[(slot0 + ch) * D + c] : 0.f;
+            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) pv[ch] = g0 + ch < nch ? a.part_y[(slot0 + g0 + ch) * D + c] : 0.f;
+#pragma unroll
+            for (int ch = 0; ch < KG_MAX_CHUNKS; ++ch) s += pv[ch];
+        }
         s = nb > 0 ? s / (float)nb : 0.f;
 #pragma unroll
         for (int r = 0; r < KT_CL; ++r) peer[r]->both[c] = s;

@@ -10,6 +10,18 @@
 //   ph6  hh1 = relu(y0 W1[256:512]^T + b1)                                       -> A3
 //   ph7  Y  += hh1 W2[:,256:512]^T;  y = Y + b2 + y0                             -> global fp32 (mean over nodes follows)
 //
+// MODE 2 (the evaluation path when no kg->rg attention map is asked for): the KG side needs the node rows only through sums
+// over each image's nodes -- the flash-style partials of the kg->rg attention (per folded key slot: max, sum of exp, sum of
+// exp x V2) and the column sums of y -- so the tile reduces them itself and S2 / V2 / y never reach global memory (31 MB per
+// batch of 32 written here and read back by kg2rg_partial, which disappears):
+//   epi1, upper half  raw kg->rg scores -> column maxima of the tile (warp butterfly + 4-warp combine) -> E = exp(s - max) as
+//                     fp16 [128 x 128] in the (dead) x tile, sum of E per slot and image -> part_m / part_l
+//   after epi3        V2 (still in T0) -> fp16 [128 x 128] halves in the (dead) P1 tile; thread (slot octet, column) adds
+//                     E[n, slot] V2[n, column] up over the rows of each image -> part_acc            (T0 is then released to ph4)
+//   epi7              y -> fp32 tile in the (dead) hh / weight-ring space -> column sums per image -> part_y
+// Partials are indexed by tile + image (rows are sorted by image, so (tile, image) pairs form a staircase and the sum is a
+// unique slot); the KG-side tail merges the slots of an image.
+//
 // Every GEMM is 128 x 256 x K on tcgen05 (fp16 operands, fp32 accumulators in the two 256-column halves T0 / T1 of
 // TMEM), its weight tiles [256 x 64] streamed through a 3-stage TMA ring; the epilogue of phase i (8 warps, one
 // TMEM lane = one node row per thread) overlaps the MMAs of the phases that do not depend on it.
@@ -28,7 +40,8 @@ namespace cm {
 constexpr int FN_THREADS = 320, FN_EPI_THREADS = 256, FN_STAGES = 3, FN_PHASES = 8;
 constexpr int FN_A1 = 0, FN_A3 = 65536, FN_X = FN_A3, FN_P1 = FN_A3 + 32768, FN_RING = 131072, FN_STAGE_BYTES = 32768;
 constexpr int FN_BAR = FN_RING + FN_STAGES * FN_STAGE_BYTES;   // 229376
-constexpr int FN_SMEM = FN_BAR + 256 + 1024;                   // + barriers, + 1 KB alignment slack
+constexpr int FN_SCR = FN_BAR + 256;                           // MODE 2: tile maxima [128] f32 + image of every row [128] i32
+constexpr int FN_SMEM = FN_BAR + 256 + 1024 + 1024;            // + barriers, + scratch, + 1 KB alignment slack
 constexpr int FN_KB_TILE = 128 * 64 * 2;                       // one [128 x 64] fp16 k-block of an activation tile
 
 // GEMM schedule: A operand (smem offset, k-blocks), weight map index + K offset, TMEM column half, accumulate,
@@ -36,7 +49,7 @@ constexpr int FN_KB_TILE = 128 * 64 * 2;                       // one [128 x 64]
 struct FnPhase {
     int a_off, a_kb, wmap, w_row0, w_k0, tmem_col, accumulate, wait_epi;
 };
-__constant__ FnPhase fn_phases[2][FN_PHASES] = {
+__constant__ FnPhase fn_phases[3][FN_PHASES] = {
     {
         // MODE 0: region-node chain
         {FN_X, 2, 1, 0, 0, 0, 0, -1},      // r
@@ -56,6 +69,17 @@ __constant__ FnPhase fn_phases[2][FN_PHASES] = {
         {FN_A1, 4, 2, 256, 0, 0, 0, 1},    // hh1           (T0 drained by epi1)
         {FN_A3, 4, 3, 0, 256, 256, 1, 3},  // Y += hh1 ...  (A3 = hh1 after epi3)
         {0, 0, 0, 0, 0, 0, 0, -1}, {0, 0, 0, 0, 0, 0, 0, -1}, {0, 0, 0, 0, 0, 0, 0, -1},
+    },
+    {
+        // MODE 2: the region-node chain again (ph4 additionally waits for V2 to leave T0: epi_done[2])
+        {FN_X, 2, 1, 0, 0, 0, 0, -1},
+        {FN_A1, 4, 2, 0, 0, 256, 0, 0},
+        {FN_A1, 4, 3, 0, 0, 0, 0, 0},
+        {FN_P1, 2, 4, 0, 0, 256, 0, 1},
+        {FN_A1, 4, 5, 0, 0, 0, 0, 3},
+        {FN_A3, 4, 6, 0, 0, 256, 0, 4},
+        {FN_A1, 4, 5, 256, 0, 0, 0, 4},
+        {FN_A3, 4, 6, 0, 256, 256, 1, 6},
     },
 };
 
@@ -123,6 +147,35 @@ __device__ __forceinline__ void load_acc_bias_s(uint32_t taddr, int c0, float br
     for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) + __shfl_sync(0xffffffffu, breg, j);
 }
 
+// MODE 2 helpers.  Butterfly transpose-reduce over the warp's 32 rows (one row per lane, v = 32 consecutive columns of it):
+// lane j ends up with column j's maximum / sum; 31 shuffles, fixed order.
+template <bool MAX>
+__device__ __forceinline__ float warp_col_reduce(float (&v)[32], int lane) {
+    const unsigned full = 0xffffffffu;
+#pragma unroll
+    for (int w = 16; w >= 1; w >>= 1) {
+        const bool up = (lane & w) != 0;
+#pragma unroll
+        for (int i = 0; i < w; ++i) {
+            const float send = up ? v[i] : v[i + w], keep = up ? v[i + w] : v[i], got = __shfl_xor_sync(full, send, w);
+            v[i] = MAX ? fmaxf(keep, got) : keep + got;
+        }
+    }
+    return v[0];
+}
+// [128 rows x 128 columns] fp16 tile, 256 bytes per row, the 16-byte chunk index XORed with row % 16: row-per-lane 16-byte
+// stores and column-per-lane 2-byte loads are both free of bank conflicts
+__device__ __forceinline__ uint32_t kgt_off(int row, int chunk) { return (uint32_t)(row * 256 + ((chunk ^ (row & 15)) << 4)); }
+
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t (&r)[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma16816_f16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
 // Measured and dropped: a node-pooled FFN.  The rg stream is used only through its mean over the image's nodes
 // (fusion_model.py:134) and the mean commutes with the FFN's second layer, so ph5 / ph7, the y epilogue and the 1 KB per node
 // of y can go: the y0 / hh epilogues add their columns up per image (warp transpose-reduce) and the KG-side tail applies W2 to
@@ -140,7 +193,7 @@ __device__ __forceinline__ void load_acc_bias_s(uint32_t taddr, int c0, float br
 // sub-partition), and the spills cost more than the hidden latency (43 -> 58 us).
 template <int MODE>
 __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid_constant__ FusionNodeArgs a) {
-    constexpr int NPH = MODE == 0 ? 8 : 5, XKB = MODE == 0 ? 2 : 4;
+    constexpr int NPH = MODE == 1 ? 5 : 8, XKB = MODE == 1 ? 4 : 2;
     extern __shared__ uint8_t smem_raw[];
     if (a.dbg && threadIdx.x == 0) {   // every CTA: first instruction / last (the buffer holds 40 + 2 x grid stamps)
         long long t;
@@ -165,7 +218,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             mbar_init(w_full + s, 1);
             mbar_init(w_empty + s, 1);
         }
-        mbar_init(x_full, (MODE == 0 && a.x32) ? 8 : 1);   // one TMA transaction, or one arrival per converting warp
+        mbar_init(x_full, (MODE != 1 && a.x32) ? 8 : 1);   // one TMA transaction, or one arrival per converting warp
         for (int i = 0; i < FN_PHASES; ++i) {
             mbar_init(acc_ready + i, 1);
             mbar_init(epi_done + i, 8);   // one arrival per epilogue warp
@@ -183,7 +236,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         auto pf = [&](const float* v, int n_floats) {
             if (v && t * 32 < n_floats) asm volatile("prefetch.global.L1 [%0];" ::"l"(v + t * 32));
         };
-        if (MODE == 0) {
+        if (MODE != 1) {
             pf(a.b_rgproj, 256);
             pf(a.ccat, 256);
             pf(a.b_v2, 256);
@@ -209,7 +262,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
     if (warp == 0) {
         // ------------------------------------------------------------------------------ TMA producer
         if (lane == 0) {
-            if (!(MODE == 0 && a.x32)) {
+            if (!(MODE != 1 && a.x32)) {
                 mbar_expect_tx(x_full, XKB * FN_KB_TILE);
                 for (int kb = 0; kb < XKB; ++kb) tma_load_2d(smem + FN_X + kb * FN_KB_TILE, &a.maps[0], x_full, kb * 64, m0);
             }
@@ -235,6 +288,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
                 if (stamp) a.dbg[ph] = now();
                 if (ph == 0) mbar_wait(x_full, 0);
                 else if (p.wait_epi >= 0) mbar_wait(epi_done + p.wait_epi, 0);
+                if (MODE == 2 && ph == 4) mbar_wait(epi_done + 2, 0);   // V2 has left T0 (it stays there until the kg->rg pass)
                 tc_fence_after();
                 if (stamp) a.dbg[8 + ph] = now();
                 for (int kb = 0; kb < p.a_kb; ++kb, ++t) {
@@ -273,7 +327,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         };
         float x[32];
 
-        if (MODE == 0 && a.x32) {
+        if (MODE != 1 && a.x32) {
             // fp32 rows -> fp16 A operand of phase 0 (SWIZZLE_128B, two 64-column K blocks): coalesced 16-byte loads,
             // eight in flight per thread, 8-byte shared-memory stores
             const int et = threadIdx.x - 64;
@@ -298,6 +352,34 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(x_full);
+        }
+
+        // MODE 2: the image of this thread's row (node_ptr[bi] <= row < node_ptr[bi + 1]; -1 past the end) for every thread of the
+        // CTA to see.  Images hold about the same number of nodes, so the proportional guess is right or one off: two loads
+        // instead of a bisection's dependent chain.
+        const int nlive = min(128, m_live - m0);   // live rows of the tile (>= 1)
+        float* s_m = reinterpret_cast<float*>(smem + FN_SCR);
+        int* s_img = reinterpret_cast<int*>(smem + FN_SCR + 512);
+        auto epi_sync = [] { asm volatile("bar.sync 1, %0;" ::"n"(FN_EPI_THREADS) : "memory"); };
+        if (MODE == 2) {
+            if (half == 0) {
+                int bi = -1;
+                if (row_ok) {
+                    int b = min(__float2int_rz((float)row * (float)a.n_graphs / (float)m_live), a.n_graphs - 1);
+                    int lo = a.node_ptr[b], hi = a.node_ptr[b + 1];
+                    while (lo > row) {
+                        hi = lo;
+                        lo = a.node_ptr[--b];
+                    }
+                    while (hi <= row) {
+                        lo = hi;
+                        hi = a.node_ptr[++b + 1];
+                    }
+                    bi = b;
+                }
+                s_img[lrow] = bi;
+            }
+            epi_sync();
         }
 
         // y0 = LN(acc + bias + residual) -> A1.  Residual: A1 itself (in place: each thread re-reads and rewrites only
@@ -332,7 +414,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
                     s2 = fmaf(x[j], x[j], s2);
                 }
             }
-            float2* stat = reinterpret_cast<float2*>(smem + FN_X);
+            float2* stat = reinterpret_cast<float2*>(smem + (MODE == 2 ? FN_P1 : FN_X));   // MODE 2: the x tile holds E; P1 is dead after acc_ready[ph]
             stat[half * 128 + lrow] = make_float2(s1, s2);
             asm volatile("bar.sync 1, %0;" ::"n"(FN_EPI_THREADS) : "memory");
             const float2 o = stat[(half ^ 1) * 128 + lrow];
@@ -376,6 +458,37 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
                 }
             }
         };
+        // MODE 2: y = Y + b2 + A1 -> fp32 tile [128][260] over the dead hh buffer + weight ring -> column sums per image
+        auto epi_final_sum = [&](int ph) {
+            const VecSlice bs = vec_slice(a.b_ffn2, half * 32, 64, lane);
+            wait_acc(ph);
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load_acc_bias_s(t1, c0, bs.r[c0 >> 6], x);
+                add_chunk_smem(sbase + FN_A1, lrow, c0, x);
+#pragma unroll
+                for (int j = 0; j < 32; j += 4)
+                    st_smem_v4(sbase + FN_A3 + (uint32_t)(lrow * 260 + c0 + j) * 4,
+                               make_uint4(__float_as_uint(x[j]), __float_as_uint(x[j + 1]), __float_as_uint(x[j + 2]), __float_as_uint(x[j + 3])));
+            }
+            epi_sync();
+            const float* yt = reinterpret_cast<const float*>(smem + FN_A3);
+            const int c = threadIdx.x - 64;
+            for (int b = s_img[0]; b <= s_img[nlive - 1]; ++b) {
+                const int lo = max(a.node_ptr[b] - m0, 0), hi = min(a.node_ptr[b + 1] - m0, nlive);
+                if (hi <= lo) continue;
+                float s4[4] = {0.f, 0.f, 0.f, 0.f};   // rows n with n % 4 == u, then combined in a fixed order
+                int n = lo;
+                for (; n + 8 <= hi; n += 8) {
+                    float v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) v[u] = yt[(n + u) * 260 + c];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) s4[u & 3] += v[u];
+                }
+                for (; n < hi; ++n) s4[(n - lo) & 3] += yt[n * 260 + c];
+                a.part_y[(size_t)(blockIdx.x + b) * 256 + c] = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+            }
+        };
 
         if (MODE == 1) {
             epi_ln(0, t1, a.b_out1, a.res_rows);
@@ -393,9 +506,61 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         done(0);
 
         // ---- epi1: half 0 -> P1 = per-head softmax of the rg->kg scores (A2); half 1 -> raw kg->rg scores (global)
-        const VecSlice c1s = vec_slice(a.ccat, half * 128, 32, lane);
-        wait_acc(1);
-        {
+        if (MODE == 2) {
+            // Each half takes two of the four 32-column chunks of BOTH score blocks: the softmax of the rg->kg scores -> P1, and
+            // the raw kg->rg scores -> flash-style partial statistics (nothing of them leaves the SM but 1 KB per image).
+            float cs[2], ce[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                cs[u] = __ldg(a.ccat + 64 * half + 32 * u + lane);
+                ce[u] = __ldg(a.ccat + 128 + 64 * half + 32 * u + lane);
+            }
+            wait_acc(1);
+            float am[32];   // unused head means (the rg->kg attention map is not produced in this mode)
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int c0 = 64 * half + 32 * u;
+                load_acc_bias_s(t1, c0, cs[u], x);
+                if (a.sm_gs == 16) softmax_groups<16, false>(x, a.sm_valid, am); else softmax_groups<32, false>(x, a.sm_valid, am);
+                store_chunk_smem(sbase + FN_P1, lrow, c0, x);
+            }
+            if (stamp && threadIdx.x == 64) a.dbg[33] = now();
+            auto kg_sync = [&] {   // the four warps of this half
+                if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory"); else asm volatile("bar.sync 3, 128;" ::: "memory");
+            };
+            float* cm = reinterpret_cast<float*>(smem + FN_X);     // [4 warps][128] column maxima (E goes over them below)
+#pragma unroll 1
+            for (int u = 0; u < 2; ++u) {
+                load_acc_bias_s(t1, 128 + 64 * half + 32 * u, ce[u], x);
+                if (!row_ok) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) x[j] = -INFINITY;
+                }
+                cm[q * 128 + 64 * half + 32 * u + lane] = warp_col_reduce<true>(x, lane);
+            }
+            kg_sync();
+            const int sj = 64 * half + (lrow & 63);   // threads lrow < 64 of the half: one slot each
+            float mj = 0.f;
+            if (lrow < 64) mj = fmaxf(fmaxf(cm[sj], cm[128 + sj]), fmaxf(cm[256 + sj], cm[384 + sj]));   // finite: row 0 of a tile is live
+            epi_sync();                                  // both halves are done with cm: E goes over it
+            if (lrow < 64) s_m[sj] = mj;
+            kg_sync();
+#pragma unroll 1
+            for (int u = 0; u < 2; ++u) {
+                const int i = 2 * half + u;
+                load_acc_bias_s(t1, 128 + 32 * i, ce[u], x);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) x[j] = row_ok ? __expf(x[j] - s_m[32 * i + j]) : 0.f;
+#pragma unroll
+                for (int v = 0; v < 4; ++v) st_smem_v4(sbase + FN_X + kgt_off(lrow, 4 * i + v), pack8(x + 8 * v));
+            }
+            // the tile's maxima for every image that has rows in the tile (the sums of E come out of the product pass below)
+            if (lrow < 64)
+                for (int b = s_img[0]; b <= s_img[nlive - 1]; ++b) a.part_m[(size_t)(blockIdx.x + b) * 128 + sj] = mj;
+            if (stamp && threadIdx.x == 192) a.dbg[34] = now();
+        } else {
+            const VecSlice c1s = vec_slice(a.ccat, half * 128, 32, lane);
+            wait_acc(1);
             float am[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) am[j] = 0.f;
@@ -428,23 +593,96 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         }
         done(1);
 
-        // ---- epi2: V2 -> global fp16
-        const VecSlice b2s = vec_slice(a.b_v2, half * 32, 64, lane);
-        wait_acc(2);
-        for (int c0 = half * 32; c0 < 256; c0 += 64) {
-            load_acc_bias_s(t0, c0, b2s.r[c0 >> 6], x);
-            if (row_ok) {
-                op_t* o = a.v2 + (size_t)row * 256 + c0;
+        if (MODE == 0) {
+            // ---- epi2: V2 -> global fp16
+            const VecSlice b2s = vec_slice(a.b_v2, half * 32, 64, lane);
+            wait_acc(2);
+            for (int c0 = half * 32; c0 < 256; c0 += 64) {
+                load_acc_bias_s(t0, c0, b2s.r[c0 >> 6], x);
+                if (row_ok) {
+                    op_t* o = a.v2 + (size_t)row * 256 + c0;
 #pragma unroll
-                for (int j = 0; j < 32; j += 16) st_global_b32x8(o + j, pack8(x + j), pack8(x + j + 8));
+                    for (int j = 0; j < 32; j += 16) st_global_b32x8(o + j, pack8(x + j), pack8(x + j + 8));
+                }
             }
+            done(2);
         }
-        done(2);
 
         epi_ln(3, t1, a.b_out1, nullptr);     // y0 = LN(r + P1 VO^T + bo1)
+
+        if (MODE == 2) {
+            // ---- kg->rg partial context: V2 (in T0 since ph2) x E, 128 columns at a time through the dead P1 tile.  Thread
+            // (slot octet kh, column cc) owns 8 slots of the column's head; rows are walked once per image of the tile.
+            float b2r[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) b2r[i] = __ldg(a.b_v2 + 128 * (i >> 1) + 64 * half + 32 * (i & 1) + lane);
+            wait_acc(2);
+            epi_sync();                      // every warp is out of the LayerNorm scratch (P1 space); E is complete
+            // Per pass (128 columns = 4 heads): warp (hw = head of the pass, n0 = column half of the head) computes the 16 slots x
+            // 16 columns block acc = E_h^T V2 as mma.sync m16n8k16 tiles, both operands by ldmatrix.trans from the row-major
+            // tiles; rows outside the image's range are masked out of the A fragment.  A third accumulator against a
+            // constant-one B fragment gives the sums of E (warps with n0 == 0).
+            const int ew = warp - 2, hw = ew >> 1, n0 = ew & 1, g = lane >> 2, t = lane & 3, lg = lane >> 3, lr = lane & 7;
+            const int b_first = s_img[0], b_last = s_img[nlive - 1];
+#pragma unroll 1
+            for (int p = 0; p < 2; ++p) {
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int c0 = 128 * p + 64 * half + 32 * u;
+                    load_acc_bias_s(t0, c0, b2r[2 * p + u], x);
+                    if (!row_ok) {       // rows past the end hold whatever the caller's buffer held: keep NaN out of the sums
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) x[j] = 0.f;
+                    }
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) st_smem_v4(sbase + FN_P1 + kgt_off(lrow, ((c0 & 127) >> 3) + v), pack8(x + 8 * v));
+                }
+                if (p == 1) {                // T0 is free for ph4
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(epi_done + 2);
+                }
+                epi_sync();
+                const int h = 4 * p + hw;                       // head of this warp's block
+                const int ech = 2 * h, vch = 4 * hw + 2 * n0;   // 16-byte chunk of E (slots 16 h ..) / of the V2 tile (columns of the pass)
+                for (int b = b_first; b <= b_last; ++b) {
+                    const int lo = max(a.node_ptr[b] - m0, 0), hi = min(a.node_ptr[b + 1] - m0, nlive);
+                    if (hi <= lo) continue;
+                    float c0[4] = {0.f, 0.f, 0.f, 0.f}, c1[4] = {0.f, 0.f, 0.f, 0.f}, cl[4] = {0.f, 0.f, 0.f, 0.f};
+                    for (int ks = lo >> 4; ks <= (hi - 1) >> 4; ++ks) {
+                        uint32_t af[4], bf[4];
+                        ldsm_x4_trans(sbase + FN_X + kgt_off(16 * ks + (lg >> 1) * 8 + lr, ech + (lg & 1)), af);
+                        ldsm_x4_trans(sbase + FN_P1 + kgt_off(16 * ks + (lg & 1) * 8 + lr, vch + (lg >> 1)), bf);
+                        // af[0], af[1]: rows 16 ks + 2 t (+1), slots g / g + 8; af[2], af[3]: rows + 8
+                        const int r0 = 16 * ks + 2 * t;
+                        const uint32_t m_lo = (r0 >= lo && r0 < hi ? 0x0000ffffu : 0u) | (r0 + 1 >= lo && r0 + 1 < hi ? 0xffff0000u : 0u);
+                        const uint32_t m_hi = (r0 + 8 >= lo && r0 + 8 < hi ? 0x0000ffffu : 0u) | (r0 + 9 >= lo && r0 + 9 < hi ? 0xffff0000u : 0u);
+                        // mma A fragment order: (m = g, k lo), (m = g + 8, k lo), (m = g, k hi), (m = g + 8, k hi)
+                        const uint32_t am[4] = {af[0] & m_lo, af[1] & m_lo, af[2] & m_hi, af[3] & m_hi};
+                        mma16816_f16(c0, am, bf[0], bf[1]);
+                        mma16816_f16(c1, am, bf[2], bf[3]);
+                        if (n0 == 0) mma16816_f16(cl, am, 0x3c003c00u, 0x3c003c00u);
+                    }
+                    const size_t slot = (size_t)blockIdx.x + b;
+                    float* o = a.part_acc + (slot * 16) * 256 + 128 * p + 32 * hw + 16 * n0 + 2 * t;
+                    *reinterpret_cast<float2*>(o + (size_t)g * 256) = make_float2(c0[0], c0[1]);
+                    *reinterpret_cast<float2*>(o + (size_t)(g + 8) * 256) = make_float2(c0[2], c0[3]);
+                    *reinterpret_cast<float2*>(o + (size_t)g * 256 + 8) = make_float2(c1[0], c1[1]);
+                    *reinterpret_cast<float2*>(o + (size_t)(g + 8) * 256 + 8) = make_float2(c1[2], c1[3]);
+                    if (n0 == 0 && t == 0) {
+                        a.part_l[slot * 128 + 16 * h + g] = cl[0];
+                        a.part_l[slot * 128 + 16 * h + g + 8] = cl[2];
+                    }
+                }
+                epi_sync();                  // the V2 tile (and after the second pass E) may be overwritten
+            }
+            if (stamp && threadIdx.x == 64) a.dbg[24 + 2] = now();
+        }
+
         epi_relu(4, a.b_ffn1);                // phase 5 has no epilogue: its accumulator stays in T1
         epi_relu(6, a.b_ffn1 + 256);
-        epi_final(7);                         // y = Y + b2 + y0
+        if (MODE == 0) epi_final(7);          // y = Y + b2 + y0
+        else epi_final_sum(7);
         }
         tc_fence_before();
     }
@@ -462,6 +700,7 @@ static void fn_set_attr() {
     if (attr.first()) {
         cudaFuncSetAttribute(fusion_node_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, FN_SMEM);
         cudaFuncSetAttribute(fusion_node_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FN_SMEM);
+        cudaFuncSetAttribute(fusion_node_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FN_SMEM);
     }
 }
 
@@ -478,7 +717,8 @@ int launch_fusion_node(FusionNodeArgs& a, const void* x, const void* w_rgproj, c
     fn_set_attr();
     {
         CM_TIMED("fusion_node", st);
-        fusion_node_kernel<0><<<ceil_div(a.M, 128), FN_THREADS, FN_SMEM, st>>>(a);
+        if (a.part_acc) fusion_node_kernel<2><<<ceil_div(a.M, 128), FN_THREADS, FN_SMEM, st>>>(a);
+        else fusion_node_kernel<0><<<ceil_div(a.M, 128), FN_THREADS, FN_SMEM, st>>>(a);
     }
     return post_launch("fusion_node");
 }

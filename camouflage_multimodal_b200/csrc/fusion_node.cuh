@@ -21,6 +21,12 @@ struct FusionNodeArgs {
     op_t* v2;              // [M,256] V of the kg->rg attention
     float* y;              // [M,256] rg stream after the FFN residual
     float* attn_mean;      // [M, sm_valid] head-averaged rg->kg probabilities or NULL
+    // MODE 2 (part_acc != NULL): the kg->rg partials and the column sums of y per (tile + image) slot instead of s2 / v2 / y
+    float *part_m = nullptr, *part_l = nullptr;   // [slots,128] tile maximum of the raw scores, sum of exp(s - max) over the image's rows
+    float* part_acc = nullptr;                    // [slots,16,256] sum of exp(s - max) V2
+    float* part_y = nullptr;                      // [slots,256] column sums of y
+    const int* node_ptr = nullptr;                // [n_graphs + 1]
+    int n_graphs = 0;
     long long* dbg = nullptr;   // phase time stamps of CTA 0 (tools/fusion_phase_profile.py): [0..7] MMA issue, [8..15] MMA waited-for, [16..23] epilogue start, [24..31] epilogue done, [32] kernel start
 };
 

@@ -202,6 +202,13 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     int rc;
     Dense d;
 
+    // With the single-kernel node side AND the fused KG-side tail the node kernel reduces what the KG side needs from the node
+    // rows (kg->rg attention partials, column sums of y) per tile (fusion_node.cu MODE 2): S2 / V2 / y are not written and
+    // kg2rg_partial does not run.  The kg->rg attention map needs S2, so asking for it keeps the unfused form.
+    const bool fused_tail = D == 256 && Kk <= 16 && !getenv("CM_FUSION_UNFUSED_TAIL");
+    const size_t part_slots = (size_t)G * KG_MAX_CHUNKS;
+    const bool tile_partials = fusion_node_fused_ok(p) && fused_tail && p->heads == 8 && f.gs == 16 && !attn_kg2rg && !attn_rg2kg &&
+                               (size_t)(M + 127) / 128 + (size_t)G + 1 <= part_slots && !getenv("CM_FUSION_NODE_UNFUSED_KG");
     if (!fusion_node_fused_ok(p) && (rc = launch_cast_f16(rg, p->rg_dim, M, p->rg_dim, m_dev, w.rgb, p->rg_dim, st)) != CM_OK) return rc;
     if (fusion_node_fused_ok(p)) {
         // the whole region-node side in one kernel (fusion_node.cu)
@@ -213,6 +220,10 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
         a.s2 = w.s2; a.v2 = w.v2; a.y = w.y; a.attn_mean = attn_rg2kg;
         a.x32 = rg;   // fp32 node embeddings are converted inside the kernel (rg_dim == 128 here)
         a.dbg = g_fusion_phase_dbg;
+        if (tile_partials) {
+            a.part_m = w.part_m; a.part_l = w.part_l; a.part_acc = w.part_acc; a.part_y = w.part_y;
+            a.node_ptr = node_ptr; a.n_graphs = G;
+        }
         if ((rc = launch_fusion_node(a, w.rgb, W(f.w_rgproj), W(f.wcat), W(f.wv2), W(f.vot), W(f.ffn1), W(f.ffn2), st)) != CM_OK) return rc;
     } else {
     const op_t* r = w.rgb;
@@ -247,7 +258,7 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     KgSideArgs ks;
     ks.s2 = w.s2; ks.v2 = w.v2; ks.y = w.y; ks.part_m = w.part_m; ks.part_l = w.part_l; ks.part_acc = w.part_acc; ks.part_y = w.part_y;
     ks.attn_kg2rg = attn_kg2rg; ks.node_cap = M;
-    if ((rc = launch_kg2rg_partial(ks, D, p->heads, f.gs, node_ptr, G, st)) != CM_OK) return rc;
+    if (!tile_partials && (rc = launch_kg2rg_partial(ks, D, p->heads, f.gs, node_ptr, G, st)) != CM_OK) return rc;
     // ---- mean over kg rows (:135), fusion layer (:138-139), heads (:239-242)
     GraphTailArgs gt;
     gt.D = D; gt.n_kg = Kk; gt.num_classes = p->num_classes;
@@ -260,10 +271,11 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
     }
     gt.fused = fused_out; gt.mask_out = mask_out; gt.inst_out = instance_out; gt.edge_out = edge_out; gt.score_out = score_out;
     const float* kp = reinterpret_cast<const float*>(base + f.kp);
-    if (D == 256 && Kk <= 16 && !getenv("CM_FUSION_UNFUSED_TAIL")) {
+    if (fused_tail) {
         // one CTA per image: merge + KG-row chain (mma.sync 16-row tiles) + fusion MLP + heads (fusion_kg.cu)
         KgTailArgs kt;
         kt.part_m = w.part_m; kt.part_l = w.part_l; kt.part_acc = w.part_acc; kt.part_y = w.part_y; kt.node_ptr = node_ptr;
+        kt.tile_partials = tile_partials ? 1 : 0;
         kt.n_kg = Kk; kt.gs = f.gs; kt.heads = p->heads;
         kt.wo2 = W(f.wo2_h); kt.w1 = W(f.kffn1_h); kt.w2 = W(f.kffn2_h);
         kt.kp = kp; kt.bo2 = p->k2r_out_b; kt.ln_g = p->ln_kg_w; kt.ln_b = p->ln_kg_b; kt.b1 = p->ffn_kg_b1; kt.b2 = p->ffn_kg_b2;
