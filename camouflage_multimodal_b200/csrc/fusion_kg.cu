@@ -419,6 +419,10 @@ __global__ void __cluster_dims__(KT_CL, 1, 1) __launch_bounds__(KT_THREADS) kg_t
 #pragma unroll
     for (int it = 0; it < ITEMS; ++it) {
         const int i = tid + it * KT_THREADS, k = i / (QD / 2), c = q * QD + (i - k * (QD / 2)) * 2;
+        if (a.v2_bias && k < K && nb > 0) {   // softmax weights sum to one: the bias of V passes through the attention
+            s0[it] += a.v2_bias[c];
+            s1[it] += a.v2_bias[c + 1];
+        }
         __half2 hi, lo;
         split2(s0[it], s1[it], &hi, &lo);
 #pragma unroll

@@ -31,6 +31,7 @@ struct KgTailArgs {
     const float *part_m, *part_l, *part_acc, *part_y;
     int tile_partials;                    // 0: KG_MAX_CHUNKS chunk partials per image (kg2rg_partial); 1: one partial per 128-row tile of
                                           // the node kernel that holds rows of the image, at slot tile + image (fusion_node.cu MODE 2)
+    const float* v2_bias;                 // tile partials: the bias of V2 [256], added to the normalised context (NULL: already inside V2)
     const int* node_ptr;
     int n_kg, gs, heads;
     const op_t *wo2, *w1, *w2;            // fp16 [256,256], [512,256], [256,512] (nn.Linear layout)

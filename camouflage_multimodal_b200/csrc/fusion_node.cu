@@ -381,6 +381,20 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             }
             epi_sync();
         }
+        // row range [lo, hi) of image b inside this tile; the first three boundaries are fetched here, once (a tile of SLIC-sized
+        // images holds two images at most), so the per-image loops below do not wait for global memory
+        int npc[3] = {0, 0, 0};
+        if (MODE == 2) {
+            const int b0 = s_img[0];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) npc[k] = a.node_ptr[min(b0 + k, a.n_graphs)];
+        }
+        auto seg_range = [&](int b, int& lo, int& hi) {
+            const int k = b - s_img[0];
+            const int p0 = k == 0 ? npc[0] : k == 1 ? npc[1] : a.node_ptr[b], p1 = k == 0 ? npc[1] : k == 1 ? npc[2] : a.node_ptr[b + 1];
+            lo = max(p0 - m0, 0);
+            hi = min(p1 - m0, nlive);
+        };
 
         // y0 = LN(acc + bias + residual) -> A1.  Residual: A1 itself (in place: each thread re-reads and rewrites only
         // its own (row, chunk) cells, and every MMA that read A1 has completed because acc_ready[ph] covers them) or
@@ -474,7 +488,8 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             const float* yt = reinterpret_cast<const float*>(smem + FN_A3);
             const int c = threadIdx.x - 64;
             for (int b = s_img[0]; b <= s_img[nlive - 1]; ++b) {
-                const int lo = max(a.node_ptr[b] - m0, 0), hi = min(a.node_ptr[b + 1] - m0, nlive);
+                int lo, hi;
+                seg_range(b, lo, hi);
                 if (hi <= lo) continue;
                 float s4[4] = {0.f, 0.f, 0.f, 0.f};   // rows n with n % 4 == u, then combined in a fixed order
                 int n = lo;
@@ -613,9 +628,8 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         if (MODE == 2) {
             // ---- kg->rg partial context: V2 (in T0 since ph2) x E, 128 columns at a time through the dead P1 tile.  Thread
             // (slot octet kh, column cc) owns 8 slots of the column's head; rows are walked once per image of the tile.
-            float b2r[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) b2r[i] = __ldg(a.b_v2 + 128 * (i >> 1) + 64 * half + 32 * (i & 1) + lane);
+            // (V2's bias is not added here: the attention weights of a slot sum to one, so the KG-side tail adds it to the
+            // normalised context instead)
             wait_acc(2);
             epi_sync();                      // every warp is out of the LayerNorm scratch (P1 space); E is complete
             // Per pass (128 columns = 4 heads): warp (hw = head of the pass, n0 = column half of the head) computes the 16 slots x
@@ -624,29 +638,43 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             // constant-one B fragment gives the sums of E (warps with n0 == 0).
             const int ew = warp - 2, hw = ew >> 1, n0 = ew & 1, g = lane >> 2, t = lane & 3, lg = lane >> 3, lr = lane & 7;
             const int b_first = s_img[0], b_last = s_img[nlive - 1];
+            // V2 leaves T0 at once -- the first 128 columns into the tile, the other 128 packed into registers until the first
+            // pass is through -- so that ph4 can start while the products are formed
+            uint4 keep[2][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int p = i >> 1, u = i & 1, c0 = 128 * p + 64 * half + 32 * u;
+                {
+                    uint32_t v[32];
+                    tc_ld32(t0 + c0, v);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) x[j] = row_ok ? __uint_as_float(v[j]) : 0.f;   // rows past the end: keep NaN out of the sums
+                }
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    if (p == 0) st_smem_v4(sbase + FN_P1 + kgt_off(lrow, ((c0 & 127) >> 3) + v), pack8(x + 8 * v));
+                    else keep[u][v] = pack8(x + 8 * v);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(epi_done + 2);   // T0 is free for ph4
+            if (stamp && threadIdx.x == 64) a.dbg[35] = now();
 #pragma unroll 1
             for (int p = 0; p < 2; ++p) {
+                if (p == 1) {
 #pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const int c0 = 128 * p + 64 * half + 32 * u;
-                    load_acc_bias_s(t0, c0, b2r[2 * p + u], x);
-                    if (!row_ok) {       // rows past the end hold whatever the caller's buffer held: keep NaN out of the sums
+                    for (int u = 0; u < 2; ++u)
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) x[j] = 0.f;
-                    }
-#pragma unroll
-                    for (int v = 0; v < 4; ++v) st_smem_v4(sbase + FN_P1 + kgt_off(lrow, ((c0 & 127) >> 3) + v), pack8(x + 8 * v));
-                }
-                if (p == 1) {                // T0 is free for ph4
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(epi_done + 2);
+                        for (int v = 0; v < 4; ++v) st_smem_v4(sbase + FN_P1 + kgt_off(lrow, ((64 * half + 32 * u) >> 3) + v), keep[u][v]);
+                    if (stamp && threadIdx.x == 64) a.dbg[37] = now();
                 }
                 epi_sync();
                 const int h = 4 * p + hw;                       // head of this warp's block
                 const int ech = 2 * h, vch = 4 * hw + 2 * n0;   // 16-byte chunk of E (slots 16 h ..) / of the V2 tile (columns of the pass)
                 for (int b = b_first; b <= b_last; ++b) {
-                    const int lo = max(a.node_ptr[b] - m0, 0), hi = min(a.node_ptr[b + 1] - m0, nlive);
+                    int lo, hi;
+                    seg_range(b, lo, hi);
                     if (hi <= lo) continue;
                     float c0[4] = {0.f, 0.f, 0.f, 0.f}, c1[4] = {0.f, 0.f, 0.f, 0.f}, cl[4] = {0.f, 0.f, 0.f, 0.f};
                     for (int ks = lo >> 4; ks <= (hi - 1) >> 4; ++ks) {
@@ -674,6 +702,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
                         a.part_l[slot * 128 + 16 * h + g + 8] = cl[2];
                     }
                 }
+                if (stamp && threadIdx.x == 64 && p == 0) a.dbg[36] = now();
                 epi_sync();                  // the V2 tile (and after the second pass E) may be overwritten
             }
             if (stamp && threadIdx.x == 64) a.dbg[24 + 2] = now();

@@ -276,6 +276,7 @@ int fusion_forward_tc(const cm_fusion_params* p, const void* folded, const float
         KgTailArgs kt;
         kt.part_m = w.part_m; kt.part_l = w.part_l; kt.part_acc = w.part_acc; kt.part_y = w.part_y; kt.node_ptr = node_ptr;
         kt.tile_partials = tile_partials ? 1 : 0;
+        kt.v2_bias = tile_partials ? p->k2r_in_b + 2 * D : nullptr;
         kt.n_kg = Kk; kt.gs = f.gs; kt.heads = p->heads;
         kt.wo2 = W(f.wo2_h); kt.w1 = W(f.kffn1_h); kt.w2 = W(f.kffn2_h);
         kt.kp = kp; kt.bo2 = p->k2r_out_b; kt.ln_g = p->ln_kg_w; kt.ln_b = p->ln_kg_b; kt.b1 = p->ffn_kg_b1; kt.b2 = p->ffn_kg_b2;
