@@ -544,6 +544,14 @@ def b200_arm(args):
                           image_dtype=pool[0].images.dtype, label_dtype=pool[0].labels.dtype, packed_masks=not args.byte_masks)
     # host batches in the pipeline's pinned staging layout (images | labels | canny | gt in one allocation): one H2D copy each
     host_pool = [stager.host_batch().fill(b.images.cpu(), b.labels.cpu(), b.canny.cpu(), b.gt.cpu()) for b in pool]
+    # The batches written last are still dirty in the CPU caches, and a device read that has to snoop them out runs at 10-30 GB/s
+    # instead of 54 (h2d_probe_per_buffer_gbs showed it on the last two buffers, and e2e fell from 145 k to 100-115 k img/s whenever
+    # those lines stayed cached over the run): push them out to DRAM, where a decoder's finished batch lies by the time it is sent.
+    if not args.keep_host_cache:
+        evict = torch.empty(512 << 20, dtype=torch.uint8)
+        evict.fill_(1)
+        evict.add_(1)
+        del evict
 
     def e2e_step(s):
         return stager.submit(s, host_pool[s % n_pool])
@@ -559,9 +567,17 @@ def b200_arm(args):
     pe1.record()
     torch.cuda.synchronize()
     h2d_probe_gbs = 20 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+    per_buffer_gbs = []          # every pinned host batch of the pool on its own (a buffer on the far NUMA node would show here)
+    for hb in host_pool:
+        pe0.record()
+        for _ in range(5):
+            probe_d.copy_(hb.flat, non_blocking=True)
+        pe1.record()
+        torch.cuda.synchronize()
+        per_buffer_gbs.append(round(5 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9, 1))
 
     # the same copy rate with the device busy: rotating over every host buffer of the pool on a copy stream while the
-    # device-resident steps run on the lane streams (on some boxes of the pool copies slow down under compute; e2e follows)
+    # device-resident steps run on the lane streams (a check that kernels do not slow the copy engine down: 54 GB/s either way once the host batches are out of the CPU caches)
     cstream = torch.cuda.Stream(dev)
     fork()
     for s in range(4 * n_pool):
@@ -697,7 +713,8 @@ def b200_arm(args):
                     "timed_window_ms": 1e3 * sum(e2e_s), "h2d_probe_gbs": h2d_probe_gbs,
                     "host_submit_us_per_step": 1e6 * statistics.median(submit_s) / args.steps,
                     "ingest": stager.ingest, "ingest_calibration_steps_per_s": stager.ingest_rates,
-                    "h2d_probe_busy_gbs": h2d_probe_busy_gbs,
+                    "h2d_probe_busy_gbs": h2d_probe_busy_gbs, "h2d_probe_per_buffer_gbs": per_buffer_gbs,
+                    "host_affinity_cores": len(os.sched_getaffinity(0)),
                     "host_format": ("uint8 RGB + int16 labels + 1-bit canny + 1-bit gt (binary masks bit-packed on the host, "
                                     "cm_unpack_bits on the device): 5.25 B/pixel" if not args.byte_masks else
                                     "uint8 RGB + int16 labels + uint8 canny + uint8 gt: 7 B/pixel") if args.input == "u8" else "float32 / int32 form",
@@ -750,6 +767,7 @@ def main():
                     help="also time every kernel once on a batch this large (0 = skip): per-kernel roofline when not launch-bound")
     ap.add_argument("--cpu-images", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--keep-host-cache", action="store_true", help="e2e: do not evict the freshly written host batches from the CPU caches")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying CUDA graphs")
     ap.add_argument("--repeats", type=int, default=0, help="timed regions of --steps steps each (0 = at least 25 and at least 100 ms in total)")
     ap.add_argument("--no-train", action="store_true", help="skip the configs[3] training-step block")

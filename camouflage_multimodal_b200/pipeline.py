@@ -332,12 +332,13 @@ class HostPipeline:
 
     def __init__(self, pipe, B, H, W, device, slots: int = 2, use_graph: bool = True, image_dtype=torch.float32,
                  label_dtype=torch.int32, packed_masks: bool = False, image_only: bool = False, ingest: str | None = None):
-        """``ingest``: how a ``BatchBuffer`` crosses PCIe -- ``"ce"`` (cudaMemcpyAsync: a copy engine), ``"sm"``
-        (``cm_ingest_copy``: a 64-block kernel reading the pinned buffer) or ``"auto"`` (both are timed at construction on this
-        machine, under the load of the slots' own captured steps, and the faster one is kept).  Default ``"ce"`` (env
-        ``CM_E2E_INGEST``): a copy engine is the faster path on an idle link (53 against 47 GB/s here) and in every end-to-end
-        run measured so far (143 k against 97 k img/s); the kernel path keeps its rate when the device is saturated with
-        independent work, where a copy engine's falls to two thirds (``tools/ingest_probe.py``)."""
+        """``ingest``: how a ``BatchBuffer`` crosses PCIe -- ``"ce"`` (cudaMemcpyAsync: a copy engine; default, env
+        ``CM_E2E_INGEST``), ``"sm"`` (``cm_ingest_copy``: a 64-block kernel reading the pinned buffer) or ``"auto"`` (both are
+        timed at construction under the load of the slots' own captured steps, the faster one is kept).  The copy engine
+        is the faster path (54 against 47 GB/s on an idle link here, 146 k against 97 k img/s end to end); the kernel form
+        exists for callers that want the transfer inside a captured graph.  Note for the producer of the batches: a pinned
+        buffer the CPU has JUST written is still dirty in its caches and is read by the device at 10-30 GB/s instead of 54
+        (``bench.py``: ``h2d_probe_per_buffer_gbs``) -- write staging buffers with streaming stores or a few batches ahead."""
         pipes = list(pipe) if isinstance(pipe, (list, tuple)) else [pipe]
         self.pipes, self.dev = pipes, device
         # One stream carries every host->device copy, in submission order: each batch crosses PCIe at the link's full rate and
