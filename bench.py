@@ -158,6 +158,7 @@ def kernel_work(name, B, M, E, K):
         # table rows x node probabilities -> every metric: the per-image tables + the probabilities in, a few hundred bytes out
         "region_table_metrics": ("hbm", 32.0 * B * (LABEL_CAP + 1) + 4.0 * M + 2048.0 * B),
         "unpack_bits": ("hbm", px * (2.0 / 8.0 + 2.0)),
+        "unpack_labels10": ("hbm", px * (1.25 + 2.0)),
         "gat_logits": ("hbm", 60.0 * M + 32.0 * M),
         "gat_aggregate": ("hbm", 60.0 * M + 4.0 * E + 240.0 * M),
         "gcn_norm": ("hbm", 8.0 * E + 4.0 * M),
@@ -540,8 +541,11 @@ def b200_arm(args):
     summary.update(gm.sod_summary_from_partial(total_sod, float(total[0].item())))
 
     # ---- end to end through the host-facing call: pinned host inputs, H2D + path + D2H every step
+    # label maps at 10 bits per pixel when they fit (SLIC at n_segments = 500 stays far below 1024) and the masks are bit-packed too
+    packed_labels = (not args.int16_labels and not args.byte_masks and args.input == "u8" and LABEL_CAP <= 1024 and (H * W) % 16 == 0)
     stager = HostPipeline(pipes, BATCH, H, W, dev, slots=max(2, 2 * lanes), use_graph=not args.no_graph,
-                          image_dtype=pool[0].images.dtype, label_dtype=pool[0].labels.dtype, packed_masks=not args.byte_masks)
+                          image_dtype=pool[0].images.dtype, label_dtype=pool[0].labels.dtype, packed_masks=not args.byte_masks,
+                          packed_labels=packed_labels)
     # host batches in the pipeline's pinned staging layout (images | labels | canny | gt in one allocation): one H2D copy each
     host_pool = [stager.host_batch().fill(b.images.cpu(), b.labels.cpu(), b.canny.cpu(), b.gt.cpu()) for b in pool]
     # The batches written last are still dirty in the CPU caches, and a device read that has to snoop them out runs at 10-30 GB/s
@@ -715,7 +719,9 @@ def b200_arm(args):
                     "ingest": stager.ingest, "ingest_calibration_steps_per_s": stager.ingest_rates,
                     "h2d_probe_busy_gbs": h2d_probe_busy_gbs, "h2d_probe_per_buffer_gbs": per_buffer_gbs,
                     "host_affinity_cores": len(os.sched_getaffinity(0)),
-                    "host_format": ("uint8 RGB + int16 labels + 1-bit canny + 1-bit gt (binary masks bit-packed on the host, "
+                    "host_format": ("uint8 RGB + 10-bit labels + 1-bit canny + 1-bit gt (label maps and binary masks bit-packed on the host, "
+                                    "cm_unpack_labels10 / cm_unpack_bits on the device): 4.5 B/pixel" if packed_labels else
+                                    "uint8 RGB + int16 labels + 1-bit canny + 1-bit gt (binary masks bit-packed on the host, "
                                     "cm_unpack_bits on the device): 5.25 B/pixel" if not args.byte_masks else
                                     "uint8 RGB + int16 labels + uint8 canny + uint8 gt: 7 B/pixel") if args.input == "u8" else "float32 / int32 form",
                     "h2d_achieved_gbs": e2e_value / world * stager.h2d_bytes / BATCH / 1e9,
@@ -767,6 +773,7 @@ def main():
                     help="also time every kernel once on a batch this large (0 = skip): per-kernel roofline when not launch-bound")
     ap.add_argument("--cpu-images", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--int16-labels", action="store_true", help="e2e: send the label maps as int16 (default: 10 bits per pixel, unpacked on the device)")
     ap.add_argument("--keep-host-cache", action="store_true", help="e2e: do not evict the freshly written host batches from the CPU caches")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying CUDA graphs")
     ap.add_argument("--repeats", type=int, default=0, help="timed regions of --steps steps each (0 = at least 25 and at least 100 ms in total)")

@@ -139,6 +139,7 @@ SIGNATURES = {
     "cm_paint_metrics_i16": (_i, [_fp, _fp, _i, _i, _i, _fp, _fp, _fp, _i, _f, _fp, _fp, _fp, _fp]),
     "cm_unpack_bits": (_i, [_fp, _i64, _i, _fp, _fp]),
     "cm_ingest_copy": (_i, [_fp, _fp, _i64, _i, _fp]),
+    "cm_unpack_labels10": (_i, [_fp, _i64, _fp, _fp]),
     "cm_metrics_dense": (_i, [_fp, _fp, _i, _i64, _f, _fp, _fp, _fp]),
     "cm_metrics_finalize": (_i, [_fp, _fp, _i, _i64, _fp, _fp, _fp]),
     "cm_sod_workspace_bytes": (_sz, [_i, _i, _i]),

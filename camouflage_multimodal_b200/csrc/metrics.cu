@@ -171,6 +171,30 @@ __global__ void __launch_bounds__(256) ingest_copy_kernel(const uint4* __restric
     for (; i < n16; i += stride) dst[i] = __ldcv(src + i);
 }
 
+// 10-bit labels, little-endian bit stream (label i = bits [10 i, 10 i + 10)): one thread per 16 labels = five 32-bit words
+// in, two 16-byte stores out
+__global__ void unpack_labels10_kernel(const uint32_t* __restrict__ packed, long long n_groups, short* __restrict__ out) {
+    const long long gidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gidx >= n_groups) return;
+    const uint32_t* p = packed + gidx * 5;
+    const uint32_t w[6] = {p[0], p[1], p[2], p[3], p[4], 0u};
+    uint32_t o[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        uint32_t v[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int bit = 10 * (2 * k + u), wi = bit >> 5, sh = bit & 31;
+            const unsigned long long two = (unsigned long long)w[wi] | ((unsigned long long)w[wi + 1] << 32);
+            v[u] = (uint32_t)(two >> sh) & 1023u;
+        }
+        o[k] = v[0] | (v[1] << 16);
+    }
+    uint4* dst = reinterpret_cast<uint4*>(out + gidx * 16);
+    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+}
+
 static int metric_chunks(long long pixels, int batch) {
     // about four CTAs per SM over the whole batch, at least 1 per image, at most one per 256 pixels
     long long want = (4LL * num_sms() + batch - 1) / batch;
@@ -217,6 +241,20 @@ extern "C" int cm_unpack_bits(const uint8_t* bits, int64_t n_bytes, int one_valu
         unpack_bits_kernel<<<ceil_div(n_bytes, 256), 256, 0, as_stream(stream)>>>(bits, n_bytes, (unsigned)one_value, out);
     }
     return post_launch("cm_unpack_bits");
+}
+
+extern "C" int cm_unpack_labels10(const uint8_t* packed, int64_t n_labels, int16_t* out, void* stream) {
+    using namespace cm;
+    CM_DEVICE_OR_RETURN();
+    CM_REQUIRE(packed && out && n_labels > 0 && n_labels % 16 == 0, "cm_unpack_labels10: NULL pointer or a label count that is not a multiple of 16");
+    CM_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+               "cm_unpack_labels10: packed must be 4-byte aligned, out 16-byte aligned");
+    {
+        CM_TIMED("unpack_labels10", as_stream(stream));
+        unpack_labels10_kernel<<<ceil_div(n_labels / 16, 256), 256, 0, as_stream(stream)>>>(reinterpret_cast<const uint32_t*>(packed), n_labels / 16,
+                                                                                             reinterpret_cast<short*>(out));
+    }
+    return post_launch("cm_unpack_labels10");
 }
 
 extern "C" int cm_ingest_copy(const void* host_src, void* dst, int64_t n_bytes, int ctas, void* stream) {

@@ -110,6 +110,14 @@ class EvalPipeline:
                 if buf is None or buf.shape != (B, H, W):
                     buf = self._bufs["canny_map"] = torch.empty((B, H, W), dtype=torch.uint8, device=dev)
                 canny = canny_edges(images, sigma=2.0, out=buf)
+        if labels is not None and labels.dtype == torch.uint8 and labels.dim() == 2:      # 10-bit label stream (pack_labels10)
+            if tuple(labels.shape) != (B, H * W * 10 // 8) or (H * W) % 16:
+                raise ValueError(f"packed labels must be [B, H*W*10/8] uint8 with H*W % 16 == 0, got {tuple(labels.shape)}")
+            buf = self._bufs.get("labels16")
+            if buf is None or buf.shape != (B, H, W):
+                buf = self._bufs["labels16"] = torch.empty((B, H, W), dtype=torch.int16, device=dev)
+            _lib.check(lib.cm_unpack_labels10(_lib.ptr(labels.contiguous()), B * H * W, _lib.ptr(buf), _lib.stream_ptr(dev)), "cm_unpack_labels10")
+            labels = buf
         use_table = (self.table_metrics and self.sod_metrics and not self.weighted_f and not self.want_pred_mask
                      and self.label_cap <= metrics.RT_MAX_LABEL_CAP and 0.0 <= self.threshold < 1.0)
         if canny.dim() == 2 or gt.dim() == 2:      # bit-packed masks: one bit per pixel over PCIe, bytes again here
@@ -237,6 +245,27 @@ def pack_mask_bits(mask: torch.Tensor) -> torch.Tensor:
     return torch.from_numpy(np.packbits(m.reshape(m.shape[0], -1), axis=1, bitorder="little"))
 
 
+def pack_labels10(labels: torch.Tensor) -> torch.Tensor:
+    """``[B,H,W]`` integer label map with values in [0, 1024) -> ``[B, H*W*10/8]`` uint8: a little-endian bit stream, label i
+    in bits [10 i, 10 i + 10) (what ``cm_unpack_labels10`` reads).  Host-side helper: 1.25 instead of 2 bytes per pixel."""
+    import numpy as np
+    lab = labels.detach().cpu().numpy()
+    B = lab.shape[0]
+    if lab.size and (lab.min() < 0 or lab.max() > 1023):
+        raise ValueError("pack_labels10: labels must lie in [0, 1024)")
+    if (lab.size // max(B, 1)) % 16:
+        raise ValueError("pack_labels10: H*W must be a multiple of 16")
+    q = lab.reshape(B, -1, 4).astype(np.uint16)
+    l0, l1, l2, l3 = q[..., 0], q[..., 1], q[..., 2], q[..., 3]
+    out = np.empty((B, q.shape[1], 5), np.uint8)
+    out[..., 0] = l0 & 255
+    out[..., 1] = (l0 >> 8) | ((l1 & 63) << 2)
+    out[..., 2] = (l1 >> 6) | ((l2 & 15) << 4)
+    out[..., 3] = (l2 >> 4) | ((l3 & 3) << 6)
+    out[..., 4] = l3 >> 2
+    return torch.from_numpy(out.reshape(B, -1))
+
+
 class BatchBuffer:
     """The four inputs of one batch as views of ONE flat byte buffer (pinned host memory or device memory), each at a
     256-byte aligned offset: a host batch laid out like this goes to the device as a single copy (54.7 GB/s for
@@ -244,16 +273,23 @@ class BatchBuffer:
     Canny map and the ground truth travel one bit per pixel (``[B, H*W/8]`` uint8; 7 -> 5.25 bytes per pixel with uint8
     images + int16 labels) -- for binary masks only: a set gt bit is read as 255."""
 
-    def __init__(self, B, H, W, image_dtype=torch.float32, label_dtype=torch.int32, device=None, packed_masks=False, image_only=False):
+    def __init__(self, B, H, W, image_dtype=torch.float32, label_dtype=torch.int32, device=None, packed_masks=False, image_only=False,
+                 packed_labels=False):
         """``image_only``: no label / Canny views -- the device front end (cm_slic, cm_canny) derives both from the image,
-        so a batch is uint8 RGB + the ground truth (3.125 bytes per pixel with a bit-packed mask)."""
+        so a batch is uint8 RGB + the ground truth (3.125 bytes per pixel with a bit-packed mask).
+        ``packed_labels``: the label map travels at 10 bits per pixel (``[B, H*W*10/8]`` uint8, ``pack_labels10``; labels
+        below 1024): 4.5 bytes per pixel with uint8 images and bit-packed masks."""
         self.packed_masks, self.image_only = bool(packed_masks), bool(image_only)
+        self.packed_labels = bool(packed_labels) and not self.image_only
+        if self.packed_labels and (H * W) % 16:
+            raise ValueError("packed labels need H*W % 16 == 0")
         mshape = (B, H * W // 8) if packed_masks else (B, H, W)
         if packed_masks and (H * W) % 8:
             raise ValueError("packed masks need H*W % 8 == 0")
         shapes = [("images", (B, H, W, 3), image_dtype)]
         if not image_only:
-            shapes += [("labels", (B, H, W), label_dtype), ("canny", mshape, torch.uint8)]
+            shapes += [("labels", (B, H * W * 10 // 8), torch.uint8) if self.packed_labels else ("labels", (B, H, W), label_dtype),
+                       ("canny", mshape, torch.uint8)]
         shapes.append(("gt", mshape, torch.uint8))
         offs, total = [], 0
         for _, shp, dt in shapes:
@@ -279,7 +315,7 @@ class BatchBuffer:
         ``image_only`` the label and Canny maps are ignored."""
         self.images.copy_(images)
         if not self.image_only:
-            self.labels.copy_(labels)
+            self.labels.copy_(pack_labels10(labels) if self.packed_labels and labels.dim() == 3 else labels)
             self.canny.copy_(pack_mask_bits(canny) if self.packed_masks and canny.dim() == 3 else canny)
         self.gt.copy_(pack_mask_bits(gt) if self.packed_masks and gt.dim() == 3 else gt)
         return self
@@ -288,11 +324,13 @@ class BatchBuffer:
 class HostStager:
     """Pinned host buffers + device buffers for one batch: the host-facing entry of the pipeline."""
 
-    def __init__(self, B, H, W, device, image_dtype=torch.float32, label_dtype=torch.int32, packed_masks=False, image_only=False):
+    def __init__(self, B, H, W, device, image_dtype=torch.float32, label_dtype=torch.int32, packed_masks=False, image_only=False,
+                 packed_labels=False):
         self.dev = device
         pin = dict(pin_memory=True)
-        self.h_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, packed_masks=packed_masks, image_only=image_only)
-        self.d_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, device=device, packed_masks=packed_masks, image_only=image_only)
+        self.h_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, packed_masks=packed_masks, image_only=image_only, packed_labels=packed_labels)
+        self.d_batch = BatchBuffer(B, H, W, image_dtype, label_dtype, device=device, packed_masks=packed_masks, image_only=image_only,
+                                   packed_labels=packed_labels)
         self.h_images, self.h_labels, self.h_canny, self.h_gt = (self.h_batch.images, self.h_batch.labels, self.h_batch.canny,
                                                                  self.h_batch.gt)
         self.d_images, self.d_labels, self.d_canny, self.d_gt = (self.d_batch.images, self.d_batch.labels, self.d_batch.canny,
@@ -331,7 +369,8 @@ class HostPipeline:
     kernels, slots sharing a pipeline are serialised through ``pipe_done`` events (they share its buffers)."""
 
     def __init__(self, pipe, B, H, W, device, slots: int = 2, use_graph: bool = True, image_dtype=torch.float32,
-                 label_dtype=torch.int32, packed_masks: bool = False, image_only: bool = False, ingest: str | None = None):
+                 label_dtype=torch.int32, packed_masks: bool = False, image_only: bool = False, ingest: str | None = None,
+                 packed_labels: bool = False):
         """``ingest``: how a ``BatchBuffer`` crosses PCIe -- ``"ce"`` (cudaMemcpyAsync: a copy engine; default, env
         ``CM_E2E_INGEST``), ``"sm"`` (``cm_ingest_copy``: a 64-block kernel reading the pinned buffer) or ``"auto"`` (both are
         timed at construction under the load of the slots' own captured steps, the faster one is kept).  The copy engine
@@ -348,7 +387,7 @@ class HostPipeline:
         self.pipe_done = [torch.cuda.Event() for _ in pipes]
         self.slots = []
         for k in range(slots):
-            st = HostStager(B, H, W, device, image_dtype, label_dtype, packed_masks=packed_masks, image_only=image_only)
+            st = HostStager(B, H, W, device, image_dtype, label_dtype, packed_masks=packed_masks, image_only=image_only, packed_labels=packed_labels)
             st.pipe_idx = k % len(pipes)
             st.stream = torch.cuda.Stream(device)
             st.d_batch.flat.zero_()
@@ -414,7 +453,7 @@ class HostPipeline:
         decode straight into them) and pass it to ``submit`` -- it then crosses PCIe as ONE copy."""
         st = self.slots[0]
         return BatchBuffer(*st.h_images.shape[:3], st.h_images.dtype, st.h_labels.dtype if st.h_labels is not None else torch.int32,
-                           packed_masks=st.h_batch.packed_masks, image_only=st.h_batch.image_only)
+                           packed_masks=st.h_batch.packed_masks, image_only=st.h_batch.image_only, packed_labels=st.h_batch.packed_labels)
 
     def submit(self, i, h_images, h_labels=None, h_canny=None, h_gt=None):
         """Queue batch ``i``: a ``BatchBuffer`` from ``host_batch()`` (one H2D copy) or four pinned host tensors (four

@@ -340,6 +340,10 @@ int cm_paint_metrics(const int32_t* labels, const uint8_t* gt, int batch, int h,
  * per pixel of the host -> device transfer; packed they are 0.25): bit i of byte j (little-endian bit order,
  * numpy.packbits(bitorder="little")) -> out[8 j + i] = one_value or 0.  out 8-byte aligned, 8 * n_bytes bytes. */
 int cm_unpack_bits(const uint8_t* bits, int64_t n_bytes, int one_value, uint8_t* out, void* stream);
+/* Label maps over PCIe at 10 bits per pixel (the hand-over of the host front end; skimage labels at
+ * n_segments = 500 stay below 1024): packed = little-endian bit stream, label i in bits [10 i, 10 i + 10) (4 labels in 5 bytes;
+ * pipeline.pack_labels10 on the host), n_labels a multiple of 16, out [n_labels] int16 (16-byte aligned). */
+int cm_unpack_labels10(const uint8_t* packed, int64_t n_labels, int16_t* out, void* stream);
 /* Host -> device staging of a batch by a kernel instead of a copy engine (the front end's hand-over; the
  * reference's `.to(device)`, models/multimodal/test_multimodal.py:96-99): host_src is PINNED host memory (cudaHostAlloc /
  * torch pin_memory: device-addressable under unified addressing), n_bytes a multiple of 16, both pointers 16-byte aligned;

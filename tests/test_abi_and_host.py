@@ -277,3 +277,15 @@ def test_embedding_cache_files_round_trip(tmp_path):
     m = EmbeddingMatcher(str(tmp_path / "all_rg_embeddings.pt"), str(tmp_path / "kg.pt"))
     rows, ptr, kgb = m.matched_ragged_batch(list(allemb), device="cpu")
     assert rows.shape == (4 + 5 + 6, 128) and ptr.tolist() == [0, 4, 9, 15] and kgb.shape == (1, 2, 128)
+
+
+def test_pack_labels10_bit_layout():
+    """Label i occupies bits [10 i, 10 i + 10) of a little-endian stream (what cm_unpack_labels10 reads)."""
+    import numpy as np
+    import torch
+    from camouflage_multimodal_b200.pipeline import pack_labels10
+    lab = np.array([[[1, 2, 1023, 0, 513, 7, 64, 999, 5, 6, 7, 8, 9, 10, 11, 12]]], dtype=np.int64)
+    stream = pack_labels10(torch.as_tensor(lab)).numpy().reshape(-1)
+    assert stream.shape == (20,)
+    big = int.from_bytes(stream.tobytes(), "little")
+    assert [(big >> (10 * i)) & 1023 for i in range(16)] == lab.reshape(-1).tolist()

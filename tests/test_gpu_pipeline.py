@@ -292,3 +292,33 @@ def test_image_only_pipeline_equals_explicit_front_end(models):
         st = hp.submit(j, hb)
     hp.synchronize()
     assert torch.equal(st.h_mask_out, ref_mask) and torch.equal(st.h_per_image, ref_per)
+
+
+def test_ten_bit_label_stream_round_trip_and_pipeline():
+    """Label maps at 10 bits per pixel (pipeline.pack_labels10 -> cm_unpack_labels10): exact round trip incl. 0 and 1023, and a
+    pipeline run on the packed stream gives the outputs of the int16 run bit for bit."""
+    import bench
+    from camouflage_multimodal_b200 import _lib, synth
+    from camouflage_multimodal_b200.pipeline import EvalPipeline, pack_labels10, pack_mask_bits
+    dev = torch.device("cuda")
+    lib = _lib.load()
+    rng = np.random.default_rng(4)
+    lab = rng.integers(0, 1024, size=(3, 48, 80)).astype(np.int16)
+    lab[0, 0, :4] = [0, 1023, 512, 1]
+    packed = pack_labels10(torch.as_tensor(lab))
+    assert packed.shape == (3, 48 * 80 * 10 // 8) and packed.dtype == torch.uint8
+    out = torch.empty((3, 48, 80), dtype=torch.int16, device=dev)
+    _lib.check(lib.cm_unpack_labels10(_lib.ptr(packed.to(dev)), lab.size, _lib.ptr(out), _lib.stream_ptr(dev)), "cm_unpack_labels10")
+    assert np.array_equal(out.cpu().numpy(), lab)
+    with pytest.raises(ValueError):
+        pack_labels10(torch.full((1, 4, 4), 1024))
+    gnn, det = bench.make_models()
+    kg, _ = bench.load_kg()
+    pipe = EvalPipeline(gnn.to(dev), det.to(dev), kg.to(dev), label_cap=bench.LABEL_CAP)
+    b = synth.make_batch(0, 6, seed=77, device=dev).as_decoded()
+    keys = ("mask_out", "per_image", "per_image_sod", "counts")
+    ref = {k: v.clone() for k, v in pipe.run(b.images, b.labels, b.canny, b.gt).items() if k in keys}
+    got = pipe.run(b.images, pack_labels10(b.labels).to(dev), pack_mask_bits(b.canny).to(dev), pack_mask_bits(b.gt).to(dev))
+    torch.cuda.synchronize()
+    for k in keys:
+        assert torch.equal(got[k], ref[k]) or torch.allclose(got[k], ref[k], rtol=0, atol=0, equal_nan=True), k
