@@ -582,7 +582,7 @@ extern "C" int cm_fusion_train_forward(const cm_fusion_params* p, const float* r
     launch_gemm(gemm_nt(w.R, D, p->r2k_in_w, w.Q1, D, M, D, D, p->r2k_in_b, 0), st, "train_linear");
     launch_gemm(gemm_nt(w.Kp, D, p->r2k_in_w + (size_t)D * D, w.KV1, 2 * D, GK, 2 * D, D, p->r2k_in_b + D, 0), st, "train_linear");
     {
-        CM_TIMED("train_attention", st);
+        CM_TIMED("train_attn_r2k_fwd", st);
         attn_r2k_fwd_kernel<<<ceil_div((long)M * H, 8), 256, 0, st>>>(w.Q1, w.KV1, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 0),
                                                                       fdrop_scale(drop, 0), w.P1, w.O1);
     }
@@ -601,7 +601,7 @@ extern "C" int cm_fusion_train_forward(const cm_fusion_params* p, const float* r
     launch_gemm(gemm_nt(w.Kp, D, p->k2r_in_w, w.Q2, D, GK, D, D, p->k2r_in_b, 0), st, "train_linear");
     launch_gemm(gemm_nt(w.R, D, p->k2r_in_w + (size_t)D * D, w.KV2, 2 * D, M, 2 * D, D, p->k2r_in_b + D, 0), st, "train_linear");
     {
-        CM_TIMED("train_attention", st);
+        CM_TIMED("train_attn_k2r_fwd", st);
         attn_k2r_fwd_kernel<<<ceil_div((long)GK * H, 8), 256, 0, st>>>(w.Q2, w.KV2, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 2),
                                                                        fdrop_scale(drop, 2), w.P2, w.O2);
     }
@@ -699,7 +699,7 @@ extern "C" int cm_fusion_backward(const cm_fusion_params* p, const float* rg, co
     launch_colsum(w.dkB, D, GK, D, w.part_d, gr->k2r_out_b, 0, st);
     launch_gemm(gemm_nn(w.dkB, D, p->k2r_out_w, w.dkA, D, GK, D, D), st, "train_dgrad");   // dkA = dO2
     {
-        CM_TIMED("train_attention", st);
+        CM_TIMED("train_attn_k2r_bwd", st);
         attn_k2r_bwd_a_kernel<<<ceil_div((long)GK * H, 8), 256, 0, st>>>(w.KV2, w.P2, w.dkA, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 2),
                                                                          fdrop_scale(drop, 2), w.dP2, w.dkB);   // dkB = dQ2
         attn_k2r_bwd_b_kernel<<<ceil_div(M, 8), 256, 0, st>>>(w.Q2, w.P2, w.dP2, w.dkA, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 2),
@@ -737,7 +737,7 @@ extern "C" int cm_fusion_backward(const cm_fusion_params* p, const float* rg, co
     launch_colsum(w.dB, D, M, D, w.part_d, gr->r2k_out_b, 0, st);
     launch_gemm(gemm_nn(w.dB, D, p->r2k_out_w, w.dA, D, M, D, D), st, "train_dgrad");   // dA = dO1
     {
-        CM_TIMED("train_attention", st);
+        CM_TIMED("train_attn_r2k_bwd", st);
         attn_r2k_bwd_kernel<<<ceil_div((long)M * H, 8), 256, 0, st>>>(w.KV1, w.P1, w.dA, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 0),
                                                                       fdrop_scale(drop, 0), w.dP1, w.dB);   // dB = dQ1
         attn_r2k_bwd_kv_kernel<<<dim3(G, H), 256, 0, st>>>(w.Q1, w.P1, w.dP1, w.dA, node_ptr, K, D, H, scale, fdrop_keep(drop, 0),
