@@ -484,6 +484,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
                     st_smem_v4(sbase + FN_A3 + (uint32_t)(lrow * 260 + c0 + j) * 4,
                                make_uint4(__float_as_uint(x[j]), __float_as_uint(x[j + 1]), __float_as_uint(x[j + 2]), __float_as_uint(x[j + 3])));
             }
+            if (stamp && threadIdx.x == 64) a.dbg[39] = now();
             epi_sync();
             const float* yt = reinterpret_cast<const float*>(smem + FN_A3);
             const int c = threadIdx.x - 64;

@@ -37,6 +37,7 @@ for ph in range(8):
     f = lambda v: f"{(v - t0) / 1e3:8.2f}" if v else "       -"
     print(f"{ph} {names[ph]:12s} {f(t[ph])} {f(t[8 + ph])} {f(t[16 + ph])} {f(t[24 + ph])}")
 print("epi1 chunk loops done: half 0 (softmax -> P1) at", round((t[33] - t0) / 1e3, 2), " half 1 (S2 -> global) at", round((t[34] - t0) / 1e3, 2))
+print("MODE 2 epi7: y tile written (before the column sums) at", round((t[39] - t0) / 1e3, 2))
 print("MODE 2 kg pass (row 2 = its start / end): V2 half 0 staged / products done / V2 half 1 staged at", *(round((t[k] - t0) / 1e3, 2) for k in (35, 36, 37)))
 print("epi1 first chunk (half 0): after TMEM load + bias", round((t[35] - t0) / 1e3, 2), " after softmax", round((t[36] - t0) / 1e3, 2), " after P1 store", round((t[37] - t0) / 1e3, 2))
 
