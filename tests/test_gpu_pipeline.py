@@ -322,3 +322,36 @@ def test_ten_bit_label_stream_round_trip_and_pipeline():
     torch.cuda.synchronize()
     for k in keys:
         assert torch.equal(got[k], ref[k]) or torch.allclose(got[k], ref[k], rtol=0, atol=0, equal_nan=True), k
+
+
+def test_pipeline_is_deterministic_run_to_run_and_across_concurrent_lanes():
+    """No floating-point atomics, fixed-order partial sums: the same batch gives bit-identical logits / metrics every time,
+    also with two pipelines replaying their captured steps concurrently on separate streams (a missing barrier in the fused
+    kernels would show up here as run-to-run noise)."""
+    import bench
+    from camouflage_multimodal_b200 import synth
+    from camouflage_multimodal_b200.pipeline import EvalPipeline
+    dev = torch.device("cuda")
+    gnn, det = bench.make_models()
+    kg, _ = bench.load_kg()
+    gnn, det, kg = gnn.to(dev), det.to(dev), kg.to(dev)
+    b = synth.make_batch(3, 32, seed=2024, device=dev).as_decoded()
+    keys = ("mask_out", "fused", "per_image", "per_image_sod", "counts", "score_out")
+    pipes = [EvalPipeline(gnn, det, kg, label_cap=bench.LABEL_CAP, lane=i) for i in range(2)]
+    ref = {k: v.clone() for k, v in pipes[0].run(b.images, b.labels, b.canny, b.gt).items() if k in keys}
+    for _ in range(4):
+        out = pipes[0].run(b.images, b.labels, b.canny, b.gt)
+        torch.cuda.synchronize()
+        for k in keys:
+            assert torch.equal(out[k].view(torch.uint8), ref[k].view(torch.uint8)), k
+    graphs = [p.capture(b.images, b.labels, b.canny, b.gt) for p in pipes]
+    streams = [torch.cuda.Stream(dev) for _ in pipes]
+    torch.cuda.synchronize()
+    for _ in range(6):
+        for (g, _), s in zip(graphs, streams):
+            with torch.cuda.stream(s):
+                g.replay()
+    torch.cuda.synchronize()
+    for _, out in graphs:
+        for k in keys:
+            assert torch.equal(out[k].view(torch.uint8), ref[k].view(torch.uint8)), k
