@@ -525,12 +525,16 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
         if (MODE == 2) {
             // Each half takes two of the four 32-column chunks of BOTH score blocks: the softmax of the rg->kg scores -> P1, and
             // the raw kg->rg scores -> flash-style partial statistics (nothing of them leaves the SM but 1 KB per image).
-            float cs[2], ce[2];
+            // (the kg->rg block has no additive term: a per-slot constant cancels in the softmax over the nodes, ccat[128..] = 0)
+            float cs[2];
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
-                cs[u] = __ldg(a.ccat + 64 * half + 32 * u + lane);
-                ce[u] = __ldg(a.ccat + 128 + 64 * half + 32 * u + lane);
-            }
+            for (int u = 0; u < 2; ++u) cs[u] = __ldg(a.ccat + 64 * half + 32 * u + lane);
+            auto load_raw = [&](int c0) {
+                uint32_t v[32];
+                tc_ld32(t1 + c0, v);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
+            };
             wait_acc(1);
             float am[32];   // unused head means (the rg->kg attention map is not produced in this mode)
 #pragma unroll
@@ -547,7 +551,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
             float* cm = reinterpret_cast<float*>(smem + FN_X);     // [4 warps][128] column maxima (E goes over them below)
 #pragma unroll 1
             for (int u = 0; u < 2; ++u) {
-                load_acc_bias_s(t1, 128 + 64 * half + 32 * u, ce[u], x);
+                load_raw(128 + 64 * half + 32 * u);
                 if (!row_ok) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) x[j] = -INFINITY;
@@ -564,7 +568,7 @@ __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid
 #pragma unroll 1
             for (int u = 0; u < 2; ++u) {
                 const int i = 2 * half + u;
-                load_acc_bias_s(t1, 128 + 32 * i, ce[u], x);
+                load_raw(128 + 32 * i);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) x[j] = row_ok ? __expf(x[j] - s_m[32 * i + j]) : 0.f;
 #pragma unroll
