@@ -176,6 +176,9 @@ __device__ __forceinline__ void mma16816_f16(float (&c)[4], const uint32_t (&a)[
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+// Measured and dropped: the per-column vectors as 7.5 KB of kernel parameters (host copies taken at fold time), read from the
+// constant bank with a warp-uniform index instead of lane slices + shuffles: LDC.64 with a register offset, no local copy --
+// and the same tile time (29.8 against 29.9 us, bench 199 k against 202 k img/s): the broadcast is not what the epilogues wait for.
 // Measured and dropped: a node-pooled FFN.  The rg stream is used only through its mean over the image's nodes
 // (fusion_model.py:134) and the mean commutes with the FFN's second layer, so ph5 / ph7, the y epilogue and the 1 KB per node
 // of y can go: the y0 / hh epilogues add their columns up per image (warp transpose-reduce) and the KG-side tail applies W2 to
