@@ -193,7 +193,10 @@ __device__ __forceinline__ void mma16816_f16(float (&c)[4], const uint32_t (&a)[
 // by what the side work would have saved (the register file allows 128 registers per thread at 448 threads).
 // Measured and dropped: keeping the next chunk's TMEM load in flight while the current chunk is processed (tc_ld32_issue /
 // tc_ld_wait in tc_ptx.cuh) needs 32 more live registers; a 320-thread CTA is capped at 168 (three warps per 16 K-register
-// sub-partition), and the spills cost more than the hidden latency (43 -> 58 us).
+// sub-partition), and the spills cost more than the hidden latency (43 -> 58 us).  Tried again for the plain-bias epilogues once
+// the kernel was down to ~125 registers (two buffers, no spills): no gain either (epi0 1.03 us as before, the ReLU epilogues
+// 1.5 instead of 1.2-1.4 us) -- with two warps per scheduler the epilogues are bound by instruction issue (~2.7 instructions
+// per element: bias broadcast, add, pack, store), not by the TMEM load latency.
 template <int MODE>
 __global__ void __launch_bounds__(FN_THREADS, 1) fusion_node_kernel(const __grid_constant__ FusionNodeArgs a) {
     constexpr int NPH = MODE == 1 ? 5 : 8, XKB = MODE == 1 ? 4 : 2;
