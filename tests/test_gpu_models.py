@@ -296,3 +296,19 @@ def test_tensor_core_path_saturates_instead_of_overflowing(detector):
     for t in out[:4]:
         assert torch.isfinite(t).all()
     assert torch.isfinite(out[4]["rg2kg"]).all() and torch.isfinite(out[4]["kg2rg"]).all()
+
+
+@pytest.mark.parametrize("n_kg", [1, 5, 16])
+def test_node_kernel_reduction_with_other_kg_sizes(detector, n_kg):
+    """The in-kernel kg->rg reduction (return_attention=False) against the unfused form (return_attention=True) for KG row
+    counts other than the bundled 13: 1 row, 5 rows, and 16 = every slot of a head in use."""
+    m, _ = detector
+    gen = torch.Generator().manual_seed(100 + n_kg)
+    kg = (torch.randn(n_kg, 128, generator=gen) * 0.5).cuda()[None]
+    sizes = [300, 129, 64, 7]
+    rows = torch.cat([torch.randn(n, 128, generator=gen).clamp_min_(0) * 0.6 for n in sizes]).cuda()
+    ptr = torch.tensor(np.concatenate([[0], np.cumsum(sizes)]), dtype=torch.int32).cuda()
+    a = m.forward_ragged(rows, ptr, len(sizes), kg, return_attention=False)
+    b = m.forward_ragged(rows, ptr, len(sizes), kg, return_attention=True)
+    for key in ("mask_out", "instance_out", "edge_out", "score_out", "fused"):
+        np.testing.assert_allclose(_np(a[key]), _np(b[key]), rtol=0, atol=(TC_FUSED if key == "fused" else TC_LOGITS) / 2, err_msg=key)
