@@ -300,15 +300,21 @@ def train_block(args, dev, world, rank):
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            loss = step()
-        e1.record()
-        torch.cuda.synchronize()
-        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        # three timed regions of `steps` steps, the median kept (max over ranks per region first): the step is bound by the host
+        # issuing ~280 launches, so one scheduling hiccup of the host inflates a single region (a 25 ms/step outlier was seen once)
+        region_ms = []
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                loss = step()
+            e1.record()
+            torch.cuda.synchronize()
+            region_ms.append(e0.elapsed_time(e1))
+        ms = torch.tensor(region_ms, dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms = ms.median().reshape(1)
         _lib.timing_enable(True)
         step()
         torch.cuda.synchronize()
