@@ -1,5 +1,6 @@
 // Strided fp32 GEMM with deterministic split-K, and column sums with fp64 partials: the dense building blocks of
 // the training-mode passes (see train_common.cuh).
+#include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -71,14 +72,105 @@ __global__ void __launch_bounds__(256) split_cols_kernel(const float* __restrict
         o[2 * kp] = b_pattern ? lo : hi;
     }
 }
-static int split_operand(const float* src, long s_row, long s_k, int rows, int K, int kp, int b_pattern, int bf16, unsigned short* out, cudaStream_t st) {
+// vector forms of the two kernels above (same arithmetic, so the same bits): 8 consecutive k per thread, 16-byte stores
+__device__ __forceinline__ void split8_store(const float (&v)[8], int b_pattern, int bf16, unsigned short* o, int kp) {
+    unsigned short hi[8], lo[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) split_parts(v[q], bf16, &hi[q], &lo[q]);
+    uint4 H, L;
+    H.x = hi[0] | ((unsigned)hi[1] << 16); H.y = hi[2] | ((unsigned)hi[3] << 16); H.z = hi[4] | ((unsigned)hi[5] << 16); H.w = hi[6] | ((unsigned)hi[7] << 16);
+    L.x = lo[0] | ((unsigned)lo[1] << 16); L.y = lo[2] | ((unsigned)lo[3] << 16); L.z = lo[4] | ((unsigned)lo[5] << 16); L.w = lo[6] | ((unsigned)lo[7] << 16);
+    *reinterpret_cast<uint4*>(o) = H;
+    *reinterpret_cast<uint4*>(o + kp) = b_pattern ? H : L;
+    *reinterpret_cast<uint4*>(o + 2 * kp) = b_pattern ? L : H;
+}
+// One operand of a split launch.  mode 0: k contiguous, source rows 16-byte aligned (stride % 4 == 0) -- thread per (r, 8 k);
+// mode 1: rows contiguous in the source (element (r, k) at src[k * stride + r]) -- a 32-row x 256-k tile through shared memory.
+struct SplitOp {
+    const float* src;
+    unsigned short* out;
+    long stride;
+    int rows, K, mode, b_pattern, blocks, nbx;
+};
+constexpr int SC_K = 256;
+__device__ __forceinline__ void split_rows_body(const SplitOp& o, int kp, int bf16, int bid) {
+    const int kp8 = kp >> 3;
+    const long total = (long)o.rows * kp8;
+    for (long i = (long)bid * 256 + threadIdx.x; i < total; i += (long)o.blocks * 256) {
+        const int r = (int)(i / kp8), c = (int)(i - (long)r * kp8) * 8;
+        const float* s = o.src + (long)r * o.stride + c;
+        float v[8];
+        if (c + 8 <= o.K) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(s)), b = __ldg(reinterpret_cast<const float4*>(s) + 1);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        } else {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = c + q < o.K ? s[q] : 0.f;
+        }
+        split8_store(v, o.b_pattern, bf16, o.out + (size_t)r * 3 * kp + c, kp);
+    }
+}
+__device__ __forceinline__ void split_cols_body(const SplitOp& o, int kp, int bf16, int bid, float (*t)[33]) {
+    const int r0 = (bid % o.nbx) * 32, k0 = (bid / o.nbx) * SC_K, tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int kn = min(SC_K, kp - k0);   // a multiple of 8
+#pragma unroll 8
+    for (int j = ty; j < kn; j += 8) {
+        const int k = k0 + j, r = r0 + tx;
+        t[j][tx] = (k < o.K && r < o.rows) ? __ldg(o.src + (long)k * o.stride + r) : 0.f;
+    }
+    __syncthreads();
+    // a warp takes 8 rows x 4 octets at a time: lane -> (row, octet) so that the 32 shared-memory reads of a step fall in 32
+    // banks ((8 octet + row) mod 32), and each row receives 64 contiguous bytes per part
+    const int kgroups = (kn + 31) >> 5;
+    for (int u = ty; u < 4 * kgroups; u += 8) {
+        const int j = (u & 3) * 8 + (tx & 7), c = ((u >> 2) * 4 + (tx >> 3)) * 8, r = r0 + j;
+        if (r >= o.rows || c >= kn) continue;
+        float v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = t[c + q][j];
+        split8_store(v, o.b_pattern, bf16, o.out + (size_t)r * 3 * kp + k0 + c, kp);
+    }
+}
+// both operands of a GEMM in one launch: blocks [0, a.blocks) work on A, the rest on B
+__global__ void __launch_bounds__(256) split_pair_kernel(const SplitOp a, const SplitOp b, int kp, int bf16) {
+    __shared__ float t[SC_K][33];
+    const bool first = (int)blockIdx.x < a.blocks;
+    const SplitOp& o = first ? a : b;
+    const int bid = first ? blockIdx.x : blockIdx.x - a.blocks;
+    if (o.mode == 0) split_rows_body(o, kp, bf16, bid);
+    else split_cols_body(o, kp, bf16, bid, t);
+}
+// -> false when the operand needs the one-element kernels (unaligned k-contiguous rows)
+static bool split_op_make(const float* src, long s_row, long s_k, int rows, int K, int kp, int b_pattern, unsigned short* out, SplitOp* o) {
+    o->src = src; o->out = out; o->rows = rows; o->K = K; o->b_pattern = b_pattern;
+    if (s_k == 1) {
+        if ((s_row & 3) != 0 || (reinterpret_cast<uintptr_t>(src) & 15) != 0) return false;
+        o->mode = 0; o->stride = s_row; o->nbx = 1;
+        o->blocks = (int)std::min<long>(((long)rows * (kp >> 3) + 255) / 256, 148L * 8);
+    } else {
+        o->mode = 1; o->stride = s_k; o->nbx = ceil_div(rows, 32);
+        o->blocks = o->nbx * ceil_div(kp, SC_K);
+    }
+    return true;
+}
+static void split_operand_scalar(const float* src, long s_row, long s_k, int rows, int K, int kp, int b_pattern, int bf16, unsigned short* out, cudaStream_t st) {
     if (s_k == 1) {
         const long total = (long)rows * kp;
         split_rows_kernel<<<(int)std::min<long>((total + 255) / 256, 148L * 16), 256, 0, st>>>(src, s_row, rows, K, kp, b_pattern, bf16, out);
     } else {
         split_cols_kernel<<<dim3(ceil_div(rows, 32), ceil_div(kp, 32)), 256, 0, st>>>(src, s_k, rows, K, kp, b_pattern, bf16, out);
     }
-    return CM_OK;
+}
+// A' = [hi | lo | hi] and B' = [hi | hi | lo] of one GEMM (header of this section)
+static void split_operands(const Gemm& g, int kp, int bf16, unsigned short* a3, unsigned short* b3, cudaStream_t st) {
+    static const bool scalar = getenv("CM_TRAIN_SPLIT_SCALAR") != nullptr;   // the one-element kernels, for A/B runs
+    SplitOp a, b;
+    if (!scalar && split_op_make(g.A, g.sam, g.sak, g.M, g.K, kp, 0, a3, &a) && split_op_make(g.B, g.sbn, g.sbk, g.N, g.K, kp, 1, b3, &b)) {
+        split_pair_kernel<<<a.blocks + b.blocks, 256, 0, st>>>(a, b, kp, bf16);
+        return;
+    }
+    split_operand_scalar(g.A, g.sam, g.sak, g.M, g.K, kp, 0, bf16, a3, st);
+    split_operand_scalar(g.B, g.sbn, g.sbk, g.N, g.K, kp, 1, bf16, b3, st);
 }
 __global__ void gemm_epilogue_kernel(const float* __restrict__ raw, int M, int N, float* __restrict__ C, long ldc, const float* __restrict__ bias,
                                      int relu, const uint8_t* __restrict__ keep, float keep_scale, float alpha, int accumulate) {
@@ -163,8 +255,7 @@ static int launch_gemm_tc(const Gemm& g, cudaStream_t st, const char* name) {
     int rc;
     {
         CM_TIMED("train_split_operand", st);
-        split_operand(g.A, g.sam, g.sak, g.M, g.K, kp, 0, bf16, a3, st);
-        split_operand(g.B, g.sbn, g.sbk, g.N, g.K, kp, 1, bf16, b3, st);
+        split_operands(g, kp, bf16, a3, b3, st);
         rc = post_launch("split_operand");
     }
     if (rc == CM_OK) {
@@ -359,8 +450,46 @@ __global__ void __launch_bounds__(256) colsum_final_kernel(const double* __restr
     }
 }
 
+// up to 8 row parts (512 rows: the per-image and KG-row matrices) in one launch: the same partial sums in the same order as
+// colsum_part_kernel + colsum_final_kernel (the final's eight lanes hold one part each), so the same bits
+__global__ void __launch_bounds__(256) colsum_small_kernel(const float* __restrict__ a, int lda, int rows, int cols, float* __restrict__ out,
+                                                           int accumulate) {
+    __shared__ double sh[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
+    double total = 0.0;
+    for (int r0 = 0; r0 < rows; r0 += CS_ROWS) {
+        const int r1 = min(rows, r0 + CS_ROWS);
+        double s = 0.0;
+        if (c < cols) {
+            float v[CS_ROWS / 8];
+#pragma unroll
+            for (int k = 0; k < CS_ROWS / 8; ++k) {
+                const int r = r0 + ty + 8 * k;
+                v[k] = r < r1 ? a[(long)r * lda + c] : 0.f;
+            }
+#pragma unroll
+            for (int k = 0; k < CS_ROWS / 8; ++k) s += (double)v[k];
+        }
+        __syncthreads();
+        sh[ty][tx] = s;
+        __syncthreads();
+        if (ty == 0) {
+#pragma unroll
+            for (int k = 1; k < 8; ++k) s += sh[k][tx];
+            total += s;
+        }
+    }
+    if (ty == 0 && c < cols) out[c] = accumulate ? out[c] + (float)total : (float)total;
+}
+
 int launch_colsum(const float* a, int lda, int rows, int cols, double* part, float* out, int accumulate, cudaStream_t st) {
     const int parts = col_parts(rows);
+    if (rows <= 8 * CS_ROWS) {
+        CM_TIMED("colsum", st);
+        colsum_small_kernel<<<ceil_div(cols, 32), 256, 0, st>>>(a, lda, rows, cols, out, accumulate);
+        return post_launch("colsum");
+    }
     {
         CM_TIMED("colsum", st);
         if (rows > 0) colsum_part_kernel<<<dim3(parts, ceil_div(cols, 32)), 256, 0, st>>>(a, lda, rows, cols, part);

@@ -11,6 +11,7 @@ runs in PyTorch.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -99,8 +100,9 @@ class GnnTrainFunction(torch.autograd.Function):
         model = ctx.model
         x, row_ptr, col, w, self_w, ws, keep, held, status = ctx.held
         dev = x.device
-        if int(status.item()) & _lib.STATUS_EDGE_OVERFLOW:
-            raise _lib.CmError("RegionGraphGNN training needs a structurally symmetric edge_index (every region adjacency is)")
+        # the symmetry flag of the forward's reverse-edge table: read without stalling the step (the backward is memory-safe
+        # either way, its gradients are not) -- raised by the next training forward, or by check_deferred_status(block=True)
+        _defer_status_check(status)
         s, keep2 = model._params_struct()
         drop = _dropout_struct(ctx.masks, model.p_conv, model.p_fc)
         grads = [torch.empty_like(t) for t in held]
@@ -115,15 +117,52 @@ class GnnTrainFunction(torch.autograd.Function):
         return (None,) * 8 + tuple(grads)
 
 
+_pending_status = []   # (event, pinned int32[1]) of backward passes whose symmetry flag has not been looked at yet
+_ASYMMETRIC = "RegionGraphGNN training needs a structurally symmetric edge_index (every region adjacency is)"
+
+
+def _defer_status_check(status):
+    if os.environ.get("CM_TRAIN_EAGER_STATUS"):     # the stalling form: the error surfaces inside this backward
+        if int(status.item()) & _lib.STATUS_EDGE_OVERFLOW:
+            raise _lib.CmError(_ASYMMETRIC)
+        return
+    host = torch.empty(1, dtype=torch.int32, pin_memory=True)
+    host.copy_(status, non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(status.device))
+    _pending_status.append((ev, host))
+
+
+def check_deferred_status(block: bool = False):
+    """Raises if a finished GNN backward ran on an edge_index that was not structurally symmetric (its gradients are
+    wrong).  ``block=True`` waits for every backward still in flight -- call it before trusting the last step of a loop;
+    every training forward calls the non-blocking form."""
+    bad, keep = False, []
+    for ev, host in _pending_status:
+        if block:
+            ev.synchronize()
+        if ev.query():
+            bad = bad or bool(int(host[0]) & _lib.STATUS_EDGE_OVERFLOW)
+        else:
+            keep.append((ev, host))
+    _pending_status[:] = keep
+    if bad:
+        raise _lib.CmError(_ASYMMETRIC)
+
+
 def gnn_train_forward(model, data):
     """``RegionGraphGNN.forward`` under ``model.train()``: returns ``(mask_out, instance_out, edge_out, node_emb)``
     attached to autograd and updates the BatchNorm running statistics (momentum 0.1, unbiased variance) like ``nn.BatchNorm1d`` does."""
+    check_deferred_status()
     row_ptr, col, w, self_w = model._csr_of(data)
     x = data.x
     n = x.shape[0]
     if n == 0:
         raise ValueError("RegionGraphGNN training step on an empty graph")
-    n_edges = int(row_ptr[-1].item()) if row_ptr.shape[0] == n + 1 else 0
+    if getattr(data, "_csr", None) is not None and data._csr[0] is row_ptr:
+        n_edges = int(col.shape[0])            # batch_to_data cut the build's CSR to its edge count: no second read
+    else:
+        n_edges = int(row_ptr[-1].item()) if row_ptr.shape[0] == n + 1 else 0
     h = model.hidden_channels
     dev = x.device
     masks = []

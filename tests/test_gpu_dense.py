@@ -81,3 +81,39 @@ def test_training_gemm_building_block(m, n, k, scale, ta):
     ref = a.double() @ w.double().t() + b.double()
     assert torch.isfinite(c).all()
     assert float((c.double() - ref).abs().max() / ref.abs().max()) <= 5e-5
+
+
+_SPLIT_CASES = [(1000, 256, 256, 0), (300, 128, 300, 0), (256, 256, 4000, 1), (512, 256, 236, 1), (640, 200, 1036, 1)]
+
+
+def _split_case_outputs():
+    from camouflage_multimodal_b200 import _lib
+    lib = _lib.load()
+    outs = []
+    for m, n, k, ta in _SPLIT_CASES:
+        gen = torch.Generator().manual_seed(3 * m + k)
+        a = torch.randn((m, k), generator=gen).cuda()
+        w = torch.randn((n, k), generator=gen).cuda()
+        c = torch.full((m, n), float("nan"), device="cuda")
+        aa = a.t().contiguous() if ta else a
+        _lib.check(lib.cm_train_gemm_f32(_lib.ptr(aa), _lib.ptr(w), None, m, n, k, ta, _lib.ptr(c), _lib.stream_ptr(a.device)), "cm_train_gemm_f32")
+        outs.append(c.cpu())
+    return outs
+
+
+def test_training_gemm_vector_operand_split_equals_the_scalar_split(tmp_path):
+    """The 8-wide operand-split kernels (train_common.cu) write the same 16-bit thirds as the one-element kernels: the GEMM
+    results of a process run with CM_TRAIN_SPLIT_SCALAR=1 are bit-equal to this process's."""
+    import os
+    import subprocess
+    import sys
+    here = _split_case_outputs()
+    path = tmp_path / "scalar.pt"
+    code = ("import sys, torch; sys.path.insert(0, %r); sys.path.insert(0, %r); import test_gpu_dense as t; "
+            "torch.save(t._split_case_outputs(), %r)") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                                          os.path.dirname(os.path.abspath(__file__)), str(path))
+    subprocess.run([sys.executable, "-c", code], check=True, env=dict(os.environ, CM_TRAIN_SPLIT_SCALAR="1"), timeout=600)
+    there = torch.load(path)
+    for (m, n, k, ta), x, y in zip(_SPLIT_CASES, here, there):
+        assert torch.isfinite(x).all()
+        assert torch.equal(x, y), (m, n, k, ta)

@@ -228,3 +228,52 @@ def test_int16_label_maps_are_read_directly_and_give_identical_graphs():
     assert torch.equal(g16.csr_row_ptr[: n + 1], g32.csr_row_ptr[: n + 1]) and torch.equal(g16.csr_col[:e], g32.csr_col[:e])
     assert torch.equal(g16.node_bbox[:n], g32.node_bbox[:n]) and torch.equal(g16.x[:n], g32.x[:n])
     assert torch.equal(g16.edge_w[:e], g32.edge_w[:e])
+
+
+def test_prefetcher_returns_the_direct_build_with_batches_in_flight():
+    """RegionGraphPrefetcher (side-stream build + pinned count read): three different batches, two in flight while the
+    caller's stream is busy; every graph and Batch view bit-equal to build_region_graphs + batch_to_data on the same inputs."""
+    from camouflage_multimodal_b200.region_graph import RegionGraphPrefetcher, batch_to_data, build_region_graphs
+    batches = [synth.make_batch(20 + 4 * k, 4, seed=77 + k, device="cuda").as_decoded() for k in range(3)]
+    ins = [(b.images, b.labels.to(torch.int32), b.canny) for b in batches]
+    pf = RegionGraphPrefetcher(label_cap=544)
+    pf.submit(*ins[0])
+    busy = torch.randn(4096, 4096, device="cuda")
+    got = []
+    for k in range(3):
+        g, data = pf.get()
+        if k + 1 < 3:
+            pf.submit(*ins[k + 1])
+        busy = busy @ busy * 1e-4                     # work on the caller's stream next to the side-stream build
+        got.append((g, data, data.x.sum() + busy[0, 0] * 0))
+    torch.cuda.synchronize()
+    assert len(pf) == 0
+    for (g, data, _), inp in zip(got, ins):
+        ref = build_region_graphs(*inp, label_cap=544)
+        rdata = batch_to_data(ref)
+        n, e = ref.counts()
+        assert data.x.shape[0] == n and data.edge_index.shape[1] == e and data.num_graphs == 4
+        for name in ("x", "edge_w", "csr_row_ptr", "csr_col", "edge_index", "node_ptr", "edge_ptr", "id_of_label", "node_label", "node_bbox"):
+            a, b = getattr(g, name), getattr(ref, name)
+            lim = {"x": n, "edge_w": e, "csr_row_ptr": n + 1, "csr_col": e, "node_label": n, "node_bbox": n}.get(name)
+            if name == "edge_index":
+                a, b = a[:, :e], b[:, :e]
+            elif lim is not None:
+                a, b = a[:lim], b[:lim]
+            assert torch.equal(a, b), name
+        assert torch.equal(data.x, rdata.x) and torch.equal(data.edge_attr, rdata.edge_attr) and torch.equal(data.batch, rdata.batch)
+        assert data._csr[0].shape[0] == n + 1 and data._csr[1].shape[0] == e
+
+
+def test_prefetcher_reports_overflow_and_misuse():
+    from camouflage_multimodal_b200 import _lib
+    from camouflage_multimodal_b200.region_graph import RegionGraphPrefetcher
+    b = synth.make_batch(0, 2, seed=5, device="cuda").as_decoded()
+    with pytest.raises(ValueError):
+        RegionGraphPrefetcher()
+    pf = RegionGraphPrefetcher(label_cap=16)          # the label maps hold ~480 labels
+    with pytest.raises(RuntimeError):
+        pf.get()
+    pf.submit(b.images, b.labels.to(torch.int32), b.canny)
+    with pytest.raises(_lib.CmError, match="label >= label_cap"):
+        pf.get()

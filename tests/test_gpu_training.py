@@ -415,3 +415,37 @@ def test_standalone_fusion_modules_train(kind):
     with torch.no_grad():
         f3, _ = mod(rg.detach(), kg.detach())
     assert torch.isfinite(f2).all() and (f2 - f3).abs().max() > 1e-4
+
+
+def test_asymmetric_edge_index_is_reported_without_stalling_the_backward():
+    """The backward needs a structurally symmetric edge_index; the flag is read through pinned memory after the
+    backward was queued (no device->host read inside the step): check_deferred_status(block=True) raises, and so does
+    the next training forward; a symmetric graph leaves nothing pending."""
+    from camouflage_multimodal_b200 import _lib, training
+    from camouflage_multimodal_b200.data import Data
+    m = _model(9).train()
+    m.p_conv = m.p_fc = 0.0
+    gen = torch.Generator().manual_seed(4)
+    x = torch.randn((40, 15), generator=gen).cuda()
+    src = torch.arange(0, 39)
+    sym = torch.cat([torch.stack([src, src + 1]), torch.stack([src + 1, src])], 1)
+    asym = torch.cat([sym, torch.tensor([[0], [17]])], 1)              # 0 -> 17 without 17 -> 0
+    training.check_deferred_status(block=True)
+    for ei, bad in ((sym, False), (asym, True)):
+        data = Data(x=x, edge_index=ei.cuda(), edge_attr=torch.rand((ei.shape[1], 1), generator=gen).cuda())
+        outs = m(data)
+        sum(o.sum() for o in outs).backward()
+        assert len(training._pending_status) == 1
+        if bad:
+            with pytest.raises(_lib.CmError, match="symmetric"):
+                training.check_deferred_status(block=True)
+        else:
+            training.check_deferred_status(block=True)
+        assert not training._pending_status
+    # and through the next forward: one more asymmetric backward left pending, then a forward
+    data = Data(x=x, edge_index=asym.cuda(), edge_attr=torch.rand((asym.shape[1], 1), generator=gen).cuda())
+    sum(o.sum() for o in m(data)).backward()
+    torch.cuda.synchronize()
+    with pytest.raises(_lib.CmError, match="symmetric"):
+        m(data)
+    assert not training._pending_status
