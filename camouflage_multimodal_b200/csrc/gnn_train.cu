@@ -21,6 +21,7 @@ struct GnnTrainWs {
     float *y[4], *a[4], *g[3], *dis, *e, *t[3];
     float *mean, *invstd;   // [4][H]
     double *bn_sums, *bn_n;  // [2H + 1] column sums (+ row count) of the layer in flight; [4] global row count per layer
+    unsigned* bn_counter;    // [ceil(H / 128)] arrival counters of bn_stats_kernel (zeroed by the forward, self-resetting)
     int* rev;
     // backward scratch
     float *dA, *dB, *dT, *dz, *dpre_edge, *dpre_self, *dasrc, *dadst, *du, *dwf, *s1, *s2;
@@ -54,6 +55,7 @@ static GnnTrainWs carve_gnn_train(void* ws, const cm_gnn_params* p, int n, int e
     w.invstd = c.take<float>(4 * H);
     w.bn_sums = c.take<double>(2 * H + 1);
     w.bn_n = c.take<double>(4);
+    w.bn_counter = c.take<unsigned>((H + 127) / 128);
     w.rev = c.take<int>(E);
     w.dA = c.take<float>(N * H);
     w.dB = c.take<float>(N * H);
@@ -417,6 +419,153 @@ __global__ void bn_bwd_part_kernel(const float* __restrict__ y, const float* __r
     part[((size_t)blockIdx.x * 2) * H + c] = s;
     part[((size_t)blockIdx.x * 2 + 1) * H + c] = q;
 }
+// The statistics of a BatchNorm layer in ONE launch (H % 4 == 0): 64 rows x 128 columns per CTA (8 row lanes x 32 float4
+// lanes, eight independent loads per thread, float64 sums combined in a fixed order), the parts written to `part`; the CTA
+// that arrives last at the column tile's counter adds the parts up (fixed order: the result does not depend on which CTA
+// it is), and -- when no data-parallel hook sits between the sums and their use (`fuse_final`) -- derives what the apply
+// kernel needs.  FWD: sums = (sum x, sum x^2, n) -> mean / invstd / batch statistics.  BWD: also rewrites d (dropout +
+// ReLU gate), sums = (sum dy, sum dy xhat) -> dgamma / dbeta (this rank's sums, always) and s1 / s2.
+struct BnStats {
+    const float* y;
+    int n, H;
+    double *part, *sums;
+    unsigned* counter;
+    int fuse_final;
+    // BWD inputs
+    const float *mean, *invstd, *gamma, *beta;
+    const uint8_t* keep;
+    float scale;
+    float* d;
+    // FWD final
+    float eps;
+    float *mean_out, *invstd_out, *batch_mean, *batch_var;
+    double* n_out;
+    // BWD final
+    float *dgamma, *dbeta, *s1, *s2;
+    const double* n_glob;
+};
+template <bool BWD>
+__global__ void __launch_bounds__(256) bn_stats_kernel(const BnStats a) {
+    __shared__ double sh_s[8][128], sh_q[8][128];
+    __shared__ int sh_last;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5, H = a.H;
+    const int cb = blockIdx.y * 128, c0 = cb + tx * 4;
+    const int r0 = blockIdx.x * BN_ROWS;
+    double s[4] = {0.0, 0.0, 0.0, 0.0}, q[4] = {0.0, 0.0, 0.0, 0.0};
+    if (c0 < H) {
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int r = r0 + ty + 8 * k;
+            v[k] = r < a.n ? *reinterpret_cast<const float4*>(a.y + (size_t)r * H + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (!BWD) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float f[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const double x = f[j];
+                    s[j] += x;
+                    q[j] += x * x;
+                }
+            }
+        } else {
+            const float4 m4 = *reinterpret_cast<const float4*>(a.mean + c0), i4 = *reinterpret_cast<const float4*>(a.invstd + c0);
+            const float m[4] = {m4.x, m4.y, m4.z, m4.w}, is[4] = {i4.x, i4.y, i4.z, i4.w};
+            const float ga[4] = {a.gamma[c0], a.gamma[c0 + 1], a.gamma[c0 + 2], a.gamma[c0 + 3]};   // parameters: any 4-byte alignment
+            const float be[4] = {a.beta[c0], a.beta[c0 + 1], a.beta[c0 + 2], a.beta[c0 + 3]};
+            float4 dv4[8];
+            uchar4 kp[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int r = r0 + ty + 8 * k;
+                const size_t i = (size_t)r * H + c0;
+                dv4[k] = r < a.n ? *reinterpret_cast<const float4*>(a.d + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                kp[k] = (a.keep && r < a.n) ? *reinterpret_cast<const uchar4*>(a.keep + i) : make_uchar4(1, 1, 1, 1);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int r = r0 + ty + 8 * k;
+                if (r >= a.n) continue;
+                const float f[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+                float dv[4] = {dv4[k].x, dv4[k].y, dv4[k].z, dv4[k].w};
+                const unsigned char kk[4] = {kp[k].x, kp[k].y, kp[k].z, kp[k].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float xh = (f[j] - m[j]) * is[j];
+                    if (a.keep) dv[j] = kk[j] ? dv[j] * a.scale : 0.f;
+                    if (!(xh * ga[j] + be[j] > 0.f)) dv[j] = 0.f;
+                    s[j] += dv[j];
+                    q[j] += (double)dv[j] * xh;
+                }
+                *reinterpret_cast<float4*>(a.d + (size_t)r * H + c0) = make_float4(dv[0], dv[1], dv[2], dv[3]);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        sh_s[ty][tx * 4 + j] = s[j];
+        sh_q[ty][tx * 4 + j] = q[j];
+    }
+    __syncthreads();
+    const int col = threadIdx.x & 127, c = cb + col;
+    const bool second = threadIdx.x >= 128;   // threads 0..127 own the first sum of a column, 128..255 the second
+    {
+        double t = 0.0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += second ? sh_q[k][col] : sh_s[k][col];
+        if (c < H) a.part[((size_t)blockIdx.x * 2 + (second ? 1 : 0)) * H + c] = t;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) sh_last = atomicAdd(a.counter + blockIdx.y, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!sh_last) return;
+    __threadfence();
+    double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+    if (c < H) {
+        const double* pp = a.part + (second ? H : 0) + c;
+        const int parts = gridDim.x;
+        int p = 0;
+        for (; p + 4 <= parts; p += 4) {
+            t0 += __ldcg(pp + (size_t)(p + 0) * 2 * H);
+            t1 += __ldcg(pp + (size_t)(p + 1) * 2 * H);
+            t2 += __ldcg(pp + (size_t)(p + 2) * 2 * H);
+            t3 += __ldcg(pp + (size_t)(p + 3) * 2 * H);
+        }
+        for (; p < parts; ++p) t0 += __ldcg(pp + (size_t)p * 2 * H);
+    }
+    const double tot = (t0 + t1) + (t2 + t3);
+    if (c < H) a.sums[(second ? H : 0) + c] = tot;
+    if (!BWD && threadIdx.x == 0 && blockIdx.y == 0) a.sums[2 * H] = (double)a.n;
+    double* sh_tot = &sh_s[0][0];   // [256]: both sums of the tile's columns, for the finishing step
+    __syncthreads();
+    sh_tot[threadIdx.x] = tot;
+    __syncthreads();
+    if (threadIdx.x == 0) a.counter[blockIdx.y] = 0;   // ready for the next layer / pass
+    if (second || c >= H) return;
+    const double sum0 = sh_tot[col], sum1 = sh_tot[128 + col];
+    if (BWD) {
+        a.dbeta[c] = (float)sum0;
+        a.dgamma[c] = (float)sum1;
+        if (a.fuse_final) {
+            const double n = *a.n_glob;
+            a.s1[c] = (float)(sum0 / n);
+            a.s2[c] = (float)(sum1 / n);
+        }
+    } else if (a.fuse_final) {
+        const double n = (double)a.n;
+        if (c == 0) *a.n_out = n;
+        const double m = sum0 / n;
+        double v = sum1 / n - m * m;   // biased variance (BatchNorm1d training normalisation)
+        v = v > 0.0 ? v : 0.0;
+        a.mean_out[c] = (float)m;
+        a.invstd_out[c] = (float)(1.0 / sqrt(v + (double)a.eps));
+        if (a.batch_mean) a.batch_mean[c] = (float)m;
+        if (a.batch_var) a.batch_var[c] = (float)v;
+    }
+}
 // dgamma / dbeta are THIS rank's sums (the gradient all-reduce adds the ranks up like every other gradient)
 __global__ void bn_bwd_grads_kernel(const double* __restrict__ sums, int H, float* __restrict__ dgamma, float* __restrict__ dbeta) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -515,6 +664,7 @@ extern "C" int cm_gnn_train_forward(const cm_gnn_params* p, const float* x, cons
     cudaStream_t st = as_stream(stream);
     const int N = n_nodes, H = p->hidden, C = p->in_channels, hd = p->heads, H2 = H / 2, KC = hd * C;
     const long NH = (long)N * H;
+    cudaMemsetAsync(w.bn_counter, 0, sizeof(unsigned) * ((H + 127) / 128), st);
     {
         CM_TIMED("train_gat_fold", st);
         gat_fold_train_kernel<<<ceil_div(H * KC, 256), 256, 0, st>>>(p->conv1_lin_weight, p->conv1_att_src, p->conv1_att_dst, H, C, hd, w.u_src,
@@ -551,12 +701,23 @@ extern "C" int cm_gnn_train_forward(const cm_gnn_params* p, const float* x, cons
         }
         {
             CM_TIMED("train_bn", st);
-            bn_fwd_part_kernel<<<dim3(parts, ceil_div(H, 128)), 128, 0, st>>>(w.y[k], N, H, w.part_d);
-            bn_reduce_parts_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.part_d, parts, N, H, w.bn_sums);
-            if (int rc = bn_sync(w.bn_sums, 2 * H + 1, st)) return rc;   // data parallel: (sum x, sum x^2, n) over every rank's nodes
-            bn_fwd_final_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, H, p->bn_eps, w.mean + k * H, w.invstd + k * H,
-                                                                  bn_batch_mean ? bn_batch_mean + k * H : nullptr,
-                                                                  bn_batch_var ? bn_batch_var + k * H : nullptr, w.bn_n + k);
+            float* bmean = bn_batch_mean ? bn_batch_mean + k * H : nullptr;
+            float* bvar = bn_batch_var ? bn_batch_var + k * H : nullptr;
+            if (H % 4 == 0) {
+                BnStats b = {};
+                b.y = w.y[k]; b.n = N; b.H = H; b.part = w.part_d; b.sums = w.bn_sums; b.counter = w.bn_counter; b.fuse_final = !g_bn_sync;
+                b.eps = p->bn_eps; b.mean_out = w.mean + k * H; b.invstd_out = w.invstd + k * H; b.batch_mean = bmean; b.batch_var = bvar;
+                b.n_out = w.bn_n + k;
+                bn_stats_kernel<false><<<dim3(parts, ceil_div(H, 128)), 256, 0, st>>>(b);
+            } else {
+                bn_fwd_part_kernel<<<dim3(parts, ceil_div(H, 128)), 128, 0, st>>>(w.y[k], N, H, w.part_d);
+                bn_reduce_parts_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.part_d, parts, N, H, w.bn_sums);
+            }
+            if (g_bn_sync || H % 4 != 0) {
+                if (int rc = bn_sync(w.bn_sums, 2 * H + 1, st)) return rc;   // data parallel: (sum x, sum x^2, n) over every rank's nodes
+                bn_fwd_final_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, H, p->bn_eps, w.mean + k * H, w.invstd + k * H, bmean, bvar,
+                                                                      w.bn_n + k);
+            }
             bn_fwd_apply_kernel<<<ceil_div(NH, 256), 256, 0, st>>>(w.y[k], w.mean + k * H, w.invstd + k * H, p->bn_weight[k], p->bn_bias[k],
                                                                    k < 3 ? drop_keep(drop, k) : nullptr, k < 3 ? drop_scale(drop, k) : 1.f,
                                                                    NH, H, w.a[k]);
@@ -639,13 +800,25 @@ extern "C" int cm_gnn_backward(const cm_gnn_params* p, const float* x, const int
     for (int k = 3; k >= 0; --k) {
         {
             CM_TIMED("train_bn", st);
-            bn_bwd_part_kernel<<<dim3(parts, ceil_div(H, 128)), 128, 0, st>>>(w.y[k], w.mean + k * H, w.invstd + k * H, p->bn_weight[k],
-                                                                              p->bn_bias[k], k < 3 ? drop_keep(drop, k) : nullptr,
-                                                                              k < 3 ? drop_scale(drop, k) : 1.f, dcur, N, H, w.part_d);
-            bn_reduce_parts_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.part_d, parts, N, H, w.bn_sums);
-            bn_bwd_grads_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, H, gr->bn_weight[k], gr->bn_bias[k]);
-            if (int rc = bn_sync(w.bn_sums, 2 * H, st)) return rc;       // (sum dy, sum dy xhat) over every rank's nodes
-            bn_bwd_final_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, w.bn_n + k, H, w.s1, w.s2);
+            const uint8_t* keep_k = k < 3 ? drop_keep(drop, k) : nullptr;
+            const float scale_k = k < 3 ? drop_scale(drop, k) : 1.f;
+            if (H % 4 == 0) {
+                BnStats b = {};
+                b.y = w.y[k]; b.n = N; b.H = H; b.part = w.part_d; b.sums = w.bn_sums; b.counter = w.bn_counter; b.fuse_final = !g_bn_sync;
+                b.mean = w.mean + k * H; b.invstd = w.invstd + k * H; b.gamma = p->bn_weight[k]; b.beta = p->bn_bias[k];
+                b.keep = keep_k; b.scale = scale_k; b.d = dcur;
+                b.dgamma = gr->bn_weight[k]; b.dbeta = gr->bn_bias[k]; b.s1 = w.s1; b.s2 = w.s2; b.n_glob = w.bn_n + k;
+                bn_stats_kernel<true><<<dim3(parts, ceil_div(H, 128)), 256, 0, st>>>(b);
+            } else {
+                bn_bwd_part_kernel<<<dim3(parts, ceil_div(H, 128)), 128, 0, st>>>(w.y[k], w.mean + k * H, w.invstd + k * H, p->bn_weight[k],
+                                                                                  p->bn_bias[k], keep_k, scale_k, dcur, N, H, w.part_d);
+                bn_reduce_parts_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.part_d, parts, N, H, w.bn_sums);
+                bn_bwd_grads_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, H, gr->bn_weight[k], gr->bn_bias[k]);
+            }
+            if (g_bn_sync || H % 4 != 0) {
+                if (int rc = bn_sync(w.bn_sums, 2 * H, st)) return rc;       // (sum dy, sum dy xhat) over every rank's nodes
+                bn_bwd_final_kernel<<<ceil_div(H, 128), 128, 0, st>>>(w.bn_sums, w.bn_n + k, H, w.s1, w.s2);
+            }
             bn_bwd_apply_kernel<<<ceil_div(NH, 256), 256, 0, st>>>(w.y[k], w.mean + k * H, w.invstd + k * H, p->bn_weight[k], dcur, w.s1, w.s2,
                                                                    NH, H, dtmp);
         }

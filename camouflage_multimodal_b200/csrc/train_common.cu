@@ -298,32 +298,60 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const float* __restrict__ A,
     for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    for (int k0 = kb; k0 < ke; k0 += GK) {
+    // the next k-tile's global loads are issued before the current tile's arithmetic (registers ra / rb): the small GEMMs that
+    // run here (KG rows, per-image layers: 16 .. 64 CTAs) are bound by the latency of that load, not by the FMAs
+    float ra[4], rb[4];
+    auto load_tiles = [&](int k0) {
         if (AKC) {
             const int m = tid >> 2, kk = (tid & 3) * 4;
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const int k = k0 + kk + q;
-                As[kk + q][m] = (m0 + m < M && k < ke) ? A[(long)(m0 + m) * sam + (long)k * sak] : 0.f;
+                ra[q] = (m0 + m < M && k < ke) ? A[(long)(m0 + m) * sam + (long)k * sak] : 0.f;
             }
         } else {
             const int kk = tid >> 4, m = (tid & 15) * 4, k = k0 + kk;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) As[kk][m + q] = (m0 + m + q < M && k < ke) ? A[(long)(m0 + m + q) * sam + (long)k * sak] : 0.f;
+            for (int q = 0; q < 4; ++q) ra[q] = (m0 + m + q < M && k < ke) ? A[(long)(m0 + m + q) * sam + (long)k * sak] : 0.f;
         }
         if (BKC) {
             const int n = tid >> 2, kk = (tid & 3) * 4;
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const int k = k0 + kk + q;
-                Bs[kk + q][n] = (n0 + n < N && k < ke) ? B[(long)k * sbk + (long)(n0 + n) * sbn] : 0.f;
+                rb[q] = (n0 + n < N && k < ke) ? B[(long)k * sbk + (long)(n0 + n) * sbn] : 0.f;
             }
         } else {
             const int kk = tid >> 4, n = (tid & 15) * 4, k = k0 + kk;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) Bs[kk][n + q] = (n0 + n + q < N && k < ke) ? B[(long)k * sbk + (long)(n0 + n + q) * sbn] : 0.f;
+            for (int q = 0; q < 4; ++q) rb[q] = (n0 + n + q < N && k < ke) ? B[(long)k * sbk + (long)(n0 + n + q) * sbn] : 0.f;
         }
+    };
+    auto store_tiles = [&]() {
+        if (AKC) {
+            const int m = tid >> 2, kk = (tid & 3) * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) As[kk + q][m] = ra[q];
+        } else {
+            const int kk = tid >> 4, m = (tid & 15) * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) As[kk][m + q] = ra[q];
+        }
+        if (BKC) {
+            const int n = tid >> 2, kk = (tid & 3) * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) Bs[kk + q][n] = rb[q];
+        } else {
+            const int kk = tid >> 4, n = (tid & 15) * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) Bs[kk][n + q] = rb[q];
+        }
+    };
+    if (kb < ke) load_tiles(kb);
+    for (int k0 = kb; k0 < ke; k0 += GK) {
+        store_tiles();
         __syncthreads();
+        if (k0 + GK < ke) load_tiles(k0 + GK);
 #pragma unroll
         for (int kk = 0; kk < GK; ++kk) {
             const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
