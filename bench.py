@@ -325,6 +325,22 @@ def train_block(args, dev, world, rank):
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         ms = ms.median().reshape(1)
+        # how long the host needs to ISSUE a step (no synchronisation inside the loop; the queue is drained before and after)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step()
+        host_ms = (time.perf_counter() - t0) * 1e3 / steps
+        torch.cuda.synchronize()
+        if args.train_host_profile and rank == 0:
+            import cProfile
+            import pstats
+            prof = cProfile.Profile()
+            prof.enable()
+            for _ in range(steps):
+                step()
+            prof.disable()
+            torch.cuda.synchronize()
+            pstats.Stats(prof, stream=sys.stderr).sort_stats("tottime").print_stats(35)
         _lib.timing_enable(True)
         step()
         torch.cuda.synchronize()
@@ -338,7 +354,7 @@ def train_block(args, dev, world, rank):
                         "+ BatchNorm-statistics and gradient all-reduce + clip + AdamW)" + ("" if prefetch is None else "; the next batch's graph build overlaps the step on a side stream"),
             "value": steps * B * world / (float(ms.item()) / 1e3), "unit": "images/sec", "ms_per_step": float(ms.item()) / steps,
             "steps": steps, "batch_per_gpu": B, "n_gpus": world, "loss": float(loss.detach()), "launches_per_step": int(sum(v[0] for v in rep.values())),
-            "kernel_ms_per_step": sum(v[1] for v in rep.values()), "bn_sync": sync is not None, "graph_prefetch": prefetch is not None,
+            "kernel_ms_per_step": sum(v[1] for v in rep.values()), "bn_sync": sync is not None, "graph_prefetch": prefetch is not None, "host_issue_ms_per_step": round(host_ms, 3),
             "kernels": {k: ([int(v[0]), round(v[1], 4)] if args.train_all_kernels else round(v[1], 4)) for k, v in top}}
 
 
@@ -806,6 +822,7 @@ def main():
     ap.add_argument("--byte-masks", action="store_true",
                     help="e2e: send the Canny map and the ground truth one BYTE per pixel (default: one bit per pixel, unpacked on the device)")
     ap.add_argument("--train-batch", type=int, default=16)
+    ap.add_argument("--train-host-profile", action="store_true", help="training block: cProfile of the host side of 20 steps, to stderr")
     ap.add_argument("--train-all-kernels", action="store_true", help="training block: every timed scope as [count, ms] instead of the top eight")
     ap.add_argument("--train-inline-build", action="store_true",
                     help="training step: build the region graphs at the top of the step (with its host read of the counts) instead of prefetching the next batch's on a side stream")

@@ -7,6 +7,8 @@
 // reaches the KG side sums over images in the ordinary weight-gradient reductions).  Attention in both directions is
 // written out per (row, head) with the probabilities saved for the backward; all reductions are gathers or
 // fixed-order sums (no float atomics), dense layers are the fp32 GEMMs of train_common.cu.
+#include <stdlib.h>
+
 #include "train_common.cuh"
 
 namespace cm {
@@ -336,6 +338,160 @@ __global__ void __launch_bounds__(256) attn_k2r_bwd_b_kernel(const float* __rest
     }
 }
 
+// ---------------------------------------------------------------- attention building blocks for head_dim 32, K <= 16
+// The kernels above walk a graph's region rows one at a time per warp (kg->rg) or per thread (dK1 / dV1): at 480 rows per
+// image those are 480-step dependent chains with strided row reads -- 0.93 ms of a 4.8 ms step.  Same sums, laid out for the
+// machine: (i) scores of every region row against its graph's K query rows from a shared-memory tile, (ii) row operations
+// (softmax / its backward) with a warp per (graph, query row, head) over contiguous memory, (iii) coefficient x row
+// accumulation with a CTA per (graph, head): eight warps take 32 rows at a time, lane = channel, sixteen running sums each,
+// combined in a fixed order (deterministic; the order differs from the sequential kernels, so results agree to rounding).
+constexpr int FA_KMAX = 16;
+static bool attn_fast_ok(int K, int D, int H) {
+    static const bool off = getenv("CM_TRAIN_ATTN_SEQUENTIAL") != nullptr;   // the kernels above, for A/B runs
+    return !off && H > 0 && D == 32 * H && K >= 1 && K <= FA_KMAX && D <= 256;
+}
+
+// out[(h K + k) M + m] = scale * <Qg[g(m) K + k, h 32 ..], X[m, xoff + h 32 ..]>; 32 region rows per CTA, thread = (row, head)
+__global__ void __launch_bounds__(256) attn_scores32_kernel(const float* __restrict__ Qg, const float* __restrict__ X, int ldx, int xoff,
+                                                            const int* __restrict__ node_ptr, int G, int M, int K, int D, int H, float scale,
+                                                            float* __restrict__ out) {
+    __shared__ float xs[32 * 257];
+    const int mb = blockIdx.x * 32, ld = D + 1;
+    for (int i = threadIdx.x; i < 32 * D; i += 256) {
+        const int r = i / D, c = i - r * D;
+        xs[r * ld + c] = mb + r < M ? X[(size_t)(mb + r) * ldx + xoff + c] : 0.f;
+    }
+    __syncthreads();
+    const int r = threadIdx.x & 31, m = mb + r;
+    if (m >= M) return;
+    const int g = ft_graph_of(node_ptr, G, m);
+    for (int h = threadIdx.x >> 5; h < H; h += 8) {
+        float x[32];
+#pragma unroll
+        for (int d = 0; d < 32; ++d) x[d] = xs[r * ld + h * 32 + d];
+        for (int k = 0; k < K; ++k) {
+            const float4* q = reinterpret_cast<const float4*>(Qg + ((size_t)g * K + k) * D + h * 32);
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+                const float4 a = __ldg(q + j), b = __ldg(q + j + 1);
+                s0 = fmaf(a.x, x[4 * j], s0); s0 = fmaf(a.y, x[4 * j + 1], s0); s0 = fmaf(a.z, x[4 * j + 2], s0); s0 = fmaf(a.w, x[4 * j + 3], s0);
+                s1 = fmaf(b.x, x[4 * j + 4], s1); s1 = fmaf(b.y, x[4 * j + 5], s1); s1 = fmaf(b.z, x[4 * j + 6], s1); s1 = fmaf(b.w, x[4 * j + 7], s1);
+            }
+            out[((size_t)h * K + k) * M + m] = (s0 + s1) * scale;
+        }
+    }
+}
+// one warp per (graph, query row, head): P[(h K + k) M + m0 .. m1) raw scores -> softmax probabilities, in place
+__global__ void __launch_bounds__(256) attn_softmax_rows_kernel(const int* __restrict__ node_ptr, int G, int M, int K, int H, float* __restrict__ P) {
+    const int wid = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (wid >= G * K * H) return;
+    const int g = wid / (K * H), k = (wid / H) % K, h = wid % H;
+    const int m0 = node_ptr[g], m1 = node_ptr[g + 1];
+    float* pr = P + ((size_t)h * K + k) * M;
+    float mx = -INFINITY;
+    for (int m = m0 + lane; m < m1; m += 32) mx = fmaxf(mx, pr[m]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int m = m0 + lane; m < m1; m += 32) {
+        const float e = expf(pr[m] - mx);
+        pr[m] = e;
+        sum += e;
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.0f / sum;
+    for (int m = m0 + lane; m < m1; m += 32) pr[m] *= inv;
+}
+// softmax backward over the same rows: T holds t = <dO, V> (raw); T <- P * (t' - sum P t'), t' = t after the dropout mask
+__global__ void __launch_bounds__(256) attn_dsoftmax_rows_kernel(const float* __restrict__ P, const int* __restrict__ node_ptr, int G, int M, int K,
+                                                                 int H, const uint8_t* __restrict__ keep, float keep_scale, float* __restrict__ T) {
+    const int wid = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (wid >= G * K * H) return;
+    const int g = wid / (K * H), k = (wid / H) % K, h = wid % H;
+    const int m0 = node_ptr[g], m1 = node_ptr[g + 1];
+    const size_t row = ((size_t)h * K + k) * M;
+    float S = 0.f;
+    for (int m = m0 + lane; m < m1; m += 32) {
+        float t = T[row + m];
+        if (keep) t = keep[row + m] ? t * keep_scale : 0.f;
+        T[row + m] = t;
+        S = fmaf(P[row + m], t, S);
+    }
+    S = warp_sum(S);
+    for (int m = m0 + lane; m < m1; m += 32) T[row + m] = P[row + m] * (T[row + m] - S);
+}
+
+struct AccumPair {
+    const float* coef;        // LAYOUT 0: [M, H, K]   LAYOUT 1: [H, K, M]
+    const uint8_t* keep;      // dropout mask over coef (same layout) or NULL
+    float keep_scale;
+    const float* x;           // rows [M, ldx], channel h 32 + d at x[m ldx + h 32 + d]
+    int ldx;
+    float out_scale;
+    float* out;               // out[(g K + k) ldo + h 32 + d]
+    int ldo;
+};
+// out_p[g, k, h, d] = out_scale_p * sum over the graph's rows m of coef_p[m, h, k] * x_p[m, h, d]
+template <int LAYOUT, int PAIRS>
+__global__ void __launch_bounds__(256) attn_accum32_kernel(const AccumPair p0, const AccumPair p1, const int* __restrict__ node_ptr, int M, int K,
+                                                           int H) {
+    __shared__ float red[PAIRS][8][FA_KMAX][32];
+    const int g = blockIdx.x, h = blockIdx.y, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = node_ptr[g], m1 = node_ptr[g + 1];
+    float acc[PAIRS][FA_KMAX];
+#pragma unroll
+    for (int p = 0; p < PAIRS; ++p)
+#pragma unroll
+        for (int k = 0; k < FA_KMAX; ++k) acc[p][k] = 0.f;
+    for (int base = m0 + 32 * w; base < m1; base += 256) {
+        const int mine = base + lane, cnt = min(32, m1 - base);
+        float ck[PAIRS][FA_KMAX];
+#pragma unroll
+        for (int p = 0; p < PAIRS; ++p) {
+            const AccumPair& a = p == 0 ? p0 : p1;
+#pragma unroll
+            for (int k = 0; k < FA_KMAX; ++k) {
+                float c = 0.f;
+                if (k < K && mine < m1) {
+                    const size_t i = LAYOUT == 0 ? ((size_t)mine * H + h) * K + k : ((size_t)h * K + k) * M + mine;
+                    c = a.coef[i];
+                    if (a.keep) c = a.keep[i] ? c * a.keep_scale : 0.f;
+                }
+                ck[p][k] = c;
+            }
+        }
+        for (int j0 = 0; j0 < cnt; j0 += 4) {
+            float xv[PAIRS][4];
+#pragma unroll
+            for (int p = 0; p < PAIRS; ++p) {
+                const AccumPair& a = p == 0 ? p0 : p1;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) xv[p][u] = j0 + u < cnt ? a.x[(size_t)(base + j0 + u) * a.ldx + h * 32 + lane] : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int p = 0; p < PAIRS; ++p)
+#pragma unroll
+                    for (int k = 0; k < FA_KMAX; ++k)
+                        acc[p][k] = fmaf(__shfl_sync(0xffffffffu, ck[p][k], (j0 + u) & 31), xv[p][u], acc[p][k]);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < PAIRS; ++p)
+#pragma unroll
+        for (int k = 0; k < FA_KMAX; ++k) red[p][w][k][lane] = acc[p][k];
+    __syncthreads();
+    for (int i = threadIdx.x; i < PAIRS * K * 32; i += 256) {
+        const int p = i / (K * 32), k = (i / 32) % K, d = i & 31;
+        float t = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < 8; ++ww) t += red[p][ww][k][d];
+        const AccumPair& a = p == 0 ? p0 : p1;
+        a.out[((size_t)g * K + k) * a.ldo + h * 32 + d] = t * a.out_scale;
+    }
+}
+
 // ---------------------------------------------------------------- pooling, sigmoid
 // out[g, off .. off+D) = mean of rows seg[g] .. seg[g+1]-1 (seg == NULL: fixed `len` rows per graph)
 __global__ void ft_mean_pool_kernel(const float* __restrict__ in, int D, const int* __restrict__ seg, int len, int G, float* __restrict__ out,
@@ -602,8 +758,15 @@ extern "C" int cm_fusion_train_forward(const cm_fusion_params* p, const float* r
     launch_gemm(gemm_nt(w.R, D, p->k2r_in_w + (size_t)D * D, w.KV2, 2 * D, M, 2 * D, D, p->k2r_in_b + D, 0), st, "train_linear");
     {
         CM_TIMED("train_attn_k2r_fwd", st);
-        attn_k2r_fwd_kernel<<<ceil_div((long)GK * H, 8), 256, 0, st>>>(w.Q2, w.KV2, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 2),
-                                                                       fdrop_scale(drop, 2), w.P2, w.O2);
+        if (attn_fast_ok(K, D, H)) {
+            attn_scores32_kernel<<<ceil_div(M, 32), 256, 0, st>>>(w.Q2, w.KV2, 2 * D, 0, node_ptr, G, M, K, D, H, scale, w.P2);
+            attn_softmax_rows_kernel<<<ceil_div((long)GK * H, 8), 256, 0, st>>>(node_ptr, G, M, K, H, w.P2);
+            const AccumPair pv = {w.P2, fdrop_keep(drop, 2), fdrop_scale(drop, 2), w.KV2 + D, 2 * D, 1.f, w.O2, D};
+            attn_accum32_kernel<1, 1><<<dim3(G, H), 256, 0, st>>>(pv, pv, node_ptr, M, K, H);
+        } else {
+            attn_k2r_fwd_kernel<<<ceil_div((long)GK * H, 8), 256, 0, st>>>(w.Q2, w.KV2, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 2),
+                                                                           fdrop_scale(drop, 2), w.P2, w.O2);
+        }
     }
     launch_gemm(gemm_nt(w.O2, D, p->k2r_out_w, w.Y1, D, GK, D, D, p->k2r_out_b, 0), st, "train_linear");
     launch_add(w.Y1, w.Kp, w.Y1, (long)GK * D, st);
@@ -700,8 +863,16 @@ extern "C" int cm_fusion_backward(const cm_fusion_params* p, const float* rg, co
     launch_gemm(gemm_nn(w.dkB, D, p->k2r_out_w, w.dkA, D, GK, D, D), st, "train_dgrad");   // dkA = dO2
     {
         CM_TIMED("train_attn_k2r_bwd", st);
-        attn_k2r_bwd_a_kernel<<<ceil_div((long)GK * H, 8), 256, 0, st>>>(w.KV2, w.P2, w.dkA, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 2),
-                                                                         fdrop_scale(drop, 2), w.dP2, w.dkB);   // dkB = dQ2
+        if (attn_fast_ok(K, D, H)) {
+            attn_scores32_kernel<<<ceil_div(M, 32), 256, 0, st>>>(w.dkA, w.KV2, 2 * D, D, node_ptr, G, M, K, D, H, 1.f, w.dP2);   // t = <dO2, V2>
+            attn_dsoftmax_rows_kernel<<<ceil_div((long)GK * H, 8), 256, 0, st>>>(w.P2, node_ptr, G, M, K, H, fdrop_keep(drop, 2),
+                                                                                 fdrop_scale(drop, 2), w.dP2);
+            const AccumPair dq = {w.dP2, nullptr, 1.f, w.KV2, 2 * D, scale, w.dkB, D};                                            // dkB = dQ2
+            attn_accum32_kernel<1, 1><<<dim3(G, H), 256, 0, st>>>(dq, dq, node_ptr, M, K, H);
+        } else {
+            attn_k2r_bwd_a_kernel<<<ceil_div((long)GK * H, 8), 256, 0, st>>>(w.KV2, w.P2, w.dkA, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 2),
+                                                                             fdrop_scale(drop, 2), w.dP2, w.dkB);   // dkB = dQ2
+        }
         attn_k2r_bwd_b_kernel<<<ceil_div(M, 8), 256, 0, st>>>(w.Q2, w.P2, w.dP2, w.dkA, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 2),
                                                               fdrop_scale(drop, 2), w.dC);                       // dC = dKV2 [M,2D]
     }
@@ -740,8 +911,14 @@ extern "C" int cm_fusion_backward(const cm_fusion_params* p, const float* rg, co
         CM_TIMED("train_attn_r2k_bwd", st);
         attn_r2k_bwd_kernel<<<ceil_div((long)M * H, 8), 256, 0, st>>>(w.KV1, w.P1, w.dA, node_ptr, G, M, K, D, H, scale, fdrop_keep(drop, 0),
                                                                       fdrop_scale(drop, 0), w.dP1, w.dB);   // dB = dQ1
-        attn_r2k_bwd_kv_kernel<<<dim3(G, H), 256, 0, st>>>(w.Q1, w.P1, w.dP1, w.dA, node_ptr, K, D, H, scale, fdrop_keep(drop, 0),
-                                                           fdrop_scale(drop, 0), w.dKV1);
+        if (attn_fast_ok(K, D, H)) {
+            const AccumPair dk = {w.dP1, nullptr, 1.f, w.Q1, D, scale, w.dKV1, 2 * D};
+            const AccumPair dv = {w.P1, fdrop_keep(drop, 0), fdrop_scale(drop, 0), w.dA, D, 1.f, w.dKV1 + D, 2 * D};
+            attn_accum32_kernel<0, 2><<<dim3(G, H), 256, 0, st>>>(dk, dv, node_ptr, M, K, H);
+        } else {
+            attn_r2k_bwd_kv_kernel<<<dim3(G, H), 256, 0, st>>>(w.Q1, w.P1, w.dP1, w.dA, node_ptr, K, D, H, scale, fdrop_keep(drop, 0),
+                                                               fdrop_scale(drop, 0), w.dKV1);
+        }
     }
     launch_gemm(gemm_tn(w.dB, D, w.R, D, gr->r2k_in_w, M, D, D, w.part_f, S), st, "train_wgrad");
     launch_colsum(w.dB, D, M, D, w.part_d, gr->r2k_in_b, 0, st);

@@ -37,17 +37,22 @@ class _FusionRunner:
 
     def __init__(self, fusion, heads=None, num_classes=2):
         self.fusion, self.heads, self.num_classes = fusion, heads, num_classes
+        self._tensor_list = None
         self._key = None
         self._struct = None
         self._fold_key = None
         self._fold = None
 
     def _tensors(self):
-        ts = list(self.fusion.parameters())
-        if self.heads is not None:
-            for h in self.heads:
-                ts += list(h.parameters())
-        return ts
+        # the Parameter objects, collected once: walking the module tree costs 0.4 ms and a step asks four times
+        # (modules keep their Parameter objects through .to() / load_state_dict; the key in params() sees new storage)
+        if self._tensor_list is None:
+            ts = list(self.fusion.parameters())
+            if self.heads is not None:
+                for h in self.heads:
+                    ts += list(h.parameters())
+            self._tensor_list = ts
+        return self._tensor_list
 
     def params(self):
         ts = self._tensors()

@@ -11,6 +11,7 @@ runs in PyTorch.
 from __future__ import annotations
 
 import ctypes as C
+import math
 import os
 
 import torch
@@ -86,6 +87,7 @@ class GnnTrainFunction(torch.autograd.Function):
                                             p(ws), ws_bytes, p(mask_out), p(inst_out), p(edge_out), p(emb), p(bmean), p(bvar),
                                             p(status), _lib.stream_ptr(dev)), "cm_gnn_train_forward")
         ctx.model, ctx.n_edges, ctx.masks = model, n_edges, masks
+        ctx.params_struct = s      # the same tensors serve the backward (autograd forbids changing them in between)
         ctx.held = (x, row_ptr, col, w, self_w, ws, keep, held, status)
         sync = BatchNormSync.active
         if sync is not None:
@@ -103,7 +105,7 @@ class GnnTrainFunction(torch.autograd.Function):
         # the symmetry flag of the forward's reverse-edge table: read without stalling the step (the backward is memory-safe
         # either way, its gradients are not) -- raised by the next training forward, or by check_deferred_status(block=True)
         _defer_status_check(status)
-        s, keep2 = model._params_struct()
+        s = ctx.params_struct
         drop = _dropout_struct(ctx.masks, model.p_conv, model.p_fc)
         grads = [torch.empty_like(t) for t in held]
         g = _gnn_grads_struct(grads)
@@ -115,6 +117,26 @@ class GnnTrainFunction(torch.autograd.Function):
         if BatchNormSync.active is not None:
             BatchNormSync.active.raise_pending()
         return (None,) * 8 + tuple(grads)
+
+
+def keep_masks(shapes, probs, device):
+    """Dropout keep masks (uint8, 1 = keep with probability 1 - p) for a list of sites: ``None`` where the shape is
+    ``None`` or p <= 0.  All sites with the same p are drawn by ONE ``torch.rand`` + ONE compare (the masks are views of
+    one byte buffer, each starting on a 16-byte boundary) -- two launches per distinct p instead of three per site."""
+    out = [None] * len(shapes)
+    by_p = {}
+    for i, (sh, p) in enumerate(zip(shapes, probs)):
+        if sh is not None and p > 0:
+            by_p.setdefault(float(p), []).append(i)
+    for p, idx in by_p.items():
+        offs, total = [], 0
+        for i in idx:
+            offs.append(total)
+            total += (math.prod(shapes[i]) + 15) // 16 * 16
+        keep = (torch.rand(total, device=device) >= p).view(torch.uint8)
+        for i, o in zip(idx, offs):
+            out[i] = keep[o:o + math.prod(shapes[i])].view(shapes[i])
+    return out
 
 
 _pending_status = []   # (event, pinned int32[1]) of backward passes whose symmetry flag has not been looked at yet
@@ -165,11 +187,7 @@ def gnn_train_forward(model, data):
         n_edges = int(row_ptr[-1].item()) if row_ptr.shape[0] == n + 1 else 0
     h = model.hidden_channels
     dev = x.device
-    masks = []
-    for k in range(7):
-        p_drop = model.p_conv if k < 3 else model.p_fc
-        width = h if k < 4 else h // 2
-        masks.append((torch.rand((n, width), device=dev) >= p_drop).to(torch.uint8) if p_drop > 0 else None)
+    masks = keep_masks([(n, h if k < 4 else h // 2) for k in range(7)], [model.p_conv if k < 3 else model.p_fc for k in range(7)], dev)
     params = _gnn_param_list(model)
     return GnnTrainFunction.apply(model, x, row_ptr, col, w, self_w, n_edges, masks, *params)
 
@@ -183,8 +201,18 @@ def update_bn_running_stats(model, batch_mean, batch_var, n):
             unbias = n / torch.clamp(n - 1, min=1)
         else:
             unbias = n / max(n - 1, 1)
-        for k, bn in enumerate((model.bn1, model.bn2, model.bn3, model.bn4)):
-            m = bn.momentum if bn.momentum is not None else 0.1
+        bns = (model.bn1, model.bn2, model.bn3, model.bn4)
+        moms = [bn.momentum if bn.momentum is not None else 0.1 for bn in bns]
+        if len(set(moms)) == 1:     # the usual case: the same arithmetic as the loop below in 6 launches instead of 28
+            m = moms[0]
+            means, vars_ = [bn.running_mean for bn in bns], [bn.running_var for bn in bns]
+            torch._foreach_mul_(means + vars_, 1 - m)
+            torch._foreach_add_(means, list(batch_mean.unbind(0)), alpha=m)
+            torch._foreach_add_(vars_, list((batch_var * unbias * m).unbind(0)))
+            torch._foreach_add_([bn.num_batches_tracked for bn in bns], 1)
+            return
+        for k, bn in enumerate(bns):
+            m = moms[k]
             bn.running_mean.mul_(1 - m).add_(batch_mean[k], alpha=m)
             bn.running_var.mul_(1 - m).add_(batch_var[k] * unbias * m)
             bn.num_batches_tracked += 1
@@ -373,7 +401,7 @@ def fusion_dropout_masks(runner, p_drop, G, M, K, device):
         shapes = [(G, D), (G, D // 2), None, None, None] + [(G, D // 4)] * 4
     if runner.heads is None:
         shapes = shapes[:5] + [None] * 4
-    return [None if sh is None else (torch.rand(sh, device=device) >= p_drop).to(torch.uint8) for sh in shapes]
+    return keep_masks(shapes, [p_drop] * len(shapes), device)
 
 
 def fusion_train_forward(det, rg_rows, node_ptr, n_graphs, kg, masks="auto"):

@@ -449,3 +449,44 @@ def test_asymmetric_edge_index_is_reported_without_stalling_the_backward():
     with pytest.raises(_lib.CmError, match="symmetric"):
         m(data)
     assert not training._pending_status
+
+
+def _attention_path_grads():
+    """One ragged training step of the default detector with every dropout mask fixed -> outputs + all gradients (CPU)."""
+    from camouflage_multimodal_b200 import training
+    det = _detector(6).train()
+    gen = torch.Generator().manual_seed(19)
+    sizes = [33, 410, 1, 257, 96]
+    M, G, K = sum(sizes), len(sizes), 13
+    rows = (torch.randn((M, 128), generator=gen).clamp_min(0) * 0.5).cuda().requires_grad_(True)
+    kg = (torch.randn((K, 128), generator=gen).clamp_min(0) * 0.25).cuda().requires_grad_(True)
+    node_ptr = torch.tensor([0] + list(np.cumsum(sizes)), dtype=torch.int32, device="cuda")
+    shapes = [(M, 8, K), (M, 512), (8, K, M), (G * K, 512), (G, 256)] + [(G, 128)] * 4
+    masks = [(torch.rand(sh, generator=gen) >= 0.1).to(torch.uint8).cuda() for sh in shapes]
+    outs = training.fusion_train_forward(det, rows, node_ptr, G, kg[None], masks=masks)
+    sum((o * torch.linspace(0.5, 1.5, o.numel(), device="cuda").view_as(o)).sum() for o in outs[1:]).backward()
+    res = {"out%d" % i: o.detach().cpu() for i, o in enumerate(outs)}
+    res.update({n: p.grad.detach().cpu() for n, p in det.named_parameters()})
+    res["<rg rows>"], res["<kg rows>"] = rows.grad.cpu(), kg.grad.cpu()
+    return res
+
+
+def test_tiled_attention_kernels_agree_with_the_sequential_kernels(tmp_path):
+    """head_dim 32, K <= 16 takes the tiled attention kernels of fusion_train.cu; CM_TRAIN_ATTN_SEQUENTIAL=1 (another
+    process) keeps the one-row-at-a-time kernels.  Same sums in another order: every output and gradient agrees to
+    1e-5 of its largest magnitude (graphs of 1 .. 410 rows, dropout masks on every site)."""
+    import os
+    import subprocess
+    import sys
+    here = _attention_path_grads()
+    path = tmp_path / "sequential.pt"
+    code = ("import sys, torch; sys.path.insert(0, %r); sys.path.insert(0, %r); import test_gpu_training as t; "
+            "torch.save(t._attention_path_grads(), %r)") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                                           os.path.dirname(os.path.abspath(__file__)), str(path))
+    subprocess.run([sys.executable, "-c", code], check=True, env=dict(os.environ, CM_TRAIN_ATTN_SEQUENTIAL="1"), timeout=600)
+    there = torch.load(path)
+    assert set(here) == set(there)
+    for name in here:
+        a, b = here[name].double(), there[name].double()
+        assert torch.isfinite(a).all(), name
+        assert float((a - b).abs().max()) <= 1e-5 * float(b.abs().max()) + 1e-12, name
