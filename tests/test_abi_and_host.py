@@ -289,3 +289,73 @@ def test_pack_labels10_bit_layout():
     assert stream.shape == (20,)
     big = int.from_bytes(stream.tobytes(), "little")
     assert [(big >> (10 * i)) & 1023 for i in range(16)] == lab.reshape(-1).tolist()
+
+
+def test_keep_masks_one_draw_per_probability():
+    """training.keep_masks: uint8 views of one byte buffer per distinct p, 16-byte aligned starts, None where the site
+    has no dropout; the kept fraction is 1 - p."""
+    from camouflage_multimodal_b200.training import keep_masks
+    torch.manual_seed(0)
+    shapes = [(1000, 33), None, (7, 5, 11), (64,), (300, 128)]
+    probs = [0.3, 0.3, 0.3, 0.0, 0.2]
+    masks = keep_masks(shapes, probs, "cpu")
+    assert masks[1] is None and masks[3] is None
+    for i in (0, 2, 4):
+        m = masks[i]
+        assert m.dtype == torch.uint8 and tuple(m.shape) == shapes[i] and m.is_contiguous() and m.data_ptr() % 16 == 0
+        assert set(m.unique().tolist()) <= {0, 1}
+    assert abs(masks[0].float().mean().item() - 0.7) < 0.01 and abs(masks[4].float().mean().item() - 0.8) < 0.01
+    assert masks[0].untyped_storage().data_ptr() == masks[2].untyped_storage().data_ptr()      # same draw
+    assert masks[0].untyped_storage().data_ptr() != masks[4].untyped_storage().data_ptr()
+    assert keep_masks([(4, 4)], [0.0], "cpu") == [None]
+
+
+_ISOLATION_WORKER = r"""
+import os, sys, subprocess, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+if "--train-only" in sys.argv:      # what bench.py's child does with its environment: a process group of the children's own
+    dist.init_process_group("gloo")
+    t = torch.ones(1) * (int(os.environ["RANK"]) + 1)
+    dist.all_reduce(t)
+    if dist.get_rank() == 0:
+        print('{"value": %d}' % int(t.item()), flush=True)
+    dist.destroy_process_group()
+    sys.exit(0)
+import argparse, bench
+bench.__file__ = os.path.abspath(__file__)          # train_block_isolated re-runs "this file" with --train-only
+args = argparse.Namespace(steps=2, warmup=3, train_batch=16, train_all_kernels=False, train_inline_build=False,
+                          train_host_profile=False, train_timeout=120)
+world, rank = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"])
+res = bench.train_block_isolated(args, world, rank)
+assert (res == {"value": 3}) if rank == 0 else (res is None), res
+dist.init_process_group("gloo")                     # the parent's own group afterwards, on the launcher's store
+t = torch.ones(1) * 10
+dist.all_reduce(t)
+assert int(t.item()) == 10 * world
+dist.destroy_process_group()
+print("rank", rank, "ok", flush=True)
+"""
+
+
+def test_bench_training_block_isolation_under_torchrun(tmp_path):
+    """bench.train_block_isolated: every rank starts a child with RANK / WORLD_SIZE kept, MASTER_PORT + 23 and no agent
+    store, the children rendezvous among themselves, rank 0's child's JSON line comes back, and the parents' own process
+    group works afterwards (2 ranks under torch.distributed.run, gloo).  Failure paths: a child that exits non-zero and a
+    child that outlives the limit both yield {"unavailable": ...}."""
+    script = tmp_path / "iso.py"
+    script.write_text(_ISOLATION_WORKER)
+    port = str(31000 + os.getpid() % 2000)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", port, str(script), ROOT], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=300)
+    out = r.stdout.decode()
+    assert r.returncode == 0, out
+    assert "rank 0 ok" in out and "rank 1 ok" in out
+    import argparse
+    sys.path.insert(0, ROOT)
+    import bench
+    args = argparse.Namespace(steps=2, warmup=3, train_batch=16, train_all_kernels=False, train_inline_build=False,
+                              train_host_profile=False, train_timeout=1)
+    assert "did not finish" in bench.train_block_isolated(args, 1, 0)["unavailable"]      # import torch alone takes longer than 1 s
+    if not torch.cuda.is_available():
+        args.train_timeout = 120
+        assert "exited with code" in bench.train_block_isolated(args, 1, 0)["unavailable"]    # no CUDA device: SystemExit in the child
