@@ -359,3 +359,40 @@ def test_bench_training_block_isolation_under_torchrun(tmp_path):
     if not torch.cuda.is_available():
         args.train_timeout = 120
         assert "exited with code" in bench.train_block_isolated(args, 1, 0)["unavailable"]    # no CUDA device: SystemExit in the child
+
+
+def test_running_statistics_update_matches_batchnorm1d():
+    """training.update_bn_running_stats (the _foreach form) == what nn.BatchNorm1d does with the same batch in train
+    mode: momentum 0.1, unbiased variance, num_batches_tracked; Python-int and 0-dim-tensor row counts agree."""
+    import torch.nn as nn
+    from camouflage_multimodal_b200.training import update_bn_running_stats
+    torch.manual_seed(3)
+    n, h = 37, 16
+
+    class M:
+        pass
+    xs = [torch.randn(n, h) * (k + 1) + k for k in range(4)]
+    ref = [nn.BatchNorm1d(h).train() for _ in range(4)]
+    for bn, x in zip(ref, xs):
+        bn(x)
+        bn(x)
+    outs = []
+    for count in (n, torch.tensor(float(n))):
+        m = M()
+        m.bn1, m.bn2, m.bn3, m.bn4 = (nn.BatchNorm1d(h) for _ in range(4))
+        mean = torch.stack([x.mean(0) for x in xs])
+        var = torch.stack([x.var(0, unbiased=False) for x in xs])
+        update_bn_running_stats(m, mean, var, count)
+        update_bn_running_stats(m, mean, var, count)
+        outs.append(m)
+        for bn, r in zip((m.bn1, m.bn2, m.bn3, m.bn4), ref):
+            torch.testing.assert_close(bn.running_mean, r.running_mean, rtol=1e-6, atol=1e-6)
+            torch.testing.assert_close(bn.running_var, r.running_var, rtol=1e-5, atol=1e-6)
+            assert int(bn.num_batches_tracked) == 2
+    for a, b in zip((outs[0].bn1, outs[0].bn4), (outs[1].bn1, outs[1].bn4)):
+        torch.testing.assert_close(a.running_var, b.running_var, rtol=1e-6, atol=1e-7)
+    m = outs[0]
+    m.bn2.momentum = 0.3                      # mixed momenta: the per-layer loop
+    before = m.bn2.running_mean.clone()
+    update_bn_running_stats(m, mean, var, n)
+    torch.testing.assert_close(m.bn2.running_mean, before * 0.7 + mean[1] * 0.3, rtol=1e-6, atol=1e-6)
