@@ -887,7 +887,7 @@ def main():
                     help="e2e: send the Canny map and the ground truth one BYTE per pixel (default: one bit per pixel, unpacked on the device)")
     ap.add_argument("--train-batch", type=int, default=16)
     ap.add_argument("--train-only", action="store_true", help="run the configs[3] training-step block alone and print its dict (what the full run starts as a child process)")
-    ap.add_argument("--train-timeout", type=int, default=240, help="seconds the training block's child process may take before it is stopped and reported unavailable")
+    ap.add_argument("--train-timeout", type=int, default=150, help="seconds the training block's child process may take before it is stopped and reported unavailable")
     ap.add_argument("--train-host-profile", action="store_true", help="training block: cProfile of the host side of 20 steps, to stderr")
     ap.add_argument("--train-all-kernels", action="store_true", help="training block: every timed scope as [count, ms] instead of the top eight")
     ap.add_argument("--train-inline-build", action="store_true",
